@@ -390,6 +390,18 @@ int cvprim_gaussian7x7_s2_u8(const unsigned char* src, int w, int h, int sstep, 
     return 0;
 }
 
+// FAST-9/16 score of every pixel at least 3 from the border (0 where score < minTh), for tests
+void cvprim_fast_score_map(const unsigned char* img, int w, int h, int step, int minTh, unsigned char* out, int ostep) {
+    int off[16];
+    for (int k = 0; k < 16; k++) off[k] = cv::kCircle[k][0] + cv::kCircle[k][1] * step;
+    for (int y = 0; y < h; y++)
+        for (int x = 0; x < w; x++) {
+            int s = 0;
+            if (x >= 3 && y >= 3 && x < w - 3 && y < h - 3) s = cv::corner_score(img + (size_t)step * y + x, off);
+            out[(size_t)ostep * y + x] = (unsigned char)(s >= minTh ? s : 0);
+        }
+}
+
 void cvprim_fast_atan2(const float* y, const float* x, float* out, int n) {
     for (int i = 0; i < n; i++) out[i] = cv::fastAtan2(y[i], x[i]);
 }

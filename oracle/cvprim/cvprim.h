@@ -56,6 +56,7 @@ int cvprim_fast9_16(const unsigned char* img, int w, int h, int step, int thresh
                     int* xyr, int cap);
 int cvprim_gaussian7x7_s2_u8(const unsigned char* src, int w, int h, int sstep,
                              unsigned char* dst, int dstep);
+void cvprim_fast_score_map(const unsigned char* img, int w, int h, int step, int minTh, unsigned char* out, int ostep);
 void cvprim_fast_atan2(const float* y, const float* x, float* out, int n);
 }
 

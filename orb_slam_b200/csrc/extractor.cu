@@ -1,0 +1,587 @@
+// Host side of the B200 ORB extractor: geometry, workspaces, launch sequence
+// and the extern "C" entry points of include/orbx.h.  No CPU fallback: every
+// compute step is one of the kernels in this directory.
+#include <cuda_runtime.h>
+
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <mutex>
+#include <vector>
+
+#include "../../include/orbx.h"
+#define ORB_PATTERN_QUAL static const
+#include "../../include/orb_pattern_31.h"
+#include "cells.cuh"
+#include "describe.cuh"
+#include "geom.h"
+#include "pyramid.cuh"
+#include "quadtree_kernel.cuh"
+
+using namespace orbx;
+
+#define CK(expr)                                                      \
+    do {                                                              \
+        cudaError_t e_ = (expr);                                      \
+        if (e_ != cudaSuccess) {                                      \
+            std::fprintf(stderr, "orbx: %s failed: %s (%s:%d)\n", #expr, cudaGetErrorString(e_), __FILE__, __LINE__); \
+            return (int)e_;                                           \
+        }                                                             \
+    } while (0)
+
+static inline int host_round_even(float v) { return (int)lrintf(v); }   // cvRound
+
+struct orbx_extractor {
+    int device = 0;
+    int nfeatures = 0, nlevels = 0, iniTh = 0, minTh = 0;
+    double scaleFactor = 0;                  // double member, reference include/ORBextractor.h:98
+    std::vector<float> sf, isf, sig2, isig2;
+    std::vector<int> nfeat;
+    int umax[ORB_HALF_PATCH + 1];
+    cudaStream_t stream = nullptr;
+    // geometry-dependent state
+    FrameGeom g{};
+    bool haveGeom = false;
+    int capFrames = 0;                       // frames the workspaces are sized for
+    int lastFrames = 0;
+    ResizeTap* d_tabs = nullptr;
+    uint8_t* d_in = nullptr; size_t inPitch = 0, inFrameStride = 0;
+    uint8_t *d_pyr = nullptr, *d_blur = nullptr, *d_score = nullptr;
+    uint32_t *d_cellCount = nullptr, *d_cellOffs = nullptr, *d_cand = nullptr;
+    uint32_t *d_keyA = nullptr, *d_keyB = nullptr, *d_valA = nullptr, *d_valB = nullptr, *d_sel = nullptr;
+    int *d_candCount = nullptr, *d_selCount = nullptr, *d_err = nullptr;
+    // result block (device + pinned host mirror): [n_out[frames]] [err] [kps] [desc]
+    uint8_t* d_res = nullptr; uint8_t* h_res = nullptr; size_t resBytes = 0;
+    uint8_t* h_in = nullptr; size_t hInBytes = 0;       // pinned staging for pageable inputs
+    int launches = 0;
+    std::mutex mtx;
+};
+
+// ---------------------------------------------------------------------------
+// constructor tables, reference src/ORBextractor.cc:466-540
+// ---------------------------------------------------------------------------
+static void init_tables(orbx_extractor* e) {
+    const int L = e->nlevels;
+    e->sf.assign(L, 0.f); e->isf.assign(L, 0.f); e->sig2.assign(L, 0.f); e->isig2.assign(L, 0.f);
+    e->sf[0] = 1.0f; e->sig2[0] = 1.0f;
+    for (int i = 1; i < L; i++) {
+        e->sf[i] = (float)(e->sf[i - 1] * e->scaleFactor);
+        e->sig2[i] = e->sf[i] * e->sf[i];
+    }
+    for (int i = 0; i < L; i++) { e->isf[i] = 1.0f / e->sf[i]; e->isig2[i] = 1.0f / e->sig2[i]; }
+    e->nfeat.assign(L, 0);
+    const float factor = (float)(1.0f / e->scaleFactor);
+    float nDesired = e->nfeatures * (1 - factor) / (1 - (float)std::pow((double)factor, (double)L));
+    int sum = 0;
+    for (int l = 0; l < L - 1; l++) {
+        e->nfeat[l] = host_round_even(nDesired);
+        sum += e->nfeat[l];
+        nDesired *= factor;
+    }
+    e->nfeat[L - 1] = std::max(e->nfeatures - sum, 0);
+    int v, v0;
+    const int vmax = (int)std::floor(ORB_HALF_PATCH * std::sqrt(2.f) / 2 + 1);
+    const int vmin = (int)std::ceil(ORB_HALF_PATCH * std::sqrt(2.f) / 2);
+    const double hp2 = ORB_HALF_PATCH * ORB_HALF_PATCH;
+    for (v = 0; v <= ORB_HALF_PATCH; v++) e->umax[v] = 0;
+    for (v = 0; v <= vmax; ++v) e->umax[v] = (int)lrint(std::sqrt(hp2 - v * v));
+    for (v = ORB_HALF_PATCH, v0 = 0; v >= vmin; --v) {
+        while (e->umax[v0] == e->umax[v0 + 1]) ++v0;
+        e->umax[v] = v0;
+        ++v0;
+    }
+}
+
+// INTER_LINEAR coefficient table of cv::resize for one axis (OpenCV 4.13
+// imgproc/resize.cpp, 8-bit fixed-point path; semantics in SURVEY §8(a) E2).
+static void resize_taps(int ssize, int dsize, bool clampFraction, std::vector<ResizeTap>& out) {
+    out.resize(dsize);
+    const double scale = 1. / ((double)dsize / ssize);
+    for (int d = 0; d < dsize; d++) {
+        float f = (float)((d + 0.5) * scale - 0.5);
+        int s = (int)std::floor(f);
+        f -= s;
+        if (clampFraction) {                   // x axis: weights collapse at the borders
+            if (s < 0) { f = 0; s = 0; }
+            if (s >= ssize - 1) { f = 0; s = ssize - 1; }
+        }
+        ResizeTap t;
+        int a0 = (int)lrintf((1.f - f) * 2048), a1 = (int)lrintf(f * 2048);
+        t.a0 = (short)a0; t.a1 = (short)a1;
+        int s0 = s, s1 = s + 1;                // y axis: row indices are clipped, weights kept
+        s0 = s0 < 0 ? 0 : (s0 >= ssize ? ssize - 1 : s0);
+        s1 = s1 < 0 ? 0 : (s1 >= ssize ? ssize - 1 : s1);
+        t.s0 = s0; t.s1 = s1;
+        out[d] = t;
+    }
+}
+
+static int ceil_log2(int v) { int b = 0; while ((1 << b) < v) b++; return b; }
+
+// all sizes for a width x height frame; returns ORBX_E_UNSUPPORTED outside the contract
+static int build_geometry(orbx_extractor* e, int width, int height, FrameGeom& g, std::vector<ResizeTap>& tabs) {
+    std::memset(&g, 0, sizeof(g));
+    const int L = e->nlevels;
+    g.nlevels = L; g.width = width; g.height = height; g.iniTh = e->iniTh; g.minTh = e->minTh;
+    tabs.clear();
+    unsigned long long pyrOff = 0, planeOff = 0, candOff = 0;
+    int cellOff = 0, selOff = 0, nodeNeed = 8;
+    for (int l = 0; l < L; l++) {
+        LevelGeom& v = g.lv[l];
+        v.w = host_round_even((float)width * e->isf[l]);          // :1348
+        v.h = host_round_even((float)height * e->isf[l]);
+        if (v.w < 8 || v.h < 8) return ORBX_E_UNSUPPORTED;
+        if (v.w - 32 > 4095 || v.h - 32 > 4095) return ORBX_E_UNSUPPORTED;   // 12-bit packed coordinates
+        v.pitch = ((ORB_XPAD + ((v.w + 15) & ~15) + 32) + 127) & ~127;
+        v.prow0 = ORB_EDGE;
+        v.pyrOff = pyrOff; pyrOff += (unsigned long long)v.pitch * (v.h + 2 * ORB_EDGE);
+        v.planeOff = planeOff; planeOff += (unsigned long long)v.pitch * v.h;
+        if (l > 0) {
+            const LevelGeom& p = g.lv[l - 1];
+            const double sx = 1. / ((double)v.w / p.w), sy = 1. / ((double)v.h / p.h);
+            if (std::fabs(sx - 2) < 1e-12 && std::fabs(sy - 2) < 1e-12) return ORBX_E_UNSUPPORTED;   // cv::resize switches to INTER_AREA
+            if (sx < 1.0 || sy < 1.0 || sx > 4.0 || sy > 4.0) return ORBX_E_UNSUPPORTED;
+            std::vector<ResizeTap> tx, ty;
+            resize_taps(p.w, v.w, true, tx);
+            resize_taps(p.h, v.h, false, ty);
+            v.xtabOff = (int)tabs.size(); tabs.insert(tabs.end(), tx.begin(), tx.end());
+            v.ytabOff = (int)tabs.size(); tabs.insert(tabs.end(), ty.begin(), ty.end());
+        }
+        // cell grid, :932-949 (float arithmetic as in the reference)
+        v.maxBorderX = v.w - ORB_BORDER_MIN; v.maxBorderY = v.h - ORB_BORDER_MIN;
+        const float fw = (float)(v.maxBorderX - ORB_BORDER_MIN), fh = (float)(v.maxBorderY - ORB_BORDER_MIN);
+        v.nCols = (int)(fw / 30.f); v.nRows = (int)(fh / 30.f);
+        if (v.nCols <= 0 || v.nRows <= 0) { v.nCols = v.nRows = 0; v.wCell = v.hCell = 1; }   // level too small: no candidates
+        else { v.wCell = (int)std::ceil(fw / v.nCols); v.hCell = (int)std::ceil(fh / v.nRows); }
+        v.cellOff = cellOff; cellOff += v.nCols * v.nRows;
+        // worst case of in-cell NMS survivors: one per 2x2 block of every cell interior
+        long cap = 0;
+        for (int i = 0; i < v.nRows; i++)
+            for (int j = 0; j < v.nCols; j++) {
+                const int iniY = ORB_BORDER_MIN + i * v.hCell, iniX = ORB_BORDER_MIN + j * v.wCell;
+                if (iniY >= v.maxBorderY - 3 || iniX >= v.maxBorderX - 6) continue;
+                const int my = std::min(iniY + v.hCell + 6, v.maxBorderY), mx = std::min(iniX + v.wCell + 6, v.maxBorderX);
+                const int iw = mx - iniX - 6, ih = my - iniY - 6;
+                if (iw > 0 && ih > 0) cap += (long)((iw + 1) / 2) * ((ih + 1) / 2);
+            }
+        v.candCap = (int)((cap + 31) & ~31L);
+        if (v.candCap >= (1 << 24)) return ORBX_E_UNSUPPORTED;
+        v.candOff = candOff; candOff += v.candCap;
+        // quadtree, :650-653
+        v.qW = v.maxBorderX - ORB_BORDER_MIN; v.qH = v.maxBorderY - ORB_BORDER_MIN;
+        v.N = e->nfeat[l];
+        v.nIni = v.qH > 0 ? (int)std::round((float)v.qW / v.qH) : 0;
+        if (v.nCols > 0 && v.nIni <= 0) return ORBX_E_UNSUPPORTED;      // reference divides by zero (:653)
+        if (v.nIni <= 0) v.nIni = 1;
+        v.hX = (float)v.qW / v.nIni;
+        const int nodeW = (int)std::ceil(v.hX) + 2;
+        v.depth = ceil_log2(std::max(std::max(nodeW, v.qH), 2)) + 1;
+        v.iniBits = ceil_log2(v.nIni);
+        if (2 * v.depth + v.iniBits > 32) return ORBX_E_UNSUPPORTED;
+        v.maxSel = std::max(v.N + 3, 4 * v.nIni);
+        v.selOff = selOff; selOff += v.maxSel;
+        nodeNeed = std::max(nodeNeed, v.maxSel + 4);
+        v.scale = e->sf[l];
+        v.patchSize = (float)(int)(31 * e->sf[l]);                       // :1013
+    }
+    g.totalCells = cellOff; g.selTotal = selOff;
+    g.pyrBytes = (pyrOff + 255) & ~255ULL; g.planeBytes = (planeOff + 255) & ~255ULL;
+    g.candTotal = (candOff + 63) & ~63ULL;
+    g.nodeCap = 1 << ceil_log2(nodeNeed);
+    if (qt_smem_bytes(g.nodeCap) > 200 * 1024) return ORBX_E_UNSUPPORTED;
+    return ORBX_OK;
+}
+
+// ---------------------------------------------------------------------------
+// workspaces
+// ---------------------------------------------------------------------------
+static void free_workspace(orbx_extractor* e) {
+    cudaFree(e->d_tabs); cudaFree(e->d_in); cudaFree(e->d_pyr); cudaFree(e->d_blur); cudaFree(e->d_score);
+    cudaFree(e->d_cellCount); cudaFree(e->d_cellOffs); cudaFree(e->d_cand);
+    cudaFree(e->d_keyA); cudaFree(e->d_keyB); cudaFree(e->d_valA); cudaFree(e->d_valB); cudaFree(e->d_sel);
+    cudaFree(e->d_candCount); cudaFree(e->d_selCount); cudaFree(e->d_res);
+    if (e->h_res) cudaFreeHost(e->h_res);
+    e->d_tabs = nullptr; e->d_in = e->d_pyr = e->d_blur = e->d_score = nullptr;
+    e->d_cellCount = e->d_cellOffs = e->d_cand = e->d_keyA = e->d_keyB = e->d_valA = e->d_valB = e->d_sel = nullptr;
+    e->d_candCount = e->d_selCount = nullptr; e->d_res = nullptr; e->h_res = nullptr;
+    e->capFrames = 0; e->haveGeom = false;
+}
+
+static size_t res_bytes(const FrameGeom& g, int frames) {
+    // [n_out: frames ints][err: 1 int][pad to 64][keypoints][descriptors]
+    size_t head = ((size_t)(frames + 1) * 4 + 63) & ~(size_t)63;
+    return head + (size_t)frames * g.selTotal * (sizeof(orbx_keypoint) + 32);
+}
+static size_t res_head(int frames) { return ((size_t)(frames + 1) * 4 + 63) & ~(size_t)63; }
+
+static int ensure_workspace(orbx_extractor* e, int width, int height, int frames, bool needInput) {
+    if (e->haveGeom && e->g.width == width && e->g.height == height && frames <= e->capFrames &&
+        (!needInput || e->d_in))
+        return ORBX_OK;
+    const bool sameGeom = e->haveGeom && e->g.width == width && e->g.height == height;
+    const int newCap = sameGeom ? std::max(frames, e->capFrames) : frames;
+    FrameGeom g;
+    std::vector<ResizeTap> tabs;
+    int rc = build_geometry(e, width, height, g, tabs);
+    if (rc != ORBX_OK) return rc;
+    CK(cudaStreamSynchronize(e->stream));
+    const bool hadInput = e->d_in != nullptr;
+    free_workspace(e);
+    e->g = g;
+    const size_t F = (size_t)newCap;
+    CK(cudaMalloc(&e->d_tabs, std::max<size_t>(tabs.size(), 1) * sizeof(ResizeTap)));
+    if (!tabs.empty()) CK(cudaMemcpy(e->d_tabs, tabs.data(), tabs.size() * sizeof(ResizeTap), cudaMemcpyHostToDevice));
+    if (needInput || hadInput) {
+        e->inPitch = ((size_t)width + 127) & ~(size_t)127;
+        e->inFrameStride = e->inPitch * height;
+        CK(cudaMalloc(&e->d_in, e->inFrameStride * F));
+    }
+    CK(cudaMalloc(&e->d_pyr, g.pyrBytes * F));
+    CK(cudaMalloc(&e->d_blur, g.planeBytes * F));
+    CK(cudaMalloc(&e->d_score, g.planeBytes * F));
+    CK(cudaMemset(e->d_pyr, 0, g.pyrBytes * F));
+    const size_t cells = (size_t)std::max(g.totalCells, 1) * F;
+    CK(cudaMalloc(&e->d_cellCount, cells * 4));
+    CK(cudaMalloc(&e->d_cellOffs, cells * 4));
+    const size_t cands = (size_t)std::max<unsigned long long>(g.candTotal, 64) * F;
+    CK(cudaMalloc(&e->d_cand, cands * 4));
+    CK(cudaMalloc(&e->d_keyA, cands * 4)); CK(cudaMalloc(&e->d_keyB, cands * 4));
+    CK(cudaMalloc(&e->d_valA, cands * 4)); CK(cudaMalloc(&e->d_valB, cands * 4));
+    CK(cudaMalloc(&e->d_sel, (size_t)g.selTotal * F * 4));
+    CK(cudaMalloc(&e->d_candCount, F * g.nlevels * 4));
+    CK(cudaMalloc(&e->d_selCount, F * g.nlevels * 4));
+    e->resBytes = res_bytes(g, newCap);
+    CK(cudaMalloc(&e->d_res, e->resBytes));
+    CK(cudaMallocHost(&e->h_res, e->resBytes));
+    e->capFrames = newCap;
+    e->haveGeom = true;
+    // kernel attributes
+    CK(cudaFuncSetAttribute(quadtree_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)qt_smem_bytes(g.nodeCap)));
+    CK(cudaFuncSetAttribute(pyr_level_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
+    return ORBX_OK;
+}
+
+static void pyr_smem_for(const LevelGeom& prev, const LevelGeom& cur, int& cols, int& rows, size_t& bytes) {
+    const double sx = (double)prev.w / cur.w, sy = (double)prev.h / cur.h;
+    cols = (((int)std::ceil((TW + 2 * HALO) * sx) + 3 + 16 + 16) + 15) & ~15;
+    rows = (int)std::ceil((TH + 2 * HALO) * sy) + 4;
+    size_t stage = std::max((size_t)cols * rows, (size_t)TH * TW);
+    bytes = (size_t)TROWS * TS + (size_t)TROWS * TW * 2 + stage;
+}
+
+// Enqueue the whole pipeline for `frames` frames whose level-0 source is (src, pitch, frameStride).
+static int enqueue_pipeline(orbx_extractor* e, const uint8_t* src, size_t srcPitch, size_t srcFrameStride, int frames,
+                            orbx_keypoint* d_kps, uint8_t* d_desc, int cap, int* d_nOut, int* d_err) {
+    const FrameGeom& g = e->g;
+    cudaStream_t st = e->stream;
+    int launches = 0;
+    CK(cudaMemsetAsync(d_err, 0, sizeof(int), st));
+    // 1. pyramid + blur + FAST score, level by level (level l reads level l-1)
+    for (int l = 0; l < g.nlevels; l++) {
+        const LevelGeom& v = g.lv[l];
+        PyrArgs a{};
+        a.pyr = e->d_pyr + v.pyrOff; a.pyrFrameStride = g.pyrBytes;
+        a.blur = e->d_blur + v.planeOff; a.score = e->d_score + v.planeOff; a.planeFrameStride = g.planeBytes;
+        a.pitch = v.pitch; a.w = v.w; a.h = v.h; a.minTh = g.minTh; a.err = d_err;
+        dim3 grid((v.w + TW - 1) / TW, (v.h + TH - 1) / TH, frames);
+        if (l == 0) {
+            a.src = src; a.srcFrameStride = srcFrameStride; a.srcPitch = (int)srcPitch; a.srcX0 = 0;
+            a.sw = v.w; a.sh = v.h;
+            const size_t smem = (size_t)TROWS * TS + (size_t)TROWS * TW * 2 + (size_t)TH * TW;
+            pyr_level_kernel<true><<<grid, PYR_THREADS, smem, st>>>(a);
+        } else {
+            const LevelGeom& p = g.lv[l - 1];
+            a.src = e->d_pyr + p.pyrOff + (size_t)ORB_EDGE * p.pitch; a.srcFrameStride = g.pyrBytes;
+            a.srcPitch = p.pitch; a.srcX0 = ORB_XPAD; a.sw = p.w; a.sh = p.h;
+            a.xtab = e->d_tabs + v.xtabOff; a.ytab = e->d_tabs + v.ytabOff;
+            size_t smem;
+            pyr_smem_for(p, v, a.srcTileCols, a.srcTileRows, smem);
+            pyr_level_kernel<false><<<grid, PYR_THREADS, smem, st>>>(a);
+        }
+        launches++;
+    }
+    // 2. REFLECT_101 frames
+    {
+        BorderArgs b{};
+        b.pyr = e->d_pyr; b.pyrFrameStride = g.pyrBytes; b.nlevels = g.nlevels;
+        int off = 0;
+        for (int l = 0; l < g.nlevels; l++) {
+            const LevelGeom& v = g.lv[l];
+            b.itemOff[l] = off;
+            off += (v.w + 2 * ORB_EDGE) * (v.h + 2 * ORB_EDGE) - v.w * v.h;
+            b.pyrOff[l] = v.pyrOff; b.w[l] = v.w; b.h[l] = v.h; b.pitch[l] = v.pitch;
+        }
+        b.itemOff[g.nlevels] = off;
+        border_kernel<<<dim3((off + 255) / 256, frames), 256, 0, st>>>(b);
+        launches++;
+    }
+    // 3. per-cell NMS + threshold fallback -> ordered candidate lists
+    CellArgs c{};
+    c.score = e->d_score; c.planeFrameStride = g.planeBytes; c.nlevels = g.nlevels; c.iniTh = g.iniTh;
+    c.totalCells = g.totalCells;
+    for (int l = 0; l < g.nlevels; l++) {
+        const LevelGeom& v = g.lv[l];
+        c.cellOff[l] = v.cellOff; c.nCols[l] = std::max(v.nCols, 1); c.wCell[l] = v.wCell; c.hCell[l] = v.hCell;
+        c.maxBX[l] = v.maxBorderX; c.maxBY[l] = v.maxBorderY; c.pitch[l] = v.pitch;
+        c.planeOff[l] = v.planeOff; c.candOff[l] = v.candOff; c.candCap[l] = v.candCap;
+    }
+    c.cellOff[g.nlevels] = g.totalCells;
+    c.candFrameStride = g.candTotal;
+    c.cellCount = e->d_cellCount; c.cellOffs = e->d_cellOffs; c.cand = e->d_cand; c.candCount = e->d_candCount;
+    if (g.totalCells > 0) {
+        dim3 cg((g.totalCells + 7) / 8, frames);
+        cell_kernel<false><<<cg, 256, 0, st>>>(c);
+        cell_scan_kernel<<<dim3(g.nlevels, frames), 256, 0, st>>>(c);
+        cell_kernel<true><<<cg, 256, 0, st>>>(c);
+        launches += 3;
+    } else {
+        CK(cudaMemsetAsync(e->d_candCount, 0, (size_t)frames * g.nlevels * 4, st));
+    }
+    // 4. quadtree distribution
+    QtArgs q{};
+    q.cand = e->d_cand; q.candFrameStride = g.candTotal; q.candCount = e->d_candCount;
+    q.keyA = e->d_keyA; q.keyB = e->d_keyB; q.valA = e->d_valA; q.valB = e->d_valB;
+    q.sel = e->d_sel; q.selCount = e->d_selCount; q.err = d_err;
+    q.nlevels = g.nlevels; q.selTotal = g.selTotal; q.nodeCap = g.nodeCap;
+    for (int l = 0; l < g.nlevels; l++) {
+        const LevelGeom& v = g.lv[l];
+        q.candOff[l] = v.candOff; q.N[l] = v.N; q.nIni[l] = v.nIni; q.qH[l] = v.qH; q.depth[l] = v.depth;
+        q.maxSel[l] = v.maxSel; q.selOff[l] = v.selOff; q.hX[l] = v.hX;
+    }
+    quadtree_kernel<<<dim3(g.nlevels, frames), QT_THREADS, qt_smem_bytes(g.nodeCap), st>>>(q);
+    launches++;
+    // 5. orientation, descriptors, output assembly
+    DescArgs d{};
+    d.pyr = e->d_pyr; d.pyrFrameStride = g.pyrBytes; d.blur = e->d_blur; d.planeFrameStride = g.planeBytes;
+    d.sel = e->d_sel; d.selCount = e->d_selCount; d.kps = d_kps; d.desc = d_desc; d.nOut = d_nOut;
+    d.cap = cap; d.nlevels = g.nlevels; d.selTotal = g.selTotal;
+    for (int l = 0; l < g.nlevels; l++) {
+        const LevelGeom& v = g.lv[l];
+        d.selOff[l] = v.selOff; d.pitch[l] = v.pitch; d.pyrOff[l] = v.pyrOff; d.planeOff[l] = v.planeOff;
+        d.scale[l] = v.scale; d.patchSize[l] = v.patchSize;
+    }
+    d.selOff[g.nlevels] = g.selTotal;
+    describe_kernel<<<dim3((g.selTotal + 7) / 8, frames), 256, 0, st>>>(d);
+    launches++;
+    e->launches = launches;
+    e->lastFrames = frames;
+    CK(cudaGetLastError());
+    return ORBX_OK;
+}
+
+// ---------------------------------------------------------------------------
+// extern "C" entry points (include/orbx.h)
+// ---------------------------------------------------------------------------
+extern "C" {
+
+const char* orbx_error_string(int code) {
+    switch (code) {
+        case ORBX_OK: return "ok";
+        case ORBX_E_INVALID: return "invalid argument";
+        case ORBX_E_NO_DEVICE: return "no usable CUDA device (sm_100 required)";
+        case ORBX_E_CAPACITY: return "output capacity too small";
+        case ORBX_E_UNSUPPORTED: return "configuration outside the supported contract";
+        case ORBX_E_INTERNAL: return "device-side consistency check failed";
+        default: return code > 0 ? cudaGetErrorString((cudaError_t)code) : "unknown error";
+    }
+}
+
+int orbx_create(orbx_t** out, int nfeatures, float scaleFactor, int nlevels, int iniThFAST, int minThFAST, int device) {
+    if (!out || nfeatures < 0 || nlevels < 1 || nlevels > ORB_MAX_LEVELS || !(scaleFactor > 1.0f) ||
+        iniThFAST < minThFAST || minThFAST < 1 || iniThFAST > 255)
+        return ORBX_E_INVALID;
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || device < 0 || device >= ndev) return ORBX_E_NO_DEVICE;
+    cudaDeviceProp prop;
+    CK(cudaGetDeviceProperties(&prop, device));
+    if (prop.major != 10) return ORBX_E_NO_DEVICE;       // built for sm_100a only
+    CK(cudaSetDevice(device));
+    orbx_extractor* e = new orbx_extractor();
+    e->device = device; e->nfeatures = nfeatures; e->nlevels = nlevels; e->iniTh = iniThFAST; e->minTh = minThFAST;
+    e->scaleFactor = scaleFactor;
+    init_tables(e);
+    cudaError_t rc = cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking);
+    if (rc == cudaSuccess) rc = cudaMalloc(&e->d_err, 64);
+    if (rc == cudaSuccess) rc = cudaMemcpyToSymbol(c_pattern, orb_pattern_31, 1024);
+    if (rc == cudaSuccess) rc = cudaMemcpyToSymbol(c_umax, e->umax, sizeof(e->umax));
+    if (rc != cudaSuccess) { delete e; return (int)rc; }
+    *out = e;
+    return ORBX_OK;
+}
+
+void orbx_destroy(orbx_t* e) {
+    if (!e) return;
+    cudaSetDevice(e->device);
+    cudaStreamSynchronize(e->stream);
+    free_workspace(e);
+    cudaFree(e->d_err);
+    if (e->h_in) cudaFreeHost(e->h_in);
+    cudaStreamDestroy(e->stream);
+    delete e;
+}
+
+int orbx_levels(const orbx_t* e) { return e ? e->nlevels : 0; }
+
+int orbx_scale_tables(const orbx_t* e, float* sf, float* isf, float* sig2, float* isig2, int* nfeat) {
+    if (!e) return ORBX_E_INVALID;
+    for (int i = 0; i < e->nlevels; i++) {
+        if (sf) sf[i] = e->sf[i];
+        if (isf) isf[i] = e->isf[i];
+        if (sig2) sig2[i] = e->sig2[i];
+        if (isig2) isig2[i] = e->isig2[i];
+        if (nfeat) nfeat[i] = e->nfeat[i];
+    }
+    return ORBX_OK;
+}
+
+int orbx_max_keypoints(const orbx_t* ce, int width, int height) {
+    orbx_extractor* e = const_cast<orbx_extractor*>(ce);
+    if (!e) return ORBX_E_INVALID;
+    if (e->haveGeom && e->g.width == width && e->g.height == height) return e->g.selTotal;
+    FrameGeom g; std::vector<ResizeTap> tabs;
+    int rc = build_geometry(e, width, height, g, tabs);
+    return rc == ORBX_OK ? g.selTotal : rc;
+}
+
+void* orbx_stream(orbx_t* e) { return e ? (void*)e->stream : nullptr; }
+
+int orbx_synchronize(orbx_t* e) {
+    if (!e) return ORBX_E_INVALID;
+    CK(cudaSetDevice(e->device));
+    CK(cudaStreamSynchronize(e->stream));
+    int err = 0;
+    CK(cudaMemcpy(&err, e->d_err, sizeof(int), cudaMemcpyDeviceToHost));
+    if (err) { std::fprintf(stderr, "orbx: device consistency check %d failed\n", err); return ORBX_E_INTERNAL; }
+    return ORBX_OK;
+}
+
+int orbx_extract_batch_device(orbx_t* e, const uint8_t* d_images, int n, int width, int height, size_t step,
+                              size_t frame_stride, orbx_keypoint* d_keypoints, uint8_t* d_descriptors, int capacity,
+                              int* d_n_out) {
+    if (!e || !d_images || n <= 0 || width <= 0 || height <= 0 || step < (size_t)width || !d_keypoints ||
+        !d_descriptors || !d_n_out)
+        return ORBX_E_INVALID;
+    std::lock_guard<std::mutex> lk(e->mtx);
+    CK(cudaSetDevice(e->device));
+    int rc = ensure_workspace(e, width, height, n, false);
+    if (rc != ORBX_OK) return rc;
+    if (capacity < e->g.selTotal) return ORBX_E_CAPACITY;
+    return enqueue_pipeline(e, d_images, step, frame_stride, n, d_keypoints, d_descriptors, capacity, d_n_out, e->d_err);
+}
+
+int orbx_extract_batch(orbx_t* e, const uint8_t* const* images, int n, int width, int height, size_t step,
+                       orbx_keypoint* keypoints, uint8_t* descriptors, int capacity, int* n_out) {
+    if (!e || !images || n <= 0 || !keypoints || !descriptors || !n_out) return ORBX_E_INVALID;
+    if (width <= 0 || height <= 0) { for (int i = 0; i < n; i++) n_out[i] = -1; return ORBX_OK; }   // empty image, :1252
+    if (step < (size_t)width) return ORBX_E_INVALID;
+    std::lock_guard<std::mutex> lk(e->mtx);
+    CK(cudaSetDevice(e->device));
+    int rc = ensure_workspace(e, width, height, n, true);
+    if (rc != ORBX_OK) return rc;
+    const FrameGeom& g = e->g;
+    const int cap = g.selTotal;                 // device-side capacity: never overflows
+    // H2D: straight from the caller's buffer when it is page-locked, else through pinned staging
+    for (int i = 0; i < n; i++) {
+        if (!images[i]) return ORBX_E_INVALID;
+        cudaPointerAttributes at{};
+        const bool pinned = cudaPointerGetAttributes(&at, images[i]) == cudaSuccess && at.type == cudaMemoryTypeHost;
+        cudaGetLastError();
+        const uint8_t* srcp = images[i];
+        size_t srcStep = step;
+        if (!pinned) {
+            const size_t need = (size_t)n * width * height;
+            if (e->hInBytes < need) {
+                CK(cudaStreamSynchronize(e->stream));
+                if (e->h_in) cudaFreeHost(e->h_in);
+                e->h_in = nullptr; e->hInBytes = 0;
+                CK(cudaMallocHost(&e->h_in, need));
+                e->hInBytes = need;
+            }
+            uint8_t* dst = e->h_in + (size_t)i * width * height;
+            for (int y = 0; y < height; y++) std::memcpy(dst + (size_t)y * width, images[i] + (size_t)y * step, width);
+            srcp = dst; srcStep = width;
+        }
+        CK(cudaMemcpy2DAsync(e->d_in + (size_t)i * e->inFrameStride, e->inPitch, srcp, srcStep, width, height,
+                             cudaMemcpyHostToDevice, e->stream));
+    }
+    const size_t head = res_head(e->capFrames);
+    int* d_n = (int*)e->d_res;
+    int* d_err = d_n + e->capFrames;
+    orbx_keypoint* d_kps = (orbx_keypoint*)(e->d_res + head);
+    uint8_t* d_desc = e->d_res + head + (size_t)e->capFrames * cap * sizeof(orbx_keypoint);
+    rc = enqueue_pipeline(e, e->d_in, e->inPitch, e->inFrameStride, n, d_kps, d_desc, cap, d_n, d_err);
+    if (rc != ORBX_OK) return rc;
+    // D2H: header (counts + error flag), keypoints and descriptors of the n frames
+    CK(cudaMemcpyAsync(e->h_res, e->d_res, head, cudaMemcpyDeviceToHost, e->stream));
+    CK(cudaMemcpyAsync(e->h_res + head, d_kps, (size_t)n * cap * sizeof(orbx_keypoint), cudaMemcpyDeviceToHost, e->stream));
+    uint8_t* h_desc = e->h_res + head + (size_t)e->capFrames * cap * sizeof(orbx_keypoint);
+    CK(cudaMemcpyAsync(h_desc, d_desc, (size_t)n * cap * 32, cudaMemcpyDeviceToHost, e->stream));
+    CK(cudaStreamSynchronize(e->stream));
+    const int* h_n = (const int*)e->h_res;
+    if (h_n[e->capFrames] != 0) {
+        std::fprintf(stderr, "orbx: device consistency check %d failed\n", h_n[e->capFrames]);
+        return ORBX_E_INTERNAL;
+    }
+    const orbx_keypoint* h_kps = (const orbx_keypoint*)(e->h_res + head);
+    for (int i = 0; i < n; i++) {
+        const int k = h_n[i];
+        n_out[i] = k;
+        if (k > capacity) return ORBX_E_CAPACITY;
+        std::memcpy(keypoints + (size_t)i * capacity, h_kps + (size_t)i * cap, (size_t)k * sizeof(orbx_keypoint));
+        std::memcpy(descriptors + (size_t)i * capacity * 32, h_desc + (size_t)i * cap * 32, (size_t)k * 32);
+    }
+    return ORBX_OK;
+}
+
+int orbx_extract(orbx_t* e, const uint8_t* image, int width, int height, size_t step, orbx_keypoint* keypoints,
+                 uint8_t* descriptors, int capacity, int* n_out) {
+    if (!n_out) return ORBX_E_INVALID;
+    if (!image || width <= 0 || height <= 0) { *n_out = -1; return ORBX_OK; }
+    const uint8_t* imgs[1] = {image};
+    return orbx_extract_batch(e, imgs, 1, width, height, step, keypoints, descriptors, capacity, n_out);
+}
+
+int orbx_level_size(const orbx_t* e, int level, int* width, int* height) {
+    if (!e || !e->haveGeom || level < 0 || level >= e->nlevels) return ORBX_E_INVALID;
+    if (width) *width = e->g.lv[level].w;
+    if (height) *height = e->g.lv[level].h;
+    return ORBX_OK;
+}
+
+int orbx_get_level(orbx_t* e, int frame, int level, int border, int blurred, uint8_t* dst, size_t dst_step) {
+    if (!e || !e->haveGeom || level < 0 || level >= e->nlevels || frame < 0 || frame >= e->lastFrames || !dst ||
+        border < 0 || border > ORB_EDGE || (blurred && border) || blurred < 0 || blurred > 2)
+        return ORBX_E_INVALID;
+    std::lock_guard<std::mutex> lk(e->mtx);
+    CK(cudaSetDevice(e->device));
+    const LevelGeom& v = e->g.lv[level];
+    const uint8_t* src;
+    if (blurred) src = (blurred == 2 ? e->d_score : e->d_blur) + (size_t)frame * e->g.planeBytes + v.planeOff + ORB_XPAD;
+    else src = e->d_pyr + (size_t)frame * e->g.pyrBytes + v.pyrOff + (size_t)(ORB_EDGE - border) * v.pitch + ORB_XPAD - border;
+    CK(cudaMemcpy2DAsync(dst, dst_step, src, v.pitch, v.w + 2 * border, v.h + 2 * border, cudaMemcpyDeviceToHost, e->stream));
+    CK(cudaStreamSynchronize(e->stream));
+    return ORBX_OK;
+}
+
+int orbx_get_candidates(orbx_t* e, int frame, int level, int32_t* xyr, int capacity, int* n_out) {
+    if (!e || !e->haveGeom || level < 0 || level >= e->nlevels || frame < 0 || frame >= e->lastFrames || !n_out)
+        return ORBX_E_INVALID;
+    std::lock_guard<std::mutex> lk(e->mtx);
+    CK(cudaSetDevice(e->device));
+    CK(cudaStreamSynchronize(e->stream));
+    int n = 0;
+    CK(cudaMemcpy(&n, e->d_candCount + frame * e->nlevels + level, sizeof(int), cudaMemcpyDeviceToHost));
+    *n_out = n;
+    if (!xyr || n == 0) return ORBX_OK;
+    std::vector<uint32_t> tmp(n);
+    CK(cudaMemcpy(tmp.data(), e->d_cand + (size_t)frame * e->g.candTotal + e->g.lv[level].candOff, (size_t)n * 4,
+                  cudaMemcpyDeviceToHost));
+    for (int i = 0; i < n && i < capacity; i++) {
+        xyr[3 * i] = (int)(tmp[i] & 0xfff); xyr[3 * i + 1] = (int)((tmp[i] >> 12) & 0xfff); xyr[3 * i + 2] = (int)(tmp[i] >> 24);
+    }
+    return ORBX_OK;
+}
+
+int orbx_launches_per_call(const orbx_t* e) { return e ? e->launches : 0; }
+
+}  // extern "C"

@@ -1,0 +1,147 @@
+// DistributeOctTree (reference src/ORBextractor.cc:644-907, DivideNode :569-629)
+// as one thread block per (frame, level).
+//
+// B200 formulation.  The reference moves keypoints between std::list nodes; a
+// node's membership, however, depends only on the keypoint's coordinates and on
+// the (deterministic) ceil-halving of the initial boxes.  So every candidate
+// gets a PATH CODE - initial node index followed by one 2-bit child digit per
+// subdivision depth (n1=0 UL, n2=1 UR, n3=2 BL, n4=3 BR, decided by the very
+// comparisons of :603-617) - the candidates are radix-sorted by that code once,
+// and from then on every node of the tree is a contiguous range of the sorted
+// array: splitting a node is three binary searches, no data moves.  The list
+// itself (front-to-back order, push_front of children, erase of parents, the
+// breadth passes and the "largest node first" passes with their early exit) is
+// replayed exactly on ranges, with block-wide scans replacing the sequential
+// walk.  Ties between equal-size nodes follow the canonical rule of SURVEY
+// §8(a) E4: newest node first (the reference orders them by heap address).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include "geom.h"
+
+namespace orbx {
+
+constexpr int QT_THREADS = 512;
+constexpr int QT_WARPS = QT_THREADS / 32;
+
+struct QtArgs {
+    const uint32_t* cand;            // packed x:12|y:12|score:8, [frames][candTotal]
+    unsigned long long candFrameStride;
+    const int* candCount;            // [frames][nlevels]
+    uint32_t* keyA; uint32_t* keyB;  // sort ping-pong, same layout as cand
+    uint32_t* valA; uint32_t* valB;
+    uint32_t* sel;                   // [frames][selTotal] retained candidates, packed like cand
+    int* selCount;                   // [frames][nlevels]
+    int* err;                        // device error flag
+    int nlevels, selTotal, nodeCap;
+    unsigned long long candOff[ORB_MAX_LEVELS];
+    int N[ORB_MAX_LEVELS], nIni[ORB_MAX_LEVELS], qH[ORB_MAX_LEVELS], depth[ORB_MAX_LEVELS];
+    int maxSel[ORB_MAX_LEVELS], selOff[ORB_MAX_LEVELS];
+    float hX[ORB_MAX_LEVELS];
+};
+
+// exclusive scan of arr[0..n) in shared memory by the whole block; returns the total
+__device__ int block_scan_excl(int* arr, int n, int* warpTmp) {
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    const int per = (n + QT_THREADS - 1) / QT_THREADS;
+    const int b = min(tid * per, n), e = min(b + per, n);
+    int s = 0;
+    for (int i = b; i < e; i++) s += arr[i];
+    int inc = s;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        const int t = __shfl_up_sync(0xffffffffu, inc, d);
+        if (lane >= d) inc += t;
+    }
+    __syncthreads();                       // protects warpTmp reuse across calls
+    if (lane == 31) warpTmp[wid] = inc;
+    __syncthreads();
+    int base = 0, total = 0;
+    for (int k = 0; k < QT_WARPS; k++) { const int v = warpTmp[k]; if (k < wid) base += v; total += v; }
+    int run = base + inc - s;
+    for (int i = b; i < e; i++) { const int v = arr[i]; arr[i] = run; run += v; }
+    __syncthreads();
+    return total;
+}
+
+// first index in [lo,hi) whose 2-bit digit at `shift` is >= q (digits are non-decreasing inside a node)
+__device__ __forceinline__ uint32_t digit_lower_bound(const uint32_t* keys, uint32_t lo, uint32_t hi, int shift, uint32_t q) {
+    while (lo < hi) {
+        const uint32_t mid = (lo + hi) >> 1;
+        if (((keys[mid] >> shift) & 3u) >= q) hi = mid; else lo = mid + 1;
+    }
+    return lo;
+}
+__device__ __forceinline__ uint32_t key_lower_bound(const uint32_t* keys, uint32_t n, uint32_t v) {
+    uint32_t lo = 0, hi = n;
+    while (lo < hi) {
+        const uint32_t mid = (lo + hi) >> 1;
+        if (keys[mid] >= v) hi = mid; else lo = mid + 1;
+    }
+    return lo;
+}
+
+// path code of one candidate: replays DivideNode's box arithmetic from the initial node down
+__device__ __forceinline__ uint32_t path_code(int x, int y, float hX, int nIni, int qH, int depth) {
+    int ini = (int)__fdiv_rn((float)x, hX);                    // vpIniNodes[kp.pt.x/hX], :682
+    ini = min(ini, nIni - 1);
+    int ulx = (int)__fmul_rn(hX, (float)ini), urx = (int)__fmul_rn(hX, (float)(ini + 1));   // :667-668
+    int uly = 0, bry = qH;
+    uint32_t code = (uint32_t)ini;
+    for (int t = 0; t < depth; t++) {
+        const int midX = ulx + ((urx - ulx + 1) >> 1);           // ceil((UR.x-UL.x)/2), :572
+        const int midY = uly + ((bry - uly + 1) >> 1);
+        uint32_t q;
+        if (x < midX) { urx = midX; q = 0; } else { ulx = midX; q = 1; }
+        if (y < midY) { bry = midY; } else { uly = midY; q |= 2; }
+        code = (code << 2) | q;
+    }
+    return code;
+}
+
+// stable LSD radix sort of (key,val) pairs by `bits` low bits of key; returns 0 if the result is in A, 1 if in B
+__device__ int block_radix_sort(uint32_t* kA, uint32_t* vA, uint32_t* kB, uint32_t* vB, int M, int bits, uint32_t* hist /*256*QT_WARPS*/, int* warpTmp) {
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    const int per = (((M + QT_WARPS - 1) / QT_WARPS) + 31) & ~31;
+    const int wb = min(wid * per, M), we = min(wb + per, M);
+    int which = 0;
+    for (int shift = 0; shift < bits; shift += 8) {
+        const uint32_t* ki = which ? kB : kA; const uint32_t* vi = which ? vB : vA;
+        uint32_t* ko = which ? kA : kB; uint32_t* vo = which ? vA : vB;
+        for (int i = tid; i < 256 * QT_WARPS; i += QT_THREADS) hist[i] = 0;
+        __syncthreads();
+        for (int base = wb; base < we; base += 32) {
+            const int i = base + lane;
+            const bool valid = i < we;
+            const unsigned act = __ballot_sync(0xffffffffu, valid);
+            if (valid) {
+                const uint32_t d = (ki[i] >> shift) & 255u;
+                const unsigned peers = __match_any_sync(act, d);
+                if (lane == __ffs(peers) - 1) hist[d * QT_WARPS + wid] += __popc(peers);
+            }
+            __syncwarp();
+        }
+        __syncthreads();
+        block_scan_excl((int*)hist, 256 * QT_WARPS, warpTmp);
+        for (int base = wb; base < we; base += 32) {
+            const int i = base + lane;
+            const bool valid = i < we;
+            const unsigned act = __ballot_sync(0xffffffffu, valid);
+            if (valid) {
+                const uint32_t k = ki[i], v = vi[i];
+                const uint32_t d = (k >> shift) & 255u;
+                const unsigned peers = __match_any_sync(act, d);
+                const uint32_t pos = hist[d * QT_WARPS + wid] + __popc(peers & ((1u << lane) - 1));
+                ko[pos] = k; vo[pos] = v;
+                __syncwarp(act);
+                if (lane == __ffs(peers) - 1) hist[d * QT_WARPS + wid] += __popc(peers);
+            }
+            __syncwarp();
+        }
+        __syncthreads();
+        which ^= 1;
+    }
+    return which;
+}
+
+}  // namespace orbx

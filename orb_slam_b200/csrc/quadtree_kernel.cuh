@@ -1,0 +1,241 @@
+// quadtree_kernel: see quadtree.cuh for the formulation.
+#pragma once
+#include "quadtree.cuh"
+
+namespace orbx {
+
+struct QtSmem {
+    uint32_t* lo[2]; uint32_t* hi[2]; uint8_t* dep[2];
+    uint32_t* b1; uint32_t* b2; uint32_t* b3;
+    int* sA; int* sB; int* sC;
+    unsigned long long* skey;
+    uint32_t* hist;
+    int* warpTmp;
+    int* misc;       // [0]=nToExpand [1]=minT [2]=ne counter
+};
+
+__host__ __device__ inline size_t qt_smem_bytes(int cap) {
+    // lo,hi x2 (16B/node) + dep x2 (2B) + b1..b3 (12B) + sA..sC (12B) + skey (8B) = 50B/node
+    return (size_t)cap * 52 + 256 * QT_WARPS * 4 + QT_WARPS * 4 + 64;
+}
+
+// children of node (lo,hi,dep): boundaries by digit; returns number of non-empty children, ne = those with >1 key
+__device__ __forceinline__ int split_node(const uint32_t* keys, uint32_t lo, uint32_t hi, int dep, int depth,
+                                          uint32_t& c1, uint32_t& c2, uint32_t& c3, int& ne) {
+    const int shift = 2 * (depth - 1 - dep);
+    c1 = digit_lower_bound(keys, lo, hi, shift, 1);
+    c2 = digit_lower_bound(keys, c1, hi, shift, 2);
+    c3 = digit_lower_bound(keys, c2, hi, shift, 3);
+    const uint32_t n1 = c1 - lo, n2 = c2 - c1, n3 = c3 - c2, n4 = hi - c3;
+    ne = (n1 > 1) + (n2 > 1) + (n3 > 1) + (n4 > 1);
+    return (n1 > 0) + (n2 > 0) + (n3 > 0) + (n4 > 0);
+}
+
+// writes the non-empty children of a node in push order n1..n4; push index p0.. ; list position = totalPushed-1-p
+__device__ __forceinline__ void emit_children(uint32_t* nlo, uint32_t* nhi, uint8_t* ndep, uint32_t lo, uint32_t c1,
+                                              uint32_t c2, uint32_t c3, uint32_t hi, int dep, int p0, int totalPushed) {
+    const uint32_t bnd[5] = {lo, c1, c2, c3, hi};
+    int p = p0;
+#pragma unroll
+    for (int q = 0; q < 4; q++)
+        if (bnd[q + 1] > bnd[q]) {
+            const int pos = totalPushed - 1 - p;
+            nlo[pos] = bnd[q]; nhi[pos] = bnd[q + 1]; ndep[pos] = (uint8_t)(dep + 1);
+            p++;
+        }
+}
+
+__global__ void __launch_bounds__(QT_THREADS) quadtree_kernel(QtArgs a) {
+    extern __shared__ __align__(16) uint8_t qsm[];
+    const int tid = threadIdx.x;
+    const int l = blockIdx.x, frame = blockIdx.y;
+    const int cap = a.nodeCap;
+    QtSmem s;
+    {
+        uint8_t* p = qsm;
+        s.skey = (unsigned long long*)p; p += (size_t)cap * 8;
+        s.lo[0] = (uint32_t*)p; p += (size_t)cap * 4; s.lo[1] = (uint32_t*)p; p += (size_t)cap * 4;
+        s.hi[0] = (uint32_t*)p; p += (size_t)cap * 4; s.hi[1] = (uint32_t*)p; p += (size_t)cap * 4;
+        s.b1 = (uint32_t*)p; p += (size_t)cap * 4; s.b2 = (uint32_t*)p; p += (size_t)cap * 4; s.b3 = (uint32_t*)p; p += (size_t)cap * 4;
+        s.sA = (int*)p; p += (size_t)cap * 4; s.sB = (int*)p; p += (size_t)cap * 4; s.sC = (int*)p; p += (size_t)cap * 4;
+        s.hist = (uint32_t*)p; p += 256 * QT_WARPS * 4;
+        s.warpTmp = (int*)p; p += QT_WARPS * 4;
+        s.misc = (int*)p; p += 64;
+        s.dep[0] = p; p += cap; s.dep[1] = p;
+    }
+    const int M = a.candCount[frame * a.nlevels + l];
+    int* selCount = a.selCount + frame * a.nlevels + l;
+    if (M <= 0) { if (tid == 0) *selCount = 0; return; }
+    const int depth = a.depth[l], N = a.N[l], nIni = a.nIni[l];
+    const size_t off = (size_t)frame * a.candFrameStride + a.candOff[l];
+    const uint32_t* cand = a.cand + off;
+    uint32_t* kA = a.keyA + off; uint32_t* kB = a.keyB + off;
+    uint32_t* vA = a.valA + off; uint32_t* vB = a.valB + off;
+
+    // 1. path codes
+    for (int i = tid; i < M; i += QT_THREADS) {
+        const uint32_t c = cand[i];
+        kA[i] = path_code((int)(c & 0xfff), (int)((c >> 12) & 0xfff), a.hX[l], nIni, a.qH[l], depth);
+        vA[i] = (c & 0xff000000u) | (uint32_t)i;
+    }
+    __syncthreads();
+    // 2. sort by code
+    int iniBits = 0;
+    while ((1 << iniBits) < nIni) iniBits++;
+    const int which = block_radix_sort(kA, vA, kB, vB, M, 2 * depth + iniBits, s.hist, s.warpTmp);
+    const uint32_t* keys = which ? kB : kA;
+    const uint32_t* vals = which ? vB : vA;
+    // distinct pixels must have distinct codes (depth was sized for it on the host)
+    for (int i = tid + 1; i < M; i += QT_THREADS)
+        if (keys[i] == keys[i - 1]) atomicExch(a.err, 101);
+
+    // 3. initial nodes in push_back order, empty ones erased (:663-699)
+    if (tid == 0) {
+        int n = 0;
+        for (int i = 0; i < nIni; i++) {
+            const uint32_t lo = key_lower_bound(keys, M, (uint32_t)i << (2 * depth));
+            const uint32_t hi = (i + 1 == nIni) ? (uint32_t)M : key_lower_bound(keys, M, (uint32_t)(i + 1) << (2 * depth));
+            if (hi > lo) { s.lo[0][n] = lo; s.hi[0][n] = hi; s.dep[0][n] = 0; n++; }
+        }
+        s.misc[3] = n;
+    }
+    __syncthreads();
+    int n = s.misc[3];
+    int cur = 0;
+    bool finish = false;
+    int fresh = 0;            // number of nodes created by the last pass (front of the list)
+    bool priority = false;
+
+    while (!finish) {
+        uint32_t* clo = s.lo[cur]; uint32_t* chi = s.hi[cur]; uint8_t* cdep = s.dep[cur];
+        uint32_t* nlo = s.lo[cur ^ 1]; uint32_t* nhi = s.hi[cur ^ 1]; uint8_t* ndep = s.dep[cur ^ 1];
+        const int prevSize = n;
+        if (tid == 0) { s.misc[0] = 0; s.misc[1] = 0x7fffffff; s.misc[2] = 0; }
+        __syncthreads();
+        if (!priority) {
+            // ---- breadth pass: split every node with more than one key (:726-789)
+            int neLocal = 0;
+            for (int i = tid; i < n; i += QT_THREADS) {
+                const uint32_t lo = clo[i], hi = chi[i];
+                int nc = 0, ne = 0;
+                if (hi - lo > 1) {
+                    if (cdep[i] >= depth) { atomicExch(a.err, 102); }
+                    else {
+                        uint32_t c1, c2, c3;
+                        nc = split_node(keys, lo, hi, cdep[i], depth, c1, c2, c3, ne);
+                        s.b1[i] = c1; s.b2[i] = c2; s.b3[i] = c3;
+                    }
+                    s.sA[i] = nc; s.sB[i] = 0;
+                } else { s.sA[i] = 0; s.sB[i] = 1; }
+                neLocal += ne;
+            }
+            if (neLocal) atomicAdd(&s.misc[0], neLocal);
+            __syncthreads();
+            const int totalPushed = block_scan_excl(s.sA, n, s.warpTmp);
+            const int totalNoMore = block_scan_excl(s.sB, n, s.warpTmp);
+            if (totalPushed + totalNoMore > cap) { if (tid == 0) atomicExch(a.err, 103); break; }
+            for (int i = tid; i < n; i += QT_THREADS) {
+                const uint32_t lo = clo[i], hi = chi[i];
+                if (hi - lo > 1) emit_children(nlo, nhi, ndep, lo, s.b1[i], s.b2[i], s.b3[i], hi, cdep[i], s.sA[i], totalPushed);
+                else { const int pos = totalPushed + s.sB[i]; nlo[pos] = lo; nhi[pos] = hi; ndep[pos] = cdep[i]; }
+            }
+            __syncthreads();
+            n = totalPushed + totalNoMore;
+            fresh = totalPushed;
+            cur ^= 1;
+            const int nToExpand = s.misc[0];
+            if (n >= N || n == prevSize) finish = true;
+            else if (n + nToExpand * 3 > N) priority = true;
+            __syncthreads();
+        } else {
+            // ---- priority pass: split the recorded expandable nodes, largest first, newest first on ties,
+            //      stopping as soon as the list holds N nodes (:805-874)
+            for (int i = tid; i < fresh; i += QT_THREADS) {
+                const uint32_t cnt = chi[i] - clo[i];
+                if (cnt > 1) {
+                    const int k = atomicAdd(&s.misc[2], 1);
+                    s.skey[k] = ((unsigned long long)cnt << 32) | (uint32_t)(fresh - 1 - i);   // (count, creation seq)
+                }
+            }
+            __syncthreads();
+            const int ne = s.misc[2];
+            int p2 = 1;
+            while (p2 < ne) p2 <<= 1;
+            for (int i = ne + tid; i < p2; i += QT_THREADS) s.skey[i] = 0;
+            __syncthreads();
+            for (int k = 2; k <= p2; k <<= 1)            // bitonic sort, descending
+                for (int j = k >> 1; j > 0; j >>= 1) {
+                    for (int i = tid; i < p2; i += QT_THREADS) {
+                        const int ixj = i ^ j;
+                        if (ixj > i) {
+                            const unsigned long long x = s.skey[i], y = s.skey[ixj];
+                            const bool desc = (i & k) == 0;
+                            if (desc ? (x < y) : (x > y)) { s.skey[i] = y; s.skey[ixj] = x; }
+                        }
+                    }
+                    __syncthreads();
+                }
+            for (int t = tid; t < ne; t += QT_THREADS) {
+                const int i = fresh - 1 - (int)(s.skey[t] & 0xffffffffu);
+                int nc = 0, dummy;
+                if (cdep[i] >= depth) atomicExch(a.err, 102);
+                else {
+                    uint32_t c1, c2, c3;
+                    nc = split_node(keys, clo[i], chi[i], cdep[i], depth, c1, c2, c3, dummy);
+                    s.b1[t] = c1; s.b2[t] = c2; s.b3[t] = c3;
+                }
+                s.sA[t] = nc; s.sB[t] = nc - 1;
+            }
+            for (int i = tid; i < n; i += QT_THREADS) s.sC[i] = 1;     // keep flags over the old list
+            __syncthreads();
+            // inclusive running size after each split; first t reaching N ends the walk (:867-868)
+            block_scan_excl(s.sB, ne, s.warpTmp);
+            for (int t = tid; t < ne; t += QT_THREADS) {
+                const int incl = s.sB[t] + (s.sA[t] - 1);
+                if (n + incl >= N) atomicMin(&s.misc[1], t);
+            }
+            __syncthreads();
+            const int tStop = (s.misc[1] == 0x7fffffff) ? ne - 1 : s.misc[1];
+            const int nProc = tStop + 1;                                 // 0 when ne == 0
+            int newSize = n;
+            if (nProc > 0) newSize = n + s.sB[tStop] + (s.sA[tStop] - 1);
+            __syncthreads();
+            const int pushedAll = block_scan_excl(s.sA, ne, s.warpTmp);
+            int totalPushed = 0;
+            if (nProc > 0) totalPushed = (nProc == ne) ? pushedAll : s.sA[nProc];
+            for (int t = tid; t < nProc; t += QT_THREADS) s.sC[fresh - 1 - (int)(s.skey[t] & 0xffffffffu)] = 0;
+            __syncthreads();
+            const int kept = block_scan_excl(s.sC, n, s.warpTmp);
+            if (totalPushed + kept > cap) { if (tid == 0) atomicExch(a.err, 103); break; }
+            for (int t = tid; t < nProc; t += QT_THREADS) {
+                const int i = fresh - 1 - (int)(s.skey[t] & 0xffffffffu);
+                emit_children(nlo, nhi, ndep, clo[i], s.b1[t], s.b2[t], s.b3[t], chi[i], cdep[i], s.sA[t], totalPushed);
+            }
+            for (int i = tid; i < n; i += QT_THREADS) {
+                const bool keep = (i + 1 < n) ? (s.sC[i + 1] != s.sC[i]) : (kept != s.sC[i]);
+                if (keep) { const int pos = totalPushed + s.sC[i]; nlo[pos] = clo[i]; nhi[pos] = chi[i]; ndep[pos] = cdep[i]; }
+            }
+            __syncthreads();
+            n = newSize;
+            fresh = totalPushed;
+            cur ^= 1;
+            if (n >= N || n == prevSize) finish = true;
+        }
+    }
+
+    // 4. retain the best key of every node, list order (:885-904): highest response, earliest candidate on ties
+    if (n > a.maxSel[l]) { if (tid == 0) atomicExch(a.err, 104); n = a.maxSel[l]; }
+    uint32_t* sel = a.sel + (size_t)frame * a.selTotal + a.selOff[l];
+    const uint32_t* flo = s.lo[cur]; const uint32_t* fhi = s.hi[cur];
+    for (int i = tid; i < n; i += QT_THREADS) {
+        uint32_t best = 0;
+        for (uint32_t k = flo[i]; k < fhi[i]; k++) {
+            const uint32_t v = vals[k] ^ 0x00ffffffu;     // response high, inverted candidate index low
+            best = max(best, v);
+        }
+        sel[i] = cand[(best ^ 0x00ffffffu) & 0x00ffffffu];
+    }
+    if (tid == 0) *selCount = n;
+}
+
+}  // namespace orbx
