@@ -1,0 +1,340 @@
+#!/usr/bin/env python
+"""bench.py — ORB frames/s on the KITTI-stereo workload (BASELINE.json configs[1]).
+
+    python bench.py --gpus N --steps K --warmup W            # this repo's CUDA path
+    python bench.py --impl reference --gpus N --steps K ...   # the reference's CPU path (oracle/_ref)
+
+A step = one pass of ORBextractor::operator() over one batch of synthetic
+1241x376 frames (left/right stereo pairs, nFeatures 2000, 8 levels, 1.2, FAST
+20/7).  `value` = frames/s with the batch resident in HBM; `e2e` = frames/s
+through the host-buffer C ABI call (pinned host images in, keypoints +
+descriptors out, both copies inside the timed region).  One JSON line on rank 0.
+"""
+from __future__ import annotations
+
+import argparse
+import ctypes as C
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+W_, H_, NFEAT = 1241, 376, 2000
+SETTINGS = dict(nFeatures=NFEAT, scaleFactor=1.2, nLevels=8, iniThFAST=20, minThFAST=7)
+METRIC = "ORB frames/s (1241x376, 2000 kp)"
+UNIT = "frames/s"
+STAGES = ["pyramid_blur_fast", "border", "cell_count", "cell_scan", "cell_emit", "quadtree", "describe"]
+
+
+def level_sizes(w, h, nlevels=8, sf=1.2):
+    s = np.float32(1.0)
+    out = []
+    for _ in range(nlevels):
+        inv = np.float32(1.0) / s
+        out.append((int(np.rint(np.float32(w) * inv)), int(np.rint(np.float32(h) * inv))))
+        s = np.float32(np.float64(s) * np.float64(np.float32(sf)))
+    return out
+
+
+def algorithmic_bytes(w, h, nkp):
+    """B_alg = W*H + A' + A + N*60, split per stage."""
+    lv = level_sizes(w, h)
+    A = sum(a * b for a, b in lv)
+    Ab = sum((a + 38) * (b + 38) for a, b in lv)
+    per_stage = {"pyramid_blur_fast": w * h + 2 * A, "border": Ab - A, "describe": nkp * 60}
+    return w * h + Ab + A + nkp * 60, per_stage
+
+
+def make_frames(n_distinct, start):
+    """left/right pairs: right = left scene shifted by a per-pair disparity"""
+    from orb_slam_b200.synth import synth_frame
+    frames = []
+    for i in range(n_distinct // 2):
+        idx = start + i
+        frames.append(synth_frame(W_, H_, idx))
+        frames.append(synth_frame(W_, H_, idx, shift=(-(5 + (idx * 7) % 56), 0)))
+    return np.stack(frames)
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md)."""
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.lines = []
+        self.proc = None
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", "-i", str(index), f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100"],
+                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        sm, mx, reasons = [], None, set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            p = [x.strip() for x in ln.split(",")]
+            if len(p) < 6:
+                continue
+            try:
+                sm.append(float(p[0])); mx = float(p[1])
+            except ValueError:
+                continue
+            for nm, v in zip(names, p[2:6]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": mx, "reasons": sorted(reasons),
+                "samples": len(sm)}
+
+
+def cpu_extract_throughput(frames, n_threads, frames_per_thread, kind):
+    """frames/s of the CPU path with one extractor instance per thread (the reference's own threading
+    model, src/Frame.cc:94-103).  kind 'reference' = oracle/_ref (the reference's ORBextractor.cc,
+    system allocator), 'port' = oracle/liborb_oracle.so."""
+    from tests import oracle_lib
+    if kind == "reference":
+        mk = lambda: oracle_lib.RefExtractor(NFEAT, 1.2, 8, 20, 7)
+        call = lambda ex, im: ex(im, canonical=False)
+    else:
+        mk = lambda: oracle_lib.OracleExtractor(NFEAT, 1.2, 8, 20, 7)
+        call = lambda ex, im: ex(im)
+    exs = [mk() for _ in range(n_threads)]
+    for ex in exs:
+        call(ex, frames[0])          # warm-up (page faults, tables)
+    barrier = threading.Barrier(n_threads + 1)
+
+    def work(t):
+        barrier.wait()
+        for k in range(frames_per_thread):
+            call(exs[t], frames[(t * frames_per_thread + k) % len(frames)])
+        barrier.wait()
+
+    th = [threading.Thread(target=work, args=(t,)) for t in range(n_threads)]
+    for t in th:
+        t.start()
+    barrier.wait()
+    t0 = time.perf_counter()
+    barrier.wait()
+    dt = time.perf_counter() - t0
+    for t in th:
+        t.join()
+    return n_threads * frames_per_thread / dt, dt
+
+
+def run_reference(args, rank, world):
+    """--impl reference: the reference's own CPU ORBextractor on the host cores (rank 0 only)."""
+    if rank != 0:
+        return
+    from tests import oracle_lib
+    kind = "reference" if oracle_lib.have_ref() else "port"
+    cores = os.cpu_count() or 1
+    frames = make_frames(16, 0)
+    per_thread = max(2, args.cpu_frames // cores)
+    vals = []
+    for _ in range(args.warmup):
+        cpu_extract_throughput(frames, cores, 1, kind)
+    t_all = 0.0
+    for _ in range(args.steps):
+        v, dt = cpu_extract_throughput(frames, cores, per_thread, kind)
+        vals.append(v); t_all += dt
+    value = cores * per_thread * args.steps / t_all
+    single, _ = cpu_extract_throughput(frames, 1, 8, kind)
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": 1e3 * t_all / args.steps, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+        "config": {"workload": "KITTI-stereo 1241x376 left+right, nFeatures 2000, 8 levels, 1.2, FAST 20/7", **SETTINGS,
+                   "frames_per_step": cores * per_thread},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": kind,
+                         "sample": f"{cores} threads x {per_thread} frames per step, one extractor instance per thread",
+                         "single_thread_frames_per_s": single},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+def run_ours(args, rank, world, local_rank):
+    import torch
+    from orb_slam_b200 import KEYPOINT_DTYPE, ORBextractor
+    from orb_slam_b200._lib import check
+
+    dist = None
+    if world > 1:
+        import torch.distributed as dist_
+        dist = dist_
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    B = args.batch
+    distinct = make_frames(min(64, B), rank * 64)
+    reps = (B + len(distinct) - 1) // len(distinct)
+    host = torch.empty((B, H_, W_), dtype=torch.uint8, pin_memory=True)
+    host.numpy()[:] = np.concatenate([distinct] * reps)[:B]
+    d_img = host.to(dev)
+
+    ex = ORBextractor(NFEAT, 1.2, 8, 20, 7, device=local_rank)
+    L, h = ex._L, ex.handle
+    cap = ex.max_keypoints(W_, H_)
+    d_kps = torch.empty((B, cap, 28), dtype=torch.uint8, device=dev)
+    d_desc = torch.empty((B, cap, 32), dtype=torch.uint8, device=dev)
+    d_n = torch.zeros(B, dtype=torch.int32, device=dev)
+    stream = torch.cuda.ExternalStream(L.orbx_stream(h), device=dev)
+
+    def step_device():
+        check(L.orbx_extract_batch_device(h, d_img.data_ptr(), B, W_, H_, W_, W_ * H_, d_kps.data_ptr(),
+                                          d_desc.data_ptr(), cap, d_n.data_ptr()), "orbx_extract_batch_device")
+
+    def barrier():
+        torch.cuda.synchronize()
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(args.warmup):
+        step_device()
+    check(L.orbx_synchronize(h), "orbx_synchronize")
+    launches = L.orbx_launches_per_call(h)
+
+    # ---- timed region 1: device-resident throughput (CUDA events on the launching stream)
+    barrier()
+    sampler = ClockSampler(local_rank)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(stream)
+    for _ in range(args.steps):
+        step_device()
+    e1.record(stream)
+    check(L.orbx_synchronize(h), "orbx_synchronize")
+    barrier()
+    ms = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
+    if dist is not None:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    total_ms = float(ms.item())
+    nkp = float(d_n.float().mean().item())
+
+    # ---- timed region 2: per-stage device times of the same steps (events inside the library)
+    check(L.orbx_set_profiling(h, 1), "orbx_set_profiling")
+    stage_ms = np.zeros(len(STAGES))
+    t = np.zeros(len(STAGES), np.float32)
+    for _ in range(args.steps):
+        step_device()
+        check(L.orbx_stage_times(h, t.ctypes.data, len(STAGES)), "orbx_stage_times")
+        stage_ms += t
+    stage_ms /= args.steps
+    check(L.orbx_set_profiling(h, 0), "orbx_set_profiling")
+
+    # ---- timed region 3: end to end through the host-buffer C ABI call (H2D + kernels + D2H)
+    kps_h = torch.empty((B, cap, 28), dtype=torch.uint8, pin_memory=True)
+    desc_h = torch.empty((B, cap, 32), dtype=torch.uint8, pin_memory=True)
+    n_h = np.zeros(B, np.int32)
+    ptrs = (C.c_void_p * B)(*[host.data_ptr() + i * W_ * H_ for i in range(B)])
+
+    def step_e2e():
+        check(L.orbx_extract_batch(h, ptrs, B, W_, H_, W_, kps_h.data_ptr(), desc_h.data_ptr(), cap, n_h.ctypes.data),
+              "orbx_extract_batch")
+
+    for _ in range(max(1, args.warmup // 2)):
+        step_e2e()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        step_e2e()
+    torch.cuda.synchronize()
+    e2e_s = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
+    barrier()
+    clocks = sampler.stop()
+    if dist is not None:
+        dist.all_reduce(e2e_s, op=dist.ReduceOp.MAX)
+    e2e_s = float(e2e_s.item())
+
+    if rank == 0:
+        frames_total = world * B * args.steps
+        value = frames_total / (total_ms * 1e-3)
+        balg, per_stage = algorithmic_bytes(W_, H_, nkp)
+        peaks = {}
+        try:
+            peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        except Exception:
+            pass
+        peak = float(peaks.get("hbm_gbs", 6650.0))
+        peak_src = "measured (MEASURED_PEAKS.json hbm_gbs)" if "hbm_gbs" in peaks else "fallback 6650 GB/s"
+        top = int(np.argmax(stage_ms))
+        top_bytes = per_stage.get(STAGES[top], 0) * B
+        achieved = top_bytes / (stage_ms[top] * 1e-3) / 1e9
+        pipe_achieved = balg * B * args.steps / (total_ms * 1e-3) / 1e9 / world
+        n_sel = int(n_h.sum())
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": total_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "u8", "data": "synthetic",
+            "config": {"workload": "KITTI-stereo 1241x376 left+right (BASELINE.json configs[1]), nFeatures 2000, 8 levels, 1.2, FAST 20/7",
+                       **SETTINGS, "frames_per_step_per_gpu": B, "l2": "inputs larger than L2 (batch %.0f MB)" % (B * W_ * H_ / 1e6),
+                       "mean_keypoints_per_frame": nkp},
+            "e2e": {"value": world * B * args.steps / e2e_s, "unit": UNIT, "h2d_bytes_per_step": B * W_ * H_,
+                    "d2h_bytes_per_step": int((B + 1) * 4 + 63) // 64 * 64 + B * cap * 60, "keypoints_returned_per_step": n_sel},
+            "gpu_launches": launches * args.steps,
+            "clocks": clocks,
+            "roofline": {"bound": "hbm", "kernel": STAGES[top], "achieved": achieved, "peak": peak, "unit": "GB/s",
+                         "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                         "algorithmic_bytes_per_launch_group": top_bytes,
+                         "kernel_ms_per_step": float(stage_ms[top]),
+                         "pipeline_achieved": pipe_achieved, "pipeline_frac": pipe_achieved / peak,
+                         "algorithmic_bytes_per_frame": balg},
+            "stages_ms_per_step": {k: float(v) for k, v in zip(STAGES, stage_ms)},
+        }
+        if world == 1 and not args.no_cpu:
+            from tests import oracle_lib
+            kind = "reference" if oracle_lib.have_ref() else "port"
+            cores = os.cpu_count() or 1
+            per_thread = max(2, args.cpu_frames // cores)
+            v, dt = cpu_extract_throughput(distinct, cores, per_thread, kind)
+            v1, _ = cpu_extract_throughput(distinct, 1, 8, kind)
+            line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": cores, "kind": kind,
+                                    "sample": f"{cores} threads x {per_thread} frames of the same workload ({dt:.1f} s wall)",
+                                    "single_thread_frames_per_s": v1}
+        print(json.dumps(line), flush=True)
+    ex.close()
+    if dist is not None:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--batch", type=int, default=512, help="frames per step per GPU")
+    ap.add_argument("--cpu-frames", type=int, default=384, help="frames in the bounded CPU sample")
+    ap.add_argument("--no-cpu", action="store_true")
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        run_reference(args, rank, world)
+    else:
+        run_ours(args, rank, world, local_rank)
+
+
+if __name__ == "__main__":
+    main()

@@ -120,6 +120,13 @@ int orbx_get_candidates(orbx_t* ex, int frame, int level, int32_t* xyr, int capa
 /* Number of kernel launches one orbx_extract_batch* call enqueues (for bench.py's gpu_launches). */
 int orbx_launches_per_call(const orbx_t* ex);
 
+/* Per-stage device times of the last orbx_extract_batch* call, measured with CUDA events on the
+ * instance's stream (profiling must have been switched on before that call).  ms[0..6] =
+ * pyramid+blur+FAST (all levels), border, cell count, cell scan, cell emit, quadtree, describe. */
+int orbx_set_profiling(orbx_t* ex, int on);
+int orbx_stage_times(orbx_t* ex, float* ms, int n);
+#define ORBX_NUM_STAGES 7
+
 const char* orbx_error_string(int code);
 
 #ifdef __cplusplus

@@ -56,6 +56,8 @@ def lib() -> C.CDLL:
     L.orbx_get_level.argtypes = [vp, i, i, i, i, vp, sz]; L.orbx_get_level.restype = i
     L.orbx_get_candidates.argtypes = [vp, i, i, vp, i, C.POINTER(i)]; L.orbx_get_candidates.restype = i
     L.orbx_launches_per_call.argtypes = [vp]; L.orbx_launches_per_call.restype = i
+    L.orbx_set_profiling.argtypes = [vp, i]; L.orbx_set_profiling.restype = i
+    L.orbx_stage_times.argtypes = [vp, vp, i]; L.orbx_stage_times.restype = i
     L.orbx_error_string.argtypes = [i]; L.orbx_error_string.restype = C.c_char_p
     _lib = L
     return L

@@ -54,6 +54,8 @@ struct orbx_extractor {
     uint8_t* d_res = nullptr; uint8_t* h_res = nullptr; size_t resBytes = 0;
     uint8_t* h_in = nullptr; size_t hInBytes = 0;       // pinned staging for pageable inputs
     int launches = 0;
+    bool profile = false;                    // record one CUDA event per stage boundary
+    cudaEvent_t ev[8] = {};
     std::mutex mtx;
 };
 
@@ -276,6 +278,7 @@ static int enqueue_pipeline(orbx_extractor* e, const uint8_t* src, size_t srcPit
     cudaStream_t st = e->stream;
     int launches = 0;
     CK(cudaMemsetAsync(d_err, 0, sizeof(int), st));
+    if (e->profile) CK(cudaEventRecord(e->ev[0], st));
     // 1. pyramid + blur + FAST score, level by level (level l reads level l-1)
     for (int l = 0; l < g.nlevels; l++) {
         const LevelGeom& v = g.lv[l];
@@ -300,6 +303,7 @@ static int enqueue_pipeline(orbx_extractor* e, const uint8_t* src, size_t srcPit
         }
         launches++;
     }
+    if (e->profile) CK(cudaEventRecord(e->ev[1], st));
     // 2. REFLECT_101 frames
     {
         BorderArgs b{};
@@ -315,6 +319,7 @@ static int enqueue_pipeline(orbx_extractor* e, const uint8_t* src, size_t srcPit
         border_kernel<<<dim3((off + 255) / 256, frames), 256, 0, st>>>(b);
         launches++;
     }
+    if (e->profile) CK(cudaEventRecord(e->ev[2], st));
     // 3. per-cell NMS + threshold fallback -> ordered candidate lists
     CellArgs c{};
     c.score = e->d_score; c.planeFrameStride = g.planeBytes; c.nlevels = g.nlevels; c.iniTh = g.iniTh;
@@ -331,12 +336,16 @@ static int enqueue_pipeline(orbx_extractor* e, const uint8_t* src, size_t srcPit
     if (g.totalCells > 0) {
         dim3 cg((g.totalCells + 7) / 8, frames);
         cell_kernel<false><<<cg, 256, 0, st>>>(c);
+        if (e->profile) CK(cudaEventRecord(e->ev[3], st));
         cell_scan_kernel<<<dim3(g.nlevels, frames), 256, 0, st>>>(c);
+        if (e->profile) CK(cudaEventRecord(e->ev[4], st));
         cell_kernel<true><<<cg, 256, 0, st>>>(c);
         launches += 3;
     } else {
         CK(cudaMemsetAsync(e->d_candCount, 0, (size_t)frames * g.nlevels * 4, st));
+        if (e->profile) { CK(cudaEventRecord(e->ev[3], st)); CK(cudaEventRecord(e->ev[4], st)); }
     }
+    if (e->profile) CK(cudaEventRecord(e->ev[5], st));
     // 4. quadtree distribution
     QtArgs q{};
     q.cand = e->d_cand; q.candFrameStride = g.candTotal; q.candCount = e->d_candCount;
@@ -350,6 +359,7 @@ static int enqueue_pipeline(orbx_extractor* e, const uint8_t* src, size_t srcPit
     }
     quadtree_kernel<<<dim3(g.nlevels, frames), QT_THREADS, qt_smem_bytes(g.nodeCap), st>>>(q);
     launches++;
+    if (e->profile) CK(cudaEventRecord(e->ev[6], st));
     // 5. orientation, descriptors, output assembly
     DescArgs d{};
     d.pyr = e->d_pyr; d.pyrFrameStride = g.pyrBytes; d.blur = e->d_blur; d.planeFrameStride = g.planeBytes;
@@ -363,6 +373,7 @@ static int enqueue_pipeline(orbx_extractor* e, const uint8_t* src, size_t srcPit
     d.selOff[g.nlevels] = g.selTotal;
     describe_kernel<<<dim3((g.selTotal + 7) / 8, frames), 256, 0, st>>>(d);
     launches++;
+    if (e->profile) CK(cudaEventRecord(e->ev[7], st));
     e->launches = launches;
     e->lastFrames = frames;
     CK(cudaGetLastError());
@@ -415,6 +426,7 @@ void orbx_destroy(orbx_t* e) {
     cudaStreamSynchronize(e->stream);
     free_workspace(e);
     cudaFree(e->d_err);
+    for (int i = 0; i < 8; i++) if (e->ev[i]) cudaEventDestroy(e->ev[i]);
     if (e->h_in) cudaFreeHost(e->h_in);
     cudaStreamDestroy(e->stream);
     delete e;
@@ -583,5 +595,23 @@ int orbx_get_candidates(orbx_t* e, int frame, int level, int32_t* xyr, int capac
 }
 
 int orbx_launches_per_call(const orbx_t* e) { return e ? e->launches : 0; }
+
+int orbx_set_profiling(orbx_t* e, int on) {
+    if (!e) return ORBX_E_INVALID;
+    std::lock_guard<std::mutex> lk(e->mtx);
+    CK(cudaSetDevice(e->device));
+    if (on && !e->ev[0]) for (int i = 0; i < 8; i++) CK(cudaEventCreate(&e->ev[i]));
+    e->profile = on != 0;
+    return ORBX_OK;
+}
+
+int orbx_stage_times(orbx_t* e, float* ms, int n) {
+    if (!e || !ms || n < 7 || !e->profile) return ORBX_E_INVALID;
+    std::lock_guard<std::mutex> lk(e->mtx);
+    CK(cudaSetDevice(e->device));
+    CK(cudaEventSynchronize(e->ev[7]));
+    for (int i = 0; i < 7; i++) CK(cudaEventElapsedTime(&ms[i], e->ev[i], e->ev[i + 1]));
+    return ORBX_OK;
+}
 
 }  // extern "C"
