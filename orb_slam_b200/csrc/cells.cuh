@@ -34,6 +34,8 @@ struct CellArgs {
     int* candCount;                   // [frames][nlevels]
 };
 
+constexpr int CELL_ROWS = 8;   // rows of a cell column loaded together
+
 struct CellBox { int x0, x1, y0, y1; bool valid; };
 
 // detection interior of cell (i,j) in level coordinates, :955-972 (+3/-3 of cv::FAST)
@@ -85,15 +87,22 @@ __global__ void __launch_bounds__(256) cell_kernel(CellArgs a) {
     const int pitch = a.pitch[l];
     if (!EMIT) {
         int nIni = 0, nMin = 0;
-        for (int y = b.y0; y < b.y1; y++)
-            for (int xb = b.x0; xb < b.x1; xb += 32) {
-                const int x = xb + lane;
-                int s = 0;
-                if (x < b.x1) s = S[(size_t)y * pitch + ORB_XPAD + x];
-                const bool keep = s > 0 && nms_keep(S, pitch, x, y, s, b);
-                nMin += __popc(__ballot_sync(0xffffffffu, keep));
-                nIni += __popc(__ballot_sync(0xffffffffu, keep && s >= a.iniTh));
+        for (int xb = b.x0; xb < b.x1; xb += 32) {
+            const int x = xb + lane;
+            for (int yb = b.y0; yb < b.y1; yb += CELL_ROWS) {
+                int sv[CELL_ROWS];
+#pragma unroll
+                for (int r = 0; r < CELL_ROWS; r++)       // independent loads first: CELL_ROWS rows in flight
+                    sv[r] = (x < b.x1 && yb + r < b.y1) ? S[(size_t)(yb + r) * pitch + ORB_XPAD + x] : 0;
+#pragma unroll
+                for (int r = 0; r < CELL_ROWS; r++) {
+                    const int s = sv[r];
+                    const bool keep = s > 0 && nms_keep(S, pitch, x, yb + r, s, b);
+                    nMin += __popc(__ballot_sync(0xffffffffu, keep));
+                    nIni += __popc(__ballot_sync(0xffffffffu, keep && s >= a.iniTh));
+                }
             }
+        }
         if (lane == 0) *cnt = nIni > 0 ? (uint32_t)nIni : ((uint32_t)nMin | 0x80000000u);
     } else {
         const uint32_t cv = *cnt;
@@ -101,19 +110,33 @@ __global__ void __launch_bounds__(256) cell_kernel(CellArgs a) {
         const int th = (cv & 0x80000000u) ? 1 : a.iniTh;      // the score plane is already 0 below minThFAST
         uint32_t pos = a.cellOffs[(size_t)frame * a.totalCells + cell];
         uint32_t* out = a.cand + (size_t)frame * a.candFrameStride + a.candOff[l];
-        for (int y = b.y0; y < b.y1; y++)
-            for (int xb = b.x0; xb < b.x1; xb += 32) {
-                const int x = xb + lane;
-                int s = 0;
-                if (x < b.x1) s = S[(size_t)y * pitch + ORB_XPAD + x];
-                const bool keep = s >= th && nms_keep(S, pitch, x, y, s, b);
-                const unsigned m = __ballot_sync(0xffffffffu, keep);
-                if (keep) {
-                    const uint32_t k = pos + __popc(m & ((1u << lane) - 1));
-                    out[k] = ((uint32_t)(x - ORB_BORDER_MIN)) | ((uint32_t)(y - ORB_BORDER_MIN) << 12) | ((uint32_t)s << 24);
+        // cells are < 60 px wide (wCell = ceil(W / floor(W/30))): at most two 32-lane chunks per row
+        const int nch = (b.x1 - b.x0 > 32) ? 2 : 1;
+        for (int yb = b.y0; yb < b.y1; yb += CELL_ROWS) {
+            int sv[CELL_ROWS][2];
+#pragma unroll
+            for (int r = 0; r < CELL_ROWS; r++)
+#pragma unroll
+                for (int c2 = 0; c2 < 2; c2++) {
+                    const int x = b.x0 + 32 * c2 + lane;
+                    sv[r][c2] = (c2 < nch && x < b.x1 && yb + r < b.y1) ? S[(size_t)(yb + r) * pitch + ORB_XPAD + x] : 0;
                 }
-                pos += __popc(m);
-            }
+#pragma unroll
+            for (int r = 0; r < CELL_ROWS; r++)
+#pragma unroll
+                for (int c2 = 0; c2 < 2; c2++) {
+                    if (c2 >= nch) continue;                 // warp-uniform
+                    const int x = b.x0 + 32 * c2 + lane, y = yb + r;
+                    const int s = sv[r][c2];
+                    const bool keep = s >= th && nms_keep(S, pitch, x, y, s, b);
+                    const unsigned m = __ballot_sync(0xffffffffu, keep);
+                    if (keep) {
+                        const uint32_t k = pos + __popc(m & ((1u << lane) - 1));
+                        out[k] = ((uint32_t)(x - ORB_BORDER_MIN)) | ((uint32_t)(y - ORB_BORDER_MIN) << 12) | ((uint32_t)s << 24);
+                    }
+                    pos += __popc(m);
+                }
+        }
     }
 }
 

@@ -49,6 +49,15 @@ __device__ __forceinline__ float fast_atan2_deg(float y, float x) {
 }
 
 __global__ void __launch_bounds__(256) describe_kernel(DescArgs a) {
+    // pattern staged in shared memory as [pair k][byte lane] words: lanes read distinct banks.  (Lane-indexed
+    // reads of __constant__ memory serialise 32-way: ncu showed 62 warps/issue stalled on mio_throttle.)
+    __shared__ uint32_t s_pat[256];
+    {
+        const int t = threadIdx.x;          // blockDim.x == 256: word t = pair (t>>5) of byte (t&31)
+        const signed char* q = c_pattern + (t & 31) * 32 + (t >> 5) * 4;
+        s_pat[t] = (uint32_t)(uint8_t)q[0] | ((uint32_t)(uint8_t)q[1] << 8) | ((uint32_t)(uint8_t)q[2] << 16) | ((uint32_t)(uint8_t)q[3] << 24);
+    }
+    __syncthreads();
     const int lane = threadIdx.x & 31;
     const int slot = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     const int frame = blockIdx.y;
@@ -76,7 +85,7 @@ __global__ void __launch_bounds__(256) describe_kernel(DescArgs a) {
     const int u = lane - ORB_HALF_PATCH;
     if (lane < 31) {
         const int au = abs(u);
-#pragma unroll 1
+#pragma unroll
         for (int v = -ORB_HALF_PATCH; v <= ORB_HALF_PATCH; v++) {
             if (au <= c_umax[abs(v)]) {
                 const int val = img[v * pitch + u];
@@ -103,11 +112,13 @@ __global__ void __launch_bounds__(256) describe_kernel(DescArgs a) {
     ca = __shfl_sync(0xffffffffu, ca, 0);
     sb = __shfl_sync(0xffffffffu, sb, 0);
     const uint8_t* bl = a.blur + (size_t)frame * a.planeFrameStride + a.planeOff[l] + (size_t)y * pitch + ORB_XPAD + x;
-    const signed char* p = c_pattern + lane * 32;
     int val = 0;
 #pragma unroll
     for (int k = 0; k < 8; k++) {
-        const float x0 = (float)p[4 * k], y0 = (float)p[4 * k + 1], x1 = (float)p[4 * k + 2], y1 = (float)p[4 * k + 3];
+        // test pair k of byte `lane`: one conflict-free 32-bit shared load (x0,y0,x1,y1 as signed bytes)
+        const int pw = (int)s_pat[k * 32 + lane];
+        const float x0 = (float)(signed char)(pw), y0 = (float)(signed char)(pw >> 8);
+        const float x1 = (float)(signed char)(pw >> 16), y1 = (float)(signed char)(pw >> 24);
         const int r0 = __float2int_rn(__fadd_rn(__fmul_rn(x0, sb), __fmul_rn(y0, ca)));      // cvRound(x*b + y*a)
         const int q0 = __float2int_rn(__fsub_rn(__fmul_rn(x0, ca), __fmul_rn(y0, sb)));      // cvRound(x*a - y*b)
         const int r1 = __float2int_rn(__fadd_rn(__fmul_rn(x1, sb), __fmul_rn(y1, ca)));
