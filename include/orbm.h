@@ -1,0 +1,131 @@
+/* orbm — C ABI of the B200 Hamming matcher and Frame grid (libfrontend_b200.so).
+ *
+ * Device boundary behind ORB_SLAM2::ORBmatcher's Hamming hot path and the grid
+ * part of ORB_SLAM2::Frame.  Plain pointers and sizes only; every function
+ * returns 0 or an ORBX_E_* / cudaError_t code (see orbx.h); no CPU fallback for
+ * the distance work.  Reference file:line citations are relative to the
+ * ORB-SLAM2 tree.
+ */
+#ifndef ORBM_H
+#define ORBM_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#include "orbx.h"
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct orbm_context orbm_t;
+
+#define ORBM_TH_HIGH 100        /* ORBmatcher::TH_HIGH, src/ORBmatcher.cc:37 */
+#define ORBM_TH_LOW 50          /* ORBmatcher::TH_LOW,  :38 */
+#define ORBM_HISTO_LENGTH 30    /* ORBmatcher::HISTO_LENGTH, :39 */
+#define ORBM_GRID_COLS 64       /* FRAME_GRID_COLS, include/Frame.h:38 */
+#define ORBM_GRID_ROWS 48       /* FRAME_GRID_ROWS, include/Frame.h:37 */
+
+/* One matcher context per host thread (ORBmatcher objects are per-call
+ * temporaries in the reference, so nothing is allocated per ORBmatcher). */
+int orbm_create(orbm_t** out, int device);
+void orbm_destroy(orbm_t* m);
+void* orbm_stream(orbm_t* m);
+int orbm_synchronize(orbm_t* m);
+
+/* ORBmatcher::DescriptorDistance (src/ORBmatcher.cc:1728-1744), host-side, one pair. */
+int orbm_descriptor_distance(const uint8_t* a32, const uint8_t* b32);
+
+/* ORBmatcher::ComputeThreeMaxima (src/ORBmatcher.cc:1679-1723) on bin counts. */
+void orbm_three_maxima(const int32_t* counts, int L, int* ind1, int* ind2, int* ind3);
+
+/* ---- brute-force Hamming 2-NN: DescriptorDistance applied
+ * exhaustively with the best / second-best scan of src/ORBmatcher.cc:205-226
+ * (strict '<' in ascending database index, so ties go to the lowest index).
+ * Result per query: best distance, best GLOBAL row index (idx_base + row),
+ * second-best distance (256 and index 0xFFFFFFFF when fewer rows exist).
+ * Queries and database are DEVICE pointers (n x 32 bytes, 4-byte aligned);
+ * outputs are DEVICE pointers.  Enqueued on the context stream. */
+typedef struct orbm_top2 {
+    uint32_t i1;        /* global index of the nearest row */
+    uint16_t d1, d2;    /* nearest / second nearest distance */
+} orbm_top2;
+int orbm_bf2nn_device(orbm_t* m, const uint8_t* d_queries, int nq, const uint8_t* d_db, size_t ndb,
+                      uint32_t idx_base, orbm_top2* d_out);
+/* Exact merge of `nparts` per-shard results ([part][nq], e.g. an NCCL all-gather
+ * of every rank's orbm_bf2nn_device output) into the global top-2. */
+int orbm_merge_top2_device(orbm_t* m, const orbm_top2* d_parts, int nparts, int nq, orbm_top2* d_out);
+/* Host-buffer convenience: H2D of the queries, 2-NN against a device-resident database, D2H. */
+int orbm_bf2nn(orbm_t* m, const uint8_t* queries, int nq, const uint8_t* d_db, size_t ndb,
+               uint32_t idx_base, orbm_top2* out);
+/* The acceptance of src/ORBmatcher.cc:228-230 applied to a top-2 result. */
+static inline int orbm_accept_low_ratio(orbm_top2 r, float nnratio) {
+    return r.d1 <= ORBM_TH_LOW && (float)r.d1 < nnratio * (float)r.d2;
+}
+/* measured integer-pipe peak: 32-bit popc per second of this GPU (microbenchmark) */
+int orbm_popc_peak(orbm_t* m, double* popc_per_s);
+
+/* ---- Frame grid (src/Frame.cc:292-311 AssignFeaturesToGrid, :504-518 PosInGrid,
+ * :410-495 GetFeaturesInArea) and the windowed matchers built on it. */
+typedef struct orbm_frame {
+    int32_t N;
+    const orbx_keypoint* keys;      /* mvKeys   (octave read by SearchByProjection, :1446) */
+    const orbx_keypoint* keysUn;    /* mvKeysUn */
+    const uint8_t* descriptors;     /* mDescriptors, N x 32 */
+    const float* uRight;            /* mvuRight, or NULL for monocular (all -1) */
+    float mnMinX, mnMaxX, mnMinY, mnMaxY;
+    float gridElementWidthInv, gridElementHeightInv;    /* mfGridElement{Width,Height}Inv */
+    float fx, fy, cx, cy, bf, b;    /* intrinsics, mbf, mb */
+    float Tcw[16];                  /* mTcw, row-major 4x4 */
+    const float* scaleFactors;      /* mvScaleFactors */
+    int32_t nScaleLevels;
+} orbm_frame;
+
+/* mGrid as CSR: cell (ix, iy) is row ix*48+iy; items of a cell are keypoint
+ * indices in ascending order (push_back order of :300-310).  cell_start has
+ * 64*48+1 entries, items has N entries (keypoints outside the grid are dropped,
+ * so cell_start[64*48] <= N).  Host pointers. */
+int orbm_grid_build(orbm_t* m, const orbm_frame* f, int32_t* cell_start, int32_t* items);
+/* Frame::GetFeaturesInArea(x, y, r, minLevel, maxLevel); returns candidates in the
+ * reference's enumeration order (ix outer, iy inner, insertion order). */
+int orbm_features_in_area(orbm_t* m, const orbm_frame* f, float x, float y, float r, int minLevel, int maxLevel,
+                          int32_t* out, int capacity, int* n_out);
+
+/* ORBmatcher::SearchForInitialization(F1, F2, vbPrevMatched, vnMatches12, windowSize)
+ * (src/ORBmatcher.cc:417-588).  prev_matched: N1 (x,y) pairs, in/out.  matches12: N1 ints out. */
+int orbm_search_for_initialization(orbm_t* m, const orbm_frame* F1, const orbm_frame* F2, float* prev_matched_xy,
+                                   int32_t* matches12, int windowSize, float nnratio, int checkOrientation,
+                                   int* nmatches);
+
+/* MapPoint fields read by the projection matchers. */
+typedef struct orbm_mappoint {
+    float world[3];            /* GetWorldPos() */
+    int32_t observations;      /* Observations() */
+    uint8_t descriptor[32];    /* GetDescriptor() */
+    uint8_t valid;             /* pointer non-null */
+    uint8_t bad;               /* isBad() */
+    uint8_t outlier;           /* mvbOutlier[i] of the owning frame (SearchByProjection frame variant) */
+    uint8_t trackInView;       /* mbTrackInView */
+    float trackProjX, trackProjY, trackProjXR, trackViewCos;
+    int32_t trackScaleLevel;
+} orbm_mappoint;
+
+/* ORBmatcher::SearchByProjection(CurrentFrame, LastFrame, th, bMono) (src/ORBmatcher.cc:1396-1538).
+ * last_points[i] describes LastFrame.mvpMapPoints[i] (valid=0 for NULL) and LastFrame.mvbOutlier[i];
+ * cur_observations[i2] = Observations() of CurrentFrame.mvpMapPoints[i2], or -1 when NULL.
+ * cur_assign[i2] out: -2 untouched, -1 set to NULL by the rotation check, else index i of the
+ * last-frame point now stored in CurrentFrame.mvpMapPoints[i2]. */
+int orbm_search_by_projection_frame(orbm_t* m, const orbm_frame* cur, const orbm_frame* last,
+                                    const orbm_mappoint* last_points, const int32_t* cur_observations,
+                                    float th, int bMono, int checkOrientation, int32_t* cur_assign, int* nmatches);
+
+/* ORBmatcher::SearchByProjection(F, vpMapPoints, th) (src/ORBmatcher.cc:45-129).
+ * frame_assign[idx] out: -2 untouched, else index iMP stored in F.mvpMapPoints[idx]. */
+int orbm_search_by_projection_points(orbm_t* m, const orbm_frame* F, const orbm_mappoint* points, int npoints,
+                                     const int32_t* frame_observations, float th, float nnratio,
+                                     int32_t* frame_assign, int* nmatches);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* ORBM_H */

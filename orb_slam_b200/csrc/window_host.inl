@@ -1,0 +1,330 @@
+// Host side of the grid / windowed matchers (included by matcher.cu).
+// The device produces, per query, the GetFeaturesInArea candidate list with Hamming
+// distances; the sequential, order-dependent acceptance rules of the reference are
+// replayed here over those lists so results equal the reference exactly.
+
+namespace {
+
+struct DeviceFrame {            // target frame resident on the device (context scratch buffers w0..w3)
+    const orbx_keypoint* keysUn; const uint32_t* desc; const int32_t* cellStart; const int32_t* items;
+    GridParams g; int N;
+};
+
+int upload_frame(orbm_context* m, const orbm_frame* f, DeviceFrame& d) {
+    const size_t N = (size_t)std::max(f->N, 1);
+    int rc;
+    if ((rc = m->w0.reserve(N * sizeof(orbx_keypoint)))) return rc;
+    if ((rc = m->w1.reserve(N * 32))) return rc;
+    if ((rc = m->w2.reserve((GRID_CELLS + 1) * 4 + N * 4))) return rc;     // cellStart | cellOf
+    if ((rc = m->w3.reserve(N * 4))) return rc;                            // items
+    if (f->N > 0) {
+        CKM(cudaMemcpyAsync(m->w0.p, f->keysUn, (size_t)f->N * sizeof(orbx_keypoint), cudaMemcpyHostToDevice, m->stream));
+        CKM(cudaMemcpyAsync(m->w1.p, f->descriptors, (size_t)f->N * 32, cudaMemcpyHostToDevice, m->stream));
+    }
+    d.keysUn = (const orbx_keypoint*)m->w0.p; d.desc = (const uint32_t*)m->w1.p;
+    int32_t* cellStart = (int32_t*)m->w2.p; int32_t* cellOf = cellStart + GRID_CELLS + 1;
+    d.cellStart = cellStart; d.items = (const int32_t*)m->w3.p; d.N = f->N;
+    d.g = GridParams{f->mnMinX, f->mnMinY, f->gridElementWidthInv, f->gridElementHeightInv};
+    grid_build_kernel<<<1, 1024, 0, m->stream>>>(d.keysUn, f->N, d.g, cellOf, cellStart, (int32_t*)m->w3.p);
+    CKM(cudaGetLastError());
+    return 0;
+}
+
+// runs the window queries against the uploaded frame; lists[q] = offs[q]..offs[q+1] in `pairs`
+int run_queries(orbm_context* m, const DeviceFrame& d, const std::vector<WQuery>& queries, std::vector<int32_t>& offs,
+                std::vector<int2>& pairs) {
+    const int nq = (int)queries.size();
+    offs.assign(nq + 1, 0);
+    pairs.clear();
+    if (nq == 0) return 0;
+    int rc;
+    if ((rc = m->w4.reserve((size_t)nq * sizeof(WQuery) + (size_t)(2 * nq + 2) * 4))) return rc;
+    WQuery* dq = (WQuery*)m->w4.p;
+    int32_t* dcnt = (int32_t*)(dq + nq); int32_t* doff = dcnt + nq;
+    CKM(cudaMemcpyAsync(dq, queries.data(), (size_t)nq * sizeof(WQuery), cudaMemcpyHostToDevice, m->stream));
+    const dim3 grid((nq + 7) / 8);
+    window_kernel<false><<<grid, 256, 0, m->stream>>>(dq, nq, d.g, d.keysUn, d.desc, d.cellStart, d.items, dcnt, nullptr, nullptr);
+    scan_counts_kernel<<<1, 1024, 0, m->stream>>>(dcnt, nq, doff);
+    CKM(cudaMemcpyAsync(offs.data(), doff, (size_t)(nq + 1) * 4, cudaMemcpyDeviceToHost, m->stream));
+    CKM(cudaStreamSynchronize(m->stream));
+    const int total = offs[nq];
+    if (total == 0) return 0;
+    if ((rc = m->w5.reserve((size_t)total * sizeof(int2)))) return rc;
+    window_kernel<true><<<grid, 256, 0, m->stream>>>(dq, nq, d.g, d.keysUn, d.desc, d.cellStart, d.items, nullptr, doff, (int2*)m->w5.p);
+    pairs.resize(total);
+    CKM(cudaMemcpyAsync(pairs.data(), m->w5.p, (size_t)total * sizeof(int2), cudaMemcpyDeviceToHost, m->stream));
+    CKM(cudaStreamSynchronize(m->stream));
+    CKM(cudaGetLastError());
+    return 0;
+}
+
+inline void set_desc(WQuery& q, const uint8_t* d) { std::memcpy(q.desc, d, 32); }
+
+// rotation-histogram bin of :528-540 / :1501-1508
+inline int rot_bin(float a1, float a2) {
+    const float factor = 1.0f / ORBM_HISTO_LENGTH;
+    float rot = a1 - a2;
+    if (rot < 0.0) rot += 360.0f;
+    int bin = (int)roundf(rot * factor);
+    if (bin == ORBM_HISTO_LENGTH) bin = 0;
+    return bin;
+}
+
+}  // namespace
+
+extern "C" {
+
+int orbm_grid_build(orbm_t* m, const orbm_frame* f, int32_t* cell_start, int32_t* items) {
+    if (!m || !f || !cell_start || !items || f->N < 0) return ORBX_E_INVALID;
+    std::lock_guard<std::mutex> lk(m->mtx);
+    CKM(cudaSetDevice(m->device));
+    DeviceFrame d;
+    int rc = upload_frame(m, f, d);
+    if (rc) return rc;
+    CKM(cudaMemcpyAsync(cell_start, d.cellStart, (GRID_CELLS + 1) * 4, cudaMemcpyDeviceToHost, m->stream));
+    if (f->N > 0) CKM(cudaMemcpyAsync(items, d.items, (size_t)f->N * 4, cudaMemcpyDeviceToHost, m->stream));
+    CKM(cudaStreamSynchronize(m->stream));
+    return ORBX_OK;
+}
+
+int orbm_features_in_area(orbm_t* m, const orbm_frame* f, float x, float y, float r, int minLevel, int maxLevel,
+                          int32_t* out, int capacity, int* n_out) {
+    if (!m || !f || !n_out) return ORBX_E_INVALID;
+    std::lock_guard<std::mutex> lk(m->mtx);
+    CKM(cudaSetDevice(m->device));
+    DeviceFrame d;
+    int rc = upload_frame(m, f, d);
+    if (rc) return rc;
+    std::vector<WQuery> q(1);
+    std::memset(&q[0], 0, sizeof(WQuery));
+    q[0].x = x; q[0].y = y; q[0].r = r; q[0].minLevel = minLevel; q[0].maxLevel = maxLevel;
+    std::vector<int32_t> offs; std::vector<int2> pairs;
+    if ((rc = run_queries(m, d, q, offs, pairs))) return rc;
+    *n_out = (int)pairs.size();
+    for (int i = 0; i < (int)pairs.size() && i < capacity; i++) out[i] = pairs[i].x;
+    return ORBX_OK;
+}
+
+// ORBmatcher::SearchForInitialization, src/ORBmatcher.cc:417-588
+int orbm_search_for_initialization(orbm_t* m, const orbm_frame* F1, const orbm_frame* F2, float* prev, int32_t* matches12,
+                                   int windowSize, float nnratio, int checkOri, int* nmatchesOut) {
+    if (!m || !F1 || !F2 || !prev || !matches12 || !nmatchesOut) return ORBX_E_INVALID;
+    std::lock_guard<std::mutex> lk(m->mtx);
+    CKM(cudaSetDevice(m->device));
+    DeviceFrame d;
+    int rc = upload_frame(m, F2, d);
+    if (rc) return rc;
+    std::vector<WQuery> queries; std::vector<int> qOf;
+    for (int i1 = 0; i1 < F1->N; i1++) {
+        const int level1 = F1->keysUn[i1].octave;
+        if (level1 > 0) continue;                                   // :451
+        WQuery q; std::memset(&q, 0, sizeof(q));
+        q.x = prev[2 * i1]; q.y = prev[2 * i1 + 1]; q.r = (float)windowSize; q.minLevel = level1; q.maxLevel = level1;
+        set_desc(q, F1->descriptors + 32 * (size_t)i1);
+        queries.push_back(q); qOf.push_back(i1);
+    }
+    std::vector<int32_t> offs; std::vector<int2> pairs;
+    if ((rc = run_queries(m, d, queries, offs, pairs))) return rc;
+
+    int nmatches = 0;
+    for (int i = 0; i < F1->N; i++) matches12[i] = -1;
+    std::vector<int> rotHist[ORBM_HISTO_LENGTH];
+    std::vector<int> matchedDistance(F2->N, INT32_MAX), matches21(F2->N, -1);
+    for (size_t qi = 0; qi < queries.size(); qi++) {
+        const int i1 = qOf[qi];
+        if (offs[qi + 1] == offs[qi]) continue;
+        int bestDist = INT32_MAX, bestDist2 = INT32_MAX, bestIdx2 = -1;
+        for (int k = offs[qi]; k < offs[qi + 1]; k++) {
+            const int i2 = pairs[k].x, dist = pairs[k].y;
+            if (matchedDistance[i2] <= dist) continue;             // :488
+            if (dist < bestDist) { bestDist2 = bestDist; bestDist = dist; bestIdx2 = i2; }
+            else if (dist < bestDist2) bestDist2 = dist;
+        }
+        if (bestDist <= ORBM_TH_LOW) {
+            if (bestDist < (float)bestDist2 * nnratio) {
+                if (matches21[bestIdx2] >= 0) { matches12[matches21[bestIdx2]] = -1; nmatches--; }
+                matches12[i1] = bestIdx2; matches21[bestIdx2] = i1; matchedDistance[bestIdx2] = bestDist;
+                nmatches++;
+                if (checkOri) rotHist[rot_bin(F1->keysUn[i1].angle, F2->keysUn[bestIdx2].angle)].push_back(i1);
+            }
+        }
+    }
+    if (checkOri) {
+        int32_t counts[ORBM_HISTO_LENGTH];
+        for (int i = 0; i < ORBM_HISTO_LENGTH; i++) counts[i] = (int)rotHist[i].size();
+        int ind1 = -1, ind2 = -1, ind3 = -1;
+        orbm_three_maxima(counts, ORBM_HISTO_LENGTH, &ind1, &ind2, &ind3);
+        for (int i = 0; i < ORBM_HISTO_LENGTH; i++) {
+            if (i == ind1 || i == ind2 || i == ind3) continue;
+            for (int idx1 : rotHist[i])
+                if (matches12[idx1] >= 0) { matches12[idx1] = -1; nmatches--; }
+        }
+    }
+    for (int i1 = 0; i1 < F1->N; i1++)
+        if (matches12[i1] >= 0) { prev[2 * i1] = F2->keysUn[matches12[i1]].x; prev[2 * i1 + 1] = F2->keysUn[matches12[i1]].y; }
+    *nmatchesOut = nmatches;
+    return ORBX_OK;
+}
+
+}  // extern "C"
+
+namespace {
+// cv::Mat float algebra as OpenCV 4.13 evaluates it for 3x3 * 3x1 (+ 3x1): products and sums in float, left to
+// right, no FMA; the "+ c" of the fused gemm is applied in double (pinned against cv2.gemm in tests/golden).
+inline void mat3_mul_add(const float* T, int rowStride, const float* x, const float* c, float* out) {
+    for (int i = 0; i < 3; i++) {
+        const float* a = T + i * rowStride;
+        float t = a[0] * x[0];
+        t = t + a[1] * x[1];
+        t = t + a[2] * x[2];
+        out[i] = c ? (float)((double)t + (double)c[i]) : t;
+    }
+}
+}  // namespace
+
+extern "C" {
+
+// ORBmatcher::SearchByProjection(CurrentFrame, LastFrame, th, bMono), src/ORBmatcher.cc:1396-1538
+int orbm_search_by_projection_frame(orbm_t* m, const orbm_frame* cur, const orbm_frame* last, const orbm_mappoint* lp,
+                                    const int32_t* curObs, float th, int bMono, int checkOri, int32_t* curAssign,
+                                    int* nmatchesOut) {
+    if (!m || !cur || !last || !lp || !curObs || !curAssign || !nmatchesOut) return ORBX_E_INVALID;
+    std::lock_guard<std::mutex> lk(m->mtx);
+    CKM(cudaSetDevice(m->device));
+    DeviceFrame d;
+    int rc = upload_frame(m, cur, d);
+    if (rc) return rc;
+    const float* Tc = cur->Tcw; const float* Tl = last->Tcw;
+    const float tcw[3] = {Tc[3], Tc[7], Tc[11]}, tlw[3] = {Tl[3], Tl[7], Tl[11]};
+    float twc[3];                                          // -Rcw.t()*tcw (general gemm path: double accumulation)
+    for (int i = 0; i < 3; i++) {
+        double s = 0;
+        for (int k = 0; k < 3; k++) s += (double)Tc[4 * k + i] * (double)tcw[k];
+        twc[i] = (float)(s * -1.0);
+    }
+    float tlc[3];
+    mat3_mul_add(Tl, 4, twc, tlw, tlc);
+    const bool bForward = tlc[2] > cur->b && !bMono;
+    const bool bBackward = -tlc[2] > cur->b && !bMono;
+
+    struct Q { int i; float u, v, radius, invzc; };
+    std::vector<Q> meta; std::vector<WQuery> queries;
+    for (int i = 0; i < last->N; i++) {
+        if (!lp[i].valid || lp[i].outlier) continue;
+        float x3Dc[3];
+        mat3_mul_add(Tc, 4, lp[i].world, tcw, x3Dc);
+        const float xc = x3Dc[0], yc = x3Dc[1];
+        const float invzc = (float)(1.0 / x3Dc[2]);
+        if (invzc < 0) continue;
+        const float u = cur->fx * xc * invzc + cur->cx;
+        const float v = cur->fy * yc * invzc + cur->cy;
+        if (u < cur->mnMinX || u > cur->mnMaxX) continue;
+        if (v < cur->mnMinY || v > cur->mnMaxY) continue;
+        const int nLastOctave = last->keys[i].octave;
+        const float radius = th * cur->scaleFactors[nLastOctave];
+        WQuery q; std::memset(&q, 0, sizeof(q));
+        q.x = u; q.y = v; q.r = radius;
+        if (bForward) { q.minLevel = nLastOctave; q.maxLevel = -1; }                 // GetFeaturesInArea(u,v,radius,nLastOctave)
+        else if (bBackward) { q.minLevel = 0; q.maxLevel = nLastOctave; }
+        else { q.minLevel = nLastOctave - 1; q.maxLevel = nLastOctave + 1; }
+        set_desc(q, lp[i].descriptor);
+        queries.push_back(q); meta.push_back(Q{i, u, v, radius, invzc});
+    }
+    std::vector<int32_t> offs; std::vector<int2> pairs;
+    if ((rc = run_queries(m, d, queries, offs, pairs))) return rc;
+
+    int nmatches = 0;
+    std::vector<int> obs(curObs, curObs + cur->N);       // Observations() of the point currently stored, -1 = NULL
+    for (int i = 0; i < cur->N; i++) curAssign[i] = -2;
+    std::vector<int> rotHist[ORBM_HISTO_LENGTH];
+    for (size_t qi = 0; qi < queries.size(); qi++) {
+        if (offs[qi + 1] == offs[qi]) continue;
+        const Q& mq = meta[qi];
+        int bestDist = 256, bestIdx2 = -1;
+        for (int k = offs[qi]; k < offs[qi + 1]; k++) {
+            const int i2 = pairs[k].x;
+            if (obs[i2] > 0) continue;                                        // :1471-1473
+            if (cur->uRight && cur->uRight[i2] > 0) {
+                const float ur = mq.u - cur->bf * mq.invzc;
+                const float er = fabsf(ur - cur->uRight[i2]);
+                if (er > mq.radius) continue;
+            }
+            const int dist = pairs[k].y;
+            if (dist < bestDist) { bestDist = dist; bestIdx2 = i2; }
+        }
+        if (bestDist <= ORBM_TH_HIGH) {
+            curAssign[bestIdx2] = mq.i; obs[bestIdx2] = lp[mq.i].observations;
+            nmatches++;
+            if (checkOri) rotHist[rot_bin(last->keysUn[mq.i].angle, cur->keysUn[bestIdx2].angle)].push_back(bestIdx2);
+        }
+    }
+    if (checkOri) {
+        int32_t counts[ORBM_HISTO_LENGTH];
+        for (int i = 0; i < ORBM_HISTO_LENGTH; i++) counts[i] = (int)rotHist[i].size();
+        int ind1 = -1, ind2 = -1, ind3 = -1;
+        orbm_three_maxima(counts, ORBM_HISTO_LENGTH, &ind1, &ind2, &ind3);
+        for (int i = 0; i < ORBM_HISTO_LENGTH; i++)
+            if (i != ind1 && i != ind2 && i != ind3)
+                for (int idx : rotHist[i]) { curAssign[idx] = -1; nmatches--; }
+    }
+    *nmatchesOut = nmatches;
+    return ORBX_OK;
+}
+
+// ORBmatcher::SearchByProjection(F, vpMapPoints, th), src/ORBmatcher.cc:45-129
+int orbm_search_by_projection_points(orbm_t* m, const orbm_frame* F, const orbm_mappoint* pts, int npts,
+                                     const int32_t* frameObs, float th, float nnratio, int32_t* frameAssign,
+                                     int* nmatchesOut) {
+    if (!m || !F || (!pts && npts) || !frameObs || !frameAssign || !nmatchesOut) return ORBX_E_INVALID;
+    std::lock_guard<std::mutex> lk(m->mtx);
+    CKM(cudaSetDevice(m->device));
+    DeviceFrame d;
+    int rc = upload_frame(m, F, d);
+    if (rc) return rc;
+    const bool bFactor = th != 1.0;
+    struct Q { int i; float rs; };
+    std::vector<Q> meta; std::vector<WQuery> queries;
+    for (int i = 0; i < npts; i++) {
+        const orbm_mappoint& p = pts[i];
+        if (!p.trackInView) continue;
+        if (p.bad) continue;
+        const int lvl = p.trackScaleLevel;
+        float r = p.trackViewCos > 0.998 ? 2.5f : 4.0f;                        // RadiusByViewingCos, :131-137
+        if (bFactor) r *= th;
+        WQuery q; std::memset(&q, 0, sizeof(q));
+        q.x = p.trackProjX; q.y = p.trackProjY; q.r = r * F->scaleFactors[lvl]; q.minLevel = lvl - 1; q.maxLevel = lvl;
+        set_desc(q, p.descriptor);
+        queries.push_back(q); meta.push_back(Q{i, r * F->scaleFactors[lvl]});
+    }
+    std::vector<int32_t> offs; std::vector<int2> pairs;
+    if ((rc = run_queries(m, d, queries, offs, pairs))) return rc;
+    int nmatches = 0;
+    std::vector<int> obs(frameObs, frameObs + F->N);
+    for (int i = 0; i < F->N; i++) frameAssign[i] = -2;
+    for (size_t qi = 0; qi < queries.size(); qi++) {
+        if (offs[qi + 1] == offs[qi]) continue;
+        const orbm_mappoint& p = pts[meta[qi].i];
+        int bestDist = 256, bestLevel = -1, bestDist2 = 256, bestLevel2 = -1, bestIdx = -1;
+        for (int k = offs[qi]; k < offs[qi + 1]; k++) {
+            const int idx = pairs[k].x;
+            if (obs[idx] > 0) continue;                                        // :87-89
+            if (F->uRight && F->uRight[idx] > 0) {
+                const float er = fabsf(p.trackProjXR - F->uRight[idx]);
+                if (er > meta[qi].rs) continue;
+            }
+            const int dist = pairs[k].y;
+            if (dist < bestDist) {
+                bestDist2 = bestDist; bestDist = dist; bestLevel2 = bestLevel; bestLevel = F->keysUn[idx].octave; bestIdx = idx;
+            } else if (dist < bestDist2) { bestLevel2 = F->keysUn[idx].octave; bestDist2 = dist; }
+        }
+        if (bestDist <= ORBM_TH_HIGH) {
+            if (bestLevel == bestLevel2 && bestDist > nnratio * bestDist2) continue;
+            frameAssign[bestIdx] = meta[qi].i; obs[bestIdx] = p.observations;
+            nmatches++;
+        }
+    }
+    *nmatchesOut = nmatches;
+    return ORBX_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,191 @@
+"""Python mirror of the ORBmatcher Hamming hot path and the Frame grid over the C ABI of include/orbm.h
+(reference include/ORBmatcher.h:37-102, include/Frame.h:87-89,161)."""
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+
+from ._lib import KEYPOINT_DTYPE, check, lib
+
+TH_HIGH, TH_LOW, HISTO_LENGTH = 100, 50, 30
+FRAME_GRID_ROWS, FRAME_GRID_COLS = 48, 64
+
+TOP2_DTYPE = np.dtype([("i1", "<u4"), ("d1", "<u2"), ("d2", "<u2")])
+MAPPOINT_DTYPE = np.dtype([
+    ("world", "<f4", 3), ("observations", "<i4"), ("descriptor", "u1", 32), ("valid", "u1"), ("bad", "u1"),
+    ("outlier", "u1"), ("trackInView", "u1"), ("trackProjX", "<f4"), ("trackProjY", "<f4"), ("trackProjXR", "<f4"),
+    ("trackViewCos", "<f4"), ("trackScaleLevel", "<i4")])
+assert MAPPOINT_DTYPE.itemsize == 72
+
+
+class FrameStruct(C.Structure):
+    _fields_ = [("N", C.c_int32), ("keys", C.c_void_p), ("keysUn", C.c_void_p), ("descriptors", C.c_void_p),
+                ("uRight", C.c_void_p), ("mnMinX", C.c_float), ("mnMaxX", C.c_float), ("mnMinY", C.c_float),
+                ("mnMaxY", C.c_float), ("gridElementWidthInv", C.c_float), ("gridElementHeightInv", C.c_float),
+                ("fx", C.c_float), ("fy", C.c_float), ("cx", C.c_float), ("cy", C.c_float), ("bf", C.c_float),
+                ("b", C.c_float), ("Tcw", C.c_float * 16), ("scaleFactors", C.c_void_p), ("nScaleLevels", C.c_int32)]
+
+
+class Frame:
+    """The members of ORB_SLAM2::Frame the matcher reads (include/Frame.h), as numpy arrays."""
+
+    def __init__(self, keys, descriptors, width, height, scale_factors, *, keys_un=None, u_right=None, K=None,
+                 bf=0.0, Tcw=None):
+        self.mvKeys = np.ascontiguousarray(keys, KEYPOINT_DTYPE)
+        self.mvKeysUn = self.mvKeys if keys_un is None else np.ascontiguousarray(keys_un, KEYPOINT_DTYPE)
+        self.mDescriptors = np.ascontiguousarray(descriptors, np.uint8).reshape(-1, 32)
+        self.N = len(self.mvKeys)
+        self.mvuRight = None if u_right is None else np.ascontiguousarray(u_right, np.float32)
+        # ComputeImageBounds without distortion (src/Frame.cc:606-612) and the grid scale (:126-127)
+        self.mnMinX, self.mnMaxX, self.mnMinY, self.mnMaxY = np.float32(0), np.float32(width), np.float32(0), np.float32(height)
+        self.mfGridElementWidthInv = np.float32(FRAME_GRID_COLS) / (self.mnMaxX - self.mnMinX)
+        self.mfGridElementHeightInv = np.float32(FRAME_GRID_ROWS) / (self.mnMaxY - self.mnMinY)
+        K = np.eye(3, dtype=np.float32) if K is None else np.asarray(K, np.float32)
+        self.fx, self.fy, self.cx, self.cy = K[0, 0], K[1, 1], K[0, 2], K[1, 2]
+        self.mbf = np.float32(bf)
+        self.mb = np.float32(self.mbf / self.fx)
+        self.mTcw = np.eye(4, dtype=np.float32) if Tcw is None else np.ascontiguousarray(Tcw, np.float32)
+        self.mvScaleFactors = np.ascontiguousarray(scale_factors, np.float32)
+
+    def struct(self) -> FrameStruct:
+        s = FrameStruct()
+        s.N = self.N
+        s.keys = self.mvKeys.ctypes.data; s.keysUn = self.mvKeysUn.ctypes.data
+        s.descriptors = self.mDescriptors.ctypes.data
+        s.uRight = None if self.mvuRight is None else self.mvuRight.ctypes.data
+        s.mnMinX, s.mnMaxX, s.mnMinY, s.mnMaxY = float(self.mnMinX), float(self.mnMaxX), float(self.mnMinY), float(self.mnMaxY)
+        s.gridElementWidthInv = float(self.mfGridElementWidthInv); s.gridElementHeightInv = float(self.mfGridElementHeightInv)
+        s.fx, s.fy, s.cx, s.cy, s.bf, s.b = (float(v) for v in (self.fx, self.fy, self.cx, self.cy, self.mbf, self.mb))
+        s.Tcw = (C.c_float * 16)(*self.mTcw.ravel().tolist())
+        s.scaleFactors = self.mvScaleFactors.ctypes.data; s.nScaleLevels = len(self.mvScaleFactors)
+        return s
+
+
+def _bind(L):
+    if getattr(L, "_orbm_bound", False):
+        return
+    vp, i, f, sz = C.c_void_p, C.c_int, C.c_float, C.c_size_t
+    L.orbm_create.argtypes = [C.POINTER(vp), i]; L.orbm_create.restype = i
+    L.orbm_destroy.argtypes = [vp]; L.orbm_destroy.restype = None
+    L.orbm_stream.argtypes = [vp]; L.orbm_stream.restype = vp
+    L.orbm_synchronize.argtypes = [vp]; L.orbm_synchronize.restype = i
+    L.orbm_descriptor_distance.argtypes = [vp, vp]; L.orbm_descriptor_distance.restype = i
+    L.orbm_three_maxima.argtypes = [vp, i, C.POINTER(i), C.POINTER(i), C.POINTER(i)]; L.orbm_three_maxima.restype = None
+    L.orbm_bf2nn_device.argtypes = [vp, vp, i, vp, sz, C.c_uint32, vp]; L.orbm_bf2nn_device.restype = i
+    L.orbm_merge_top2_device.argtypes = [vp, vp, i, i, vp]; L.orbm_merge_top2_device.restype = i
+    L.orbm_bf2nn.argtypes = [vp, vp, i, vp, sz, C.c_uint32, vp]; L.orbm_bf2nn.restype = i
+    L.orbm_popc_peak.argtypes = [vp, C.POINTER(C.c_double)]; L.orbm_popc_peak.restype = i
+    L.orbm_grid_build.argtypes = [vp, vp, vp, vp]; L.orbm_grid_build.restype = i
+    L.orbm_features_in_area.argtypes = [vp, vp, f, f, f, i, i, vp, i, C.POINTER(i)]; L.orbm_features_in_area.restype = i
+    L.orbm_search_for_initialization.argtypes = [vp, vp, vp, vp, vp, i, f, i, C.POINTER(i)]
+    L.orbm_search_for_initialization.restype = i
+    L.orbm_search_by_projection_frame.argtypes = [vp, vp, vp, vp, vp, f, i, i, vp, C.POINTER(i)]
+    L.orbm_search_by_projection_frame.restype = i
+    L.orbm_search_by_projection_points.argtypes = [vp, vp, vp, i, vp, f, f, vp, C.POINTER(i)]
+    L.orbm_search_by_projection_points.restype = i
+    L._orbm_bound = True
+
+
+class MatcherContext:
+    """Device context shared by ORBmatcher objects of one host thread (orbm_create)."""
+
+    def __init__(self, device: int = 0):
+        self._L = lib(); _bind(self._L)
+        h = C.c_void_p()
+        check(self._L.orbm_create(C.byref(h), device), "orbm_create")
+        self.h = h
+
+    def close(self):
+        if getattr(self, "h", None):
+            self._L.orbm_destroy(self.h); self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def popc_peak(self) -> float:
+        v = C.c_double()
+        check(self._L.orbm_popc_peak(self.h, C.byref(v)), "orbm_popc_peak")
+        return v.value
+
+    def grid_build(self, F: Frame):
+        cs = np.zeros(FRAME_GRID_COLS * FRAME_GRID_ROWS + 1, np.int32); items = np.zeros(max(F.N, 1), np.int32)
+        s = F.struct()
+        check(self._L.orbm_grid_build(self.h, C.byref(s), cs.ctypes.data, items.ctypes.data), "orbm_grid_build")
+        return cs, items[: cs[-1]]
+
+    def features_in_area(self, F: Frame, x, y, r, minLevel=-1, maxLevel=-1):
+        out = np.zeros(max(F.N, 1), np.int32); n = C.c_int()
+        s = F.struct()
+        check(self._L.orbm_features_in_area(self.h, C.byref(s), x, y, r, minLevel, maxLevel, out.ctypes.data, len(out),
+                                            C.byref(n)), "orbm_features_in_area")
+        return out[: n.value].copy()
+
+    def bf2nn(self, queries: np.ndarray, d_db_ptr: int, ndb: int, idx_base: int = 0) -> np.ndarray:
+        q = np.ascontiguousarray(queries, np.uint8).reshape(-1, 32)
+        out = np.zeros(len(q), TOP2_DTYPE)
+        check(self._L.orbm_bf2nn(self.h, q.ctypes.data, len(q), d_db_ptr, ndb, idx_base, out.ctypes.data), "orbm_bf2nn")
+        return out
+
+
+class ORBmatcher:
+    """ORBmatcher(nnratio=0.6, checkOri=True) — construction is free, as in the reference."""
+    TH_HIGH, TH_LOW, HISTO_LENGTH = TH_HIGH, TH_LOW, HISTO_LENGTH
+
+    def __init__(self, nnratio: float = 0.6, checkOri: bool = True, context: MatcherContext | None = None):
+        self.mfNNratio = float(np.float32(nnratio)); self.mbCheckOrientation = bool(checkOri)
+        self.ctx = context
+
+    def _c(self):
+        if self.ctx is None:
+            self.ctx = MatcherContext()
+        return self.ctx
+
+    @staticmethod
+    def DescriptorDistance(a: np.ndarray, b: np.ndarray) -> int:
+        L = lib(); _bind(L)
+        a = np.ascontiguousarray(a, np.uint8); b = np.ascontiguousarray(b, np.uint8)
+        return L.orbm_descriptor_distance(a.ctypes.data, b.ctypes.data)
+
+    @staticmethod
+    def ComputeThreeMaxima(counts):
+        L = lib(); _bind(L)
+        c = np.ascontiguousarray(counts, np.int32)
+        i1, i2, i3 = C.c_int(-1), C.c_int(-1), C.c_int(-1)
+        L.orbm_three_maxima(c.ctypes.data, len(c), C.byref(i1), C.byref(i2), C.byref(i3))
+        return i1.value, i2.value, i3.value
+
+    def SearchForInitialization(self, F1: Frame, F2: Frame, vbPrevMatched: np.ndarray, windowSize: int = 10):
+        """returns (nmatches, vnMatches12); vbPrevMatched (N1 x 2 float32) is updated in place"""
+        c = self._c()
+        assert vbPrevMatched.dtype == np.float32 and vbPrevMatched.flags.c_contiguous
+        m12 = np.zeros(max(F1.N, 1), np.int32); n = C.c_int()
+        s1, s2 = F1.struct(), F2.struct()
+        check(c._L.orbm_search_for_initialization(c.h, C.byref(s1), C.byref(s2), vbPrevMatched.ctypes.data, m12.ctypes.data,
+                                                  windowSize, self.mfNNratio, int(self.mbCheckOrientation), C.byref(n)),
+              "orbm_search_for_initialization")
+        return n.value, m12[: F1.N]
+
+    def SearchByProjectionFrame(self, CurrentFrame: Frame, LastFrame: Frame, last_points: np.ndarray,
+                                cur_observations: np.ndarray, th: float, bMono: bool):
+        c = self._c()
+        lp = np.ascontiguousarray(last_points, MAPPOINT_DTYPE); co = np.ascontiguousarray(cur_observations, np.int32)
+        out = np.zeros(max(CurrentFrame.N, 1), np.int32); n = C.c_int()
+        sc, sl = CurrentFrame.struct(), LastFrame.struct()
+        check(c._L.orbm_search_by_projection_frame(c.h, C.byref(sc), C.byref(sl), lp.ctypes.data, co.ctypes.data, th,
+                                                   int(bMono), int(self.mbCheckOrientation), out.ctypes.data, C.byref(n)),
+              "orbm_search_by_projection_frame")
+        return n.value, out[: CurrentFrame.N]
+
+    def SearchByProjectionPoints(self, F: Frame, points: np.ndarray, frame_observations: np.ndarray, th: float = 3.0):
+        c = self._c()
+        p = np.ascontiguousarray(points, MAPPOINT_DTYPE); fo = np.ascontiguousarray(frame_observations, np.int32)
+        out = np.zeros(max(F.N, 1), np.int32); n = C.c_int()
+        s = F.struct()
+        check(c._L.orbm_search_by_projection_points(c.h, C.byref(s), p.ctypes.data, len(p), fo.ctypes.data, th,
+                                                    self.mfNNratio, out.ctypes.data, C.byref(n)),
+              "orbm_search_by_projection_points")
+        return n.value, out[: F.N]

@@ -134,3 +134,80 @@ class RefExtractor:
         out = np.zeros((h.value + 2 * border, w.value + 2 * border), np.uint8)
         self.L.orbref_get_level(self.h, l, border, out.ctypes.data, out.strides[0])
         return out
+
+
+# ---------------- matcher / grid oracle (oracle/orb_oracle_matcher.cc) ----------------
+def _bind_matcher(L):
+    if getattr(L, "_m_bound", False):
+        return L
+    vp, i, f = C.c_void_p, C.c_int, C.c_float
+    L.orbo_descriptor_distance.argtypes = [vp, vp]
+    L.orbo_three_maxima.argtypes = [vp, i, vp, vp, vp]
+    L.orbo_grid_build.argtypes = [vp, vp, vp]
+    L.orbo_features_in_area.argtypes = [vp, f, f, f, i, i, vp, i]
+    L.orbo_search_for_initialization.argtypes = [vp, vp, vp, vp, i, f, i]
+    L.orbo_search_by_projection_frame.argtypes = [vp, vp, vp, vp, f, i, i, vp]
+    L.orbo_search_by_projection_points.argtypes = [vp, vp, i, vp, f, f, vp]
+    L.orbo_bf2nn.argtypes = [vp, i, vp, C.c_size_t, C.c_uint32, vp]
+    L._m_bound = True
+    return L
+
+
+class OracleMatcher:
+    """CPU oracle with the ORBmatcher call shape; frames are orb_slam_b200.matcher.Frame objects
+    (plain data carriers: the struct layout of include/orbm.h)."""
+
+    def __init__(self, nnratio=0.6, checkOri=True):
+        self.L = _bind_matcher(oracle())
+        self.nnratio = float(np.float32(nnratio)); self.checkOri = bool(checkOri)
+
+    def DescriptorDistance(self, a, b):
+        a = np.ascontiguousarray(a, np.uint8); b = np.ascontiguousarray(b, np.uint8)
+        return self.L.orbo_descriptor_distance(a.ctypes.data, b.ctypes.data)
+
+    def ComputeThreeMaxima(self, counts):
+        c = np.ascontiguousarray(counts, np.int32)
+        a, b, d = C.c_int(-1), C.c_int(-1), C.c_int(-1)
+        self.L.orbo_three_maxima(c.ctypes.data, len(c), C.byref(a), C.byref(b), C.byref(d))
+        return a.value, b.value, d.value
+
+    def grid_build(self, F):
+        cs = np.zeros(64 * 48 + 1, np.int32); items = np.zeros(max(F.N, 1), np.int32)
+        s = F.struct()
+        self.L.orbo_grid_build(C.byref(s), cs.ctypes.data, items.ctypes.data)
+        return cs, items[: cs[-1]]
+
+    def features_in_area(self, F, x, y, r, minLevel=-1, maxLevel=-1):
+        out = np.zeros(max(F.N, 1), np.int32)
+        s = F.struct()
+        n = self.L.orbo_features_in_area(C.byref(s), x, y, r, minLevel, maxLevel, out.ctypes.data, len(out))
+        return out[:n].copy()
+
+    def SearchForInitialization(self, F1, F2, prev, windowSize=10):
+        m12 = np.zeros(max(F1.N, 1), np.int32)
+        s1, s2 = F1.struct(), F2.struct()
+        n = self.L.orbo_search_for_initialization(C.byref(s1), C.byref(s2), prev.ctypes.data, m12.ctypes.data, windowSize,
+                                                  self.nnratio, int(self.checkOri))
+        return n, m12[: F1.N]
+
+    def SearchByProjectionFrame(self, cur, last, last_points, cur_obs, th, bMono):
+        out = np.zeros(max(cur.N, 1), np.int32)
+        sc, sl = cur.struct(), last.struct()
+        lp = np.ascontiguousarray(last_points); co = np.ascontiguousarray(cur_obs, np.int32)
+        n = self.L.orbo_search_by_projection_frame(C.byref(sc), C.byref(sl), lp.ctypes.data, co.ctypes.data, th, int(bMono),
+                                                   int(self.checkOri), out.ctypes.data)
+        return n, out[: cur.N]
+
+    def SearchByProjectionPoints(self, F, points, frame_obs, th=3.0):
+        out = np.zeros(max(F.N, 1), np.int32)
+        s = F.struct()
+        p = np.ascontiguousarray(points); fo = np.ascontiguousarray(frame_obs, np.int32)
+        n = self.L.orbo_search_by_projection_points(C.byref(s), p.ctypes.data, len(p), fo.ctypes.data, th, self.nnratio,
+                                                    out.ctypes.data)
+        return n, out[: F.N]
+
+    def bf2nn(self, q, db, idx_base=0):
+        q = np.ascontiguousarray(q, np.uint8).reshape(-1, 32); db = np.ascontiguousarray(db, np.uint8).reshape(-1, 32)
+        out = np.zeros(len(q), np.dtype([("i1", "<u4"), ("d1", "<u2"), ("d2", "<u2")]))
+        self.L.orbo_bf2nn(q.ctypes.data, len(q), db.ctypes.data, len(db), idx_base, out.ctypes.data)
+        return out
