@@ -59,9 +59,7 @@ int orbm_merge_top2_device(orbm_t* m, const orbm_top2* d_parts, int nparts, int 
 int orbm_bf2nn(orbm_t* m, const uint8_t* queries, int nq, const uint8_t* d_db, size_t ndb,
                uint32_t idx_base, orbm_top2* out);
 /* The acceptance of src/ORBmatcher.cc:228-230 applied to a top-2 result. */
-static inline int orbm_accept_low_ratio(orbm_top2 r, float nnratio) {
-    return r.d1 <= ORBM_TH_LOW && (float)r.d1 < nnratio * (float)r.d2;
-}
+int orbm_accept_low_ratio(orbm_top2 r, float nnratio);
 /* measured integer-pipe peak: 32-bit popc per second of this GPU (microbenchmark) */
 int orbm_popc_peak(orbm_t* m, double* popc_per_s);
 

@@ -165,6 +165,10 @@ int orbm_bf2nn(orbm_t* m, const uint8_t* queries, int nq, const uint8_t* d_db, s
     return ORBX_OK;
 }
 
+int orbm_accept_low_ratio(orbm_top2 r, float nnratio) {
+    return r.d1 <= ORBM_TH_LOW && (float)r.d1 < nnratio * (float)r.d2;
+}
+
 int orbm_popc_peak(orbm_t* m, double* popc_per_s) {
     if (!m || !popc_per_s) return ORBX_E_INVALID;
     std::lock_guard<std::mutex> lk(m->mtx);
