@@ -1,0 +1,157 @@
+// B200 implementations of the ORBmatcher Hamming hot path, as member functions of the reference's own class:
+//   ORBmatcher::DescriptorDistance                       src/ORBmatcher.cc:1728-1744
+//   ORBmatcher::SearchForInitialization                  :417-588
+//   ORBmatcher::SearchByProjection(Frame&, const Frame&) :1396-1538
+//   ORBmatcher::SearchByProjection(Frame&, MapPoints)    :45-129
+// Compiled against the reference's ORBmatcher.h / Frame.h / MapPoint.h inside the ORB-SLAM2 tree (delete these four
+// bodies from src/ORBmatcher.cc) or against host/lite/*.h in this repository.  Each function
+// marshals the members the reference loop reads into the plain structs of include/orbm.h, calls the C ABI (device:
+// grid build, GetFeaturesInArea enumeration, Hamming distances; host: the order-dependent acceptance replay) and
+// writes the results back into the same members the reference writes.
+#include "ORBmatcher.h"
+
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <memory>
+
+#include "b200_context.h"
+#include "orbm.h"
+
+namespace ORB_SLAM2 {
+
+namespace b200 {
+
+void Check(int rc, const char* what) {
+    if (rc == ORBX_OK) return;
+    std::fprintf(stderr, "ORB_SLAM2 (B200 matcher): %s failed: %s (code %d)\n", what, orbx_error_string(rc), rc);
+    std::abort();
+}
+
+namespace {
+struct Ctx {
+    orbm_t* m = nullptr;
+    ~Ctx() { if (m) orbm_destroy(m); }
+};
+}  // namespace
+
+orbm_t* MatcherContext() {
+    static thread_local Ctx ctx;
+    if (!ctx.m) {
+        const char* e = std::getenv("ORB_B200_DEVICE");
+        Check(orbm_create(&ctx.m, e ? std::atoi(e) : 0), "orbm_create");
+    }
+    return ctx.m;
+}
+
+void FillFrame(orbm_frame& f, const Frame& F) {
+    std::memset(&f, 0, sizeof(f));
+    f.N = F.N;
+    f.keys = (const orbx_keypoint*)F.mvKeys.data();
+    f.keysUn = (const orbx_keypoint*)F.mvKeysUn.data();
+    assert(F.N == 0 || (F.mDescriptors.isContinuous() && F.mDescriptors.cols == 32));
+    f.descriptors = F.mDescriptors.data;
+    f.uRight = F.mvuRight.empty() ? nullptr : F.mvuRight.data();
+    f.mnMinX = Frame::mnMinX; f.mnMaxX = Frame::mnMaxX; f.mnMinY = Frame::mnMinY; f.mnMaxY = Frame::mnMaxY;
+    f.gridElementWidthInv = Frame::mfGridElementWidthInv; f.gridElementHeightInv = Frame::mfGridElementHeightInv;
+    f.fx = Frame::fx; f.fy = Frame::fy; f.cx = Frame::cx; f.cy = Frame::cy; f.bf = F.mbf; f.b = F.mb;
+    if (!F.mTcw.empty())
+        for (int r = 0; r < 4; r++)
+            for (int c = 0; c < 4; c++) f.Tcw[4 * r + c] = F.mTcw.at<float>(r, c);
+    f.scaleFactors = F.mvScaleFactors.data();
+    f.nScaleLevels = (int)F.mvScaleFactors.size();
+}
+
+static void FillPoint(orbm_mappoint& p, MapPoint* pMP) {
+    std::memset(&p, 0, sizeof(p));
+    if (!pMP) return;
+    p.valid = 1;
+    const cv::Mat x3Dw = pMP->GetWorldPos();
+    p.world[0] = x3Dw.at<float>(0); p.world[1] = x3Dw.at<float>(1); p.world[2] = x3Dw.at<float>(2);
+    p.observations = pMP->Observations();
+    const cv::Mat d = pMP->GetDescriptor();
+    std::memcpy(p.descriptor, d.data, 32);
+    p.bad = pMP->isBad();
+    p.trackInView = pMP->mbTrackInView;
+    p.trackProjX = pMP->mTrackProjX; p.trackProjY = pMP->mTrackProjY; p.trackProjXR = pMP->mTrackProjXR;
+    p.trackViewCos = pMP->mTrackViewCos; p.trackScaleLevel = pMP->mnTrackScaleLevel;
+}
+
+static void Observations(const Frame& F, std::vector<int32_t>& obs) {
+    obs.resize(F.N);
+    for (int i = 0; i < F.N; i++) obs[i] = F.mvpMapPoints[i] ? F.mvpMapPoints[i]->Observations() : -1;
+}
+
+}  // namespace b200
+
+int ORBmatcher::DescriptorDistance(const cv::Mat& a, const cv::Mat& b) {
+    return orbm_descriptor_distance(a.ptr<uint8_t>(), b.ptr<uint8_t>());
+}
+
+int ORBmatcher::SearchForInitialization(Frame& F1, Frame& F2, std::vector<cv::Point2f>& vbPrevMatched,
+                                        std::vector<int>& vnMatches12, int windowSize) {
+    orbm_frame f1, f2;
+    b200::FillFrame(f1, F1); b200::FillFrame(f2, F2);
+    vnMatches12 = std::vector<int>(F1.mvKeysUn.size(), -1);                 // :420
+    static_assert(sizeof(cv::Point2f) == 8, "Point2f is two floats");
+    int nmatches = 0;
+    b200::Check(orbm_search_for_initialization(b200::MatcherContext(), &f1, &f2, (float*)vbPrevMatched.data(),
+                                               vnMatches12.data(), windowSize, mfNNratio, mbCheckOrientation, &nmatches),
+                "orbm_search_for_initialization");
+    return nmatches;
+}
+
+int ORBmatcher::SearchByProjection(Frame& CurrentFrame, const Frame& LastFrame, const float th, const bool bMono) {
+    orbm_frame cur, last;
+    b200::FillFrame(cur, CurrentFrame); b200::FillFrame(last, LastFrame);
+    std::vector<orbm_mappoint> pts(LastFrame.N);
+    for (int i = 0; i < LastFrame.N; i++) {
+        b200::FillPoint(pts[i], LastFrame.mvpMapPoints[i]);
+        pts[i].outlier = LastFrame.mvbOutlier[i];
+    }
+    std::vector<int32_t> obs, assign(CurrentFrame.N, -2);
+    b200::Observations(CurrentFrame, obs);
+    int nmatches = 0;
+    b200::Check(orbm_search_by_projection_frame(b200::MatcherContext(), &cur, &last, pts.data(), obs.data(), th, bMono,
+                                                mbCheckOrientation, assign.data(), &nmatches),
+                "orbm_search_by_projection_frame");
+    for (int i2 = 0; i2 < CurrentFrame.N; i2++) {
+        if (assign[i2] >= 0) CurrentFrame.mvpMapPoints[i2] = LastFrame.mvpMapPoints[assign[i2]];     // :1496
+        else if (assign[i2] == -1) CurrentFrame.mvpMapPoints[i2] = static_cast<MapPoint*>(NULL);     // :1530
+    }
+    return nmatches;
+}
+
+int ORBmatcher::SearchByProjection(Frame& F, const std::vector<MapPoint*>& vpMapPoints, const float th) {
+    orbm_frame f;
+    b200::FillFrame(f, F);
+    std::vector<orbm_mappoint> pts(vpMapPoints.size());
+    for (size_t i = 0; i < vpMapPoints.size(); i++) b200::FillPoint(pts[i], vpMapPoints[i]);
+    std::vector<int32_t> obs, assign(F.N, -2);
+    b200::Observations(F, obs);
+    int nmatches = 0;
+    b200::Check(orbm_search_by_projection_points(b200::MatcherContext(), &f, pts.data(), (int)pts.size(), obs.data(), th,
+                                                 mfNNratio, assign.data(), &nmatches),
+                "orbm_search_by_projection_points");
+    for (int idx = 0; idx < F.N; idx++)
+        if (assign[idx] >= 0) F.mvpMapPoints[idx] = vpMapPoints[assign[idx]];                       // :123
+    return nmatches;
+}
+
+#ifdef ORB_B200_STANDALONE
+// The rest of the class lives in the reference's src/ORBmatcher.cc; in the stand-alone build of this repository
+// the pieces the accelerated functions depend on are provided here.
+const int ORBmatcher::TH_HIGH = ORBM_TH_HIGH;
+const int ORBmatcher::TH_LOW = ORBM_TH_LOW;
+const int ORBmatcher::HISTO_LENGTH = ORBM_HISTO_LENGTH;
+ORBmatcher::ORBmatcher(float nnratio, bool checkOri) : mfNNratio(nnratio), mbCheckOrientation(checkOri) {}
+float ORBmatcher::RadiusByViewingCos(const float& viewCos) { return viewCos > 0.998 ? 2.5f : 4.0f; }
+void ORBmatcher::ComputeThreeMaxima(std::vector<int>* histo, const int L, int& ind1, int& ind2, int& ind3) {
+    std::vector<int32_t> counts(L);
+    for (int i = 0; i < L; i++) counts[i] = (int32_t)histo[i].size();
+    ind1 = ind2 = ind3 = -1;
+    orbm_three_maxima(counts.data(), L, &ind1, &ind2, &ind3);
+}
+#endif
+
+}  // namespace ORB_SLAM2

@@ -1,0 +1,37 @@
+// Stand-in for ORB_SLAM2::MapPoint exposing exactly the members the accelerated ORBmatcher functions read
+// (reference include/MapPoint.h:37-150), with the reference's names and types.  Used only to build and test
+// ORBmatcher_b200.cc in this repository, where the real MapPoint.h (-> KeyFrame.h -> DBoW2 -> full OpenCV)
+// cannot be compiled; inside the ORB-SLAM2 tree the real header is used instead.
+#ifndef MAPPOINT_H
+#define MAPPOINT_H
+#include <opencv2/core/core.hpp>
+
+namespace ORB_SLAM2 {
+
+class MapPoint {
+public:
+    MapPoint() : mTrackProjX(0), mTrackProjY(0), mTrackProjXR(0), mbTrackInView(false), mnTrackScaleLevel(0),
+                 mTrackViewCos(0), mnLastFrameSeen(0), mWorldPos(3, 1, CV_32F), mDescriptor(1, 32, CV_8U), nObs(0), mbBad(false) {}
+    cv::Mat GetWorldPos() { return mWorldPos.clone(); }
+    cv::Mat GetDescriptor() { return mDescriptor.clone(); }
+    int Observations() { return nObs; }
+    bool isBad() { return mbBad; }
+
+    // Variables used by the tracking (include/MapPoint.h:92-99)
+    float mTrackProjX;
+    float mTrackProjY;
+    float mTrackProjXR;
+    bool mbTrackInView;
+    int mnTrackScaleLevel;
+    float mTrackViewCos;
+    long unsigned int mnLastFrameSeen;
+
+    // test access (protected in the reference)
+    cv::Mat mWorldPos;
+    cv::Mat mDescriptor;
+    int nObs;
+    bool mbBad;
+};
+
+}  // namespace ORB_SLAM2
+#endif

@@ -1,0 +1,37 @@
+// Declaration of ORB_SLAM2::ORBmatcher as in the reference (include/ORBmatcher.h:37-102), restricted to what can be
+// declared without DBoW2 / the full OpenCV API.  Only used for the in-repo build of ORBmatcher_b200.cc; inside the
+// ORB-SLAM2 tree the reference's own ORBmatcher.h is used unchanged.
+#ifndef ORBMATCHER_H
+#define ORBMATCHER_H
+#include <set>
+#include <vector>
+#include <opencv2/core/core.hpp>
+#include "MapPoint.h"
+#include "KeyFrame.h"
+#include "Frame.h"
+
+namespace ORB_SLAM2 {
+
+class ORBmatcher {
+public:
+    ORBmatcher(float nnratio = 0.6, bool checkOri = true);
+    static int DescriptorDistance(const cv::Mat& a, const cv::Mat& b);
+    int SearchByProjection(Frame& F, const std::vector<MapPoint*>& vpMapPoints, const float th = 3);
+    int SearchByProjection(Frame& CurrentFrame, const Frame& LastFrame, const float th, const bool bMono);
+    int SearchForInitialization(Frame& F1, Frame& F2, std::vector<cv::Point2f>& vbPrevMatched,
+                                std::vector<int>& vnMatches12, int windowSize = 10);
+    // SearchByProjection(Frame&, KeyFrame*, ...), SearchByProjection(KeyFrame*, Scw, ...), SearchByBoW x2,
+    // SearchForTriangulation, SearchBySim3, Fuse x2: SURVEY 8(f) "next" rows - they stay the reference's own code.
+public:
+    static const int TH_LOW;
+    static const int TH_HIGH;
+    static const int HISTO_LENGTH;
+protected:
+    float RadiusByViewingCos(const float& viewCos);
+    void ComputeThreeMaxima(std::vector<int>* histo, const int L, int& ind1, int& ind2, int& ind3);
+    float mfNNratio;
+    bool mbCheckOrientation;
+};
+
+}  // namespace ORB_SLAM2
+#endif

@@ -1,0 +1,177 @@
+// Test harness (tests/ only): drives the C++ drop-in classes ORB_SLAM2::ORBextractor / ORBmatcher / Frame the way
+// Frame.cc and Tracking.cc drive the reference's (Frame::ExtractORB src/Frame.cc:320-326; Tracking.cc:635-644,
+// :921-944, :1236-1243), and hands the results to pytest as plain arrays.
+#include <cstring>
+#include <memory>
+#include <thread>
+#include <vector>
+
+#include "ORBextractor.h"
+#include "ORBmatcher.h"
+#include "orbm.h"
+
+using namespace ORB_SLAM2;
+
+static std::unique_ptr<Frame> frame_from(const orbm_frame* f) {
+    std::unique_ptr<Frame> F(new Frame());
+    F->N = f->N;
+    F->mvKeys.assign((const cv::KeyPoint*)f->keys, (const cv::KeyPoint*)f->keys + f->N);
+    F->mvKeysUn.assign((const cv::KeyPoint*)f->keysUn, (const cv::KeyPoint*)f->keysUn + f->N);
+    F->mDescriptors.create(f->N, 32, CV_8U);
+    if (f->N) std::memcpy(F->mDescriptors.data, f->descriptors, (size_t)f->N * 32);
+    if (f->uRight) F->mvuRight.assign(f->uRight, f->uRight + f->N); else F->mvuRight.assign(f->N, -1.0f);
+    F->mvpMapPoints.assign(f->N, static_cast<MapPoint*>(NULL));
+    F->mvbOutlier.assign(f->N, false);
+    Frame::mnMinX = f->mnMinX; Frame::mnMaxX = f->mnMaxX; Frame::mnMinY = f->mnMinY; Frame::mnMaxY = f->mnMaxY;
+    Frame::mfGridElementWidthInv = f->gridElementWidthInv; Frame::mfGridElementHeightInv = f->gridElementHeightInv;
+    Frame::fx = f->fx; Frame::fy = f->fy; Frame::cx = f->cx; Frame::cy = f->cy;
+    F->mbf = f->bf; F->mb = f->b;
+    F->mTcw.create(4, 4, CV_32F);
+    std::memcpy(F->mTcw.data, f->Tcw, 64);
+    F->mvScaleFactors.assign(f->scaleFactors, f->scaleFactors + f->nScaleLevels);
+    return F;
+}
+
+static void point_from(MapPoint& p, const orbm_mappoint& s) {
+    for (int k = 0; k < 3; k++) p.mWorldPos.at<float>(k) = s.world[k];
+    std::memcpy(p.mDescriptor.data, s.descriptor, 32);
+    p.nObs = s.observations; p.mbBad = s.bad; p.mbTrackInView = s.trackInView;
+    p.mTrackProjX = s.trackProjX; p.mTrackProjY = s.trackProjY; p.mTrackProjXR = s.trackProjXR;
+    p.mTrackViewCos = s.trackViewCos; p.mnTrackScaleLevel = s.trackScaleLevel;
+}
+
+extern "C" {
+
+// ORBextractor::operator() through the C++ class.  levels: optional buffer receiving the concatenated bordered
+// (w+38)x(h+38) buffers behind mvImagePyramid[l]; returns the keypoint count.
+int dropin_extract(const uint8_t* img, int w, int h, size_t step, int nfeatures, float sf, int nlevels, int iniTh, int minTh,
+                   cv::KeyPoint* kps, uint8_t* desc, int cap, uint8_t* levels, int* levelDims) {
+    ORBextractor ex(nfeatures, sf, nlevels, iniTh, minTh);
+    cv::Mat im(h, w, CV_8UC1, (void*)img, step);
+    std::vector<cv::KeyPoint> keys;
+    cv::Mat descriptors;
+    ex(im, cv::Mat(), keys, descriptors);
+    const int n = (int)keys.size();
+    for (int i = 0; i < n && i < cap; i++) { kps[i] = keys[i]; std::memcpy(desc + 32 * (size_t)i, descriptors.ptr(i), 32); }
+    if (levels) {
+        size_t off = 0;
+        for (int l = 0; l < ex.GetLevels(); l++) {
+            const cv::Mat& lv = ex.mvImagePyramid[l];
+            levelDims[2 * l] = lv.cols; levelDims[2 * l + 1] = lv.rows;
+            for (int r = -19; r < lv.rows + 19; r++) {
+                std::memcpy(levels + off, lv.data + (ptrdiff_t)r * (ptrdiff_t)lv.step - 19, lv.cols + 38);
+                off += lv.cols + 38;
+            }
+        }
+    }
+    return n;
+}
+
+// the stereo constructor's pattern: two extractor INSTANCES on two host threads (src/Frame.cc:94-103)
+int dropin_extract_stereo(const uint8_t* left, const uint8_t* right, int w, int h, int nfeatures, cv::KeyPoint* kl,
+                          uint8_t* dl, int* nl, cv::KeyPoint* kr, uint8_t* dr, int* nr, int cap, int reps) {
+    ORBextractor exL(nfeatures, 1.2f, 8, 20, 7), exR(nfeatures, 1.2f, 8, 20, 7);
+    std::vector<cv::KeyPoint> keysL, keysR;
+    cv::Mat descL, descR;
+    for (int r = 0; r < reps; r++) {
+        cv::Mat imL(h, w, CV_8UC1, (void*)left, (size_t)w), imR(h, w, CV_8UC1, (void*)right, (size_t)w);
+        std::thread tl([&] { exL(imL, cv::Mat(), keysL, descL); });
+        std::thread tr([&] { exR(imR, cv::Mat(), keysR, descR); });
+        tl.join(); tr.join();
+    }
+    *nl = (int)keysL.size(); *nr = (int)keysR.size();
+    for (int i = 0; i < *nl && i < cap; i++) { kl[i] = keysL[i]; std::memcpy(dl + 32 * (size_t)i, descL.ptr(i), 32); }
+    for (int i = 0; i < *nr && i < cap; i++) { kr[i] = keysR[i]; std::memcpy(dr + 32 * (size_t)i, descR.ptr(i), 32); }
+    return 0;
+}
+
+int dropin_batch(const uint8_t* imgs, int n, int w, int h, int nfeatures, cv::KeyPoint* kps, uint8_t* desc, int cap, int* counts) {
+    ORBextractor ex(nfeatures, 1.2f, 8, 20, 7);
+    std::vector<cv::Mat> images;
+    for (int i = 0; i < n; i++) images.push_back(cv::Mat(h, w, CV_8UC1, (void*)(imgs + (size_t)i * w * h), (size_t)w));
+    std::vector<std::vector<cv::KeyPoint> > keys;
+    std::vector<cv::Mat> descs;
+    ex.ExtractBatch(images, keys, descs);
+    for (int i = 0; i < n; i++) {
+        counts[i] = (int)keys[i].size();
+        for (int k = 0; k < counts[i] && k < cap; k++) {
+            kps[(size_t)i * cap + k] = keys[i][k];
+            std::memcpy(desc + ((size_t)i * cap + k) * 32, descs[i].ptr(k), 32);
+        }
+    }
+    return 0;
+}
+
+int dropin_grid(const orbm_frame* f, int32_t* cellStart, int32_t* items) {
+    std::unique_ptr<Frame> F = frame_from(f);
+    F->AssignFeaturesToGrid();
+    int n = 0;
+    for (int i = 0; i < FRAME_GRID_COLS; i++)
+        for (int j = 0; j < FRAME_GRID_ROWS; j++) {
+            cellStart[i * FRAME_GRID_ROWS + j] = n;
+            for (size_t v : F->mGrid[i][j]) items[n++] = (int32_t)v;
+        }
+    cellStart[FRAME_GRID_COLS * FRAME_GRID_ROWS] = n;
+    return n;
+}
+
+int dropin_features_in_area(const orbm_frame* f, float x, float y, float r, int minLevel, int maxLevel, int32_t* out) {
+    std::unique_ptr<Frame> F = frame_from(f);
+    const std::vector<size_t> v = F->GetFeaturesInArea(x, y, r, minLevel, maxLevel);
+    for (size_t i = 0; i < v.size(); i++) out[i] = (int32_t)v[i];
+    return (int)v.size();
+}
+
+int dropin_search_for_initialization(const orbm_frame* f1, const orbm_frame* f2, float* prev, int32_t* m12, int windowSize,
+                                     float nnratio, int checkOri) {
+    std::unique_ptr<Frame> F1 = frame_from(f1), F2 = frame_from(f2);
+    std::vector<cv::Point2f> vbPrevMatched(f1->N);
+    for (int i = 0; i < f1->N; i++) vbPrevMatched[i] = cv::Point2f(prev[2 * i], prev[2 * i + 1]);
+    std::vector<int> vnMatches12;
+    ORBmatcher matcher(nnratio, checkOri != 0);
+    const int n = matcher.SearchForInitialization(*F1, *F2, vbPrevMatched, vnMatches12, windowSize);
+    for (int i = 0; i < f1->N; i++) { m12[i] = vnMatches12[i]; prev[2 * i] = vbPrevMatched[i].x; prev[2 * i + 1] = vbPrevMatched[i].y; }
+    return n;
+}
+
+int dropin_search_by_projection_frame(const orbm_frame* cur, const orbm_frame* last, const orbm_mappoint* lp,
+                                      const int32_t* curObs, float th, int bMono, int checkOri, int32_t* assign) {
+    std::unique_ptr<Frame> C = frame_from(cur), L = frame_from(last);
+    std::vector<MapPoint> lastPts(last->N), curPts(cur->N);
+    for (int i = 0; i < last->N; i++) {
+        if (lp[i].valid) { point_from(lastPts[i], lp[i]); L->mvpMapPoints[i] = &lastPts[i]; }
+        L->mvbOutlier[i] = lp[i].outlier != 0;
+    }
+    for (int i = 0; i < cur->N; i++)
+        if (curObs[i] >= 0) { curPts[i].nObs = curObs[i]; C->mvpMapPoints[i] = &curPts[i]; }
+    std::vector<MapPoint*> before = C->mvpMapPoints;
+    ORBmatcher matcher(0.9f, checkOri != 0);
+    const int n = matcher.SearchByProjection(*C, *L, th, bMono != 0);
+    for (int i = 0; i < cur->N; i++) {
+        MapPoint* p = C->mvpMapPoints[i];
+        if (p == before[i]) assign[i] = -2;
+        else if (!p) assign[i] = -1;
+        else assign[i] = (int32_t)(p - lastPts.data());
+    }
+    return n;
+}
+
+int dropin_search_by_projection_points(const orbm_frame* f, const orbm_mappoint* pts, int npts, const int32_t* obs, float th,
+                                       float nnratio, int32_t* assign) {
+    std::unique_ptr<Frame> F = frame_from(f);
+    std::vector<MapPoint> mps(npts), held(f->N);
+    std::vector<MapPoint*> vp(npts);
+    for (int i = 0; i < npts; i++) { point_from(mps[i], pts[i]); vp[i] = &mps[i]; }
+    for (int i = 0; i < f->N; i++)
+        if (obs[i] >= 0) { held[i].nObs = obs[i]; F->mvpMapPoints[i] = &held[i]; }
+    std::vector<MapPoint*> before = F->mvpMapPoints;
+    ORBmatcher matcher(nnratio, true);
+    const int n = matcher.SearchByProjection(*F, vp, th);
+    for (int i = 0; i < f->N; i++) {
+        MapPoint* p = F->mvpMapPoints[i];
+        assign[i] = (p == before[i]) ? -2 : (int32_t)(p - mps.data());
+    }
+    return n;
+}
+
+}  // extern "C"

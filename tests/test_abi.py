@@ -46,3 +46,23 @@ def test_no_product_import_of_oracle():
         if os.path.isfile(path) and path.endswith((".py", ".cu", ".cuh", ".h", ".cc", ".cpp", "Makefile")):
             txt = open(path, errors="ignore").read()
             assert not bad.search(txt), path
+
+
+def test_cpp_dropin_library_exports_the_reference_class_symbols():
+    """liborbslam2_frontend_b200.so defines the members a reference build links against
+    (include/ORBextractor.h:45-111, include/ORBmatcher.h:41-68, include/Frame.h:87-89,202)."""
+    import subprocess
+    so = os.path.join(ROOT, "orb_slam_b200", "liborbslam2_frontend_b200.so")
+    assert os.path.exists(so), "build first (make -C orb_slam_b200/csrc/host)"
+    syms = subprocess.check_output(["nm", "-DC", "--defined-only", so], text=True)
+    for want in ["ORB_SLAM2::ORBextractor::ORBextractor(int, float, int, int, int)",
+                 "ORB_SLAM2::ORBextractor::operator()(cv::_InputArray const&, cv::_InputArray const&, std::vector<cv::KeyPoint",
+                 "ORB_SLAM2::ORBmatcher::DescriptorDistance(cv::Mat const&, cv::Mat const&)",
+                 "ORB_SLAM2::ORBmatcher::SearchForInitialization(ORB_SLAM2::Frame&, ORB_SLAM2::Frame&",
+                 "ORB_SLAM2::ORBmatcher::SearchByProjection(ORB_SLAM2::Frame&, ORB_SLAM2::Frame const&, float, bool)",
+                 "ORB_SLAM2::ORBmatcher::SearchByProjection(ORB_SLAM2::Frame&, std::vector<ORB_SLAM2::MapPoint*",
+                 "ORB_SLAM2::Frame::AssignFeaturesToGrid()",
+                 "ORB_SLAM2::Frame::GetFeaturesInArea(float const&, float const&, float const&, int, int) const",
+                 "ORB_SLAM2::Frame::PosInGrid(cv::KeyPoint const&, int&, int&)"]:
+        assert want in syms, want
+    ctypes.CDLL(so)
