@@ -127,3 +127,26 @@ def test_bruteforce_2nn_and_sharded_merge(ctx):
     # edge: fewer than two rows
     one = ctx.bf2nn(q[:3], d_db.data_ptr(), 1)
     assert (one["d2"] == 256).all() and (one["i1"] == 0).all()
+
+
+def test_sharded_database_single_rank(ctx):
+    """ShardedDatabase at world size 1 (no collective) equals the oracle scan."""
+    from orb_slam_b200.sharded import ShardedDatabase
+    db = synth_descriptors(70001, 0xDB)
+    q = db[::997].copy(); q[:, 5] ^= 0x5A
+    got = ShardedDatabase(db, 0, context=ctx).query(q)
+    assert got.tobytes() == OracleMatcher().bf2nn(q, db).tobytes()
+
+
+def test_sharded_database_nccl_two_ranks():
+    """the product's distributed path (NCCL all-gather + merge kernel) on 2 GPUs, when the box has them"""
+    import os, socket, subprocess, sys
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs >= 2 GPUs")
+    s = socket.socket(); s.bind(("127.0.0.1", 0)); port = s.getsockname()[1]; s.close()
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr", "127.0.0.1",
+           "--master-port", str(port), os.path.join(root, "tests", "dist_worker.py"), "nccl", "300001", "512"]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=600, cwd=root)
+    assert r.returncode == 0 and "DIST_OK" in r.stdout, r.stdout[-2000:] + r.stderr[-2000:]
