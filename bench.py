@@ -190,7 +190,9 @@ def run_ours(args, rank, world, local_rank):
     reps = (B + len(distinct) - 1) // len(distinct)
     host = torch.empty((B, H_, W_), dtype=torch.uint8, pin_memory=True)
     host.numpy()[:] = np.concatenate([distinct] * reps)[:B]
-    d_img = host.to(dev)
+    PITCH = (W_ + 127) // 128 * 128            # device-resident frames use a 128-byte aligned row pitch (HBM layout)
+    d_img = torch.zeros((B, H_, PITCH), dtype=torch.uint8, device=dev)
+    d_img[:, :, :W_] = host.to(dev)
 
     ex = ORBextractor(NFEAT, 1.2, 8, 20, 7, device=local_rank)
     L, h = ex._L, ex.handle
@@ -201,7 +203,7 @@ def run_ours(args, rank, world, local_rank):
     stream = torch.cuda.ExternalStream(L.orbx_stream(h), device=dev)
 
     def step_device():
-        check(L.orbx_extract_batch_device(h, d_img.data_ptr(), B, W_, H_, W_, W_ * H_, d_kps.data_ptr(),
+        check(L.orbx_extract_batch_device(h, d_img.data_ptr(), B, W_, H_, PITCH, PITCH * H_, d_kps.data_ptr(),
                                           d_desc.data_ptr(), cap, d_n.data_ptr()), "orbx_extract_batch_device")
 
     def barrier():

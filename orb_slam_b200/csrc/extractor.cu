@@ -267,8 +267,7 @@ static void pyr_smem_for(const LevelGeom& prev, const LevelGeom& cur, int& cols,
     const double sx = (double)prev.w / cur.w, sy = (double)prev.h / cur.h;
     cols = (((int)std::ceil((TW + 2 * HALO) * sx) + 3 + 16 + 16) + 15) & ~15;
     rows = (int)std::ceil((TH + 2 * HALO) * sy) + 4;
-    size_t stage = std::max((size_t)cols * rows, (size_t)TH * TW);
-    bytes = (size_t)TROWS * TS + (size_t)TROWS * TW * 2 + stage;
+    bytes = pyr_smem_bytes(false, rows, cols);
 }
 
 // Enqueue the whole pipeline for `frames` frames whose level-0 source is (src, pitch, frameStride).
@@ -290,7 +289,7 @@ static int enqueue_pipeline(orbx_extractor* e, const uint8_t* src, size_t srcPit
         if (l == 0) {
             a.src = src; a.srcFrameStride = srcFrameStride; a.srcPitch = (int)srcPitch; a.srcX0 = 0;
             a.sw = v.w; a.sh = v.h;
-            const size_t smem = (size_t)TROWS * TS + (size_t)TROWS * TW * 2 + (size_t)TH * TW;
+            const size_t smem = pyr_smem_bytes(true, 0, 0);
             pyr_level_kernel<true><<<grid, PYR_THREADS, smem, st>>>(a);
         } else {
             const LevelGeom& p = g.lv[l - 1];

@@ -8,6 +8,11 @@
 //     (GaussianBlur of the level clone, :1300-1306).
 // The level is read from HBM/L2 exactly once by its consumers on this path.
 // Integer arithmetic throughout; results are bit-exact with OpenCV 4.13.
+//
+// Instruction economy (the kernel is bound by the integer ALU pipe, not by HBM):
+// every thread works on 4 horizontally adjacent pixels held as two u16x2 registers
+// (pixels c,c+2 and c+1,c+3), shared memory is read as 32-bit words and split with
+// PRMT, and the 9-of-16 arc order statistics of FAST run on VIMNMX3.U16x2 (DPX).
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
@@ -18,9 +23,11 @@ namespace orbx {
 constexpr int TW = 128;          // tile width  (pixels)
 constexpr int TH = 32;           // tile height
 constexpr int HALO = 3;          // FAST ring radius == blur radius
-constexpr int TCOL0 = 4;         // shared-memory column of tile pixel x0 (keeps interior word-aligned)
-constexpr int TS = 144;          // shared-memory row stride of the level tile
+constexpr int TCOL0 = 4;         // shared-memory byte of tile pixel x0 in a T row (keeps 4-pixel groups word-aligned)
+constexpr int TS = 144;          // shared-memory row stride of the level tile (bytes)
 constexpr int TROWS = TH + 2 * HALO;
+constexpr int TBYTES = 136;      // T bytes written per row: byte b <-> level column x0 - 4 + b
+constexpr int HQS = 136;         // u16 stride of the horizontally resized staging rows
 constexpr int PYR_THREADS = 256;
 
 __device__ __forceinline__ int reflect101(int p, int len) {
@@ -30,58 +37,103 @@ __device__ __forceinline__ int reflect101(int p, int len) {
     return p;
 }
 
-__device__ __forceinline__ bool run9(unsigned m16) {
-    unsigned x = m16 | (m16 << 16);
-    x &= x >> 1;
-    x &= x >> 2;
-    x &= x >> 4;
-    x &= x >> 1;
-    return x != 0;
+// ---- packed helpers ---------------------------------------------------------
+// A 32-bit word w of four pixels (b0..b3) splits into E = (b0,b2) and O = (b1,b3) as u16x2 (zero-extended bytes);
+// cross(lo, hi) of two such registers is (lo.hi16, hi.lo16): the stride-2 pair straddling two words.
+__device__ __forceinline__ uint32_t pk_even(uint32_t w) { return __byte_perm(w, 0u, 0x4240); }
+__device__ __forceinline__ uint32_t pk_odd(uint32_t w) { return __byte_perm(w, 0u, 0x4341); }
+__device__ __forceinline__ uint32_t pk_cross(uint32_t lo, uint32_t hi) { return __byte_perm(lo, hi, 0x1412); }
+
+// the eight stride-2 pixel pairs around a 4-pixel group at column c that FAST and the 7-tap blur need from one row
+struct RowPairs {
+    uint32_t ol;   // (c-3, c-1)
+    uint32_t x3;   // (c-2, c  )
+    uint32_t x1;   // (c-1, c+1)
+    uint32_t em;   // (c  , c+2)
+    uint32_t om;   // (c+1, c+3)
+    uint32_t x2;   // (c+2, c+4)
+    uint32_t x4;   // (c+3, c+5)
+    uint32_t er;   // (c+4, c+6)
+};
+
+// row points at the word holding pixels c-4..c-1
+__device__ __forceinline__ RowPairs row_pairs(const uint32_t* __restrict__ row) {
+    const uint32_t L = row[0], M = row[1], R = row[2];
+    const uint32_t el = pk_even(L), ol = pk_odd(L), em = pk_even(M), om = pk_odd(M), er = pk_even(R), orr = pk_odd(R);
+    RowPairs p;
+    p.ol = ol; p.em = em; p.om = om; p.er = er;
+    p.x1 = pk_cross(ol, om); p.x2 = pk_cross(em, er); p.x3 = pk_cross(el, em); p.x4 = pk_cross(om, orr);
+    return p;
 }
 
-// FAST-9/16 score of the pixel at T (shared memory, row stride TS): the largest
-// threshold at which it is still a corner, or 0 when that is below minTh.
-__device__ __forceinline__ int fast_score(const uint8_t* __restrict__ T, int minTh) {
-    const int v = T[0];
-    // opposite pairs first: an arc of 9 contains a pixel of every opposite pair
-    const int p0 = T[3 * TS], p8 = T[-3 * TS];
-    if (abs(p0 - v) <= minTh && abs(p8 - v) <= minTh) return 0;
-    const int p4 = T[3], p12 = T[-3];
-    if (abs(p4 - v) <= minTh && abs(p12 - v) <= minTh) return 0;
-    int e[16];   // v - p_k, clockwise ring as OpenCV numbers it
-    e[0] = v - p0;                 e[1] = v - T[1 + 3 * TS];   e[2] = v - T[2 + 2 * TS];  e[3] = v - T[3 + TS];
-    e[4] = v - p4;                 e[5] = v - T[3 - TS];       e[6] = v - T[2 - 2 * TS];  e[7] = v - T[1 - 3 * TS];
-    e[8] = v - p8;                 e[9] = v - T[-1 - 3 * TS];  e[10] = v - T[-2 - 2 * TS]; e[11] = v - T[-3 - TS];
-    e[12] = v - p12;               e[13] = v - T[-3 + TS];     e[14] = v - T[-2 + 2 * TS]; e[15] = v - T[-1 + 3 * TS];
-    unsigned mdark = 0, mbright = 0;   // ring pixel darker / brighter than the centre by more than minTh
+// max over the 16 arcs of 9 contiguous ring pixels of the arc minimum (MAXOFMIN) or min of the arc maximum,
+// lane-wise on u16x2.  arc9[k] = op3(t[k], t[k+3], t[k+6]) with t[k] = op3(P[k], P[k+1], P[k+2]).
+template <bool MAXOFMIN>
+__device__ __forceinline__ uint32_t arc9_extreme(const uint32_t (&P)[16]) {
+    uint32_t t[16];
 #pragma unroll
-    for (int k = 0; k < 16; k++) {
-        mdark |= (unsigned)(e[k] > minTh) << k;
-        mbright |= (unsigned)(e[k] < -minTh) << k;
-    }
-    if (!run9(mdark) && !run9(mbright)) return 0;
-    // score+1 = max over the 16 arcs of 9 of max( min(v-p), min(p-v) )  (cornerScore<16>).
-    // Both halves are written as MIN networks over e and -e.  (The equivalent max-network form,
-    // best = max(min9(e), -max9(e)), is miscompiled by nvcc 12.9 -O3 for sm_100a: verified on a
-    // B200 against the same source built with -Xcicc -O0; see DESIGN.md "toolchain notes".)
-    int f[16];
+    for (int k = 0; k < 16; k++)
+        t[k] = MAXOFMIN ? __vimin3_u16x2(P[k], P[(k + 1) & 15], P[(k + 2) & 15]) : __vimax3_u16x2(P[k], P[(k + 1) & 15], P[(k + 2) & 15]);
+    uint32_t a[16];
 #pragma unroll
-    for (int k = 0; k < 16; k++) f[k] = -e[k];
-    int a2[16], b2[16], a4[16], b4[16];
+    for (int k = 0; k < 16; k++)
+        a[k] = MAXOFMIN ? __vimin3_u16x2(t[k], t[(k + 3) & 15], t[(k + 6) & 15]) : __vimax3_u16x2(t[k], t[(k + 3) & 15], t[(k + 6) & 15]);
+    uint32_t r[6];
 #pragma unroll
-    for (int k = 0; k < 16; k++) { a2[k] = min(e[k], e[(k + 1) & 15]); b2[k] = min(f[k], f[(k + 1) & 15]); }
-#pragma unroll
-    for (int k = 0; k < 16; k++) { a4[k] = min(a2[k], a2[(k + 2) & 15]); b4[k] = min(b2[k], b2[(k + 2) & 15]); }
-    int best = -256;
-#pragma unroll
-    for (int k = 0; k < 16; k++) {
-        const int a9 = min(min(a4[k], a4[(k + 4) & 15]), e[(k + 8) & 15]);
-        const int b9 = min(min(b4[k], b4[(k + 4) & 15]), f[(k + 8) & 15]);
-        best = max(best, max(a9, b9));
-    }
-    const int score = best - 1;
-    return score >= minTh ? score : 0;
+    for (int k = 0; k < 5; k++)
+        r[k] = MAXOFMIN ? __vimax3_u16x2(a[3 * k], a[3 * k + 1], a[3 * k + 2]) : __vimin3_u16x2(a[3 * k], a[3 * k + 1], a[3 * k + 2]);
+    r[5] = a[15];
+    const uint32_t u = MAXOFMIN ? __vimax3_u16x2(r[0], r[1], r[2]) : __vimin3_u16x2(r[0], r[1], r[2]);
+    const uint32_t v = MAXOFMIN ? __vimax3_u16x2(r[3], r[4], r[5]) : __vimin3_u16x2(r[3], r[4], r[5]);
+    return MAXOFMIN ? __vmaxu2(u, v) : __vminu2(u, v);
 }
+
+// cornerScore<16> of OpenCV for two pixels at once (u16x2 lanes): the largest threshold at which the centre is still
+// a FAST-9/16 corner = max( max_arcs min9(p) - v , v - min_arcs max9(p) ) - 1.  Returns lanes holding score+257.
+__device__ __forceinline__ uint32_t fast_score_pair(const uint32_t (&P)[16], uint32_t V) {
+    const uint32_t hi = arc9_extreme<true>(P);     // brightest "all 9 brighter" bound
+    const uint32_t lo = arc9_extreme<false>(P);    // darkest  "all 9 darker" bound
+    const uint32_t bias = 0x01000100u;
+    return __vmaxu2(hi + bias - V, V + bias - lo);
+}
+
+// FAST score of the 4 pixels of group word column `g` on tile row r (0..TH-1).  T is the level tile with halo.
+// Result: four score bytes (pixel order), 0 where score < minTh.
+__device__ __forceinline__ uint32_t fast_score4(const uint8_t* __restrict__ T, int r, int g, int minTh) {
+    // tile pixel column c = 4g sits at byte TCOL0 + c: the word holding c-4..c-1 is word g of the row
+    const uint32_t* base = (const uint32_t*)(T + r * TS) + g;           // row r of T = level row y0 + r - HALO
+    constexpr int W = TS / 4;
+    const RowPairs m3 = row_pairs(base);            // dy = -3
+    const RowPairs m2 = row_pairs(base + W);
+    const RowPairs m1 = row_pairs(base + 2 * W);
+    const RowPairs z0 = row_pairs(base + 3 * W);    // centre row
+    const RowPairs p1 = row_pairs(base + 4 * W);
+    const RowPairs p2 = row_pairs(base + 5 * W);
+    const RowPairs p3 = row_pairs(base + 6 * W);    // dy = +3
+    // ring k -> (dx,dy): 0:(0,3) 1:(1,3) 2:(2,2) 3:(3,1) 4:(3,0) 5:(3,-1) 6:(2,-2) 7:(1,-3) 8:(0,-3) 9:(-1,-3)
+    //                    10:(-2,-2) 11:(-3,-1) 12:(-3,0) 13:(-3,1) 14:(-2,2) 15:(-1,3)
+    // pair A = pixels (c, c+2): offset dx -> -3:ol -2:x3 -1:x1 0:em 1:om 2:x2 3:x4
+    // pair B = pixels (c+1, c+3):          -3:x3 -2:x1 -1:em 0:om 1:x2 2:x4 3:er
+    const uint32_t PA[16] = {p3.em, p3.om, p2.x2, p1.x4, z0.x4, m1.x4, m2.x2, m3.om,
+                             m3.em, m3.x1, m2.x3, m1.ol, z0.ol, p1.ol, p2.x3, p3.x1};
+    const uint32_t PB[16] = {p3.om, p3.x2, p2.x4, p1.er, z0.er, m1.er, m2.x4, m3.x2,
+                             m3.om, m3.em, m2.x1, m1.x3, z0.x3, p1.x3, p2.x1, p3.em};
+    const uint32_t tA = fast_score_pair(PA, z0.em);
+    const uint32_t tB = fast_score_pair(PB, z0.om);
+    int s0 = (int)(tA & 0xffffu) - 257, s2 = (int)(tA >> 16) - 257;
+    int s1 = (int)(tB & 0xffffu) - 257, s3 = (int)(tB >> 16) - 257;
+    s0 = s0 >= minTh ? s0 : 0; s1 = s1 >= minTh ? s1 : 0; s2 = s2 >= minTh ? s2 : 0; s3 = s3 >= minTh ? s3 : 0;
+    return (uint32_t)s0 | ((uint32_t)s1 << 8) | ((uint32_t)s2 << 16) | ((uint32_t)s3 << 24);
+}
+
+// 7-tap blur row sums (kernel 18,34,48,56,48,34,18) of the 4 pixels of a group, from one row's pairs:
+// A = (H(c), H(c+2)), B = (H(c+1), H(c+3)) as exact u16x2 (max 255*256 = 65280).
+__device__ __forceinline__ void hblur4(const RowPairs& p, uint32_t& A, uint32_t& B) {
+    A = 18u * (p.ol + p.x4) + 34u * (p.x3 + p.x2) + 48u * (p.x1 + p.om) + 56u * p.em;
+    B = 18u * (p.x3 + p.er) + 34u * (p.x1 + p.x4) + 48u * (p.em + p.x2) + 56u * p.om;
+}
+
+struct TapX { unsigned short o0, o1; short a0, a1; };   // source byte offsets inside the staged row + 11-bit weights
 
 struct PyrArgs {
     const uint8_t* src;          // level l-1 planes (frame 0), or the input images for level 0
@@ -103,31 +155,59 @@ struct PyrArgs {
     int* err;                    // device error flag
 };
 
+// shared memory carve-up (bytes); level 0 uses only T and U
+__host__ __device__ inline size_t pyr_smem_T() { return (size_t)TROWS * TS; }
+__host__ __device__ inline size_t pyr_smem_taps() { return (size_t)TBYTES * sizeof(TapX) + 40 * sizeof(TapX); }
+__host__ __device__ inline size_t pyr_smem_U(int srcRows) {
+    const size_t hs = (size_t)TROWS * TW * 2, hq = (size_t)srcRows * HQS * 2;
+    return ((hs > hq ? hs : hq) + 15) & ~(size_t)15;
+}
+__host__ __device__ inline size_t pyr_smem_bytes(bool level0, int srcRows, int srcCols) {
+    if (level0) return pyr_smem_T() + pyr_smem_U(0);
+    return pyr_smem_T() + pyr_smem_taps() + pyr_smem_U(srcRows) + (size_t)srcRows * srcCols;
+}
+
 template <bool LEVEL0>
 __global__ void __launch_bounds__(PYR_THREADS) pyr_level_kernel(PyrArgs a) {
     extern __shared__ __align__(16) uint8_t smem[];
     uint8_t* T = smem;                                   // TROWS x TS level tile with halo
-    unsigned short* Hs = (unsigned short*)(smem + TROWS * TS);          // TROWS x TW horizontal blur sums
-    uint8_t* S = smem + TROWS * TS + TROWS * TW * 2;     // source staging, later reused for output staging
-
-    const int tid = threadIdx.x;
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
     const int x0 = blockIdx.x * TW, y0 = blockIdx.y * TH;
     const int frame = blockIdx.z;
     const int w = a.w, h = a.h;
     const uint8_t* src = a.src + (size_t)frame * a.srcFrameStride;
+    unsigned short* Hs;                                  // TROWS x TW blur row sums, [group][A.lo A.hi B.lo B.hi]
 
     if (LEVEL0) {
-        // level 0 is the caller's image: copy with REFLECT_101 halo (copyMakeBorder, :1372)
-        for (int i = tid; i < TROWS * (TW + 2 * HALO); i += PYR_THREADS) {
-            const int ty = i / (TW + 2 * HALO), tx = i - ty * (TW + 2 * HALO);
-            const int x = x0 - HALO + tx, y = y0 - HALO + ty;
-            uint8_t v = 0;
-            if (x < w + HALO && y < h + HALO)
-                v = __ldg(src + (size_t)reflect101(y, h) * a.srcPitch + a.srcX0 + reflect101(x, w));
-            T[ty * TS + TCOL0 - HALO + tx] = v;
+        Hs = (unsigned short*)(smem + pyr_smem_T());
+        // level 0 is the caller's image: copy with REFLECT_101 halo (copyMakeBorder, :1372); byte b of a T row is
+        // column x0 - 4 + b.  Aligned interior words go as one 32-bit load.
+        const bool aligned = ((((size_t)src + a.srcX0) | (size_t)a.srcPitch) & 3) == 0;
+        for (int i = tid; i < TROWS * (TBYTES / 4); i += PYR_THREADS) {
+            const int ty = i / (TBYTES / 4), q = i - ty * (TBYTES / 4);
+            const int y = y0 - HALO + ty, xb = x0 - 4 + 4 * q;
+            uint32_t v = 0;
+            if (y < h + HALO) {
+                const uint8_t* row = src + (size_t)reflect101(y, h) * a.srcPitch + a.srcX0;
+                if (aligned && xb >= 0 && xb + 3 < w) v = __ldg((const uint32_t*)(row + xb));
+                else {
+#pragma unroll
+                    for (int j = 0; j < 4; j++) {
+                        const int x = xb + j;
+                        if (x >= -HALO && x < w + HALO) v |= (uint32_t)__ldg(row + reflect101(x, w)) << (8 * j);
+                    }
+                }
+            }
+            *(uint32_t*)(T + ty * TS + 4 * q) = v;
         }
     } else {
-        // stage the source rows/columns this tile touches (16-byte vector loads), then interpolate
+        TapX* tapx = (TapX*)(smem + pyr_smem_T());
+        TapX* tapy = tapx + TBYTES;
+        uint8_t* U = smem + pyr_smem_T() + pyr_smem_taps();
+        unsigned short* Hq = (unsigned short*)U;         // staged source rows after the horizontal pass (h >> 4)
+        Hs = (unsigned short*)U;                         // reused once T is complete
+        uint8_t* S = U + pyr_smem_U(a.srcTileRows);      // staged source rows
+        // source rows/columns this tile touches
         const int ylo = max(0, y0 - HALO), yhi = min(h - 1, y0 + TH + HALO - 1);
         const int xlo = max(0, x0 - HALO), xhi = min(w - 1, x0 + TW + HALO - 1);
         const int sy_lo = a.ytab[ylo].s0, sy_hi = a.ytab[yhi].s1;
@@ -141,72 +221,120 @@ __global__ void __launch_bounds__(PYR_THREADS) pyr_level_kernel(PyrArgs a) {
             const uint4 v = __ldg((const uint4*)(src + (size_t)(sy_lo + r) * a.srcPitch + a.srcX0 + sx_lo + 16 * c));
             *(uint4*)(S + r * scols + 16 * c) = v;
         }
-        __syncthreads();
-        for (int i = tid; i < TROWS * (TW + 2 * HALO); i += PYR_THREADS) {
-            const int ty = i / (TW + 2 * HALO), tx = i - ty * (TW + 2 * HALO);
-            const int x = x0 - HALO + tx, y = y0 - HALO + ty;
-            uint8_t v = 0;
-            if (x < w + HALO && y < h + HALO) {
-                const ResizeTap tx_ = a.xtab[reflect101(x, w)];
-                const ResizeTap ty_ = a.ytab[reflect101(y, h)];
-                const uint8_t* r0 = S + (ty_.s0 - sy_lo) * scols - sx_lo;
-                const uint8_t* r1 = S + (ty_.s1 - sy_lo) * scols - sx_lo;
-                const int h0 = r0[tx_.s0] * tx_.a0 + r0[tx_.s1] * tx_.a1;      // HResizeLinear, int32
-                const int h1 = r1[tx_.s0] * tx_.a0 + r1[tx_.s1] * tx_.a1;
-                v = (uint8_t)((((ty_.a0 * (h0 >> 4)) >> 16) + ((ty_.a1 * (h1 >> 4)) >> 16) + 2) >> 2);   // VResizeLinear 8u
+        // per-tile tap tables: T byte b <-> level column x0 - 4 + b (b = 0 and b = 135 unused -> zero weights)
+        if (tid < TBYTES) {
+            const int x = x0 - 4 + tid;
+            TapX t; t.o0 = 0; t.o1 = 0; t.a0 = 0; t.a1 = 0;
+            if (tid >= 1 && tid <= TW + 2 * HALO && x < w + HALO) {
+                const ResizeTap s = a.xtab[reflect101(x, w)];
+                t.o0 = (unsigned short)(s.s0 - sx_lo); t.o1 = (unsigned short)(s.s1 - sx_lo); t.a0 = s.a0; t.a1 = s.a1;
             }
-            T[ty * TS + TCOL0 - HALO + tx] = v;
+            tapx[tid] = t;
+        } else if (tid >= 192 && tid < 192 + TROWS) {
+            const int ty = tid - 192, y = y0 - HALO + ty;
+            TapX t; t.o0 = 0; t.o1 = 0; t.a0 = 0; t.a1 = 0;
+            if (y < h + HALO) {
+                const ResizeTap s = a.ytab[reflect101(y, h)];
+                t.o0 = (unsigned short)(s.s0 - sy_lo); t.o1 = (unsigned short)(s.s1 - sy_lo); t.a0 = s.a0; t.a1 = s.a1;
+            }
+            tapy[ty] = t;
+        }
+        __syncthreads();
+        // horizontal pass (HResizeLinear, int32): Hq[r][b] = (S[r][o0]*a0 + S[r][o1]*a1) >> 4, two columns per item
+        for (int i = tid; i < nrows * (TBYTES / 2); i += PYR_THREADS) {
+            const int r = i / (TBYTES / 2), k = i - r * (TBYTES / 2);
+            const uint4 tp = *(const uint4*)(tapx + 2 * k);
+            const uint8_t* Sr = S + r * scols;
+            const int h0 = Sr[tp.x & 0xffffu] * (int)(short)(tp.y & 0xffffu) + Sr[tp.x >> 16] * ((int)tp.y >> 16);
+            const int h1 = Sr[tp.z & 0xffffu] * (int)(short)(tp.w & 0xffffu) + Sr[tp.z >> 16] * ((int)tp.w >> 16);
+            *(uint32_t*)(Hq + r * HQS + 2 * k) = (uint32_t)(h0 >> 4) | ((uint32_t)(h1 >> 4) << 16);
+        }
+        __syncthreads();
+        // vertical pass (VResizeLinear 8u): four columns per item
+        for (int i = tid; i < TROWS * (TBYTES / 4); i += PYR_THREADS) {
+            const int ty = i / (TBYTES / 4), q = i - ty * (TBYTES / 4);
+            const uint2 tp = *(const uint2*)(tapy + ty);
+            const int b0 = (int)(short)(tp.y & 0xffffu), b1 = (int)tp.y >> 16;
+            const uint2 u0 = *(const uint2*)(Hq + (tp.x & 0xffffu) * HQS + 4 * q);
+            const uint2 u1 = *(const uint2*)(Hq + (tp.x >> 16) * HQS + 4 * q);
+            const int v0 = (((b0 * (int)(u0.x & 0xffffu)) >> 16) + ((b1 * (int)(u1.x & 0xffffu)) >> 16) + 2) >> 2;
+            const int v1 = (((b0 * (int)(u0.x >> 16)) >> 16) + ((b1 * (int)(u1.x >> 16)) >> 16) + 2) >> 2;
+            const int v2 = (((b0 * (int)(u0.y & 0xffffu)) >> 16) + ((b1 * (int)(u1.y & 0xffffu)) >> 16) + 2) >> 2;
+            const int v3 = (((b0 * (int)(u0.y >> 16)) >> 16) + ((b1 * (int)(u1.y >> 16)) >> 16) + 2) >> 2;
+            *(uint32_t*)(T + ty * TS + 4 * q) = (uint32_t)v0 | ((uint32_t)v1 << 8) | ((uint32_t)v2 << 16) | ((uint32_t)v3 << 24);
         }
     }
     __syncthreads();
 
-    const int vx = (tid & 7) * 16, vy = tid >> 3;            // this thread's 16-pixel output segment
-    const bool vstore = (y0 + vy < h) && (x0 + vx < w);
-    const size_t rowOff = (size_t)(y0 + vy) * a.pitch + ORB_XPAD + x0 + vx;
-
-    // ---- level plane -------------------------------------------------------
-    if (vstore) {
-        const uint32_t* t = (const uint32_t*)(T + (vy + HALO) * TS + TCOL0 + vx);
-        uint4 v = make_uint4(t[0], t[1], t[2], t[3]);
-        *(uint4*)(a.pyr + (size_t)frame * a.pyrFrameStride + (size_t)ORB_EDGE * a.pitch + rowOff) = v;
+    // ---- level plane: 16 pixels per thread ------------------------------------
+    {
+        const int vx = (tid & 7) * 16, vy = tid >> 3;
+        if ((y0 + vy < h) && (x0 + vx < w)) {
+            const uint32_t* t = (const uint32_t*)(T + (vy + HALO) * TS + TCOL0 + vx);
+            const uint4 v = make_uint4(t[0], t[1], t[2], t[3]);
+            *(uint4*)(a.pyr + (size_t)frame * a.pyrFrameStride + (size_t)(ORB_EDGE + y0 + vy) * a.pitch + ORB_XPAD + x0 + vx) = v;
+        }
     }
 
-    // ---- horizontal blur sums (exact, <= 16 bit) ----------------------------
-    for (int i = tid; i < TROWS * TW; i += PYR_THREADS) {
-        const int r = i / TW, c = i - r * TW;
-        const uint8_t* p = T + r * TS + TCOL0 - HALO + c;
-        Hs[i] = (unsigned short)(18 * (p[0] + p[6]) + 34 * (p[1] + p[5]) + 48 * (p[2] + p[4]) + 56 * p[3]);
+    // ---- horizontal blur sums: one warp per T row, one 4-pixel group per lane ----
+    for (int r = wid; r < TROWS; r += PYR_THREADS / 32) {
+        const RowPairs p = row_pairs((const uint32_t*)(T + r * TS) + lane);
+        uint32_t A, B;
+        hblur4(p, A, B);
+        *(uint2*)(Hs + r * TW + 4 * lane) = make_uint2(A, B);
     }
 
-    // ---- FAST score (reads T only) ------------------------------------------
-    uint8_t* O = S;   // TH x TW output staging; the source staging is dead by now
-    __syncthreads();  // all reads of S done (level>0), Hs complete
-    for (int i = tid; i < TH * TW; i += PYR_THREADS) {
-        const int r = i / TW, c = i - r * TW;
-        const int x = x0 + c, y = y0 + r;
-        int s = 0;
-        if (x >= ORB_EDGE && x < w - ORB_EDGE && y >= ORB_EDGE && y < h - ORB_EDGE)
-            s = fast_score(T + (r + HALO) * TS + TCOL0 + c, a.minTh);
-        O[i] = (uint8_t)s;
+    // ---- FAST score: warp `wid` owns tile rows 4*wid..4*wid+3, lane = 4-pixel group (reads T only) ----
+    const int gx = x0 + 4 * lane;                        // level column of the group's first pixel
+#pragma unroll 1
+    for (int k = 0; k < 4; k++) {
+        const int r = 4 * wid + k, y = y0 + r;
+        if (y >= h || gx >= w) continue;
+        uint32_t s = 0;
+        if (y >= ORB_EDGE && y < h - ORB_EDGE && gx + 3 >= ORB_EDGE && gx < w - ORB_EDGE) {
+            s = fast_score4(T, r, lane, a.minTh);
+            if (gx < ORB_EDGE || gx + 3 >= w - ORB_EDGE) {           // group straddles the detection area
+                uint32_t m = 0;
+#pragma unroll
+                for (int j = 0; j < 4; j++)
+                    if (gx + j >= ORB_EDGE && gx + j < w - ORB_EDGE) m |= 0xffu << (8 * j);
+                s &= m;
+            }
+        }
+        *(uint32_t*)(a.score + (size_t)frame * a.planeFrameStride + (size_t)y * a.pitch + ORB_XPAD + gx) = s;
     }
-    __syncthreads();
-    if (vstore) {
-        const uint4 v = *(const uint4*)(O + vy * TW + vx);
-        *(uint4*)(a.score + (size_t)frame * a.planeFrameStride + rowOff) = v;
-    }
-    __syncthreads();
+    __syncthreads();      // Hs complete
 
-    // ---- vertical blur pass ---------------------------------------------------
-    for (int i = tid; i < TH * TW; i += PYR_THREADS) {
-        const int r = i / TW, c = i - r * TW;
-        const unsigned short* q = Hs + r * TW + c;
-        const unsigned v = 18u * (q[0] + q[6 * TW]) + 34u * (q[TW] + q[5 * TW]) + 48u * (q[2 * TW] + q[4 * TW]) + 56u * q[3 * TW];
-        O[i] = (uint8_t)((v + 32768u) >> 16);
-    }
-    __syncthreads();
-    if (vstore) {
-        const uint4 v = *(const uint4*)(O + vy * TW + vx);
-        *(uint4*)(a.blur + (size_t)frame * a.planeFrameStride + rowOff) = v;
+    // ---- vertical blur pass: warp `wid` owns tile rows 4*wid..4*wid+3, sliding 7-row window in registers ----
+    {
+        const unsigned short* col = Hs + 4 * lane;
+        uint32_t qa[7], qb[7];                           // (H(c),H(c+2)) and (H(c+1),H(c+3)) of the 7 window rows
+#pragma unroll
+        for (int j = 0; j < 6; j++) {
+            const uint2 v = *(const uint2*)(col + (4 * wid + j) * TW);
+            qa[j] = v.x; qb[j] = v.y;
+        }
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+            const int r = 4 * wid + k, y = y0 + r;
+            const uint2 v = *(const uint2*)(col + (r + 6) * TW);
+            qa[6] = v.x; qb[6] = v.y;
+            uint32_t o[4];
+#pragma unroll
+            for (int j = 0; j < 4; j++) {
+                const uint32_t* q = (j & 1) ? qb : qa;
+                const int sh = (j & 2) ? 16 : 0;
+                const uint32_t t0 = (q[0] >> sh) & 0xffffu, t1 = (q[1] >> sh) & 0xffffu, t2 = (q[2] >> sh) & 0xffffu,
+                               t3 = (q[3] >> sh) & 0xffffu, t4 = (q[4] >> sh) & 0xffffu, t5 = (q[5] >> sh) & 0xffffu,
+                               t6 = (q[6] >> sh) & 0xffffu;
+                o[j] = (18u * (t0 + t6) + 34u * (t1 + t5) + 48u * (t2 + t4) + 56u * t3 + 32768u) >> 16;
+            }
+            if (y < h && gx < w)
+                *(uint32_t*)(a.blur + (size_t)frame * a.planeFrameStride + (size_t)y * a.pitch + ORB_XPAD + gx) =
+                    o[0] | (o[1] << 8) | (o[2] << 16) | (o[3] << 24);
+#pragma unroll
+            for (int j = 0; j < 6; j++) { qa[j] = qa[j + 1]; qb[j] = qb[j + 1]; }
+        }
     }
 }
 
