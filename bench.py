@@ -30,7 +30,7 @@ W_, H_, NFEAT = 1241, 376, 2000
 SETTINGS = dict(nFeatures=NFEAT, scaleFactor=1.2, nLevels=8, iniThFAST=20, minThFAST=7)
 METRIC = "ORB frames/s (1241x376, 2000 kp)"
 UNIT = "frames/s"
-STAGES = ["pyramid_blur_fast", "border", "cell_count", "cell_scan", "cell_emit", "quadtree", "describe"]
+STAGES = ["pyramid_blur_fast", "border", "cell_nms", "quadtree", "describe"]
 
 
 def level_sizes(w, h, nlevels=8, sf=1.2):

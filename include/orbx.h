@@ -121,11 +121,11 @@ int orbx_get_candidates(orbx_t* ex, int frame, int level, int32_t* xyr, int capa
 int orbx_launches_per_call(const orbx_t* ex);
 
 /* Per-stage device times of the last orbx_extract_batch* call, measured with CUDA events on the
- * instance's stream (profiling must have been switched on before that call).  ms[0..6] =
- * pyramid+blur+FAST (all levels), border, cell count, cell scan, cell emit, quadtree, describe. */
+ * instance's stream (profiling must have been switched on before that call).  ms[0..4] =
+ * pyramid+blur+FAST (all levels), border, per-cell NMS, quadtree (incl. candidate gather), describe. */
 int orbx_set_profiling(orbx_t* ex, int on);
 int orbx_stage_times(orbx_t* ex, float* ms, int n);
-#define ORBX_NUM_STAGES 7
+#define ORBX_NUM_STAGES 5
 
 const char* orbx_error_string(int code);
 

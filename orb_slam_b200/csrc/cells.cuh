@@ -3,15 +3,22 @@
 // suppression restricted to the cell's detection interior (cv::FAST is run on
 // the cell sub-image, so scores outside the interior count as 0), keep the
 // corners at iniThFAST, or - if the cell has none - those at minThFAST.
-// Output: vToDistributeKeys in the reference's order (cell row-major, then
-// pixel row-major), coordinates relative to (16,16), packed x:12|y:12|score:8.
-// Three launches: count per cell -> exclusive scan per (frame, level) -> emit.
+//
+// One launch, one warp per cell: the score plane is read exactly once (lane =
+// column, three rows rolling through registers, neighbours by warp shuffle),
+// every row leaves two ballots (kept at minThFAST / kept at iniThFAST), and the
+// cell's survivors are written in pixel row-major order into the cell's own
+// slot list, packed x:12|y:12|score:8 with coordinates relative to (16,16).
+// The quadtree kernel concatenates the slot lists in cell row-major order,
+// which is exactly the order of vToDistributeKeys (:938-1002).
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include "geom.h"
 
 namespace orbx {
+
+constexpr int CELL_MAX_DIM = 64;   // interior of a cell is < 60 px in each direction (wCell = ceil(W / floor(W/30)))
 
 struct CellArgs {
     const uint8_t* score;             // frame 0 score block
@@ -25,16 +32,13 @@ struct CellArgs {
     int maxBX[ORB_MAX_LEVELS], maxBY[ORB_MAX_LEVELS];
     int pitch[ORB_MAX_LEVELS];
     unsigned long long planeOff[ORB_MAX_LEVELS];
-    unsigned long long candOff[ORB_MAX_LEVELS];
-    int candCap[ORB_MAX_LEVELS];
-    unsigned long long candFrameStride;   // elements
-    uint32_t* cellCount;              // [frames][totalCells]: count | (useMin << 31); after the scan: offsets in cellOffs
-    uint32_t* cellOffs;               // [frames][totalCells]
-    uint32_t* cand;                   // [frames][candTotal]
-    int* candCount;                   // [frames][nlevels]
+    unsigned long long slotOff[ORB_MAX_LEVELS];   // element offset of the level's first cell slot list inside one frame
+    int slotCap[ORB_MAX_LEVELS];                  // elements per cell slot list
+    unsigned long long slotFrameStride;           // elements
+    uint32_t* cellCount;              // [frames][totalCells]
+    uint32_t* slots;                  // [frames][slotTotal]
+    int* err;
 };
-
-constexpr int CELL_ROWS = 8;   // rows of a cell column loaded together
 
 struct CellBox { int x0, x1, y0, y1; bool valid; };
 
@@ -52,26 +56,96 @@ __device__ __forceinline__ CellBox cell_box(const CellArgs& a, int l, int i, int
     return b;
 }
 
-__device__ __forceinline__ bool nms_keep(const uint8_t* __restrict__ S, int pitch, int x, int y, int s, const CellBox& b) {
-    // strictly greater than all 8 neighbours; neighbours outside the interior count 0 (s > 0 already)
-    const bool l = x > b.x0, r = x + 1 < b.x1, u = y > b.y0, d = y + 1 < b.y1;
-    const uint8_t* p = S + (size_t)y * pitch + ORB_XPAD + x;
-    if (l && p[-1] >= s) return false;
-    if (r && p[1] >= s) return false;
-    if (u) {
-        const uint8_t* q = p - pitch;
-        if (q[0] >= s || (l && q[-1] >= s) || (r && q[1] >= s)) return false;
-    }
-    if (d) {
-        const uint8_t* q = p + pitch;
-        if (q[0] >= s || (l && q[-1] >= s) || (r && q[1] >= s)) return false;
-    }
-    return true;
+// horizontal neighbours of a two-chunk row held as (c0, c1) per lane: chunk 0 covers columns x0..x0+31, chunk 1 the next 32
+__device__ __forceinline__ void row_lr(int c0, int c1, int lane, int& l0, int& r0, int& l1, int& r1) {
+    const int up0 = __shfl_up_sync(0xffffffffu, c0, 1), dn0 = __shfl_down_sync(0xffffffffu, c0, 1);
+    const int up1 = __shfl_up_sync(0xffffffffu, c1, 1), dn1 = __shfl_down_sync(0xffffffffu, c1, 1);
+    const int last0 = __shfl_sync(0xffffffffu, c0, 31), first1 = __shfl_sync(0xffffffffu, c1, 0);
+    l0 = lane ? up0 : 0;
+    r0 = lane < 31 ? dn0 : first1;
+    l1 = lane ? up1 : last0;
+    r1 = lane < 31 ? dn1 : 0;
 }
 
-// one warp per cell; EMIT=false counts, EMIT=true writes candidates at the scanned offsets
-template <bool EMIT>
-__global__ void __launch_bounds__(256) cell_kernel(CellArgs a) {
+template <bool TWO>
+__device__ __forceinline__ void cell_scan(const CellArgs& a, const uint8_t* __restrict__ S, int pitch, const CellBox b, int lane,
+                                          uint32_t* __restrict__ out, int cap, uint32_t* __restrict__ cnt, int* err) {
+    // per-lane ballots of the rows lane and lane+32 (interior height < 64)
+    unsigned mMin[2][2] = {{0, 0}, {0, 0}}, mIni[2][2] = {{0, 0}, {0, 0}};   // [chunk][row >> 5]
+    int nIni = 0, nMin = 0;
+    const int xa = b.x0 + lane, xb = b.x0 + 32 + lane;
+    const bool ina = xa < b.x1, inb = TWO && xb < b.x1;
+    const uint8_t* col = S + ORB_XPAD;
+    auto ld = [&](int y, int& c0, int& c1) {
+        c0 = (ina && y < b.y1) ? col[(size_t)y * pitch + xa] : 0;
+        c1 = (inb && y < b.y1) ? col[(size_t)y * pitch + xb] : 0;
+    };
+    int p0 = 0, p1 = 0, hp0 = 0, hp1 = 0;             // previous row and its horizontal 3-max
+    int c0, c1, n0, n1;
+    ld(b.y0, c0, c1);
+    int cl0, cr0, cl1 = 0, cr1 = 0;
+    if (TWO) row_lr(c0, c1, lane, cl0, cr0, cl1, cr1);
+    else { cl0 = __shfl_up_sync(0xffffffffu, c0, 1); cr0 = __shfl_down_sync(0xffffffffu, c0, 1); if (!lane) cl0 = 0; if (lane == 31) cr0 = 0; }
+    const int rows = b.y1 - b.y0;
+    for (int r = 0; r < rows; r++) {
+        const int y = b.y0 + r;
+        ld(y + 1, n0, n1);                              // zeros past the last interior row
+        int nl0, nr0, nl1 = 0, nr1 = 0;
+        if (TWO) row_lr(n0, n1, lane, nl0, nr0, nl1, nr1);
+        else { nl0 = __shfl_up_sync(0xffffffffu, n0, 1); nr0 = __shfl_down_sync(0xffffffffu, n0, 1); if (!lane) nl0 = 0; if (lane == 31) nr0 = 0; }
+        const int hc0 = max(max(cl0, cr0), c0), hn0 = max(max(nl0, nr0), n0);
+        // strictly greater than all 8 neighbours (non-corners and everything outside the interior count 0)
+        const bool k0 = c0 > max(max(hp0, hn0), max(cl0, cr0));
+        const unsigned bm0 = __ballot_sync(0xffffffffu, k0), bi0 = __ballot_sync(0xffffffffu, k0 && c0 >= a.iniTh);
+        nMin += __popc(bm0); nIni += __popc(bi0);
+        if (lane == (r & 31)) { mMin[0][0] = (r < 32) ? bm0 : mMin[0][0]; mMin[0][1] = (r >= 32) ? bm0 : mMin[0][1];
+                                mIni[0][0] = (r < 32) ? bi0 : mIni[0][0]; mIni[0][1] = (r >= 32) ? bi0 : mIni[0][1]; }
+        hp0 = hc0; p0 = c0; c0 = n0; cl0 = nl0; cr0 = nr0;
+        if (TWO) {
+            const int hc1 = max(max(cl1, cr1), c1), hn1 = max(max(nl1, nr1), n1);
+            const bool k1 = c1 > max(max(hp1, hn1), max(cl1, cr1));
+            const unsigned bm1 = __ballot_sync(0xffffffffu, k1), bi1 = __ballot_sync(0xffffffffu, k1 && c1 >= a.iniTh);
+            nMin += __popc(bm1); nIni += __popc(bi1);
+            if (lane == (r & 31)) { mMin[1][0] = (r < 32) ? bm1 : mMin[1][0]; mMin[1][1] = (r >= 32) ? bm1 : mMin[1][1];
+                                    mIni[1][0] = (r < 32) ? bi1 : mIni[1][0]; mIni[1][1] = (r >= 32) ? bi1 : mIni[1][1]; }
+            hp1 = hc1; p1 = c1; c1 = n1; cl1 = nl1; cr1 = nr1;
+        }
+    }
+    (void)p0; (void)p1;
+    const bool useIni = nIni > 0;                       // :976-987: iniThFAST first, minThFAST only if that found nothing
+    const int total = useIni ? nIni : nMin;
+    if (lane == 0) *cnt = (uint32_t)total;
+    if (total == 0) return;
+    if (total > cap) { if (lane == 0) atomicExch(err, 301); return; }
+    int pos = 0;
+    for (int r = 0; r < rows; r++) {
+        const int y = b.y0 + r;
+        const unsigned w0 = useIni ? ((r < 32) ? mIni[0][0] : mIni[0][1]) : ((r < 32) ? mMin[0][0] : mMin[0][1]);
+        const unsigned m0 = __shfl_sync(0xffffffffu, w0, r & 31);
+        if (m0) {
+            if ((m0 >> lane) & 1u) {
+                const uint32_t s = col[(size_t)y * pitch + xa];
+                out[pos + __popc(m0 & ((1u << lane) - 1))] =
+                    ((uint32_t)(xa - ORB_BORDER_MIN)) | ((uint32_t)(y - ORB_BORDER_MIN) << 12) | (s << 24);
+            }
+            pos += __popc(m0);
+        }
+        if (TWO) {
+            const unsigned w1 = useIni ? ((r < 32) ? mIni[1][0] : mIni[1][1]) : ((r < 32) ? mMin[1][0] : mMin[1][1]);
+            const unsigned m1 = __shfl_sync(0xffffffffu, w1, r & 31);
+            if (m1) {
+                if ((m1 >> lane) & 1u) {
+                    const uint32_t s = col[(size_t)y * pitch + xb];
+                    out[pos + __popc(m1 & ((1u << lane) - 1))] =
+                        ((uint32_t)(xb - ORB_BORDER_MIN)) | ((uint32_t)(y - ORB_BORDER_MIN) << 12) | (s << 24);
+                }
+                pos += __popc(m1);
+            }
+        }
+    }
+}
+
+__global__ void __launch_bounds__(256) cell_nms_kernel(CellArgs a) {
     const int lane = threadIdx.x & 31;
     const int cell = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     const int frame = blockIdx.y;
@@ -82,95 +156,12 @@ __global__ void __launch_bounds__(256) cell_kernel(CellArgs a) {
     const int i = c / a.nCols[l], j = c - i * a.nCols[l];
     const CellBox b = cell_box(a, l, i, j);
     uint32_t* cnt = a.cellCount + (size_t)frame * a.totalCells + cell;
-    if (!b.valid) { if (!EMIT && lane == 0) *cnt = 0; return; }
+    if (!b.valid) { if (lane == 0) *cnt = 0; return; }
+    if (b.x1 - b.x0 > CELL_MAX_DIM || b.y1 - b.y0 > CELL_MAX_DIM) { if (lane == 0) { *cnt = 0; atomicExch(a.err, 302); } return; }
     const uint8_t* S = a.score + (size_t)frame * a.planeFrameStride + a.planeOff[l];
-    const int pitch = a.pitch[l];
-    if (!EMIT) {
-        int nIni = 0, nMin = 0;
-        for (int xb = b.x0; xb < b.x1; xb += 32) {
-            const int x = xb + lane;
-            for (int yb = b.y0; yb < b.y1; yb += CELL_ROWS) {
-                int sv[CELL_ROWS];
-#pragma unroll
-                for (int r = 0; r < CELL_ROWS; r++)       // independent loads first: CELL_ROWS rows in flight
-                    sv[r] = (x < b.x1 && yb + r < b.y1) ? S[(size_t)(yb + r) * pitch + ORB_XPAD + x] : 0;
-#pragma unroll
-                for (int r = 0; r < CELL_ROWS; r++) {
-                    const int s = sv[r];
-                    const bool keep = s > 0 && nms_keep(S, pitch, x, yb + r, s, b);
-                    nMin += __popc(__ballot_sync(0xffffffffu, keep));
-                    nIni += __popc(__ballot_sync(0xffffffffu, keep && s >= a.iniTh));
-                }
-            }
-        }
-        if (lane == 0) *cnt = nIni > 0 ? (uint32_t)nIni : ((uint32_t)nMin | 0x80000000u);
-    } else {
-        const uint32_t cv = *cnt;
-        if ((cv & 0x7fffffffu) == 0) return;
-        const int th = (cv & 0x80000000u) ? 1 : a.iniTh;      // the score plane is already 0 below minThFAST
-        uint32_t pos = a.cellOffs[(size_t)frame * a.totalCells + cell];
-        uint32_t* out = a.cand + (size_t)frame * a.candFrameStride + a.candOff[l];
-        // cells are < 60 px wide (wCell = ceil(W / floor(W/30))): at most two 32-lane chunks per row
-        const int nch = (b.x1 - b.x0 > 32) ? 2 : 1;
-        for (int yb = b.y0; yb < b.y1; yb += CELL_ROWS) {
-            int sv[CELL_ROWS][2];
-#pragma unroll
-            for (int r = 0; r < CELL_ROWS; r++)
-#pragma unroll
-                for (int c2 = 0; c2 < 2; c2++) {
-                    const int x = b.x0 + 32 * c2 + lane;
-                    sv[r][c2] = (c2 < nch && x < b.x1 && yb + r < b.y1) ? S[(size_t)(yb + r) * pitch + ORB_XPAD + x] : 0;
-                }
-#pragma unroll
-            for (int r = 0; r < CELL_ROWS; r++)
-#pragma unroll
-                for (int c2 = 0; c2 < 2; c2++) {
-                    if (c2 >= nch) continue;                 // warp-uniform
-                    const int x = b.x0 + 32 * c2 + lane, y = yb + r;
-                    const int s = sv[r][c2];
-                    const bool keep = s >= th && nms_keep(S, pitch, x, y, s, b);
-                    const unsigned m = __ballot_sync(0xffffffffu, keep);
-                    if (keep) {
-                        const uint32_t k = pos + __popc(m & ((1u << lane) - 1));
-                        out[k] = ((uint32_t)(x - ORB_BORDER_MIN)) | ((uint32_t)(y - ORB_BORDER_MIN) << 12) | ((uint32_t)s << 24);
-                    }
-                    pos += __popc(m);
-                }
-        }
-    }
-}
-
-// exclusive scan of the cell counts of one (frame, level); block per (level, frame)
-__global__ void __launch_bounds__(256) cell_scan_kernel(CellArgs a) {
-    __shared__ uint32_t warpSum[8];
-    __shared__ uint32_t carry;
-    const int l = blockIdx.x, frame = blockIdx.y;
-    const int n = a.cellOff[l + 1] - a.cellOff[l];
-    const uint32_t* cnt = a.cellCount + (size_t)frame * a.totalCells + a.cellOff[l];
-    uint32_t* offs = a.cellOffs + (size_t)frame * a.totalCells + a.cellOff[l];
-    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-    if (threadIdx.x == 0) carry = 0;
-    __syncthreads();
-    for (int base = 0; base < n; base += 256) {
-        const int i = base + threadIdx.x;
-        const uint32_t v = i < n ? (cnt[i] & 0x7fffffffu) : 0;
-        uint32_t inc = v;
-#pragma unroll
-        for (int d = 1; d < 32; d <<= 1) {
-            const uint32_t t = __shfl_up_sync(0xffffffffu, inc, d);
-            if (lane >= d) inc += t;
-        }
-        if (lane == 31) warpSum[wid] = inc;
-        __syncthreads();
-        uint32_t wbase = 0;
-        for (int k = 0; k < wid; k++) wbase += warpSum[k];
-        const uint32_t c0 = carry;
-        if (i < n) offs[i] = c0 + wbase + inc - v;
-        __syncthreads();
-        if (threadIdx.x == 255) carry = c0 + wbase + inc;
-        __syncthreads();
-    }
-    if (threadIdx.x == 0) a.candCount[frame * a.nlevels + l] = (int)carry;
+    uint32_t* out = a.slots + (size_t)frame * a.slotFrameStride + a.slotOff[l] + (size_t)c * a.slotCap[l];
+    if (b.x1 - b.x0 > 32) cell_scan<true>(a, S, a.pitch[l], b, lane, out, a.slotCap[l], cnt, a.err);
+    else cell_scan<false>(a, S, a.pitch[l], b, lane, out, a.slotCap[l], cnt, a.err);
 }
 
 }  // namespace orbx

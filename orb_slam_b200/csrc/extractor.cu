@@ -47,7 +47,7 @@ struct orbx_extractor {
     ResizeTap* d_tabs = nullptr;
     uint8_t* d_in = nullptr; size_t inPitch = 0, inFrameStride = 0;
     uint8_t *d_pyr = nullptr, *d_blur = nullptr, *d_score = nullptr;
-    uint32_t *d_cellCount = nullptr, *d_cellOffs = nullptr, *d_cand = nullptr;
+    uint32_t *d_cellCount = nullptr, *d_cellOffs = nullptr, *d_cand = nullptr, *d_slots = nullptr;
     uint32_t *d_keyA = nullptr, *d_keyB = nullptr, *d_valA = nullptr, *d_valB = nullptr, *d_sel = nullptr;
     int *d_candCount = nullptr, *d_selCount = nullptr, *d_err = nullptr;
     // result block (device + pinned host mirror): [n_out[frames]] [err] [kps] [desc]
@@ -126,7 +126,7 @@ static int build_geometry(orbx_extractor* e, int width, int height, FrameGeom& g
     const int L = e->nlevels;
     g.nlevels = L; g.width = width; g.height = height; g.iniTh = e->iniTh; g.minTh = e->minTh;
     tabs.clear();
-    unsigned long long pyrOff = 0, planeOff = 0, candOff = 0;
+    unsigned long long pyrOff = 0, planeOff = 0, candOff = 0, slotOff = 0;
     int cellOff = 0, selOff = 0, nodeNeed = 8;
     for (int l = 0; l < L; l++) {
         LevelGeom& v = g.lv[l];
@@ -157,15 +157,21 @@ static int build_geometry(orbx_extractor* e, int width, int height, FrameGeom& g
         else { v.wCell = (int)std::ceil(fw / v.nCols); v.hCell = (int)std::ceil(fh / v.nRows); }
         v.cellOff = cellOff; cellOff += v.nCols * v.nRows;
         // worst case of in-cell NMS survivors: one per 2x2 block of every cell interior
-        long cap = 0;
+        long cap = 0, cellMax = 0;
         for (int i = 0; i < v.nRows; i++)
             for (int j = 0; j < v.nCols; j++) {
                 const int iniY = ORB_BORDER_MIN + i * v.hCell, iniX = ORB_BORDER_MIN + j * v.wCell;
                 if (iniY >= v.maxBorderY - 3 || iniX >= v.maxBorderX - 6) continue;
                 const int my = std::min(iniY + v.hCell + 6, v.maxBorderY), mx = std::min(iniX + v.wCell + 6, v.maxBorderX);
                 const int iw = mx - iniX - 6, ih = my - iniY - 6;
-                if (iw > 0 && ih > 0) cap += (long)((iw + 1) / 2) * ((ih + 1) / 2);
+                if (iw > CELL_MAX_DIM || ih > CELL_MAX_DIM) return ORBX_E_UNSUPPORTED;
+                if (iw > 0 && ih > 0) {
+                    cap += (long)((iw + 1) / 2) * ((ih + 1) / 2);
+                    cellMax = std::max(cellMax, (long)((iw + 1) / 2) * ((ih + 1) / 2));
+                }
             }
+        v.slotCap = (int)((cellMax + 31) & ~31L);
+        v.slotOff = slotOff; slotOff += (unsigned long long)v.slotCap * v.nCols * v.nRows;
         v.candCap = (int)((cap + 31) & ~31L);
         if (v.candCap >= (1 << 24)) return ORBX_E_UNSUPPORTED;
         v.candOff = candOff; candOff += v.candCap;
@@ -189,6 +195,7 @@ static int build_geometry(orbx_extractor* e, int width, int height, FrameGeom& g
     g.totalCells = cellOff; g.selTotal = selOff;
     g.pyrBytes = (pyrOff + 255) & ~255ULL; g.planeBytes = (planeOff + 255) & ~255ULL;
     g.candTotal = (candOff + 63) & ~63ULL;
+    g.slotTotal = (slotOff + 63) & ~63ULL;
     g.nodeCap = 1 << ceil_log2(nodeNeed);
     if (qt_smem_bytes(g.nodeCap) > 200 * 1024) return ORBX_E_UNSUPPORTED;
     return ORBX_OK;
@@ -199,11 +206,12 @@ static int build_geometry(orbx_extractor* e, int width, int height, FrameGeom& g
 // ---------------------------------------------------------------------------
 static void free_workspace(orbx_extractor* e) {
     cudaFree(e->d_tabs); cudaFree(e->d_in); cudaFree(e->d_pyr); cudaFree(e->d_blur); cudaFree(e->d_score);
-    cudaFree(e->d_cellCount); cudaFree(e->d_cellOffs); cudaFree(e->d_cand);
+    cudaFree(e->d_cellCount); cudaFree(e->d_cellOffs); cudaFree(e->d_cand); cudaFree(e->d_slots);
     cudaFree(e->d_keyA); cudaFree(e->d_keyB); cudaFree(e->d_valA); cudaFree(e->d_valB); cudaFree(e->d_sel);
     cudaFree(e->d_candCount); cudaFree(e->d_selCount); cudaFree(e->d_res);
     if (e->h_res) cudaFreeHost(e->h_res);
     e->d_tabs = nullptr; e->d_in = e->d_pyr = e->d_blur = e->d_score = nullptr;
+    e->d_slots = nullptr;
     e->d_cellCount = e->d_cellOffs = e->d_cand = e->d_keyA = e->d_keyB = e->d_valA = e->d_valB = e->d_sel = nullptr;
     e->d_candCount = e->d_selCount = nullptr; e->d_res = nullptr; e->h_res = nullptr;
     e->capFrames = 0; e->haveGeom = false;
@@ -247,6 +255,7 @@ static int ensure_workspace(orbx_extractor* e, int width, int height, int frames
     CK(cudaMalloc(&e->d_cellOffs, cells * 4));
     const size_t cands = (size_t)std::max<unsigned long long>(g.candTotal, 64) * F;
     CK(cudaMalloc(&e->d_cand, cands * 4));
+    CK(cudaMalloc(&e->d_slots, (size_t)std::max<unsigned long long>(g.slotTotal, 64) * F * 4));
     CK(cudaMalloc(&e->d_keyA, cands * 4)); CK(cudaMalloc(&e->d_keyB, cands * 4));
     CK(cudaMalloc(&e->d_valA, cands * 4)); CK(cudaMalloc(&e->d_valB, cands * 4));
     CK(cudaMalloc(&e->d_sel, (size_t)g.selTotal * F * 4));
@@ -319,7 +328,7 @@ static int enqueue_pipeline(orbx_extractor* e, const uint8_t* src, size_t srcPit
         launches++;
     }
     if (e->profile) CK(cudaEventRecord(e->ev[2], st));
-    // 3. per-cell NMS + threshold fallback -> ordered candidate lists
+    // 3. per-cell NMS + threshold fallback -> per-cell survivor lists (one launch, score plane read once)
     CellArgs c{};
     c.score = e->d_score; c.planeFrameStride = g.planeBytes; c.nlevels = g.nlevels; c.iniTh = g.iniTh;
     c.totalCells = g.totalCells;
@@ -327,27 +336,21 @@ static int enqueue_pipeline(orbx_extractor* e, const uint8_t* src, size_t srcPit
         const LevelGeom& v = g.lv[l];
         c.cellOff[l] = v.cellOff; c.nCols[l] = std::max(v.nCols, 1); c.wCell[l] = v.wCell; c.hCell[l] = v.hCell;
         c.maxBX[l] = v.maxBorderX; c.maxBY[l] = v.maxBorderY; c.pitch[l] = v.pitch;
-        c.planeOff[l] = v.planeOff; c.candOff[l] = v.candOff; c.candCap[l] = v.candCap;
+        c.planeOff[l] = v.planeOff; c.slotOff[l] = v.slotOff; c.slotCap[l] = v.slotCap;
     }
     c.cellOff[g.nlevels] = g.totalCells;
-    c.candFrameStride = g.candTotal;
-    c.cellCount = e->d_cellCount; c.cellOffs = e->d_cellOffs; c.cand = e->d_cand; c.candCount = e->d_candCount;
+    c.slotFrameStride = g.slotTotal;
+    c.cellCount = e->d_cellCount; c.slots = e->d_slots; c.err = d_err;
     if (g.totalCells > 0) {
-        dim3 cg((g.totalCells + 7) / 8, frames);
-        cell_kernel<false><<<cg, 256, 0, st>>>(c);
-        if (e->profile) CK(cudaEventRecord(e->ev[3], st));
-        cell_scan_kernel<<<dim3(g.nlevels, frames), 256, 0, st>>>(c);
-        if (e->profile) CK(cudaEventRecord(e->ev[4], st));
-        cell_kernel<true><<<cg, 256, 0, st>>>(c);
-        launches += 3;
-    } else {
-        CK(cudaMemsetAsync(e->d_candCount, 0, (size_t)frames * g.nlevels * 4, st));
-        if (e->profile) { CK(cudaEventRecord(e->ev[3], st)); CK(cudaEventRecord(e->ev[4], st)); }
+        cell_nms_kernel<<<dim3((g.totalCells + 7) / 8, frames), 256, 0, st>>>(c);
+        launches++;
     }
-    if (e->profile) CK(cudaEventRecord(e->ev[5], st));
-    // 4. quadtree distribution
+    if (e->profile) CK(cudaEventRecord(e->ev[3], st));
+    // 4. quadtree distribution (gathers the cell lists into vToDistributeKeys first)
     QtArgs q{};
     q.cand = e->d_cand; q.candFrameStride = g.candTotal; q.candCount = e->d_candCount;
+    q.cellCount = e->d_cellCount; q.cellOffs = e->d_cellOffs; q.slots = e->d_slots; q.slotFrameStride = g.slotTotal;
+    q.totalCells = g.totalCells;
     q.keyA = e->d_keyA; q.keyB = e->d_keyB; q.valA = e->d_valA; q.valB = e->d_valB;
     q.sel = e->d_sel; q.selCount = e->d_selCount; q.err = d_err;
     q.nlevels = g.nlevels; q.selTotal = g.selTotal; q.nodeCap = g.nodeCap;
@@ -355,10 +358,12 @@ static int enqueue_pipeline(orbx_extractor* e, const uint8_t* src, size_t srcPit
         const LevelGeom& v = g.lv[l];
         q.candOff[l] = v.candOff; q.N[l] = v.N; q.nIni[l] = v.nIni; q.qH[l] = v.qH; q.depth[l] = v.depth;
         q.maxSel[l] = v.maxSel; q.selOff[l] = v.selOff; q.hX[l] = v.hX;
+        q.cellOff[l] = v.cellOff; q.slotOff[l] = v.slotOff; q.slotCap[l] = v.slotCap; q.candCap[l] = v.candCap;
     }
+    q.cellOff[g.nlevels] = g.totalCells;
     quadtree_kernel<<<dim3(g.nlevels, frames), QT_THREADS, qt_smem_bytes(g.nodeCap), st>>>(q);
     launches++;
-    if (e->profile) CK(cudaEventRecord(e->ev[6], st));
+    if (e->profile) CK(cudaEventRecord(e->ev[4], st));
     // 5. orientation, descriptors, output assembly
     DescArgs d{};
     d.pyr = e->d_pyr; d.pyrFrameStride = g.pyrBytes; d.blur = e->d_blur; d.planeFrameStride = g.planeBytes;
@@ -372,7 +377,7 @@ static int enqueue_pipeline(orbx_extractor* e, const uint8_t* src, size_t srcPit
     d.selOff[g.nlevels] = g.selTotal;
     describe_kernel<<<dim3((g.selTotal + 7) / 8, frames), 256, 0, st>>>(d);
     launches++;
-    if (e->profile) CK(cudaEventRecord(e->ev[7], st));
+    if (e->profile) CK(cudaEventRecord(e->ev[5], st));
     e->launches = launches;
     e->lastFrames = frames;
     CK(cudaGetLastError());
@@ -605,11 +610,11 @@ int orbx_set_profiling(orbx_t* e, int on) {
 }
 
 int orbx_stage_times(orbx_t* e, float* ms, int n) {
-    if (!e || !ms || n < 7 || !e->profile) return ORBX_E_INVALID;
+    if (!e || !ms || n < ORBX_NUM_STAGES || !e->profile) return ORBX_E_INVALID;
     std::lock_guard<std::mutex> lk(e->mtx);
     CK(cudaSetDevice(e->device));
-    CK(cudaEventSynchronize(e->ev[7]));
-    for (int i = 0; i < 7; i++) CK(cudaEventElapsedTime(&ms[i], e->ev[i], e->ev[i + 1]));
+    CK(cudaEventSynchronize(e->ev[ORBX_NUM_STAGES]));
+    for (int i = 0; i < ORBX_NUM_STAGES; i++) CK(cudaEventElapsedTime(&ms[i], e->ev[i], e->ev[i + 1]));
     return ORBX_OK;
 }
 

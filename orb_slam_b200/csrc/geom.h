@@ -28,6 +28,8 @@ struct LevelGeom {
     int cellOff;             // index of this level's first cell in the per-frame cell arrays
     // candidates
     int candCap;             // worst-case number of NMS survivors
+    int slotCap;             // per-cell survivor list capacity (worst case of the largest cell)
+    unsigned long long slotOff;   // element offset of the level's first cell slot list inside one frame's slot array
     unsigned long long candOff;   // element offset inside one frame's candidate array
     // quadtree, :644-907
     int N;                   // mnFeaturesPerLevel[level]
@@ -52,6 +54,7 @@ struct FrameGeom {
     unsigned long long pyrBytes;     // per frame
     unsigned long long planeBytes;   // per frame (blur block and score block each)
     unsigned long long candTotal;    // candidate elements per frame
+    unsigned long long slotTotal;    // cell slot elements per frame
     int nodeCap;             // quadtree node capacity (power of two) over all levels
     LevelGeom lv[ORB_MAX_LEVELS];
 };

@@ -25,9 +25,19 @@ constexpr int QT_THREADS = 512;
 constexpr int QT_WARPS = QT_THREADS / 32;
 
 struct QtArgs {
-    const uint32_t* cand;            // packed x:12|y:12|score:8, [frames][candTotal]
+    uint32_t* cand;                  // packed x:12|y:12|score:8, [frames][candTotal]: vToDistributeKeys, built here
     unsigned long long candFrameStride;
-    const int* candCount;            // [frames][nlevels]
+    int* candCount;                  // [frames][nlevels] (written here)
+    // per-cell survivor lists of cell_nms_kernel (cells.cuh), concatenated in cell row-major order
+    const uint32_t* cellCount;       // [frames][totalCells]
+    uint32_t* cellOffs;              // [frames][totalCells] scratch: exclusive scan of cellCount inside a level
+    const uint32_t* slots;           // [frames][slotTotal]
+    unsigned long long slotFrameStride;
+    int totalCells;
+    int cellOff[ORB_MAX_LEVELS + 1];
+    unsigned long long slotOff[ORB_MAX_LEVELS];
+    int slotCap[ORB_MAX_LEVELS];
+    int candCap[ORB_MAX_LEVELS];
     uint32_t* keyA; uint32_t* keyB;  // sort ping-pong, same layout as cand
     uint32_t* valA; uint32_t* valB;
     uint32_t* sel;                   // [frames][selTotal] retained candidates, packed like cand

@@ -63,14 +63,54 @@ __global__ void __launch_bounds__(QT_THREADS) quadtree_kernel(QtArgs a) {
         s.misc = (int*)p; p += 64;
         s.dep[0] = p; p += cap; s.dep[1] = p;
     }
-    const int M = a.candCount[frame * a.nlevels + l];
     int* selCount = a.selCount + frame * a.nlevels + l;
-    if (M <= 0) { if (tid == 0) *selCount = 0; return; }
     const int depth = a.depth[l], N = a.N[l], nIni = a.nIni[l];
     const size_t off = (size_t)frame * a.candFrameStride + a.candOff[l];
-    const uint32_t* cand = a.cand + off;
+    uint32_t* cand = a.cand + off;
     uint32_t* kA = a.keyA + off; uint32_t* kB = a.keyB + off;
     uint32_t* vA = a.valA + off; uint32_t* vB = a.valB + off;
+
+    // 0. vToDistributeKeys = the cells' survivor lists in cell row-major order (:952-1002): scan the counts, gather
+    int M;
+    {
+        const int nc = a.cellOff[l + 1] - a.cellOff[l];
+        const uint32_t* cnt = a.cellCount + (size_t)frame * a.totalCells + a.cellOff[l];
+        uint32_t* offs = a.cellOffs + (size_t)frame * a.totalCells + a.cellOff[l];
+        const int lane = tid & 31, wid = tid >> 5;
+        const int per = (nc + QT_THREADS - 1) / QT_THREADS;
+        const int b = min(tid * per, nc), e = min(b + per, nc);
+        int sum = 0;
+        for (int i = b; i < e; i++) sum += (int)cnt[i];
+        int inc = sum;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            const int t = __shfl_up_sync(0xffffffffu, inc, d);
+            if (lane >= d) inc += t;
+        }
+        if (lane == 31) s.warpTmp[wid] = inc;
+        __syncthreads();
+        int base = 0, total = 0;
+        for (int k = 0; k < QT_WARPS; k++) { const int v = s.warpTmp[k]; if (k < wid) base += v; total += v; }
+        int run = base + inc - sum;
+        for (int i = b; i < e; i++) { offs[i] = (uint32_t)run; run += (int)cnt[i]; }
+        M = total;
+        if (M > a.candCap[l]) { if (tid == 0) { atomicExch(a.err, 105); *selCount = 0; a.candCount[frame * a.nlevels + l] = 0; } return; }
+        __syncthreads();
+        const uint32_t* slots = a.slots + (size_t)frame * a.slotFrameStride + a.slotOff[l];
+        const int cap = a.slotCap[l];
+        for (int c0 = wid * 32; c0 < nc; c0 += QT_WARPS * 32) {
+            const int c = c0 + lane;
+            const int n = c < nc ? (int)cnt[c] : 0;
+            const int o = c < nc ? (int)offs[c] : 0;
+            for (int j = 0; j < 32 && c0 + j < nc; j++) {
+                const int nj = __shfl_sync(0xffffffffu, n, j), oj = __shfl_sync(0xffffffffu, o, j);
+                for (int t = lane; t < nj; t += 32) cand[oj + t] = slots[(size_t)(c0 + j) * cap + t];
+            }
+        }
+        if (tid == 0) a.candCount[frame * a.nlevels + l] = M;
+        __syncthreads();
+    }
+    if (M <= 0) { if (tid == 0) *selCount = 0; return; }
 
     // 1. path codes
     for (int i = tid; i < M; i += QT_THREADS) {
