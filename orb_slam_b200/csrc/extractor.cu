@@ -45,14 +45,17 @@ struct orbx_extractor {
     int capFrames = 0;                       // frames the workspaces are sized for
     int lastFrames = 0;
     ResizeTap* d_tabs = nullptr;
-    uint8_t* d_in = nullptr; size_t inPitch = 0, inFrameStride = 0;
+    uint8_t* d_in[2] = {nullptr, nullptr}; size_t inBytes = 0;   // double-buffered H2D targets (host layout kept: linear copies)
     uint8_t *d_pyr = nullptr, *d_blur = nullptr, *d_score = nullptr;
     uint32_t *d_cellCount = nullptr, *d_cellOffs = nullptr, *d_cand = nullptr, *d_slots = nullptr;
     uint32_t *d_keyA = nullptr, *d_keyB = nullptr, *d_valA = nullptr, *d_valB = nullptr, *d_sel = nullptr;
     int *d_candCount = nullptr, *d_selCount = nullptr, *d_err = nullptr;
     // result block (device + pinned host mirror): [n_out[frames]] [err] [kps] [desc]
-    uint8_t* d_res = nullptr; uint8_t* h_res = nullptr; size_t resBytes = 0;
-    uint8_t* h_in = nullptr; size_t hInBytes = 0;       // pinned staging for pageable inputs
+    uint8_t* d_res[2] = {nullptr, nullptr}; uint8_t* h_res[2] = {nullptr, nullptr}; size_t resBytes = 0;
+    uint8_t* h_in[2] = {nullptr, nullptr}; size_t hInBytes = 0;       // pinned staging for pageable inputs
+    // host-buffer path: chunks of the batch flow through copy-in / compute / copy-out streams
+    cudaStream_t sIn = nullptr, sOut = nullptr;
+    cudaEvent_t evIn[2] = {}, evCompute[2] = {}, evOut[2] = {};
     int launches = 0;
     bool profile = false;                    // record one CUDA event per stage boundary
     cudaEvent_t ev[8] = {};
@@ -205,15 +208,15 @@ static int build_geometry(orbx_extractor* e, int width, int height, FrameGeom& g
 // workspaces
 // ---------------------------------------------------------------------------
 static void free_workspace(orbx_extractor* e) {
-    cudaFree(e->d_tabs); cudaFree(e->d_in); cudaFree(e->d_pyr); cudaFree(e->d_blur); cudaFree(e->d_score);
+    cudaFree(e->d_tabs); cudaFree(e->d_pyr); cudaFree(e->d_blur); cudaFree(e->d_score);
     cudaFree(e->d_cellCount); cudaFree(e->d_cellOffs); cudaFree(e->d_cand); cudaFree(e->d_slots);
     cudaFree(e->d_keyA); cudaFree(e->d_keyB); cudaFree(e->d_valA); cudaFree(e->d_valB); cudaFree(e->d_sel);
-    cudaFree(e->d_candCount); cudaFree(e->d_selCount); cudaFree(e->d_res);
-    if (e->h_res) cudaFreeHost(e->h_res);
-    e->d_tabs = nullptr; e->d_in = e->d_pyr = e->d_blur = e->d_score = nullptr;
+    cudaFree(e->d_candCount); cudaFree(e->d_selCount); cudaFree(e->d_res[0]); cudaFree(e->d_res[1]);
+    for (int b = 0; b < 2; b++) if (e->h_res[b]) cudaFreeHost(e->h_res[b]);
+    e->d_tabs = nullptr; e->d_pyr = e->d_blur = e->d_score = nullptr;
     e->d_slots = nullptr;
     e->d_cellCount = e->d_cellOffs = e->d_cand = e->d_keyA = e->d_keyB = e->d_valA = e->d_valB = e->d_sel = nullptr;
-    e->d_candCount = e->d_selCount = nullptr; e->d_res = nullptr; e->h_res = nullptr;
+    e->d_candCount = e->d_selCount = nullptr; e->d_res[0] = e->d_res[1] = nullptr; e->h_res[0] = e->h_res[1] = nullptr;
     e->capFrames = 0; e->haveGeom = false;
 }
 
@@ -226,7 +229,7 @@ static size_t res_head(int frames) { return ((size_t)(frames + 1) * 4 + 63) & ~(
 
 static int ensure_workspace(orbx_extractor* e, int width, int height, int frames, bool needInput) {
     if (e->haveGeom && e->g.width == width && e->g.height == height && frames <= e->capFrames &&
-        (!needInput || e->d_in))
+        (!needInput || e->d_res[1]))
         return ORBX_OK;
     const bool sameGeom = e->haveGeom && e->g.width == width && e->g.height == height;
     const int newCap = sameGeom ? std::max(frames, e->capFrames) : frames;
@@ -235,17 +238,13 @@ static int ensure_workspace(orbx_extractor* e, int width, int height, int frames
     int rc = build_geometry(e, width, height, g, tabs);
     if (rc != ORBX_OK) return rc;
     CK(cudaStreamSynchronize(e->stream));
-    const bool hadInput = e->d_in != nullptr;
+    const bool hadInput = e->d_res[1] != nullptr;
+    CK(cudaStreamSynchronize(e->sIn)); CK(cudaStreamSynchronize(e->sOut));
     free_workspace(e);
     e->g = g;
     const size_t F = (size_t)newCap;
     CK(cudaMalloc(&e->d_tabs, std::max<size_t>(tabs.size(), 1) * sizeof(ResizeTap)));
     if (!tabs.empty()) CK(cudaMemcpy(e->d_tabs, tabs.data(), tabs.size() * sizeof(ResizeTap), cudaMemcpyHostToDevice));
-    if (needInput || hadInput) {
-        e->inPitch = ((size_t)width + 127) & ~(size_t)127;
-        e->inFrameStride = e->inPitch * height;
-        CK(cudaMalloc(&e->d_in, e->inFrameStride * F));
-    }
     CK(cudaMalloc(&e->d_pyr, g.pyrBytes * F));
     CK(cudaMalloc(&e->d_blur, g.planeBytes * F));
     CK(cudaMalloc(&e->d_score, g.planeBytes * F));
@@ -262,8 +261,10 @@ static int ensure_workspace(orbx_extractor* e, int width, int height, int frames
     CK(cudaMalloc(&e->d_candCount, F * g.nlevels * 4));
     CK(cudaMalloc(&e->d_selCount, F * g.nlevels * 4));
     e->resBytes = res_bytes(g, newCap);
-    CK(cudaMalloc(&e->d_res, e->resBytes));
-    CK(cudaMallocHost(&e->h_res, e->resBytes));
+    for (int b = 0; b < (needInput || hadInput ? 2 : 1); b++) {
+        CK(cudaMalloc(&e->d_res[b], e->resBytes));
+        CK(cudaMallocHost(&e->h_res[b], e->resBytes));
+    }
     e->capFrames = newCap;
     e->haveGeom = true;
     // kernel attributes
@@ -416,6 +417,13 @@ int orbx_create(orbx_t** out, int nfeatures, float scaleFactor, int nlevels, int
     e->scaleFactor = scaleFactor;
     init_tables(e);
     cudaError_t rc = cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking);
+    if (rc == cudaSuccess) rc = cudaStreamCreateWithFlags(&e->sIn, cudaStreamNonBlocking);
+    if (rc == cudaSuccess) rc = cudaStreamCreateWithFlags(&e->sOut, cudaStreamNonBlocking);
+    for (int b = 0; b < 2 && rc == cudaSuccess; b++) {
+        rc = cudaEventCreateWithFlags(&e->evIn[b], cudaEventDisableTiming);
+        if (rc == cudaSuccess) rc = cudaEventCreateWithFlags(&e->evCompute[b], cudaEventDisableTiming);
+        if (rc == cudaSuccess) rc = cudaEventCreateWithFlags(&e->evOut[b], cudaEventDisableTiming);
+    }
     if (rc == cudaSuccess) rc = cudaMalloc(&e->d_err, 64);
     if (rc == cudaSuccess) rc = cudaMemcpyToSymbol(c_pattern, orb_pattern_31, 1024);
     if (rc == cudaSuccess) rc = cudaMemcpyToSymbol(c_umax, e->umax, sizeof(e->umax));
@@ -431,7 +439,15 @@ void orbx_destroy(orbx_t* e) {
     free_workspace(e);
     cudaFree(e->d_err);
     for (int i = 0; i < 8; i++) if (e->ev[i]) cudaEventDestroy(e->ev[i]);
-    if (e->h_in) cudaFreeHost(e->h_in);
+    for (int b = 0; b < 2; b++) {
+        cudaFree(e->d_in[b]);
+        if (e->h_in[b]) cudaFreeHost(e->h_in[b]);
+        if (e->evIn[b]) cudaEventDestroy(e->evIn[b]);
+        if (e->evCompute[b]) cudaEventDestroy(e->evCompute[b]);
+        if (e->evOut[b]) cudaEventDestroy(e->evOut[b]);
+    }
+    if (e->sIn) cudaStreamDestroy(e->sIn);
+    if (e->sOut) cudaStreamDestroy(e->sOut);
     cudaStreamDestroy(e->stream);
     delete e;
 }
@@ -485,68 +501,141 @@ int orbx_extract_batch_device(orbx_t* e, const uint8_t* d_images, int n, int wid
     return enqueue_pipeline(e, d_images, step, frame_stride, n, d_keypoints, d_descriptors, capacity, d_n_out, e->d_err);
 }
 
+// frames per pipeline chunk of the host-buffer path: large enough to fill the GPU (>= 8 CTAs per SM on the
+// smallest level), small enough that copy-in / compute / copy-out of neighbouring chunks overlap
+#define ORBX_CHUNK 64
+
+static bool is_pinned(const void* p) {
+    cudaPointerAttributes at{};
+    const bool pinned = cudaPointerGetAttributes(&at, p) == cudaSuccess && at.type == cudaMemoryTypeHost;
+    cudaGetLastError();
+    return pinned;
+}
+
 int orbx_extract_batch(orbx_t* e, const uint8_t* const* images, int n, int width, int height, size_t step,
                        orbx_keypoint* keypoints, uint8_t* descriptors, int capacity, int* n_out) {
     if (!e || !images || n <= 0 || !keypoints || !descriptors || !n_out) return ORBX_E_INVALID;
     if (width <= 0 || height <= 0) { for (int i = 0; i < n; i++) n_out[i] = -1; return ORBX_OK; }   // empty image, :1252
     if (step < (size_t)width) return ORBX_E_INVALID;
+    for (int i = 0; i < n; i++) if (!images[i]) return ORBX_E_INVALID;
     std::lock_guard<std::mutex> lk(e->mtx);
     CK(cudaSetDevice(e->device));
-    int rc = ensure_workspace(e, width, height, n, true);
+    const int chunk = std::min(n, ORBX_CHUNK);
+    int rc = ensure_workspace(e, width, height, chunk, true);
     if (rc != ORBX_OK) return rc;
     const FrameGeom& g = e->g;
     const int cap = g.selTotal;                 // device-side capacity: never overflows
-    // H2D: straight from the caller's buffer when it is page-locked, else through pinned staging
-    for (int i = 0; i < n; i++) {
-        if (!images[i]) return ORBX_E_INVALID;
-        cudaPointerAttributes at{};
-        const bool pinned = cudaPointerGetAttributes(&at, images[i]) == cudaSuccess && at.type == cudaMemoryTypeHost;
-        cudaGetLastError();
-        const uint8_t* srcp = images[i];
-        size_t srcStep = step;
-        if (!pinned) {
-            const size_t need = (size_t)n * width * height;
-            if (e->hInBytes < need) {
-                CK(cudaStreamSynchronize(e->stream));
-                if (e->h_in) cudaFreeHost(e->h_in);
-                e->h_in = nullptr; e->hInBytes = 0;
-                CK(cudaMallocHost(&e->h_in, need));
-                e->hInBytes = need;
+    const int F = e->capFrames;
+    const size_t head = res_head(F);
+    const size_t kpBytes = sizeof(orbx_keypoint);
+    // H2D straight from the caller's buffers when they are page-locked, else through pinned staging; same for D2H
+    bool inPinned = is_pinned(images[0]) && is_pinned(images[n - 1]);
+    const bool outPinned = capacity >= cap && is_pinned(keypoints) && is_pinned(descriptors) &&
+                           is_pinned(keypoints + (size_t)n * capacity - 1) && is_pinned(descriptors + (size_t)n * capacity * 32 - 1);
+    // The device copy keeps the host layout (row pitch = step) so that every H2D is a LINEAR copy: a 2-D copy of
+    // 1241-byte rows into a padded pitch runs at 10 GB/s on this box, a linear one at 55 GB/s (tools/copybench.cu).
+    // The level-0 kernel reads unaligned rows with aligned word loads + funnel shifts.
+    if (inPinned && step > 2 * (size_t)width) inPinned = false;          // very sparse rows: pack through staging instead
+    const size_t devPitch = inPinned ? step : (size_t)width;
+    const size_t devStride = devPitch * height;
+    if (!inPinned) {
+        const size_t need = (size_t)F * width * height;
+        if (e->hInBytes < need) {
+            CK(cudaStreamSynchronize(e->sIn));
+            for (int b = 0; b < 2; b++) {
+                if (e->h_in[b]) cudaFreeHost(e->h_in[b]);
+                e->h_in[b] = nullptr;
+                CK(cudaMallocHost(&e->h_in[b], need));
             }
-            uint8_t* dst = e->h_in + (size_t)i * width * height;
-            for (int y = 0; y < height; y++) std::memcpy(dst + (size_t)y * width, images[i] + (size_t)y * step, width);
-            srcp = dst; srcStep = width;
+            e->hInBytes = need;
         }
-        CK(cudaMemcpy2DAsync(e->d_in + (size_t)i * e->inFrameStride, e->inPitch, srcp, srcStep, width, height,
-                             cudaMemcpyHostToDevice, e->stream));
     }
-    const size_t head = res_head(e->capFrames);
-    int* d_n = (int*)e->d_res;
-    int* d_err = d_n + e->capFrames;
-    orbx_keypoint* d_kps = (orbx_keypoint*)(e->d_res + head);
-    uint8_t* d_desc = e->d_res + head + (size_t)e->capFrames * cap * sizeof(orbx_keypoint);
-    rc = enqueue_pipeline(e, e->d_in, e->inPitch, e->inFrameStride, n, d_kps, d_desc, cap, d_n, d_err);
-    if (rc != ORBX_OK) return rc;
-    // D2H: header (counts + error flag), keypoints and descriptors of the n frames
-    CK(cudaMemcpyAsync(e->h_res, e->d_res, head, cudaMemcpyDeviceToHost, e->stream));
-    CK(cudaMemcpyAsync(e->h_res + head, d_kps, (size_t)n * cap * sizeof(orbx_keypoint), cudaMemcpyDeviceToHost, e->stream));
-    uint8_t* h_desc = e->h_res + head + (size_t)e->capFrames * cap * sizeof(orbx_keypoint);
-    CK(cudaMemcpyAsync(h_desc, d_desc, (size_t)n * cap * 32, cudaMemcpyDeviceToHost, e->stream));
-    CK(cudaStreamSynchronize(e->stream));
-    const int* h_n = (const int*)e->h_res;
-    if (h_n[e->capFrames] != 0) {
-        std::fprintf(stderr, "orbx: device consistency check %d failed\n", h_n[e->capFrames]);
-        return ORBX_E_INTERNAL;
+    if (e->inBytes < devStride * F + 64) {
+        CK(cudaStreamSynchronize(e->sIn)); CK(cudaStreamSynchronize(e->stream));
+        for (int b = 0; b < 2; b++) {
+            cudaFree(e->d_in[b]); e->d_in[b] = nullptr;
+            CK(cudaMalloc(&e->d_in[b], devStride * F + 64));
+        }
+        e->inBytes = devStride * F + 64;
     }
-    const orbx_keypoint* h_kps = (const orbx_keypoint*)(e->h_res + head);
-    for (int i = 0; i < n; i++) {
-        const int k = h_n[i];
-        n_out[i] = k;
-        if (k > capacity) return ORBX_E_CAPACITY;
-        std::memcpy(keypoints + (size_t)i * capacity, h_kps + (size_t)i * cap, (size_t)k * sizeof(orbx_keypoint));
-        std::memcpy(descriptors + (size_t)i * capacity * 32, h_desc + (size_t)i * cap * 32, (size_t)k * 32);
+    const int nchunks = (n + chunk - 1) / chunk;
+    int status = ORBX_OK;
+    auto finalize = [&](int k) -> int {        // host side of chunk k: counts, error flag, staged results
+        const int b = k & 1, f0 = k * chunk, nf = std::min(chunk, n - f0);
+        CK(cudaEventSynchronize(e->evOut[b]));
+        const int* h_n = (const int*)e->h_res[b];
+        if (h_n[F] != 0) {
+            std::fprintf(stderr, "orbx: device consistency check %d failed\n", h_n[F]);
+            return ORBX_E_INTERNAL;
+        }
+        const orbx_keypoint* h_kps = (const orbx_keypoint*)(e->h_res[b] + head);
+        const uint8_t* h_desc = e->h_res[b] + head + (size_t)F * cap * kpBytes;
+        for (int i = 0; i < nf; i++) {
+            const int kq = h_n[i];
+            n_out[f0 + i] = kq;
+            if (kq > capacity) return ORBX_E_CAPACITY;
+            if (!outPinned) {
+                std::memcpy(keypoints + (size_t)(f0 + i) * capacity, h_kps + (size_t)i * cap, (size_t)kq * kpBytes);
+                std::memcpy(descriptors + (size_t)(f0 + i) * capacity * 32, h_desc + (size_t)i * cap * 32, (size_t)kq * 32);
+            }
+        }
+        return ORBX_OK;
+    };
+    for (int k = 0; k < nchunks; k++) {
+        const int b = k & 1, f0 = k * chunk, nf = std::min(chunk, n - f0);
+        // ---- copy-in stream: d_in[b] is free once the compute of chunk k-2 has finished
+        if (k >= 2) CK(cudaStreamWaitEvent(e->sIn, e->evCompute[b], 0));
+        if (inPinned) {
+            // frames that lie back to back in host memory go as one linear copy
+            int i = 0;
+            while (i < nf) {
+                int j = i + 1;
+                while (j < nf && images[f0 + j] == images[f0 + j - 1] + devStride) j++;
+                const size_t bytes = (size_t)(j - i - 1) * devStride + (size_t)(height - 1) * step + width;   // never past the last pixel
+                CK(cudaMemcpyAsync(e->d_in[b] + (size_t)i * devStride, images[f0 + i], bytes, cudaMemcpyHostToDevice, e->sIn));
+                i = j;
+            }
+        } else {
+            if (k >= 2) CK(cudaEventSynchronize(e->evIn[b]));          // staging buffer b consumed by the H2D of chunk k-2
+            for (int i = 0; i < nf; i++) {
+                uint8_t* dst = e->h_in[b] + (size_t)i * width * height;
+                const uint8_t* srcp = images[f0 + i];
+                if (step == (size_t)width) std::memcpy(dst, srcp, (size_t)width * height);
+                else for (int y = 0; y < height; y++) std::memcpy(dst + (size_t)y * width, srcp + (size_t)y * step, width);
+            }
+            CK(cudaMemcpyAsync(e->d_in[b], e->h_in[b], (size_t)width * height * nf, cudaMemcpyHostToDevice, e->sIn));
+        }
+        CK(cudaEventRecord(e->evIn[b], e->sIn));
+        // ---- compute stream: needs the input, and d_res[b] drained by the copy-out of chunk k-2
+        CK(cudaStreamWaitEvent(e->stream, e->evIn[b], 0));
+        if (k >= 2) CK(cudaStreamWaitEvent(e->stream, e->evOut[b], 0));
+        int* d_n = (int*)e->d_res[b];
+        int* d_err = d_n + F;
+        orbx_keypoint* d_kps = (orbx_keypoint*)(e->d_res[b] + head);
+        uint8_t* d_desc = e->d_res[b] + head + (size_t)F * cap * kpBytes;
+        rc = enqueue_pipeline(e, e->d_in[b], devPitch, devStride, nf, d_kps, d_desc, cap, d_n, d_err);
+        if (rc != ORBX_OK) { status = rc; break; }
+        CK(cudaEventRecord(e->evCompute[b], e->stream));
+        // ---- copy-out stream
+        CK(cudaStreamWaitEvent(e->sOut, e->evCompute[b], 0));
+        CK(cudaMemcpyAsync(e->h_res[b], e->d_res[b], head, cudaMemcpyDeviceToHost, e->sOut));
+        if (outPinned) {
+            CK(cudaMemcpy2DAsync(keypoints + (size_t)f0 * capacity, (size_t)capacity * kpBytes, d_kps, (size_t)cap * kpBytes,
+                                 (size_t)cap * kpBytes, nf, cudaMemcpyDeviceToHost, e->sOut));
+            CK(cudaMemcpy2DAsync(descriptors + (size_t)f0 * capacity * 32, (size_t)capacity * 32, d_desc, (size_t)cap * 32,
+                                 (size_t)cap * 32, nf, cudaMemcpyDeviceToHost, e->sOut));
+        } else {
+            CK(cudaMemcpyAsync(e->h_res[b] + head, d_kps, (size_t)nf * cap * kpBytes, cudaMemcpyDeviceToHost, e->sOut));
+            CK(cudaMemcpyAsync(e->h_res[b] + head + (size_t)F * cap * kpBytes, d_desc, (size_t)nf * cap * 32,
+                               cudaMemcpyDeviceToHost, e->sOut));
+        }
+        CK(cudaEventRecord(e->evOut[b], e->sOut));
+        // ---- host: finish chunk k-1 while the GPU works on chunk k
+        if (k >= 1 && status == ORBX_OK) { rc = finalize(k - 1); if (rc != ORBX_OK) status = rc; }
     }
-    return ORBX_OK;
+    if (status == ORBX_OK) status = finalize(nchunks - 1);
+    CK(cudaStreamSynchronize(e->sIn)); CK(cudaStreamSynchronize(e->stream)); CK(cudaStreamSynchronize(e->sOut));
+    return status;
 }
 
 int orbx_extract(orbx_t* e, const uint8_t* image, int width, int height, size_t step, orbx_keypoint* keypoints,

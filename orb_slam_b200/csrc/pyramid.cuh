@@ -182,15 +182,20 @@ __global__ void __launch_bounds__(PYR_THREADS) pyr_level_kernel(PyrArgs a) {
         Hs = (unsigned short*)(smem + pyr_smem_T());
         // level 0 is the caller's image: copy with REFLECT_101 halo (copyMakeBorder, :1372); byte b of a T row is
         // column x0 - 4 + b.  Aligned interior words go as one 32-bit load.
-        const bool aligned = ((((size_t)src + a.srcX0) | (size_t)a.srcPitch) & 3) == 0;
         for (int i = tid; i < TROWS * (TBYTES / 4); i += PYR_THREADS) {
             const int ty = i / (TBYTES / 4), q = i - ty * (TBYTES / 4);
             const int y = y0 - HALO + ty, xb = x0 - 4 + 4 * q;
             uint32_t v = 0;
             if (y < h + HALO) {
                 const uint8_t* row = src + (size_t)reflect101(y, h) * a.srcPitch + a.srcX0;
-                if (aligned && xb >= 0 && xb + 3 < w) v = __ldg((const uint32_t*)(row + xb));
-                else {
+                if (xb >= 4 && xb + 7 < w) {
+                    // interior word of a row at any alignment: two aligned loads + funnel shift (both stay inside the row)
+                    const uint8_t* p = row + xb;
+                    const unsigned mis = (unsigned)((size_t)p & 3);
+                    const uint32_t* ap = (const uint32_t*)(p - mis);
+                    const uint32_t lo = __ldg(ap), hi = mis ? __ldg(ap + 1) : 0u;
+                    v = __funnelshift_r(lo, hi, 8 * mis);
+                } else {
 #pragma unroll
                     for (int j = 0; j < 4; j++) {
                         const int x = xb + j;
