@@ -107,7 +107,7 @@ int orbx_synchronize(orbx_t* ex);
  * including `border` (0..19) pixels of its BORDER_REFLECT_101 frame.
  * `blurred` != 0 returns the 7x7 sigma-2 Gaussian-blurred level instead
  * (the workingMat of src/ORBextractor.cc:1300-1306; border must be 0);
- * `blurred` == 2 returns the FAST score plane (0 below minThFAST), for tests. */
+ * `blurred` == 2 returns the FAST score plane, encoded max(0, score + 1 - minThFAST), for debugging. */
 int orbx_level_size(const orbx_t* ex, int level, int* width, int* height);
 int orbx_get_level(orbx_t* ex, int frame, int level, int border, int blurred, uint8_t* dst,
                    size_t dst_step);

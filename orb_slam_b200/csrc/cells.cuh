@@ -24,7 +24,7 @@ struct CellArgs {
     const uint8_t* score;             // frame 0 score block
     unsigned long long planeFrameStride;
     int nlevels;
-    int iniTh;
+    int iniTh, minTh;                 // the plane stores max(0, score + 1 - minTh)
     int totalCells;                   // per frame
     // per level
     int cellOff[ORB_MAX_LEVELS + 1];
@@ -67,75 +67,91 @@ __device__ __forceinline__ void row_lr(int c0, int c1, int lane, int& l0, int& r
     r1 = lane < 31 ? dn1 : 0;
 }
 
+// masks: this warp's shared scratch, [kind (0 = kept at minTh, 1 = kept at iniTh)][chunk][row] ballots
 template <bool TWO>
 __device__ __forceinline__ void cell_scan(const CellArgs& a, const uint8_t* __restrict__ S, int pitch, const CellBox b, int lane,
-                                          uint32_t* __restrict__ out, int cap, uint32_t* __restrict__ cnt, int* err) {
-    // per-lane ballots of the rows lane and lane+32 (interior height < 64)
-    unsigned mMin[2][2] = {{0, 0}, {0, 0}}, mIni[2][2] = {{0, 0}, {0, 0}};   // [chunk][row >> 5]
-    int nIni = 0, nMin = 0;
+                                          uint32_t* __restrict__ out, int cap, uint32_t* __restrict__ cnt, int* err,
+                                          unsigned (*masks)[2][CELL_MAX_DIM]) {
     const int xa = b.x0 + lane, xb = b.x0 + 32 + lane;
     const bool ina = xa < b.x1, inb = TWO && xb < b.x1;
-    const uint8_t* col = S + ORB_XPAD;
-    auto ld = [&](int y, int& c0, int& c1) {
-        c0 = (ina && y < b.y1) ? col[(size_t)y * pitch + xa] : 0;
-        c1 = (inb && y < b.y1) ? col[(size_t)y * pitch + xb] : 0;
-    };
-    int p0 = 0, p1 = 0, hp0 = 0, hp1 = 0;             // previous row and its horizontal 3-max
-    int c0, c1, n0, n1;
-    ld(b.y0, c0, c1);
-    int cl0, cr0, cl1 = 0, cr1 = 0;
-    if (TWO) row_lr(c0, c1, lane, cl0, cr0, cl1, cr1);
-    else { cl0 = __shfl_up_sync(0xffffffffu, c0, 1); cr0 = __shfl_down_sync(0xffffffffu, c0, 1); if (!lane) cl0 = 0; if (lane == 31) cr0 = 0; }
+    const uint8_t* pa = S + ORB_XPAD + (size_t)b.y0 * pitch + xa;        // walks down the column
     const int rows = b.y1 - b.y0;
-    for (int r = 0; r < rows; r++) {
-        const int y = b.y0 + r;
-        ld(y + 1, n0, n1);                              // zeros past the last interior row
-        int nl0, nr0, nl1 = 0, nr1 = 0;
-        if (TWO) row_lr(n0, n1, lane, nl0, nr0, nl1, nr1);
-        else { nl0 = __shfl_up_sync(0xffffffffu, n0, 1); nr0 = __shfl_down_sync(0xffffffffu, n0, 1); if (!lane) nl0 = 0; if (lane == 31) nr0 = 0; }
-        const int hc0 = max(max(cl0, cr0), c0), hn0 = max(max(nl0, nr0), n0);
-        // strictly greater than all 8 neighbours (non-corners and everything outside the interior count 0)
-        const bool k0 = c0 > max(max(hp0, hn0), max(cl0, cr0));
-        const unsigned bm0 = __ballot_sync(0xffffffffu, k0), bi0 = __ballot_sync(0xffffffffu, k0 && c0 >= a.iniTh);
-        nMin += __popc(bm0); nIni += __popc(bi0);
-        if (lane == (r & 31)) { mMin[0][0] = (r < 32) ? bm0 : mMin[0][0]; mMin[0][1] = (r >= 32) ? bm0 : mMin[0][1];
-                                mIni[0][0] = (r < 32) ? bi0 : mIni[0][0]; mIni[0][1] = (r >= 32) ? bi0 : mIni[0][1]; }
-        hp0 = hc0; p0 = c0; c0 = n0; cl0 = nl0; cr0 = nr0;
-        if (TWO) {
-            const int hc1 = max(max(cl1, cr1), c1), hn1 = max(max(nl1, nr1), n1);
-            const bool k1 = c1 > max(max(hp1, hn1), max(cl1, cr1));
-            const unsigned bm1 = __ballot_sync(0xffffffffu, k1), bi1 = __ballot_sync(0xffffffffu, k1 && c1 >= a.iniTh);
-            nMin += __popc(bm1); nIni += __popc(bi1);
-            if (lane == (r & 31)) { mMin[1][0] = (r < 32) ? bm1 : mMin[1][0]; mMin[1][1] = (r >= 32) ? bm1 : mMin[1][1];
-                                    mIni[1][0] = (r < 32) ? bi1 : mIni[1][0]; mIni[1][1] = (r >= 32) ? bi1 : mIni[1][1]; }
-            hp1 = hc1; p1 = c1; c1 = n1; cl1 = nl1; cr1 = nr1;
+    const int iniTh = a.iniTh - a.minTh + 1;             // in the plane's encoding
+    const uint32_t sBias = (uint32_t)(a.minTh - 1);
+    // rolling state per chunk: centre value c, max(left,right) of its row lr, 3-max of the previous row hp
+    int c0 = ina ? pa[0] : 0, c1 = inb ? pa[32] : 0;
+    int lr0, lr1 = 0, hp0 = 0, hp1 = 0;
+    {
+        int l0, r0, l1, r1;
+        if (TWO) { row_lr(c0, c1, lane, l0, r0, l1, r1); lr1 = max(l1, r1); }
+        else { l0 = __shfl_up_sync(0xffffffffu, c0, 1); r0 = __shfl_down_sync(0xffffffffu, c0, 1); if (!lane) l0 = 0; if (lane == 31) r0 = 0; }
+        lr0 = max(l0, r0);
+    }
+    constexpr int RB = 8;                                // rows fetched together: RB independent loads in flight per lane
+    for (int rb = 0; rb < rows; rb += RB) {
+        int v0[RB], v1[RB];
+#pragma unroll
+        for (int i = 0; i < RB; i++) {                   // row rb+i+1 (the "next" row of step rb+i); zeros past the interior
+            const bool more = rb + i + 1 < rows;
+            v0[i] = (ina && more) ? pa[(size_t)(i + 1) * pitch] : 0;
+            v1[i] = (inb && more) ? pa[(size_t)(i + 1) * pitch + 32] : 0;
+        }
+        pa += (size_t)RB * pitch;
+#pragma unroll
+        for (int i = 0; i < RB; i++) {
+            const int r = rb + i;
+            if (r >= rows) break;                        // warp-uniform
+            const int n0 = v0[i], n1 = v1[i];
+            int nl0, nr0, nl1 = 0, nr1 = 0;
+            if (TWO) row_lr(n0, n1, lane, nl0, nr0, nl1, nr1);
+            else { nl0 = __shfl_up_sync(0xffffffffu, n0, 1); nr0 = __shfl_down_sync(0xffffffffu, n0, 1); if (!lane) nl0 = 0; if (lane == 31) nr0 = 0; }
+            // strictly greater than all 8 neighbours (non-corners and everything outside the interior count 0)
+            const int nlr0 = max(nl0, nr0), hn0 = max(nlr0, n0);
+            const bool k0 = c0 > max(max(hp0, hn0), lr0);
+            const unsigned bm0 = __ballot_sync(0xffffffffu, k0), bi0 = __ballot_sync(0xffffffffu, k0 && c0 >= iniTh);
+            if (lane == 0) { masks[0][0][r] = bm0; masks[1][0][r] = bi0; }
+            hp0 = max(lr0, c0); c0 = n0; lr0 = nlr0;
+            if (TWO) {
+                const int nlr1 = max(nl1, nr1), hn1 = max(nlr1, n1);
+                const bool k1 = c1 > max(max(hp1, hn1), lr1);
+                const unsigned bm1 = __ballot_sync(0xffffffffu, k1), bi1 = __ballot_sync(0xffffffffu, k1 && c1 >= iniTh);
+                if (lane == 0) { masks[0][1][r] = bm1; masks[1][1][r] = bi1; }
+                hp1 = max(lr1, c1); c1 = n1; lr1 = nlr1;
+            }
         }
     }
-    (void)p0; (void)p1;
-    const bool useIni = nIni > 0;                       // :976-987: iniThFAST first, minThFAST only if that found nothing
-    const int total = useIni ? nIni : nMin;
+    __syncwarp();
+    // totals at both thresholds (rows < 64: two mask rows per lane)
+    int nMin = 0, nIni = 0;
+    for (int r = lane; r < rows; r += 32) {
+        nMin += __popc(masks[0][0][r]); nIni += __popc(masks[1][0][r]);
+        if (TWO) { nMin += __popc(masks[0][1][r]); nIni += __popc(masks[1][1][r]); }
+    }
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) { nMin += __shfl_xor_sync(0xffffffffu, nMin, d); nIni += __shfl_xor_sync(0xffffffffu, nIni, d); }
+    const int kind = nIni > 0 ? 1 : 0;                   // :976-987: iniThFAST first, minThFAST only if that found nothing
+    const int total = kind ? nIni : nMin;
     if (lane == 0) *cnt = (uint32_t)total;
     if (total == 0) return;
     if (total > cap) { if (lane == 0) atomicExch(err, 301); return; }
+    const uint8_t* col = S + ORB_XPAD;
     int pos = 0;
     for (int r = 0; r < rows; r++) {
         const int y = b.y0 + r;
-        const unsigned w0 = useIni ? ((r < 32) ? mIni[0][0] : mIni[0][1]) : ((r < 32) ? mMin[0][0] : mMin[0][1]);
-        const unsigned m0 = __shfl_sync(0xffffffffu, w0, r & 31);
+        const unsigned m0 = masks[kind][0][r];
         if (m0) {
             if ((m0 >> lane) & 1u) {
-                const uint32_t s = col[(size_t)y * pitch + xa];
+                const uint32_t s = col[(size_t)y * pitch + xa] + sBias;
                 out[pos + __popc(m0 & ((1u << lane) - 1))] =
                     ((uint32_t)(xa - ORB_BORDER_MIN)) | ((uint32_t)(y - ORB_BORDER_MIN) << 12) | (s << 24);
             }
             pos += __popc(m0);
         }
         if (TWO) {
-            const unsigned w1 = useIni ? ((r < 32) ? mIni[1][0] : mIni[1][1]) : ((r < 32) ? mMin[1][0] : mMin[1][1]);
-            const unsigned m1 = __shfl_sync(0xffffffffu, w1, r & 31);
+            const unsigned m1 = masks[kind][1][r];
             if (m1) {
                 if ((m1 >> lane) & 1u) {
-                    const uint32_t s = col[(size_t)y * pitch + xb];
+                    const uint32_t s = col[(size_t)y * pitch + xb] + sBias;
                     out[pos + __popc(m1 & ((1u << lane) - 1))] =
                         ((uint32_t)(xb - ORB_BORDER_MIN)) | ((uint32_t)(y - ORB_BORDER_MIN) << 12) | (s << 24);
                 }
@@ -146,10 +162,12 @@ __device__ __forceinline__ void cell_scan(const CellArgs& a, const uint8_t* __re
 }
 
 __global__ void __launch_bounds__(256) cell_nms_kernel(CellArgs a) {
+    __shared__ unsigned s_masks[8][2][2][CELL_MAX_DIM];
     const int lane = threadIdx.x & 31;
     const int cell = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     const int frame = blockIdx.y;
     if (cell >= a.totalCells) return;
+    unsigned (*masks)[2][CELL_MAX_DIM] = s_masks[threadIdx.x >> 5];
     int l = 0;
     while (cell >= a.cellOff[l + 1]) l++;
     const int c = cell - a.cellOff[l];
@@ -160,8 +178,8 @@ __global__ void __launch_bounds__(256) cell_nms_kernel(CellArgs a) {
     if (b.x1 - b.x0 > CELL_MAX_DIM || b.y1 - b.y0 > CELL_MAX_DIM) { if (lane == 0) { *cnt = 0; atomicExch(a.err, 302); } return; }
     const uint8_t* S = a.score + (size_t)frame * a.planeFrameStride + a.planeOff[l];
     uint32_t* out = a.slots + (size_t)frame * a.slotFrameStride + a.slotOff[l] + (size_t)c * a.slotCap[l];
-    if (b.x1 - b.x0 > 32) cell_scan<true>(a, S, a.pitch[l], b, lane, out, a.slotCap[l], cnt, a.err);
-    else cell_scan<false>(a, S, a.pitch[l], b, lane, out, a.slotCap[l], cnt, a.err);
+    if (b.x1 - b.x0 > 32) cell_scan<true>(a, S, a.pitch[l], b, lane, out, a.slotCap[l], cnt, a.err, masks);
+    else cell_scan<false>(a, S, a.pitch[l], b, lane, out, a.slotCap[l], cnt, a.err, masks);
 }
 
 }  // namespace orbx

@@ -48,18 +48,23 @@ __device__ __forceinline__ float fast_atan2_deg(float y, float x) {
     return a;
 }
 
+constexpr int DP_ROWS = 2 * ORB_EDGE + 1;      // blurred patch: 39 rows, |offset| <= ceil(13*sqrt(2)) = 19
+constexpr int DP_WORDS = 11;                   // 39 bytes at any alignment fit in 11 aligned words
+constexpr int IP_ROWS = 2 * ORB_HALF_PATCH + 1;   // intensity-centroid patch: 31 rows
+constexpr int IP_WORDS = 9;                    // 31 bytes at any alignment fit in 9 aligned words
+
+__device__ uint32_t g_pattern32[256];          // bit_pattern_31_ as [pair k][descriptor byte] words (x0,y0,x1,y1 signed bytes)
+
 __global__ void __launch_bounds__(256) describe_kernel(DescArgs a) {
-    // pattern staged in shared memory as [pair k][byte lane] words: lanes read distinct banks.  (Lane-indexed
-    // reads of __constant__ memory serialise 32-way: ncu showed 62 warps/issue stalled on mio_throttle.)
+    // Both patches of a keypoint are staged in shared memory with aligned, coalesced 32-bit loads (all in flight at
+    // once); the 961 moment reads and 512 rotated-BRIEF gathers then hit shared memory instead of L1/L2.
     __shared__ uint32_t s_pat[256];
-    {
-        const int t = threadIdx.x;          // blockDim.x == 256: word t = pair (t>>5) of byte (t&31)
-        const signed char* q = c_pattern + (t & 31) * 32 + (t >> 5) * 4;
-        s_pat[t] = (uint32_t)(uint8_t)q[0] | ((uint32_t)(uint8_t)q[1] << 8) | ((uint32_t)(uint8_t)q[2] << 16) | ((uint32_t)(uint8_t)q[3] << 24);
-    }
+    __shared__ uint32_t s_blur[8][DP_ROWS * DP_WORDS];
+    __shared__ uint32_t s_img[8][IP_ROWS * IP_WORDS];
+    s_pat[threadIdx.x] = g_pattern32[threadIdx.x];       // blockDim.x == 256
     __syncthreads();
-    const int lane = threadIdx.x & 31;
-    const int slot = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    const int slot = blockIdx.x * (blockDim.x >> 5) + wid;
     const int frame = blockIdx.y;
     if (slot >= a.selTotal) return;
     int l = 0;
@@ -79,20 +84,38 @@ __global__ void __launch_bounds__(256) describe_kernel(DescArgs a) {
     const int x = (int)(c & 0xfff) + ORB_BORDER_MIN, y = (int)((c >> 12) & 0xfff) + ORB_BORDER_MIN;   // :1021-1022
     const int pitch = a.pitch[l];
 
+    // ---- stage the patches (rows start 16-byte aligned at interior column 0: alignment = column & 3)
+    const int bx0 = (x - ORB_EDGE) & ~3, ix0 = (x - ORB_HALF_PATCH) & ~3;     // both >= 0: keypoints sit >= 19 px inside
+    {
+        const uint8_t* bl = a.blur + (size_t)frame * a.planeFrameStride + a.planeOff[l] + (size_t)(y - ORB_EDGE) * pitch + ORB_XPAD + bx0;
+        for (int t = lane; t < DP_ROWS * DP_WORDS; t += 32) {
+            const int r = t / DP_WORDS, wv = t - r * DP_WORDS;
+            s_blur[wid][t] = __ldg((const uint32_t*)(bl + (size_t)r * pitch) + wv);
+        }
+        const uint8_t* im = a.pyr + (size_t)frame * a.pyrFrameStride + a.pyrOff[l] + (size_t)(ORB_EDGE + y - ORB_HALF_PATCH) * pitch + ORB_XPAD + ix0;
+        for (int t = lane; t < IP_ROWS * IP_WORDS; t += 32) {
+            const int r = t / IP_WORDS, wv = t - r * IP_WORDS;
+            s_img[wid][t] = __ldg((const uint32_t*)(im + (size_t)r * pitch) + wv);
+        }
+    }
+    __syncwarp();
+
     // ---- IC_Angle: lanes 0..30 own column u = lane-15 of the disc
-    const uint8_t* img = a.pyr + (size_t)frame * a.pyrFrameStride + a.pyrOff[l] + (size_t)(ORB_EDGE + y) * pitch + ORB_XPAD + x;
     int m10 = 0, m01 = 0;
     const int u = lane - ORB_HALF_PATCH;
     if (lane < 31) {
+        const uint8_t* img = (const uint8_t*)s_img[wid] + (x - ORB_HALF_PATCH - ix0) + lane;   // row 0 = v = -15
         const int au = abs(u);
+        int colsum = 0;
 #pragma unroll
         for (int v = -ORB_HALF_PATCH; v <= ORB_HALF_PATCH; v++) {
             if (au <= c_umax[abs(v)]) {
-                const int val = img[v * pitch + u];
-                m10 += u * val;
+                const int val = img[(v + ORB_HALF_PATCH) * (IP_WORDS * 4)];
+                colsum += val;
                 m01 += v * val;
             }
         }
+        m10 = u * colsum;
     }
 #pragma unroll
     for (int d = 16; d > 0; d >>= 1) {
@@ -111,7 +134,7 @@ __global__ void __launch_bounds__(256) describe_kernel(DescArgs a) {
     }
     ca = __shfl_sync(0xffffffffu, ca, 0);
     sb = __shfl_sync(0xffffffffu, sb, 0);
-    const uint8_t* bl = a.blur + (size_t)frame * a.planeFrameStride + a.planeOff[l] + (size_t)y * pitch + ORB_XPAD + x;
+    const uint8_t* bl = (const uint8_t*)s_blur[wid] + ORB_EDGE * (DP_WORDS * 4) + (x - bx0);     // patch centre
     int val = 0;
 #pragma unroll
     for (int k = 0; k < 8; k++) {
@@ -123,7 +146,7 @@ __global__ void __launch_bounds__(256) describe_kernel(DescArgs a) {
         const int q0 = __float2int_rn(__fsub_rn(__fmul_rn(x0, ca), __fmul_rn(y0, sb)));      // cvRound(x*a - y*b)
         const int r1 = __float2int_rn(__fadd_rn(__fmul_rn(x1, sb), __fmul_rn(y1, ca)));
         const int q1 = __float2int_rn(__fsub_rn(__fmul_rn(x1, ca), __fmul_rn(y1, sb)));
-        const int t0 = bl[r0 * pitch + q0], t1 = bl[r1 * pitch + q1];
+        const int t0 = bl[r0 * (DP_WORDS * 4) + q0], t1 = bl[r1 * (DP_WORDS * 4) + q1];
         val |= (t0 < t1) << k;
     }
     const size_t o = (size_t)frame * a.cap + outIdx;

@@ -135,7 +135,7 @@ static int build_geometry(orbx_extractor* e, int width, int height, FrameGeom& g
         LevelGeom& v = g.lv[l];
         v.w = host_round_even((float)width * e->isf[l]);          // :1348
         v.h = host_round_even((float)height * e->isf[l]);
-        if (v.w < 8 || v.h < 8) return ORBX_E_UNSUPPORTED;
+        if (v.w <= ORB_EDGE || v.h <= ORB_EDGE) return ORBX_E_UNSUPPORTED;   // single-reflection borders need w, h > 19
         if (v.w - 32 > 4095 || v.h - 32 > 4095) return ORBX_E_UNSUPPORTED;   // 12-bit packed coordinates
         v.pitch = ((ORB_XPAD + ((v.w + 15) & ~15) + 32) + 127) & ~127;
         v.prow0 = ORB_EDGE;
@@ -320,18 +320,18 @@ static int enqueue_pipeline(orbx_extractor* e, const uint8_t* src, size_t srcPit
         int off = 0;
         for (int l = 0; l < g.nlevels; l++) {
             const LevelGeom& v = g.lv[l];
-            b.itemOff[l] = off;
-            off += (v.w + 2 * ORB_EDGE) * (v.h + 2 * ORB_EDGE) - v.w * v.h;
+            b.rowOff[l] = off;
+            off += v.h + 2 * ORB_EDGE;
             b.pyrOff[l] = v.pyrOff; b.w[l] = v.w; b.h[l] = v.h; b.pitch[l] = v.pitch;
         }
-        b.itemOff[g.nlevels] = off;
-        border_kernel<<<dim3((off + 255) / 256, frames), 256, 0, st>>>(b);
+        b.rowOff[g.nlevels] = off;
+        border_kernel<<<dim3((off + 7) / 8, frames), 256, 0, st>>>(b);
         launches++;
     }
     if (e->profile) CK(cudaEventRecord(e->ev[2], st));
     // 3. per-cell NMS + threshold fallback -> per-cell survivor lists (one launch, score plane read once)
     CellArgs c{};
-    c.score = e->d_score; c.planeFrameStride = g.planeBytes; c.nlevels = g.nlevels; c.iniTh = g.iniTh;
+    c.score = e->d_score; c.planeFrameStride = g.planeBytes; c.nlevels = g.nlevels; c.iniTh = g.iniTh; c.minTh = g.minTh;
     c.totalCells = g.totalCells;
     for (int l = 0; l < g.nlevels; l++) {
         const LevelGeom& v = g.lv[l];
@@ -426,6 +426,16 @@ int orbx_create(orbx_t** out, int nfeatures, float scaleFactor, int nlevels, int
     }
     if (rc == cudaSuccess) rc = cudaMalloc(&e->d_err, 64);
     if (rc == cudaSuccess) rc = cudaMemcpyToSymbol(c_pattern, orb_pattern_31, 1024);
+    if (rc == cudaSuccess) {
+        // [pair k][descriptor byte i] -> (x0, y0, x1, y1) of test 8*i + k, as one word (computeOrbDescriptor, :166-189)
+        uint32_t pat32[256];
+        const signed char* pt = (const signed char*)orb_pattern_31;
+        for (int t = 0; t < 256; t++) {
+            const signed char* q = pt + (t & 31) * 32 + (t >> 5) * 4;
+            pat32[t] = (uint32_t)(uint8_t)q[0] | ((uint32_t)(uint8_t)q[1] << 8) | ((uint32_t)(uint8_t)q[2] << 16) | ((uint32_t)(uint8_t)q[3] << 24);
+        }
+        rc = cudaMemcpyToSymbol(g_pattern32, pat32, sizeof(pat32));
+    }
     if (rc == cudaSuccess) rc = cudaMemcpyToSymbol(c_umax, e->umax, sizeof(e->umax));
     if (rc != cudaSuccess) { delete e; return (int)rc; }
     *out = e;

@@ -98,7 +98,7 @@ __device__ __forceinline__ uint32_t fast_score_pair(const uint32_t (&P)[16], uin
 }
 
 // FAST score of the 4 pixels of group word column `g` on tile row r (0..TH-1).  T is the level tile with halo.
-// Result: four score bytes (pixel order), 0 where score < minTh.
+// Result: four bytes (pixel order) of max(0, score + 1 - minTh) - the score plane's encoding.
 __device__ __forceinline__ uint32_t fast_score4(const uint8_t* __restrict__ T, int r, int g, int minTh) {
     // tile pixel column c = 4g sits at byte TCOL0 + c: the word holding c-4..c-1 is word g of the row
     const uint32_t* base = (const uint32_t*)(T + r * TS) + g;           // row r of T = level row y0 + r - HALO
@@ -120,10 +120,10 @@ __device__ __forceinline__ uint32_t fast_score4(const uint8_t* __restrict__ T, i
                              m3.om, m3.em, m2.x1, m1.x3, z0.x3, p1.x3, p2.x1, p3.em};
     const uint32_t tA = fast_score_pair(PA, z0.em);
     const uint32_t tB = fast_score_pair(PB, z0.om);
-    int s0 = (int)(tA & 0xffffu) - 257, s2 = (int)(tA >> 16) - 257;
-    int s1 = (int)(tB & 0xffffu) - 257, s3 = (int)(tB >> 16) - 257;
-    s0 = s0 >= minTh ? s0 : 0; s1 = s1 >= minTh ? s1 : 0; s2 = s2 >= minTh ? s2 : 0; s3 = s3 >= minTh ? s3 : 0;
-    return (uint32_t)s0 | ((uint32_t)s1 << 8) | ((uint32_t)s2 << 16) | ((uint32_t)s3 << 24);
+    // lanes hold score + 257; the plane stores max(0, score + 1 - minTh): 0 <=> not a corner at minTh
+    const uint32_t D = 0x01000100u + (uint32_t)minTh * 0x00010001u;
+    const uint32_t uA = __vmaxu2(tA, D) - D, uB = __vmaxu2(tB, D) - D;
+    return __byte_perm(uA, uB, 0x6240);                  // bytes: pixel c, c+1, c+2, c+3
 }
 
 // 7-tap blur row sums (kernel 18,34,48,56,48,34,18) of the 4 pixels of a group, from one row's pairs:
@@ -164,7 +164,7 @@ __host__ __device__ inline size_t pyr_smem_U(int srcRows) {
 }
 __host__ __device__ inline size_t pyr_smem_bytes(bool level0, int srcRows, int srcCols) {
     if (level0) return pyr_smem_T() + pyr_smem_U(0);
-    return pyr_smem_T() + pyr_smem_taps() + pyr_smem_U(srcRows) + (size_t)srcRows * srcCols;
+    return pyr_smem_T() + pyr_smem_taps() + pyr_smem_U(srcRows) + (size_t)srcRows * srcCols + 16;   // +16: S[o0 + 1] of the last column
 }
 
 template <bool LEVEL0>
@@ -245,28 +245,40 @@ __global__ void __launch_bounds__(PYR_THREADS) pyr_level_kernel(PyrArgs a) {
             tapy[ty] = t;
         }
         __syncthreads();
-        // horizontal pass (HResizeLinear, int32): Hq[r][b] = (S[r][o0]*a0 + S[r][o1]*a1) >> 4, two columns per item
-        for (int i = tid; i < nrows * (TBYTES / 2); i += PYR_THREADS) {
-            const int r = i / (TBYTES / 2), k = i - r * (TBYTES / 2);
-            const uint4 tp = *(const uint4*)(tapx + 2 * k);
-            const uint8_t* Sr = S + r * scols;
-            const int h0 = Sr[tp.x & 0xffffu] * (int)(short)(tp.y & 0xffffu) + Sr[tp.x >> 16] * ((int)tp.y >> 16);
-            const int h1 = Sr[tp.z & 0xffffu] * (int)(short)(tp.w & 0xffffu) + Sr[tp.z >> 16] * ((int)tp.w >> 16);
-            *(uint32_t*)(Hq + r * HQS + 2 * k) = (uint32_t)(h0 >> 4) | ((uint32_t)(h1 >> 4) << 16);
+        // Both passes: thread = (4-column group q, row slot); 34 groups x 7 slots = 238 active threads, so the
+        // column taps of the horizontal pass are decoded once per thread and stay in registers.
+        const int q = tid % (TBYTES / 4), slot = tid / (TBYTES / 4);
+        if (slot < 7) {
+            // horizontal pass (HResizeLinear, int32): Hq[r][b] = (S[r][o0]*a0 + S[r][o0+1]*a1) >> 4.
+            // o1 == o0 + 1 whenever a1 != 0 (the x taps collapse the weight, not the index, at the borders).
+            int o[4], a0[4], a1[4];
+#pragma unroll
+            for (int j = 0; j < 4; j++) {
+                const uint2 tp = *(const uint2*)(tapx + 4 * q + j);
+                o[j] = (int)(tp.x & 0xffffu); a0[j] = (int)(short)(tp.y & 0xffffu); a1[j] = (int)tp.y >> 16;
+            }
+            for (int r = slot; r < nrows; r += 7) {
+                const uint8_t* Sr = S + r * scols;
+                int hh[4];
+#pragma unroll
+                for (int j = 0; j < 4; j++) hh[j] = (Sr[o[j]] * a0[j] + Sr[o[j] + 1] * a1[j]) >> 4;
+                *(uint2*)(Hq + r * HQS + 4 * q) = make_uint2((uint32_t)hh[0] | ((uint32_t)hh[1] << 16), (uint32_t)hh[2] | ((uint32_t)hh[3] << 16));
+            }
         }
         __syncthreads();
-        // vertical pass (VResizeLinear 8u): four columns per item
-        for (int i = tid; i < TROWS * (TBYTES / 4); i += PYR_THREADS) {
-            const int ty = i / (TBYTES / 4), q = i - ty * (TBYTES / 4);
-            const uint2 tp = *(const uint2*)(tapy + ty);
-            const int b0 = (int)(short)(tp.y & 0xffffu), b1 = (int)tp.y >> 16;
-            const uint2 u0 = *(const uint2*)(Hq + (tp.x & 0xffffu) * HQS + 4 * q);
-            const uint2 u1 = *(const uint2*)(Hq + (tp.x >> 16) * HQS + 4 * q);
-            const int v0 = (((b0 * (int)(u0.x & 0xffffu)) >> 16) + ((b1 * (int)(u1.x & 0xffffu)) >> 16) + 2) >> 2;
-            const int v1 = (((b0 * (int)(u0.x >> 16)) >> 16) + ((b1 * (int)(u1.x >> 16)) >> 16) + 2) >> 2;
-            const int v2 = (((b0 * (int)(u0.y & 0xffffu)) >> 16) + ((b1 * (int)(u1.y & 0xffffu)) >> 16) + 2) >> 2;
-            const int v3 = (((b0 * (int)(u0.y >> 16)) >> 16) + ((b1 * (int)(u1.y >> 16)) >> 16) + 2) >> 2;
-            *(uint32_t*)(T + ty * TS + 4 * q) = (uint32_t)v0 | ((uint32_t)v1 << 8) | ((uint32_t)v2 << 16) | ((uint32_t)v3 << 24);
+        if (slot < 7) {
+            // vertical pass (VResizeLinear 8u): ((b0*H0)>>16) + ((b1*H1)>>16) + 2 >> 2; (b*lo16(u))>>16 == umulhi(u<<16, b)
+            for (int ty = slot; ty < TROWS; ty += 7) {
+                const uint2 tp = *(const uint2*)(tapy + ty);
+                const uint32_t b0 = tp.y & 0xffffu, b1 = tp.y >> 16;     // weights are in [0, 2048]
+                const uint2 u0 = *(const uint2*)(Hq + (tp.x & 0xffffu) * HQS + 4 * q);
+                const uint2 u1 = *(const uint2*)(Hq + (tp.x >> 16) * HQS + 4 * q);
+                const uint32_t v0 = (__umulhi(u0.x << 16, b0) + __umulhi(u1.x << 16, b1) + 2u) >> 2;
+                const uint32_t v1 = (__umulhi(u0.x & 0xffff0000u, b0) + __umulhi(u1.x & 0xffff0000u, b1) + 2u) >> 2;
+                const uint32_t v2 = (__umulhi(u0.y << 16, b0) + __umulhi(u1.y << 16, b1) + 2u) >> 2;
+                const uint32_t v3 = (__umulhi(u0.y & 0xffff0000u, b0) + __umulhi(u1.y & 0xffff0000u, b1) + 2u) >> 2;
+                *(uint32_t*)(T + ty * TS + 4 * q) = v0 | (v1 << 8) | (v2 << 16) | (v3 << 24);
+            }
         }
     }
     __syncthreads();
@@ -313,67 +325,67 @@ __global__ void __launch_bounds__(PYR_THREADS) pyr_level_kernel(PyrArgs a) {
     // ---- vertical blur pass: warp `wid` owns tile rows 4*wid..4*wid+3, sliding 7-row window in registers ----
     {
         const unsigned short* col = Hs + 4 * lane;
-        uint32_t qa[7], qb[7];                           // (H(c),H(c+2)) and (H(c+1),H(c+3)) of the 7 window rows
+        uint32_t u[7][4];                                // unpacked row sums of the 7 window rows, pixel order
 #pragma unroll
         for (int j = 0; j < 6; j++) {
             const uint2 v = *(const uint2*)(col + (4 * wid + j) * TW);
-            qa[j] = v.x; qb[j] = v.y;
+            u[j][0] = v.x & 0xffffu; u[j][2] = v.x >> 16; u[j][1] = v.y & 0xffffu; u[j][3] = v.y >> 16;
         }
 #pragma unroll
         for (int k = 0; k < 4; k++) {
             const int r = 4 * wid + k, y = y0 + r;
             const uint2 v = *(const uint2*)(col + (r + 6) * TW);
-            qa[6] = v.x; qb[6] = v.y;
+            u[6][0] = v.x & 0xffffu; u[6][2] = v.x >> 16; u[6][1] = v.y & 0xffffu; u[6][3] = v.y >> 16;
             uint32_t o[4];
 #pragma unroll
-            for (int j = 0; j < 4; j++) {
-                const uint32_t* q = (j & 1) ? qb : qa;
-                const int sh = (j & 2) ? 16 : 0;
-                const uint32_t t0 = (q[0] >> sh) & 0xffffu, t1 = (q[1] >> sh) & 0xffffu, t2 = (q[2] >> sh) & 0xffffu,
-                               t3 = (q[3] >> sh) & 0xffffu, t4 = (q[4] >> sh) & 0xffffu, t5 = (q[5] >> sh) & 0xffffu,
-                               t6 = (q[6] >> sh) & 0xffffu;
-                o[j] = (18u * (t0 + t6) + 34u * (t1 + t5) + 48u * (t2 + t4) + 56u * t3 + 32768u) >> 16;
-            }
+            for (int j = 0; j < 4; j++)
+                o[j] = (18u * (u[0][j] + u[6][j]) + 34u * (u[1][j] + u[5][j]) + 48u * (u[2][j] + u[4][j]) + 56u * u[3][j] + 32768u) >> 16;
             if (y < h && gx < w)
                 *(uint32_t*)(a.blur + (size_t)frame * a.planeFrameStride + (size_t)y * a.pitch + ORB_XPAD + gx) =
                     o[0] | (o[1] << 8) | (o[2] << 16) | (o[3] << 24);
 #pragma unroll
-            for (int j = 0; j < 6; j++) { qa[j] = qa[j + 1]; qb[j] = qb[j + 1]; }
+            for (int i = 0; i < 6; i++)
+#pragma unroll
+                for (int j = 0; j < 4; j++) u[i][j] = u[i + 1][j];
         }
     }
 }
 
 // BORDER_REFLECT_101 frame of 19 pixels around every level (copyMakeBorder,
-// :1364-1365,:1372-1373).  One thread per border pixel.
+// :1364-1365,:1372-1373).  One warp per bordered row: the 19 top and bottom rows are
+// full-width copies of the reflected interior row, all other rows get their 2 x 19 side pixels.
 struct BorderArgs {
     uint8_t* pyr;                 // frame 0 pyramid block
     unsigned long long pyrFrameStride;
     int nlevels;
-    int itemOff[ORB_MAX_LEVELS + 1];   // prefix sum of border pixels per level
+    int rowOff[ORB_MAX_LEVELS + 1];    // prefix sum of bordered rows (h + 38) per level
     unsigned long long pyrOff[ORB_MAX_LEVELS];
     int w[ORB_MAX_LEVELS], h[ORB_MAX_LEVELS], pitch[ORB_MAX_LEVELS];
 };
 
-__global__ void border_kernel(BorderArgs a) {
-    const int item = blockIdx.x * blockDim.x + threadIdx.x;
-    if (item >= a.itemOff[a.nlevels]) return;
+__global__ void __launch_bounds__(256) border_kernel(BorderArgs a) {
+    const int lane = threadIdx.x & 31;
+    const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (row >= a.rowOff[a.nlevels]) return;
     int l = 0;
-    while (item >= a.itemOff[l + 1]) l++;
-    int i = item - a.itemOff[l];
-    const int w = a.w[l], h = a.h[l], bw = w + 2 * ORB_EDGE;
-    int bx, by;   // coordinates in the bordered plane
-    if (i < ORB_EDGE * bw) { by = i / bw; bx = i - by * bw; }
-    else if ((i -= ORB_EDGE * bw) < ORB_EDGE * bw) { by = i / bw; bx = i - by * bw; by += ORB_EDGE + h; }
-    else {
-        i -= ORB_EDGE * bw;
-        by = i / (2 * ORB_EDGE); bx = i - by * (2 * ORB_EDGE);
-        by += ORB_EDGE;
-        if (bx >= ORB_EDGE) bx += w;
-    }
+    while (row >= a.rowOff[l + 1]) l++;
+    const int by = row - a.rowOff[l];                    // row of the bordered plane
+    const int w = a.w[l], h = a.h[l], pitch = a.pitch[l];
     uint8_t* plane = a.pyr + (size_t)blockIdx.y * a.pyrFrameStride + a.pyrOff[l];
-    const int sx = reflect101(bx - ORB_EDGE, w), sy = reflect101(by - ORB_EDGE, h);
-    const int xbase = ORB_XPAD - ORB_EDGE;
-    plane[(size_t)by * a.pitch[l] + xbase + bx] = plane[(size_t)(sy + ORB_EDGE) * a.pitch[l] + ORB_XPAD + sx];
+    const int sy = reflect101(by - ORB_EDGE, h);
+    const uint8_t* srow = plane + (size_t)(sy + ORB_EDGE) * pitch + ORB_XPAD;     // interior row it mirrors
+    uint8_t* drow = plane + (size_t)by * pitch + ORB_XPAD;
+    if (by < ORB_EDGE || by >= ORB_EDGE + h) {
+        // interior part as 32-bit words (both rows start 16-byte aligned), then the two side strips
+        const uint32_t* s4 = (const uint32_t*)srow;
+        uint32_t* d4 = (uint32_t*)drow;
+        for (int i = lane; i < (w + 3) / 4; i += 32) d4[i] = s4[i];      // may run up to 3 bytes into the right strip: rewritten below
+        __syncwarp();
+    }
+    if (lane < ORB_EDGE) {
+        drow[-1 - lane] = srow[1 + lane];                                 // column -1-k mirrors column 1+k
+        drow[w + lane] = srow[w - 2 - lane];                              // column w+k mirrors column w-2-k
+    }
 }
 
 }  // namespace orbx
