@@ -63,6 +63,16 @@ def make_frames(n_distinct, start):
     return np.stack(frames)
 
 
+def measured_traffic(batch):
+    """dram__bytes_read.sum + dram__bytes_write.sum of the dominant kernel's launches (all 8 levels of pyr_level_kernel)
+    from the committed `ncu --set full` capture, scaled from the capture's batch to this run's (profiles/*.json)."""
+    try:
+        t = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
+        return t["pyramid_blur_fast_dram_bytes_per_frame"] * batch
+    except Exception:
+        return None
+
+
 class ClockSampler:
     """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md)."""
     Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
@@ -173,6 +183,106 @@ def run_reference(args, rank, world):
     print(json.dumps(line), flush=True)
 
 
+HAM_NQ = 4096
+HAM_ROWS_PER_GPU = 1_250_000          # BASELINE.json configs[3]: 10M rows over 8 GPUs
+
+
+def make_hamming_case(rank, world):
+    """config 4: uniform random database (seed 0xDB, counter-based so every rank can build its own shard),
+    queries = database rows at stride 2441 with up to 40 flipped bits (identical on every rank)."""
+    from orb_slam_b200.sharded import shard_range
+    from orb_slam_b200.synth import synth_descriptors, splitmix64
+    ndb = HAM_ROWS_PER_GPU * world
+    lo, hi = shard_range(ndb, world, rank)
+    # rows are generated from the global row counter: shard = slice of the global stream (32 B = 4 words per row)
+    idx = np.arange(lo * 4, hi * 4, dtype=np.uint64)
+    with np.errstate(over="ignore"):
+        shard = splitmix64(splitmix64(np.uint64(0xDB)) ^ idx).view(np.uint8).reshape(-1, 32)
+    qrows = (np.arange(HAM_NQ, dtype=np.uint64) * np.uint64(2441)) % np.uint64(ndb)
+    qi = (qrows[:, None] * np.uint64(4) + np.arange(4, dtype=np.uint64)[None, :]).ravel()
+    with np.errstate(over="ignore"):
+        q = splitmix64(splitmix64(np.uint64(0xDB)) ^ qi).view(np.uint8).reshape(-1, 32).copy()
+    rng = np.random.default_rng(7)
+    for i in range(HAM_NQ):
+        for b in rng.integers(0, 256, rng.integers(0, 41)):
+            q[i, b >> 3] ^= 1 << (b & 7)
+    return shard, lo, q, ndb
+
+
+def run_hamming(args, rank, world, local_rank, dist):
+    """Sharded brute-force Hamming 2-NN: per-rank scan + NCCL all-gather + exact merge."""
+    import torch
+    from orb_slam_b200.matcher import TOP2_DTYPE
+    from orb_slam_b200.sharded import ShardedDatabase
+    dev = torch.device("cuda", local_rank)
+    shard, lo, q, ndb = make_hamming_case(rank, world)
+    sd = ShardedDatabase(shard, lo, device=local_rank)
+    d_q = torch.from_numpy(q).to(dev)
+    steps, warm = max(3, args.steps), max(3, args.warmup)
+    for _ in range(warm):
+        sd.query_device(d_q)
+    sd.stream.synchronize(); torch.cuda.synchronize()
+    if dist is not None:
+        dist.barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(sd.stream)
+    for _ in range(steps):
+        out = sd.query_device(d_q)
+    e1.record(sd.stream)
+    sd.stream.synchronize(); torch.cuda.synchronize()
+    ms = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
+    # end to end: host queries in, host top-2 out
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        res = sd.query(q)
+    e2e = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
+    if dist is not None:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX); dist.all_reduce(e2e, op=dist.ReduceOp.MAX)
+    if rank != 0:
+        return None
+    popc_peak = sd.ctx.popc_peak()
+    sec = float(ms.item()) * 1e-3 / steps
+    pairs = HAM_NQ * float(ndb)
+    # analytic check: a query with k <= 40 flips of row r has distance <= k to row r, far below any random row (~128 +- 8)
+    exp_rows = (np.arange(HAM_NQ, dtype=np.int64) * 2441) % ndb
+    ok = bool((res["i1"].astype(np.int64) == exp_rows).all() and (res["d1"] <= 40).all() and (res["d2"] > 60).all())
+    return {"metric": "Hamming 2-NN queries/s", "value": HAM_NQ / sec, "unit": "queries/s", "ms_per_step": sec * 1e3,
+            "config": {"workload": "BASELINE.json configs[3] at %d GPU(s): %d queries vs %d-row database (%d rows per GPU), "
+                                   "NCCL all-gather top-2 merge" % (world, HAM_NQ, ndb, HAM_ROWS_PER_GPU), "scaling": "weak"},
+            "e2e": {"value": HAM_NQ * steps / float(e2e.item()), "unit": "queries/s", "h2d_bytes_per_step": HAM_NQ * 32,
+                    "d2h_bytes_per_step": HAM_NQ * 8},
+            "roofline": {"bound": "int-popc", "achieved": pairs * 8 / sec / 1e12 / world, "peak": popc_peak / 1e12,
+                         "unit": "Tpopc32/s per GPU", "frac": pairs * 8 / sec / world / popc_peak,
+                         "peak_source": "orbm_popc_peak microbenchmark on this GPU",
+                         "hbm_GBps_per_gpu": HAM_ROWS_PER_GPU * 32 * ((HAM_NQ + 1023) // 1024) / sec / 1e9},
+            "nearest_neighbours_verified": ok}
+
+
+def cpu_hamming_baseline(cores):
+    """DescriptorDistance loop (oracle port of src/ORBmatcher.cc:1728-1744 + the top-2 scan) on a bounded sample"""
+    from tests.oracle_lib import OracleMatcher
+    from orb_slam_b200.synth import synth_descriptors
+    db = synth_descriptors(HAM_ROWS_PER_GPU, 0xDB)
+    per = 16
+    q = db[: cores * per].copy()
+    o = OracleMatcher()
+    o.bf2nn(q[:1], db[:1000])
+    barrier = threading.Barrier(cores + 1)
+
+    def work(t):
+        barrier.wait()
+        o.bf2nn(q[t * per:(t + 1) * per], db)
+        barrier.wait()
+    th = [threading.Thread(target=work, args=(t,)) for t in range(cores)]
+    for t in th:
+        t.start()
+    barrier.wait(); t0 = time.perf_counter(); barrier.wait(); dt = time.perf_counter() - t0
+    for t in th:
+        t.join()
+    return {"value": cores * per / dt, "unit": "queries/s", "cores": cores, "kind": "port",
+            "sample": f"{cores} threads x {per} queries vs {HAM_ROWS_PER_GPU} rows ({dt:.1f} s wall)"}
+
+
 def run_ours(args, rank, world, local_rank):
     import torch
     from orb_slam_b200 import KEYPOINT_DTYPE, ORBextractor
@@ -268,6 +378,30 @@ def run_ours(args, rank, world, local_rank):
         dist.all_reduce(e2e_s, op=dist.ReduceOp.MAX)
     e2e_s = float(e2e_s.item())
 
+    # ---- what Tracking sees: one orbx_extract call per frame (pageable numpy image in, keypoints out), latency
+    one = np.ascontiguousarray(host[0].numpy())
+    k1 = np.empty((cap, 28), np.uint8); d1 = np.empty((cap, 32), np.uint8); n1 = C.c_int()
+    lat = []
+    for i in range(60):
+        t0 = time.perf_counter()
+        check(L.orbx_extract(h, one.ctypes.data, W_, H_, W_, k1.ctypes.data, d1.ctypes.data, cap, C.byref(n1)), "orbx_extract")
+        lat.append(time.perf_counter() - t0)
+    lat_ms = float(np.median(lat[10:]) * 1e3)
+    # ---- the same batch call with pageable (numpy) buffers: staging through pinned memory inside the library
+    pg_in = np.ascontiguousarray(host.numpy()[: min(B, 256)])
+    nb = len(pg_in)
+    pg_k = np.empty((nb, cap, 28), np.uint8); pg_d = np.empty((nb, cap, 32), np.uint8); pg_n = np.zeros(nb, np.int32)
+    pg_ptrs = (C.c_void_p * nb)(*[pg_in.ctypes.data + i * W_ * H_ for i in range(nb)])
+    for rep in range(3):
+        t0 = time.perf_counter()
+        check(L.orbx_extract_batch(h, pg_ptrs, nb, W_, H_, W_, pg_k.ctypes.data, pg_d.ctypes.data, cap, pg_n.ctypes.data),
+              "orbx_extract_batch")
+        pageable_fps = nb / (time.perf_counter() - t0)
+
+    ham = None
+    if not args.no_hamming:
+        ham = run_hamming(args, rank, world, local_rank, dist)
+
     if rank == 0:
         frames_total = world * B * args.steps
         value = frames_total / (total_ms * 1e-3)
@@ -302,7 +436,12 @@ def run_ours(args, rank, world, local_rank):
                          "pipeline_achieved": pipe_achieved, "pipeline_frac": pipe_achieved / peak,
                          "algorithmic_bytes_per_frame": balg},
             "stages_ms_per_step": {k: float(v) for k, v in zip(STAGES, stage_ms)},
+            "single_frame_latency_ms": lat_ms,
+            "e2e_pageable_frames_per_s": pageable_fps,
         }
+        line["roofline"]["traffic"] = measured_traffic(B)
+        if ham is not None:
+            line["hamming_2nn"] = ham
         if world == 1 and not args.no_cpu:
             from tests import oracle_lib
             kind = "reference" if oracle_lib.have_ref() else "port"
@@ -313,6 +452,8 @@ def run_ours(args, rank, world, local_rank):
             line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": cores, "kind": kind,
                                     "sample": f"{cores} threads x {per_thread} frames of the same workload ({dt:.1f} s wall)",
                                     "single_thread_frames_per_s": v1}
+            if ham is not None:
+                line["hamming_2nn"]["cpu_baseline"] = cpu_hamming_baseline(cores)
         print(json.dumps(line), flush=True)
     ex.close()
     if dist is not None:
@@ -328,6 +469,7 @@ def main():
     ap.add_argument("--batch", type=int, default=512, help="frames per step per GPU")
     ap.add_argument("--cpu-frames", type=int, default=384, help="frames in the bounded CPU sample")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-hamming", action="store_true")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
