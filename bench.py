@@ -255,6 +255,7 @@ def run_hamming(args, rank, world, local_rank, dist):
                          "unit": "Tpopc32/s per GPU", "frac": pairs * 8 / sec / world / popc_peak,
                          "peak_source": "orbm_popc_peak microbenchmark on this GPU",
                          "hbm_GBps_per_gpu": HAM_ROWS_PER_GPU * 32 * ((HAM_NQ + 1023) // 1024) / sec / 1e9},
+            "pairs_per_s_all_gpus": pairs / sec,
             "nearest_neighbours_verified": ok}
 
 
@@ -290,6 +291,8 @@ def run_ours(args, rank, world, local_rank):
 
     dist = None
     if world > 1:
+        if os.environ.get("NCCL_DEBUG", "VERSION").upper() == "VERSION":
+            os.environ["NCCL_DEBUG"] = "WARN"          # keep stdout to the one JSON line
         import torch.distributed as dist_
         dist = dist_
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
