@@ -53,15 +53,15 @@ constexpr int DP_WORDS = 11;                   // 39 bytes at any alignment fit 
 constexpr int IP_ROWS = 2 * ORB_HALF_PATCH + 1;   // intensity-centroid patch: 31 rows
 constexpr int IP_WORDS = 9;                    // 31 bytes at any alignment fit in 9 aligned words
 
-__device__ uint32_t g_pattern32[256];          // bit_pattern_31_ as [pair k][descriptor byte] words (x0,y0,x1,y1 signed bytes)
+__device__ float4 g_pattern4[256];             // bit_pattern_31_ as [pair k][descriptor byte] -> (x0, y0, x1, y1) of test 8*byte + k
 
 __global__ void __launch_bounds__(256) describe_kernel(DescArgs a) {
     // Both patches of a keypoint are staged in shared memory with aligned, coalesced 32-bit loads (all in flight at
     // once); the 961 moment reads and 512 rotated-BRIEF gathers then hit shared memory instead of L1/L2.
-    __shared__ uint32_t s_pat[256];
+    __shared__ float4 s_pat[256];
     __shared__ uint32_t s_blur[8][DP_ROWS * DP_WORDS];
     __shared__ uint32_t s_img[8][IP_ROWS * IP_WORDS];
-    s_pat[threadIdx.x] = g_pattern32[threadIdx.x];       // blockDim.x == 256
+    s_pat[threadIdx.x] = g_pattern4[threadIdx.x];        // blockDim.x == 256
     __syncthreads();
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     const int slot = blockIdx.x * (blockDim.x >> 5) + wid;
@@ -88,15 +88,23 @@ __global__ void __launch_bounds__(256) describe_kernel(DescArgs a) {
     const int bx0 = (x - ORB_EDGE) & ~3, ix0 = (x - ORB_HALF_PATCH) & ~3;     // both >= 0: keypoints sit >= 19 px inside
     {
         const uint8_t* bl = a.blur + (size_t)frame * a.planeFrameStride + a.planeOff[l] + (size_t)(y - ORB_EDGE) * pitch + ORB_XPAD + bx0;
-        for (int t = lane; t < DP_ROWS * DP_WORDS; t += 32) {
-            const int r = t / DP_WORDS, wv = t - r * DP_WORDS;
-            s_blur[wid][t] = __ldg((const uint32_t*)(bl + (size_t)r * pitch) + wv);
-        }
         const uint8_t* im = a.pyr + (size_t)frame * a.pyrFrameStride + a.pyrOff[l] + (size_t)(ORB_EDGE + y - ORB_HALF_PATCH) * pitch + ORB_XPAD + ix0;
-        for (int t = lane; t < IP_ROWS * IP_WORDS; t += 32) {
-            const int r = t / IP_WORDS, wv = t - r * IP_WORDS;
-            s_img[wid][t] = __ldg((const uint32_t*)(im + (size_t)r * pitch) + wv);
+        constexpr int NB = (DP_ROWS * DP_WORDS + 31) / 32, NI = (IP_ROWS * IP_WORDS + 31) / 32;
+        uint32_t vb[NB], vi[NI];
+#pragma unroll
+        for (int j = 0; j < NB; j++) {                   // all loads first: NB + NI independent requests in flight per lane
+            const int t = lane + 32 * j, r = t / DP_WORDS, wv = t - r * DP_WORDS;
+            vb[j] = t < DP_ROWS * DP_WORDS ? __ldg((const uint32_t*)(bl + (size_t)r * pitch) + wv) : 0u;
         }
+#pragma unroll
+        for (int j = 0; j < NI; j++) {
+            const int t = lane + 32 * j, r = t / IP_WORDS, wv = t - r * IP_WORDS;
+            vi[j] = t < IP_ROWS * IP_WORDS ? __ldg((const uint32_t*)(im + (size_t)r * pitch) + wv) : 0u;
+        }
+#pragma unroll
+        for (int j = 0; j < NB; j++) { const int t = lane + 32 * j; if (t < DP_ROWS * DP_WORDS) s_blur[wid][t] = vb[j]; }
+#pragma unroll
+        for (int j = 0; j < NI; j++) { const int t = lane + 32 * j; if (t < IP_ROWS * IP_WORDS) s_img[wid][t] = vi[j]; }
     }
     __syncwarp();
 
@@ -138,10 +146,9 @@ __global__ void __launch_bounds__(256) describe_kernel(DescArgs a) {
     int val = 0;
 #pragma unroll
     for (int k = 0; k < 8; k++) {
-        // test pair k of byte `lane`: one conflict-free 32-bit shared load (x0,y0,x1,y1 as signed bytes)
-        const int pw = (int)s_pat[k * 32 + lane];
-        const float x0 = (float)(signed char)(pw), y0 = (float)(signed char)(pw >> 8);
-        const float x1 = (float)(signed char)(pw >> 16), y1 = (float)(signed char)(pw >> 24);
+        // test pair k of byte `lane`: one 128-bit shared load (x0, y0, x1, y1)
+        const float4 pw = s_pat[k * 32 + lane];
+        const float x0 = pw.x, y0 = pw.y, x1 = pw.z, y1 = pw.w;
         const int r0 = __float2int_rn(__fadd_rn(__fmul_rn(x0, sb), __fmul_rn(y0, ca)));      // cvRound(x*b + y*a)
         const int q0 = __float2int_rn(__fsub_rn(__fmul_rn(x0, ca), __fmul_rn(y0, sb)));      // cvRound(x*a - y*b)
         const int r1 = __float2int_rn(__fadd_rn(__fmul_rn(x1, sb), __fmul_rn(y1, ca)));

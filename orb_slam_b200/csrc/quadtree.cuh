@@ -21,7 +21,7 @@
 
 namespace orbx {
 
-constexpr int QT_THREADS = 512;
+constexpr int QT_THREADS = 256;
 constexpr int QT_WARPS = QT_THREADS / 32;
 
 struct QtArgs {
