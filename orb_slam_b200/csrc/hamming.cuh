@@ -5,8 +5,9 @@
 // Layout: every thread keeps 4 query descriptors (32 registers) and their
 // top-2 state; the database streams through shared memory in 128-row tiles
 // (cp.async, double buffered) and every warp reads a row as two broadcast
-// 128-bit loads.  The inner loop is 8 LOP3.XOR + 8 POPC + adds per pair: the
-// bound is the integer POPC pipe, not HBM (a shard is read once per query tile).
+// 128-bit loads.  The inner loop is 8 LOP3.XOR + 6 LOP3 (carry-save adders) + 5 POPC
+// + adds per pair: the bound is the integer POPC / ALU pipes, not HBM (a shard is read
+// once per query tile).
 // top-2 is kept as packed keys (distance << 23 | local row) so the update is
 // min/max only, and equal distances resolve to the lowest row = the
 // reference's strict '<' scan in ascending index.
@@ -54,8 +55,9 @@ __global__ void __launch_bounds__(BF_THREADS) bf2nn_kernel(const uint32_t* __res
         }
     }
     uint32_t b1[BF_QPT], b2[BF_QPT];
+    uint32_t thr[BF_QPT];                              // distance of the current second best (512 = none yet)
 #pragma unroll
-    for (int j = 0; j < BF_QPT; j++) { b1[j] = 0xffffffffu; b2[j] = 0xffffffffu; }
+    for (int j = 0; j < BF_QPT; j++) { b1[j] = 0xffffffffu; b2[j] = 0xffffffffu; thr[j] = 0x1ffu; }
 
     const unsigned long long r0 = (unsigned long long)slice * rowsPerSlice;
     const unsigned long long r1 = min(ndb, r0 + rowsPerSlice);
@@ -81,14 +83,32 @@ __global__ void __launch_bounds__(BF_THREADS) bf2nn_kernel(const uint32_t* __res
 #pragma unroll 2
         for (unsigned r = 0; r < cnt; r++) {
             const uint4 w0 = *(const uint4*)&tile[buf][r * 8], w1 = *(const uint4*)&tile[buf][r * 8 + 4];
+            uint32_t d[BF_QPT];
+            bool any = false;
 #pragma unroll
             for (int j = 0; j < BF_QPT; j++) {
-                const uint32_t d = __popc(qr[j][0] ^ w0.x) + __popc(qr[j][1] ^ w0.y) + __popc(qr[j][2] ^ w0.z) +
-                                   __popc(qr[j][3] ^ w0.w) + __popc(qr[j][4] ^ w1.x) + __popc(qr[j][5] ^ w1.y) +
-                                   __popc(qr[j][6] ^ w1.z) + __popc(qr[j][7] ^ w1.w);
-                const uint32_t key = (d << 23) | (rowBase + r);
-                b2[j] = min(b2[j], max(key, b1[j]));
-                b1[j] = min(b1[j], key);
+                // 256-bit Hamming distance with 4 POPC instead of 8: carry-save adders (LOP3 xor3 / majority) compress
+                // the eight XOR words to two weight-1, one weight-2 and one weight-4 word first.  POPC costs four ALU
+                // issue slots, a LOP3 one.
+                const uint32_t x0 = qr[j][0] ^ w0.x, x1 = qr[j][1] ^ w0.y, x2 = qr[j][2] ^ w0.z, x3 = qr[j][3] ^ w0.w;
+                const uint32_t x4 = qr[j][4] ^ w1.x, x5 = qr[j][5] ^ w1.y, x6 = qr[j][6] ^ w1.z, x7 = qr[j][7] ^ w1.w;
+                const uint32_t s1 = x0 ^ x1 ^ x2, c1 = (x0 & x1) | (x2 & (x0 | x1));
+                const uint32_t s2 = x3 ^ x4 ^ x5, c2 = (x3 & x4) | (x5 & (x3 | x4));
+                const uint32_t s3 = x6 ^ x7 ^ s1, c3 = (x6 & x7) | (s1 & (x6 | x7));
+                const uint32_t t2 = c1 ^ c2 ^ c3, f4 = (c1 & c2) | (c3 & (c1 | c2));
+                d[j] = __popc(s2) + __popc(s3) + 2u * __popc(t2) + 4u * __popc(f4);
+                any |= d[j] < thr[j];
+            }
+            // rows arrive in ascending index, so a row enters the top-2 only with a strictly smaller distance than the
+            // current second best: after the first few hundred rows almost no warp takes this branch
+            if (__any_sync(0xffffffffu, any)) {
+#pragma unroll
+                for (int j = 0; j < BF_QPT; j++) {
+                    const uint32_t key = (d[j] << 23) | (rowBase + r);
+                    b2[j] = min(b2[j], max(key, b1[j]));
+                    b1[j] = min(b1[j], key);
+                    thr[j] = b2[j] >> 23;
+                }
             }
         }
         __syncthreads();
