@@ -117,6 +117,16 @@ int orbx_get_level(orbx_t* ex, int frame, int level, int border, int blurred, ui
  * int triples, coordinates relative to (minBorderX, minBorderY) = (16, 16). */
 int orbx_get_candidates(orbx_t* ex, int frame, int level, int32_t* xyr, int capacity, int* n_out);
 
+/* Frame::ComputeStereoMatches (src/Frame.cc:630-872): stereo correspondences of the left keypoints against the right
+ * keypoints of a rectified pair, on the pyramids still resident in the two extractor instances after their last
+ * orbx_extract* call (`frame` = index inside that call's last chunk, 0 for single-frame calls).  Row-band candidate
+ * search, Hamming coarse match (thOrbDist 75), 11x11 SAD refinement +-5 px on the left keypoint's level, parabola
+ * sub-pixel fit, disparity gate [0, mbf/mb), median-based outlier cut.  Outputs mvuRight / mvDepth (-1 = no match),
+ * nL floats each, and the number of surviving matches.  Host pointers in and out. */
+int orbx_stereo_match(orbx_t* left, orbx_t* right, int frame, const orbx_keypoint* keysL, const uint8_t* descL, int nL,
+                      const orbx_keypoint* keysR, const uint8_t* descR, int nR, float mbf, float mb, float* uRight,
+                      float* depth, int* n_matched);
+
 /* Number of kernel launches one orbx_extract_batch* call enqueues (for bench.py's gpu_launches). */
 int orbx_launches_per_call(const orbx_t* ex);
 

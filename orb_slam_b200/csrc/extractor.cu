@@ -17,6 +17,7 @@
 #include "geom.h"
 #include "pyramid.cuh"
 #include "quadtree_kernel.cuh"
+#include "stereo.cuh"
 
 using namespace orbx;
 
@@ -56,6 +57,7 @@ struct orbx_extractor {
     // host-buffer path: chunks of the batch flow through copy-in / compute / copy-out streams
     cudaStream_t sIn = nullptr, sOut = nullptr;
     cudaEvent_t evIn[2] = {}, evCompute[2] = {}, evOut[2] = {};
+    uint8_t* d_stereo = nullptr; size_t stereoBytes = 0;     // scratch of orbx_stereo_match
     int launches = 0;
     bool profile = false;                    // record one CUDA event per stage boundary
     cudaEvent_t ev[8] = {};
@@ -447,7 +449,7 @@ void orbx_destroy(orbx_t* e) {
     cudaSetDevice(e->device);
     cudaStreamSynchronize(e->stream);
     free_workspace(e);
-    cudaFree(e->d_err);
+    cudaFree(e->d_err); cudaFree(e->d_stereo);
     for (int i = 0; i < 8; i++) if (e->ev[i]) cudaEventDestroy(e->ev[i]);
     for (int b = 0; b < 2; b++) {
         cudaFree(e->d_in[b]);
@@ -694,6 +696,64 @@ int orbx_get_candidates(orbx_t* e, int frame, int level, int32_t* xyr, int capac
     for (int i = 0; i < n && i < capacity; i++) {
         xyr[3 * i] = (int)(tmp[i] & 0xfff); xyr[3 * i + 1] = (int)((tmp[i] >> 12) & 0xfff); xyr[3 * i + 2] = (int)(tmp[i] >> 24);
     }
+    return ORBX_OK;
+}
+
+// Frame::ComputeStereoMatches, src/Frame.cc:630-872
+int orbx_stereo_match(orbx_t* left, orbx_t* right, int frame, const orbx_keypoint* keysL, const uint8_t* descL, int nL,
+                      const orbx_keypoint* keysR, const uint8_t* descR, int nR, float mbf, float mb, float* uRight,
+                      float* depth, int* n_matched) {
+    if (!left || !right || nL < 0 || nR < 0 || (nL && (!keysL || !descL || !uRight || !depth)) || (nR && (!keysR || !descR)))
+        return ORBX_E_INVALID;
+    if (nR >= 65536 || !(mb > 0)) return ORBX_E_INVALID;
+    if (n_matched) *n_matched = 0;
+    if (nL == 0) return ORBX_OK;
+    std::lock_guard<std::mutex> lk(left->mtx);
+    if (!left->haveGeom || !right->haveGeom || left->device != right->device || left->g.width != right->g.width ||
+        left->g.height != right->g.height || left->nlevels != right->nlevels || frame < 0 || frame >= left->lastFrames ||
+        frame >= right->lastFrames)
+        return ORBX_E_INVALID;
+    CK(cudaSetDevice(left->device));
+    CK(cudaStreamSynchronize(right->stream));                 // the right pyramid is complete
+    const size_t kb = sizeof(orbx_keypoint);
+    const size_t oKL = 0, oDL = oKL + (((size_t)nL * kb + 255) & ~(size_t)255), oKR = oDL + (size_t)nL * 32 + 256;
+    const size_t oDR = oKR + (((size_t)nR * kb + 255) & ~(size_t)255), oU = oDR + (size_t)std::max(nR, 1) * 32 + 256;
+    const size_t oZ = oU + (size_t)nL * 4 + 256, oS = oZ + (size_t)nL * 4 + 256, oN = oS + (size_t)nL * 4 + 256, need = oN + 256;
+    orbx_extractor* e = left;
+    if (e->stereoBytes < need) {
+        CK(cudaStreamSynchronize(e->stream));
+        cudaFree(e->d_stereo); e->d_stereo = nullptr; e->stereoBytes = 0;
+        CK(cudaMalloc(&e->d_stereo, need));
+        e->stereoBytes = need;
+    }
+    uint8_t* d = e->d_stereo;
+    cudaStream_t st = e->stream;
+    CK(cudaMemcpyAsync(d + oKL, keysL, (size_t)nL * kb, cudaMemcpyHostToDevice, st));
+    CK(cudaMemcpyAsync(d + oDL, descL, (size_t)nL * 32, cudaMemcpyHostToDevice, st));
+    if (nR) {
+        CK(cudaMemcpyAsync(d + oKR, keysR, (size_t)nR * kb, cudaMemcpyHostToDevice, st));
+        CK(cudaMemcpyAsync(d + oDR, descR, (size_t)nR * 32, cudaMemcpyHostToDevice, st));
+    }
+    StereoArgs a{};
+    a.keysL = (const orbx_keypoint*)(d + oKL); a.descL = (const uint32_t*)(d + oDL); a.nL = nL;
+    a.keysR = (const orbx_keypoint*)(d + oKR); a.descR = (const uint32_t*)(d + oDR); a.nR = nR;
+    a.pyrL = left->d_pyr + (size_t)frame * left->g.pyrBytes; a.pyrR = right->d_pyr + (size_t)frame * right->g.pyrBytes;
+    a.nlevels = e->nlevels;
+    for (int l = 0; l < e->nlevels; l++) {
+        a.pyrOff[l] = e->g.lv[l].pyrOff; a.pitch[l] = e->g.lv[l].pitch; a.cols[l] = e->g.lv[l].w;
+        a.sf[l] = e->sf[l]; a.isf[l] = e->isf[l];
+    }
+    a.mbf = mbf; a.maxD = mbf / mb;                           // minZ = mb, maxD = mbf / minZ, :678-682
+    a.uRight = (float*)(d + oU); a.depth = (float*)(d + oZ); a.sad = (int*)(d + oS);
+    stereo_match_kernel<<<(nL + 7) / 8, 256, 0, st>>>(a);
+    stereo_outlier_kernel<<<1, 1024, 0, st>>>(nL, a.sad, a.uRight, a.depth, (int*)(d + oN));
+    CK(cudaGetLastError());
+    CK(cudaMemcpyAsync(uRight, a.uRight, (size_t)nL * 4, cudaMemcpyDeviceToHost, st));
+    CK(cudaMemcpyAsync(depth, a.depth, (size_t)nL * 4, cudaMemcpyDeviceToHost, st));
+    int nm = 0;
+    CK(cudaMemcpyAsync(&nm, d + oN, 4, cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    if (n_matched) *n_matched = nm;
     return ORBX_OK;
 }
 

@@ -48,6 +48,8 @@ public:
                       std::vector<cv::Mat>& descriptors);
     // CUDA device ordinal used by instances constructed afterwards on this thread (default: $ORB_B200_DEVICE or 0).
     static void SetDevice(int device);
+    // The device-side instance (include/orbx.h), for the drop-in Frame::ComputeStereoMatches which reads the resident pyramids.
+    orbx_extractor* DeviceHandle() const { return mpDev; }
 
 protected:
     int nfeatures;

@@ -8,6 +8,7 @@
 #include <vector>
 #include <opencv2/core/core.hpp>
 #include "MapPoint.h"
+#include "ORBextractor.h"
 
 namespace ORB_SLAM2 {
 #define FRAME_GRID_ROWS 48
@@ -15,7 +16,7 @@ namespace ORB_SLAM2 {
 
 class Frame {
 public:
-    Frame() : mbf(0), mb(0), N(0) {}
+    Frame() : mpORBextractorLeft(NULL), mpORBextractorRight(NULL), mbf(0), mb(0), N(0) {}
     // test helper (not in the reference): fills the keypoint-side members the way the Frame constructors do
     // (src/Frame.cc:212-284) for an undistorted camera and assigns the grid.
     Frame(const std::vector<cv::KeyPoint>& keys, const cv::Mat& descriptors, int width, int height,
@@ -26,6 +27,10 @@ public:
     std::vector<size_t> GetFeaturesInArea(const float& x, const float& y, const float& r, const int minLevel = -1,
                                           const int maxLevel = -1) const;
     void AssignFeaturesToGrid();
+    // src/Frame.cc:630-872
+    void ComputeStereoMatches();
+
+    ORBextractor *mpORBextractorLeft, *mpORBextractorRight;
 
     static float fx, fy, cx, cy, invfx, invfy;
     float mbf;
@@ -43,6 +48,7 @@ public:
     std::vector<std::size_t> mGrid[FRAME_GRID_COLS][FRAME_GRID_ROWS];
     cv::Mat mTcw;
     std::vector<float> mvScaleFactors;
+    std::vector<float> mvInvScaleFactors;
     static float mnMinX, mnMaxX, mnMinY, mnMaxY;
     static bool mbInitialComputations;
 };

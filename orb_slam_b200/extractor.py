@@ -107,6 +107,17 @@ class ORBextractor:
               "orbx_get_candidates")
         return out[: n.value]
 
+    def stereo_match(self, right: "ORBextractor", keysL, descL, keysR, descR, mbf: float, mb: float, frame: int = 0):
+        """Frame::ComputeStereoMatches (src/Frame.cc:630-872) with self = mpORBextractorLeft, right = mpORBextractorRight,
+        on the pyramids of their last extraction.  Returns (mvuRight, mvDepth, number of matches)."""
+        kL = np.ascontiguousarray(keysL, KEYPOINT_DTYPE); kR = np.ascontiguousarray(keysR, KEYPOINT_DTYPE)
+        dL = np.ascontiguousarray(descL, np.uint8); dR = np.ascontiguousarray(descR, np.uint8)
+        u = np.empty(len(kL), np.float32); z = np.empty(len(kL), np.float32); n = C.c_int()
+        check(self._L.orbx_stereo_match(self._h, right._h, frame, kL.ctypes.data, dL.ctypes.data, len(kL), kR.ctypes.data,
+                                        dR.ctypes.data, len(kR), mbf, mb, u.ctypes.data, z.ctypes.data, C.byref(n)),
+              "orbx_stereo_match")
+        return u, z, n.value
+
     @property
     def handle(self):
         return self._h

@@ -102,6 +102,26 @@ int dropin_batch(const uint8_t* imgs, int n, int w, int h, int nfeatures, cv::Ke
     return 0;
 }
 
+// the stereo Frame constructor (src/Frame.cc:74-143): ExtractORB on two threads, then ComputeStereoMatches
+int dropin_stereo_frame(const uint8_t* left, const uint8_t* right, int w, int h, int nfeatures, float mbf, float mb,
+                        cv::KeyPoint* kl, int* nl, float* uRight, float* depth, int cap, int downloadPyramid) {
+    ORBextractor exL(nfeatures, 1.2f, 8, 20, 7), exR(nfeatures, 1.2f, 8, 20, 7);
+    exL.SetPyramidDownload(downloadPyramid != 0); exR.SetPyramidDownload(downloadPyramid != 0);
+    Frame F;
+    F.mpORBextractorLeft = &exL; F.mpORBextractorRight = &exR;
+    cv::Mat imL(h, w, CV_8UC1, (void*)left, (size_t)w), imR(h, w, CV_8UC1, (void*)right, (size_t)w);
+    std::thread tl([&] { exL(imL, cv::Mat(), F.mvKeys, F.mDescriptors); });
+    std::thread tr([&] { exR(imR, cv::Mat(), F.mvKeysRight, F.mDescriptorsRight); });
+    tl.join(); tr.join();
+    F.N = (int)F.mvKeys.size();
+    F.mvScaleFactors = exL.GetScaleFactors(); F.mvInvScaleFactors = exL.GetInverseScaleFactors();
+    F.mbf = mbf; F.mb = mb;
+    F.ComputeStereoMatches();
+    *nl = F.N;
+    for (int i = 0; i < F.N && i < cap; i++) { kl[i] = F.mvKeys[i]; uRight[i] = F.mvuRight[i]; depth[i] = F.mvDepth[i]; }
+    return 0;
+}
+
 int dropin_grid(const orbm_frame* f, int32_t* cellStart, int32_t* items) {
     std::unique_ptr<Frame> F = frame_from(f);
     F->AssignFeaturesToGrid();

@@ -136,6 +136,30 @@ class RefExtractor:
         return out
 
 
+def oracle_stereo_matches(exL, exR, kL, dL, kR, dR, mbf, mb):
+    """Frame::ComputeStereoMatches restated (oracle/orb_oracle_stereo.cc) on the pyramids of two OracleExtractor
+    instances that have just extracted the left / right image."""
+    L = oracle()
+    n = exL.nlevels
+    levL = [exL.get_level(l, border=19) for l in range(n)]
+    levR = [exR.get_level(l, border=19) for l in range(n)]
+    ptr = lambda a: a.ctypes.data + 19 * a.strides[0] + 19
+    pL = (C.c_void_p * n)(*[ptr(a) for a in levL]); pR = (C.c_void_p * n)(*[ptr(a) for a in levR])
+    sL = (C.c_size_t * n)(*[a.strides[0] for a in levL]); sR = (C.c_size_t * n)(*[a.strides[0] for a in levR])
+    cols = (C.c_int * n)(*[a.shape[1] - 38 for a in levL])
+    sf, isf = exL.tables()[0], exL.tables()[1]
+    kL = np.ascontiguousarray(kL, KP); kR = np.ascontiguousarray(kR, KP)
+    dL = np.ascontiguousarray(dL, np.uint8); dR = np.ascontiguousarray(dR, np.uint8)
+    u = np.zeros(len(kL), np.float32); z = np.zeros(len(kL), np.float32)
+    L.orbo_compute_stereo_matches.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p,
+                                              C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                              C.c_int, C.c_float, C.c_float, C.c_void_p, C.c_void_p]
+    kept = L.orbo_compute_stereo_matches(kL.ctypes.data, len(kL), dL.ctypes.data, kR.ctypes.data, len(kR), dR.ctypes.data,
+                                         sf.ctypes.data, isf.ctypes.data, n, pL, pR, sL, sR, cols, levL[0].shape[0] - 38,
+                                         mbf, mb, u.ctypes.data, z.ctypes.data)
+    return u, z, kept
+
+
 # ---------------- matcher / grid oracle (oracle/orb_oracle_matcher.cc) ----------------
 def _bind_matcher(L):
     if getattr(L, "_m_bound", False):
