@@ -286,6 +286,71 @@ def cpu_hamming_baseline(cores):
             "sample": f"{cores} threads x {per} queries vs {HAM_ROWS_PER_GPU} rows ({dt:.1f} s wall)"}
 
 
+def run_stereo_frontend(local_rank, with_cpu):
+    """BASELINE.json configs[1] as Tracking runs it, one stereo pair at a time (latency, not throughput): ExtractORB on
+    two extractor instances from two host threads (src/Frame.cc:94-103), Frame::ComputeStereoMatches, then
+    ORBmatcher::SearchByProjection(CurrentFrame, LastFrame, th=7) with 2000 synthetic map points.  Median ms per pair."""
+    from orb_slam_b200 import ORBextractor
+    from orb_slam_b200.matcher import MatcherContext, ORBmatcher
+    from orb_slam_b200.synth import synth_frame
+    from tests import scenes
+    exL, exR = ORBextractor(NFEAT, 1.2, 8, 20, 7, device=local_rank), ORBextractor(NFEAT, 1.2, 8, 20, 7, device=local_rank)
+    ctx = MatcherContext(local_rank)
+    mbf = float(scenes.KITTI_BF); mb = float(np.float32(scenes.KITTI_BF) / scenes.KITTI_K[0, 0])
+    # one scene drifting 2 px per frame (so consecutive frames do match), right image = left shifted by the disparity
+    pairs = [(synth_frame(W_, H_, 500, shift=(-2 * i, 0)), synth_frame(W_, H_, 500, shift=(-2 * i - 15, 0))) for i in range(6)]
+    out = {}
+
+    def extract_pair(l, r, a, b):
+        res = [None, None]
+        t = threading.Thread(target=lambda: res.__setitem__(1, b(r)))
+        t.start(); res[0] = a(l); t.join()
+        return res
+
+    def one(l, r, a, b, stereo, proj, last):
+        t0 = time.perf_counter()
+        (kl, dl), (kr, dr) = extract_pair(l, r, a, b)
+        t1 = time.perf_counter()
+        u, z, n = stereo(kl, dl, kr, dr)
+        t2 = time.perf_counter()
+        cur = scenes.make_frame(kl, dl, W_, H_, stereo=False, Tcw=np.eye(4, dtype=np.float32))
+        cur.mvuRight = u
+        nm = 0
+        t3 = time.perf_counter()
+        if last is not None:
+            nm = proj(cur, *last)
+        t4 = time.perf_counter()
+        return (t1 - t0, t2 - t1, t4 - t3), (cur, kl, dl), n, nm
+
+    def gpu_stereo(kl, dl, kr, dr):
+        return exL.stereo_match(exR, kl, dl, kr, dr, mbf, mb)
+
+    def gpu_proj(cur, lastF, pts, obs):
+        return ORBmatcher(0.9, True, ctx).SearchByProjectionFrame(cur, lastF, pts, obs, 7.0, False)[0]
+
+    def loop(a, b, stereo, proj, reps):
+        ts, last = [], None
+        for i in range(reps):
+            l, r = pairs[i % len(pairs)]
+            t, (cur, kl, dl), n, nm = one(l, r, a, b, stereo, proj, last)
+            pts = scenes.last_frame_points(cur, seed=i)
+            last = (cur, pts, np.full(cur.N, -1, np.int32))
+            ts.append(t)
+        ts = np.array(ts[2:]) * 1e3
+        return {"extract_pair_ms": float(np.median(ts[:, 0])), "stereo_match_ms": float(np.median(ts[:, 1])),
+                "search_by_projection_ms": float(np.median(ts[:, 2])), "stereo_matches": int(n), "projection_matches": int(nm)}
+
+    out["b200"] = loop(exL, exR, gpu_stereo, gpu_proj, 24)
+    if with_cpu:
+        from tests import oracle_lib
+        oa, ob = oracle_lib.OracleExtractor(NFEAT, 1.2, 8, 20, 7), oracle_lib.OracleExtractor(NFEAT, 1.2, 8, 20, 7)
+        om = oracle_lib.OracleMatcher(0.9, True)
+        out["cpu_port"] = loop(oa, ob, lambda kl, dl, kr, dr: oracle_lib.oracle_stereo_matches(oa, ob, kl, dl, kr, dr, mbf, mb),
+                               lambda cur, lastF, pts, obs: om.SearchByProjectionFrame(cur, lastF, pts, obs, 7.0, False)[0], 8)
+    exL.close(); exR.close(); ctx.close()
+    return out
+
+
 def run_ours(args, rank, world, local_rank):
     import torch
     from orb_slam_b200 import KEYPOINT_DTYPE, ORBextractor
@@ -447,6 +512,8 @@ def run_ours(args, rank, world, local_rank):
         line["roofline"]["traffic"] = measured_traffic(B)
         if ham is not None:
             line["hamming_2nn"] = ham
+        if world == 1 and not args.no_frontend:
+            line["kitti_stereo_frontend"] = run_stereo_frontend(local_rank, not args.no_cpu)
         if world == 1 and not args.no_cpu:
             from tests import oracle_lib
             kind = "reference" if oracle_lib.have_ref() else "port"
@@ -475,6 +542,7 @@ def main():
     ap.add_argument("--cpu-frames", type=int, default=384, help="frames in the bounded CPU sample")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-hamming", action="store_true")
+    ap.add_argument("--no-frontend", action="store_true")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
