@@ -5,6 +5,7 @@
 
 #include <cmath>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <mutex>
 #include <vector>
@@ -32,6 +33,8 @@ using namespace orbx;
 
 static inline int host_round_even(float v) { return (int)lrintf(v); }   // cvRound
 
+#define ORBX_NBUF 4     // input / result buffers in flight in the host-buffer pipeline (the host runs this many chunks ahead)
+
 struct orbx_extractor {
     int device = 0;
     int nfeatures = 0, nlevels = 0, iniTh = 0, minTh = 0;
@@ -39,28 +42,38 @@ struct orbx_extractor {
     std::vector<float> sf, isf, sig2, isig2;
     std::vector<int> nfeat;
     int umax[ORB_HALF_PATCH + 1];
-    cudaStream_t stream = nullptr;
+    cudaStream_t stream = nullptr;           // == ws[0].stream: the stream callers time and synchronise on
     // geometry-dependent state
     FrameGeom g{};
     bool haveGeom = false;
-    int capFrames = 0;                       // frames the workspaces are sized for
-    int lastFrames = 0;
+    int capFrames = 0;                       // frames EACH workspace is sized for
     ResizeTap* d_tabs = nullptr;
-    uint8_t* d_in[2] = {nullptr, nullptr}; size_t inBytes = 0;   // double-buffered H2D targets (host layout kept: linear copies)
-    uint8_t *d_pyr = nullptr, *d_blur = nullptr, *d_score = nullptr;
-    uint32_t *d_cellCount = nullptr, *d_cellOffs = nullptr, *d_cand = nullptr, *d_slots = nullptr;
-    uint32_t *d_keyA = nullptr, *d_keyB = nullptr, *d_valA = nullptr, *d_valB = nullptr, *d_sel = nullptr;
-    int *d_candCount = nullptr, *d_selCount = nullptr, *d_err = nullptr;
+    uint8_t* d_in[ORBX_NBUF] = {}; size_t inBytes = 0;   // double-buffered H2D targets (host layout kept: linear copies)
+    // Two complete kernel workspaces, each with its own compute stream: neighbouring chunks (host path) or the two halves
+    // of a batch (device path) run concurrently, so the latency-bound stages of one (quadtree, describe) fill the issue
+    // slots the ALU-bound stages of the other (pyramid/FAST, cell NMS) leave idle.
+    struct Workspace {
+        cudaStream_t stream = nullptr;
+        uint8_t *d_pyr = nullptr, *d_blur = nullptr, *d_score = nullptr;
+        uint32_t *d_cellCount = nullptr, *d_cellOffs = nullptr, *d_cand = nullptr, *d_slots = nullptr;
+        uint32_t *d_keyA = nullptr, *d_keyB = nullptr, *d_valA = nullptr, *d_valB = nullptr, *d_sel = nullptr;
+        int *d_candCount = nullptr, *d_selCount = nullptr;
+        int lastFrames = 0;
+    } ws[2];
+    int lastWs = 0;                          // workspace holding the most recent frames (introspection, stereo)
+    cudaEvent_t evFork = nullptr, evJoin = nullptr;
+    int* d_err = nullptr;
     // result block (device + pinned host mirror): [n_out[frames]] [err] [kps] [desc]
-    uint8_t* d_res[2] = {nullptr, nullptr}; uint8_t* h_res[2] = {nullptr, nullptr}; size_t resBytes = 0;
-    uint8_t* h_in[2] = {nullptr, nullptr}; size_t hInBytes = 0;       // pinned staging for pageable inputs
+    uint8_t* d_res[ORBX_NBUF] = {}; uint8_t* h_res[ORBX_NBUF] = {}; size_t resBytes = 0;
+    uint8_t* h_in[ORBX_NBUF] = {}; size_t hInBytes = 0;       // pinned staging for pageable inputs
     // host-buffer path: chunks of the batch flow through copy-in / compute / copy-out streams
     cudaStream_t sIn = nullptr, sOut = nullptr;
-    cudaEvent_t evIn[2] = {}, evCompute[2] = {}, evOut[2] = {};
+    cudaEvent_t evIn[ORBX_NBUF] = {}, evCompute[ORBX_NBUF] = {}, evOut[ORBX_NBUF] = {};
     uint8_t* d_stereo = nullptr; size_t stereoBytes = 0;     // scratch of orbx_stereo_match
     int launches = 0;
     bool profile = false;                    // record one CUDA event per stage boundary
-    cudaEvent_t ev[8] = {};
+    int profiledHalves = 0;
+    cudaEvent_t ev[2][8] = {};               // per half of a profiled batch
     std::mutex mtx;
 };
 
@@ -210,15 +223,21 @@ static int build_geometry(orbx_extractor* e, int width, int height, FrameGeom& g
 // workspaces
 // ---------------------------------------------------------------------------
 static void free_workspace(orbx_extractor* e) {
-    cudaFree(e->d_tabs); cudaFree(e->d_pyr); cudaFree(e->d_blur); cudaFree(e->d_score);
-    cudaFree(e->d_cellCount); cudaFree(e->d_cellOffs); cudaFree(e->d_cand); cudaFree(e->d_slots);
-    cudaFree(e->d_keyA); cudaFree(e->d_keyB); cudaFree(e->d_valA); cudaFree(e->d_valB); cudaFree(e->d_sel);
-    cudaFree(e->d_candCount); cudaFree(e->d_selCount); cudaFree(e->d_res[0]); cudaFree(e->d_res[1]);
-    for (int b = 0; b < 2; b++) if (e->h_res[b]) cudaFreeHost(e->h_res[b]);
-    e->d_tabs = nullptr; e->d_pyr = e->d_blur = e->d_score = nullptr;
-    e->d_slots = nullptr;
-    e->d_cellCount = e->d_cellOffs = e->d_cand = e->d_keyA = e->d_keyB = e->d_valA = e->d_valB = e->d_sel = nullptr;
-    e->d_candCount = e->d_selCount = nullptr; e->d_res[0] = e->d_res[1] = nullptr; e->h_res[0] = e->h_res[1] = nullptr;
+    cudaFree(e->d_tabs); e->d_tabs = nullptr;
+    for (auto& w : e->ws) {
+        cudaFree(w.d_pyr); cudaFree(w.d_blur); cudaFree(w.d_score);
+        cudaFree(w.d_cellCount); cudaFree(w.d_cellOffs); cudaFree(w.d_cand); cudaFree(w.d_slots);
+        cudaFree(w.d_keyA); cudaFree(w.d_keyB); cudaFree(w.d_valA); cudaFree(w.d_valB); cudaFree(w.d_sel);
+        cudaFree(w.d_candCount); cudaFree(w.d_selCount);
+        w.d_pyr = w.d_blur = w.d_score = nullptr;
+        w.d_cellCount = w.d_cellOffs = w.d_cand = w.d_slots = w.d_keyA = w.d_keyB = w.d_valA = w.d_valB = w.d_sel = nullptr;
+        w.d_candCount = w.d_selCount = nullptr; w.lastFrames = 0;
+    }
+    for (int b = 0; b < ORBX_NBUF; b++) {
+        cudaFree(e->d_res[b]); e->d_res[b] = nullptr;
+        if (e->h_res[b]) cudaFreeHost(e->h_res[b]);
+        e->h_res[b] = nullptr;
+    }
     e->capFrames = 0; e->haveGeom = false;
 }
 
@@ -229,6 +248,7 @@ static size_t res_bytes(const FrameGeom& g, int frames) {
 }
 static size_t res_head(int frames) { return ((size_t)(frames + 1) * 4 + 63) & ~(size_t)63; }
 
+// `frames` = frames per workspace
 static int ensure_workspace(orbx_extractor* e, int width, int height, int frames, bool needInput) {
     if (e->haveGeom && e->g.width == width && e->g.height == height && frames <= e->capFrames &&
         (!needInput || e->d_res[1]))
@@ -239,7 +259,7 @@ static int ensure_workspace(orbx_extractor* e, int width, int height, int frames
     std::vector<ResizeTap> tabs;
     int rc = build_geometry(e, width, height, g, tabs);
     if (rc != ORBX_OK) return rc;
-    CK(cudaStreamSynchronize(e->stream));
+    for (auto& w : e->ws) CK(cudaStreamSynchronize(w.stream));
     const bool hadInput = e->d_res[1] != nullptr;
     CK(cudaStreamSynchronize(e->sIn)); CK(cudaStreamSynchronize(e->sOut));
     free_workspace(e);
@@ -247,23 +267,25 @@ static int ensure_workspace(orbx_extractor* e, int width, int height, int frames
     const size_t F = (size_t)newCap;
     CK(cudaMalloc(&e->d_tabs, std::max<size_t>(tabs.size(), 1) * sizeof(ResizeTap)));
     if (!tabs.empty()) CK(cudaMemcpy(e->d_tabs, tabs.data(), tabs.size() * sizeof(ResizeTap), cudaMemcpyHostToDevice));
-    CK(cudaMalloc(&e->d_pyr, g.pyrBytes * F));
-    CK(cudaMalloc(&e->d_blur, g.planeBytes * F));
-    CK(cudaMalloc(&e->d_score, g.planeBytes * F));
-    CK(cudaMemset(e->d_pyr, 0, g.pyrBytes * F));
     const size_t cells = (size_t)std::max(g.totalCells, 1) * F;
-    CK(cudaMalloc(&e->d_cellCount, cells * 4));
-    CK(cudaMalloc(&e->d_cellOffs, cells * 4));
     const size_t cands = (size_t)std::max<unsigned long long>(g.candTotal, 64) * F;
-    CK(cudaMalloc(&e->d_cand, cands * 4));
-    CK(cudaMalloc(&e->d_slots, (size_t)std::max<unsigned long long>(g.slotTotal, 64) * F * 4));
-    CK(cudaMalloc(&e->d_keyA, cands * 4)); CK(cudaMalloc(&e->d_keyB, cands * 4));
-    CK(cudaMalloc(&e->d_valA, cands * 4)); CK(cudaMalloc(&e->d_valB, cands * 4));
-    CK(cudaMalloc(&e->d_sel, (size_t)g.selTotal * F * 4));
-    CK(cudaMalloc(&e->d_candCount, F * g.nlevels * 4));
-    CK(cudaMalloc(&e->d_selCount, F * g.nlevels * 4));
+    for (auto& w : e->ws) {
+        CK(cudaMalloc(&w.d_pyr, g.pyrBytes * F));
+        CK(cudaMalloc(&w.d_blur, g.planeBytes * F));
+        CK(cudaMalloc(&w.d_score, g.planeBytes * F));
+        CK(cudaMemset(w.d_pyr, 0, g.pyrBytes * F));
+        CK(cudaMalloc(&w.d_cellCount, cells * 4));
+        CK(cudaMalloc(&w.d_cellOffs, cells * 4));
+        CK(cudaMalloc(&w.d_cand, cands * 4));
+        CK(cudaMalloc(&w.d_slots, (size_t)std::max<unsigned long long>(g.slotTotal, 64) * F * 4));
+        CK(cudaMalloc(&w.d_keyA, cands * 4)); CK(cudaMalloc(&w.d_keyB, cands * 4));
+        CK(cudaMalloc(&w.d_valA, cands * 4)); CK(cudaMalloc(&w.d_valB, cands * 4));
+        CK(cudaMalloc(&w.d_sel, (size_t)g.selTotal * F * 4));
+        CK(cudaMalloc(&w.d_candCount, F * g.nlevels * 4));
+        CK(cudaMalloc(&w.d_selCount, F * g.nlevels * 4));
+    }
     e->resBytes = res_bytes(g, newCap);
-    for (int b = 0; b < (needInput || hadInput ? 2 : 1); b++) {
+    for (int b = 0; b < (needInput || hadInput ? ORBX_NBUF : 1); b++) {
         CK(cudaMalloc(&e->d_res[b], e->resBytes));
         CK(cudaMallocHost(&e->h_res[b], e->resBytes));
     }
@@ -283,19 +305,20 @@ static void pyr_smem_for(const LevelGeom& prev, const LevelGeom& cur, int& cols,
 }
 
 // Enqueue the whole pipeline for `frames` frames whose level-0 source is (src, pitch, frameStride).
-static int enqueue_pipeline(orbx_extractor* e, const uint8_t* src, size_t srcPitch, size_t srcFrameStride, int frames,
-                            orbx_keypoint* d_kps, uint8_t* d_desc, int cap, int* d_nOut, int* d_err) {
+// Enqueue the whole pipeline for `frames` frames on workspace `wi` (its stream).  `evs` (profiling) = 6 events or null.
+static int enqueue_pipeline(orbx_extractor* e, int wi, const uint8_t* src, size_t srcPitch, size_t srcFrameStride, int frames,
+                            orbx_keypoint* d_kps, uint8_t* d_desc, int cap, int* d_nOut, int* d_err, cudaEvent_t* evs) {
     const FrameGeom& g = e->g;
-    cudaStream_t st = e->stream;
+    orbx_extractor::Workspace& w = e->ws[wi];
+    cudaStream_t st = w.stream;
     int launches = 0;
-    CK(cudaMemsetAsync(d_err, 0, sizeof(int), st));
-    if (e->profile) CK(cudaEventRecord(e->ev[0], st));
+    if (evs) CK(cudaEventRecord(evs[0], st));
     // 1. pyramid + blur + FAST score, level by level (level l reads level l-1)
     for (int l = 0; l < g.nlevels; l++) {
         const LevelGeom& v = g.lv[l];
         PyrArgs a{};
-        a.pyr = e->d_pyr + v.pyrOff; a.pyrFrameStride = g.pyrBytes;
-        a.blur = e->d_blur + v.planeOff; a.score = e->d_score + v.planeOff; a.planeFrameStride = g.planeBytes;
+        a.pyr = w.d_pyr + v.pyrOff; a.pyrFrameStride = g.pyrBytes;
+        a.blur = w.d_blur + v.planeOff; a.score = w.d_score + v.planeOff; a.planeFrameStride = g.planeBytes;
         a.pitch = v.pitch; a.w = v.w; a.h = v.h; a.minTh = g.minTh; a.err = d_err;
         dim3 grid((v.w + TW - 1) / TW, (v.h + TH - 1) / TH, frames);
         if (l == 0) {
@@ -305,7 +328,7 @@ static int enqueue_pipeline(orbx_extractor* e, const uint8_t* src, size_t srcPit
             pyr_level_kernel<true><<<grid, PYR_THREADS, smem, st>>>(a);
         } else {
             const LevelGeom& p = g.lv[l - 1];
-            a.src = e->d_pyr + p.pyrOff + (size_t)ORB_EDGE * p.pitch; a.srcFrameStride = g.pyrBytes;
+            a.src = w.d_pyr + p.pyrOff + (size_t)ORB_EDGE * p.pitch; a.srcFrameStride = g.pyrBytes;
             a.srcPitch = p.pitch; a.srcX0 = ORB_XPAD; a.sw = p.w; a.sh = p.h;
             a.xtab = e->d_tabs + v.xtabOff; a.ytab = e->d_tabs + v.ytabOff;
             size_t smem;
@@ -314,11 +337,11 @@ static int enqueue_pipeline(orbx_extractor* e, const uint8_t* src, size_t srcPit
         }
         launches++;
     }
-    if (e->profile) CK(cudaEventRecord(e->ev[1], st));
+    if (evs) CK(cudaEventRecord(evs[1], st));
     // 2. REFLECT_101 frames
     {
         BorderArgs b{};
-        b.pyr = e->d_pyr; b.pyrFrameStride = g.pyrBytes; b.nlevels = g.nlevels;
+        b.pyr = w.d_pyr; b.pyrFrameStride = g.pyrBytes; b.nlevels = g.nlevels;
         int off = 0;
         for (int l = 0; l < g.nlevels; l++) {
             const LevelGeom& v = g.lv[l];
@@ -330,10 +353,10 @@ static int enqueue_pipeline(orbx_extractor* e, const uint8_t* src, size_t srcPit
         border_kernel<<<dim3((off + 7) / 8, frames), 256, 0, st>>>(b);
         launches++;
     }
-    if (e->profile) CK(cudaEventRecord(e->ev[2], st));
+    if (evs) CK(cudaEventRecord(evs[2], st));
     // 3. per-cell NMS + threshold fallback -> per-cell survivor lists (one launch, score plane read once)
     CellArgs c{};
-    c.score = e->d_score; c.planeFrameStride = g.planeBytes; c.nlevels = g.nlevels; c.iniTh = g.iniTh; c.minTh = g.minTh;
+    c.score = w.d_score; c.planeFrameStride = g.planeBytes; c.nlevels = g.nlevels; c.iniTh = g.iniTh; c.minTh = g.minTh;
     c.totalCells = g.totalCells;
     for (int l = 0; l < g.nlevels; l++) {
         const LevelGeom& v = g.lv[l];
@@ -343,19 +366,19 @@ static int enqueue_pipeline(orbx_extractor* e, const uint8_t* src, size_t srcPit
     }
     c.cellOff[g.nlevels] = g.totalCells;
     c.slotFrameStride = g.slotTotal;
-    c.cellCount = e->d_cellCount; c.slots = e->d_slots; c.err = d_err;
+    c.cellCount = w.d_cellCount; c.slots = w.d_slots; c.err = d_err;
     if (g.totalCells > 0) {
         cell_nms_kernel<<<dim3((g.totalCells + 7) / 8, frames), 256, 0, st>>>(c);
         launches++;
     }
-    if (e->profile) CK(cudaEventRecord(e->ev[3], st));
+    if (evs) CK(cudaEventRecord(evs[3], st));
     // 4. quadtree distribution (gathers the cell lists into vToDistributeKeys first)
     QtArgs q{};
-    q.cand = e->d_cand; q.candFrameStride = g.candTotal; q.candCount = e->d_candCount;
-    q.cellCount = e->d_cellCount; q.cellOffs = e->d_cellOffs; q.slots = e->d_slots; q.slotFrameStride = g.slotTotal;
+    q.cand = w.d_cand; q.candFrameStride = g.candTotal; q.candCount = w.d_candCount;
+    q.cellCount = w.d_cellCount; q.cellOffs = w.d_cellOffs; q.slots = w.d_slots; q.slotFrameStride = g.slotTotal;
     q.totalCells = g.totalCells;
-    q.keyA = e->d_keyA; q.keyB = e->d_keyB; q.valA = e->d_valA; q.valB = e->d_valB;
-    q.sel = e->d_sel; q.selCount = e->d_selCount; q.err = d_err;
+    q.keyA = w.d_keyA; q.keyB = w.d_keyB; q.valA = w.d_valA; q.valB = w.d_valB;
+    q.sel = w.d_sel; q.selCount = w.d_selCount; q.err = d_err;
     q.nlevels = g.nlevels; q.selTotal = g.selTotal; q.nodeCap = g.nodeCap;
     for (int l = 0; l < g.nlevels; l++) {
         const LevelGeom& v = g.lv[l];
@@ -366,11 +389,11 @@ static int enqueue_pipeline(orbx_extractor* e, const uint8_t* src, size_t srcPit
     q.cellOff[g.nlevels] = g.totalCells;
     quadtree_kernel<<<dim3(g.nlevels, frames), QT_THREADS, qt_smem_bytes(g.nodeCap), st>>>(q);
     launches++;
-    if (e->profile) CK(cudaEventRecord(e->ev[4], st));
+    if (evs) CK(cudaEventRecord(evs[4], st));
     // 5. orientation, descriptors, output assembly
     DescArgs d{};
-    d.pyr = e->d_pyr; d.pyrFrameStride = g.pyrBytes; d.blur = e->d_blur; d.planeFrameStride = g.planeBytes;
-    d.sel = e->d_sel; d.selCount = e->d_selCount; d.kps = d_kps; d.desc = d_desc; d.nOut = d_nOut;
+    d.pyr = w.d_pyr; d.pyrFrameStride = g.pyrBytes; d.blur = w.d_blur; d.planeFrameStride = g.planeBytes;
+    d.sel = w.d_sel; d.selCount = w.d_selCount; d.kps = d_kps; d.desc = d_desc; d.nOut = d_nOut;
     d.cap = cap; d.nlevels = g.nlevels; d.selTotal = g.selTotal;
     for (int l = 0; l < g.nlevels; l++) {
         const LevelGeom& v = g.lv[l];
@@ -380,9 +403,9 @@ static int enqueue_pipeline(orbx_extractor* e, const uint8_t* src, size_t srcPit
     d.selOff[g.nlevels] = g.selTotal;
     describe_kernel<<<dim3((g.selTotal + 7) / 8, frames), 256, 0, st>>>(d);
     launches++;
-    if (e->profile) CK(cudaEventRecord(e->ev[5], st));
-    e->launches = launches;
-    e->lastFrames = frames;
+    if (evs) CK(cudaEventRecord(evs[5], st));
+    e->launches += launches;
+    w.lastFrames = frames; e->lastWs = wi;
     CK(cudaGetLastError());
     return ORBX_OK;
 }
@@ -419,9 +442,13 @@ int orbx_create(orbx_t** out, int nfeatures, float scaleFactor, int nlevels, int
     e->scaleFactor = scaleFactor;
     init_tables(e);
     cudaError_t rc = cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking);
+    e->ws[0].stream = e->stream;
+    if (rc == cudaSuccess) rc = cudaStreamCreateWithFlags(&e->ws[1].stream, cudaStreamNonBlocking);
+    if (rc == cudaSuccess) rc = cudaEventCreateWithFlags(&e->evFork, cudaEventDisableTiming);
+    if (rc == cudaSuccess) rc = cudaEventCreateWithFlags(&e->evJoin, cudaEventDisableTiming);
     if (rc == cudaSuccess) rc = cudaStreamCreateWithFlags(&e->sIn, cudaStreamNonBlocking);
     if (rc == cudaSuccess) rc = cudaStreamCreateWithFlags(&e->sOut, cudaStreamNonBlocking);
-    for (int b = 0; b < 2 && rc == cudaSuccess; b++) {
+    for (int b = 0; b < ORBX_NBUF && rc == cudaSuccess; b++) {
         rc = cudaEventCreateWithFlags(&e->evIn[b], cudaEventDisableTiming);
         if (rc == cudaSuccess) rc = cudaEventCreateWithFlags(&e->evCompute[b], cudaEventDisableTiming);
         if (rc == cudaSuccess) rc = cudaEventCreateWithFlags(&e->evOut[b], cudaEventDisableTiming);
@@ -447,11 +474,14 @@ int orbx_create(orbx_t** out, int nfeatures, float scaleFactor, int nlevels, int
 void orbx_destroy(orbx_t* e) {
     if (!e) return;
     cudaSetDevice(e->device);
-    cudaStreamSynchronize(e->stream);
+    for (auto& w : e->ws) if (w.stream) cudaStreamSynchronize(w.stream);
     free_workspace(e);
     cudaFree(e->d_err); cudaFree(e->d_stereo);
-    for (int i = 0; i < 8; i++) if (e->ev[i]) cudaEventDestroy(e->ev[i]);
-    for (int b = 0; b < 2; b++) {
+    for (int hlf = 0; hlf < 2; hlf++) for (int i = 0; i < 8; i++) if (e->ev[hlf][i]) cudaEventDestroy(e->ev[hlf][i]);
+    if (e->evFork) cudaEventDestroy(e->evFork);
+    if (e->evJoin) cudaEventDestroy(e->evJoin);
+    if (e->ws[1].stream) cudaStreamDestroy(e->ws[1].stream);
+    for (int b = 0; b < ORBX_NBUF; b++) {
         cudaFree(e->d_in[b]);
         if (e->h_in[b]) cudaFreeHost(e->h_in[b]);
         if (e->evIn[b]) cudaEventDestroy(e->evIn[b]);
@@ -492,7 +522,7 @@ void* orbx_stream(orbx_t* e) { return e ? (void*)e->stream : nullptr; }
 int orbx_synchronize(orbx_t* e) {
     if (!e) return ORBX_E_INVALID;
     CK(cudaSetDevice(e->device));
-    CK(cudaStreamSynchronize(e->stream));
+    CK(cudaStreamSynchronize(e->stream));            // the second workspace stream is joined into this one by every call
     int err = 0;
     CK(cudaMemcpy(&err, e->d_err, sizeof(int), cudaMemcpyDeviceToHost));
     if (err) { std::fprintf(stderr, "orbx: device consistency check %d failed\n", err); return ORBX_E_INTERNAL; }
@@ -507,10 +537,35 @@ int orbx_extract_batch_device(orbx_t* e, const uint8_t* d_images, int n, int wid
         return ORBX_E_INVALID;
     std::lock_guard<std::mutex> lk(e->mtx);
     CK(cudaSetDevice(e->device));
-    int rc = ensure_workspace(e, width, height, n, false);
+    // two halves on the two workspaces / streams; the second stream is forked from and joined back into the first,
+    // so callers keep ordering and timing everything on orbx_stream()
+    const int h0 = (n + 1) / 2, h1 = n - h0;
+    int rc = ensure_workspace(e, width, height, h0, false);
     if (rc != ORBX_OK) return rc;
     if (capacity < e->g.selTotal) return ORBX_E_CAPACITY;
-    return enqueue_pipeline(e, d_images, step, frame_stride, n, d_keypoints, d_descriptors, capacity, d_n_out, e->d_err);
+    CK(cudaMemsetAsync(e->d_err, 0, sizeof(int), e->stream));
+    e->launches = 0;
+    if (e->profile) {
+        // per-stage events need one stream: run the halves back to back on the first workspace
+        rc = enqueue_pipeline(e, 0, d_images, step, frame_stride, h0, d_keypoints, d_descriptors, capacity, d_n_out, e->d_err, e->ev[0]);
+        if (rc == ORBX_OK && h1)
+            rc = enqueue_pipeline(e, 0, d_images + (size_t)h0 * frame_stride, step, frame_stride, h1, d_keypoints + (size_t)h0 * capacity,
+                                  d_descriptors + (size_t)h0 * capacity * 32, capacity, d_n_out + h0, e->d_err, e->ev[1]);
+        e->profiledHalves = h1 ? 2 : 1;
+        return rc;
+    }
+    if (h1) {
+        CK(cudaEventRecord(e->evFork, e->stream));
+        CK(cudaStreamWaitEvent(e->ws[1].stream, e->evFork, 0));
+        rc = enqueue_pipeline(e, 1, d_images + (size_t)h0 * frame_stride, step, frame_stride, h1, d_keypoints + (size_t)h0 * capacity,
+                              d_descriptors + (size_t)h0 * capacity * 32, capacity, d_n_out + h0, e->d_err, nullptr);
+        if (rc != ORBX_OK) return rc;
+        CK(cudaEventRecord(e->evJoin, e->ws[1].stream));
+    }
+    rc = enqueue_pipeline(e, 0, d_images, step, frame_stride, h0, d_keypoints, d_descriptors, capacity, d_n_out, e->d_err, nullptr);
+    if (rc != ORBX_OK) return rc;
+    if (h1) CK(cudaStreamWaitEvent(e->stream, e->evJoin, 0));
+    return ORBX_OK;
 }
 
 // frames per pipeline chunk of the host-buffer path: large enough to fill the GPU (>= 8 CTAs per SM on the
@@ -532,7 +587,8 @@ int orbx_extract_batch(orbx_t* e, const uint8_t* const* images, int n, int width
     for (int i = 0; i < n; i++) if (!images[i]) return ORBX_E_INVALID;
     std::lock_guard<std::mutex> lk(e->mtx);
     CK(cudaSetDevice(e->device));
-    const int chunk = std::min(n, ORBX_CHUNK);
+    static const int chunkFrames = [] { const char* v = std::getenv("ORBX_CHUNK_FRAMES"); const int c = v ? std::atoi(v) : 0; return c > 0 ? c : ORBX_CHUNK; }();
+    const int chunk = std::min(n, chunkFrames);
     int rc = ensure_workspace(e, width, height, chunk, true);
     if (rc != ORBX_OK) return rc;
     const FrameGeom& g = e->g;
@@ -554,7 +610,7 @@ int orbx_extract_batch(orbx_t* e, const uint8_t* const* images, int n, int width
         const size_t need = (size_t)F * width * height;
         if (e->hInBytes < need) {
             CK(cudaStreamSynchronize(e->sIn));
-            for (int b = 0; b < 2; b++) {
+            for (int b = 0; b < ORBX_NBUF; b++) {
                 if (e->h_in[b]) cudaFreeHost(e->h_in[b]);
                 e->h_in[b] = nullptr;
                 CK(cudaMallocHost(&e->h_in[b], need));
@@ -563,8 +619,8 @@ int orbx_extract_batch(orbx_t* e, const uint8_t* const* images, int n, int width
         }
     }
     if (e->inBytes < devStride * F + 64) {
-        CK(cudaStreamSynchronize(e->sIn)); CK(cudaStreamSynchronize(e->stream));
-        for (int b = 0; b < 2; b++) {
+        CK(cudaStreamSynchronize(e->sIn)); CK(cudaStreamSynchronize(e->ws[0].stream)); CK(cudaStreamSynchronize(e->ws[1].stream));
+        for (int b = 0; b < ORBX_NBUF; b++) {
             cudaFree(e->d_in[b]); e->d_in[b] = nullptr;
             CK(cudaMalloc(&e->d_in[b], devStride * F + 64));
         }
@@ -572,8 +628,14 @@ int orbx_extract_batch(orbx_t* e, const uint8_t* const* images, int n, int width
     }
     const int nchunks = (n + chunk - 1) / chunk;
     int status = ORBX_OK;
+    e->launches = 0;
+    // ORBX_TRACE=1: device timeline of the chunk pipeline (debug aid; costs five timing events per chunk)
+    static const bool trace = std::getenv("ORBX_TRACE") != nullptr;
+    std::vector<cudaEvent_t> tev;
+    if (trace) { tev.resize((size_t)nchunks * 5 + 1); for (auto& t : tev) cudaEventCreate(&t); cudaEventRecord(tev.back(), e->sIn); }
+    auto mark = [&](int k, int what, cudaStream_t st) { if (trace) cudaEventRecord(tev[(size_t)k * 5 + what], st); };
     auto finalize = [&](int k) -> int {        // host side of chunk k: counts, error flag, staged results
-        const int b = k & 1, f0 = k * chunk, nf = std::min(chunk, n - f0);
+        const int b = k % ORBX_NBUF, f0 = k * chunk, nf = std::min(chunk, n - f0);
         CK(cudaEventSynchronize(e->evOut[b]));
         const int* h_n = (const int*)e->h_res[b];
         if (h_n[F] != 0) {
@@ -593,10 +655,17 @@ int orbx_extract_batch(orbx_t* e, const uint8_t* const* images, int n, int width
         }
         return ORBX_OK;
     };
+    int finalized = 0;                          // chunks [0, finalized) are complete on the host
     for (int k = 0; k < nchunks; k++) {
-        const int b = k & 1, f0 = k * chunk, nf = std::min(chunk, n - f0);
-        // ---- copy-in stream: d_in[b] is free once the compute of chunk k-2 has finished
-        if (k >= 2) CK(cudaStreamWaitEvent(e->sIn, e->evCompute[b], 0));
+        const int b = k % ORBX_NBUF, f0 = k * chunk, nf = std::min(chunk, n - f0);
+        // buffer set b was last used by chunk k - ORBX_NBUF: finish it on the host before its staging is reused.  The
+        // host therefore runs up to ORBX_NBUF chunks ahead of the device, which keeps both copy engines and the two
+        // compute streams fed.
+        while (status == ORBX_OK && finalized <= k - ORBX_NBUF) { rc = finalize(finalized++); if (rc != ORBX_OK) status = rc; }
+        if (status != ORBX_OK) break;
+        // ---- copy-in stream: d_in[b] is free once the compute of chunk k - ORBX_NBUF has finished
+        if (k >= ORBX_NBUF) CK(cudaStreamWaitEvent(e->sIn, e->evCompute[b], 0));
+        mark(k, 0, e->sIn);
         if (inPinned) {
             // frames that lie back to back in host memory go as one linear copy
             int i = 0;
@@ -608,7 +677,7 @@ int orbx_extract_batch(orbx_t* e, const uint8_t* const* images, int n, int width
                 i = j;
             }
         } else {
-            if (k >= 2) CK(cudaEventSynchronize(e->evIn[b]));          // staging buffer b consumed by the H2D of chunk k-2
+            if (k >= ORBX_NBUF) CK(cudaEventSynchronize(e->evIn[b]));  // staging buffer b consumed by the H2D of chunk k - ORBX_NBUF
             for (int i = 0; i < nf; i++) {
                 uint8_t* dst = e->h_in[b] + (size_t)i * width * height;
                 const uint8_t* srcp = images[f0 + i];
@@ -618,16 +687,21 @@ int orbx_extract_batch(orbx_t* e, const uint8_t* const* images, int n, int width
             CK(cudaMemcpyAsync(e->d_in[b], e->h_in[b], (size_t)width * height * nf, cudaMemcpyHostToDevice, e->sIn));
         }
         CK(cudaEventRecord(e->evIn[b], e->sIn));
+        mark(k, 1, e->sIn);
         // ---- compute stream: needs the input, and d_res[b] drained by the copy-out of chunk k-2
-        CK(cudaStreamWaitEvent(e->stream, e->evIn[b], 0));
-        if (k >= 2) CK(cudaStreamWaitEvent(e->stream, e->evOut[b], 0));
+        cudaStream_t cst = e->ws[k & 1].stream;                          // workspace / compute stream of this parity
+        CK(cudaStreamWaitEvent(cst, e->evIn[b], 0));
+        if (k >= ORBX_NBUF) CK(cudaStreamWaitEvent(cst, e->evOut[b], 0));
+        mark(k, 2, cst);
         int* d_n = (int*)e->d_res[b];
         int* d_err = d_n + F;
         orbx_keypoint* d_kps = (orbx_keypoint*)(e->d_res[b] + head);
         uint8_t* d_desc = e->d_res[b] + head + (size_t)F * cap * kpBytes;
-        rc = enqueue_pipeline(e, e->d_in[b], devPitch, devStride, nf, d_kps, d_desc, cap, d_n, d_err);
+        CK(cudaMemsetAsync(d_err, 0, sizeof(int), cst));
+        rc = enqueue_pipeline(e, k & 1, e->d_in[b], devPitch, devStride, nf, d_kps, d_desc, cap, d_n, d_err, nullptr);
         if (rc != ORBX_OK) { status = rc; break; }
-        CK(cudaEventRecord(e->evCompute[b], e->stream));
+        CK(cudaEventRecord(e->evCompute[b], cst));
+        mark(k, 3, cst);
         // ---- copy-out stream
         CK(cudaStreamWaitEvent(e->sOut, e->evCompute[b], 0));
         CK(cudaMemcpyAsync(e->h_res[b], e->d_res[b], head, cudaMemcpyDeviceToHost, e->sOut));
@@ -642,11 +716,19 @@ int orbx_extract_batch(orbx_t* e, const uint8_t* const* images, int n, int width
                                cudaMemcpyDeviceToHost, e->sOut));
         }
         CK(cudaEventRecord(e->evOut[b], e->sOut));
-        // ---- host: finish chunk k-1 while the GPU works on chunk k
-        if (k >= 1 && status == ORBX_OK) { rc = finalize(k - 1); if (rc != ORBX_OK) status = rc; }
+        mark(k, 4, e->sOut);
     }
-    if (status == ORBX_OK) status = finalize(nchunks - 1);
-    CK(cudaStreamSynchronize(e->sIn)); CK(cudaStreamSynchronize(e->stream)); CK(cudaStreamSynchronize(e->sOut));
+    while (status == ORBX_OK && finalized < nchunks) { rc = finalize(finalized++); if (rc != ORBX_OK) status = rc; }
+    CK(cudaStreamSynchronize(e->sIn)); CK(cudaStreamSynchronize(e->ws[0].stream)); CK(cudaStreamSynchronize(e->ws[1].stream));
+    CK(cudaStreamSynchronize(e->sOut));
+    if (trace) {
+        for (int k = 0; k < nchunks; k++) {
+            float t[5];
+            for (int j = 0; j < 5; j++) cudaEventElapsedTime(&t[j], tev.back(), tev[(size_t)k * 5 + j]);
+            std::fprintf(stderr, "orbx trace chunk %2d: h2d %7.3f-%7.3f  compute %7.3f-%7.3f  d2h done %7.3f ms\n", k, t[0], t[1], t[2], t[3], t[4]);
+        }
+        for (auto& t : tev) cudaEventDestroy(t);
+    }
     return status;
 }
 
@@ -666,32 +748,33 @@ int orbx_level_size(const orbx_t* e, int level, int* width, int* height) {
 }
 
 int orbx_get_level(orbx_t* e, int frame, int level, int border, int blurred, uint8_t* dst, size_t dst_step) {
-    if (!e || !e->haveGeom || level < 0 || level >= e->nlevels || frame < 0 || frame >= e->lastFrames || !dst ||
+    if (!e || !e->haveGeom || level < 0 || level >= e->nlevels || frame < 0 || frame >= e->ws[e->lastWs].lastFrames || !dst ||
         border < 0 || border > ORB_EDGE || (blurred && border) || blurred < 0 || blurred > 2)
         return ORBX_E_INVALID;
     std::lock_guard<std::mutex> lk(e->mtx);
     CK(cudaSetDevice(e->device));
     const LevelGeom& v = e->g.lv[level];
+    const orbx_extractor::Workspace& w = e->ws[e->lastWs];
     const uint8_t* src;
-    if (blurred) src = (blurred == 2 ? e->d_score : e->d_blur) + (size_t)frame * e->g.planeBytes + v.planeOff + ORB_XPAD;
-    else src = e->d_pyr + (size_t)frame * e->g.pyrBytes + v.pyrOff + (size_t)(ORB_EDGE - border) * v.pitch + ORB_XPAD - border;
+    if (blurred) src = (blurred == 2 ? w.d_score : w.d_blur) + (size_t)frame * e->g.planeBytes + v.planeOff + ORB_XPAD;
+    else src = w.d_pyr + (size_t)frame * e->g.pyrBytes + v.pyrOff + (size_t)(ORB_EDGE - border) * v.pitch + ORB_XPAD - border;
     CK(cudaMemcpy2DAsync(dst, dst_step, src, v.pitch, v.w + 2 * border, v.h + 2 * border, cudaMemcpyDeviceToHost, e->stream));
     CK(cudaStreamSynchronize(e->stream));
     return ORBX_OK;
 }
 
 int orbx_get_candidates(orbx_t* e, int frame, int level, int32_t* xyr, int capacity, int* n_out) {
-    if (!e || !e->haveGeom || level < 0 || level >= e->nlevels || frame < 0 || frame >= e->lastFrames || !n_out)
+    if (!e || !e->haveGeom || level < 0 || level >= e->nlevels || frame < 0 || frame >= e->ws[e->lastWs].lastFrames || !n_out)
         return ORBX_E_INVALID;
     std::lock_guard<std::mutex> lk(e->mtx);
     CK(cudaSetDevice(e->device));
     CK(cudaStreamSynchronize(e->stream));
     int n = 0;
-    CK(cudaMemcpy(&n, e->d_candCount + frame * e->nlevels + level, sizeof(int), cudaMemcpyDeviceToHost));
+    CK(cudaMemcpy(&n, e->ws[e->lastWs].d_candCount + frame * e->nlevels + level, sizeof(int), cudaMemcpyDeviceToHost));
     *n_out = n;
     if (!xyr || n == 0) return ORBX_OK;
     std::vector<uint32_t> tmp(n);
-    CK(cudaMemcpy(tmp.data(), e->d_cand + (size_t)frame * e->g.candTotal + e->g.lv[level].candOff, (size_t)n * 4,
+    CK(cudaMemcpy(tmp.data(), e->ws[e->lastWs].d_cand + (size_t)frame * e->g.candTotal + e->g.lv[level].candOff, (size_t)n * 4,
                   cudaMemcpyDeviceToHost));
     for (int i = 0; i < n && i < capacity; i++) {
         xyr[3 * i] = (int)(tmp[i] & 0xfff); xyr[3 * i + 1] = (int)((tmp[i] >> 12) & 0xfff); xyr[3 * i + 2] = (int)(tmp[i] >> 24);
@@ -710,11 +793,12 @@ int orbx_stereo_match(orbx_t* left, orbx_t* right, int frame, const orbx_keypoin
     if (nL == 0) return ORBX_OK;
     std::lock_guard<std::mutex> lk(left->mtx);
     if (!left->haveGeom || !right->haveGeom || left->device != right->device || left->g.width != right->g.width ||
-        left->g.height != right->g.height || left->nlevels != right->nlevels || frame < 0 || frame >= left->lastFrames ||
-        frame >= right->lastFrames)
+        left->g.height != right->g.height || left->nlevels != right->nlevels || frame < 0 || frame >= left->ws[left->lastWs].lastFrames ||
+        frame >= right->ws[right->lastWs].lastFrames)
         return ORBX_E_INVALID;
     CK(cudaSetDevice(left->device));
-    CK(cudaStreamSynchronize(right->stream));                 // the right pyramid is complete
+    CK(cudaStreamSynchronize(right->ws[right->lastWs].stream));   // the right pyramid is complete
+    if (left->lastWs) CK(cudaStreamSynchronize(left->ws[1].stream));
     const size_t kb = sizeof(orbx_keypoint);
     const size_t oKL = 0, oDL = oKL + (((size_t)nL * kb + 255) & ~(size_t)255), oKR = oDL + (size_t)nL * 32 + 256;
     const size_t oDR = oKR + (((size_t)nR * kb + 255) & ~(size_t)255), oU = oDR + (size_t)std::max(nR, 1) * 32 + 256;
@@ -737,7 +821,8 @@ int orbx_stereo_match(orbx_t* left, orbx_t* right, int frame, const orbx_keypoin
     StereoArgs a{};
     a.keysL = (const orbx_keypoint*)(d + oKL); a.descL = (const uint32_t*)(d + oDL); a.nL = nL;
     a.keysR = (const orbx_keypoint*)(d + oKR); a.descR = (const uint32_t*)(d + oDR); a.nR = nR;
-    a.pyrL = left->d_pyr + (size_t)frame * left->g.pyrBytes; a.pyrR = right->d_pyr + (size_t)frame * right->g.pyrBytes;
+    a.pyrL = left->ws[left->lastWs].d_pyr + (size_t)frame * left->g.pyrBytes;
+    a.pyrR = right->ws[right->lastWs].d_pyr + (size_t)frame * right->g.pyrBytes;
     a.nlevels = e->nlevels;
     for (int l = 0; l < e->nlevels; l++) {
         a.pyrOff[l] = e->g.lv[l].pyrOff; a.pitch[l] = e->g.lv[l].pitch; a.cols[l] = e->g.lv[l].w;
@@ -763,7 +848,7 @@ int orbx_set_profiling(orbx_t* e, int on) {
     if (!e) return ORBX_E_INVALID;
     std::lock_guard<std::mutex> lk(e->mtx);
     CK(cudaSetDevice(e->device));
-    if (on && !e->ev[0]) for (int i = 0; i < 8; i++) CK(cudaEventCreate(&e->ev[i]));
+    if (on && !e->ev[0][0]) for (int hlf = 0; hlf < 2; hlf++) for (int i = 0; i < 8; i++) CK(cudaEventCreate(&e->ev[hlf][i]));
     e->profile = on != 0;
     return ORBX_OK;
 }
@@ -772,8 +857,15 @@ int orbx_stage_times(orbx_t* e, float* ms, int n) {
     if (!e || !ms || n < ORBX_NUM_STAGES || !e->profile) return ORBX_E_INVALID;
     std::lock_guard<std::mutex> lk(e->mtx);
     CK(cudaSetDevice(e->device));
-    CK(cudaEventSynchronize(e->ev[ORBX_NUM_STAGES]));
-    for (int i = 0; i < ORBX_NUM_STAGES; i++) CK(cudaEventElapsedTime(&ms[i], e->ev[i], e->ev[i + 1]));
+    for (int i = 0; i < ORBX_NUM_STAGES; i++) ms[i] = 0.f;
+    for (int hlf = 0; hlf < e->profiledHalves; hlf++) {
+        CK(cudaEventSynchronize(e->ev[hlf][ORBX_NUM_STAGES]));
+        for (int i = 0; i < ORBX_NUM_STAGES; i++) {
+            float t = 0.f;
+            CK(cudaEventElapsedTime(&t, e->ev[hlf][i], e->ev[hlf][i + 1]));
+            ms[i] += t;
+        }
+    }
     return ORBX_OK;
 }
 
