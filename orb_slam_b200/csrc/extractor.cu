@@ -294,6 +294,7 @@ static int ensure_workspace(orbx_extractor* e, int width, int height, int frames
     // kernel attributes
     CK(cudaFuncSetAttribute(quadtree_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)qt_smem_bytes(g.nodeCap)));
     CK(cudaFuncSetAttribute(pyr_level_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
+    CK(cudaFuncSetAttribute(pyr_level_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
     return ORBX_OK;
 }
 

@@ -67,25 +67,31 @@ __device__ __forceinline__ RowPairs row_pairs(const uint32_t* __restrict__ row) 
 }
 
 // max over the 16 arcs of 9 contiguous ring pixels of the arc minimum (MAXOFMIN) or min of the arc maximum,
-// lane-wise on u16x2.  arc9[k] = op3(t[k], t[k+3], t[k+6]) with t[k] = op3(P[k], P[k+1], P[k+2]).
+// lane-wise on u16x2, in 47 two-input comparisons: arcs 2i and 2i+1 share the 8 pixels 2i+1..2i+8, and
+//   max( min(m8, P[2i]), min(m8, P[2i+9]) ) = min( m8, max(P[2i], P[2i+9]) ),
+// so only the eight odd-aligned windows m8[i] = op(P[2i+1..2i+8]) are built (log-doubling, 24 comparisons), each is
+// closed with one pre-combined end pixel (16), and the eight results are reduced (7).  Two-input VIMNMX.U16x2 issues
+// at twice the rate of VIMNMX3 on sm_100 (tools/pipebench.cu), so comparisons - not instructions - are the cost.
 template <bool MAXOFMIN>
 __device__ __forceinline__ uint32_t arc9_extreme(const uint32_t (&P)[16]) {
-    uint32_t t[16];
+#define ARC_OP(x, y) (MAXOFMIN ? __vminu2((x), (y)) : __vmaxu2((x), (y)))
+#define ARC_RO(x, y) (MAXOFMIN ? __vmaxu2((x), (y)) : __vminu2((x), (y)))
+    uint32_t m2[8], m4[8], r[8];
 #pragma unroll
-    for (int k = 0; k < 16; k++)
-        t[k] = MAXOFMIN ? __vimin3_u16x2(P[k], P[(k + 1) & 15], P[(k + 2) & 15]) : __vimax3_u16x2(P[k], P[(k + 1) & 15], P[(k + 2) & 15]);
-    uint32_t a[16];
+    for (int i = 0; i < 8; i++) m2[i] = ARC_OP(P[2 * i + 1], P[(2 * i + 2) & 15]);
 #pragma unroll
-    for (int k = 0; k < 16; k++)
-        a[k] = MAXOFMIN ? __vimin3_u16x2(t[k], t[(k + 3) & 15], t[(k + 6) & 15]) : __vimax3_u16x2(t[k], t[(k + 3) & 15], t[(k + 6) & 15]);
-    uint32_t r[6];
+    for (int i = 0; i < 8; i++) m4[i] = ARC_OP(m2[i], m2[(i + 1) & 7]);
 #pragma unroll
-    for (int k = 0; k < 5; k++)
-        r[k] = MAXOFMIN ? __vimax3_u16x2(a[3 * k], a[3 * k + 1], a[3 * k + 2]) : __vimin3_u16x2(a[3 * k], a[3 * k + 1], a[3 * k + 2]);
-    r[5] = a[15];
-    const uint32_t u = MAXOFMIN ? __vimax3_u16x2(r[0], r[1], r[2]) : __vimin3_u16x2(r[0], r[1], r[2]);
-    const uint32_t v = MAXOFMIN ? __vimax3_u16x2(r[3], r[4], r[5]) : __vimin3_u16x2(r[3], r[4], r[5]);
-    return MAXOFMIN ? __vmaxu2(u, v) : __vminu2(u, v);
+    for (int i = 0; i < 8; i++) {
+        const uint32_t m8 = ARC_OP(m4[i], m4[(i + 2) & 7]);              // pixels 2i+1 .. 2i+8
+        const uint32_t e = ARC_RO(P[2 * i], P[(2 * i + 9) & 15]);          // the two possible ninth pixels
+        r[i] = ARC_OP(m8, e);
+    }
+    const uint32_t a = ARC_RO(ARC_RO(r[0], r[1]), ARC_RO(r[2], r[3]));
+    const uint32_t b = ARC_RO(ARC_RO(r[4], r[5]), ARC_RO(r[6], r[7]));
+    return ARC_RO(a, b);
+#undef ARC_OP
+#undef ARC_RO
 }
 
 // cornerScore<16> of OpenCV for two pixels at once (u16x2 lanes): the largest threshold at which the centre is still
@@ -97,29 +103,28 @@ __device__ __forceinline__ uint32_t fast_score_pair(const uint32_t (&P)[16], uin
     return __vmaxu2(hi + bias - V, V + bias - lo);
 }
 
-// FAST score of the 4 pixels of group word column `g` on tile row r (0..TH-1).  T is the level tile with halo.
+// FAST score of the 4 pixels of group `g` on tile row r (0..TH-1), from the pair planes of the 7 tile rows r..r+6
+// (PA[row][g] = {x1, em, om, x2}, PB[row][g] = {ol, x4, x3, er}: each row's stride-2 pixel pairs are split out of
+// the level tile once, by the row pass, instead of once per ring row that needs them).
 // Result: four bytes (pixel order) of max(0, score + 1 - minTh) - the score plane's encoding.
-__device__ __forceinline__ uint32_t fast_score4(const uint8_t* __restrict__ T, int r, int g, int minTh) {
-    // tile pixel column c = 4g sits at byte TCOL0 + c: the word holding c-4..c-1 is word g of the row
-    const uint32_t* base = (const uint32_t*)(T + r * TS) + g;           // row r of T = level row y0 + r - HALO
-    constexpr int W = TS / 4;
-    const RowPairs m3 = row_pairs(base);            // dy = -3
-    const RowPairs m2 = row_pairs(base + W);
-    const RowPairs m1 = row_pairs(base + 2 * W);
-    const RowPairs z0 = row_pairs(base + 3 * W);    // centre row
-    const RowPairs p1 = row_pairs(base + 4 * W);
-    const RowPairs p2 = row_pairs(base + 5 * W);
-    const RowPairs p3 = row_pairs(base + 6 * W);    // dy = +3
+__device__ __forceinline__ uint32_t fast_score4(const uint4* __restrict__ PA, const uint4* __restrict__ PB, int r, int g, int minTh) {
+    const uint4* a = PA + r * 32 + g;
+    const uint4* b = PB + r * 32 + g;
+    const uint4 a0 = a[0], a6 = a[6 * 32];                       // dy = -3, +3: x1 em om x2
+    const uint4 a1 = a[32], b1 = b[32], a5 = a[5 * 32], b5 = b[5 * 32];      // dy = -2, +2: x3 x2 x1 x4
+    const uint4 b2 = b[2 * 32], b4 = b[4 * 32];                  // dy = -1, +1: ol x4 x3 er
+    const uint4 a3 = a[3 * 32], b3 = b[3 * 32];                  // centre row: ol x4 x3 er + em om
     // ring k -> (dx,dy): 0:(0,3) 1:(1,3) 2:(2,2) 3:(3,1) 4:(3,0) 5:(3,-1) 6:(2,-2) 7:(1,-3) 8:(0,-3) 9:(-1,-3)
     //                    10:(-2,-2) 11:(-3,-1) 12:(-3,0) 13:(-3,1) 14:(-2,2) 15:(-1,3)
     // pair A = pixels (c, c+2): offset dx -> -3:ol -2:x3 -1:x1 0:em 1:om 2:x2 3:x4
     // pair B = pixels (c+1, c+3):          -3:x3 -2:x1 -1:em 0:om 1:x2 2:x4 3:er
-    const uint32_t PA[16] = {p3.em, p3.om, p2.x2, p1.x4, z0.x4, m1.x4, m2.x2, m3.om,
-                             m3.em, m3.x1, m2.x3, m1.ol, z0.ol, p1.ol, p2.x3, p3.x1};
-    const uint32_t PB[16] = {p3.om, p3.x2, p2.x4, p1.er, z0.er, m1.er, m2.x4, m3.x2,
-                             m3.om, m3.em, m2.x1, m1.x3, z0.x3, p1.x3, p2.x1, p3.em};
-    const uint32_t tA = fast_score_pair(PA, z0.em);
-    const uint32_t tB = fast_score_pair(PB, z0.om);
+    // uint4 fields: PA = (x: x1, y: em, z: om, w: x2), PB = (x: ol, y: x4, z: x3, w: er)
+    const uint32_t PAr[16] = {a6.y, a6.z, a5.w, b4.y, b3.y, b2.y, a1.w, a0.z,
+                              a0.y, a0.x, b1.z, b2.x, b3.x, b4.x, b5.z, a6.x};
+    const uint32_t PBr[16] = {a6.z, a6.w, b5.y, b4.w, b3.w, b2.w, b1.y, a0.w,
+                              a0.z, a0.y, a1.x, b2.z, b3.z, b4.z, a5.x, a6.y};
+    const uint32_t tA = fast_score_pair(PAr, a3.y);
+    const uint32_t tB = fast_score_pair(PBr, a3.z);
     // lanes hold score + 257; the plane stores max(0, score + 1 - minTh): 0 <=> not a corner at minTh
     const uint32_t D = 0x01000100u + (uint32_t)minTh * 0x00010001u;
     const uint32_t uA = __vmaxu2(tA, D) - D, uB = __vmaxu2(tB, D) - D;
@@ -162,9 +167,12 @@ __host__ __device__ inline size_t pyr_smem_U(int srcRows) {
     const size_t hs = (size_t)TROWS * TW * 2, hq = (size_t)srcRows * HQS * 2;
     return ((hs > hq ? hs : hq) + 15) & ~(size_t)15;
 }
+__host__ __device__ inline size_t pyr_smem_planes() { return (size_t)2 * TROWS * 32 * sizeof(uint4); }     // PA + PB
 __host__ __device__ inline size_t pyr_smem_bytes(bool level0, int srcRows, int srcCols) {
-    if (level0) return pyr_smem_T() + pyr_smem_U(0);
-    return pyr_smem_T() + pyr_smem_taps() + pyr_smem_U(srcRows) + (size_t)srcRows * srcCols + 16;   // +16: S[o0 + 1] of the last column
+    if (level0) return pyr_smem_T() + pyr_smem_U(0) + pyr_smem_planes();
+    const size_t stage = (size_t)srcRows * srcCols + 16;            // +16: S[o0 + 1] of the last column
+    const size_t tail = stage > pyr_smem_planes() ? stage : pyr_smem_planes();   // the planes reuse the source staging
+    return pyr_smem_T() + pyr_smem_taps() + pyr_smem_U(srcRows) + tail;
 }
 
 template <bool LEVEL0>
@@ -177,9 +185,11 @@ __global__ void __launch_bounds__(PYR_THREADS) pyr_level_kernel(PyrArgs a) {
     const int w = a.w, h = a.h;
     const uint8_t* src = a.src + (size_t)frame * a.srcFrameStride;
     unsigned short* Hs;                                  // TROWS x TW blur row sums, [group][A.lo A.hi B.lo B.hi]
+    uint4* PA;                                           // TROWS x 32 pair planes (see fast_score4); PB = PA + TROWS * 32
 
     if (LEVEL0) {
         Hs = (unsigned short*)(smem + pyr_smem_T());
+        PA = (uint4*)(smem + pyr_smem_T() + pyr_smem_U(0));
         // level 0 is the caller's image: copy with REFLECT_101 halo (copyMakeBorder, :1372); byte b of a T row is
         // column x0 - 4 + b.  Aligned interior words go as one 32-bit load.
         for (int i = tid; i < TROWS * (TBYTES / 4); i += PYR_THREADS) {
@@ -212,6 +222,7 @@ __global__ void __launch_bounds__(PYR_THREADS) pyr_level_kernel(PyrArgs a) {
         unsigned short* Hq = (unsigned short*)U;         // staged source rows after the horizontal pass (h >> 4)
         Hs = (unsigned short*)U;                         // reused once T is complete
         uint8_t* S = U + pyr_smem_U(a.srcTileRows);      // staged source rows
+        PA = (uint4*)S;                                  // reused once the horizontal pass has consumed S
         // source rows/columns this tile touches
         const int ylo = max(0, y0 - HALO), yhi = min(h - 1, y0 + TH + HALO - 1);
         const int xlo = max(0, x0 - HALO), xhi = min(w - 1, x0 + TW + HALO - 1);
@@ -293,15 +304,20 @@ __global__ void __launch_bounds__(PYR_THREADS) pyr_level_kernel(PyrArgs a) {
         }
     }
 
-    // ---- horizontal blur sums: one warp per T row, one 4-pixel group per lane ----
+    // ---- row pass: one warp per T row, one 4-pixel group per lane: split the row into its stride-2 pixel pairs
+    //      (kept in the pair planes for FAST) and form the horizontal blur sums ----
+    uint4* PB = PA + TROWS * 32;
     for (int r = wid; r < TROWS; r += PYR_THREADS / 32) {
         const RowPairs p = row_pairs((const uint32_t*)(T + r * TS) + lane);
+        PA[r * 32 + lane] = make_uint4(p.x1, p.em, p.om, p.x2);
+        PB[r * 32 + lane] = make_uint4(p.ol, p.x4, p.x3, p.er);
         uint32_t A, B;
         hblur4(p, A, B);
         *(uint2*)(Hs + r * TW + 4 * lane) = make_uint2(A, B);
     }
+    __syncthreads();      // planes and Hs complete
 
-    // ---- FAST score: warp `wid` owns tile rows 4*wid..4*wid+3, lane = 4-pixel group (reads T only) ----
+    // ---- FAST score: warp `wid` owns tile rows 4*wid..4*wid+3, lane = 4-pixel group ----
     const int gx = x0 + 4 * lane;                        // level column of the group's first pixel
 #pragma unroll 1
     for (int k = 0; k < 4; k++) {
@@ -309,7 +325,7 @@ __global__ void __launch_bounds__(PYR_THREADS) pyr_level_kernel(PyrArgs a) {
         if (y >= h || gx >= w) continue;
         uint32_t s = 0;
         if (y >= ORB_EDGE && y < h - ORB_EDGE && gx + 3 >= ORB_EDGE && gx < w - ORB_EDGE) {
-            s = fast_score4(T, r, lane, a.minTh);
+            s = fast_score4(PA, PB, r, lane, a.minTh);
             if (gx < ORB_EDGE || gx + 3 >= w - ORB_EDGE) {           // group straddles the detection area
                 uint32_t m = 0;
 #pragma unroll
@@ -320,7 +336,6 @@ __global__ void __launch_bounds__(PYR_THREADS) pyr_level_kernel(PyrArgs a) {
         }
         *(uint32_t*)(a.score + (size_t)frame * a.planeFrameStride + (size_t)y * a.pitch + ORB_XPAD + gx) = s;
     }
-    __syncthreads();      // Hs complete
 
     // ---- vertical blur pass: warp `wid` owns tile rows 4*wid..4*wid+3, sliding 7-row window in registers ----
     {
