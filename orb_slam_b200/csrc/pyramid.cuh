@@ -160,19 +160,20 @@ struct PyrArgs {
     int* err;                    // device error flag
 };
 
-// shared memory carve-up (bytes); level 0 uses only T and U
+// shared memory carve-up (bytes).  T is live from the resize to the row pass; everything else lives in one region R
+// behind it that is used twice: [tap tables | Hq | staged source rows] while T is being built, then
+// [Hs | pair planes PA, PB] once T is complete.  54 KB per CTA at every level -> four CTAs per SM.
 __host__ __device__ inline size_t pyr_smem_T() { return (size_t)TROWS * TS; }
 __host__ __device__ inline size_t pyr_smem_taps() { return (size_t)TBYTES * sizeof(TapX) + 40 * sizeof(TapX); }
-__host__ __device__ inline size_t pyr_smem_U(int srcRows) {
-    const size_t hs = (size_t)TROWS * TW * 2, hq = (size_t)srcRows * HQS * 2;
-    return ((hs > hq ? hs : hq) + 15) & ~(size_t)15;
-}
+__host__ __device__ inline size_t pyr_smem_Hs() { return (size_t)TROWS * TW * 2; }
+__host__ __device__ inline size_t pyr_smem_Hq(int srcRows) { return (((size_t)srcRows * HQS * 2) + 15) & ~(size_t)15; }
 __host__ __device__ inline size_t pyr_smem_planes() { return (size_t)2 * TROWS * 32 * sizeof(uint4); }     // PA + PB
 __host__ __device__ inline size_t pyr_smem_bytes(bool level0, int srcRows, int srcCols) {
-    if (level0) return pyr_smem_T() + pyr_smem_U(0) + pyr_smem_planes();
+    const size_t late = pyr_smem_Hs() + pyr_smem_planes();
+    if (level0) return pyr_smem_T() + late;
     const size_t stage = (size_t)srcRows * srcCols + 16;            // +16: S[o0 + 1] of the last column
-    const size_t tail = stage > pyr_smem_planes() ? stage : pyr_smem_planes();   // the planes reuse the source staging
-    return pyr_smem_T() + pyr_smem_taps() + pyr_smem_U(srcRows) + tail;
+    const size_t early = pyr_smem_taps() + pyr_smem_Hq(srcRows) + stage;
+    return pyr_smem_T() + (early > late ? early : late);
 }
 
 template <bool LEVEL0>
@@ -187,9 +188,9 @@ __global__ void __launch_bounds__(PYR_THREADS) pyr_level_kernel(PyrArgs a) {
     unsigned short* Hs;                                  // TROWS x TW blur row sums, [group][A.lo A.hi B.lo B.hi]
     uint4* PA;                                           // TROWS x 32 pair planes (see fast_score4); PB = PA + TROWS * 32
 
+    Hs = (unsigned short*)(smem + pyr_smem_T());
+    PA = (uint4*)(smem + pyr_smem_T() + pyr_smem_Hs());
     if (LEVEL0) {
-        Hs = (unsigned short*)(smem + pyr_smem_T());
-        PA = (uint4*)(smem + pyr_smem_T() + pyr_smem_U(0));
         // level 0 is the caller's image: copy with REFLECT_101 halo (copyMakeBorder, :1372); byte b of a T row is
         // column x0 - 4 + b.  Aligned interior words go as one 32-bit load.
         for (int i = tid; i < TROWS * (TBYTES / 4); i += PYR_THREADS) {
@@ -218,11 +219,8 @@ __global__ void __launch_bounds__(PYR_THREADS) pyr_level_kernel(PyrArgs a) {
     } else {
         TapX* tapx = (TapX*)(smem + pyr_smem_T());
         TapX* tapy = tapx + TBYTES;
-        uint8_t* U = smem + pyr_smem_T() + pyr_smem_taps();
-        unsigned short* Hq = (unsigned short*)U;         // staged source rows after the horizontal pass (h >> 4)
-        Hs = (unsigned short*)U;                         // reused once T is complete
-        uint8_t* S = U + pyr_smem_U(a.srcTileRows);      // staged source rows
-        PA = (uint4*)S;                                  // reused once the horizontal pass has consumed S
+        unsigned short* Hq = (unsigned short*)(smem + pyr_smem_T() + pyr_smem_taps());   // source rows after the horizontal pass (h >> 4)
+        uint8_t* S = (uint8_t*)Hq + pyr_smem_Hq(a.srcTileRows);                          // staged source rows
         // source rows/columns this tile touches
         const int ylo = max(0, y0 - HALO), yhi = min(h - 1, y0 + TH + HALO - 1);
         const int xlo = max(0, x0 - HALO), xhi = min(w - 1, x0 + TW + HALO - 1);
@@ -259,7 +257,9 @@ __global__ void __launch_bounds__(PYR_THREADS) pyr_level_kernel(PyrArgs a) {
         // Both passes: thread = (4-column group q, row slot); 34 groups x 7 slots = 238 active threads, so the
         // column taps of the horizontal pass are decoded once per thread and stay in registers.
         const int q = tid % (TBYTES / 4), slot = tid / (TBYTES / 4);
-        if (slot < 7) {
+        const bool live = slot < 7 && x0 - 4 + 4 * q < w + HALO;     // groups right of the image + halo are never read
+        const int tyEnd = min(TROWS, h + 2 * HALO - y0);             // T rows below the image + halo are never read
+        if (live) {
             // horizontal pass (HResizeLinear, int32): Hq[r][b] = (S[r][o0]*a0 + S[r][o0+1]*a1) >> 4.
             // o1 == o0 + 1 whenever a1 != 0 (the x taps collapse the weight, not the index, at the borders).
             int o[4], a0[4], a1[4];
@@ -277,9 +277,9 @@ __global__ void __launch_bounds__(PYR_THREADS) pyr_level_kernel(PyrArgs a) {
             }
         }
         __syncthreads();
-        if (slot < 7) {
+        if (live) {
             // vertical pass (VResizeLinear 8u): ((b0*H0)>>16) + ((b1*H1)>>16) + 2 >> 2; (b*lo16(u))>>16 == umulhi(u<<16, b)
-            for (int ty = slot; ty < TROWS; ty += 7) {
+            for (int ty = slot; ty < tyEnd; ty += 7) {
                 const uint2 tp = *(const uint2*)(tapy + ty);
                 const uint32_t b0 = tp.y & 0xffffu, b1 = tp.y >> 16;     // weights are in [0, 2048]
                 const uint2 u0 = *(const uint2*)(Hq + (tp.x & 0xffffu) * HQS + 4 * q);
@@ -307,7 +307,8 @@ __global__ void __launch_bounds__(PYR_THREADS) pyr_level_kernel(PyrArgs a) {
     // ---- row pass: one warp per T row, one 4-pixel group per lane: split the row into its stride-2 pixel pairs
     //      (kept in the pair planes for FAST) and form the horizontal blur sums ----
     uint4* PB = PA + TROWS * 32;
-    for (int r = wid; r < TROWS; r += PYR_THREADS / 32) {
+    const int rEnd = min(TROWS, h + 2 * HALO - y0);       // rows below the image + halo feed nothing that is stored
+    for (int r = wid; r < rEnd; r += PYR_THREADS / 32) {
         const RowPairs p = row_pairs((const uint32_t*)(T + r * TS) + lane);
         PA[r * 32 + lane] = make_uint4(p.x1, p.em, p.om, p.x2);
         PB[r * 32 + lane] = make_uint4(p.ol, p.x4, p.x3, p.er);
