@@ -49,131 +49,180 @@ __device__ __forceinline__ float fast_atan2_deg(float y, float x) {
 }
 
 constexpr int DP_ROWS = 2 * ORB_EDGE + 1;      // blurred patch: 39 rows, |offset| <= ceil(13*sqrt(2)) = 19
-constexpr int DP_WORDS = 11;                   // 39 bytes at any alignment fit in 11 aligned words
-constexpr int IP_ROWS = 2 * ORB_HALF_PATCH + 1;   // intensity-centroid patch: 31 rows
-constexpr int IP_WORDS = 9;                    // 31 bytes at any alignment fit in 9 aligned words
+constexpr int DP_VECS = 4;                     // 39 bytes starting anywhere inside a 16-byte vector fit in 4 vectors
+constexpr int DP_SV = 5;                       // staged row stride in vectors: 80 bytes spreads the rows over all banks
+constexpr int DP_STRIDE = DP_SV * 16;
+constexpr int IP_ROWS = 2 * ORB_HALF_PATCH + 1;   // intensity-centroid disc: 31 rows
+constexpr int IP_VECS = 3;                     // 31 bytes starting anywhere inside a 16-byte vector fit in 3 vectors
+constexpr int DESC_KPW = 4;                    // keypoint slots per warp
+constexpr int DESC_SLOTS_PER_CTA = 8 * DESC_KPW;
 
 __device__ float4 g_pattern4[256];             // bit_pattern_31_ as [pair k][descriptor byte] -> (x0, y0, x1, y1) of test 8*byte + k
+// IC_Angle weights of disc row v = r - 15 (r = 0..30; row 31 is all zero), byte i <-> u = i - 15:
+// [r][0..1] = 1 inside the disc (|u| <= umax[|v|]), [r][2..3] = u + 15 inside the disc
+__device__ uint4 g_icw[32][4];
 
-__global__ void __launch_bounds__(256) describe_kernel(DescArgs a) {
-    // Both patches of a keypoint are staged in shared memory with aligned, coalesced 32-bit loads (all in flight at
-    // once); the 961 moment reads and 512 rotated-BRIEF gathers then hit shared memory instead of L1/L2.
-    __shared__ float4 s_pat[256];
-    __shared__ uint32_t s_blur[8][DP_ROWS * DP_WORDS];
-    __shared__ uint32_t s_img[8][IP_ROWS * IP_WORDS];
-    s_pat[threadIdx.x] = g_pattern4[threadIdx.x];        // blockDim.x == 256
-    __syncthreads();
-    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-    const int slot = blockIdx.x * (blockDim.x >> 5) + wid;
-    const int frame = blockIdx.y;
-    if (slot >= a.selTotal) return;
-    int l = 0;
-    while (slot >= a.selOff[l + 1]) l++;
-    const int i = slot - a.selOff[l];
-    const int* cnt = a.selCount + frame * a.nlevels;
-    if (slot == 0 && lane == 0) {
-        int n = 0;
-        for (int k = 0; k < a.nlevels; k++) n += cnt[k];
-        a.nOut[frame] = n;
-    }
-    if (i >= cnt[l]) return;
-    int outIdx = i;
-    for (int k = 0; k < l; k++) outIdx += cnt[k];
-    if (outIdx >= a.cap) return;                      // host reports ORBX_E_CAPACITY from nOut
-    const uint32_t c = a.sel[(size_t)frame * a.selTotal + slot];
-    const int x = (int)(c & 0xfff) + ORB_BORDER_MIN, y = (int)((c >> 12) & 0xfff) + ORB_BORDER_MIN;   // :1021-1022
-    const int pitch = a.pitch[l];
-
-    // ---- stage the patches (rows start 16-byte aligned at interior column 0: alignment = column & 3)
-    const int bx0 = (x - ORB_EDGE) & ~3, ix0 = (x - ORB_HALF_PATCH) & ~3;     // both >= 0: keypoints sit >= 19 px inside
-    {
-        const uint8_t* bl = a.blur + (size_t)frame * a.planeFrameStride + a.planeOff[l] + (size_t)(y - ORB_EDGE) * pitch + ORB_XPAD + bx0;
-        const uint8_t* im = a.pyr + (size_t)frame * a.pyrFrameStride + a.pyrOff[l] + (size_t)(ORB_EDGE + y - ORB_HALF_PATCH) * pitch + ORB_XPAD + ix0;
-        constexpr int NB = (DP_ROWS * DP_WORDS + 31) / 32, NI = (IP_ROWS * IP_WORDS + 31) / 32;
-        uint32_t vb[NB], vi[NI];
-#pragma unroll
-        for (int j = 0; j < NB; j++) {                   // all loads first: NB + NI independent requests in flight per lane
-            const int t = lane + 32 * j, r = t / DP_WORDS, wv = t - r * DP_WORDS;
-            vb[j] = t < DP_ROWS * DP_WORDS ? __ldg((const uint32_t*)(bl + (size_t)r * pitch) + wv) : 0u;
-        }
-#pragma unroll
-        for (int j = 0; j < NI; j++) {
-            const int t = lane + 32 * j, r = t / IP_WORDS, wv = t - r * IP_WORDS;
-            vi[j] = t < IP_ROWS * IP_WORDS ? __ldg((const uint32_t*)(im + (size_t)r * pitch) + wv) : 0u;
-        }
-#pragma unroll
-        for (int j = 0; j < NB; j++) { const int t = lane + 32 * j; if (t < DP_ROWS * DP_WORDS) s_blur[wid][t] = vb[j]; }
-#pragma unroll
-        for (int j = 0; j < NI; j++) { const int t = lane + 32 * j; if (t < IP_ROWS * IP_WORDS) s_img[wid][t] = vi[j]; }
-    }
-    __syncwarp();
-
-    // ---- IC_Angle: lanes 0..30 own column u = lane-15 of the disc
-    int m10 = 0, m01 = 0;
-    const int u = lane - ORB_HALF_PATCH;
-    if (lane < 31) {
-        const uint8_t* img = (const uint8_t*)s_img[wid] + (x - ORB_HALF_PATCH - ix0) + lane;   // row 0 = v = -15
-        const int au = abs(u);
-        int colsum = 0;
-#pragma unroll
-        for (int v = -ORB_HALF_PATCH; v <= ORB_HALF_PATCH; v++) {
-            if (au <= c_umax[abs(v)]) {
-                const int val = img[(v + ORB_HALF_PATCH) * (IP_WORDS * 4)];
-                colsum += val;
-                m01 += v * val;
-            }
-        }
-        m10 = u * colsum;
-    }
-#pragma unroll
-    for (int d = 16; d > 0; d >>= 1) {
-        m10 += __shfl_xor_sync(0xffffffffu, m10, d);
-        m01 += __shfl_xor_sync(0xffffffffu, m01, d);
-    }
-    const float angle = fast_atan2_deg((float)m01, (float)m10);
-
-    // ---- rotated BRIEF: lane i produces descriptor byte i (16 pattern points)
-    float ca = 0.f, sb = 0.f;
-    if (lane == 0) {
-        const float rad = __fmul_rn(angle, (float)(3.1415926535897932384626433832795 / 180.f));   // factorPI, :131
-        double s_, c_;
-        sincos((double)rad, &s_, &c_);       // correctly-rounded stand-in for glibc cosf/sinf (:148)
-        ca = (float)c_; sb = (float)s_;
-    }
-    ca = __shfl_sync(0xffffffffu, ca, 0);
-    sb = __shfl_sync(0xffffffffu, sb, 0);
-    const uint8_t* bl = (const uint8_t*)s_blur[wid] + ORB_EDGE * (DP_WORDS * 4) + (x - bx0);     // patch centre
-    int val = 0;
+// rowsum = sum of the row's disc pixels, su = sum of (u + 15) * pixel: 16 DP4A over the 32 bytes that start `sh/8` bytes
+// into word WQ of the 12 loaded words
+template <int WQ>
+__device__ __forceinline__ void ic_row(const uint32_t (&W)[12], unsigned sh, const uint4* __restrict__ wrow, uint32_t& rowsum, uint32_t& su) {
+    const uint4 o0 = wrow[0], o1 = wrow[1], u0 = wrow[2], u1 = wrow[3];
+    const uint32_t one[8] = {o0.x, o0.y, o0.z, o0.w, o1.x, o1.y, o1.z, o1.w};
+    const uint32_t uw[8] = {u0.x, u0.y, u0.z, u0.w, u1.x, u1.y, u1.z, u1.w};
 #pragma unroll
     for (int k = 0; k < 8; k++) {
-        // test pair k of byte `lane`: one 128-bit shared load (x0, y0, x1, y1)
-        const float4 pw = s_pat[k * 32 + lane];
-        const float x0 = pw.x, y0 = pw.y, x1 = pw.z, y1 = pw.w;
-        const int r0 = __float2int_rn(__fadd_rn(__fmul_rn(x0, sb), __fmul_rn(y0, ca)));      // cvRound(x*b + y*a)
-        const int q0 = __float2int_rn(__fsub_rn(__fmul_rn(x0, ca), __fmul_rn(y0, sb)));      // cvRound(x*a - y*b)
-        const int r1 = __float2int_rn(__fadd_rn(__fmul_rn(x1, sb), __fmul_rn(y1, ca)));
-        const int q1 = __float2int_rn(__fsub_rn(__fmul_rn(x1, ca), __fmul_rn(y1, sb)));
-        const int t0 = bl[r0 * (DP_WORDS * 4) + q0], t1 = bl[r1 * (DP_WORDS * 4) + q1];
-        val |= (t0 < t1) << k;
+        const uint32_t d = __funnelshift_r(W[WQ + k], W[WQ + k + 1], sh);
+        rowsum = __dp4a(d, one[k], rowsum);
+        su = __dp4a(d, uw[k], su);
     }
-    const size_t o = (size_t)frame * a.cap + outIdx;
-    a.desc[o * 32 + lane] = (uint8_t)val;
-    if (lane < 7) {
-        const float sc = a.scale[l];
-        float f;
-        int iv = 0;
-        bool isInt = false;
-        switch (lane) {
-            case 0: f = l ? __fmul_rn((float)x, sc) : (float)x; break;     // keypoint->pt *= scale, :1322-1329
-            case 1: f = l ? __fmul_rn((float)y, sc) : (float)y; break;
-            case 2: f = a.patchSize[l]; break;
-            case 3: f = angle; break;
-            case 4: f = (float)(c >> 24); break;
-            case 5: iv = l; isInt = true; f = 0; break;
-            default: iv = -1; isInt = true; f = 0; break;
+}
+
+__global__ void __launch_bounds__(256) describe_kernel(DescArgs a) {
+    // A warp walks DESC_KPW consecutive selection slots.  Both patches of a keypoint are staged in shared memory with
+    // aligned, coalesced 128-bit loads (all in flight at once): the blurred patch for the 512 rotated-BRIEF gathers,
+    // the intensity-centroid disc so that every lane can pick up one disc row as three vectors.
+    __shared__ float4 s_pat[256];
+    __shared__ uint4 s_icw[32 * 4];
+    __shared__ uint4 s_blur[8][DP_ROWS * DP_SV];
+    __shared__ uint4 s_img[8][32 * IP_VECS];
+    s_pat[threadIdx.x] = g_pattern4[threadIdx.x];        // blockDim.x == 256
+    if (threadIdx.x < 128) s_icw[threadIdx.x] = ((const uint4*)g_icw)[threadIdx.x];
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    const int frame = blockIdx.y;
+    // level counts: lane k fetches count k
+    const int myCnt = lane < a.nlevels ? a.selCount[frame * a.nlevels + lane] : 0;
+    if (blockIdx.x == 0 && wid == 0) {
+        int all = myCnt;
+#pragma unroll
+        for (int d = 16; d > 0; d >>= 1) all += __shfl_xor_sync(0xffffffffu, all, d);
+        if (lane == 0) a.nOut[frame] = all;
+    }
+    if (lane >= 31) {                                    // row 31 of the disc rows does not exist: zero it once
+        s_img[wid][31 * IP_VECS] = make_uint4(0, 0, 0, 0); s_img[wid][31 * IP_VECS + 1] = make_uint4(0, 0, 0, 0);
+        s_img[wid][31 * IP_VECS + 2] = make_uint4(0, 0, 0, 0);
+    }
+    __syncthreads();
+    const int slot0 = (blockIdx.x * 8 + wid) * DESC_KPW;
+    // lane `it` holds the selection word of slot slot0 + it (fetched before the first keypoint needs it)
+    const uint32_t myC = (lane < DESC_KPW && slot0 + lane < a.selTotal) ? a.sel[(size_t)frame * a.selTotal + slot0 + lane] : 0u;
+#pragma unroll 1
+    for (int it = 0; it < DESC_KPW; it++) {
+        const int slot = slot0 + it;
+        if (slot >= a.selTotal) break;                   // warp-uniform
+        int l = 0;
+        while (slot >= a.selOff[l + 1]) l++;
+        const int i = slot - a.selOff[l];
+        if (i >= __shfl_sync(0xffffffffu, myCnt, l)) continue;
+        int before = lane < l ? myCnt : 0;
+#pragma unroll
+        for (int d = 16; d > 0; d >>= 1) before += __shfl_xor_sync(0xffffffffu, before, d);
+        const int outIdx = i + before;
+        if (outIdx >= a.cap) continue;                   // host reports ORBX_E_CAPACITY from nOut
+        const uint32_t c = __shfl_sync(0xffffffffu, myC, it);
+        const int x = (int)(c & 0xfff) + ORB_BORDER_MIN, y = (int)((c >> 12) & 0xfff) + ORB_BORDER_MIN;   // :1021-1022
+        const int pitch = a.pitch[l];
+
+        // ---- loads: rows start 16-byte aligned at interior column 0 and every row has >= 32 bytes behind column w,
+        //      so whole vectors around the patch can be read (keypoints sit >= 19 px inside the level)
+        const int bx0 = (x - ORB_EDGE) & ~15, ix0 = (x - ORB_HALF_PATCH) & ~15;
+        constexpr int NB = (DP_ROWS * DP_VECS + 31) / 32, NI = (IP_ROWS * IP_VECS + 31) / 32;
+        uint4 vb[NB], vi[NI];
+        {
+            const uint8_t* bl = a.blur + (size_t)frame * a.planeFrameStride + a.planeOff[l] + (size_t)(y - ORB_EDGE) * pitch + ORB_XPAD + bx0;
+            const uint8_t* p = bl + (size_t)(lane >> 2) * pitch + 16 * (lane & 3);
+#pragma unroll
+            for (int j = 0; j < NB; j++) {               // lane t = row t/4, vector t%4; 8 rows per step
+                vb[j] = (lane + 32 * j < DP_ROWS * DP_VECS) ? __ldg((const uint4*)p) : make_uint4(0, 0, 0, 0);
+                p += (size_t)8 * pitch;
+            }
+            const uint8_t* im = a.pyr + (size_t)frame * a.pyrFrameStride + a.pyrOff[l] + (size_t)(ORB_EDGE + y - ORB_HALF_PATCH) * pitch + ORB_XPAD + ix0;
+#pragma unroll
+            for (int j = 0; j < NI; j++) {               // lane t = row t/3, vector t%3
+                const int t = lane + 32 * j, r = t / IP_VECS, v = t - r * IP_VECS;
+                vi[j] = t < IP_ROWS * IP_VECS ? __ldg((const uint4*)(im + (size_t)r * pitch) + v) : make_uint4(0, 0, 0, 0);
+            }
         }
-        int* dst = (int*)(a.kps + o) + lane;
-        *dst = isInt ? iv : __float_as_int(f);
+#pragma unroll
+        for (int j = 0; j < NB; j++) { const int t = lane + 32 * j; if (t < DP_ROWS * DP_VECS) s_blur[wid][(t >> 2) * DP_SV + (t & 3)] = vb[j]; }
+#pragma unroll
+        for (int j = 0; j < NI; j++) { const int t = lane + 32 * j; if (t < IP_ROWS * IP_VECS) s_img[wid][t] = vi[j]; }
+        __syncwarp();
+
+        // ---- IC_Angle (:84-128): lane = disc row v + 15; m01 = sum v * rowsum(v), m10 = sum over rows of sum u * pixel
+        int m10, m01;
+        {
+            uint32_t W[12];
+            const uint4 i0 = s_img[wid][lane * IP_VECS], i1 = s_img[wid][lane * IP_VECS + 1], i2 = s_img[wid][lane * IP_VECS + 2];
+            W[0] = i0.x; W[1] = i0.y; W[2] = i0.z; W[3] = i0.w; W[4] = i1.x; W[5] = i1.y; W[6] = i1.z; W[7] = i1.w;
+            W[8] = i2.x; W[9] = i2.y; W[10] = i2.z; W[11] = i2.w;
+            const int off = (x - ORB_HALF_PATCH) - ix0;     // 0..15, warp-uniform
+            const unsigned sh = 8u * (unsigned)(off & 3);
+            const uint4* wrow = s_icw + lane * 4;
+            uint32_t rowsum = 0, su = 0;
+            switch (off >> 2) {
+                case 0: ic_row<0>(W, sh, wrow, rowsum, su); break;
+                case 1: ic_row<1>(W, sh, wrow, rowsum, su); break;
+                case 2: ic_row<2>(W, sh, wrow, rowsum, su); break;
+                default: ic_row<3>(W, sh, wrow, rowsum, su); break;
+            }
+            m10 = (int)su - ORB_HALF_PATCH * (int)rowsum;
+            m01 = (lane - ORB_HALF_PATCH) * (int)rowsum;
+        }
+#pragma unroll
+        for (int d = 16; d > 0; d >>= 1) {
+            m10 += __shfl_xor_sync(0xffffffffu, m10, d);
+            m01 += __shfl_xor_sync(0xffffffffu, m01, d);
+        }
+        const float angle = fast_atan2_deg((float)m01, (float)m10);
+
+        // ---- rotated BRIEF: lane i produces descriptor byte i (16 pattern points)
+        float ca = 0.f, sb = 0.f;
+        if (lane == 0) {
+            const float rad = __fmul_rn(angle, (float)(3.1415926535897932384626433832795 / 180.f));   // factorPI, :131
+            double s_, c_;
+            sincos((double)rad, &s_, &c_);       // correctly-rounded stand-in for glibc cosf/sinf (:148)
+            ca = (float)c_; sb = (float)s_;
+        }
+        ca = __shfl_sync(0xffffffffu, ca, 0);
+        sb = __shfl_sync(0xffffffffu, sb, 0);
+        // patch centre, minus the integer image of the rounding constant in both index terms
+        const uint8_t* bl = (const uint8_t*)s_blur[wid] + ORB_EDGE * DP_STRIDE + (x - bx0) - (ptrdiff_t)0x4B400000 * (DP_STRIDE + 1);
+        int val = 0;
+#pragma unroll
+        for (int k = 0; k < 8; k++) {
+            // test pair k of byte `lane`: one 128-bit shared load (x0, y0, x1, y1)
+            const float4 pw = s_pat[k * 32 + lane];
+            const float x0 = pw.x, y0 = pw.y, x1 = pw.z, y1 = pw.w;
+            // cvRound(x*b + y*a), cvRound(x*a - y*b) (:166-168): adding 1.5 * 2^23 leaves the round-to-nearest-even integer
+            // in the low mantissa bits (|value| < 2^22), so the conversion stays on the FP32 pipe
+            const float MAGIC = 12582912.0f;
+            const int r0 = __float_as_int(__fadd_rn(__fadd_rn(__fmul_rn(x0, sb), __fmul_rn(y0, ca)), MAGIC));
+            const int q0 = __float_as_int(__fadd_rn(__fsub_rn(__fmul_rn(x0, ca), __fmul_rn(y0, sb)), MAGIC));
+            const int r1 = __float_as_int(__fadd_rn(__fadd_rn(__fmul_rn(x1, sb), __fmul_rn(y1, ca)), MAGIC));
+            const int q1 = __float_as_int(__fadd_rn(__fsub_rn(__fmul_rn(x1, ca), __fmul_rn(y1, sb)), MAGIC));
+            const int t0 = bl[r0 * DP_STRIDE + q0], t1 = bl[r1 * DP_STRIDE + q1];
+            val |= (t0 < t1) << k;
+        }
+        __syncwarp();                                    // the staged patches may be overwritten by the next slot
+        const size_t o = (size_t)frame * a.cap + outIdx;
+        a.desc[o * 32 + lane] = (uint8_t)val;
+        if (lane < 7) {
+            const float sc = a.scale[l];
+            float f;
+            int iv = 0;
+            bool isInt = false;
+            switch (lane) {
+                case 0: f = l ? __fmul_rn((float)x, sc) : (float)x; break;     // keypoint->pt *= scale, :1322-1329
+                case 1: f = l ? __fmul_rn((float)y, sc) : (float)y; break;
+                case 2: f = a.patchSize[l]; break;
+                case 3: f = angle; break;
+                case 4: f = (float)(c >> 24); break;
+                case 5: iv = l; isInt = true; f = 0; break;
+                default: iv = -1; isInt = true; f = 0; break;
+            }
+            int* dst = (int*)(a.kps + o) + lane;
+            *dst = isInt ? iv : __float_as_int(f);
+        }
     }
 }
 

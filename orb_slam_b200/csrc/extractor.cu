@@ -402,7 +402,7 @@ static int enqueue_pipeline(orbx_extractor* e, int wi, const uint8_t* src, size_
         d.scale[l] = v.scale; d.patchSize[l] = v.patchSize;
     }
     d.selOff[g.nlevels] = g.selTotal;
-    describe_kernel<<<dim3((g.selTotal + 7) / 8, frames), 256, 0, st>>>(d);
+    describe_kernel<<<dim3((g.selTotal + DESC_SLOTS_PER_CTA - 1) / DESC_SLOTS_PER_CTA, frames), 256, 0, st>>>(d);
     launches++;
     if (evs) CK(cudaEventRecord(evs[5], st));
     e->launches += launches;
@@ -467,6 +467,19 @@ int orbx_create(orbx_t** out, int nfeatures, float scaleFactor, int nlevels, int
         rc = cudaMemcpyToSymbol(g_pattern4, pat4, sizeof(pat4));
     }
     if (rc == cudaSuccess) rc = cudaMemcpyToSymbol(c_umax, e->umax, sizeof(e->umax));
+    if (rc == cudaSuccess) {
+        // IC_Angle disc weights per row, see describe.cuh
+        static uint8_t icw[32][64];
+        memset(icw, 0, sizeof(icw));
+        for (int r = 0; r < 31; r++) {
+            const int v = r - ORB_HALF_PATCH, um = e->umax[v < 0 ? -v : v];
+            for (int i = 0; i < 31; i++) {
+                const int u = i - ORB_HALF_PATCH;
+                if ((u < 0 ? -u : u) <= um) { icw[r][i] = 1; icw[r][32 + i] = (uint8_t)(u + ORB_HALF_PATCH); }
+            }
+        }
+        rc = cudaMemcpyToSymbol(g_icw, icw, sizeof(icw));
+    }
     if (rc != cudaSuccess) { delete e; return (int)rc; }
     *out = e;
     return ORBX_OK;

@@ -262,18 +262,38 @@ __global__ void __launch_bounds__(PYR_THREADS) pyr_level_kernel(PyrArgs a) {
         if (live) {
             // horizontal pass (HResizeLinear, int32): Hq[r][b] = (S[r][o0]*a0 + S[r][o0+1]*a1) >> 4.
             // o1 == o0 + 1 whenever a1 != 0 (the x taps collapse the weight, not the index, at the borders).
-            int o[4], a0[4], a1[4];
+            // A group's four tap pairs lie within 8 consecutive source bytes (scale < 2): fetch that window as three
+            // aligned words + two funnel shifts, pick each (S[o], S[o+1]) pair with a per-thread constant PRMT selector
+            // and weight it with one DP2A.
+            int o[4];
+            uint32_t wt[4];
+            int base = 0x7fffffff;
 #pragma unroll
             for (int j = 0; j < 4; j++) {
                 const uint2 tp = *(const uint2*)(tapx + 4 * q + j);
-                o[j] = (int)(tp.x & 0xffffu); a0[j] = (int)(short)(tp.y & 0xffffu); a1[j] = (int)tp.y >> 16;
+                o[j] = (int)(tp.x & 0xffffu); wt[j] = tp.y;                 // a0 | a1 << 16
+                if (wt[j]) base = min(base, o[j]);
             }
-            for (int r = slot; r < nrows; r += 7) {
-                const uint8_t* Sr = S + r * scols;
-                int hh[4];
+            if (base == 0x7fffffff) base = 0;
+            uint32_t sel[4];
+            bool bad = false;
 #pragma unroll
-                for (int j = 0; j < 4; j++) hh[j] = (Sr[o[j]] * a0[j] + Sr[o[j] + 1] * a1[j]) >> 4;
-                *(uint2*)(Hq + r * HQS + 4 * q) = make_uint2((uint32_t)hh[0] | ((uint32_t)hh[1] << 16), (uint32_t)hh[2] | ((uint32_t)hh[3] << 16));
+            for (int j = 0; j < 4; j++) {
+                const int d = wt[j] ? o[j] - base : 0;
+                bad |= d > 6;
+                sel[j] = (uint32_t)d | ((uint32_t)(d + 1) << 4);
+            }
+            if (bad) atomicExch(a.err, 202);
+            const int wb = base >> 2;
+            const unsigned sh = 8u * (unsigned)(base & 3);
+            for (int r = slot; r < nrows; r += 7) {
+                const uint32_t* Sw = (const uint32_t*)(S + r * scols) + wb;
+                const uint32_t w0 = Sw[0], w1 = Sw[1], w2 = Sw[2];
+                const uint32_t X0 = __funnelshift_r(w0, w1, sh), X1 = __funnelshift_r(w1, w2, sh);
+                uint32_t hh[4];
+#pragma unroll
+                for (int j = 0; j < 4; j++) hh[j] = __dp2a_lo(wt[j], __byte_perm(X0, X1, sel[j]), 0u) >> 4;
+                *(uint2*)(Hq + r * HQS + 4 * q) = make_uint2(hh[0] | (hh[1] << 16), hh[2] | (hh[3] << 16));
             }
         }
         __syncthreads();
