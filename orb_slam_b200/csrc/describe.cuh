@@ -57,10 +57,18 @@ constexpr int IP_VECS = 3;                     // 31 bytes starting anywhere ins
 constexpr int DESC_KPW = 4;                    // keypoint slots per warp
 constexpr int DESC_SLOTS_PER_CTA = 8 * DESC_KPW;
 
-__device__ float4 g_pattern4[256];             // bit_pattern_31_ as [pair k][descriptor byte] -> (x0, y0, x1, y1) of test 8*byte + k
+__device__ uint32_t g_pattern_s8[256];         // bit_pattern_31_ as [pair k][descriptor byte] -> signed bytes (x0, y0, x1, y1) of test 8*byte + k
 // IC_Angle weights of disc row v = r - 15 (r = 0..30; row 31 is all zero), byte i <-> u = i - 15:
 // [r][0..1] = 1 inside the disc (|u| <= umax[|v|]), [r][2..3] = u + 15 inside the disc
 __device__ uint4 g_icw[32][4];
+
+// byte n of w sign-extended to 32 bits: PRMT with the sign-replicate selector bit (SEL = 0x8880 | n * 0x1111)
+template <unsigned SEL>
+__device__ __forceinline__ int sext_byte(uint32_t w) {
+    int r;
+    asm volatile("prmt.b32 %0, %1, %1, %2;" : "=r"(r) : "r"(w), "n"(SEL));     // volatile: keeps the 32 unpacked values out of loop-invariant registers
+    return r;
+}
 
 // rowsum = sum of the row's disc pixels, su = sum of (u + 15) * pixel: 16 DP4A over the 32 bytes that start `sh/8` bytes
 // into word WQ of the 12 loaded words
@@ -77,15 +85,13 @@ __device__ __forceinline__ void ic_row(const uint32_t (&W)[12], unsigned sh, con
     }
 }
 
-__global__ void __launch_bounds__(256) describe_kernel(DescArgs a) {
+__global__ void __launch_bounds__(256, 4) describe_kernel(DescArgs a) {
     // A warp walks DESC_KPW consecutive selection slots.  Both patches of a keypoint are staged in shared memory with
     // aligned, coalesced 128-bit loads (all in flight at once): the blurred patch for the 512 rotated-BRIEF gathers,
     // the intensity-centroid disc so that every lane can pick up one disc row as three vectors.
-    __shared__ float4 s_pat[256];
     __shared__ uint4 s_icw[32 * 4];
     __shared__ uint4 s_blur[8][DP_ROWS * DP_SV];
     __shared__ uint4 s_img[8][32 * IP_VECS];
-    s_pat[threadIdx.x] = g_pattern4[threadIdx.x];        // blockDim.x == 256
     if (threadIdx.x < 128) s_icw[threadIdx.x] = ((const uint4*)g_icw)[threadIdx.x];
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     const int frame = blockIdx.y;
@@ -103,6 +109,11 @@ __global__ void __launch_bounds__(256) describe_kernel(DescArgs a) {
     }
     __syncthreads();
     const int slot0 = (blockIdx.x * 8 + wid) * DESC_KPW;
+    const int brow = (lane >> 3) + 4 * ((lane >> 2) & 1);     // blurred-patch row (mod 8) this lane stages
+    // test pair k of descriptor byte `lane` as four signed bytes (x0, y0, x1, y1), kept in registers for all slots
+    uint32_t pat[8];
+#pragma unroll
+    for (int k = 0; k < 8; k++) pat[k] = g_pattern_s8[k * 32 + lane];
     // lane `it` holds the selection word of slot slot0 + it (fetched before the first keypoint needs it)
     const uint32_t myC = (lane < DESC_KPW && slot0 + lane < a.selTotal) ? a.sel[(size_t)frame * a.selTotal + slot0 + lane] : 0u;
 #pragma unroll 1
@@ -129,10 +140,12 @@ __global__ void __launch_bounds__(256) describe_kernel(DescArgs a) {
         uint4 vb[NB], vi[NI];
         {
             const uint8_t* bl = a.blur + (size_t)frame * a.planeFrameStride + a.planeOff[l] + (size_t)(y - ORB_EDGE) * pitch + ORB_XPAD + bx0;
-            const uint8_t* p = bl + (size_t)(lane >> 2) * pitch + 16 * (lane & 3);
+            // lane -> (row, vector): a quarter-warp holds rows r and r + 4, whose staged vectors (80-byte row stride) fall
+            // into disjoint banks, so the 128-bit shared stores below are conflict-free
+            const uint8_t* p = bl + (size_t)brow * pitch + 16 * (lane & 3);
 #pragma unroll
-            for (int j = 0; j < NB; j++) {               // lane t = row t/4, vector t%4; 8 rows per step
-                vb[j] = (lane + 32 * j < DP_ROWS * DP_VECS) ? __ldg((const uint4*)p) : make_uint4(0, 0, 0, 0);
+            for (int j = 0; j < NB; j++) {               // 8 rows per step
+                vb[j] = (brow + 8 * j < DP_ROWS) ? __ldg((const uint4*)p) : make_uint4(0, 0, 0, 0);
                 p += (size_t)8 * pitch;
             }
             const uint8_t* im = a.pyr + (size_t)frame * a.pyrFrameStride + a.pyrOff[l] + (size_t)(ORB_EDGE + y - ORB_HALF_PATCH) * pitch + ORB_XPAD + ix0;
@@ -143,7 +156,7 @@ __global__ void __launch_bounds__(256) describe_kernel(DescArgs a) {
             }
         }
 #pragma unroll
-        for (int j = 0; j < NB; j++) { const int t = lane + 32 * j; if (t < DP_ROWS * DP_VECS) s_blur[wid][(t >> 2) * DP_SV + (t & 3)] = vb[j]; }
+        for (int j = 0; j < NB; j++) if (brow + 8 * j < DP_ROWS) s_blur[wid][(brow + 8 * j) * DP_SV + (lane & 3)] = vb[j];
 #pragma unroll
         for (int j = 0; j < NI; j++) { const int t = lane + 32 * j; if (t < IP_ROWS * IP_VECS) s_img[wid][t] = vi[j]; }
         __syncwarp();
@@ -190,9 +203,9 @@ __global__ void __launch_bounds__(256) describe_kernel(DescArgs a) {
         int val = 0;
 #pragma unroll
         for (int k = 0; k < 8; k++) {
-            // test pair k of byte `lane`: one 128-bit shared load (x0, y0, x1, y1)
-            const float4 pw = s_pat[k * 32 + lane];
-            const float x0 = pw.x, y0 = pw.y, x1 = pw.z, y1 = pw.w;
+            // sign-extending PRMT + int->float per coordinate (|coordinate| <= 15)
+            const float x0 = (float)sext_byte<0x8880>(pat[k]), y0 = (float)sext_byte<0x9991>(pat[k]);
+            const float x1 = (float)sext_byte<0xaaa2>(pat[k]), y1 = (float)sext_byte<0xbbb3>(pat[k]);
             // cvRound(x*b + y*a), cvRound(x*a - y*b) (:166-168): adding 1.5 * 2^23 leaves the round-to-nearest-even integer
             // in the low mantissa bits (|value| < 2^22), so the conversion stays on the FP32 pipe
             const float MAGIC = 12582912.0f;

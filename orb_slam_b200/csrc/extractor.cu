@@ -458,13 +458,13 @@ int orbx_create(orbx_t** out, int nfeatures, float scaleFactor, int nlevels, int
     if (rc == cudaSuccess) rc = cudaMemcpyToSymbol(c_pattern, orb_pattern_31, 1024);
     if (rc == cudaSuccess) {
         // [pair k][descriptor byte i] -> (x0, y0, x1, y1) of test 8*i + k, as one word (computeOrbDescriptor, :166-189)
-        static float4 pat4[256];
+        static uint32_t pat4[256];
         const signed char* pt = (const signed char*)orb_pattern_31;
         for (int t = 0; t < 256; t++) {
-            const signed char* q = pt + (t & 31) * 32 + (t >> 5) * 4;
-            pat4[t] = make_float4((float)q[0], (float)q[1], (float)q[2], (float)q[3]);
+            const unsigned char* q = (const unsigned char*)(pt + (t & 31) * 32 + (t >> 5) * 4);
+            pat4[t] = (uint32_t)q[0] | ((uint32_t)q[1] << 8) | ((uint32_t)q[2] << 16) | ((uint32_t)q[3] << 24);
         }
-        rc = cudaMemcpyToSymbol(g_pattern4, pat4, sizeof(pat4));
+        rc = cudaMemcpyToSymbol(g_pattern_s8, pat4, sizeof(pat4));
     }
     if (rc == cudaSuccess) rc = cudaMemcpyToSymbol(c_umax, e->umax, sizeof(e->umax));
     if (rc == cudaSuccess) {
