@@ -206,7 +206,7 @@ static int build_geometry(orbx_extractor* e, int width, int height, FrameGeom& g
         if (2 * v.depth + v.iniBits > 32) return ORBX_E_UNSUPPORTED;
         v.maxSel = std::max(v.N + 3, 4 * v.nIni);
         v.selOff = selOff; selOff += v.maxSel;
-        nodeNeed = std::max(nodeNeed, v.maxSel + 4);
+        nodeNeed = std::max(nodeNeed, std::max(v.maxSel + 4, (v.nCols * v.nRows + 31) / 32));   // (the node arrays also hold the per-32-cell chunk totals)
         v.scale = e->sf[l];
         v.patchSize = (float)(int)(31 * e->sf[l]);                       // :1013
     }

@@ -21,7 +21,7 @@
 
 namespace orbx {
 
-constexpr int QT_THREADS = 256;
+constexpr int QT_THREADS = 128;
 constexpr int QT_WARPS = QT_THREADS / 32;
 
 struct QtArgs {
@@ -50,26 +50,32 @@ struct QtArgs {
     float hX[ORB_MAX_LEVELS];
 };
 
-// exclusive scan of arr[0..n) in shared memory by the whole block; returns the total
+// exclusive scan of arr[0..n) in shared memory by the whole block; returns the total.  Every warp scans one contiguous
+// segment 32 elements at a time (conflict-free, carry in a register); the warp totals are exchanged once.
 __device__ int block_scan_excl(int* arr, int n, int* warpTmp) {
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
-    const int per = (n + QT_THREADS - 1) / QT_THREADS;
-    const int b = min(tid * per, n), e = min(b + per, n);
-    int s = 0;
-    for (int i = b; i < e; i++) s += arr[i];
-    int inc = s;
+    const int seg = (((n + QT_WARPS - 1) / QT_WARPS) + 31) & ~31;
+    const int b = min(wid * seg, n), e = min(b + seg, n);
+    int carry = 0;
+    for (int i0 = b; i0 < e; i0 += 32) {
+        const int i = i0 + lane;
+        const int v = i < e ? arr[i] : 0;
+        int inc = v;
 #pragma unroll
-    for (int d = 1; d < 32; d <<= 1) {
-        const int t = __shfl_up_sync(0xffffffffu, inc, d);
-        if (lane >= d) inc += t;
+        for (int d = 1; d < 32; d <<= 1) {
+            const int t = __shfl_up_sync(0xffffffffu, inc, d);
+            if (lane >= d) inc += t;
+        }
+        if (i < e) arr[i] = carry + inc - v;
+        carry += __shfl_sync(0xffffffffu, inc, 31);
     }
     __syncthreads();                       // protects warpTmp reuse across calls
-    if (lane == 31) warpTmp[wid] = inc;
+    if (lane == 0) warpTmp[wid] = carry;
     __syncthreads();
     int base = 0, total = 0;
+#pragma unroll
     for (int k = 0; k < QT_WARPS; k++) { const int v = warpTmp[k]; if (k < wid) base += v; total += v; }
-    int run = base + inc - s;
-    for (int i = b; i < e; i++) { const int v = arr[i]; arr[i] = run; run += v; }
+    if (base) for (int i = b + lane; i < e; i += 32) arr[i] += base;
     __syncthreads();
     return total;
 }

@@ -70,41 +70,54 @@ __global__ void __launch_bounds__(QT_THREADS) quadtree_kernel(QtArgs a) {
     uint32_t* kA = a.keyA + off; uint32_t* kB = a.keyB + off;
     uint32_t* vA = a.valA + off; uint32_t* vB = a.valB + off;
 
-    // 0. vToDistributeKeys = the cells' survivor lists in cell row-major order (:952-1002): scan the counts, gather
+    // 0. vToDistributeKeys = the cells' survivor lists in cell row-major order (:952-1002).  Cells are taken in chunks
+    //    of 32 (one per lane); chunk totals give every chunk its base, and inside a chunk the warp copies the
+    //    concatenated lists element by element (lane t of a step finds its cell by a shuffle search over the lanes'
+    //    running totals), so the copy is balanced however the survivors are spread over the cells.
     int M;
     {
         const int nc = a.cellOff[l + 1] - a.cellOff[l];
         const uint32_t* cnt = a.cellCount + (size_t)frame * a.totalCells + a.cellOff[l];
-        uint32_t* offs = a.cellOffs + (size_t)frame * a.totalCells + a.cellOff[l];
         const int lane = tid & 31, wid = tid >> 5;
-        const int per = (nc + QT_THREADS - 1) / QT_THREADS;
-        const int b = min(tid * per, nc), e = min(b + per, nc);
-        int sum = 0;
-        for (int i = b; i < e; i++) sum += (int)cnt[i];
-        int inc = sum;
+        const int nchunks = (nc + 31) >> 5;
+        int* chunkSum = s.sA;                                    // nchunks <= cap is checked on the host
+        for (int ch = wid; ch < nchunks; ch += QT_WARPS) {
+            const int c = ch * 32 + lane;
+            int v = c < nc ? (int)cnt[c] : 0;
 #pragma unroll
-        for (int d = 1; d < 32; d <<= 1) {
-            const int t = __shfl_up_sync(0xffffffffu, inc, d);
-            if (lane >= d) inc += t;
+            for (int d = 16; d > 0; d >>= 1) v += __shfl_xor_sync(0xffffffffu, v, d);
+            if (lane == 0) chunkSum[ch] = v;
         }
-        if (lane == 31) s.warpTmp[wid] = inc;
         __syncthreads();
-        int base = 0, total = 0;
-        for (int k = 0; k < QT_WARPS; k++) { const int v = s.warpTmp[k]; if (k < wid) base += v; total += v; }
-        int run = base + inc - sum;
-        for (int i = b; i < e; i++) { offs[i] = (uint32_t)run; run += (int)cnt[i]; }
+        int total = 0;
+        for (int ch = 0; ch < nchunks; ch++) total += chunkSum[ch];
         M = total;
         if (M > a.candCap[l]) { if (tid == 0) { atomicExch(a.err, 105); *selCount = 0; a.candCount[frame * a.nlevels + l] = 0; } return; }
-        __syncthreads();
         const uint32_t* slots = a.slots + (size_t)frame * a.slotFrameStride + a.slotOff[l];
-        const int cap = a.slotCap[l];
-        for (int c0 = wid * 32; c0 < nc; c0 += QT_WARPS * 32) {
-            const int c = c0 + lane;
-            const int n = c < nc ? (int)cnt[c] : 0;
-            const int o = c < nc ? (int)offs[c] : 0;
-            for (int j = 0; j < 32 && c0 + j < nc; j++) {
-                const int nj = __shfl_sync(0xffffffffu, n, j), oj = __shfl_sync(0xffffffffu, o, j);
-                for (int t = lane; t < nj; t += 32) cand[oj + t] = slots[(size_t)(c0 + j) * cap + t];
+        const int scap = a.slotCap[l];
+        for (int ch = wid; ch < nchunks; ch += QT_WARPS) {
+            int base = 0;
+            for (int k = 0; k < ch; k++) base += chunkSum[k];
+            const int c = ch * 32 + lane;
+            const int nmine = c < nc ? (int)cnt[c] : 0;
+            int incl = nmine;
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) {
+                const int t = __shfl_up_sync(0xffffffffu, incl, d);
+                if (lane >= d) incl += t;
+            }
+            const int T = __shfl_sync(0xffffffffu, incl, 31);
+            for (int t0 = 0; t0 < T; t0 += 32) {
+                const int t = t0 + lane;
+                int j = 0;                                       // first lane whose running total exceeds t
+#pragma unroll
+                for (int step = 16; step > 0; step >>= 1) {
+                    const int v = __shfl_sync(0xffffffffu, incl, j + step - 1);
+                    if (v <= t) j += step;
+                }
+                j = min(j, 31);
+                const int startj = __shfl_sync(0xffffffffu, incl - nmine, j);
+                if (t < T) cand[base + t] = slots[(size_t)(ch * 32 + j) * scap + (t - startj)];
             }
         }
         if (tid == 0) a.candCount[frame * a.nlevels + l] = M;
