@@ -18,6 +18,7 @@
 
 namespace orbx {
 
+constexpr int CELL_MASK_ROWS = 72;  // CELL_MAX_DIM rounded up to whole 8-row batches
 constexpr int CELL_MAX_DIM = 64;   // interior of a cell is < 60 px in each direction (wCell = ceil(W / floor(W/30)))
 
 struct CellArgs {
@@ -71,7 +72,7 @@ __device__ __forceinline__ void row_lr(int c0, int c1, int lane, int& l0, int& r
 template <bool TWO>
 __device__ __forceinline__ void cell_scan(const CellArgs& a, const uint8_t* __restrict__ S, int pitch, const CellBox b, int lane,
                                           uint32_t* __restrict__ out, int cap, uint32_t* __restrict__ cnt, int* err,
-                                          unsigned (*masks)[2][CELL_MAX_DIM]) {
+                                          unsigned (*masks)[2][CELL_MASK_ROWS]) {
     const int xa = b.x0 + lane, xb = b.x0 + 32 + lane;
     const bool ina = xa < b.x1, inb = TWO && xb < b.x1;
     const uint8_t* pa = S + ORB_XPAD + (size_t)b.y0 * pitch + xa;        // walks down the column
@@ -87,21 +88,27 @@ __device__ __forceinline__ void cell_scan(const CellArgs& a, const uint8_t* __re
         else { l0 = __shfl_up_sync(0xffffffffu, c0, 1); r0 = __shfl_down_sync(0xffffffffu, c0, 1); if (!lane) l0 = 0; if (lane == 31) r0 = 0; }
         lr0 = max(l0, r0);
     }
-    constexpr int RB = 8;                                // rows fetched together: RB independent loads in flight per lane
-    for (int rb = 0; rb < rows; rb += RB) {
-        int v0[RB], v1[RB];
-#pragma unroll
-        for (int i = 0; i < RB; i++) {                   // row rb+i+1 (the "next" row of step rb+i); zeros past the interior
-            const bool more = rb + i + 1 < rows;
-            v0[i] = (ina && more) ? pa[(size_t)(i + 1) * pitch] : 0;
-            v1[i] = (inb && more) ? pa[(size_t)(i + 1) * pitch + 32] : 0;
-        }
-        pa += (size_t)RB * pitch;
+    constexpr int RB = 8;                                // rows per batch; the next batch is fetched while this one is scanned
+    int v0[RB], v1[RB];
+    auto fetch = [&](int rb) {                           // rows rb+1 .. rb+RB (the "next" rows of steps rb .. rb+RB-1); zeros past the interior
 #pragma unroll
         for (int i = 0; i < RB; i++) {
-            const int r = rb + i;
-            if (r >= rows) break;                        // warp-uniform
-            const int n0 = v0[i], n1 = v1[i];
+            const bool more = rb + i + 1 < rows;
+            v0[i] = (ina && more) ? pa[(size_t)(i + 1) * pitch] : 0;
+            if (TWO) v1[i] = (inb && more) ? pa[(size_t)(i + 1) * pitch + 32] : 0;
+        }
+        pa += (size_t)RB * pitch;
+    };
+    fetch(0);
+    for (int rb = 0; rb < rows; rb += RB) {
+        int n0v[RB], n1v[RB];
+#pragma unroll
+        for (int i = 0; i < RB; i++) { n0v[i] = v0[i]; if (TWO) n1v[i] = v1[i]; }
+        if (rb + RB < rows) fetch(rb + RB);              // warp-uniform
+#pragma unroll
+        for (int i = 0; i < RB; i++) {
+            const int r = rb + i;                        // rows >= `rows` see zeros only and leave empty masks (the mask rows exist)
+            const int n0 = n0v[i], n1 = TWO ? n1v[i] : 0;
             int nl0, nr0, nl1 = 0, nr1 = 0;
             if (TWO) row_lr(n0, n1, lane, nl0, nr0, nl1, nr1);
             else { nl0 = __shfl_up_sync(0xffffffffu, n0, 1); nr0 = __shfl_down_sync(0xffffffffu, n0, 1); if (!lane) nl0 = 0; if (lane == 31) nr0 = 0; }
@@ -121,53 +128,63 @@ __device__ __forceinline__ void cell_scan(const CellArgs& a, const uint8_t* __re
         }
     }
     __syncwarp();
-    // totals at both thresholds (rows < 64: two mask rows per lane)
+    // totals at both thresholds: lane = row (rows <= 64: two rounds)
+    unsigned mm[2][2], mi[2][2];                         // [round][chunk]
     int nMin = 0, nIni = 0;
-    for (int r = lane; r < rows; r += 32) {
-        nMin += __popc(masks[0][0][r]); nIni += __popc(masks[1][0][r]);
-        if (TWO) { nMin += __popc(masks[0][1][r]); nIni += __popc(masks[1][1][r]); }
-    }
 #pragma unroll
-    for (int d = 16; d > 0; d >>= 1) { nMin += __shfl_xor_sync(0xffffffffu, nMin, d); nIni += __shfl_xor_sync(0xffffffffu, nIni, d); }
-    const int kind = nIni > 0 ? 1 : 0;                   // :976-987: iniThFAST first, minThFAST only if that found nothing
-    const int total = kind ? nIni : nMin;
+    for (int q = 0; q < 2; q++) {
+        const int r = lane + 32 * q;
+        const bool in = r < rows;
+        mm[q][0] = in ? masks[0][0][r] : 0u; mi[q][0] = in ? masks[1][0][r] : 0u;
+        mm[q][1] = (TWO && in) ? masks[0][1][r] : 0u; mi[q][1] = (TWO && in) ? masks[1][1][r] : 0u;
+        nMin += __popc(mm[q][0]) + __popc(mm[q][1]); nIni += __popc(mi[q][0]) + __popc(mi[q][1]);
+    }
+    int tMin = nMin, tIni = nIni;
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) { tMin += __shfl_xor_sync(0xffffffffu, tMin, d); tIni += __shfl_xor_sync(0xffffffffu, tIni, d); }
+    const bool useIni = tIni > 0;                        // :976-987: iniThFAST first, minThFAST only if that found nothing
+    const int total = useIni ? tIni : tMin;
     if (lane == 0) *cnt = (uint32_t)total;
     if (total == 0) return;
     if (total > cap) { if (lane == 0) atomicExch(err, 301); return; }
+    // emission, pixel row-major: every lane writes the survivors of its own row(s) at the row's offset
     const uint8_t* col = S + ORB_XPAD;
-    int pos = 0;
-    for (int r = 0; r < rows; r++) {
-        const int y = b.y0 + r;
-        const unsigned m0 = masks[kind][0][r];
-        if (m0) {
-            if ((m0 >> lane) & 1u) {
-                const uint32_t s = col[(size_t)y * pitch + xa] + sBias;
-                out[pos + __popc(m0 & ((1u << lane) - 1))] =
-                    ((uint32_t)(xa - ORB_BORDER_MIN)) | ((uint32_t)(y - ORB_BORDER_MIN) << 12) | (s << 24);
-            }
-            pos += __popc(m0);
+    int carry = 0;
+#pragma unroll
+    for (int q = 0; q < 2; q++) {
+        if (32 * q >= rows) break;                       // warp-uniform
+        unsigned m0 = useIni ? mi[q][0] : mm[q][0], m1 = useIni ? mi[q][1] : mm[q][1];
+        const int mine = __popc(m0) + __popc(m1);
+        int incl = mine;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            const int t = __shfl_up_sync(0xffffffffu, incl, d);
+            if (lane >= d) incl += t;
         }
-        if (TWO) {
-            const unsigned m1 = masks[kind][1][r];
-            if (m1) {
-                if ((m1 >> lane) & 1u) {
-                    const uint32_t s = col[(size_t)y * pitch + xb] + sBias;
-                    out[pos + __popc(m1 & ((1u << lane) - 1))] =
-                        ((uint32_t)(xb - ORB_BORDER_MIN)) | ((uint32_t)(y - ORB_BORDER_MIN) << 12) | (s << 24);
-                }
-                pos += __popc(m1);
-            }
+        int pos = carry + incl - mine;
+        carry += __shfl_sync(0xffffffffu, incl, 31);
+        const int y = b.y0 + lane + 32 * q;
+        const uint8_t* rowp = col + (size_t)y * pitch;
+        while (m0) {
+            const int x = b.x0 + __ffs(m0) - 1;
+            m0 &= m0 - 1;
+            out[pos++] = ((uint32_t)(x - ORB_BORDER_MIN)) | ((uint32_t)(y - ORB_BORDER_MIN) << 12) | (((uint32_t)rowp[x] + sBias) << 24);
+        }
+        if (TWO) while (m1) {
+            const int x = b.x0 + 32 + __ffs(m1) - 1;
+            m1 &= m1 - 1;
+            out[pos++] = ((uint32_t)(x - ORB_BORDER_MIN)) | ((uint32_t)(y - ORB_BORDER_MIN) << 12) | (((uint32_t)rowp[x] + sBias) << 24);
         }
     }
 }
 
-__global__ void __launch_bounds__(256) cell_nms_kernel(CellArgs a) {
-    __shared__ unsigned s_masks[8][2][2][CELL_MAX_DIM];
+__global__ void __launch_bounds__(256, 4) cell_nms_kernel(CellArgs a) {
+    __shared__ unsigned s_masks[8][2][2][CELL_MASK_ROWS];
     const int lane = threadIdx.x & 31;
     const int cell = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     const int frame = blockIdx.y;
     if (cell >= a.totalCells) return;
-    unsigned (*masks)[2][CELL_MAX_DIM] = s_masks[threadIdx.x >> 5];
+    unsigned (*masks)[2][CELL_MASK_ROWS] = s_masks[threadIdx.x >> 5];
     int l = 0;
     while (cell >= a.cellOff[l + 1]) l++;
     const int c = cell - a.cellOff[l];
