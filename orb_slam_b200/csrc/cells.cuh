@@ -88,7 +88,7 @@ __device__ __forceinline__ void cell_scan(const CellArgs& a, const uint8_t* __re
         else { l0 = __shfl_up_sync(0xffffffffu, c0, 1); r0 = __shfl_down_sync(0xffffffffu, c0, 1); if (!lane) l0 = 0; if (lane == 31) r0 = 0; }
         lr0 = max(l0, r0);
     }
-    constexpr int RB = 8;                                // rows per batch; the next batch is fetched while this one is scanned
+    constexpr int RB = TWO ? 4 : 8;                      // rows per batch; the next batch is fetched while this one is scanned
     int v0[RB], v1[RB];
     auto fetch = [&](int rb) {                           // rows rb+1 .. rb+RB (the "next" rows of steps rb .. rb+RB-1); zeros past the interior
 #pragma unroll
@@ -178,7 +178,7 @@ __device__ __forceinline__ void cell_scan(const CellArgs& a, const uint8_t* __re
     }
 }
 
-__global__ void __launch_bounds__(256, 4) cell_nms_kernel(CellArgs a) {
+__global__ void __launch_bounds__(256, 5) cell_nms_kernel(CellArgs a) {
     __shared__ unsigned s_masks[8][2][2][CELL_MASK_ROWS];
     const int lane = threadIdx.x & 31;
     const int cell = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
