@@ -640,7 +640,17 @@ int orbx_extract_batch(orbx_t* e, const uint8_t* const* images, int n, int width
         }
         e->inBytes = devStride * F + 64;
     }
-    const int nchunks = (n + chunk - 1) / chunk;
+    // chunk schedule: a short first and second chunk (the device starts after a quarter of a chunk has arrived instead
+    // of a whole one), full chunks, and whatever is left as a short tail (short drain)
+    std::vector<int> cStart, cCount;
+    {
+        int f = 0;
+        auto push = [&](int c) { cStart.push_back(f); cCount.push_back(c); f += c; };
+        if (n >= 2 * chunk && chunk >= 8) { push(chunk / 4); push(chunk / 2); }
+        while (n - f > chunk) push(chunk);
+        if (n - f > 0) push(n - f);
+    }
+    const int nchunks = (int)cStart.size();
     int status = ORBX_OK;
     e->launches = 0;
     // ORBX_TRACE=1: device timeline of the chunk pipeline (debug aid; costs five timing events per chunk)
@@ -649,7 +659,7 @@ int orbx_extract_batch(orbx_t* e, const uint8_t* const* images, int n, int width
     if (trace) { tev.resize((size_t)nchunks * 5 + 1); for (auto& t : tev) cudaEventCreate(&t); cudaEventRecord(tev.back(), e->sIn); }
     auto mark = [&](int k, int what, cudaStream_t st) { if (trace) cudaEventRecord(tev[(size_t)k * 5 + what], st); };
     auto finalize = [&](int k) -> int {        // host side of chunk k: counts, error flag, staged results
-        const int b = k % ORBX_NBUF, f0 = k * chunk, nf = std::min(chunk, n - f0);
+        const int b = k % ORBX_NBUF, f0 = cStart[k], nf = cCount[k];
         CK(cudaEventSynchronize(e->evOut[b]));
         const int* h_n = (const int*)e->h_res[b];
         if (h_n[F] != 0) {
@@ -671,7 +681,7 @@ int orbx_extract_batch(orbx_t* e, const uint8_t* const* images, int n, int width
     };
     int finalized = 0;                          // chunks [0, finalized) are complete on the host
     for (int k = 0; k < nchunks; k++) {
-        const int b = k % ORBX_NBUF, f0 = k * chunk, nf = std::min(chunk, n - f0);
+        const int b = k % ORBX_NBUF, f0 = cStart[k], nf = cCount[k];
         // buffer set b was last used by chunk k - ORBX_NBUF: finish it on the host before its staging is reused.  The
         // host therefore runs up to ORBX_NBUF chunks ahead of the device, which keeps both copy engines and the two
         // compute streams fed.
