@@ -329,16 +329,18 @@ def run_stereo_frontend(local_rank, with_cpu):
         return ORBmatcher(0.9, True, ctx).SearchByProjectionFrame(cur, lastF, pts, obs, 7.0, False)[0]
 
     def loop(a, b, stereo, proj, reps):
-        ts, last = [], None
+        ts, last, counts = [], None, None
         for i in range(reps):
             l, r = pairs[i % len(pairs)]
             t, (cur, kl, dl), n, nm = one(l, r, a, b, stereo, proj, last)
+            if i == 7:
+                counts = (int(n), int(nm))           # same pair and map points in both arms: the counts must agree
             pts = scenes.last_frame_points(cur, seed=i)
             last = (cur, pts, np.full(cur.N, -1, np.int32))
             ts.append(t)
         ts = np.array(ts[2:]) * 1e3
         return {"extract_pair_ms": float(np.median(ts[:, 0])), "stereo_match_ms": float(np.median(ts[:, 1])),
-                "search_by_projection_ms": float(np.median(ts[:, 2])), "stereo_matches": int(n), "projection_matches": int(nm)}
+                "search_by_projection_ms": float(np.median(ts[:, 2])), "stereo_matches": counts[0], "projection_matches": counts[1]}
 
     out["b200"] = loop(exL, exR, gpu_stereo, gpu_proj, 24)
     if with_cpu:

@@ -192,26 +192,61 @@ __global__ void __launch_bounds__(PYR_THREADS) pyr_level_kernel(PyrArgs a) {
     PA = (uint4*)(smem + pyr_smem_T() + pyr_smem_Hs());
     if (LEVEL0) {
         // level 0 is the caller's image: copy with REFLECT_101 halo (copyMakeBorder, :1372); byte b of a T row is
-        // column x0 - 4 + b.  Aligned interior words go as one 32-bit load.
-        for (int i = tid; i < TROWS * (TBYTES / 4); i += PYR_THREADS) {
-            const int ty = i / (TBYTES / 4), q = i - ty * (TBYTES / 4);
+        // column x0 - 4 + b.  Rows arrive at any alignment (the device copy keeps the host row step): interior
+        // bytes go as aligned word loads + funnel shifts, the image edges byte by byte through reflect101.
+        auto edge_word = [&](const uint8_t* row, int xb) {
+            uint32_t v = 0;
+#pragma unroll
+            for (int j = 0; j < 4; j++) {
+                const int x = xb + j;
+                if (x >= -HALO && x < w + HALO) v |= (uint32_t)__ldg(row + reflect101(x, w)) << (8 * j);
+            }
+            return v;
+        };
+        // pass A: bytes 0..127 of every T row, two rows per warp step (half-warp = row, lane = 8 bytes)
+        {
+            const int half = lane >> 4, c = lane & 15;
+            const int xb = x0 - 4 + 8 * c;
+            const bool inner = xb >= 4 && xb + 11 < w;       // the three aligned words stay inside the row
+            uint2 v[3];
+#pragma unroll
+            for (int j = 0; j < 3; j++) {
+                const int ty = 2 * (wid + 8 * j) + half;
+                const int y = y0 - HALO + ty;
+                v[j] = make_uint2(0u, 0u);
+                if (ty < TROWS && y < h + HALO) {
+                    const uint8_t* row = src + (size_t)reflect101(y, h) * a.srcPitch + a.srcX0;
+                    if (inner) {
+                        const uint8_t* p = row + xb;
+                        const unsigned mis = (unsigned)((size_t)p & 3);
+                        const uint32_t* ap = (const uint32_t*)(p - mis);
+                        const uint32_t w0 = __ldg(ap), w1 = __ldg(ap + 1), w2 = __ldg(ap + 2);
+                        v[j] = make_uint2(__funnelshift_r(w0, w1, 8 * mis), __funnelshift_r(w1, w2, 8 * mis));
+                    } else {
+                        v[j] = make_uint2(edge_word(row, xb), edge_word(row, xb + 4));
+                    }
+                }
+            }
+#pragma unroll
+            for (int j = 0; j < 3; j++) {
+                const int ty = 2 * (wid + 8 * j) + half;
+                if (ty < TROWS) *(uint2*)(T + ty * TS + 8 * c) = v[j];
+            }
+        }
+        // pass B: bytes 128..135 (the right halo) of every T row
+        if (tid < 2 * TROWS) {
+            const int ty = tid >> 1, q = 32 + (tid & 1);
             const int y = y0 - HALO + ty, xb = x0 - 4 + 4 * q;
             uint32_t v = 0;
             if (y < h + HALO) {
                 const uint8_t* row = src + (size_t)reflect101(y, h) * a.srcPitch + a.srcX0;
-                if (xb >= 4 && xb + 7 < w) {
-                    // interior word of a row at any alignment: two aligned loads + funnel shift (both stay inside the row)
+                if (xb + 7 < w) {
                     const uint8_t* p = row + xb;
                     const unsigned mis = (unsigned)((size_t)p & 3);
                     const uint32_t* ap = (const uint32_t*)(p - mis);
-                    const uint32_t lo = __ldg(ap), hi = mis ? __ldg(ap + 1) : 0u;
-                    v = __funnelshift_r(lo, hi, 8 * mis);
+                    v = __funnelshift_r(__ldg(ap), __ldg(ap + 1), 8 * mis);
                 } else {
-#pragma unroll
-                    for (int j = 0; j < 4; j++) {
-                        const int x = xb + j;
-                        if (x >= -HALO && x < w + HALO) v |= (uint32_t)__ldg(row + reflect101(x, w)) << (8 * j);
-                    }
+                    v = edge_word(row, xb);
                 }
             }
             *(uint32_t*)(T + ty * TS + 4 * q) = v;
