@@ -48,6 +48,7 @@ struct orbx_extractor {
     bool haveGeom = false;
     int capFrames = 0;                       // frames EACH workspace is sized for
     ResizeTap* d_tabs = nullptr;
+    std::vector<ResizeTap> h_tabs;                   // host copy: per-tile source extents go into the kernel arguments
     uint8_t* d_in[ORBX_NBUF] = {}; size_t inBytes = 0;   // double-buffered H2D targets (host layout kept: linear copies)
     // Two complete kernel workspaces, each with its own compute stream: neighbouring chunks (host path) or the two halves
     // of a batch (device path) run concurrently, so the latency-bound stages of one (quadtree, describe) fill the issue
@@ -267,6 +268,7 @@ static int ensure_workspace(orbx_extractor* e, int width, int height, int frames
     const size_t F = (size_t)newCap;
     CK(cudaMalloc(&e->d_tabs, std::max<size_t>(tabs.size(), 1) * sizeof(ResizeTap)));
     if (!tabs.empty()) CK(cudaMemcpy(e->d_tabs, tabs.data(), tabs.size() * sizeof(ResizeTap), cudaMemcpyHostToDevice));
+    e->h_tabs = tabs;
     const size_t cells = (size_t)std::max(g.totalCells, 1) * F;
     const size_t cands = (size_t)std::max<unsigned long long>(g.candTotal, 64) * F;
     for (auto& w : e->ws) {
@@ -332,6 +334,19 @@ static int enqueue_pipeline(orbx_extractor* e, int wi, const uint8_t* src, size_
             a.src = w.d_pyr + p.pyrOff + (size_t)ORB_EDGE * p.pitch; a.srcFrameStride = g.pyrBytes;
             a.srcPitch = p.pitch; a.srcX0 = ORB_XPAD; a.sw = p.w; a.sh = p.h;
             a.xtab = e->d_tabs + v.xtabOff; a.ytab = e->d_tabs + v.ytabOff;
+            // source extent of every tile column / row, so that a tile can start fetching without a table lookup
+            a.haveTiles = (int)grid.x <= PYR_MAX_TILES_X && (int)grid.y <= PYR_MAX_TILES_Y;
+            if (a.haveTiles) {
+                const ResizeTap* hx = e->h_tabs.data() + v.xtabOff; const ResizeTap* hy = e->h_tabs.data() + v.ytabOff;
+                for (int t = 0; t < (int)grid.x; t++) {
+                    const int lo = std::max(0, t * TW - HALO), hi = std::min(v.w - 1, t * TW + TW + HALO - 1);
+                    a.tileX[t] = (uint32_t)(hx[lo].s0 & ~15) | ((uint32_t)hx[hi].s1 << 16);
+                }
+                for (int t = 0; t < (int)grid.y; t++) {
+                    const int lo = std::max(0, t * TH - HALO), hi = std::min(v.h - 1, t * TH + TH + HALO - 1);
+                    a.tileY[t] = (uint32_t)hy[lo].s0 | ((uint32_t)hy[hi].s1 << 16);
+                }
+            }
             size_t smem;
             pyr_smem_for(p, v, a.srcTileCols, a.srcTileRows, smem);
             pyr_level_kernel<false><<<grid, PYR_THREADS, smem, st>>>(a);

@@ -140,6 +140,8 @@ __device__ __forceinline__ void hblur4(const RowPairs& p, uint32_t& A, uint32_t&
 
 struct TapX { unsigned short o0, o1; short a0, a1; };   // source byte offsets inside the staged row + 11-bit weights
 
+constexpr int PYR_MAX_TILES_X = 64, PYR_MAX_TILES_Y = 160;    // 8192 x 5120 px; larger levels read the tap tables instead
+
 struct PyrArgs {
     const uint8_t* src;          // level l-1 planes (frame 0), or the input images for level 0
     unsigned long long srcFrameStride;
@@ -158,6 +160,9 @@ struct PyrArgs {
     int srcTileCols, srcTileRows;   // staging capacity (level > 0)
     int minTh;
     int* err;                    // device error flag
+    int haveTiles;               // tileX / tileY are filled in (the level has few enough tiles)
+    uint32_t tileX[PYR_MAX_TILES_X];   // per tile column: first staged source column (16-aligned) | last source column << 16
+    uint32_t tileY[PYR_MAX_TILES_Y];   // per tile row: first | last source row
 };
 
 // shared memory carve-up (bytes).  T is live from the resize to the row pass; everything else lives in one region R
@@ -259,8 +264,14 @@ __global__ void __launch_bounds__(PYR_THREADS) pyr_level_kernel(PyrArgs a) {
         // source rows/columns this tile touches
         const int ylo = max(0, y0 - HALO), yhi = min(h - 1, y0 + TH + HALO - 1);
         const int xlo = max(0, x0 - HALO), xhi = min(w - 1, x0 + TW + HALO - 1);
-        const int sy_lo = a.ytab[ylo].s0, sy_hi = a.ytab[yhi].s1;
-        const int sx_lo = a.xtab[xlo].s0 & ~15, sx_hi = a.xtab[xhi].s1;
+        int sy_lo, sy_hi, sx_lo, sx_hi;
+        if (a.haveTiles) {                                     // from the kernel arguments: no memory round trip before the fetch
+            const uint32_t ex = a.tileX[blockIdx.x], ey = a.tileY[blockIdx.y];
+            sx_lo = (int)(ex & 0xffffu); sx_hi = (int)(ex >> 16); sy_lo = (int)(ey & 0xffffu); sy_hi = (int)(ey >> 16);
+        } else {
+            sy_lo = a.ytab[ylo].s0; sy_hi = a.ytab[yhi].s1;
+            sx_lo = a.xtab[xlo].s0 & ~15; sx_hi = a.xtab[xhi].s1;
+        }
         const int scols = a.srcTileCols;                       // multiple of 16
         const int nvec = (sx_hi - sx_lo) / 16 + 1;
         const int nrows = sy_hi - sy_lo + 1;
