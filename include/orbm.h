@@ -123,6 +123,31 @@ int orbm_search_by_projection_points(orbm_t* m, const orbm_frame* F, const orbm_
                                      const int32_t* frame_observations, float th, float nnratio,
                                      int32_t* frame_assign, int* nmatches);
 
+/* ---- ORBmatcher::SearchByBoW.  A DBoW2::FeatureVector (std::map<NodeId,
+ * std::vector<unsigned>>) flattened in map order: node ids ascending, start[k]..start[k+1] = the
+ * node's feature indices in their vector order. */
+typedef struct orbm_featvec {
+    int32_t nnodes;
+    const uint32_t* node_ids;   /* nnodes, strictly ascending */
+    const int32_t* start;       /* nnodes + 1 */
+    const uint32_t* items;      /* start[nnodes] feature indices */
+} orbm_featvec;
+
+#define ORBM_BOW_KEYFRAME_FRAME 0      /* SearchByBoW(KeyFrame* pKF, Frame& F, vpMapPointMatches), src/ORBmatcher.cc:159-288 */
+#define ORBM_BOW_KEYFRAME_KEYFRAME 1   /* SearchByBoW(KeyFrame* pKF1, KeyFrame* pKF2, vpMatches12), :590-723 */
+
+/* Side 1 is always the key frame whose map points drive the outer loop (pKF / pKF1); side 2 is F / pKF2.
+ * desc: n x 32 bytes; angle: the angles the rotation histogram reads (variant 0: pKF->mvKeysUn[i].angle and
+ * F.mvKeys[i].angle; variant 1: mvKeysUn of both); valid1[i] = map point i of side 1 non-NULL and !isBad();
+ * valid2 likewise for pKF2 (variant 1; ignored and may be NULL for variant 0).
+ * match out: variant 0 -> n2 entries, match[iF] = side-1 feature index whose map point is stored in
+ * vpMapPointMatches[iF], -1 for NULL; variant 1 -> n1 entries, match[idx1] = idx2 with
+ * vpMatches12[idx1] = vpMapPoints2[idx2], -1 for NULL.  *nmatches = the function's return value. */
+int orbm_search_by_bow(orbm_t* m, int variant,
+                       const uint8_t* desc1, const float* angle1, const uint8_t* valid1, int n1, const orbm_featvec* fv1,
+                       const uint8_t* desc2, const float* angle2, const uint8_t* valid2, int n2, const orbm_featvec* fv2,
+                       float nnratio, int checkOrientation, int32_t* match, int* nmatches);
+
 #ifdef __cplusplus
 }
 #endif

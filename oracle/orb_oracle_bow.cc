@@ -1,0 +1,148 @@
+// ORACLE — test infrastructure only (see orb_oracle.h).
+//
+// CPU restatement of ORBmatcher::SearchByBoW:
+//   SearchByBoW(KeyFrame* pKF, Frame& F, vector<MapPoint*>& vpMapPointMatches)      src/ORBmatcher.cc:159-288
+//   SearchByBoW(KeyFrame* pKF1, KeyFrame* pKF2, vector<MapPoint*>& vpMatches12)     src/ORBmatcher.cc:590-723
+// The two feature vectors are rebuilt as std::map<unsigned, std::vector<unsigned>> (= DBoW2::FeatureVector) from the
+// flattened orbm_featvec and the loops follow the reference statement by statement (iterators, lower_bound,
+// continue's, '<=' vs '<' on TH_LOW).  Map points are represented by what the loops read of them: a validity flag
+// (pointer non-NULL and !isBad()).  Parity unpinned by reference object code: ORBmatcher.cc needs OpenCV/DBoW2/g2o
+// headers to compile.
+#include <cmath>
+#include <cstdint>
+#include <cstring>
+#include <map>
+#include <vector>
+
+#include "../include/orbm.h"
+
+extern "C" int orbo_descriptor_distance(const uint8_t* a, const uint8_t* b);
+extern "C" void orbo_three_maxima(const int32_t* counts, int L, int* i1, int* i2, int* i3);
+
+namespace {
+const int TH_LOW = 50, HISTO_LENGTH = 30;
+typedef std::map<unsigned int, std::vector<unsigned int> > FeatureVector;
+
+FeatureVector unflatten(const orbm_featvec* fv) {
+    FeatureVector m;
+    for (int k = 0; k < fv->nnodes; k++)
+        m[fv->node_ids[k]] = std::vector<unsigned int>(fv->items + fv->start[k], fv->items + fv->start[k + 1]);
+    return m;
+}
+
+void cull(std::vector<int>* rotHist, int32_t* match, int& nmatches) {     // :263-285, :698-720
+    int32_t counts[HISTO_LENGTH];
+    for (int i = 0; i < HISTO_LENGTH; i++) counts[i] = (int32_t)rotHist[i].size();
+    int ind1 = -1, ind2 = -1, ind3 = -1;
+    orbo_three_maxima(counts, HISTO_LENGTH, &ind1, &ind2, &ind3);
+    for (int i = 0; i < HISTO_LENGTH; i++) {
+        if (i == ind1 || i == ind2 || i == ind3) continue;
+        for (size_t j = 0, jend = rotHist[i].size(); j < jend; j++) { match[rotHist[i][j]] = -1; nmatches--; }
+    }
+}
+}  // namespace
+
+// variant 0: vpMapPointMatches[iF] as the index of the key-frame feature whose map point it holds (-1 = NULL)
+extern "C" int orbo_search_by_bow_kf_frame(const uint8_t* descKF, const float* angleKFun, const uint8_t* validKF, int nKF,
+                                           const orbm_featvec* fvKF, const uint8_t* descF, const float* angleF, int nF,
+                                           const orbm_featvec* fvF, float mfNNratio, int mbCheckOrientation, int32_t* vpMapPointMatches) {
+    (void)nKF;
+    for (int i = 0; i < nF; i++) vpMapPointMatches[i] = -1;
+    const FeatureVector vFeatVecKF = unflatten(fvKF), vFeatVecF = unflatten(fvF);
+    int nmatches = 0;
+    std::vector<int> rotHist[HISTO_LENGTH];
+    const float factor = 1.0f / HISTO_LENGTH;
+    FeatureVector::const_iterator KFit = vFeatVecKF.begin(), Fit = vFeatVecF.begin();
+    const FeatureVector::const_iterator KFend = vFeatVecKF.end(), Fend = vFeatVecF.end();
+    while (KFit != KFend && Fit != Fend) {
+        if (KFit->first == Fit->first) {
+            const std::vector<unsigned int> vIndicesKF = KFit->second;
+            const std::vector<unsigned int> vIndicesF = Fit->second;
+            for (size_t iKF = 0; iKF < vIndicesKF.size(); iKF++) {
+                const unsigned int realIdxKF = vIndicesKF[iKF];
+                if (!validKF[realIdxKF]) continue;                           // !pMP || pMP->isBad()
+                const uint8_t* dKF = descKF + 32 * (size_t)realIdxKF;
+                int bestDist1 = 256, bestIdxF = -1, bestDist2 = 256;
+                for (size_t iF = 0; iF < vIndicesF.size(); iF++) {
+                    const unsigned int realIdxF = vIndicesF[iF];
+                    if (vpMapPointMatches[realIdxF] >= 0) continue;
+                    const int dist = orbo_descriptor_distance(dKF, descF + 32 * (size_t)realIdxF);
+                    if (dist < bestDist1) { bestDist2 = bestDist1; bestDist1 = dist; bestIdxF = (int)realIdxF; }
+                    else if (dist < bestDist2) bestDist2 = dist;
+                }
+                if (bestDist1 <= TH_LOW) {
+                    if (static_cast<float>(bestDist1) < mfNNratio * static_cast<float>(bestDist2)) {
+                        vpMapPointMatches[bestIdxF] = (int32_t)realIdxKF;
+                        if (mbCheckOrientation) {
+                            float rot = angleKFun[realIdxKF] - angleF[bestIdxF];
+                            if (rot < 0.0) rot += 360.0f;
+                            int bin = (int)std::round(rot * factor);
+                            if (bin == HISTO_LENGTH) bin = 0;
+                            rotHist[bin].push_back(bestIdxF);
+                        }
+                        nmatches++;
+                    }
+                }
+            }
+            KFit++; Fit++;
+        } else if (KFit->first < Fit->first) {
+            KFit = vFeatVecKF.lower_bound(Fit->first);
+        } else {
+            Fit = vFeatVecF.lower_bound(KFit->first);
+        }
+    }
+    if (mbCheckOrientation) cull(rotHist, vpMapPointMatches, nmatches);
+    return nmatches;
+}
+
+// variant 1: vpMatches12[idx1] as the index idx2 of the map point of pKF2 it holds (-1 = NULL)
+extern "C" int orbo_search_by_bow_kf_kf(const uint8_t* desc1, const float* angle1, const uint8_t* valid1, int n1, const orbm_featvec* fv1,
+                                        const uint8_t* desc2, const float* angle2, const uint8_t* valid2, int n2, const orbm_featvec* fv2,
+                                        float mfNNratio, int mbCheckOrientation, int32_t* vpMatches12) {
+    for (int i = 0; i < n1; i++) vpMatches12[i] = -1;
+    std::vector<bool> vbMatched2(n2, false);
+    const FeatureVector vFeatVec1 = unflatten(fv1), vFeatVec2 = unflatten(fv2);
+    std::vector<int> rotHist[HISTO_LENGTH];
+    const float factor = 1.0f / HISTO_LENGTH;
+    int nmatches = 0;
+    FeatureVector::const_iterator f1it = vFeatVec1.begin(), f2it = vFeatVec2.begin();
+    const FeatureVector::const_iterator f1end = vFeatVec1.end(), f2end = vFeatVec2.end();
+    while (f1it != f1end && f2it != f2end) {
+        if (f1it->first == f2it->first) {
+            for (size_t i1 = 0, iend1 = f1it->second.size(); i1 < iend1; i1++) {
+                const size_t idx1 = f1it->second[i1];
+                if (!valid1[idx1]) continue;
+                const uint8_t* d1 = desc1 + 32 * idx1;
+                int bestDist1 = 256, bestIdx2 = -1, bestDist2 = 256;
+                for (size_t i2 = 0, iend2 = f2it->second.size(); i2 < iend2; i2++) {
+                    const size_t idx2 = f2it->second[i2];
+                    if (vbMatched2[idx2] || !valid2[idx2]) continue;        // matched, NULL or bad
+                    const int dist = orbo_descriptor_distance(d1, desc2 + 32 * idx2);
+                    if (dist < bestDist1) { bestDist2 = bestDist1; bestDist1 = dist; bestIdx2 = (int)idx2; }
+                    else if (dist < bestDist2) bestDist2 = dist;
+                }
+                if (bestDist1 < TH_LOW) {
+                    if (static_cast<float>(bestDist1) < mfNNratio * static_cast<float>(bestDist2)) {
+                        vpMatches12[idx1] = bestIdx2;
+                        vbMatched2[bestIdx2] = true;
+                        if (mbCheckOrientation) {
+                            float rot = angle1[idx1] - angle2[bestIdx2];
+                            if (rot < 0.0) rot += 360.0f;
+                            int bin = (int)std::round(rot * factor);
+                            if (bin == HISTO_LENGTH) bin = 0;
+                            rotHist[bin].push_back((int)idx1);
+                        }
+                        nmatches++;
+                    }
+                }
+            }
+            f1it++; f2it++;
+        } else if (f1it->first < f2it->first) {
+            f1it = vFeatVec1.lower_bound(f2it->first);
+        } else {
+            f2it = vFeatVec2.lower_bound(f1it->first);
+        }
+    }
+    if (mbCheckOrientation) cull(rotHist, vpMatches12, nmatches);
+    return nmatches;
+}

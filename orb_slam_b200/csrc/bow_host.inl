@@ -1,0 +1,117 @@
+// Host side of ORBmatcher::SearchByBoW (included by matcher.cu).  The device produces every DescriptorDistance the
+// reference would evaluate (one row per map point of side 1, over the features of side 2 in the same vocabulary
+// node); the scan order, the "already matched" skips, the TH_LOW / mfNNratio acceptance and the rotation histogram
+// are order-dependent and are replayed here exactly as written in src/ORBmatcher.cc:159-288 and :590-723.
+
+extern "C" int orbm_search_by_bow(orbm_t* m, int variant,
+                                  const uint8_t* desc1, const float* angle1, const uint8_t* valid1, int n1, const orbm_featvec* fv1,
+                                  const uint8_t* desc2, const float* angle2, const uint8_t* valid2, int n2, const orbm_featvec* fv2,
+                                  float nnratio, int checkOrientation, int32_t* match, int* nmatches) {
+    if (!m || !fv1 || !fv2 || !match || !nmatches || n1 < 0 || n2 < 0 || (variant != 0 && variant != 1)) return ORBX_E_INVALID;
+    if ((n1 > 0 && (!desc1 || !valid1 || !angle1)) || (n2 > 0 && (!desc2 || !angle2)) || (variant == 1 && n2 > 0 && !valid2))
+        return ORBX_E_INVALID;
+    if (fv1->nnodes < 0 || fv2->nnodes < 0) return ORBX_E_INVALID;
+    {   // well-formed feature vectors: ascending node ids, monotone ranges, indices inside the frames
+        const orbm_featvec* fv[2] = {fv1, fv2};
+        const int nn[2] = {n1, n2};
+        for (int s = 0; s < 2; s++) {
+            if (fv[s]->nnodes > 0 && (!fv[s]->node_ids || !fv[s]->start)) return ORBX_E_INVALID;
+            if (fv[s]->nnodes == 0) continue;
+            if (fv[s]->start[0] != 0) return ORBX_E_INVALID;
+            for (int k = 0; k < fv[s]->nnodes; k++) {
+                if (k && fv[s]->node_ids[k] <= fv[s]->node_ids[k - 1]) return ORBX_E_INVALID;
+                if (fv[s]->start[k + 1] < fv[s]->start[k]) return ORBX_E_INVALID;
+            }
+            const int total = fv[s]->start[fv[s]->nnodes];
+            if (total > 0 && !fv[s]->items) return ORBX_E_INVALID;
+            for (int t = 0; t < total; t++) if (fv[s]->items[t] >= (uint32_t)nn[s]) return ORBX_E_INVALID;
+        }
+    }
+    const int nout = variant == ORBM_BOW_KEYFRAME_FRAME ? n2 : n1;
+    for (int i = 0; i < nout; i++) match[i] = -1;
+    *nmatches = 0;
+    std::lock_guard<std::mutex> lk(m->mtx);
+    CKM(cudaSetDevice(m->device));
+
+    // ---- the merge walk over the two sorted node lists (:176-249, :614-690); lower_bound on a std::map == first id >= key
+    struct Block { int k1, k2; };
+    std::vector<Block> blocks;
+    {
+        int a = 0, b = 0;
+        while (a < fv1->nnodes && b < fv2->nnodes) {
+            const uint32_t ia = fv1->node_ids[a], ib = fv2->node_ids[b];
+            if (ia == ib) { blocks.push_back({a, b}); a++; b++; }
+            else if (ia < ib) a = (int)(std::lower_bound(fv1->node_ids + a, fv1->node_ids + fv1->nnodes, ib) - fv1->node_ids);
+            else b = (int)(std::lower_bound(fv2->node_ids + b, fv2->node_ids + fv2->nnodes, ia) - fv2->node_ids);
+        }
+    }
+    // ---- one device row per side-1 feature whose map point exists (:192-197, :626-630)
+    std::vector<BowRow> rows;
+    size_t total = 0;
+    for (const Block& bk : blocks) {
+        const int s1 = fv1->start[bk.k1], e1 = fv1->start[bk.k1 + 1], s2 = fv2->start[bk.k2], e2 = fv2->start[bk.k2 + 1];
+        for (int t = s1; t < e1; t++) {
+            const uint32_t i1 = fv1->items[t];
+            if (!valid1[i1] || e2 == s2) continue;
+            if (total + (size_t)(e2 - s2) > 0xffffffffull) return ORBX_E_CAPACITY;
+            rows.push_back(BowRow{i1, s2, e2 - s2, (uint32_t)total});
+            total += (size_t)(e2 - s2);
+        }
+    }
+    std::vector<uint16_t> dist(total);
+    if (!rows.empty()) {
+        const size_t nitems2 = (size_t)fv2->start[fv2->nnodes];      // > 0: some row has candidates
+        int rc;
+        if ((rc = m->w0.reserve((size_t)n1 * 32))) return rc;
+        if ((rc = m->w1.reserve((size_t)n2 * 32))) return rc;
+        if ((rc = m->w2.reserve(nitems2 * 4))) return rc;
+        if ((rc = m->w3.reserve(rows.size() * sizeof(BowRow)))) return rc;
+        if ((rc = m->w4.reserve(total * 2))) return rc;
+        CKM(cudaMemcpyAsync(m->w0.p, desc1, (size_t)n1 * 32, cudaMemcpyHostToDevice, m->stream));
+        CKM(cudaMemcpyAsync(m->w1.p, desc2, (size_t)n2 * 32, cudaMemcpyHostToDevice, m->stream));
+        CKM(cudaMemcpyAsync(m->w2.p, fv2->items, nitems2 * 4, cudaMemcpyHostToDevice, m->stream));
+        CKM(cudaMemcpyAsync(m->w3.p, rows.data(), rows.size() * sizeof(BowRow), cudaMemcpyHostToDevice, m->stream));
+        const int nrows = (int)rows.size();
+        bow_dist_kernel<<<(nrows + 7) / 8, 256, 0, m->stream>>>((const BowRow*)m->w3.p, nrows, (const uint32_t*)m->w0.p,
+                                                                 (const uint32_t*)m->w1.p, (const uint32_t*)m->w2.p, (uint16_t*)m->w4.p);
+        CKM(cudaGetLastError());
+        CKM(cudaMemcpyAsync(dist.data(), m->w4.p, total * 2, cudaMemcpyDeviceToHost, m->stream));
+        CKM(cudaStreamSynchronize(m->stream));
+    }
+    // ---- replay
+    std::vector<int> rotHist[ORBM_HISTO_LENGTH];
+    std::vector<uint8_t> matched2(variant == ORBM_BOW_KEYFRAME_KEYFRAME ? (size_t)n2 : 0, 0);    // vbMatched2, :603
+    int nm = 0;
+    for (const BowRow& r : rows) {
+        int bestDist1 = 256, bestIdx2 = -1, bestDist2 = 256;
+        const uint16_t* d = dist.data() + r.out;
+        for (int j = 0; j < r.cnt2; j++) {
+            const uint32_t i2 = fv2->items[r.off2 + j];
+            if (variant == ORBM_BOW_KEYFRAME_FRAME) { if (match[i2] >= 0) continue; }          // :209-210
+            else { if (matched2[i2] || !valid2[i2]) continue; }                                 // :646-650
+            const int dd = d[j];
+            if (dd < bestDist1) { bestDist2 = bestDist1; bestDist1 = dd; bestIdx2 = (int)i2; }
+            else if (dd < bestDist2) bestDist2 = dd;
+        }
+        const bool low = variant == ORBM_BOW_KEYFRAME_FRAME ? bestDist1 <= ORBM_TH_LOW : bestDist1 < ORBM_TH_LOW;   // :228 vs :668
+        if (low && (float)bestDist1 < nnratio * (float)bestDist2) {
+            if (variant == ORBM_BOW_KEYFRAME_FRAME) match[bestIdx2] = (int32_t)r.idx1;
+            else { match[r.idx1] = bestIdx2; matched2[bestIdx2] = 1; }
+            if (checkOrientation)
+                rotHist[rot_bin(angle1[r.idx1], angle2[bestIdx2])].push_back(variant == ORBM_BOW_KEYFRAME_FRAME ? bestIdx2 : (int)r.idx1);
+            nm++;
+        }
+    }
+    if (checkOrientation) {
+        int32_t counts[ORBM_HISTO_LENGTH];
+        for (int i = 0; i < ORBM_HISTO_LENGTH; i++) counts[i] = (int32_t)rotHist[i].size();
+        int ind1, ind2, ind3;
+        orbm_three_maxima(counts, ORBM_HISTO_LENGTH, &ind1, &ind2, &ind3);
+        for (int i = 0; i < ORBM_HISTO_LENGTH; i++) {
+            if (i == ind1 || i == ind2 || i == ind3) continue;
+            for (int idx : rotHist[i]) { match[idx] = -1; nm--; }
+        }
+    }
+    *nmatches = nm;
+    return ORBX_OK;
+}

@@ -10,6 +10,8 @@
 // writes the results back into the same members the reference writes.
 #include "ORBmatcher.h"
 
+#include <algorithm>
+#include <cassert>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -135,6 +137,74 @@ int ORBmatcher::SearchByProjection(Frame& F, const std::vector<MapPoint*>& vpMap
                 "orbm_search_by_projection_points");
     for (int idx = 0; idx < F.N; idx++)
         if (assign[idx] >= 0) F.mvpMapPoints[idx] = vpMapPoints[assign[idx]];                       // :123
+    return nmatches;
+}
+
+namespace b200 {
+// DBoW2::FeatureVector in map order -> orbm_featvec
+struct FlatFeatVec {
+    std::vector<uint32_t> ids, items;
+    std::vector<int32_t> start;
+    orbm_featvec fv;
+    explicit FlatFeatVec(const DBoW2::FeatureVector& v) {
+        start.push_back(0);
+        for (DBoW2::FeatureVector::const_iterator it = v.begin(); it != v.end(); ++it) {
+            ids.push_back(it->first);
+            items.insert(items.end(), it->second.begin(), it->second.end());
+            start.push_back((int32_t)items.size());
+        }
+        fv.nnodes = (int32_t)ids.size(); fv.node_ids = ids.data(); fv.start = start.data(); fv.items = items.data();
+    }
+};
+static void Angles(const std::vector<cv::KeyPoint>& k, std::vector<float>& a) {
+    a.resize(k.size());
+    for (size_t i = 0; i < k.size(); i++) a[i] = k[i].angle;
+}
+static void Valid(const std::vector<MapPoint*>& v, std::vector<uint8_t>& ok) {
+    ok.resize(v.size());
+    for (size_t i = 0; i < v.size(); i++) ok[i] = v[i] && !v[i]->isBad();       // :194-198, :628-631, :648-652
+}
+}  // namespace b200
+
+// src/ORBmatcher.cc:159-288
+int ORBmatcher::SearchByBoW(KeyFrame* pKF, Frame& F, std::vector<MapPoint*>& vpMapPointMatches) {
+    const std::vector<MapPoint*> vpMapPointsKF = pKF->GetMapPointMatches();
+    vpMapPointMatches = std::vector<MapPoint*>(F.N, static_cast<MapPoint*>(NULL));
+    const b200::FlatFeatVec fvKF(pKF->mFeatVec), fvF(F.mFeatVec);
+    std::vector<float> aKF, aF;
+    std::vector<uint8_t> okKF;
+    b200::Angles(pKF->mvKeysUn, aKF); b200::Angles(F.mvKeys, aF); b200::Valid(vpMapPointsKF, okKF);
+    assert(pKF->mDescriptors.isContinuous() && F.mDescriptors.isContinuous());
+    std::vector<int32_t> match(std::max(F.N, 1));
+    int nmatches = 0;
+    b200::Check(orbm_search_by_bow(b200::MatcherContext(), ORBM_BOW_KEYFRAME_FRAME, pKF->mDescriptors.data, aKF.data(), okKF.data(),
+                                   (int)vpMapPointsKF.size(), &fvKF.fv, F.mDescriptors.data, aF.data(), NULL, F.N, &fvF.fv,
+                                   mfNNratio, mbCheckOrientation, match.data(), &nmatches),
+                "orbm_search_by_bow");
+    for (int iF = 0; iF < F.N; iF++)
+        if (match[iF] >= 0) vpMapPointMatches[iF] = vpMapPointsKF[match[iF]];                        // :232
+    return nmatches;
+}
+
+// src/ORBmatcher.cc:590-723
+int ORBmatcher::SearchByBoW(KeyFrame* pKF1, KeyFrame* pKF2, std::vector<MapPoint*>& vpMatches12) {
+    const std::vector<MapPoint*> vpMapPoints1 = pKF1->GetMapPointMatches();
+    const std::vector<MapPoint*> vpMapPoints2 = pKF2->GetMapPointMatches();
+    vpMatches12 = std::vector<MapPoint*>(vpMapPoints1.size(), static_cast<MapPoint*>(NULL));
+    const b200::FlatFeatVec fv1(pKF1->mFeatVec), fv2(pKF2->mFeatVec);
+    std::vector<float> a1, a2;
+    std::vector<uint8_t> ok1, ok2;
+    b200::Angles(pKF1->mvKeysUn, a1); b200::Angles(pKF2->mvKeysUn, a2);
+    b200::Valid(vpMapPoints1, ok1); b200::Valid(vpMapPoints2, ok2);
+    assert(pKF1->mDescriptors.isContinuous() && pKF2->mDescriptors.isContinuous());
+    std::vector<int32_t> match(std::max<size_t>(vpMapPoints1.size(), 1));
+    int nmatches = 0;
+    b200::Check(orbm_search_by_bow(b200::MatcherContext(), ORBM_BOW_KEYFRAME_KEYFRAME, pKF1->mDescriptors.data, a1.data(), ok1.data(),
+                                   (int)vpMapPoints1.size(), &fv1.fv, pKF2->mDescriptors.data, a2.data(), ok2.data(),
+                                   (int)vpMapPoints2.size(), &fv2.fv, mfNNratio, mbCheckOrientation, match.data(), &nmatches),
+                "orbm_search_by_bow");
+    for (size_t idx1 = 0; idx1 < vpMapPoints1.size(); idx1++)
+        if (match[idx1] >= 0) vpMatches12[idx1] = vpMapPoints2[match[idx1]];                        // :672
     return nmatches;
 }
 

@@ -7,6 +7,7 @@
 #include <cstddef>
 #include <vector>
 #include <opencv2/core/core.hpp>
+#include "Thirdparty/DBoW2/DBoW2/FeatureVector.h"
 #include "MapPoint.h"
 #include "ORBextractor.h"
 
@@ -41,6 +42,7 @@ public:
     std::vector<float> mvuRight;
     std::vector<float> mvDepth;
     cv::Mat mDescriptors, mDescriptorsRight;
+    DBoW2::FeatureVector mFeatVec;                 // include/Frame.h:149
     std::vector<MapPoint*> mvpMapPoints;
     std::vector<bool> mvbOutlier;
     static float mfGridElementWidthInv;

@@ -11,6 +11,7 @@
 #include "../../include/orbm.h"
 #include "hamming.cuh"
 #include "window.cuh"
+#include "bow.cuh"
 
 using namespace orbm;
 
@@ -195,3 +196,4 @@ int orbm_popc_peak(orbm_t* m, double* popc_per_s) {
 }  // extern "C"
 
 #include "window_host.inl"
+#include "bow_host.inl"

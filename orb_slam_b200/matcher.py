@@ -62,6 +62,33 @@ class Frame:
         return s
 
 
+class FeatVecStruct(C.Structure):
+    """orbm_featvec of include/orbm.h."""
+    _fields_ = [("nnodes", C.c_int32), ("node_ids", C.c_void_p), ("start", C.c_void_p), ("items", C.c_void_p)]
+
+
+class FeatureVector:
+    """DBoW2::FeatureVector (std::map<NodeId, std::vector<unsigned>>) flattened in map order for the C ABI.
+    Built from a dict {node_id: [feature indices]} or an iterable of (node_id, indices)."""
+
+    def __init__(self, nodes):
+        pairs = sorted(nodes.items() if hasattr(nodes, "items") else nodes, key=lambda kv: kv[0])
+        self.node_ids = np.array([k for k, _ in pairs], np.uint32)
+        lens = [len(v) for _, v in pairs]
+        self.start = np.zeros(len(pairs) + 1, np.int32)
+        if lens:
+            self.start[1:] = np.cumsum(lens)
+        self.items = (np.concatenate([np.asarray(v, np.uint32) for _, v in pairs]) if lens and sum(lens)
+                      else np.zeros(0, np.uint32))
+        self.items = np.ascontiguousarray(self.items, np.uint32)
+
+    def struct(self) -> FeatVecStruct:
+        s = FeatVecStruct()
+        s.nnodes = len(self.node_ids)
+        s.node_ids = self.node_ids.ctypes.data; s.start = self.start.ctypes.data; s.items = self.items.ctypes.data
+        return s
+
+
 def _bind(L):
     if getattr(L, "_orbm_bound", False):
         return
@@ -84,6 +111,8 @@ def _bind(L):
     L.orbm_search_by_projection_frame.restype = i
     L.orbm_search_by_projection_points.argtypes = [vp, vp, vp, i, vp, f, f, vp, C.POINTER(i)]
     L.orbm_search_by_projection_points.restype = i
+    L.orbm_search_by_bow.argtypes = [vp, i, vp, vp, vp, i, vp, vp, vp, vp, i, vp, f, i, vp, C.POINTER(i)]
+    L.orbm_search_by_bow.restype = i
     L._orbm_bound = True
 
 
@@ -189,3 +218,26 @@ class ORBmatcher:
                                                     self.mfNNratio, out.ctypes.data, C.byref(n)),
               "orbm_search_by_projection_points")
         return n.value, out[: F.N]
+
+    def _bow(self, variant, desc1, angle1, valid1, fv1: FeatureVector, desc2, angle2, valid2, fv2: FeatureVector):
+        c = self._c()
+        d1 = np.ascontiguousarray(desc1, np.uint8).reshape(-1, 32); d2 = np.ascontiguousarray(desc2, np.uint8).reshape(-1, 32)
+        a1 = np.ascontiguousarray(angle1, np.float32); a2 = np.ascontiguousarray(angle2, np.float32)
+        v1 = np.ascontiguousarray(valid1, np.uint8)
+        v2 = np.ascontiguousarray(valid2, np.uint8) if valid2 is not None else None
+        out = np.zeros(max(len(d2) if variant == 0 else len(d1), 1), np.int32); n = C.c_int()
+        s1, s2 = fv1.struct(), fv2.struct()
+        check(c._L.orbm_search_by_bow(c.h, variant, d1.ctypes.data, a1.ctypes.data, v1.ctypes.data, len(d1), C.byref(s1),
+                                      d2.ctypes.data, a2.ctypes.data, v2.ctypes.data if v2 is not None else None, len(d2),
+                                      C.byref(s2), self.mfNNratio, int(self.mbCheckOrientation), out.ctypes.data, C.byref(n)),
+              "orbm_search_by_bow")
+        return n.value, out[: (len(d2) if variant == 0 else len(d1))]
+
+    def SearchByBoWFrame(self, descKF, angleKFun, validKF, fvKF: FeatureVector, descF, angleF, fvF: FeatureVector):
+        """SearchByBoW(KeyFrame* pKF, Frame& F, vpMapPointMatches) (src/ORBmatcher.cc:159-288).  Returns (nmatches,
+        match) with match[iF] = key-frame feature index whose map point lands in vpMapPointMatches[iF], -1 for NULL."""
+        return self._bow(0, descKF, angleKFun, validKF, fvKF, descF, angleF, None, fvF)
+
+    def SearchByBoWKeyFrames(self, desc1, angle1, valid1, fv1: FeatureVector, desc2, angle2, valid2, fv2: FeatureVector):
+        """SearchByBoW(KeyFrame* pKF1, KeyFrame* pKF2, vpMatches12) (:590-723).  match[idx1] = idx2 or -1."""
+        return self._bow(1, desc1, angle1, valid1, fv1, desc2, angle2, valid2, fv2)

@@ -194,4 +194,57 @@ int dropin_search_by_projection_points(const orbm_frame* f, const orbm_mappoint*
     return n;
 }
 
+static void keyframe_from(KeyFrame& K, std::vector<MapPoint>& store, const uint8_t* desc, const float* angle, const uint8_t* valid,
+                          const uint8_t* bad, int n, const orbm_featvec* fv) {
+    K.mvKeysUn.resize(n);
+    K.mDescriptors.create(n, 32, CV_8U);
+    if (n) std::memcpy(K.mDescriptors.data, desc, (size_t)n * 32);
+    store.resize(n);
+    K.mvpMapPoints.assign(n, static_cast<MapPoint*>(NULL));
+    for (int i = 0; i < n; i++) {
+        K.mvKeysUn[i].angle = angle[i];
+        if (valid[i] || bad[i]) { store[i].mbBad = bad[i] != 0; K.mvpMapPoints[i] = &store[i]; }   // NULL, bad and good map points
+    }
+    for (int k = 0; k < fv->nnodes; k++)
+        for (int t = fv->start[k]; t < fv->start[k + 1]; t++) K.mFeatVec.addFeature(fv->node_ids[k], fv->items[t]);
+}
+
+// ORBmatcher::SearchByBoW(KeyFrame*, Frame&, vpMapPointMatches) as Tracking::TrackReferenceKeyFrame / Relocalization call it
+// (Tracking.cc:760-768, :1370-1378).  valid1[i] = good map point, bad1[i] = map point present but isBad().
+int dropin_search_by_bow_frame(const uint8_t* desc1, const float* angle1, const uint8_t* valid1, const uint8_t* bad1, int n1,
+                               const orbm_featvec* fv1, const uint8_t* desc2, const float* angle2, int n2, const orbm_featvec* fv2,
+                               float nnratio, int checkOri, int32_t* match) {
+    KeyFrame K; std::vector<MapPoint> store;
+    keyframe_from(K, store, desc1, angle1, valid1, bad1, n1, fv1);
+    Frame F;
+    F.N = n2;
+    F.mvKeys.resize(n2);
+    for (int i = 0; i < n2; i++) F.mvKeys[i].angle = angle2[i];
+    F.mDescriptors.create(n2, 32, CV_8U);
+    if (n2) std::memcpy(F.mDescriptors.data, desc2, (size_t)n2 * 32);
+    for (int k = 0; k < fv2->nnodes; k++)
+        for (int t = fv2->start[k]; t < fv2->start[k + 1]; t++) F.mFeatVec.addFeature(fv2->node_ids[k], fv2->items[t]);
+    std::vector<MapPoint*> vpMapPointMatches(3, reinterpret_cast<MapPoint*>(8));      // must be replaced, not appended to
+    ORBmatcher matcher(nnratio, checkOri != 0);
+    const int n = matcher.SearchByBoW(&K, F, vpMapPointMatches);
+    if ((int)vpMapPointMatches.size() != n2) return -1000;
+    for (int i = 0; i < n2; i++) match[i] = vpMapPointMatches[i] ? (int32_t)(vpMapPointMatches[i] - store.data()) : -1;
+    return n;
+}
+
+// ORBmatcher::SearchByBoW(KeyFrame*, KeyFrame*, vpMatches12) as LoopClosing::ComputeSim3 calls it (LoopClosing.cc:262)
+int dropin_search_by_bow_keyframes(const uint8_t* desc1, const float* angle1, const uint8_t* valid1, const uint8_t* bad1, int n1,
+                                   const orbm_featvec* fv1, const uint8_t* desc2, const float* angle2, const uint8_t* valid2,
+                                   const uint8_t* bad2, int n2, const orbm_featvec* fv2, float nnratio, int checkOri, int32_t* match) {
+    KeyFrame K1, K2; std::vector<MapPoint> s1, s2;
+    keyframe_from(K1, s1, desc1, angle1, valid1, bad1, n1, fv1);
+    keyframe_from(K2, s2, desc2, angle2, valid2, bad2, n2, fv2);
+    std::vector<MapPoint*> vpMatches12;
+    ORBmatcher matcher(nnratio, checkOri != 0);
+    const int n = matcher.SearchByBoW(&K1, &K2, vpMatches12);
+    if ((int)vpMatches12.size() != n1) return -1000;
+    for (int i = 0; i < n1; i++) match[i] = vpMatches12[i] ? (int32_t)(vpMatches12[i] - s2.data()) : -1;
+    return n;
+}
+
 }  // extern "C"

@@ -173,6 +173,8 @@ def _bind_matcher(L):
     L.orbo_search_by_projection_frame.argtypes = [vp, vp, vp, vp, f, i, i, vp]
     L.orbo_search_by_projection_points.argtypes = [vp, vp, i, vp, f, f, vp]
     L.orbo_bf2nn.argtypes = [vp, i, vp, C.c_size_t, C.c_uint32, vp]
+    L.orbo_search_by_bow_kf_frame.argtypes = [vp, vp, vp, i, vp, vp, vp, i, vp, f, i, vp]
+    L.orbo_search_by_bow_kf_kf.argtypes = [vp, vp, vp, i, vp, vp, vp, vp, i, vp, f, i, vp]
     L._m_bound = True
     return L
 
@@ -235,3 +237,24 @@ class OracleMatcher:
         out = np.zeros(len(q), np.dtype([("i1", "<u4"), ("d1", "<u2"), ("d2", "<u2")]))
         self.L.orbo_bf2nn(q.ctypes.data, len(q), db.ctypes.data, len(db), idx_base, out.ctypes.data)
         return out
+
+    def SearchByBoWFrame(self, descKF, angleKFun, validKF, fvKF, descF, angleF, fvF):
+        d1 = np.ascontiguousarray(descKF, np.uint8).reshape(-1, 32); d2 = np.ascontiguousarray(descF, np.uint8).reshape(-1, 32)
+        a1 = np.ascontiguousarray(angleKFun, np.float32); a2 = np.ascontiguousarray(angleF, np.float32)
+        v1 = np.ascontiguousarray(validKF, np.uint8)
+        out = np.zeros(max(len(d2), 1), np.int32)
+        s1, s2 = fvKF.struct(), fvF.struct()
+        n = self.L.orbo_search_by_bow_kf_frame(d1.ctypes.data, a1.ctypes.data, v1.ctypes.data, len(d1), C.byref(s1), d2.ctypes.data,
+                                               a2.ctypes.data, len(d2), C.byref(s2), self.nnratio, int(self.checkOri), out.ctypes.data)
+        return n, out[: len(d2)]
+
+    def SearchByBoWKeyFrames(self, desc1, angle1, valid1, fv1, desc2, angle2, valid2, fv2):
+        d1 = np.ascontiguousarray(desc1, np.uint8).reshape(-1, 32); d2 = np.ascontiguousarray(desc2, np.uint8).reshape(-1, 32)
+        a1 = np.ascontiguousarray(angle1, np.float32); a2 = np.ascontiguousarray(angle2, np.float32)
+        v1 = np.ascontiguousarray(valid1, np.uint8); v2 = np.ascontiguousarray(valid2, np.uint8)
+        out = np.zeros(max(len(d1), 1), np.int32)
+        s1, s2 = fv1.struct(), fv2.struct()
+        n = self.L.orbo_search_by_bow_kf_kf(d1.ctypes.data, a1.ctypes.data, v1.ctypes.data, len(d1), C.byref(s1), d2.ctypes.data,
+                                            a2.ctypes.data, v2.ctypes.data, len(d2), C.byref(s2), self.nnratio, int(self.checkOri),
+                                            out.ctypes.data)
+        return n, out[: len(d1)]

@@ -71,3 +71,48 @@ def local_map_points(F: Frame, seed=0):
     pts["trackScaleLevel"] = np.clip(F.mvKeysUn["octave"] + rng.integers(0, 2, n), 0, 7)
     pts["observations"] = rng.integers(0, 4, n)
     return pts
+
+
+def bow_scene(seed=0, n1=1500, n2=1600, *, n_nodes=64, p_common=0.7, flips=12, p_valid=0.8, rotation=25.0, ties=0):
+    """Two descriptor sets with a synthetic vocabulary for ORBmatcher::SearchByBoW: side 2 holds noisy copies (up to
+    `flips` flipped bits) of a share of side 1 plus unrelated descriptors; a feature's node is a hash of a few
+    descriptor bits (so some true pairs land in different nodes, as with a real vocabulary tree); feature vectors
+    list the features of a node in ascending index (DBoW2 appends them in feature order).  `ties` duplicates that
+    many side-2 descriptors inside their node so equal distances occur.  Returns a dict of arrays + FeatureVectors."""
+    from orb_slam_b200.matcher import FeatureVector
+    rng = np.random.default_rng(seed)
+    d1 = rng.integers(0, 256, (n1, 32), dtype=np.uint8)
+    d2 = rng.integers(0, 256, (n2, 32), dtype=np.uint8)
+    ncommon = int(min(n1, n2) * p_common)
+    src = rng.permutation(n1)[:ncommon]
+    dst = rng.permutation(n2)[:ncommon]
+    for a, b in zip(src, dst):
+        d = d1[a].copy()
+        for bit in rng.integers(0, 256, rng.integers(0, flips + 1)):
+            d[bit >> 3] ^= np.uint8(1 << (bit & 7))
+        d2[b] = d
+    for _ in range(ties):
+        if n2 >= 2:
+            a, b = rng.integers(0, n2, 2)
+            d2[b] = d2[a]
+    a1 = rng.uniform(0, 360, n1).astype(np.float32)
+    a2 = rng.uniform(0, 360, n2).astype(np.float32)
+    a2[dst] = ((a1[src] - np.float32(rotation) + rng.normal(0, 3, ncommon)) % 360).astype(np.float32)
+
+    def node_of(d):
+        return ((d[:, 0].astype(np.uint32) ^ (d[:, 7].astype(np.uint32) << 1)) % np.uint32(max(n_nodes, 1))) * 3 + 11
+
+    def featvec(d, drop):
+        nodes = {}
+        for i, nd in enumerate(node_of(d)):
+            if nd in drop:
+                continue
+            nodes.setdefault(int(nd), []).append(i)
+        return FeatureVector(nodes)
+
+    ids = np.unique(np.concatenate([node_of(d1), node_of(d2)])) if n1 + n2 else np.zeros(0, np.uint32)
+    drop1 = set(int(x) for x in ids[rng.random(len(ids)) < 0.1])       # nodes missing on one side exercise lower_bound
+    drop2 = set(int(x) for x in ids[rng.random(len(ids)) < 0.1])
+    v1 = (rng.random(n1) < p_valid).astype(np.uint8)
+    v2 = (rng.random(n2) < p_valid).astype(np.uint8)
+    return dict(desc1=d1, desc2=d2, angle1=a1, angle2=a2, valid1=v1, valid2=v2, fv1=featvec(d1, drop1), fv2=featvec(d2, drop2))

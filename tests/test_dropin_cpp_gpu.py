@@ -158,3 +158,28 @@ def test_stereo_frame_constructor_path(H):
     # boundary), which can flip a coarse match: allow that fraction of rows to differ, demand the rest bit-exact
     same = (u[:n] == ou) & (z[:n] == oz)
     assert same.mean() >= 0.995 and kept > 0.3 * n
+
+
+@pytest.mark.parametrize("seed", [21, 22])
+def test_search_by_bow_members(H, seed):
+    """ORBmatcher::SearchByBoW(KeyFrame*, Frame&, ...) and (KeyFrame*, KeyFrame*, ...) members; map points NULL, bad and good"""
+    s = scenes.bow_scene(seed=seed, n1=1400, n2=1500, n_nodes=80, ties=40)
+    rng = np.random.default_rng(seed)
+    bad1 = ((s["valid1"] == 0) & (rng.random(len(s["valid1"])) < 0.5)).astype(np.uint8)      # some of the unusable ones are bad, the rest NULL
+    bad2 = ((s["valid2"] == 0) & (rng.random(len(s["valid2"])) < 0.5)).astype(np.uint8)
+    p = lambda a: C.c_void_p(a.ctypes.data)
+    f1, f2 = s["fv1"].struct(), s["fv2"].struct()
+    n1, n2 = len(s["desc1"]), len(s["desc2"])
+    m = np.zeros(n2, np.int32)
+    n = H.dropin_search_by_bow_frame(p(s["desc1"]), p(s["angle1"]), p(s["valid1"]), p(bad1), n1, C.byref(f1), p(s["desc2"]),
+                                     p(s["angle2"]), n2, C.byref(f2), C.c_float(0.7), 1, p(m))
+    on, om = OracleMatcher(0.7, True).SearchByBoWFrame(s["desc1"], s["angle1"], s["valid1"], s["fv1"], s["desc2"], s["angle2"], s["fv2"])
+    assert n == on and n > 50
+    np.testing.assert_array_equal(m, om)
+    m12 = np.zeros(n1, np.int32)
+    n = H.dropin_search_by_bow_keyframes(p(s["desc1"]), p(s["angle1"]), p(s["valid1"]), p(bad1), n1, C.byref(f1), p(s["desc2"]),
+                                         p(s["angle2"]), p(s["valid2"]), p(bad2), n2, C.byref(f2), C.c_float(0.8), 1, p(m12))
+    on, om = OracleMatcher(0.8, True).SearchByBoWKeyFrames(s["desc1"], s["angle1"], s["valid1"], s["fv1"], s["desc2"], s["angle2"],
+                                                           s["valid2"], s["fv2"])
+    assert n == on and n > 50
+    np.testing.assert_array_equal(m12, om)
