@@ -325,30 +325,53 @@ def run_stereo_frontend(local_rank, with_cpu):
     def gpu_stereo(kl, dl, kr, dr):
         return exL.stereo_match(exR, kl, dl, kr, dr, mbf, mb)
 
+    def featvec(d):
+        # synthetic vocabulary: a feature's node is a hash of a few descriptor bits (no ORBvoc file on this box)
+        from orb_slam_b200.matcher import FeatureVector
+        nodes = {}
+        for i, nd in enumerate(((d[:, 0].astype(np.uint32) ^ (d[:, 7].astype(np.uint32) << 1)) % np.uint32(100)).tolist()):
+            nodes.setdefault(nd, []).append(i)
+        return FeatureVector(nodes)
+
+    def bow_inputs(cur, last):
+        (kc, dc), (kl, dl) = cur, last
+        valid = (np.arange(len(dl)) % 5 != 0).astype(np.uint8)                 # 80 % of the key frame's features hold a map point
+        return dl, kl["angle"].astype(np.float32), valid, featvec(dl), dc, kc["angle"].astype(np.float32), featvec(dc)
+
     def gpu_proj(cur, lastF, pts, obs):
         return ORBmatcher(0.9, True, ctx).SearchByProjectionFrame(cur, lastF, pts, obs, 7.0, False)[0]
 
-    def loop(a, b, stereo, proj, reps):
-        ts, last, counts = [], None, None
+    def loop(a, b, stereo, proj, bow, reps):
+        ts, last, counts, prev_kd = [], None, None, None
         for i in range(reps):
             l, r = pairs[i % len(pairs)]
             t, (cur, kl, dl), n, nm = one(l, r, a, b, stereo, proj, last)
+            tb, nb = 0.0, 0
+            if prev_kd is not None:                  # TrackReferenceKeyFrame's SearchByBoW(last as key frame, current frame)
+                args = bow_inputs((kl, dl), prev_kd)
+                t5 = time.perf_counter()
+                nb = bow(*args)
+                tb = time.perf_counter() - t5
+            prev_kd = (kl, dl)
+            t = t + (tb,)
             if i == 7:
-                counts = (int(n), int(nm))           # same pair and map points in both arms: the counts must agree
+                counts = (int(n), int(nm), int(nb))  # same pair and map points in both arms: the counts must agree
             pts = scenes.last_frame_points(cur, seed=i)
             last = (cur, pts, np.full(cur.N, -1, np.int32))
             ts.append(t)
         ts = np.array(ts[2:]) * 1e3
         return {"extract_pair_ms": float(np.median(ts[:, 0])), "stereo_match_ms": float(np.median(ts[:, 1])),
-                "search_by_projection_ms": float(np.median(ts[:, 2])), "stereo_matches": counts[0], "projection_matches": counts[1]}
+                "search_by_projection_ms": float(np.median(ts[:, 2])), "search_by_bow_ms": float(np.median(ts[:, 3])),
+                "stereo_matches": counts[0], "projection_matches": counts[1], "bow_matches": counts[2]}
 
-    out["b200"] = loop(exL, exR, gpu_stereo, gpu_proj, 24)
+    out["b200"] = loop(exL, exR, gpu_stereo, gpu_proj, lambda *x: ORBmatcher(0.7, True, ctx).SearchByBoWFrame(*x)[0], 24)
     if with_cpu:
         from tests import oracle_lib
         oa, ob = oracle_lib.OracleExtractor(NFEAT, 1.2, 8, 20, 7), oracle_lib.OracleExtractor(NFEAT, 1.2, 8, 20, 7)
         om = oracle_lib.OracleMatcher(0.9, True)
         out["cpu_port"] = loop(oa, ob, lambda kl, dl, kr, dr: oracle_lib.oracle_stereo_matches(oa, ob, kl, dl, kr, dr, mbf, mb),
-                               lambda cur, lastF, pts, obs: om.SearchByProjectionFrame(cur, lastF, pts, obs, 7.0, False)[0], 8)
+                               lambda cur, lastF, pts, obs: om.SearchByProjectionFrame(cur, lastF, pts, obs, 7.0, False)[0],
+                               lambda *x: oracle_lib.OracleMatcher(0.7, True).SearchByBoWFrame(*x)[0], 8)
     exL.close(); exR.close(); ctx.close()
     return out
 
