@@ -123,6 +123,24 @@ int orbm_search_by_projection_points(orbm_t* m, const orbm_frame* F, const orbm_
                                      const int32_t* frame_observations, float th, float nnratio,
                                      int32_t* frame_assign, int* nmatches);
 
+/* ORBmatcher::SearchByProjection(CurrentFrame, pKF, sAlreadyFound, th, ORBdist) (src/ORBmatcher.cc:1540-1667,
+ * called from Tracking::Relocalization).  kf_points[i] describes pKF->GetMapPointMatches()[i] (world, descriptor,
+ * valid = pointer non-NULL, bad = isBad()); min/max_distance_inv[i] = GetMin/MaxDistanceInvariance() of that point;
+ * already_found[i] = sAlreadyFound.count(pMP); kf_angle[i] = pKF->mvKeysUn[i].angle; cur_has_point[i2] =
+ * CurrentFrame.mvpMapPoints[i2] != NULL.  The predicted scale level is MapPoint::PredictScale(dist3D, &CurrentFrame)
+ * (src/MapPoint.cc:402-417): supplied by `predict` when non-NULL (the C++ binding calls the map point's own method,
+ * whose mfMaxDistance is not publicly readable), otherwise evaluated from max_distance[i] (= mfMaxDistance) and
+ * log_scale_factor (= Frame::mfLogScaleFactor) with cur->nScaleLevels.
+ * cur_assign[i2] out: -2 untouched, -1 set to NULL by the rotation check, else index i of the key-frame point now
+ * stored in CurrentFrame.mvpMapPoints[i2]. */
+typedef int (*orbm_predict_scale_fn)(void* user, int i, float dist3D);
+int orbm_search_by_projection_keyframe(orbm_t* m, const orbm_frame* cur, const orbm_mappoint* kf_points, int npoints,
+                                       const float* min_distance_inv, const float* max_distance_inv,
+                                       const float* max_distance, float log_scale_factor,
+                                       orbm_predict_scale_fn predict, void* user,
+                                       const uint8_t* already_found, const float* kf_angle, const uint8_t* cur_has_point,
+                                       float th, int ORBdist, int checkOrientation, int32_t* cur_assign, int* nmatches);
+
 /* ---- ORBmatcher::SearchByBoW.  A DBoW2::FeatureVector (std::map<NodeId,
  * std::vector<unsigned>>) flattened in map order: node ids ascending, start[k]..start[k+1] = the
  * node's feature indices in their vector order. */

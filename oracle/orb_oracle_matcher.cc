@@ -4,7 +4,8 @@
 //   ORBmatcher::DescriptorDistance       src/ORBmatcher.cc:1728-1744
 //   ORBmatcher::ComputeThreeMaxima       src/ORBmatcher.cc:1679-1723
 //   ORBmatcher::SearchForInitialization  src/ORBmatcher.cc:417-588
-//   ORBmatcher::SearchByProjection       src/ORBmatcher.cc:1396-1538 (Frame,Frame) and :45-129 (Frame,MapPoints)
+//   ORBmatcher::SearchByProjection       src/ORBmatcher.cc:1396-1538 (Frame,Frame), :45-129 (Frame,MapPoints) and
+//                                        :1540-1667 (Frame,KeyFrame; with MapPoint::PredictScale src/MapPoint.cc:402-417)
 //   Frame::AssignFeaturesToGrid / PosInGrid / GetFeaturesInArea   src/Frame.cc:292-311, :504-518, :410-495
 // plus the exhaustive 2-NN of SURVEY §8(a) M6.  Plain sequential loops over the
 // reference's own data layout (vector<size_t> mGrid[64][48]); the data-carrier
@@ -245,6 +246,73 @@ int orbo_search_by_projection_frame(const orbm_frame* C, const orbm_frame* Lf, c
             curAssign[bestIdx2] = i; obs[bestIdx2] = lp[i].observations;
             nmatches++;
             if (checkOri) rotHist[rot_bin(Lf->keysUn[i].angle, C->keysUn[bestIdx2].angle)].push_back(bestIdx2);
+        }
+    }
+    if (checkOri) {
+        int ind1 = -1, ind2 = -1, ind3 = -1;
+        ComputeThreeMaxima(rotHist, HISTO_LENGTH, ind1, ind2, ind3);
+        for (int i = 0; i < HISTO_LENGTH; i++)
+            if (i != ind1 && i != ind2 && i != ind3)
+                for (int idx : rotHist[i]) { curAssign[idx] = -1; nmatches--; }
+    }
+    return nmatches;
+}
+
+// ORBmatcher::SearchByProjection(CurrentFrame, pKF, sAlreadyFound, th, ORBdist), src/ORBmatcher.cc:1540-1667, with
+// MapPoint::GetMin/MaxDistanceInvariance (src/MapPoint.cc:373-383) and MapPoint::PredictScale(dist, Frame*) (:402-417)
+// evaluated from mfMinDistance / mfMaxDistance (minMaxDistance[2*i], [2*i+1]) and Frame::mfLogScaleFactor.
+int orbo_search_by_projection_keyframe(const orbm_frame* C, const orbm_mappoint* vpMPs, int n, const float* minMaxDistance,
+                                       float mfLogScaleFactor, const uint8_t* sAlreadyFound, const float* kfAngle,
+                                       const uint8_t* curHasPoint, float th, int ORBdist, int checkOri, int32_t* curAssign) {
+    Grid g; AssignFeaturesToGrid(*C, g);
+    int nmatches = 0;
+    const float* Tc = C->Tcw;
+    const float tcw[3] = {Tc[3], Tc[7], Tc[11]};
+    float Ow[3];
+    for (int i = 0; i < 3; i++) {
+        double s = 0;
+        for (int k = 0; k < 3; k++) s += (double)Tc[4 * k + i] * (double)tcw[k];
+        Ow[i] = (float)(s * -1.0);
+    }
+    std::vector<int> rotHist[HISTO_LENGTH];
+    std::vector<uint8_t> has(curHasPoint, curHasPoint + C->N);
+    for (int i = 0; i < C->N; i++) curAssign[i] = -2;
+    for (int i = 0; i < n; i++) {
+        if (!vpMPs[i].valid) continue;
+        if (vpMPs[i].bad || sAlreadyFound[i]) continue;
+        float x3Dc[3];
+        mul3(Tc, vpMPs[i].world, tcw, x3Dc);
+        const float xc = x3Dc[0], yc = x3Dc[1];
+        const float invzc = (float)(1.0 / x3Dc[2]);
+        const float u = C->fx * xc * invzc + C->cx;
+        const float v = C->fy * yc * invzc + C->cy;
+        if (u < C->mnMinX || u > C->mnMaxX) continue;
+        if (v < C->mnMinY || v > C->mnMaxY) continue;
+        float PO[3];
+        for (int k = 0; k < 3; k++) PO[k] = vpMPs[i].world[k] - Ow[k];
+        double nrm = 0;                                      // cv::norm, NORM_L2 on CV_32F: double accumulator
+        for (int k = 0; k < 3; k++) nrm += (double)PO[k] * (double)PO[k];
+        const float dist3D = (float)std::sqrt(nrm);
+        const float maxDistance = 1.2f * minMaxDistance[2 * i + 1];
+        const float minDistance = 0.8f * minMaxDistance[2 * i];
+        if (dist3D < minDistance || dist3D > maxDistance) continue;
+        const float ratio = minMaxDistance[2 * i + 1] / dist3D;
+        int nPredictedLevel = (int)std::ceil(std::log(ratio) / mfLogScaleFactor);
+        if (nPredictedLevel < 0) nPredictedLevel = 0;
+        else if (nPredictedLevel >= C->nScaleLevels) nPredictedLevel = C->nScaleLevels - 1;
+        const float radius = th * C->scaleFactors[nPredictedLevel];
+        const std::vector<size_t> vIndices2 = GetFeaturesInArea(*C, g, u, v, radius, nPredictedLevel - 1, nPredictedLevel + 1);
+        if (vIndices2.empty()) continue;
+        int bestDist = 256, bestIdx2 = -1;
+        for (size_t i2 : vIndices2) {
+            if (has[i2]) continue;
+            const int dist = DescriptorDistance(vpMPs[i].descriptor, C->descriptors + 32 * i2);
+            if (dist < bestDist) { bestDist = dist; bestIdx2 = (int)i2; }
+        }
+        if (bestDist <= ORBdist) {
+            curAssign[bestIdx2] = i; has[bestIdx2] = 1;
+            nmatches++;
+            if (checkOri) rotHist[rot_bin(kfAngle[i], C->keysUn[bestIdx2].angle)].push_back(bestIdx2);
         }
     }
     if (checkOri) {

@@ -166,6 +166,46 @@ static void Valid(const std::vector<MapPoint*>& v, std::vector<uint8_t>& ok) {
 }
 }  // namespace b200
 
+// src/ORBmatcher.cc:1540-1667 (Tracking::Relocalization)
+namespace b200 {
+struct PredictCtx { const std::vector<MapPoint*>* pts; Frame* F; };
+static int PredictThunk(void* user, int i, float dist3D) {
+    PredictCtx* c = static_cast<PredictCtx*>(user);
+    return (*c->pts)[i]->PredictScale(dist3D, c->F);                       // :1593, the map point's own method
+}
+}  // namespace b200
+
+int ORBmatcher::SearchByProjection(Frame& CurrentFrame, KeyFrame* pKF, const std::set<MapPoint*>& sAlreadyFound, const float th,
+                                   const int ORBdist) {
+    orbm_frame cur;
+    b200::FillFrame(cur, CurrentFrame);
+    const std::vector<MapPoint*> vpMPs = pKF->GetMapPointMatches();
+    const size_t n = vpMPs.size();
+    std::vector<orbm_mappoint> pts(n);
+    std::vector<float> minInv(n), maxInv(n), kfAngle(n);
+    std::vector<uint8_t> found(n), has(std::max(CurrentFrame.N, 1));
+    for (size_t i = 0; i < n; i++) {
+        b200::FillPoint(pts[i], vpMPs[i]);
+        kfAngle[i] = pKF->mvKeysUn[i].angle;
+        if (!vpMPs[i]) continue;
+        minInv[i] = vpMPs[i]->GetMinDistanceInvariance(); maxInv[i] = vpMPs[i]->GetMaxDistanceInvariance();
+        found[i] = sAlreadyFound.count(vpMPs[i]) ? 1 : 0;
+    }
+    for (int i2 = 0; i2 < CurrentFrame.N; i2++) has[i2] = CurrentFrame.mvpMapPoints[i2] != NULL;
+    std::vector<int32_t> assign(std::max(CurrentFrame.N, 1), -2);
+    b200::PredictCtx pc = {&vpMPs, &CurrentFrame};
+    int nmatches = 0;
+    b200::Check(orbm_search_by_projection_keyframe(b200::MatcherContext(), &cur, pts.data(), (int)n, minInv.data(), maxInv.data(),
+                                                   NULL, 0.f, b200::PredictThunk, &pc, found.data(), kfAngle.data(), has.data(), th,
+                                                   ORBdist, mbCheckOrientation, assign.data(), &nmatches),
+                "orbm_search_by_projection_keyframe");
+    for (int i2 = 0; i2 < CurrentFrame.N; i2++) {
+        if (assign[i2] >= 0) CurrentFrame.mvpMapPoints[i2] = vpMPs[assign[i2]];                     // :1629
+        else if (assign[i2] == -1) CurrentFrame.mvpMapPoints[i2] = static_cast<MapPoint*>(NULL);   // :1660
+    }
+    return nmatches;
+}
+
 // src/ORBmatcher.cc:159-288
 int ORBmatcher::SearchByBoW(KeyFrame* pKF, Frame& F, std::vector<MapPoint*>& vpMapPointMatches) {
     const std::vector<MapPoint*> vpMapPointsKF = pKF->GetMapPointMatches();

@@ -6,6 +6,7 @@
 #define FRAME_H
 #include <cstddef>
 #include <vector>
+#include <cmath>
 #include <opencv2/core/core.hpp>
 #include "Thirdparty/DBoW2/DBoW2/FeatureVector.h"
 #include "MapPoint.h"
@@ -51,9 +52,20 @@ public:
     cv::Mat mTcw;
     std::vector<float> mvScaleFactors;
     std::vector<float> mvInvScaleFactors;
+    int mnScaleLevels;                             // include/Frame.h:176-178
+    float mfScaleFactor;
+    float mfLogScaleFactor;
     static float mnMinX, mnMaxX, mnMinY, mnMaxY;
     static bool mbInitialComputations;
 };
+
+inline int MapPoint::PredictScale(const float& currentDist, Frame* pF) {
+    const float ratio = mfMaxDistance / currentDist;
+    int nScale = (int)std::ceil(std::log(ratio) / pF->mfLogScaleFactor);
+    if (nScale < 0) nScale = 0;
+    else if (nScale >= pF->mnScaleLevels) nScale = pF->mnScaleLevels - 1;
+    return nScale;
+}
 
 }  // namespace ORB_SLAM2
 #endif

@@ -8,14 +8,20 @@
 
 namespace ORB_SLAM2 {
 
+class Frame;
+
 class MapPoint {
 public:
     MapPoint() : mTrackProjX(0), mTrackProjY(0), mTrackProjXR(0), mbTrackInView(false), mnTrackScaleLevel(0),
-                 mTrackViewCos(0), mnLastFrameSeen(0), mWorldPos(3, 1, CV_32F), mDescriptor(1, 32, CV_8U), nObs(0), mbBad(false) {}
+                 mTrackViewCos(0), mnLastFrameSeen(0), mWorldPos(3, 1, CV_32F), mDescriptor(1, 32, CV_8U), nObs(0), mbBad(false),
+                 mfMinDistance(0), mfMaxDistance(0) {}
     cv::Mat GetWorldPos() { return mWorldPos.clone(); }
     cv::Mat GetDescriptor() { return mDescriptor.clone(); }
     int Observations() { return nObs; }
     bool isBad() { return mbBad; }
+    float GetMinDistanceInvariance() { return 0.8f * mfMinDistance; }      // src/MapPoint.cc:373-383
+    float GetMaxDistanceInvariance() { return 1.2f * mfMaxDistance; }
+    int PredictScale(const float& currentDist, Frame* pF);                // src/MapPoint.cc:402-417 (defined in lite/Frame.h)
 
     // Variables used by the tracking (include/MapPoint.h:92-99)
     float mTrackProjX;
@@ -31,6 +37,7 @@ public:
     cv::Mat mDescriptor;
     int nObs;
     bool mbBad;
+    float mfMinDistance, mfMaxDistance;
 };
 
 }  // namespace ORB_SLAM2

@@ -20,9 +20,10 @@ public:
     int SearchByProjection(Frame& CurrentFrame, const Frame& LastFrame, const float th, const bool bMono);
     int SearchForInitialization(Frame& F1, Frame& F2, std::vector<cv::Point2f>& vbPrevMatched,
                                 std::vector<int>& vnMatches12, int windowSize = 10);
+    int SearchByProjection(Frame& CurrentFrame, KeyFrame* pKF, const std::set<MapPoint*>& sAlreadyFound, const float th, const int ORBdist);
     int SearchByBoW(KeyFrame* pKF, Frame& F, std::vector<MapPoint*>& vpMapPointMatches);
     int SearchByBoW(KeyFrame* pKF1, KeyFrame* pKF2, std::vector<MapPoint*>& vpMatches12);
-    // SearchByProjection(Frame&, KeyFrame*, ...), SearchByProjection(KeyFrame*, Scw, ...), SearchForTriangulation,
+    // SearchByProjection(KeyFrame*, Scw, ...), SearchForTriangulation,
     // SearchBySim3, Fuse x2: SURVEY 8(f) "next" rows - they stay the reference's own code.
 public:
     static const int TH_LOW;

@@ -327,4 +327,92 @@ int orbm_search_by_projection_points(orbm_t* m, const orbm_frame* F, const orbm_
     return ORBX_OK;
 }
 
+// ORBmatcher::SearchByProjection(CurrentFrame, pKF, sAlreadyFound, th, ORBdist), src/ORBmatcher.cc:1540-1667
+int orbm_search_by_projection_keyframe(orbm_t* m, const orbm_frame* cur, const orbm_mappoint* pts, int npts,
+                                       const float* minInv, const float* maxInv, const float* maxDistance, float logScaleFactor,
+                                       orbm_predict_scale_fn predict, void* user, const uint8_t* alreadyFound,
+                                       const float* kfAngle, const uint8_t* curHasPoint, float th, int ORBdist, int checkOri,
+                                       int32_t* curAssign, int* nmatchesOut) {
+    if (!m || !cur || (!pts && npts) || npts < 0 || !curAssign || !nmatchesOut || (cur->N > 0 && !curHasPoint)) return ORBX_E_INVALID;
+    if (npts > 0 && (!minInv || !maxInv || !alreadyFound || !kfAngle || (!predict && !maxDistance))) return ORBX_E_INVALID;
+    if (cur->nScaleLevels <= 0) return ORBX_E_INVALID;
+    std::lock_guard<std::mutex> lk(m->mtx);
+    CKM(cudaSetDevice(m->device));
+    DeviceFrame d;
+    int rc = upload_frame(m, cur, d);
+    if (rc) return rc;
+    const float* Tc = cur->Tcw;
+    const float tcw[3] = {Tc[3], Tc[7], Tc[11]};
+    float Ow[3];                                           // -Rcw.t()*tcw (general gemm path: double accumulation)
+    for (int i = 0; i < 3; i++) {
+        double s = 0;
+        for (int k = 0; k < 3; k++) s += (double)Tc[4 * k + i] * (double)tcw[k];
+        Ow[i] = (float)(s * -1.0);
+    }
+    std::vector<int> meta; std::vector<WQuery> queries;
+    for (int i = 0; i < npts; i++) {
+        if (!pts[i].valid) continue;
+        if (pts[i].bad || alreadyFound[i]) continue;
+        float x3Dc[3];
+        mat3_mul_add(Tc, 4, pts[i].world, tcw, x3Dc);
+        const float xc = x3Dc[0], yc = x3Dc[1];
+        const float invzc = (float)(1.0 / x3Dc[2]);
+        const float u = cur->fx * xc * invzc + cur->cx;
+        const float v = cur->fy * yc * invzc + cur->cy;
+        if (u < cur->mnMinX || u > cur->mnMaxX) continue;
+        if (v < cur->mnMinY || v > cur->mnMaxY) continue;
+        // cv::norm(x3Dw - Ow): float differences, squares summed in double, square root in double (:1581-1582)
+        double s2 = 0;
+        for (int k = 0; k < 3; k++) { const float po = pts[i].world[k] - Ow[k]; s2 += (double)po * (double)po; }
+        const float dist3D = (float)std::sqrt(s2);
+        if (dist3D < minInv[i] || dist3D > maxInv[i]) continue;
+        int nPredictedLevel;
+        if (predict) nPredictedLevel = predict(user, i, dist3D);
+        else {                                              // MapPoint::PredictScale, src/MapPoint.cc:402-417
+            const float ratio = maxDistance[i] / dist3D;
+            nPredictedLevel = (int)std::ceil(std::log(ratio) / logScaleFactor);
+            if (nPredictedLevel < 0) nPredictedLevel = 0;
+            else if (nPredictedLevel >= cur->nScaleLevels) nPredictedLevel = cur->nScaleLevels - 1;
+        }
+        if (nPredictedLevel < 0 || nPredictedLevel >= cur->nScaleLevels) return ORBX_E_INVALID;
+        WQuery q; std::memset(&q, 0, sizeof(q));
+        q.x = u; q.y = v; q.r = th * cur->scaleFactors[nPredictedLevel];
+        q.minLevel = nPredictedLevel - 1; q.maxLevel = nPredictedLevel + 1;
+        set_desc(q, pts[i].descriptor);
+        queries.push_back(q); meta.push_back(i);
+    }
+    std::vector<int32_t> offs; std::vector<int2> pairs;
+    if ((rc = run_queries(m, d, queries, offs, pairs))) return rc;
+    int nmatches = 0;
+    std::vector<uint8_t> has(curHasPoint, curHasPoint + cur->N);
+    for (int i = 0; i < cur->N; i++) curAssign[i] = -2;
+    std::vector<int> rotHist[ORBM_HISTO_LENGTH];
+    for (size_t qi = 0; qi < queries.size(); qi++) {
+        if (offs[qi + 1] == offs[qi]) continue;
+        int bestDist = 256, bestIdx2 = -1;
+        for (int k = offs[qi]; k < offs[qi + 1]; k++) {
+            const int i2 = pairs[k].x;
+            if (has[i2]) continue;                                             // :1613-1614
+            const int dist = pairs[k].y;
+            if (dist < bestDist) { bestDist = dist; bestIdx2 = i2; }
+        }
+        if (bestDist <= ORBdist) {
+            curAssign[bestIdx2] = meta[qi]; has[bestIdx2] = 1;
+            nmatches++;
+            if (checkOri) rotHist[rot_bin(kfAngle[meta[qi]], cur->keysUn[bestIdx2].angle)].push_back(bestIdx2);
+        }
+    }
+    if (checkOri) {
+        int32_t counts[ORBM_HISTO_LENGTH];
+        for (int i = 0; i < ORBM_HISTO_LENGTH; i++) counts[i] = (int)rotHist[i].size();
+        int ind1 = -1, ind2 = -1, ind3 = -1;
+        orbm_three_maxima(counts, ORBM_HISTO_LENGTH, &ind1, &ind2, &ind3);
+        for (int i = 0; i < ORBM_HISTO_LENGTH; i++)
+            if (i != ind1 && i != ind2 && i != ind3)
+                for (int idx : rotHist[i]) { curAssign[idx] = -1; nmatches--; }
+    }
+    *nmatchesOut = nmatches;
+    return ORBX_OK;
+}
+
 }  // extern "C"

@@ -111,6 +111,8 @@ def _bind(L):
     L.orbm_search_by_projection_frame.restype = i
     L.orbm_search_by_projection_points.argtypes = [vp, vp, vp, i, vp, f, f, vp, C.POINTER(i)]
     L.orbm_search_by_projection_points.restype = i
+    L.orbm_search_by_projection_keyframe.argtypes = [vp, vp, vp, i, vp, vp, vp, f, vp, vp, vp, vp, vp, f, i, i, vp, C.POINTER(i)]
+    L.orbm_search_by_projection_keyframe.restype = i
     L.orbm_search_by_bow.argtypes = [vp, i, vp, vp, vp, i, vp, vp, vp, vp, i, vp, f, i, vp, C.POINTER(i)]
     L.orbm_search_by_bow.restype = i
     L._orbm_bound = True
@@ -218,6 +220,28 @@ class ORBmatcher:
                                                     self.mfNNratio, out.ctypes.data, C.byref(n)),
               "orbm_search_by_projection_points")
         return n.value, out[: F.N]
+
+    def SearchByProjectionKeyFrame(self, CurrentFrame: Frame, kf_points: np.ndarray, min_max_distance: np.ndarray,
+                                   already_found: np.ndarray, kf_angle: np.ndarray, cur_has_point: np.ndarray,
+                                   th: float, ORBdist: int, log_scale_factor: float | None = None):
+        """SearchByProjection(CurrentFrame, pKF, sAlreadyFound, th, ORBdist) (src/ORBmatcher.cc:1540-1667).
+        min_max_distance[i] = (mfMinDistance, mfMaxDistance) of key-frame map point i."""
+        c = self._c()
+        p = np.ascontiguousarray(kf_points, MAPPOINT_DTYPE)
+        mm = np.ascontiguousarray(min_max_distance, np.float32).reshape(-1, 2)
+        mn_inv = (np.float32(0.8) * mm[:, 0]).astype(np.float32); mx_inv = (np.float32(1.2) * mm[:, 1]).astype(np.float32)
+        mx = np.ascontiguousarray(mm[:, 1])
+        af = np.ascontiguousarray(already_found, np.uint8); ang = np.ascontiguousarray(kf_angle, np.float32)
+        has = np.ascontiguousarray(cur_has_point, np.uint8)
+        if log_scale_factor is None:
+            log_scale_factor = float(np.log(np.float32(CurrentFrame.mvScaleFactors[1])))    # Frame::mfLogScaleFactor = log(mfScaleFactor)
+        out = np.zeros(max(CurrentFrame.N, 1), np.int32); n = C.c_int()
+        sc = CurrentFrame.struct()
+        check(c._L.orbm_search_by_projection_keyframe(c.h, C.byref(sc), p.ctypes.data, len(p), mn_inv.ctypes.data, mx_inv.ctypes.data,
+                                                      mx.ctypes.data, log_scale_factor, None, None, af.ctypes.data, ang.ctypes.data,
+                                                      has.ctypes.data, th, int(ORBdist), int(self.mbCheckOrientation),
+                                                      out.ctypes.data, C.byref(n)), "orbm_search_by_projection_keyframe")
+        return n.value, out[: CurrentFrame.N]
 
     def _bow(self, variant, desc1, angle1, valid1, fv1: FeatureVector, desc2, angle2, valid2, fv2: FeatureVector):
         c = self._c()

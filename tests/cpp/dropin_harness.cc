@@ -2,7 +2,9 @@
 // Frame.cc and Tracking.cc drive the reference's (Frame::ExtractORB src/Frame.cc:320-326; Tracking.cc:635-644,
 // :921-944, :1236-1243), and hands the results to pytest as plain arrays.
 #include <cstring>
+#include <cmath>
 #include <memory>
+#include <set>
 #include <thread>
 #include <vector>
 
@@ -245,6 +247,40 @@ int dropin_search_by_bow_keyframes(const uint8_t* desc1, const float* angle1, co
     if ((int)vpMatches12.size() != n1) return -1000;
     for (int i = 0; i < n1; i++) match[i] = vpMatches12[i] ? (int32_t)(vpMatches12[i] - s2.data()) : -1;
     return n;
+}
+
+// ORBmatcher::SearchByProjection(CurrentFrame, pKF, sAlreadyFound, th, ORBdist) as Tracking::Relocalization calls it
+// (Tracking.cc:1421, :1435).  minmax[2i], [2i+1] = mfMinDistance, mfMaxDistance of key-frame point i.
+int dropin_search_by_projection_keyframe(const orbm_frame* cur, const orbm_mappoint* kp, int n, const float* minmax,
+                                         const uint8_t* already, const float* kfAngle, const uint8_t* curHas, float th, int ORBdist,
+                                         int checkOri, int32_t* assign) {
+    std::unique_ptr<Frame> C = frame_from(cur);
+    C->mnScaleLevels = cur->nScaleLevels;
+    C->mfScaleFactor = cur->scaleFactors[1];
+    C->mfLogScaleFactor = std::log(C->mfScaleFactor);                                  // src/Frame.cc:86
+    KeyFrame K; std::vector<MapPoint> store(n), held(cur->N);
+    K.mvKeysUn.resize(n);
+    K.mvpMapPoints.assign(n, static_cast<MapPoint*>(NULL));
+    std::set<MapPoint*> sFound;
+    for (int i = 0; i < n; i++) {
+        K.mvKeysUn[i].angle = kfAngle[i];
+        if (!kp[i].valid) continue;
+        point_from(store[i], kp[i]);
+        store[i].mfMinDistance = minmax[2 * i]; store[i].mfMaxDistance = minmax[2 * i + 1];
+        K.mvpMapPoints[i] = &store[i];
+        if (already[i]) sFound.insert(&store[i]);
+    }
+    for (int i = 0; i < cur->N; i++) if (curHas[i]) C->mvpMapPoints[i] = &held[i];
+    std::vector<MapPoint*> before = C->mvpMapPoints;
+    ORBmatcher matcher(0.9f, checkOri != 0);
+    const int nm = matcher.SearchByProjection(*C, &K, sFound, th, ORBdist);
+    for (int i = 0; i < cur->N; i++) {
+        MapPoint* p = C->mvpMapPoints[i];
+        if (p == before[i]) assign[i] = -2;
+        else if (!p) assign[i] = -1;
+        else assign[i] = (int32_t)(p - store.data());
+    }
+    return nm;
 }
 
 }  // extern "C"

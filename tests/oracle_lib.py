@@ -173,6 +173,7 @@ def _bind_matcher(L):
     L.orbo_search_by_projection_frame.argtypes = [vp, vp, vp, vp, f, i, i, vp]
     L.orbo_search_by_projection_points.argtypes = [vp, vp, i, vp, f, f, vp]
     L.orbo_bf2nn.argtypes = [vp, i, vp, C.c_size_t, C.c_uint32, vp]
+    L.orbo_search_by_projection_keyframe.argtypes = [vp, vp, i, vp, f, vp, vp, vp, f, i, i, vp]
     L.orbo_search_by_bow_kf_frame.argtypes = [vp, vp, vp, i, vp, vp, vp, i, vp, f, i, vp]
     L.orbo_search_by_bow_kf_kf.argtypes = [vp, vp, vp, i, vp, vp, vp, vp, i, vp, f, i, vp]
     L._m_bound = True
@@ -237,6 +238,20 @@ class OracleMatcher:
         out = np.zeros(len(q), np.dtype([("i1", "<u4"), ("d1", "<u2"), ("d2", "<u2")]))
         self.L.orbo_bf2nn(q.ctypes.data, len(q), db.ctypes.data, len(db), idx_base, out.ctypes.data)
         return out
+
+    def SearchByProjectionKeyFrame(self, cur, kf_points, min_max_distance, already_found, kf_angle, cur_has_point, th, ORBdist,
+                                   log_scale_factor=None):
+        from orb_slam_b200.matcher import MAPPOINT_DTYPE
+        p = np.ascontiguousarray(kf_points, MAPPOINT_DTYPE); mm = np.ascontiguousarray(min_max_distance, np.float32).reshape(-1, 2)
+        af = np.ascontiguousarray(already_found, np.uint8); ang = np.ascontiguousarray(kf_angle, np.float32)
+        has = np.ascontiguousarray(cur_has_point, np.uint8)
+        if log_scale_factor is None:
+            log_scale_factor = float(np.log(np.float32(cur.mvScaleFactors[1])))
+        out = np.zeros(max(cur.N, 1), np.int32)
+        s = cur.struct()
+        n = self.L.orbo_search_by_projection_keyframe(C.byref(s), p.ctypes.data, len(p), mm.ctypes.data, log_scale_factor, af.ctypes.data,
+                                                      ang.ctypes.data, has.ctypes.data, th, int(ORBdist), int(self.checkOri), out.ctypes.data)
+        return n, out[: cur.N]
 
     def SearchByBoWFrame(self, descKF, angleKFun, validKF, fvKF, descF, angleF, fvF):
         d1 = np.ascontiguousarray(descKF, np.uint8).reshape(-1, 32); d2 = np.ascontiguousarray(descF, np.uint8).reshape(-1, 32)

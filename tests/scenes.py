@@ -73,6 +73,31 @@ def local_map_points(F: Frame, seed=0):
     return pts
 
 
+def keyframe_points(kf: Frame, seed=0, p_valid=0.85):
+    """Map points of a key frame for the relocalisation matcher: keypoint i back-projected at a random depth (key-frame
+    pose = identity), with the scale-invariance distances MapPoint::UpdateNormalAndDepth would give it
+    (src/MapPoint.cc:352-370: mfMaxDistance = dist * scaleFactor^level, mfMinDistance = mfMaxDistance / scaleFactor^(nLevels-1))."""
+    rng = np.random.default_rng(seed)
+    n = kf.N
+    pts = np.zeros(n, MAPPOINT_DTYPE)
+    z = rng.uniform(4, 60, n).astype(np.float32)
+    pts["world"][:, 0] = (kf.mvKeysUn["x"] - kf.cx) * z / kf.fx
+    pts["world"][:, 1] = (kf.mvKeysUn["y"] - kf.cy) * z / kf.fy
+    pts["world"][:, 2] = z
+    pts["descriptor"] = kf.mDescriptors
+    flip = rng.integers(0, 32, n)
+    pts["descriptor"][np.arange(n), flip] ^= rng.integers(0, 256, n).astype(np.uint8)
+    pts["valid"] = rng.random(n) < p_valid
+    pts["bad"] = rng.random(n) < 0.05
+    dist = np.linalg.norm(pts["world"], axis=1).astype(np.float32)
+    sf = kf.mvScaleFactors
+    mx = (dist * sf[np.clip(kf.mvKeysUn["octave"], 0, len(sf) - 1)]).astype(np.float32)
+    mn = (mx / sf[-1]).astype(np.float32)
+    mm = np.stack([mn, mx], axis=1).astype(np.float32)
+    already = (rng.random(n) < 0.2).astype(np.uint8)
+    return pts, mm, already
+
+
 def bow_scene(seed=0, n1=1500, n2=1600, *, n_nodes=64, p_common=0.7, flips=12, p_valid=0.8, rotation=25.0, ties=0):
     """Two descriptor sets with a synthetic vocabulary for ORBmatcher::SearchByBoW: side 2 holds noisy copies (up to
     `flips` flipped bits) of a share of side 1 plus unrelated descriptors; a feature's node is a hash of a few

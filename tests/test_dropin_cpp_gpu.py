@@ -183,3 +183,26 @@ def test_search_by_bow_members(H, seed):
                                                            s["valid2"], s["fv2"])
     assert n == on and n > 50
     np.testing.assert_array_equal(m12, om)
+
+
+@pytest.mark.parametrize("th,orbdist", [(10.0, 100), (3.0, 64)])
+def test_search_by_projection_keyframe_member(H, th, orbdist):
+    """ORBmatcher::SearchByProjection(Frame&, KeyFrame*, set<MapPoint*>, th, ORBdist): the predicted level comes from
+    MapPoint::PredictScale through the binding's callback"""
+    (ka, da), (kb, db) = scenes.extract_pair(OracleExtractor, 1241, 376, 2000, 34, (5, 2))
+    kf = scenes.make_frame(ka, da, 1241, 376)
+    Tcw = np.eye(4, dtype=np.float32); Tcw[:3, 3] = [0.02, -0.02, 0.5]
+    cur = scenes.make_frame(kb, db, 1241, 376, Tcw=Tcw, seed=5)
+    pts, mm, already = scenes.keyframe_points(kf, seed=13)
+    has = (np.random.default_rng(14).random(cur.N) < 0.3).astype(np.uint8)
+    ang = np.ascontiguousarray(kf.mvKeysUn["angle"], np.float32)
+    a = np.zeros(cur.N, np.int32)
+    sc = cur.struct()
+    p = lambda x: C.c_void_p(x.ctypes.data)
+    mmc = np.ascontiguousarray(mm, np.float32)
+    n = H.dropin_search_by_projection_keyframe(C.byref(sc), p(pts), len(pts), p(mmc), p(already), p(ang), p(has), C.c_float(th), orbdist, 1, p(a))
+    n_o, a_o = OracleMatcher(0.9, True).SearchByProjectionKeyFrame(cur, pts, mm, already, ang, has, th, orbdist)
+    assert n == n_o and n_o > 20
+    # only empty slots receive points, so a slot NULLed again by the rotation check looks untouched to the harness
+    assert (a_o == -1).sum() > 0
+    np.testing.assert_array_equal(a, np.where(a_o == -1, -2, a_o))

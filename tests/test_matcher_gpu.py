@@ -96,6 +96,27 @@ def test_search_by_projection_points(ctx, th):
     assert np.array_equal(a_g, a_o)
 
 
+@pytest.mark.parametrize("th,orbdist,tz", [(10.0, 100, 0.3), (3.0, 64, -0.4), (10.0, 100, 4.0)])
+def test_search_by_projection_keyframe(ctx, th, orbdist, tz):
+    """Tracking::Relocalization's SearchByProjection(CurrentFrame, pKF, sFound, th, ORBdist) (:1540-1667)"""
+    from orb_slam_b200.matcher import ORBmatcher
+    (ka, da), (kb, db) = scenes.extract_pair(OracleExtractor, 1241, 376, 2000, 33, (4, -2))
+    kf = scenes.make_frame(ka, da, 1241, 376)
+    Tcw = np.eye(4, dtype=np.float32); Tcw[:3, 3] = [0.03, 0.01, tz]
+    cur = scenes.make_frame(kb, db, 1241, 376, Tcw=Tcw, seed=3)
+    pts, mm, already = scenes.keyframe_points(kf, seed=11)
+    has = (np.random.default_rng(12).random(cur.N) < 0.3).astype(np.uint8)
+    args = (cur, pts, mm, already, kf.mvKeysUn["angle"], has, th, orbdist)
+    n_g, a_g = ORBmatcher(0.9, True, ctx).SearchByProjectionKeyFrame(*args)
+    n_o, a_o = OracleMatcher(0.9, True).SearchByProjectionKeyFrame(*args)
+    assert n_g == n_o
+    assert np.array_equal(a_g, a_o)
+    if tz < 1:
+        assert (a_o >= 0).sum() > 20
+    m = a_g[a_g >= 0]
+    assert not np.any(has[a_g >= 0]) and not np.any(already[m]) and np.all(pts["valid"][m] == 1) and not np.any(pts["bad"][m])
+
+
 def test_bruteforce_2nn_and_sharded_merge(ctx):
     import ctypes as C
     import torch
