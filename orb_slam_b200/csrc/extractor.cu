@@ -403,7 +403,7 @@ static int enqueue_pipeline(orbx_extractor* e, int wi, const uint8_t* src, size_
         q.cellOff[l] = v.cellOff; q.slotOff[l] = v.slotOff; q.slotCap[l] = v.slotCap; q.candCap[l] = v.candCap;
     }
     q.cellOff[g.nlevels] = g.totalCells;
-    quadtree_kernel<<<dim3(g.nlevels, frames), QT_THREADS, qt_smem_bytes(g.nodeCap), st>>>(q);
+    quadtree_kernel<<<dim3(frames, g.nlevels), QT_THREADS, qt_smem_bytes(g.nodeCap), st>>>(q);
     launches++;
     if (evs) CK(cudaEventRecord(evs[4], st));
     // 5. orientation, descriptors, output assembly

@@ -48,7 +48,7 @@ __device__ __forceinline__ void emit_children(uint32_t* nlo, uint32_t* nhi, uint
 __global__ void __launch_bounds__(QT_THREADS) quadtree_kernel(QtArgs a) {
     extern __shared__ __align__(16) uint8_t qsm[];
     const int tid = threadIdx.x;
-    const int l = blockIdx.x, frame = blockIdx.y;
+    const int l = blockIdx.y, frame = blockIdx.x;        // level-major launch order: the long level-0 blocks start first
     const int cap = a.nodeCap;
     QtSmem s;
     {
