@@ -166,6 +166,25 @@ int orbm_search_by_bow(orbm_t* m, int variant,
                        const uint8_t* desc2, const float* angle2, const uint8_t* valid2, int n2, const orbm_featvec* fv2,
                        float nnratio, int checkOrientation, int32_t* match, int* nmatches);
 
+/* ORBmatcher::SearchForTriangulation(pKF1, pKF2, F12, vMatchedPairs, bOnlyStereo) (src/ORBmatcher.cc:725-891, with
+ * CheckDistEpipolarLine :140-157).  A key frame as the function reads it: */
+typedef struct orbm_keyframe {
+    int32_t N;
+    const orbx_keypoint* keysUn;    /* mvKeysUn */
+    const uint8_t* descriptors;     /* mDescriptors, N x 32 */
+    const float* uRight;            /* mvuRight (negative = monocular point) */
+    const uint8_t* has_point;       /* GetMapPoint(i) != NULL */
+    const orbm_featvec* featvec;    /* mFeatVec */
+} orbm_keyframe;
+/* Cw1 = pKF1->GetCameraCenter(); R2w (row-major 3x3), t2w = pKF2->GetRotation(), GetTranslation(); fx..cy,
+ * scale_factors2 / level_sigma2_2 (nlevels entries) = pKF2's intrinsics, mvScaleFactors, mvLevelSigma2; F12 row-major.
+ * matches12 out: N1 entries, vMatches12 (idx2 or -1); vMatchedPairs = the (i, matches12[i]) with matches12[i] >= 0 in
+ * ascending i (:879-886). */
+int orbm_search_for_triangulation(orbm_t* m, const orbm_keyframe* kf1, const orbm_keyframe* kf2, const float* Cw1,
+                                  const float* R2w, const float* t2w, float fx2, float fy2, float cx2, float cy2,
+                                  const float* scale_factors2, const float* level_sigma2_2, int nlevels, const float* F12,
+                                  int onlyStereo, int checkOrientation, int32_t* matches12, int* nmatches);
+
 #ifdef __cplusplus
 }
 #endif

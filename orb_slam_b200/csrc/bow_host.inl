@@ -115,3 +115,126 @@ extern "C" int orbm_search_by_bow(orbm_t* m, int variant,
     *nmatches = nm;
     return ORBX_OK;
 }
+
+namespace {
+// well-formed feature vector: ascending node ids, monotone ranges, indices below n
+bool featvec_ok(const orbm_featvec* fv, int n) {
+    if (!fv || fv->nnodes < 0) return false;
+    if (fv->nnodes == 0) return true;
+    if (!fv->node_ids || !fv->start || fv->start[0] != 0) return false;
+    for (int k = 0; k < fv->nnodes; k++) {
+        if (k && fv->node_ids[k] <= fv->node_ids[k - 1]) return false;
+        if (fv->start[k + 1] < fv->start[k]) return false;
+    }
+    const int total = fv->start[fv->nnodes];
+    if (total > 0 && !fv->items) return false;
+    for (int t = 0; t < total; t++) if (fv->items[t] >= (uint32_t)n) return false;
+    return true;
+}
+}  // namespace
+
+extern "C" int orbm_search_for_triangulation(orbm_t* m, const orbm_keyframe* kf1, const orbm_keyframe* kf2, const float* Cw1,
+                                             const float* R2w, const float* t2w, float fx2, float fy2, float cx2, float cy2,
+                                             const float* scaleFactors2, const float* levelSigma2, int nlevels, const float* F12,
+                                             int onlyStereo, int checkOri, int32_t* matches12, int* nmatchesOut) {
+    if (!m || !kf1 || !kf2 || !Cw1 || !R2w || !t2w || !scaleFactors2 || !levelSigma2 || nlevels <= 0 || !F12 || !matches12 || !nmatchesOut)
+        return ORBX_E_INVALID;
+    const int n1 = kf1->N, n2 = kf2->N;
+    if (n1 < 0 || n2 < 0 || !featvec_ok(kf1->featvec, n1) || !featvec_ok(kf2->featvec, n2)) return ORBX_E_INVALID;
+    if ((n1 > 0 && (!kf1->keysUn || !kf1->descriptors || !kf1->uRight || !kf1->has_point)) ||
+        (n2 > 0 && (!kf2->keysUn || !kf2->descriptors || !kf2->uRight || !kf2->has_point))) return ORBX_E_INVALID;
+    for (int i = 0; i < n2; i++) if (kf2->keysUn[i].octave < 0 || kf2->keysUn[i].octave >= nlevels) return ORBX_E_INVALID;
+    for (int i = 0; i < n1; i++) matches12[i] = -1;
+    *nmatchesOut = 0;
+    std::lock_guard<std::mutex> lk(m->mtx);
+    CKM(cudaSetDevice(m->device));
+    const orbm_featvec* fv1 = kf1->featvec; const orbm_featvec* fv2 = kf2->featvec;
+    // rows: features of key frame 1 without a map point (and stereo when bOnlyStereo) in nodes both frames share (:758-777)
+    std::vector<BowRow> rows;
+    {
+        int a = 0, b = 0;
+        while (a < fv1->nnodes && b < fv2->nnodes) {
+            const uint32_t ia = fv1->node_ids[a], ib = fv2->node_ids[b];
+            if (ia == ib) {
+                const int s2 = fv2->start[b], c2 = fv2->start[b + 1] - s2;
+                if (c2 > 0xffff) return ORBX_E_CAPACITY;
+                if (c2 > 0)
+                    for (int t = fv1->start[a]; t < fv1->start[a + 1]; t++) {
+                        const uint32_t i1 = fv1->items[t];
+                        if (kf1->has_point[i1]) continue;
+                        if (onlyStereo && !(kf1->uRight[i1] >= 0)) continue;
+                        rows.push_back(BowRow{i1, s2, c2, 0u});
+                    }
+                a++; b++;
+            } else if (ia < ib) a = (int)(std::lower_bound(fv1->node_ids + a, fv1->node_ids + fv1->nnodes, ib) - fv1->node_ids);
+            else b = (int)(std::lower_bound(fv2->node_ids + b, fv2->node_ids + fv2->nnodes, ia) - fv2->node_ids);
+        }
+    }
+    if (rows.empty()) return ORBX_OK;
+    // epipole in the second image (:733-740): C2 = R2w*Cw + t2w
+    float C2[3];
+    mat3_mul_add(R2w, 3, Cw1, t2w, C2);
+    const float invz = 1.0f / C2[2];
+    TriArgs ta;
+    ta.ex = fx2 * C2[0] * invz + cx2;
+    ta.ey = fy2 * C2[1] * invz + cy2;
+    std::memcpy(ta.F, F12, sizeof(ta.F));
+    ta.onlyStereo = onlyStereo ? 1 : 0;
+    // device layout in one scratch buffer
+    const size_t nitems2 = (size_t)fv2->start[fv2->nnodes];
+    auto al = [](size_t v) { return (v + 255) & ~(size_t)255; };
+    size_t off = 0;
+    const size_t oDesc1 = off; off += al((size_t)n1 * 32);
+    const size_t oDesc2 = off; off += al((size_t)n2 * 32);
+    const size_t oKeys1 = off; off += al((size_t)n1 * sizeof(orbx_keypoint));
+    const size_t oKeys2 = off; off += al((size_t)n2 * sizeof(orbx_keypoint));
+    const size_t oUr1 = off; off += al((size_t)n1 * 4);
+    const size_t oUr2 = off; off += al((size_t)n2 * 4);
+    const size_t oHas2 = off; off += al((size_t)n2);
+    const size_t oItems2 = off; off += al(nitems2 * 4);
+    const size_t oRows = off; off += al(rows.size() * sizeof(BowRow));
+    const size_t oSf = off; off += al((size_t)nlevels * 4);
+    const size_t oSig = off; off += al((size_t)nlevels * 4);
+    const size_t oMatch = off; off += al((size_t)n1 * 4);
+    int rc;
+    if ((rc = m->w0.reserve(off))) return rc;
+    uint8_t* base = (uint8_t*)m->w0.p;
+    auto up = [&](size_t o, const void* src, size_t bytes) { return bytes ? cudaMemcpyAsync(base + o, src, bytes, cudaMemcpyHostToDevice, m->stream) : cudaSuccess; };
+    CKM(up(oDesc1, kf1->descriptors, (size_t)n1 * 32)); CKM(up(oDesc2, kf2->descriptors, (size_t)n2 * 32));
+    CKM(up(oKeys1, kf1->keysUn, (size_t)n1 * sizeof(orbx_keypoint))); CKM(up(oKeys2, kf2->keysUn, (size_t)n2 * sizeof(orbx_keypoint)));
+    CKM(up(oUr1, kf1->uRight, (size_t)n1 * 4)); CKM(up(oUr2, kf2->uRight, (size_t)n2 * 4));
+    CKM(up(oHas2, kf2->has_point, (size_t)n2)); CKM(up(oItems2, fv2->items, nitems2 * 4));
+    CKM(up(oRows, rows.data(), rows.size() * sizeof(BowRow)));
+    CKM(up(oSf, scaleFactors2, (size_t)nlevels * 4)); CKM(up(oSig, levelSigma2, (size_t)nlevels * 4));
+    CKM(cudaMemsetAsync(base + oMatch, 0xff, (size_t)n1 * 4, m->stream));                      // -1
+    ta.rows = (const BowRow*)(base + oRows); ta.nrows = (int)rows.size();
+    ta.desc1 = (const uint32_t*)(base + oDesc1); ta.desc2 = (const uint32_t*)(base + oDesc2); ta.items2 = (const uint32_t*)(base + oItems2);
+    ta.keys1 = (const orbx_keypoint*)(base + oKeys1); ta.keys2 = (const orbx_keypoint*)(base + oKeys2);
+    ta.uRight1 = (const float*)(base + oUr1); ta.uRight2 = (const float*)(base + oUr2); ta.has2 = base + oHas2;
+    ta.scaleFactors2 = (const float*)(base + oSf); ta.levelSigma2 = (const float*)(base + oSig);
+    ta.matches12 = (int32_t*)(base + oMatch);
+    triangulation_match_kernel<<<(ta.nrows + 7) / 8, 256, 0, m->stream>>>(ta);
+    CKM(cudaGetLastError());
+    CKM(cudaMemcpyAsync(matches12, base + oMatch, (size_t)n1 * 4, cudaMemcpyDeviceToHost, m->stream));
+    CKM(cudaStreamSynchronize(m->stream));
+    // rotation consistency (:829-875): only the bin sizes matter, every entry of a losing bin is dropped
+    int nm = 0;
+    std::vector<int> rotHist[ORBM_HISTO_LENGTH];
+    for (int i1 = 0; i1 < n1; i1++) {
+        if (matches12[i1] < 0) continue;
+        nm++;
+        if (checkOri) rotHist[rot_bin(kf1->keysUn[i1].angle, kf2->keysUn[matches12[i1]].angle)].push_back(i1);
+    }
+    if (checkOri) {
+        int32_t counts[ORBM_HISTO_LENGTH];
+        for (int i = 0; i < ORBM_HISTO_LENGTH; i++) counts[i] = (int32_t)rotHist[i].size();
+        int ind1 = -1, ind2 = -1, ind3 = -1;
+        orbm_three_maxima(counts, ORBM_HISTO_LENGTH, &ind1, &ind2, &ind3);
+        for (int i = 0; i < ORBM_HISTO_LENGTH; i++) {
+            if (i == ind1 || i == ind2 || i == ind3) continue;
+            for (int idx : rotHist[i]) { matches12[idx] = -1; nm--; }
+        }
+    }
+    *nmatchesOut = nm;
+    return ORBX_OK;
+}

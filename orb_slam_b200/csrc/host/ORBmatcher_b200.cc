@@ -248,6 +248,38 @@ int ORBmatcher::SearchByBoW(KeyFrame* pKF1, KeyFrame* pKF2, std::vector<MapPoint
     return nmatches;
 }
 
+// src/ORBmatcher.cc:725-891 (LocalMapping::CreateNewMapPoints)
+int ORBmatcher::SearchForTriangulation(KeyFrame* pKF1, KeyFrame* pKF2, cv::Mat F12,
+                                       std::vector<std::pair<size_t, size_t> >& vMatchedPairs, const bool bOnlyStereo) {
+    const b200::FlatFeatVec fv1(pKF1->mFeatVec), fv2(pKF2->mFeatVec);
+    std::vector<uint8_t> has1(pKF1->N), has2(pKF2->N);
+    for (int i = 0; i < pKF1->N; i++) has1[i] = pKF1->GetMapPoint(i) != NULL;                       // :763-767
+    for (int i = 0; i < pKF2->N; i++) has2[i] = pKF2->GetMapPoint(i) != NULL;                       // :785-789
+    assert(pKF1->mDescriptors.isContinuous() && pKF2->mDescriptors.isContinuous());
+    orbm_keyframe k1, k2;
+    k1.N = pKF1->N; k1.keysUn = (const orbx_keypoint*)pKF1->mvKeysUn.data(); k1.descriptors = pKF1->mDescriptors.data;
+    k1.uRight = pKF1->mvuRight.data(); k1.has_point = has1.data(); k1.featvec = &fv1.fv;
+    k2.N = pKF2->N; k2.keysUn = (const orbx_keypoint*)pKF2->mvKeysUn.data(); k2.descriptors = pKF2->mDescriptors.data;
+    k2.uRight = pKF2->mvuRight.data(); k2.has_point = has2.data(); k2.featvec = &fv2.fv;
+    const cv::Mat Cw = pKF1->GetCameraCenter(), R2w = pKF2->GetRotation(), t2w = pKF2->GetTranslation();
+    float cw[3], r2w[9], tw[3], f12[9];
+    for (int r = 0; r < 3; r++) {
+        cw[r] = Cw.at<float>(r); tw[r] = t2w.at<float>(r);
+        for (int c = 0; c < 3; c++) { r2w[3 * r + c] = R2w.at<float>(r, c); f12[3 * r + c] = F12.at<float>(r, c); }
+    }
+    std::vector<int32_t> vMatches12(std::max(pKF1->N, 1), -1);
+    int nmatches = 0;
+    b200::Check(orbm_search_for_triangulation(b200::MatcherContext(), &k1, &k2, cw, r2w, tw, pKF2->fx, pKF2->fy, pKF2->cx, pKF2->cy,
+                                              pKF2->mvScaleFactors.data(), pKF2->mvLevelSigma2.data(), (int)pKF2->mvScaleFactors.size(),
+                                              f12, bOnlyStereo, mbCheckOrientation, vMatches12.data(), &nmatches),
+                "orbm_search_for_triangulation");
+    vMatchedPairs.clear();
+    vMatchedPairs.reserve(nmatches);
+    for (int i = 0; i < pKF1->N; i++)
+        if (vMatches12[i] >= 0) vMatchedPairs.push_back(std::make_pair((size_t)i, (size_t)vMatches12[i]));   // :879-886
+    return nmatches;
+}
+
 #ifdef ORB_B200_STANDALONE
 // The rest of the class lives in the reference's src/ORBmatcher.cc; in the stand-alone build of this repository
 // the pieces the accelerated functions depend on are provided here.

@@ -21,9 +21,11 @@ public:
     int SearchForInitialization(Frame& F1, Frame& F2, std::vector<cv::Point2f>& vbPrevMatched,
                                 std::vector<int>& vnMatches12, int windowSize = 10);
     int SearchByProjection(Frame& CurrentFrame, KeyFrame* pKF, const std::set<MapPoint*>& sAlreadyFound, const float th, const int ORBdist);
+    int SearchForTriangulation(KeyFrame* pKF1, KeyFrame* pKF2, cv::Mat F12, std::vector<std::pair<size_t, size_t> >& vMatchedPairs,
+                               const bool bOnlyStereo);
     int SearchByBoW(KeyFrame* pKF, Frame& F, std::vector<MapPoint*>& vpMapPointMatches);
     int SearchByBoW(KeyFrame* pKF1, KeyFrame* pKF2, std::vector<MapPoint*>& vpMatches12);
-    // SearchByProjection(KeyFrame*, Scw, ...), SearchForTriangulation,
+    // SearchByProjection(KeyFrame*, Scw, ...),
     // SearchBySim3, Fuse x2: SURVEY 8(f) "next" rows - they stay the reference's own code.
 public:
     static const int TH_LOW;

@@ -89,6 +89,32 @@ class FeatureVector:
         return s
 
 
+class KeyFrameStruct(C.Structure):
+    """orbm_keyframe of include/orbm.h."""
+    _fields_ = [("N", C.c_int32), ("keysUn", C.c_void_p), ("descriptors", C.c_void_p), ("uRight", C.c_void_p),
+                ("has_point", C.c_void_p), ("featvec", C.c_void_p)]
+
+
+class KeyFrameView:
+    """The members of ORB_SLAM2::KeyFrame that SearchForTriangulation reads."""
+
+    def __init__(self, keys_un, descriptors, u_right, has_point, featvec: FeatureVector):
+        self.keysUn = np.ascontiguousarray(keys_un, KEYPOINT_DTYPE)
+        self.descriptors = np.ascontiguousarray(descriptors, np.uint8).reshape(-1, 32)
+        self.uRight = np.ascontiguousarray(u_right, np.float32)
+        self.has_point = np.ascontiguousarray(has_point, np.uint8)
+        self.featvec = featvec
+        self.N = len(self.keysUn)
+
+    def struct(self) -> KeyFrameStruct:
+        self._fv = self.featvec.struct()
+        s = KeyFrameStruct()
+        s.N = self.N; s.keysUn = self.keysUn.ctypes.data; s.descriptors = self.descriptors.ctypes.data
+        s.uRight = self.uRight.ctypes.data; s.has_point = self.has_point.ctypes.data
+        s.featvec = C.cast(C.pointer(self._fv), C.c_void_p)
+        return s
+
+
 def _bind(L):
     if getattr(L, "_orbm_bound", False):
         return
@@ -113,6 +139,8 @@ def _bind(L):
     L.orbm_search_by_projection_points.restype = i
     L.orbm_search_by_projection_keyframe.argtypes = [vp, vp, vp, i, vp, vp, vp, f, vp, vp, vp, vp, vp, f, i, i, vp, C.POINTER(i)]
     L.orbm_search_by_projection_keyframe.restype = i
+    L.orbm_search_for_triangulation.argtypes = [vp, vp, vp, vp, vp, vp, f, f, f, f, vp, vp, i, vp, i, i, vp, C.POINTER(i)]
+    L.orbm_search_for_triangulation.restype = i
     L.orbm_search_by_bow.argtypes = [vp, i, vp, vp, vp, i, vp, vp, vp, vp, i, vp, f, i, vp, C.POINTER(i)]
     L.orbm_search_by_bow.restype = i
     L._orbm_bound = True
@@ -265,3 +293,19 @@ class ORBmatcher:
     def SearchByBoWKeyFrames(self, desc1, angle1, valid1, fv1: FeatureVector, desc2, angle2, valid2, fv2: FeatureVector):
         """SearchByBoW(KeyFrame* pKF1, KeyFrame* pKF2, vpMatches12) (:590-723).  match[idx1] = idx2 or -1."""
         return self._bow(1, desc1, angle1, valid1, fv1, desc2, angle2, valid2, fv2)
+
+    def SearchForTriangulation(self, kf1: KeyFrameView, kf2: KeyFrameView, Cw1, R2w, t2w, K2, scale_factors2, level_sigma2_2, F12,
+                               bOnlyStereo: bool = False):
+        """SearchForTriangulation(pKF1, pKF2, F12, vMatchedPairs, bOnlyStereo) (src/ORBmatcher.cc:725-891).
+        Returns (nmatches, vMatches12); vMatchedPairs = [(i, m) for i, m in enumerate(vMatches12) if m >= 0]."""
+        c = self._c()
+        f32 = lambda a: np.ascontiguousarray(a, np.float32)
+        Cw1, R2w, t2w, F12 = f32(Cw1).ravel(), f32(R2w).ravel(), f32(t2w).ravel(), f32(F12).ravel()
+        sf, sg = f32(scale_factors2), f32(level_sigma2_2)
+        out = np.zeros(max(kf1.N, 1), np.int32); n = C.c_int()
+        s1, s2 = kf1.struct(), kf2.struct()
+        check(c._L.orbm_search_for_triangulation(c.h, C.byref(s1), C.byref(s2), Cw1.ctypes.data, R2w.ctypes.data, t2w.ctypes.data,
+                                                 float(K2[0, 0]), float(K2[1, 1]), float(K2[0, 2]), float(K2[1, 2]), sf.ctypes.data,
+                                                 sg.ctypes.data, len(sf), F12.ctypes.data, int(bOnlyStereo), int(self.mbCheckOrientation),
+                                                 out.ctypes.data, C.byref(n)), "orbm_search_for_triangulation")
+        return n.value, out[: kf1.N]

@@ -283,4 +283,39 @@ int dropin_search_by_projection_keyframe(const orbm_frame* cur, const orbm_mappo
     return nm;
 }
 
+static void keyframe_view(KeyFrame& K, std::vector<MapPoint>& store, const orbm_keyframe* v) {
+    K.N = v->N;
+    K.mvKeysUn.assign((const cv::KeyPoint*)v->keysUn, (const cv::KeyPoint*)v->keysUn + v->N);
+    K.mDescriptors.create(v->N, 32, CV_8U);
+    if (v->N) std::memcpy(K.mDescriptors.data, v->descriptors, (size_t)v->N * 32);
+    K.mvuRight.assign(v->uRight, v->uRight + v->N);
+    store.resize(v->N);
+    K.mvpMapPoints.assign(v->N, static_cast<MapPoint*>(NULL));
+    for (int i = 0; i < v->N; i++) if (v->has_point[i]) K.mvpMapPoints[i] = &store[i];
+    for (int k = 0; k < v->featvec->nnodes; k++)
+        for (int t = v->featvec->start[k]; t < v->featvec->start[k + 1]; t++) K.mFeatVec.addFeature(v->featvec->node_ids[k], v->featvec->items[t]);
+}
+
+// ORBmatcher::SearchForTriangulation as LocalMapping::CreateNewMapPoints calls it (LocalMapping.cc:262-264)
+int dropin_search_for_triangulation(const orbm_keyframe* kf1, const orbm_keyframe* kf2, const float* Cw1, const float* R2w, const float* t2w,
+                                    float fx, float fy, float cx, float cy, const float* sf, const float* sig2, int nlevels,
+                                    const float* F12, int onlyStereo, int checkOri, int32_t* pairs, int cap) {
+    KeyFrame K1, K2; std::vector<MapPoint> s1, s2;
+    keyframe_view(K1, s1, kf1); keyframe_view(K2, s2, kf2);
+    for (int r = 0; r < 3; r++) {
+        K1.Ow.at<float>(r) = Cw1[r]; K2.tcw.at<float>(r) = t2w[r];
+        for (int c = 0; c < 3; c++) K2.Rcw.at<float>(r, c) = R2w[3 * r + c];
+    }
+    K2.fx = fx; K2.fy = fy; K2.cx = cx; K2.cy = cy;
+    K2.mvScaleFactors.assign(sf, sf + nlevels); K2.mvLevelSigma2.assign(sig2, sig2 + nlevels);
+    cv::Mat F(3, 3, CV_32F);
+    std::memcpy(F.data, F12, 36);
+    std::vector<std::pair<size_t, size_t> > vMatchedPairs(2);
+    ORBmatcher matcher(0.6f, checkOri != 0);
+    const int n = matcher.SearchForTriangulation(&K1, &K2, F, vMatchedPairs, onlyStereo != 0);
+    if ((int)vMatchedPairs.size() != n || n > cap) return -1000;
+    for (int i = 0; i < n; i++) { pairs[2 * i] = (int32_t)vMatchedPairs[i].first; pairs[2 * i + 1] = (int32_t)vMatchedPairs[i].second; }
+    return n;
+}
+
 }  // extern "C"

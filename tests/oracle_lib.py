@@ -174,6 +174,7 @@ def _bind_matcher(L):
     L.orbo_search_by_projection_points.argtypes = [vp, vp, i, vp, f, f, vp]
     L.orbo_bf2nn.argtypes = [vp, i, vp, C.c_size_t, C.c_uint32, vp]
     L.orbo_search_by_projection_keyframe.argtypes = [vp, vp, i, vp, f, vp, vp, vp, f, i, i, vp]
+    L.orbo_search_for_triangulation.argtypes = [vp, vp, vp, vp, vp, f, f, f, f, vp, vp, vp, i, i, vp]
     L.orbo_search_by_bow_kf_frame.argtypes = [vp, vp, vp, i, vp, vp, vp, i, vp, f, i, vp]
     L.orbo_search_by_bow_kf_kf.argtypes = [vp, vp, vp, i, vp, vp, vp, vp, i, vp, f, i, vp]
     L._m_bound = True
@@ -273,3 +274,14 @@ class OracleMatcher:
                                             a2.ctypes.data, v2.ctypes.data, len(d2), C.byref(s2), self.nnratio, int(self.checkOri),
                                             out.ctypes.data)
         return n, out[: len(d1)]
+
+    def SearchForTriangulation(self, kf1, kf2, Cw1, R2w, t2w, K2, scale_factors2, level_sigma2_2, F12, bOnlyStereo=False):
+        f32 = lambda a: np.ascontiguousarray(a, np.float32)
+        Cw1, R2w, t2w, F12 = f32(Cw1).ravel(), f32(R2w).ravel(), f32(t2w).ravel(), f32(F12).ravel()
+        sf, sg = f32(scale_factors2), f32(level_sigma2_2)
+        out = np.zeros(max(kf1.N, 1), np.int32)
+        s1, s2 = kf1.struct(), kf2.struct()
+        n = self.L.orbo_search_for_triangulation(C.byref(s1), C.byref(s2), Cw1.ctypes.data, R2w.ctypes.data, t2w.ctypes.data,
+                                                 float(K2[0, 0]), float(K2[1, 1]), float(K2[0, 2]), float(K2[1, 2]), sf.ctypes.data,
+                                                 sg.ctypes.data, F12.ctypes.data, int(bOnlyStereo), int(self.checkOri), out.ctypes.data)
+        return n, out[: kf1.N]

@@ -98,6 +98,68 @@ def keyframe_points(kf: Frame, seed=0, p_valid=0.85):
     return pts, mm, already
 
 
+def triangulation_scene(seed=0, n=1500, extra=400, t=(0.4, 0.02, 0.05), stereo_frac=0.5, n_nodes=60, flips=6, outlier_frac=0.1):
+    """Two key frames for ORBmatcher::SearchForTriangulation: key frame 1 at the origin, key frame 2 = translation t.
+    Key frame 2 observes noisy reprojections of key frame 1's points (descriptors with up to `flips` flipped bits; a
+    share displaced off the epipolar line) plus unrelated keypoints.  F12 as LocalMapping::ComputeF12
+    (src/LocalMapping.cc:651-668) with R12 = I, t12 = -t."""
+    from orb_slam_b200._lib import KEYPOINT_DTYPE
+    from orb_slam_b200.matcher import FeatureVector, KeyFrameView
+    rng = np.random.default_rng(seed)
+    K = KITTI_K.astype(np.float32)
+    fx, fy, cx, cy = K[0, 0], K[1, 1], K[0, 2], K[1, 2]
+    sf = scale_factors(8, 1.2); sig2 = (sf * sf).astype(np.float32)
+    k1 = np.zeros(n, KEYPOINT_DTYPE)
+    k1["x"] = rng.uniform(20, 1220, n); k1["y"] = rng.uniform(20, 355, n)
+    k1["octave"] = rng.integers(0, 8, n); k1["angle"] = rng.uniform(0, 360, n); k1["size"] = 31
+    z = rng.uniform(4, 40, n).astype(np.float32)
+    X = np.stack([(k1["x"] - cx) * z / fx, (k1["y"] - cy) * z / fy, z], axis=1) + np.asarray(t, np.float32)
+    n2 = n + extra
+    k2 = np.zeros(n2, KEYPOINT_DTYPE)
+    perm = rng.permutation(n2)[:n]
+    k2["x"] = rng.uniform(20, 1220, n2); k2["y"] = rng.uniform(20, 355, n2)
+    k2["octave"] = rng.integers(0, 8, n2); k2["angle"] = rng.uniform(0, 360, n2); k2["size"] = 31
+    k2["x"][perm] = fx * X[:, 0] / X[:, 2] + cx + rng.normal(0, 0.4, n)
+    k2["y"][perm] = fy * X[:, 1] / X[:, 2] + cy + rng.normal(0, 0.4, n)
+    off = rng.random(n) < outlier_frac
+    k2["y"][perm[off]] += rng.choice([-1, 1], off.sum()) * rng.uniform(8, 30, off.sum())
+    k2["octave"][perm] = np.clip(k1["octave"] + rng.integers(-1, 2, n), 0, 7)
+    k2["angle"][perm] = (k1["angle"] - 12 + rng.normal(0, 3, n)) % 360
+    d1 = rng.integers(0, 256, (n, 32), dtype=np.uint8)
+    d2 = rng.integers(0, 256, (n2, 32), dtype=np.uint8)
+    for a, b in zip(range(n), perm):
+        d = d1[a].copy()
+        for bit in rng.integers(0, 256, rng.integers(0, flips + 1)):
+            d[bit >> 3] ^= np.uint8(1 << (bit & 7))
+        d2[b] = d
+    if n >= 80:
+        d2[perm[:40]] = d2[perm[40:80]]                   # equal distances inside a node: ties go to the LAST candidate
+
+    def node_of(d):
+        return ((d[:, 1].astype(np.uint32) >> 2) % np.uint32(n_nodes)) * 2 + 5
+
+    def featvec(d):
+        nodes = {}
+        for i, nd in enumerate(node_of(d)):
+            nodes.setdefault(int(nd), []).append(i)
+        return FeatureVector(nodes)
+
+    def uright(k):
+        u = np.full(len(k), -1, np.float32)
+        st = rng.random(len(k)) < stereo_frac
+        u[st] = k["x"][st] - rng.uniform(2, 60, st.sum()).astype(np.float32)
+        return u
+
+    kf1 = KeyFrameView(k1, d1, uright(k1), (rng.random(n) < 0.3).astype(np.uint8), featvec(d1))
+    kf2 = KeyFrameView(k2, d2, uright(k2), (rng.random(n2) < 0.3).astype(np.uint8), featvec(d2))
+    tt = np.asarray(t, np.float64); t12 = -tt
+    t12x = np.array([[0, -t12[2], t12[1]], [t12[2], 0, -t12[0]], [-t12[1], t12[0], 0]])
+    Kd = K.astype(np.float64)
+    F12 = (np.linalg.inv(Kd).T @ t12x @ np.linalg.inv(Kd)).astype(np.float32)
+    return dict(kf1=kf1, kf2=kf2, Cw1=np.zeros(3, np.float32), R2w=np.eye(3, dtype=np.float32), t2w=np.asarray(t, np.float32),
+                K2=K, sf=sf, sig2=sig2, F12=F12, true12=perm, off=off)
+
+
 def bow_scene(seed=0, n1=1500, n2=1600, *, n_nodes=64, p_common=0.7, flips=12, p_valid=0.8, rotation=25.0, ties=0):
     """Two descriptor sets with a synthetic vocabulary for ORBmatcher::SearchByBoW: side 2 holds noisy copies (up to
     `flips` flipped bits) of a share of side 1 plus unrelated descriptors; a feature's node is a hash of a few

@@ -58,3 +58,33 @@ def test_bow_rejects_bad_arguments(ctx):
     bad = FeatureVector({3: [0, 1, 99]})                 # feature index past n1
     with pytest.raises(FrontendError):
         ORBmatcher(0.7, True, ctx).SearchByBoWFrame(s["desc1"], s["angle1"], s["valid1"], bad, s["desc2"], s["angle2"], s["fv2"])
+
+
+@pytest.mark.parametrize("seed,only_stereo,ori", [(1, False, True), (2, True, True), (3, False, False), (4, False, True)])
+def test_search_for_triangulation(ctx, seed, only_stereo, ori):
+    """SearchForTriangulation (src/ORBmatcher.cc:725-891): the whole inner loop runs on the device"""
+    from orb_slam_b200.matcher import ORBmatcher
+    kw = dict(t=(0.02, 0.01, 0.6), stereo_frac=0.0) if seed == 4 else {}         # seed 4: monocular, epipole inside the image
+    s = scenes.triangulation_scene(seed, **kw)
+    args = (s["kf1"], s["kf2"], s["Cw1"], s["R2w"], s["t2w"], s["K2"], s["sf"], s["sig2"], s["F12"], only_stereo)
+    n_g, m_g = ORBmatcher(0.6, ori, ctx).SearchForTriangulation(*args)
+    n_o, m_o = OracleMatcher(0.6, ori).SearchForTriangulation(*args)
+    assert n_g == n_o
+    np.testing.assert_array_equal(m_g, m_o)
+    assert n_g == int((m_g >= 0).sum()) and n_g > 50
+    i = np.nonzero(m_g >= 0)[0]
+    assert not np.any(s["kf1"].has_point[i]) and not np.any(s["kf2"].has_point[m_g[i]])
+    if only_stereo:
+        assert np.all(s["kf1"].uRight[i] >= 0) and np.all(s["kf2"].uRight[m_g[i]] >= 0)
+    assert (m_g[i] == s["true12"][i]).mean() > 0.9                              # and they are the planted correspondences
+
+
+def test_search_for_triangulation_empty(ctx):
+    from orb_slam_b200.matcher import FeatureVector, KeyFrameView, ORBmatcher
+    from orb_slam_b200._lib import KEYPOINT_DTYPE
+    s = scenes.triangulation_scene(5, n=50, extra=10)
+    empty = KeyFrameView(np.zeros(0, KEYPOINT_DTYPE), np.zeros((0, 32), np.uint8), np.zeros(0, np.float32), np.zeros(0, np.uint8), FeatureVector({}))
+    n, m = ORBmatcher(0.6, True, ctx).SearchForTriangulation(empty, s["kf2"], s["Cw1"], s["R2w"], s["t2w"], s["K2"], s["sf"], s["sig2"], s["F12"])
+    assert n == 0 and len(m) == 0
+    n, m = ORBmatcher(0.6, True, ctx).SearchForTriangulation(s["kf1"], empty, s["Cw1"], s["R2w"], s["t2w"], s["K2"], s["sf"], s["sig2"], s["F12"])
+    assert n == 0 and np.all(m == -1)

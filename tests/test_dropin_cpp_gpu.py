@@ -206,3 +206,23 @@ def test_search_by_projection_keyframe_member(H, th, orbdist):
     # only empty slots receive points, so a slot NULLed again by the rotation check looks untouched to the harness
     assert (a_o == -1).sum() > 0
     np.testing.assert_array_equal(a, np.where(a_o == -1, -2, a_o))
+
+
+@pytest.mark.parametrize("seed,only_stereo", [(31, False), (32, True)])
+def test_search_for_triangulation_member(H, seed, only_stereo):
+    """ORBmatcher::SearchForTriangulation(pKF1, pKF2, F12, vMatchedPairs, bOnlyStereo) member"""
+    s = scenes.triangulation_scene(seed)
+    n_o, m_o = OracleMatcher(0.6, True).SearchForTriangulation(s["kf1"], s["kf2"], s["Cw1"], s["R2w"], s["t2w"], s["K2"], s["sf"],
+                                                               s["sig2"], s["F12"], only_stereo)
+    s1, s2 = s["kf1"].struct(), s["kf2"].struct()
+    p = lambda a: C.c_void_p(np.ascontiguousarray(a, np.float32).ctypes.data)
+    K = s["K2"]
+    cw, r2w, t2w, f12 = (np.ascontiguousarray(s[k], np.float32) for k in ("Cw1", "R2w", "t2w", "F12"))
+    pairs = np.zeros((s["kf1"].N, 2), np.int32)
+    n = H.dropin_search_for_triangulation(C.byref(s1), C.byref(s2), C.c_void_p(cw.ctypes.data), C.c_void_p(r2w.ctypes.data),
+                                          C.c_void_p(t2w.ctypes.data), C.c_float(K[0, 0]), C.c_float(K[1, 1]), C.c_float(K[0, 2]),
+                                          C.c_float(K[1, 2]), C.c_void_p(s["sf"].ctypes.data), C.c_void_p(s["sig2"].ctypes.data), len(s["sf"]),
+                                          C.c_void_p(f12.ctypes.data), int(only_stereo), 1, C.c_void_p(pairs.ctypes.data), len(pairs))
+    assert n == n_o and n > 50
+    i = np.nonzero(m_o >= 0)[0]
+    np.testing.assert_array_equal(pairs[:n], np.stack([i, m_o[i]], axis=1))
