@@ -141,6 +141,22 @@ int orbm_search_by_projection_keyframe(orbm_t* m, const orbm_frame* cur, const o
                                        const uint8_t* already_found, const float* kf_angle, const uint8_t* cur_has_point,
                                        float th, int ORBdist, int checkOrientation, int32_t* cur_assign, int* nmatches);
 
+/* ORBmatcher::Fuse(pKF, vpMapPoints, th) (src/ORBmatcher.cc:893-1040), the selection part: for every map point the
+ * key-frame keypoint it would fuse with.  Selections are independent of one another; the caller applies
+ * Replace / AddObservation / AddMapPoint in order i, re-checking isBad() / IsInKeyFrame(pKF) first (an earlier
+ * replacement can only remove points from the eligible set, never add or alter one).
+ * kf: the key frame through the orbm_frame view (keysUn, descriptors, uRight = mvuRight (required), grid bounds,
+ * intrinsics, bf = mbf, Tcw = pose, scaleFactors); camera_center = pKF->GetCameraCenter() (3 floats; NULL: derived
+ * from Tcw as -Rcw.t()*tcw); inv_level_sigma2 = pKF->mvInvLevelSigma2.  points[i]: world,
+ * descriptor, valid, bad; in_keyframe[i] = pMP->IsInKeyFrame(pKF); normals = GetNormal() (3 floats per point);
+ * distances and `predict` as in orbm_search_by_projection_keyframe (PredictScale(dist3D, pKF), src/MapPoint.cc:385-400).
+ * best_idx out: npoints entries, keypoint index with bestDist <= TH_LOW, else -1. */
+int orbm_fuse_select(orbm_t* m, const orbm_frame* kf, const float* camera_center, const float* inv_level_sigma2,
+                     const orbm_mappoint* points, int npoints,
+                     const uint8_t* in_keyframe, const float* normals, const float* min_distance_inv, const float* max_distance_inv,
+                     const float* max_distance, float log_scale_factor, orbm_predict_scale_fn predict, void* user, float th,
+                     int32_t* best_idx);
+
 /* ---- ORBmatcher::SearchByBoW.  A DBoW2::FeatureVector (std::map<NodeId,
  * std::vector<unsigned>>) flattened in map order: node ids ascending, start[k]..start[k+1] = the
  * node's feature indices in their vector order. */

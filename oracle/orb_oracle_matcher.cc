@@ -325,6 +325,78 @@ int orbo_search_by_projection_keyframe(const orbm_frame* C, const orbm_mappoint*
     return nmatches;
 }
 
+// ORBmatcher::Fuse(pKF, vpMapPoints, th), src/ORBmatcher.cc:893-1040, up to the choice of bestIdx (the map edits that
+// follow - Replace / AddObservation / AddMapPoint - belong to the caller).  KeyFrame::GetFeaturesInArea
+// (src/KeyFrame.cc:569-608) is Frame::GetFeaturesInArea without the level gate, over the same grid.
+int orbo_fuse_select(const orbm_frame* pKF, const float* cameraCenter, const float* mvInvLevelSigma2, const orbm_mappoint* vpMapPoints, int nMPs,
+                     const uint8_t* inKeyFrame, const float* normals, const float* minMaxDistance, float mfLogScaleFactor, float th,
+                     int32_t* bestIdxOut) {
+    Grid g; AssignFeaturesToGrid(*pKF, g);
+    const float* Tc = pKF->Tcw;
+    const float tcw[3] = {Tc[3], Tc[7], Tc[11]};
+    float Ow[3];
+    for (int i = 0; i < 3; i++) {
+        double s = 0;
+        for (int k = 0; k < 3; k++) s += (double)Tc[4 * k + i] * (double)tcw[k];
+        Ow[i] = cameraCenter ? cameraCenter[i] : (float)(s * -1.0);      // pKF->GetCameraCenter()
+    }
+    const float fx = pKF->fx, fy = pKF->fy, cx = pKF->cx, cy = pKF->cy, bf = pKF->bf;
+    int nFused = 0;
+    for (int i = 0; i < nMPs; i++) {
+        bestIdxOut[i] = -1;
+        if (!vpMapPoints[i].valid) continue;
+        if (vpMapPoints[i].bad || inKeyFrame[i]) continue;
+        const float* p3Dw = vpMapPoints[i].world;
+        float p3Dc[3];
+        mul3(Tc, p3Dw, tcw, p3Dc);
+        if (p3Dc[2] < 0.0f) continue;
+        const float invz = 1 / p3Dc[2];
+        const float x = p3Dc[0] * invz;
+        const float y = p3Dc[1] * invz;
+        const float u = fx * x + cx;
+        const float v = fy * y + cy;
+        if (!(u >= pKF->mnMinX && u < pKF->mnMaxX && v >= pKF->mnMinY && v < pKF->mnMaxY)) continue;
+        const float ur = u - bf * invz;
+        const float maxDistance = 1.2f * minMaxDistance[2 * i + 1];
+        const float minDistance = 0.8f * minMaxDistance[2 * i];
+        float PO[3];
+        for (int k = 0; k < 3; k++) PO[k] = p3Dw[k] - Ow[k];
+        double nrm = 0;
+        for (int k = 0; k < 3; k++) nrm += (double)PO[k] * (double)PO[k];
+        const float dist3D = (float)std::sqrt(nrm);
+        if (dist3D < minDistance || dist3D > maxDistance) continue;
+        double dot = 0;                                      // cv::Mat::dot, CV_32F: double accumulator
+        for (int k = 0; k < 3; k++) dot += (double)PO[k] * (double)normals[3 * i + k];
+        if (dot < 0.5 * dist3D) continue;
+        const float ratio = minMaxDistance[2 * i + 1] / dist3D;
+        int nPredictedLevel = (int)std::ceil(std::log(ratio) / mfLogScaleFactor);
+        if (nPredictedLevel < 0) nPredictedLevel = 0;
+        else if (nPredictedLevel >= pKF->nScaleLevels) nPredictedLevel = pKF->nScaleLevels - 1;
+        const float radius = th * pKF->scaleFactors[nPredictedLevel];
+        const std::vector<size_t> vIndices = GetFeaturesInArea(*pKF, g, u, v, radius);
+        if (vIndices.empty()) continue;
+        int bestDist = 256, bestIdx = -1;
+        for (size_t idx : vIndices) {
+            const orbx_keypoint& kp = pKF->keysUn[idx];
+            const int kpLevel = kp.octave;
+            if (kpLevel < nPredictedLevel - 1 || kpLevel > nPredictedLevel) continue;
+            if (pKF->uRight[idx] >= 0) {
+                const float ex = u - kp.x, ey = v - kp.y, er = ur - pKF->uRight[idx];
+                const float e2 = ex * ex + ey * ey + er * er;
+                if (e2 * mvInvLevelSigma2[kpLevel] > 7.8) continue;
+            } else {
+                const float ex = u - kp.x, ey = v - kp.y;
+                const float e2 = ex * ex + ey * ey;
+                if (e2 * mvInvLevelSigma2[kpLevel] > 5.99) continue;
+            }
+            const int dist = DescriptorDistance(vpMapPoints[i].descriptor, pKF->descriptors + 32 * idx);
+            if (dist < bestDist) { bestDist = dist; bestIdx = (int)idx; }
+        }
+        if (bestDist <= TH_LOW) { bestIdxOut[i] = bestIdx; nFused++; }
+    }
+    return nFused;
+}
+
 int orbo_search_by_projection_points(const orbm_frame* F, const orbm_mappoint* pts, int npts, const int32_t* frameObs,
                                      float th, float mfNNratio, int32_t* frameAssign) {
     Grid g; AssignFeaturesToGrid(*F, g);

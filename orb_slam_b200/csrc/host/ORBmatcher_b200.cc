@@ -248,6 +248,81 @@ int ORBmatcher::SearchByBoW(KeyFrame* pKF1, KeyFrame* pKF2, std::vector<MapPoint
     return nmatches;
 }
 
+// src/ORBmatcher.cc:893-1040 (LocalMapping::SearchInNeighbors)
+namespace b200 {
+struct PredictKFCtx { const std::vector<MapPoint*>* pts; KeyFrame* pKF; };
+static int PredictKFThunk(void* user, int i, float dist3D) {
+    PredictKFCtx* c = static_cast<PredictKFCtx*>(user);
+    return (*c->pts)[i]->PredictScale(dist3D, c->pKF);                    // :954
+}
+// the key frame through the orbm_frame view (grid bounds are the key frame's own copies, include/KeyFrame.h:175-181)
+static void FillKeyFrame(orbm_frame& f, KeyFrame* pKF) {
+    std::memset(&f, 0, sizeof(f));
+    f.N = pKF->N;
+    f.keys = f.keysUn = (const orbx_keypoint*)pKF->mvKeysUn.data();
+    assert(pKF->N == 0 || (pKF->mDescriptors.isContinuous() && pKF->mDescriptors.cols == 32));
+    f.descriptors = pKF->mDescriptors.data;
+    f.uRight = pKF->mvuRight.data();
+    f.mnMinX = pKF->mnMinX; f.mnMaxX = pKF->mnMaxX; f.mnMinY = pKF->mnMinY; f.mnMaxY = pKF->mnMaxY;
+    f.gridElementWidthInv = pKF->mfGridElementWidthInv; f.gridElementHeightInv = pKF->mfGridElementHeightInv;
+    f.fx = pKF->fx; f.fy = pKF->fy; f.cx = pKF->cx; f.cy = pKF->cy; f.bf = pKF->mbf;
+    const cv::Mat Rcw = pKF->GetRotation(), tcw = pKF->GetTranslation();
+    for (int r = 0; r < 3; r++) {
+        for (int c = 0; c < 3; c++) f.Tcw[4 * r + c] = Rcw.at<float>(r, c);
+        f.Tcw[4 * r + 3] = tcw.at<float>(r);
+    }
+    f.Tcw[15] = 1.0f;
+    f.scaleFactors = pKF->mvScaleFactors.data();
+    f.nScaleLevels = (int)pKF->mvScaleFactors.size();
+}
+}  // namespace b200
+
+int ORBmatcher::Fuse(KeyFrame* pKF, const std::vector<MapPoint*>& vpMapPoints, const float th) {
+    orbm_frame kf;
+    b200::FillKeyFrame(kf, pKF);
+    const int nMPs = (int)vpMapPoints.size();
+    std::vector<orbm_mappoint> pts(nMPs);
+    std::vector<float> minInv(nMPs), maxInv(nMPs), normals(3 * (size_t)nMPs);
+    std::vector<uint8_t> inKF(nMPs);
+    for (int i = 0; i < nMPs; i++) {
+        MapPoint* pMP = vpMapPoints[i];
+        b200::FillPoint(pts[i], pMP);
+        if (!pMP) continue;
+        inKF[i] = pMP->IsInKeyFrame(pKF);
+        minInv[i] = pMP->GetMinDistanceInvariance(); maxInv[i] = pMP->GetMaxDistanceInvariance();
+        const cv::Mat Pn = pMP->GetNormal();
+        for (int k = 0; k < 3; k++) normals[3 * (size_t)i + k] = Pn.at<float>(k);
+    }
+    std::vector<int32_t> best(std::max(nMPs, 1), -1);
+    b200::PredictKFCtx pc = {&vpMapPoints, pKF};
+    const cv::Mat Ow = pKF->GetCameraCenter();
+    const float ow[3] = {Ow.at<float>(0), Ow.at<float>(1), Ow.at<float>(2)};
+    b200::Check(orbm_fuse_select(b200::MatcherContext(), &kf, ow, pKF->mvInvLevelSigma2.data(), pts.data(), nMPs, inKF.data(), normals.data(),
+                                 minInv.data(), maxInv.data(), NULL, 0.f, b200::PredictKFThunk, &pc, th, best.data()),
+                "orbm_fuse_select");
+    // the map edits of :1012-1035, in the reference's order; a point an earlier edit made bad or put into pKF is skipped,
+    // exactly as the reference's per-iteration test at :915 would
+    int nFused = 0;
+    for (int i = 0; i < nMPs; i++) {
+        if (best[i] < 0) continue;
+        MapPoint* pMP = vpMapPoints[i];
+        if (pMP->isBad() || pMP->IsInKeyFrame(pKF)) continue;
+        const int bestIdx = best[i];
+        MapPoint* pMPinKF = pKF->GetMapPoint(bestIdx);
+        if (pMPinKF) {
+            if (!pMPinKF->isBad()) {
+                if (pMPinKF->Observations() > pMP->Observations()) pMP->Replace(pMPinKF);
+                else pMPinKF->Replace(pMP);
+            }
+        } else {
+            pMP->AddObservation(pKF, bestIdx);
+            pKF->AddMapPoint(pMP, bestIdx);
+        }
+        nFused++;
+    }
+    return nFused;
+}
+
 // src/ORBmatcher.cc:725-891 (LocalMapping::CreateNewMapPoints)
 int ORBmatcher::SearchForTriangulation(KeyFrame* pKF1, KeyFrame* pKF2, cv::Mat F12,
                                        std::vector<std::pair<size_t, size_t> >& vMatchedPairs, const bool bOnlyStereo) {

@@ -4,17 +4,19 @@
 // cannot be compiled; inside the ORB-SLAM2 tree the real header is used instead.
 #ifndef MAPPOINT_H
 #define MAPPOINT_H
+#include <map>
 #include <opencv2/core/core.hpp>
 
 namespace ORB_SLAM2 {
 
 class Frame;
+class KeyFrame;
 
 class MapPoint {
 public:
     MapPoint() : mTrackProjX(0), mTrackProjY(0), mTrackProjXR(0), mbTrackInView(false), mnTrackScaleLevel(0),
                  mTrackViewCos(0), mnLastFrameSeen(0), mWorldPos(3, 1, CV_32F), mDescriptor(1, 32, CV_8U), nObs(0), mbBad(false),
-                 mfMinDistance(0), mfMaxDistance(0) {}
+                 mfMinDistance(0), mfMaxDistance(0), mNormalVector(3, 1, CV_32F), mpReplaced(NULL) {}
     cv::Mat GetWorldPos() { return mWorldPos.clone(); }
     cv::Mat GetDescriptor() { return mDescriptor.clone(); }
     int Observations() { return nObs; }
@@ -22,6 +24,12 @@ public:
     float GetMinDistanceInvariance() { return 0.8f * mfMinDistance; }      // src/MapPoint.cc:373-383
     float GetMaxDistanceInvariance() { return 1.2f * mfMaxDistance; }
     int PredictScale(const float& currentDist, Frame* pF);                // src/MapPoint.cc:402-417 (defined in lite/Frame.h)
+    int PredictScale(const float& currentDist, KeyFrame* pKF);            // src/MapPoint.cc:385-400 (defined in lite/KeyFrame.h)
+    cv::Mat GetNormal() { return mNormalVector.clone(); }
+    bool IsInKeyFrame(KeyFrame* pKF) { return mObservations.count(pKF) != 0; }
+    // simplified stand-ins of src/MapPoint.cc:104-121 and :186-225 (single key frame bookkeeping; defined in lite/KeyFrame.h)
+    void AddObservation(KeyFrame* pKF, size_t idx);
+    void Replace(MapPoint* pMP);
 
     // Variables used by the tracking (include/MapPoint.h:92-99)
     float mTrackProjX;
@@ -38,6 +46,9 @@ public:
     int nObs;
     bool mbBad;
     float mfMinDistance, mfMaxDistance;
+    cv::Mat mNormalVector;
+    std::map<KeyFrame*, size_t> mObservations;
+    MapPoint* mpReplaced;
 };
 
 }  // namespace ORB_SLAM2

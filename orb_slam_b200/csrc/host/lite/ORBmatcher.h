@@ -23,10 +23,11 @@ public:
     int SearchByProjection(Frame& CurrentFrame, KeyFrame* pKF, const std::set<MapPoint*>& sAlreadyFound, const float th, const int ORBdist);
     int SearchForTriangulation(KeyFrame* pKF1, KeyFrame* pKF2, cv::Mat F12, std::vector<std::pair<size_t, size_t> >& vMatchedPairs,
                                const bool bOnlyStereo);
+    int Fuse(KeyFrame* pKF, const std::vector<MapPoint*>& vpMapPoints, const float th = 3.0);
     int SearchByBoW(KeyFrame* pKF, Frame& F, std::vector<MapPoint*>& vpMapPointMatches);
     int SearchByBoW(KeyFrame* pKF1, KeyFrame* pKF2, std::vector<MapPoint*>& vpMatches12);
     // SearchByProjection(KeyFrame*, Scw, ...),
-    // SearchBySim3, Fuse x2: SURVEY 8(f) "next" rows - they stay the reference's own code.
+    // SearchBySim3, Fuse(pKF, Scw, ...): SURVEY 8(f) "next" rows - they stay the reference's own code.
 public:
     static const int TH_LOW;
     static const int TH_HIGH;

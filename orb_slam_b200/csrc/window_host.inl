@@ -415,4 +415,89 @@ int orbm_search_by_projection_keyframe(orbm_t* m, const orbm_frame* cur, const o
     return ORBX_OK;
 }
 
+// ORBmatcher::Fuse(pKF, vpMapPoints, th), src/ORBmatcher.cc:893-1040: selection of the keypoint every map point fuses with
+int orbm_fuse_select(orbm_t* m, const orbm_frame* kf, const float* cameraCenter, const float* invLevelSigma2,
+                     const orbm_mappoint* pts, int npts,
+                     const uint8_t* inKeyFrame, const float* normals, const float* minInv, const float* maxInv, const float* maxDistance,
+                     float logScaleFactor, orbm_predict_scale_fn predict, void* user, float th, int32_t* bestIdxOut) {
+    if (!m || !kf || !invLevelSigma2 || (!pts && npts) || npts < 0 || !bestIdxOut) return ORBX_E_INVALID;
+    if (npts > 0 && (!inKeyFrame || !normals || !minInv || !maxInv || (!predict && !maxDistance))) return ORBX_E_INVALID;
+    if (kf->nScaleLevels <= 0 || (kf->N > 0 && !kf->uRight)) return ORBX_E_INVALID;
+    std::lock_guard<std::mutex> lk(m->mtx);
+    CKM(cudaSetDevice(m->device));
+    DeviceFrame d;
+    int rc = upload_frame(m, kf, d);
+    if (rc) return rc;
+    const float* Tc = kf->Tcw;
+    const float tcw[3] = {Tc[3], Tc[7], Tc[11]};
+    float Ow[3];                                           // GetCameraCenter() = -Rcw.t()*tcw (KeyFrame::SetPose, src/KeyFrame.cc:70-85)
+    for (int i = 0; i < 3; i++) {
+        double s = 0;
+        for (int k = 0; k < 3; k++) s += (double)Tc[4 * k + i] * (double)tcw[k];
+        Ow[i] = cameraCenter ? cameraCenter[i] : (float)(s * -1.0);
+    }
+    struct Q { int i; float u, v, ur; };
+    std::vector<Q> meta; std::vector<WQuery> queries;
+    for (int i = 0; i < npts; i++) {
+        bestIdxOut[i] = -1;
+        if (!pts[i].valid) continue;
+        if (pts[i].bad || inKeyFrame[i]) continue;
+        float p3Dc[3];
+        mat3_mul_add(Tc, 4, pts[i].world, tcw, p3Dc);
+        if (p3Dc[2] < 0.0f) continue;                                          // depth must be positive
+        const float invz = 1 / p3Dc[2];
+        const float x = p3Dc[0] * invz, y = p3Dc[1] * invz;
+        const float u = kf->fx * x + kf->cx, v = kf->fy * y + kf->cy;
+        if (!(u >= kf->mnMinX && u < kf->mnMaxX && v >= kf->mnMinY && v < kf->mnMaxY)) continue;    // KeyFrame::IsInImage
+        const float ur = u - kf->bf * invz;
+        float PO[3];
+        double s2 = 0, dot = 0;
+        for (int k = 0; k < 3; k++) {
+            PO[k] = pts[i].world[k] - Ow[k];
+            s2 += (double)PO[k] * (double)PO[k];                               // cv::norm: double accumulator
+            dot += (double)PO[k] * (double)normals[3 * i + k];                 // cv::Mat::dot on CV_32F: double accumulator
+        }
+        const float dist3D = (float)std::sqrt(s2);
+        if (dist3D < minInv[i] || dist3D > maxInv[i]) continue;
+        if (dot < 0.5 * dist3D) continue;                                      // viewing angle below 60 degrees
+        int nPredictedLevel;
+        if (predict) nPredictedLevel = predict(user, i, dist3D);
+        else {
+            const float ratio = maxDistance[i] / dist3D;
+            nPredictedLevel = (int)std::ceil(std::log(ratio) / logScaleFactor);
+            if (nPredictedLevel < 0) nPredictedLevel = 0;
+            else if (nPredictedLevel >= kf->nScaleLevels) nPredictedLevel = kf->nScaleLevels - 1;
+        }
+        if (nPredictedLevel < 0 || nPredictedLevel >= kf->nScaleLevels) return ORBX_E_INVALID;
+        WQuery q; std::memset(&q, 0, sizeof(q));
+        q.x = u; q.y = v; q.r = th * kf->scaleFactors[nPredictedLevel];
+        q.minLevel = nPredictedLevel - 1; q.maxLevel = nPredictedLevel;        // the kpLevel gate of :972-973
+        set_desc(q, pts[i].descriptor);
+        queries.push_back(q); meta.push_back(Q{i, u, v, ur});
+    }
+    std::vector<int32_t> offs; std::vector<int2> pairs;
+    if ((rc = run_queries(m, d, queries, offs, pairs))) return rc;
+    for (size_t qi = 0; qi < queries.size(); qi++) {
+        const Q& mq = meta[qi];
+        int bestDist = 256, bestIdx = -1;
+        for (int k = offs[qi]; k < offs[qi + 1]; k++) {
+            const int idx = pairs[k].x;
+            const orbx_keypoint& kp = kf->keysUn[idx];
+            const float ex = mq.u - kp.x, ey = mq.v - kp.y;
+            if (kf->uRight[idx] >= 0) {                                        // stereo reprojection error, :975-989
+                const float er = mq.ur - kf->uRight[idx];
+                const float e2 = ex * ex + ey * ey + er * er;
+                if (e2 * invLevelSigma2[kp.octave] > 7.8) continue;
+            } else {
+                const float e2 = ex * ex + ey * ey;
+                if (e2 * invLevelSigma2[kp.octave] > 5.99) continue;
+            }
+            const int dist = pairs[k].y;
+            if (dist < bestDist) { bestDist = dist; bestIdx = idx; }
+        }
+        if (bestDist <= ORBM_TH_LOW) bestIdxOut[mq.i] = bestIdx;
+    }
+    return ORBX_OK;
+}
+
 }  // extern "C"

@@ -139,6 +139,8 @@ def _bind(L):
     L.orbm_search_by_projection_points.restype = i
     L.orbm_search_by_projection_keyframe.argtypes = [vp, vp, vp, i, vp, vp, vp, f, vp, vp, vp, vp, vp, f, i, i, vp, C.POINTER(i)]
     L.orbm_search_by_projection_keyframe.restype = i
+    L.orbm_fuse_select.argtypes = [vp, vp, vp, vp, vp, i, vp, vp, vp, vp, vp, f, vp, vp, f, vp]
+    L.orbm_fuse_select.restype = i
     L.orbm_search_for_triangulation.argtypes = [vp, vp, vp, vp, vp, vp, f, f, f, f, vp, vp, i, vp, i, i, vp, C.POINTER(i)]
     L.orbm_search_for_triangulation.restype = i
     L.orbm_search_by_bow.argtypes = [vp, i, vp, vp, vp, i, vp, vp, vp, vp, i, vp, f, i, vp, C.POINTER(i)]
@@ -270,6 +272,26 @@ class ORBmatcher:
                                                       has.ctypes.data, th, int(ORBdist), int(self.mbCheckOrientation),
                                                       out.ctypes.data, C.byref(n)), "orbm_search_by_projection_keyframe")
         return n.value, out[: CurrentFrame.N]
+
+    def FuseSelect(self, KF: Frame, inv_level_sigma2, points: np.ndarray, in_keyframe, normals, min_max_distance, th: float = 3.0,
+                   log_scale_factor: float | None = None):
+        """Selection part of Fuse(pKF, vpMapPoints, th) (src/ORBmatcher.cc:893-1040): best_idx[i] = key-frame keypoint map
+        point i fuses with, or -1.  KF is the key frame seen through the Frame view (pose in mTcw, mvuRight set)."""
+        c = self._c()
+        p = np.ascontiguousarray(points, MAPPOINT_DTYPE)
+        mm = np.ascontiguousarray(min_max_distance, np.float32).reshape(-1, 2)
+        mn_inv = (np.float32(0.8) * mm[:, 0]).astype(np.float32); mx_inv = (np.float32(1.2) * mm[:, 1]).astype(np.float32)
+        mx = np.ascontiguousarray(mm[:, 1])
+        ik = np.ascontiguousarray(in_keyframe, np.uint8); nr = np.ascontiguousarray(normals, np.float32).reshape(-1, 3)
+        sg = np.ascontiguousarray(inv_level_sigma2, np.float32)
+        if log_scale_factor is None:
+            log_scale_factor = float(np.log(np.float32(KF.mvScaleFactors[1])))
+        out = np.zeros(max(len(p), 1), np.int32)
+        sk = KF.struct()
+        check(c._L.orbm_fuse_select(c.h, C.byref(sk), None, sg.ctypes.data, p.ctypes.data, len(p), ik.ctypes.data, nr.ctypes.data,
+                                    mn_inv.ctypes.data, mx_inv.ctypes.data, mx.ctypes.data, log_scale_factor, None, None, th,
+                                    out.ctypes.data), "orbm_fuse_select")
+        return out[: len(p)]
 
     def _bow(self, variant, desc1, angle1, valid1, fv1: FeatureVector, desc2, angle2, valid2, fv2: FeatureVector):
         c = self._c()

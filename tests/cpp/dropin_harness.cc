@@ -318,4 +318,57 @@ int dropin_search_for_triangulation(const orbm_keyframe* kf1, const orbm_keyfram
     return n;
 }
 
+// ORBmatcher::Fuse(pKF, vpMapPoints, th) as LocalMapping::SearchInNeighbors calls it (LocalMapping.cc:411-417).
+// order[j] = index into the point table of the j-th entry of vpMapPoints (so one point can be listed twice);
+// kfPoint[idx] >= 0: the key frame already holds a map point at keypoint idx with that many observations (kfBad: isBad()).
+// Out: kfSlot[idx] = -1 empty, -2 the original point, >= 0 point-table index now stored there; pointBad[i] after the call.
+int dropin_fuse(const orbm_frame* kf, const float* invSigma2, const orbm_mappoint* pts, int npts, const float* minmax, const float* normals,
+                const uint8_t* inKF, const int32_t* order, int norder, const int32_t* kfPoint, const uint8_t* kfBad, float th,
+                int32_t* kfSlot, uint8_t* pointBad) {
+    KeyFrame K;
+    K.N = kf->N;
+    K.mvKeysUn.assign((const cv::KeyPoint*)kf->keysUn, (const cv::KeyPoint*)kf->keysUn + kf->N);
+    K.mDescriptors.create(kf->N, 32, CV_8U);
+    if (kf->N) std::memcpy(K.mDescriptors.data, kf->descriptors, (size_t)kf->N * 32);
+    K.mvuRight.assign(kf->uRight, kf->uRight + kf->N);
+    K.fx = kf->fx; K.fy = kf->fy; K.cx = kf->cx; K.cy = kf->cy; K.mbf = kf->bf;
+    K.mnMinX = (int)kf->mnMinX; K.mnMaxX = (int)kf->mnMaxX; K.mnMinY = (int)kf->mnMinY; K.mnMaxY = (int)kf->mnMaxY;
+    K.mfGridElementWidthInv = kf->gridElementWidthInv; K.mfGridElementHeightInv = kf->gridElementHeightInv;
+    K.mvScaleFactors.assign(kf->scaleFactors, kf->scaleFactors + kf->nScaleLevels);
+    K.mvInvLevelSigma2.assign(invSigma2, invSigma2 + kf->nScaleLevels);
+    K.mnScaleLevels = kf->nScaleLevels; K.mfScaleFactor = kf->scaleFactors[1]; K.mfLogScaleFactor = std::log(K.mfScaleFactor);
+    for (int r = 0; r < 3; r++) {
+        K.tcw.at<float>(r) = kf->Tcw[4 * r + 3];
+        for (int c = 0; c < 3; c++) K.Rcw.at<float>(r, c) = kf->Tcw[4 * r + c];
+    }
+    for (int i = 0; i < 3; i++) {                                     // Ow = -Rwc*tcw (KeyFrame::SetPose)
+        double s = 0;
+        for (int k = 0; k < 3; k++) s += (double)kf->Tcw[4 * k + i] * (double)kf->Tcw[4 * k + 3];
+        K.Ow.at<float>(i) = (float)(s * -1.0);
+    }
+    std::vector<MapPoint> orig(kf->N), table(npts);
+    KeyFrame other;                                                    // where listed points "already in a key frame" live
+    other.mvuRight.assign(1, -1.0f); other.mvpMapPoints.assign(1, static_cast<MapPoint*>(NULL));
+    K.mvpMapPoints.assign(kf->N, static_cast<MapPoint*>(NULL));
+    for (int i = 0; i < kf->N; i++)
+        if (kfPoint[i] >= 0) { orig[i].mbBad = kfBad[i] != 0; K.mvpMapPoints[i] = &orig[i]; orig[i].mObservations[&K] = i; orig[i].nObs = kfPoint[i]; }
+    for (int i = 0; i < npts; i++) {
+        if (!pts[i].valid) continue;
+        point_from(table[i], pts[i]);
+        table[i].mfMinDistance = minmax[2 * i]; table[i].mfMaxDistance = minmax[2 * i + 1];
+        for (int k = 0; k < 3; k++) table[i].mNormalVector.at<float>(k) = normals[3 * i + k];
+        if (inKF[i]) table[i].mObservations[&K] = 0;                   // IsInKeyFrame(pKF)
+    }
+    std::vector<MapPoint*> vp(norder);
+    for (int j = 0; j < norder; j++) vp[j] = (order[j] >= 0 && pts[order[j]].valid) ? &table[order[j]] : static_cast<MapPoint*>(NULL);
+    ORBmatcher matcher(0.6f, true);
+    const int n = matcher.Fuse(&K, vp, th);
+    for (int i = 0; i < kf->N; i++) {
+        MapPoint* p = K.mvpMapPoints[i];
+        kfSlot[i] = !p ? -1 : (p == &orig[i] ? -2 : (int32_t)(p - table.data()));
+    }
+    for (int i = 0; i < npts; i++) pointBad[i] = table[i].mbBad;
+    return n;
+}
+
 }  // extern "C"

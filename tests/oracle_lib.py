@@ -174,6 +174,7 @@ def _bind_matcher(L):
     L.orbo_search_by_projection_points.argtypes = [vp, vp, i, vp, f, f, vp]
     L.orbo_bf2nn.argtypes = [vp, i, vp, C.c_size_t, C.c_uint32, vp]
     L.orbo_search_by_projection_keyframe.argtypes = [vp, vp, i, vp, f, vp, vp, vp, f, i, i, vp]
+    L.orbo_fuse_select.argtypes = [vp, vp, vp, vp, i, vp, vp, vp, f, f, vp]
     L.orbo_search_for_triangulation.argtypes = [vp, vp, vp, vp, vp, f, f, f, f, vp, vp, vp, i, i, vp]
     L.orbo_search_by_bow_kf_frame.argtypes = [vp, vp, vp, i, vp, vp, vp, i, vp, f, i, vp]
     L.orbo_search_by_bow_kf_kf.argtypes = [vp, vp, vp, i, vp, vp, vp, vp, i, vp, f, i, vp]
@@ -253,6 +254,19 @@ class OracleMatcher:
         n = self.L.orbo_search_by_projection_keyframe(C.byref(s), p.ctypes.data, len(p), mm.ctypes.data, log_scale_factor, af.ctypes.data,
                                                       ang.ctypes.data, has.ctypes.data, th, int(ORBdist), int(self.checkOri), out.ctypes.data)
         return n, out[: cur.N]
+
+    def FuseSelect(self, KF, inv_level_sigma2, points, in_keyframe, normals, min_max_distance, th=3.0, log_scale_factor=None):
+        from orb_slam_b200.matcher import MAPPOINT_DTYPE
+        p = np.ascontiguousarray(points, MAPPOINT_DTYPE); mm = np.ascontiguousarray(min_max_distance, np.float32).reshape(-1, 2)
+        ik = np.ascontiguousarray(in_keyframe, np.uint8); nr = np.ascontiguousarray(normals, np.float32).reshape(-1, 3)
+        sg = np.ascontiguousarray(inv_level_sigma2, np.float32)
+        if log_scale_factor is None:
+            log_scale_factor = float(np.log(np.float32(KF.mvScaleFactors[1])))
+        out = np.zeros(max(len(p), 1), np.int32)
+        s = KF.struct()
+        self.L.orbo_fuse_select(C.byref(s), None, sg.ctypes.data, p.ctypes.data, len(p), ik.ctypes.data, nr.ctypes.data, mm.ctypes.data,
+                                log_scale_factor, th, out.ctypes.data)
+        return out[: len(p)]
 
     def SearchByBoWFrame(self, descKF, angleKFun, validKF, fvKF, descF, angleF, fvF):
         d1 = np.ascontiguousarray(descKF, np.uint8).reshape(-1, 32); d2 = np.ascontiguousarray(descF, np.uint8).reshape(-1, 32)

@@ -98,6 +98,22 @@ def keyframe_points(kf: Frame, seed=0, p_valid=0.85):
     return pts, mm, already
 
 
+def fuse_points(src: Frame, seed=0):
+    """Map points seen from a neighbouring key frame `src` (pose identity) that LocalMapping::SearchInNeighbors would try
+    to fuse into another key frame: keyframe_points plus the mean viewing direction (MapPoint::GetNormal) and the
+    IsInKeyFrame flag."""
+    rng = np.random.default_rng(seed + 1000)
+    pts, mm, _ = keyframe_points(src, seed=seed, p_valid=0.9)
+    w = pts["world"].astype(np.float32)
+    normals = w / np.linalg.norm(w, axis=1, keepdims=True)
+    normals = normals + rng.normal(0, 0.15, normals.shape)
+    flip = rng.random(len(w)) < 0.05                     # a few seen from the other side: viewing-angle gate
+    normals[flip] *= -1
+    normals = (normals / np.linalg.norm(normals, axis=1, keepdims=True)).astype(np.float32)
+    in_kf = (rng.random(len(w)) < 0.2).astype(np.uint8)
+    return pts, mm, normals, in_kf
+
+
 def triangulation_scene(seed=0, n=1500, extra=400, t=(0.4, 0.02, 0.05), stereo_frac=0.5, n_nodes=60, flips=6, outlier_frac=0.1):
     """Two key frames for ORBmatcher::SearchForTriangulation: key frame 1 at the origin, key frame 2 = translation t.
     Key frame 2 observes noisy reprojections of key frame 1's points (descriptors with up to `flips` flipped bits; a

@@ -226,3 +226,54 @@ def test_search_for_triangulation_member(H, seed, only_stereo):
     assert n == n_o and n > 50
     i = np.nonzero(m_o >= 0)[0]
     np.testing.assert_array_equal(pairs[:n], np.stack([i, m_o[i]], axis=1))
+
+
+def test_fuse_member(H):
+    """ORBmatcher::Fuse(pKF, vpMapPoints, th): selection on the device, Replace / AddObservation applied by the member in the
+    reference's order (points listed twice, occupied and bad slots)"""
+    from orb_slam_b200.matcher import MAPPOINT_DTYPE
+    (ka, da), (kb, db) = scenes.extract_pair(OracleExtractor, 1241, 376, 2000, 36, (-3, 2))
+    src = scenes.make_frame(ka, da, 1241, 376)
+    Tcw = np.eye(4, dtype=np.float32); Tcw[:3, 3] = [-0.05, 0.02, 0.2]
+    kf = scenes.make_frame(kb, db, 1241, 376, stereo=False, Tcw=Tcw, seed=8)
+    kf.mvuRight = np.full(kf.N, -1, np.float32)
+    pts, mm, normals, in_kf = scenes.fuse_points(src, seed=22)
+    rng = np.random.default_rng(23)
+    pts["observations"] = rng.integers(1, 6, len(pts))
+    sf = kf.mvScaleFactors
+    inv_sigma2 = (1.0 / (sf * sf)).astype(np.float32)
+    order = np.concatenate([np.arange(len(pts)), rng.integers(0, len(pts), 300)]).astype(np.int32)     # 300 points listed twice
+    kf_point = np.where(rng.random(kf.N) < 0.4, rng.integers(1, 6, kf.N), -1).astype(np.int32)         # occupied slots: observations
+    kf_bad = ((kf_point >= 0) & (rng.random(kf.N) < 0.1)).astype(np.uint8)
+    best = OracleMatcher(0.6, True).FuseSelect(kf, inv_sigma2, pts, in_kf, normals, mm, 3.0)
+    # replay of src/ORBmatcher.cc:1012-1035 on plain arrays
+    slot = np.where(kf_point >= 0, -2, -1).astype(np.int32)
+    slot_obs = kf_point.copy(); slot_bad = kf_bad.copy().astype(bool)
+    p_bad = pts["bad"].astype(bool).copy(); p_in = in_kf.astype(bool).copy(); p_obs = pts["observations"].astype(np.int64).copy()
+    n_exp = 0
+    for j in order:
+        if not pts["valid"][j] or best[j] < 0 or p_bad[j] or p_in[j]:
+            continue
+        b = best[j]
+        if slot[b] != -1:
+            if not slot_bad[b]:
+                if slot_obs[b] > p_obs[j]:
+                    p_bad[j] = True                                   # pMP->Replace(pMPinKF)
+                else:                                                 # pMPinKF->Replace(pMP): pMP takes the slot and its observation
+                    if slot[b] >= 0:
+                        p_bad[slot[b]] = True
+                    slot[b] = j; slot_obs[b] = p_obs[j] + 1; p_obs[j] += 1; p_in[j] = True
+        else:
+            slot[b] = j; p_in[j] = True; p_obs[j] += 1; slot_obs[b] = p_obs[j]; slot_bad[b] = False
+        n_exp += 1
+    p = lambda a: C.c_void_p(a.ctypes.data)
+    sk = kf.struct()
+    ptsc = np.ascontiguousarray(pts, MAPPOINT_DTYPE); mmc = np.ascontiguousarray(mm, np.float32); nrc = np.ascontiguousarray(normals, np.float32)
+    got_slot = np.zeros(kf.N, np.int32); got_bad = np.zeros(len(pts), np.uint8)
+    n = H.dropin_fuse(C.byref(sk), p(inv_sigma2), p(ptsc), len(pts), p(mmc), p(nrc), p(in_kf), p(order), len(order), p(kf_point), p(kf_bad),
+                      C.c_float(3.0), p(got_slot), p(got_bad))
+    assert n == n_exp and n > 100
+    np.testing.assert_array_equal(got_slot, slot)
+    ok = pts["valid"] == 1                                        # NULL entries have no MapPoint object behind them
+    np.testing.assert_array_equal(got_bad.astype(bool)[ok], p_bad[ok])
+    assert (p_bad & ~pts["bad"].astype(bool))[ok].sum() > 10      # replacements did happen

@@ -117,6 +117,28 @@ def test_search_by_projection_keyframe(ctx, th, orbdist, tz):
     assert not np.any(has[a_g >= 0]) and not np.any(already[m]) and np.all(pts["valid"][m] == 1) and not np.any(pts["bad"][m])
 
 
+@pytest.mark.parametrize("stereo,th,tz", [(True, 3.0, 0.2), (False, 3.0, -0.3), (True, 6.0, 1.5)])
+def test_fuse_select(ctx, stereo, th, tz):
+    """ORBmatcher::Fuse(pKF, vpMapPoints, th) (:893-1040): the keypoint every map point fuses with"""
+    from orb_slam_b200.matcher import ORBmatcher
+    (ka, da), (kb, db) = scenes.extract_pair(OracleExtractor, 1241, 376, 2000, 35, (-3, 2))
+    src = scenes.make_frame(ka, da, 1241, 376)
+    Tcw = np.eye(4, dtype=np.float32); Tcw[:3, 3] = [-0.05, 0.02, tz]
+    kf = scenes.make_frame(kb, db, 1241, 376, stereo=stereo, Tcw=Tcw, seed=7)
+    if not stereo:
+        kf.mvuRight = np.full(kf.N, -1, np.float32)
+    pts, mm, normals, in_kf = scenes.fuse_points(src, seed=21)
+    sf = kf.mvScaleFactors
+    inv_sigma2 = (1.0 / (sf * sf)).astype(np.float32)
+    args = (kf, inv_sigma2, pts, in_kf, normals, mm, th)
+    g = ORBmatcher(0.6, True, ctx).FuseSelect(*args)
+    o = OracleMatcher(0.6, True).FuseSelect(*args)
+    assert np.array_equal(g, o)
+    sel = g >= 0
+    assert sel.sum() > 20
+    assert not np.any(in_kf[sel]) and np.all(pts["valid"][sel] == 1) and not np.any(pts["bad"][sel])
+
+
 def test_bruteforce_2nn_and_sharded_merge(ctx):
     import ctypes as C
     import torch
