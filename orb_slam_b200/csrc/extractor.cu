@@ -216,7 +216,7 @@ static int build_geometry(orbx_extractor* e, int width, int height, FrameGeom& g
     g.candTotal = (candOff + 63) & ~63ULL;
     g.slotTotal = (slotOff + 63) & ~63ULL;
     g.nodeCap = 1 << ceil_log2(nodeNeed);
-    if (qt_smem_bytes(g.nodeCap) > 200 * 1024) return ORBX_E_UNSUPPORTED;
+    if (qt_smem_bytes(g.nodeCap, QT_THREADS_LATENCY) > 200 * 1024) return ORBX_E_UNSUPPORTED;
     return ORBX_OK;
 }
 
@@ -294,7 +294,8 @@ static int ensure_workspace(orbx_extractor* e, int width, int height, int frames
     e->capFrames = newCap;
     e->haveGeom = true;
     // kernel attributes
-    CK(cudaFuncSetAttribute(quadtree_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)qt_smem_bytes(g.nodeCap)));
+    CK(cudaFuncSetAttribute(quadtree_kernel<QT_THREADS_BATCH>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)qt_smem_bytes(g.nodeCap, QT_THREADS_BATCH)));
+    CK(cudaFuncSetAttribute(quadtree_kernel<QT_THREADS_LATENCY>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)qt_smem_bytes(g.nodeCap, QT_THREADS_LATENCY)));
     CK(cudaFuncSetAttribute(pyr_level_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
     CK(cudaFuncSetAttribute(pyr_level_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
     return ORBX_OK;
@@ -403,7 +404,11 @@ static int enqueue_pipeline(orbx_extractor* e, int wi, const uint8_t* src, size_
         q.cellOff[l] = v.cellOff; q.slotOff[l] = v.slotOff; q.slotCap[l] = v.slotCap; q.candCap[l] = v.candCap;
     }
     q.cellOff[g.nlevels] = g.totalCells;
-    quadtree_kernel<<<dim3(frames, g.nlevels), QT_THREADS, qt_smem_bytes(g.nodeCap), st>>>(q);
+    // many frames: small blocks (throughput); a handful of frames: the level-0 block is the critical path, give it more threads
+    if (frames * g.nlevels >= 2 * 148)
+        quadtree_kernel<QT_THREADS_BATCH><<<dim3(frames, g.nlevels), QT_THREADS_BATCH, qt_smem_bytes(g.nodeCap, QT_THREADS_BATCH), st>>>(q);
+    else
+        quadtree_kernel<QT_THREADS_LATENCY><<<dim3(frames, g.nlevels), QT_THREADS_LATENCY, qt_smem_bytes(g.nodeCap, QT_THREADS_LATENCY), st>>>(q);
     launches++;
     if (evs) CK(cudaEventRecord(evs[4], st));
     // 5. orientation, descriptors, output assembly
@@ -702,9 +707,13 @@ int orbx_extract_batch(orbx_t* e, const uint8_t* const* images, int n, int width
         // compute streams fed.
         while (status == ORBX_OK && finalized <= k - ORBX_NBUF) { rc = finalize(finalized++); if (rc != ORBX_OK) status = rc; }
         if (status != ORBX_OK) break;
+        // a call with a single chunk (one frame: Tracking's case) runs copy-in, kernels and copy-out on one stream:
+        // no cross-stream event hops on the latency path
+        cudaStream_t cst = e->ws[k & 1].stream;                          // workspace / compute stream of this parity
+        cudaStream_t sIn = nchunks == 1 ? cst : e->sIn, sOut = nchunks == 1 ? cst : e->sOut;
         // ---- copy-in stream: d_in[b] is free once the compute of chunk k - ORBX_NBUF has finished
-        if (k >= ORBX_NBUF) CK(cudaStreamWaitEvent(e->sIn, e->evCompute[b], 0));
-        mark(k, 0, e->sIn);
+        if (k >= ORBX_NBUF) CK(cudaStreamWaitEvent(sIn, e->evCompute[b], 0));
+        mark(k, 0, sIn);
         if (inPinned) {
             // frames that lie back to back in host memory go as one linear copy
             int i = 0;
@@ -712,7 +721,7 @@ int orbx_extract_batch(orbx_t* e, const uint8_t* const* images, int n, int width
                 int j = i + 1;
                 while (j < nf && images[f0 + j] == images[f0 + j - 1] + devStride) j++;
                 const size_t bytes = (size_t)(j - i - 1) * devStride + (size_t)(height - 1) * step + width;   // never past the last pixel
-                CK(cudaMemcpyAsync(e->d_in[b] + (size_t)i * devStride, images[f0 + i], bytes, cudaMemcpyHostToDevice, e->sIn));
+                CK(cudaMemcpyAsync(e->d_in[b] + (size_t)i * devStride, images[f0 + i], bytes, cudaMemcpyHostToDevice, sIn));
                 i = j;
             }
         } else {
@@ -723,13 +732,12 @@ int orbx_extract_batch(orbx_t* e, const uint8_t* const* images, int n, int width
                 if (step == (size_t)width) std::memcpy(dst, srcp, (size_t)width * height);
                 else for (int y = 0; y < height; y++) std::memcpy(dst + (size_t)y * width, srcp + (size_t)y * step, width);
             }
-            CK(cudaMemcpyAsync(e->d_in[b], e->h_in[b], (size_t)width * height * nf, cudaMemcpyHostToDevice, e->sIn));
+            CK(cudaMemcpyAsync(e->d_in[b], e->h_in[b], (size_t)width * height * nf, cudaMemcpyHostToDevice, sIn));
         }
-        CK(cudaEventRecord(e->evIn[b], e->sIn));
-        mark(k, 1, e->sIn);
+        CK(cudaEventRecord(e->evIn[b], sIn));
+        mark(k, 1, sIn);
         // ---- compute stream: needs the input, and d_res[b] drained by the copy-out of chunk k-2
-        cudaStream_t cst = e->ws[k & 1].stream;                          // workspace / compute stream of this parity
-        CK(cudaStreamWaitEvent(cst, e->evIn[b], 0));
+        if (nchunks > 1) CK(cudaStreamWaitEvent(cst, e->evIn[b], 0));
         if (k >= ORBX_NBUF) CK(cudaStreamWaitEvent(cst, e->evOut[b], 0));
         mark(k, 2, cst);
         int* d_n = (int*)e->d_res[b];
@@ -742,24 +750,26 @@ int orbx_extract_batch(orbx_t* e, const uint8_t* const* images, int n, int width
         CK(cudaEventRecord(e->evCompute[b], cst));
         mark(k, 3, cst);
         // ---- copy-out stream
-        CK(cudaStreamWaitEvent(e->sOut, e->evCompute[b], 0));
-        CK(cudaMemcpyAsync(e->h_res[b], e->d_res[b], head, cudaMemcpyDeviceToHost, e->sOut));
+        if (nchunks > 1) CK(cudaStreamWaitEvent(sOut, e->evCompute[b], 0));
+        CK(cudaMemcpyAsync(e->h_res[b], e->d_res[b], head, cudaMemcpyDeviceToHost, sOut));
         if (outPinned) {
             CK(cudaMemcpy2DAsync(keypoints + (size_t)f0 * capacity, (size_t)capacity * kpBytes, d_kps, (size_t)cap * kpBytes,
-                                 (size_t)cap * kpBytes, nf, cudaMemcpyDeviceToHost, e->sOut));
+                                 (size_t)cap * kpBytes, nf, cudaMemcpyDeviceToHost, sOut));
             CK(cudaMemcpy2DAsync(descriptors + (size_t)f0 * capacity * 32, (size_t)capacity * 32, d_desc, (size_t)cap * 32,
-                                 (size_t)cap * 32, nf, cudaMemcpyDeviceToHost, e->sOut));
+                                 (size_t)cap * 32, nf, cudaMemcpyDeviceToHost, sOut));
         } else {
-            CK(cudaMemcpyAsync(e->h_res[b] + head, d_kps, (size_t)nf * cap * kpBytes, cudaMemcpyDeviceToHost, e->sOut));
+            CK(cudaMemcpyAsync(e->h_res[b] + head, d_kps, (size_t)nf * cap * kpBytes, cudaMemcpyDeviceToHost, sOut));
             CK(cudaMemcpyAsync(e->h_res[b] + head + (size_t)F * cap * kpBytes, d_desc, (size_t)nf * cap * 32,
-                               cudaMemcpyDeviceToHost, e->sOut));
+                               cudaMemcpyDeviceToHost, sOut));
         }
-        CK(cudaEventRecord(e->evOut[b], e->sOut));
-        mark(k, 4, e->sOut);
+        CK(cudaEventRecord(e->evOut[b], sOut));
+        mark(k, 4, sOut);
     }
     while (status == ORBX_OK && finalized < nchunks) { rc = finalize(finalized++); if (rc != ORBX_OK) status = rc; }
-    CK(cudaStreamSynchronize(e->sIn)); CK(cudaStreamSynchronize(e->ws[0].stream)); CK(cudaStreamSynchronize(e->ws[1].stream));
-    CK(cudaStreamSynchronize(e->sOut));
+    if (nchunks > 1 || status != ORBX_OK) {     // (a single chunk was fully waited for by finalize)
+        CK(cudaStreamSynchronize(e->sIn)); CK(cudaStreamSynchronize(e->ws[0].stream)); CK(cudaStreamSynchronize(e->ws[1].stream));
+        CK(cudaStreamSynchronize(e->sOut));
+    }
     if (trace) {
         for (int k = 0; k < nchunks; k++) {
             float t[5];

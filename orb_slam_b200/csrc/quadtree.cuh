@@ -21,8 +21,10 @@
 
 namespace orbx {
 
-constexpr int QT_THREADS = 128;
-constexpr int QT_WARPS = QT_THREADS / 32;
+// block sizes of quadtree_kernel<NT>: small blocks for batches (many independent (frame, level) blocks per SM), large ones
+// when a call holds only a few frames and the level-0 block is the critical path
+constexpr int QT_THREADS_BATCH = 128;
+constexpr int QT_THREADS_LATENCY = 512;
 
 struct QtArgs {
     uint32_t* cand;                  // packed x:12|y:12|score:8, [frames][candTotal]: vToDistributeKeys, built here
@@ -52,7 +54,10 @@ struct QtArgs {
 
 // exclusive scan of arr[0..n) in shared memory by the whole block; returns the total.  Every warp scans one contiguous
 // segment 32 elements at a time (conflict-free, carry in a register); the warp totals are exchanged once.
+template <int NT>
 __device__ int block_scan_excl(int* arr, int n, int* warpTmp) {
+    constexpr int QT_THREADS = NT, QT_WARPS = NT / 32;
+    (void)QT_THREADS;
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
     const int seg = (((n + QT_WARPS - 1) / QT_WARPS) + 31) & ~31;
     const int b = min(wid * seg, n), e = min(b + seg, n);
@@ -116,7 +121,9 @@ __device__ __forceinline__ uint32_t path_code(int x, int y, float hX, int nIni, 
 }
 
 // stable LSD radix sort of (key,val) pairs by `bits` low bits of key; returns 0 if the result is in A, 1 if in B
+template <int NT>
 __device__ int block_radix_sort(uint32_t* kA, uint32_t* vA, uint32_t* kB, uint32_t* vB, int M, int bits, uint32_t* hist /*256*QT_WARPS*/, int* warpTmp) {
+    constexpr int QT_THREADS = NT, QT_WARPS = NT / 32;
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
     const int per = (((M + QT_WARPS - 1) / QT_WARPS) + 31) & ~31;
     const int wb = min(wid * per, M), we = min(wb + per, M);
@@ -138,7 +145,7 @@ __device__ int block_radix_sort(uint32_t* kA, uint32_t* vA, uint32_t* kB, uint32
             __syncwarp();
         }
         __syncthreads();
-        block_scan_excl((int*)hist, 256 * QT_WARPS, warpTmp);
+        block_scan_excl<NT>((int*)hist, 256 * QT_WARPS, warpTmp);
         for (int base = wb; base < we; base += 32) {
             const int i = base + lane;
             const bool valid = i < we;

@@ -14,9 +14,9 @@ struct QtSmem {
     int* misc;       // [0]=nToExpand [1]=minT [2]=ne counter
 };
 
-__host__ __device__ inline size_t qt_smem_bytes(int cap) {
+__host__ __device__ inline size_t qt_smem_bytes(int cap, int nthreads) {
     // lo,hi x2 (16B/node) + dep x2 (2B) + b1..b3 (12B) + sA..sC (12B) + skey (8B) = 50B/node
-    return (size_t)cap * 52 + 256 * QT_WARPS * 4 + QT_WARPS * 4 + 64;
+    return (size_t)cap * 52 + 256 * (nthreads / 32) * 4 + (nthreads / 32) * 4 + 64;
 }
 
 // children of node (lo,hi,dep): boundaries by digit; returns number of non-empty children, ne = those with >1 key
@@ -45,7 +45,9 @@ __device__ __forceinline__ void emit_children(uint32_t* nlo, uint32_t* nhi, uint
         }
 }
 
-__global__ void __launch_bounds__(QT_THREADS) quadtree_kernel(QtArgs a) {
+template <int NT>
+__global__ void __launch_bounds__(NT) quadtree_kernel(QtArgs a) {
+    constexpr int QT_THREADS = NT, QT_WARPS = NT / 32;
     extern __shared__ __align__(16) uint8_t qsm[];
     const int tid = threadIdx.x;
     const int l = blockIdx.y, frame = blockIdx.x;        // level-major launch order: the long level-0 blocks start first
@@ -135,7 +137,7 @@ __global__ void __launch_bounds__(QT_THREADS) quadtree_kernel(QtArgs a) {
     // 2. sort by code
     int iniBits = 0;
     while ((1 << iniBits) < nIni) iniBits++;
-    const int which = block_radix_sort(kA, vA, kB, vB, M, 2 * depth + iniBits, s.hist, s.warpTmp);
+    const int which = block_radix_sort<NT>(kA, vA, kB, vB, M, 2 * depth + iniBits, s.hist, s.warpTmp);
     const uint32_t* keys = which ? kB : kA;
     const uint32_t* vals = which ? vB : vA;
     // distinct pixels must have distinct codes (depth was sized for it on the host)
@@ -184,8 +186,8 @@ __global__ void __launch_bounds__(QT_THREADS) quadtree_kernel(QtArgs a) {
             }
             if (neLocal) atomicAdd(&s.misc[0], neLocal);
             __syncthreads();
-            const int totalPushed = block_scan_excl(s.sA, n, s.warpTmp);
-            const int totalNoMore = block_scan_excl(s.sB, n, s.warpTmp);
+            const int totalPushed = block_scan_excl<NT>(s.sA, n, s.warpTmp);
+            const int totalNoMore = block_scan_excl<NT>(s.sB, n, s.warpTmp);
             if (totalPushed + totalNoMore > cap) { if (tid == 0) atomicExch(a.err, 103); break; }
             for (int i = tid; i < n; i += QT_THREADS) {
                 const uint32_t lo = clo[i], hi = chi[i];
@@ -242,7 +244,7 @@ __global__ void __launch_bounds__(QT_THREADS) quadtree_kernel(QtArgs a) {
             for (int i = tid; i < n; i += QT_THREADS) s.sC[i] = 1;     // keep flags over the old list
             __syncthreads();
             // inclusive running size after each split; first t reaching N ends the walk (:867-868)
-            block_scan_excl(s.sB, ne, s.warpTmp);
+            block_scan_excl<NT>(s.sB, ne, s.warpTmp);
             for (int t = tid; t < ne; t += QT_THREADS) {
                 const int incl = s.sB[t] + (s.sA[t] - 1);
                 if (n + incl >= N) atomicMin(&s.misc[1], t);
@@ -253,12 +255,12 @@ __global__ void __launch_bounds__(QT_THREADS) quadtree_kernel(QtArgs a) {
             int newSize = n;
             if (nProc > 0) newSize = n + s.sB[tStop] + (s.sA[tStop] - 1);
             __syncthreads();
-            const int pushedAll = block_scan_excl(s.sA, ne, s.warpTmp);
+            const int pushedAll = block_scan_excl<NT>(s.sA, ne, s.warpTmp);
             int totalPushed = 0;
             if (nProc > 0) totalPushed = (nProc == ne) ? pushedAll : s.sA[nProc];
             for (int t = tid; t < nProc; t += QT_THREADS) s.sC[fresh - 1 - (int)(s.skey[t] & 0xffffffffu)] = 0;
             __syncthreads();
-            const int kept = block_scan_excl(s.sC, n, s.warpTmp);
+            const int kept = block_scan_excl<NT>(s.sC, n, s.warpTmp);
             if (totalPushed + kept > cap) { if (tid == 0) atomicExch(a.err, 103); break; }
             for (int t = tid; t < nProc; t += QT_THREADS) {
                 const int i = fresh - 1 - (int)(s.skey[t] & 0xffffffffu);

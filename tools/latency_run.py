@@ -1,0 +1,39 @@
+"""Single-frame latency of orbx_extract (pageable and pinned image), with the ORBX_TRACE device timeline."""
+import ctypes as C, os, sys, time
+import numpy as np, torch
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from orb_slam_b200 import ORBextractor
+from orb_slam_b200._lib import check
+from orb_slam_b200.synth import synth_frame
+W, H = 1241, 376
+ex = ORBextractor(2000, 1.2, 8, 20, 7); L = ex._L; h = ex.handle; cap = ex.max_keypoints(W, H)
+img = synth_frame(W, H, 3)
+pin = torch.empty((H, W), dtype=torch.uint8, pin_memory=True); pin.numpy()[:] = img
+k = np.empty((cap, 28), np.uint8); d = np.empty((cap, 32), np.uint8); n = C.c_int()
+kp = torch.empty((cap, 28), dtype=torch.uint8, pin_memory=True); dp = torch.empty((cap, 32), dtype=torch.uint8, pin_memory=True)
+for name, ptr, ko, do in (("pageable", img.ctypes.data, k.ctypes.data, d.ctypes.data), ("pinned", pin.data_ptr(), kp.data_ptr(), dp.data_ptr())):
+    lat = []
+    for i in range(200):
+        t0 = time.perf_counter()
+        check(L.orbx_extract(h, ptr, W, H, W, ko, do, cap, C.byref(n)), "orbx_extract")
+        lat.append(time.perf_counter() - t0)
+    lat = np.array(lat[20:]) * 1e3
+    print(f"{name}: median {np.median(lat):.3f} ms  p10 {np.percentile(lat, 10):.3f}  p90 {np.percentile(lat, 90):.3f}  n={n.value}")
+# per-stage device time of a single frame (profiling mode: stages run back to back with events in between)
+L.orbx_set_profiling.argtypes = [C.c_void_p, C.c_int]; L.orbx_stage_times.argtypes = [C.c_void_p, C.c_void_p, C.c_int]
+L.orbx_extract_batch_device.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_size_t, C.c_size_t, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
+L.orbx_synchronize.argtypes = [C.c_void_p]
+dimg = torch.zeros((H, 1280), dtype=torch.uint8, device="cuda"); dimg[:, :W] = torch.from_numpy(img).cuda()
+dk = torch.empty((cap, 28), dtype=torch.uint8, device="cuda"); dd = torch.empty((cap, 32), dtype=torch.uint8, device="cuda")
+dn = torch.zeros(4, dtype=torch.int32, device="cuda")
+torch.cuda.synchronize()
+check(L.orbx_set_profiling(h, 1), "prof")
+acc = np.zeros(5)
+t = np.zeros(5, np.float32)
+for i in range(50):
+    check(L.orbx_extract_batch_device(h, dimg.data_ptr(), 1, W, H, 1280, 1280 * H, dk.data_ptr(), dd.data_ptr(), cap, dn.data_ptr()), "dev")
+    check(L.orbx_synchronize(h), "sync")
+    check(L.orbx_stage_times(h, t.ctypes.data, 5), "st")
+    if i >= 10:
+        acc += t
+print("single-frame stage ms:", dict(zip(["pyramid_blur_fast", "border", "cell_nms", "quadtree", "describe"], (acc / 40).round(4).tolist())))
