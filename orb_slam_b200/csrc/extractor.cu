@@ -216,7 +216,7 @@ static int build_geometry(orbx_extractor* e, int width, int height, FrameGeom& g
     g.candTotal = (candOff + 63) & ~63ULL;
     g.slotTotal = (slotOff + 63) & ~63ULL;
     g.nodeCap = 1 << ceil_log2(nodeNeed);
-    if (qt_smem_bytes(g.nodeCap, QT_THREADS_LATENCY) > 200 * 1024) return ORBX_E_UNSUPPORTED;
+    if (qt_smem_bytes(g.nodeCap, QT_THREADS_LATENCY) + (size_t)QT_KEYS_SMEM * 16 > 200 * 1024) return ORBX_E_UNSUPPORTED;
     return ORBX_OK;
 }
 
@@ -295,7 +295,7 @@ static int ensure_workspace(orbx_extractor* e, int width, int height, int frames
     e->haveGeom = true;
     // kernel attributes
     CK(cudaFuncSetAttribute(quadtree_kernel<QT_THREADS_BATCH>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)qt_smem_bytes(g.nodeCap, QT_THREADS_BATCH)));
-    CK(cudaFuncSetAttribute(quadtree_kernel<QT_THREADS_LATENCY>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)qt_smem_bytes(g.nodeCap, QT_THREADS_LATENCY)));
+    CK(cudaFuncSetAttribute(quadtree_kernel<QT_THREADS_LATENCY>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(qt_smem_bytes(g.nodeCap, QT_THREADS_LATENCY) + (size_t)QT_KEYS_SMEM * 16)));
     CK(cudaFuncSetAttribute(pyr_level_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
     CK(cudaFuncSetAttribute(pyr_level_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
     return ORBX_OK;
@@ -405,10 +405,14 @@ static int enqueue_pipeline(orbx_extractor* e, int wi, const uint8_t* src, size_
     }
     q.cellOff[g.nlevels] = g.totalCells;
     // many frames: small blocks (throughput); a handful of frames: the level-0 block is the critical path, give it more threads
-    if (frames * g.nlevels >= 2 * 148)
+    if (frames * g.nlevels >= 2 * 148) {
+        q.keyCap = 0;
         quadtree_kernel<QT_THREADS_BATCH><<<dim3(frames, g.nlevels), QT_THREADS_BATCH, qt_smem_bytes(g.nodeCap, QT_THREADS_BATCH), st>>>(q);
-    else
-        quadtree_kernel<QT_THREADS_LATENCY><<<dim3(frames, g.nlevels), QT_THREADS_LATENCY, qt_smem_bytes(g.nodeCap, QT_THREADS_LATENCY), st>>>(q);
+    } else {
+        q.keyCap = QT_KEYS_SMEM;                 // one block per SM at most: the sort arrays live in shared memory
+        quadtree_kernel<QT_THREADS_LATENCY><<<dim3(frames, g.nlevels), QT_THREADS_LATENCY,
+                                              qt_smem_bytes(g.nodeCap, QT_THREADS_LATENCY) + (size_t)QT_KEYS_SMEM * 16, st>>>(q);
+    }
     launches++;
     if (evs) CK(cudaEventRecord(evs[4], st));
     // 5. orientation, descriptors, output assembly

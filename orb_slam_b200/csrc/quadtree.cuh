@@ -25,6 +25,7 @@ namespace orbx {
 // when a call holds only a few frames and the level-0 block is the critical path
 constexpr int QT_THREADS_BATCH = 128;
 constexpr int QT_THREADS_LATENCY = 512;
+constexpr int QT_KEYS_SMEM = 4096;         // keys per sort array kept in shared memory by the latency variant (64 KB)
 
 struct QtArgs {
     uint32_t* cand;                  // packed x:12|y:12|score:8, [frames][candTotal]: vToDistributeKeys, built here
@@ -46,6 +47,7 @@ struct QtArgs {
     int* selCount;                   // [frames][nlevels]
     int* err;                        // device error flag
     int nlevels, selTotal, nodeCap;
+    int keyCap;                      // keys per sort array that fit in the dynamic shared memory behind the node arrays (0 = none)
     unsigned long long candOff[ORB_MAX_LEVELS];
     int N[ORB_MAX_LEVELS], nIni[ORB_MAX_LEVELS], qH[ORB_MAX_LEVELS], depth[ORB_MAX_LEVELS];
     int maxSel[ORB_MAX_LEVELS], selOff[ORB_MAX_LEVELS];

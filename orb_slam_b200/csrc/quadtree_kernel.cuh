@@ -127,6 +127,12 @@ __global__ void __launch_bounds__(NT) quadtree_kernel(QtArgs a) {
     }
     if (M <= 0) { if (tid == 0) *selCount = 0; return; }
 
+    // sort arrays in shared memory when this launch reserved room for them (generic pointers from here on): the binary
+    // searches of the passes below are chains of dependent loads, 10x shorter from shared memory than from L2
+    if (M <= a.keyCap) {
+        uint32_t* ks = (uint32_t*)(qsm + qt_smem_bytes(cap, NT));
+        kA = ks; kB = ks + a.keyCap; vA = ks + 2 * a.keyCap; vB = ks + 3 * a.keyCap;
+    }
     // 1. path codes
     for (int i = tid; i < M; i += QT_THREADS) {
         const uint32_t c = cand[i];
@@ -218,7 +224,10 @@ __global__ void __launch_bounds__(NT) quadtree_kernel(QtArgs a) {
             while (p2 < ne) p2 <<= 1;
             for (int i = ne + tid; i < p2; i += QT_THREADS) s.skey[i] = 0;
             __syncthreads();
-            for (int k = 2; k <= p2; k <<= 1)            // bitonic sort, descending
+            // bitonic sort, descending.  Element i belongs to thread i % NT, so a compare-exchange distance j < 32 stays
+            // inside one warp's 32-element blocks: those stages need only a warp barrier; a block barrier separates
+            // them from the stages that cross warps.
+            for (int k = 2; k <= p2; k <<= 1)
                 for (int j = k >> 1; j > 0; j >>= 1) {
                     for (int i = tid; i < p2; i += QT_THREADS) {
                         const int ixj = i ^ j;
@@ -228,7 +237,9 @@ __global__ void __launch_bounds__(NT) quadtree_kernel(QtArgs a) {
                             if (desc ? (x < y) : (x > y)) { s.skey[i] = y; s.skey[ixj] = x; }
                         }
                     }
-                    __syncthreads();
+                    const int jn = j > 1 ? (j >> 1) : k;             // distance of the next stage (k = first stage of the next round)
+                    if (j >= 32 || (jn >= 32 && 2 * k <= p2) || (j == 1 && k == p2)) __syncthreads();
+                    else __syncwarp();
                 }
             for (int t = tid; t < ne; t += QT_THREADS) {
                 const int i = fresh - 1 - (int)(s.skey[t] & 0xffffffffu);
