@@ -13,7 +13,7 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libfrontend_b200.so")
+LIB_PATH = os.environ.get("ORB_B200_LIB") or os.path.join(_HERE, "libfrontend_b200.so")     # (override: instrumented debug builds)
 
 KEYPOINT_DTYPE = np.dtype(
     [("x", "<f4"), ("y", "<f4"), ("size", "<f4"), ("angle", "<f4"), ("response", "<f4"),

@@ -816,6 +816,12 @@ int orbx_get_level(orbx_t* e, int frame, int level, int border, int blurred, uin
     return ORBX_OK;
 }
 
+#ifdef QT_PROFILE
+extern "C" int orbx_debug_qt_clock(long long* out64) {      // debug build only (-DQT_PROFILE): phase clocks of block (0, 0)
+    return (int)cudaMemcpyFromSymbol(out64, g_qt_clock, sizeof(long long) * 64);
+}
+#endif
+
 int orbx_get_candidates(orbx_t* e, int frame, int level, int32_t* xyr, int capacity, int* n_out) {
     if (!e || !e->haveGeom || level < 0 || level >= e->nlevels || frame < 0 || frame >= e->ws[e->lastWs].lastFrames || !n_out)
         return ORBX_E_INVALID;

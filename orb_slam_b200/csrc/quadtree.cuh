@@ -135,33 +135,50 @@ __device__ int block_radix_sort(uint32_t* kA, uint32_t* vA, uint32_t* kB, uint32
         uint32_t* ko = which ? kA : kB; uint32_t* vo = which ? vA : vB;
         for (int i = tid; i < 256 * QT_WARPS; i += QT_THREADS) hist[i] = 0;
         __syncthreads();
-        for (int base = wb; base < we; base += 32) {
-            const int i = base + lane;
-            const bool valid = i < we;
-            const unsigned act = __ballot_sync(0xffffffffu, valid);
-            if (valid) {
-                const uint32_t d = (ki[i] >> shift) & 255u;
-                const unsigned peers = __match_any_sync(act, d);
-                if (lane == __ffs(peers) - 1) hist[d * QT_WARPS + wid] += __popc(peers);
+        // both loops fetch RU 32-key chunks ahead of processing them: the fetches are independent, the histogram
+        // updates are not
+        constexpr int RU = 4;
+        for (int base = wb; base < we; base += 32 * RU) {
+            uint32_t kk[RU];
+#pragma unroll
+            for (int u = 0; u < RU; u++) { const int i = base + 32 * u + lane; kk[u] = i < we ? ki[i] : 0u; }
+#pragma unroll
+            for (int u = 0; u < RU; u++) {
+                const int i = base + 32 * u + lane;
+                if (base + 32 * u >= we) break;                     // warp-uniform
+                const bool valid = i < we;
+                const unsigned act = __ballot_sync(0xffffffffu, valid);
+                if (valid) {
+                    const uint32_t d = (kk[u] >> shift) & 255u;
+                    const unsigned peers = __match_any_sync(act, d);
+                    if (lane == __ffs(peers) - 1) hist[d * QT_WARPS + wid] += __popc(peers);
+                }
+                __syncwarp();
             }
-            __syncwarp();
         }
         __syncthreads();
         block_scan_excl<NT>((int*)hist, 256 * QT_WARPS, warpTmp);
-        for (int base = wb; base < we; base += 32) {
-            const int i = base + lane;
-            const bool valid = i < we;
-            const unsigned act = __ballot_sync(0xffffffffu, valid);
-            if (valid) {
-                const uint32_t k = ki[i], v = vi[i];
-                const uint32_t d = (k >> shift) & 255u;
-                const unsigned peers = __match_any_sync(act, d);
-                const uint32_t pos = hist[d * QT_WARPS + wid] + __popc(peers & ((1u << lane) - 1));
-                ko[pos] = k; vo[pos] = v;
-                __syncwarp(act);
-                if (lane == __ffs(peers) - 1) hist[d * QT_WARPS + wid] += __popc(peers);
+        for (int base = wb; base < we; base += 32 * RU) {
+            uint32_t kk[RU], vv[RU];
+#pragma unroll
+            for (int u = 0; u < RU; u++) { const int i = base + 32 * u + lane; const bool in = i < we; kk[u] = in ? ki[i] : 0u; vv[u] = in ? vi[i] : 0u; }
+#pragma unroll
+            for (int u = 0; u < RU; u++) {
+                const int i = base + 32 * u + lane;
+                if (base + 32 * u >= we) break;                     // warp-uniform
+                const bool valid = i < we;
+                const unsigned act = __ballot_sync(0xffffffffu, valid);
+                if (valid) {
+                    const uint32_t k = kk[u], v = vv[u];
+                    const uint32_t d = (k >> shift) & 255u;
+                    const unsigned peers = __match_any_sync(act, d);
+                    const uint32_t pos = hist[d * QT_WARPS + wid] + __popc(peers & ((1u << lane) - 1));
+                    ko[pos] = k; vo[pos] = v;
+                    __syncwarp(act);
+                    if (lane == __ffs(peers) - 1) hist[d * QT_WARPS + wid] += __popc(peers);
+                }
+                __syncwarp();
             }
-            __syncwarp();
         }
         __syncthreads();
         which ^= 1;

@@ -45,9 +45,17 @@ __device__ __forceinline__ void emit_children(uint32_t* nlo, uint32_t* nhi, uint
         }
 }
 
+#ifdef QT_PROFILE
+__device__ long long g_qt_clock[64];
+#define QT_MARK(k) do { if (threadIdx.x == 0 && blockIdx.x == 0 && blockIdx.y == 0) g_qt_clock[k] = clock64(); } while (0)
+#else
+#define QT_MARK(k) do { } while (0)
+#endif
+
 template <int NT>
 __global__ void __launch_bounds__(NT) quadtree_kernel(QtArgs a) {
     constexpr int QT_THREADS = NT, QT_WARPS = NT / 32;
+    QT_MARK(0);
     extern __shared__ __align__(16) uint8_t qsm[];
     const int tid = threadIdx.x;
     const int l = blockIdx.y, frame = blockIdx.x;        // level-major launch order: the long level-0 blocks start first
@@ -125,6 +133,7 @@ __global__ void __launch_bounds__(NT) quadtree_kernel(QtArgs a) {
         if (tid == 0) a.candCount[frame * a.nlevels + l] = M;
         __syncthreads();
     }
+    QT_MARK(1);
     if (M <= 0) { if (tid == 0) *selCount = 0; return; }
 
     // sort arrays in shared memory when this launch reserved room for them (generic pointers from here on): the binary
@@ -140,10 +149,12 @@ __global__ void __launch_bounds__(NT) quadtree_kernel(QtArgs a) {
         vA[i] = (c & 0xff000000u) | (uint32_t)i;
     }
     __syncthreads();
+    QT_MARK(2);
     // 2. sort by code
     int iniBits = 0;
     while ((1 << iniBits) < nIni) iniBits++;
     const int which = block_radix_sort<NT>(kA, vA, kB, vB, M, 2 * depth + iniBits, s.hist, s.warpTmp);
+    QT_MARK(3);
     const uint32_t* keys = which ? kB : kA;
     const uint32_t* vals = which ? vB : vA;
     // distinct pixels must have distinct codes (depth was sized for it on the host)
@@ -151,11 +162,13 @@ __global__ void __launch_bounds__(NT) quadtree_kernel(QtArgs a) {
         if (keys[i] == keys[i - 1]) atomicExch(a.err, 101);
 
     // 3. initial nodes in push_back order, empty ones erased (:663-699)
+    // (boundaries of the nIni ranges by nIni + 1 threads, then thread 0 compacts the non-empty ones in order)
+    if (tid <= nIni && tid < cap) s.b1[tid] = (tid == nIni) ? (uint32_t)M : key_lower_bound(keys, M, (uint32_t)tid << (2 * depth));
+    __syncthreads();
     if (tid == 0) {
         int n = 0;
         for (int i = 0; i < nIni; i++) {
-            const uint32_t lo = key_lower_bound(keys, M, (uint32_t)i << (2 * depth));
-            const uint32_t hi = (i + 1 == nIni) ? (uint32_t)M : key_lower_bound(keys, M, (uint32_t)(i + 1) << (2 * depth));
+            const uint32_t lo = s.b1[i], hi = s.b1[i + 1];
             if (hi > lo) { s.lo[0][n] = lo; s.hi[0][n] = hi; s.dep[0][n] = 0; n++; }
         }
         s.misc[3] = n;
@@ -166,8 +179,17 @@ __global__ void __launch_bounds__(NT) quadtree_kernel(QtArgs a) {
     bool finish = false;
     int fresh = 0;            // number of nodes created by the last pass (front of the list)
     bool priority = false;
+    QT_MARK(4);
+#ifdef QT_PROFILE
+    int qtIter = 0;
+#endif
 
     while (!finish) {
+#ifdef QT_PROFILE
+        if (qtIter < 20) QT_MARK(8 + qtIter);
+        if (tid == 0 && blockIdx.x == 0 && blockIdx.y == 0) g_qt_clock[40 + min(qtIter, 19)] = priority ? -n : n;
+        qtIter++;
+#endif
         uint32_t* clo = s.lo[cur]; uint32_t* chi = s.hi[cur]; uint8_t* cdep = s.dep[cur];
         uint32_t* nlo = s.lo[cur ^ 1]; uint32_t* nhi = s.hi[cur ^ 1]; uint8_t* ndep = s.dep[cur ^ 1];
         const int prevSize = n;
@@ -289,6 +311,10 @@ __global__ void __launch_bounds__(NT) quadtree_kernel(QtArgs a) {
         }
     }
 
+    QT_MARK(5);
+#ifdef QT_PROFILE
+    if (tid == 0 && blockIdx.x == 0 && blockIdx.y == 0) { g_qt_clock[7] = qtIter; g_qt_clock[39] = M; }
+#endif
     // 4. retain the best key of every node, list order (:885-904): highest response, earliest candidate on ties
     if (n > a.maxSel[l]) { if (tid == 0) atomicExch(a.err, 104); n = a.maxSel[l]; }
     uint32_t* sel = a.sel + (size_t)frame * a.selTotal + a.selOff[l];
@@ -302,6 +328,7 @@ __global__ void __launch_bounds__(NT) quadtree_kernel(QtArgs a) {
         sel[i] = cand[(best ^ 0x00ffffffu) & 0x00ffffffu];
     }
     if (tid == 0) *selCount = n;
+    QT_MARK(6);
 }
 
 }  // namespace orbx
