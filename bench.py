@@ -63,6 +63,17 @@ def make_frames(n_distinct, start):
     return np.stack(frames)
 
 
+def ncu_pipe_utilisation():
+    """ALU-pipe and issue-slot utilisation of the dominant kernel from the committed ncu capture (profiles/traffic.json): the
+    figures that say how close the ALU-bound K1 is to its real bound."""
+    try:
+        t = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
+        k = t["kernels"]["pyr_level_kernel"]
+        return {"alu_pipe_pct": round(k["alu_pipe_pct"], 1), "issue_active_pct": round(k["issue_active_pct"], 1), "source": "profiles/" + t["source"].replace(".ncu-rep", "") + " (ncu --set full)"}
+    except Exception:
+        return None
+
+
 def measured_traffic(batch):
     """dram__bytes_read.sum + dram__bytes_write.sum of the dominant kernel's launches (all 8 levels of pyr_level_kernel)
     from the committed `ncu --set full` capture, scaled from the capture's batch to this run's (profiles/*.json)."""
@@ -535,6 +546,9 @@ def run_ours(args, rank, world, local_rank):
             "e2e_pageable_frames_per_s": pageable_fps,
         }
         line["roofline"]["traffic"] = measured_traffic(B)
+        line["roofline"]["alu_bound_note"] = ("K1 is ALU-pipe bound, not HBM bound (about 120 integer instructions per pixel against 4 B "
+                                              "of traffic): see ncu_pipe for its pipe utilisation")
+        line["roofline"]["ncu_pipe"] = ncu_pipe_utilisation()
         if ham is not None:
             line["hamming_2nn"] = ham
         if world == 1 and not args.no_frontend:

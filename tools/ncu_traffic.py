@@ -28,10 +28,13 @@ def main(rep, frames, out_csv, out_json):
                     f"{r[ix['sm__inst_executed_pipe_alu.avg.pct_of_peak_sustained_active']]},"
                     f"{r[ix['smsp__issue_active.avg.pct_of_peak_sustained_active']]}\n")
             k = name.split("<")[0]
-            a = tot.setdefault(k, [0.0, 0.0, 0.0, 0])
+            a = tot.setdefault(k, [0.0, 0.0, 0.0, 0, 0.0, 0.0])
             a[0] += t; a[1] += rd; a[2] += wr; a[3] += 1
+            a[4] += t * float(r[ix['sm__inst_executed_pipe_alu.avg.pct_of_peak_sustained_active']])      # time-weighted
+            a[5] += t * float(r[ix['smsp__issue_active.avg.pct_of_peak_sustained_active']])
     total_t = sum(a[0] for a in tot.values())
-    summary = {k: {"launches": a[3], "time_us": a[0], "share": a[0] / total_t, "dram_read_bytes": a[1], "dram_write_bytes": a[2]}
+    summary = {k: {"launches": a[3], "time_us": a[0], "share": a[0] / total_t, "dram_read_bytes": a[1], "dram_write_bytes": a[2],
+                   "alu_pipe_pct": a[4] / a[0], "issue_active_pct": a[5] / a[0]}
                for k, a in tot.items()}
     p = tot["pyr_level_kernel"]
     json.dump({"source": rep.split("/")[-1], "frames_per_launch": frames, "kernels": summary,
