@@ -157,6 +157,48 @@ int orbm_fuse_select(orbm_t* m, const orbm_frame* kf, const float* camera_center
                      const float* max_distance, float log_scale_factor, orbm_predict_scale_fn predict, void* user, float th,
                      int32_t* best_idx);
 
+/* The two Sim3 matchers of loop closing.  The similarity is passed the way both functions decompose it themselves
+ * (src/ORBmatcher.cc:299-303, :1052-1056): Rcw (row-major 3x3, scale removed), tcw, Ow = -Rcw.t()*tcw, evaluated by
+ * the caller with its own matrix library.  kf, points, normals, distances and `predict` as in orbm_fuse_select;
+ * excluded[i] = pMP->isBad() || spAlreadyFound.count(pMP) (every points[i] must be valid: the reference dereferences them).
+ *
+ * ORBmatcher::SearchByProjection(pKF, Scw, vpPoints, vpMatched, th) (:290-403, LoopClosing::ComputeSim3):
+ * matched_in[idx] = vpMatched[idx] != NULL on entry; match out (kf->N entries): -2 untouched, else the index iMP of
+ * the point now stored in vpMatched[idx]. */
+int orbm_search_by_projection_sim3(orbm_t* m, const orbm_frame* kf, const float* Rcw, const float* tcw, const float* Ow,
+                                   const orbm_mappoint* points, int npoints, const uint8_t* excluded, const float* normals,
+                                   const float* min_distance_inv, const float* max_distance_inv, const float* max_distance,
+                                   float log_scale_factor, orbm_predict_scale_fn predict, void* user,
+                                   const uint8_t* matched_in, int th, int32_t* match, int* nmatches);
+/* ORBmatcher::Fuse(pKF, Scw, vpPoints, th, vpReplacePoint) (:1044-1168, LoopClosing::SearchAndFuse), selection part:
+ * best_idx[iMP] = key-frame keypoint with bestDist <= TH_LOW, else -1; the caller then fills vpReplacePoint /
+ * AddObservation / AddMapPoint in order iMP (GetMapPoint(bestIdx) is read at that time). */
+int orbm_fuse_select_sim3(orbm_t* m, const orbm_frame* kf, const float* Rcw, const float* tcw, const float* Ow,
+                          const orbm_mappoint* points, int npoints, const uint8_t* excluded, const float* normals,
+                          const float* min_distance_inv, const float* max_distance_inv, const float* max_distance,
+                          float log_scale_factor, orbm_predict_scale_fn predict, void* user, float th, int32_t* best_idx);
+
+/* ORBmatcher::SearchBySim3(pKF1, pKF2, vpMatches12, s12, R12, t12, th) (:1170-1394, LoopClosing::ComputeSim3).
+ * One orbm_sim3_side per key frame: its view (Tcw = GetRotation/GetTranslation, grid bounds, scale factors), the map
+ * points of GetMapPointMatches() by keypoint (valid = 0: NULL), skip[i] = vbAlreadyMatched[i] || pMP->isBad()
+ * (:1199-1210 evaluated by the caller: it needs MapPoint::GetIndexInKeyFrame), the distance invariance bounds and
+ * PredictScale INTO THE OTHER key frame (callback, or max_distance + that key frame's log scale factor).
+ * sR12 = s12*R12, sR21 = (1.0/s12)*R12.t(), t21 = -sR21*t12 (:1187-1189) come from the caller's matrix library.
+ * match12 out (side1->kf->N entries): index in key frame 2 whose map point is stored in vpMatches12[i1], else -1. */
+typedef struct orbm_sim3_side {
+    const orbm_frame* kf;
+    const orbm_mappoint* points;      /* kf->N */
+    const uint8_t* skip;              /* kf->N */
+    const float* min_distance_inv;    /* kf->N, GetMinDistanceInvariance() */
+    const float* max_distance_inv;    /* kf->N, GetMaxDistanceInvariance() */
+    const float* max_distance;        /* kf->N, mfMaxDistance; used when predict == NULL */
+    float log_scale_factor;           /* of the OTHER key frame; used when predict == NULL */
+    orbm_predict_scale_fn predict;    /* pMP->PredictScale(dist3D, other key frame) of point i, or NULL */
+    void* user;
+} orbm_sim3_side;
+int orbm_search_by_sim3(orbm_t* m, const orbm_sim3_side* side1, const orbm_sim3_side* side2, const float* sR12, const float* t12,
+                        const float* sR21, const float* t21, float th, int32_t* match12, int* nfound);
+
 /* ---- ORBmatcher::SearchByBoW.  A DBoW2::FeatureVector (std::map<NodeId,
  * std::vector<unsigned>>) flattened in map order: node ids ascending, start[k]..start[k+1] = the
  * node's feature indices in their vector order. */

@@ -397,6 +397,194 @@ int orbo_fuse_select(const orbm_frame* pKF, const float* cameraCenter, const flo
     return nFused;
 }
 
+// ORBmatcher::SearchByProjection(pKF, Scw, vpPoints, vpMatched, th), src/ORBmatcher.cc:290-403.  Scw arrives decomposed
+// (Rcw row-major 3x3 without the scale, tcw, Ow) exactly as :299-303 produce it; the matrix algebra of that decomposition
+// belongs to the caller's matrix library.
+int orbo_search_by_projection_sim3(const orbm_frame* pKF, const float* Rcw, const float* tcw, const float* Ow,
+                                   const orbm_mappoint* vpPoints, int n, const uint8_t* excluded, const float* normals,
+                                   const float* minMaxDistance, float mfLogScaleFactor, const uint8_t* matchedIn, int th, int32_t* match) {
+    Grid g; AssignFeaturesToGrid(*pKF, g);
+    const float fx = pKF->fx, fy = pKF->fy, cx = pKF->cx, cy = pKF->cy;
+    std::vector<uint8_t> vpMatched(matchedIn, matchedIn + pKF->N);
+    for (int i = 0; i < pKF->N; i++) match[i] = -2;
+    int nmatches = 0;
+    for (int iMP = 0; iMP < n; iMP++) {
+        if (excluded[iMP]) continue;                         // isBad() || spAlreadyFound.count(pMP)
+        const float* p3Dw = vpPoints[iMP].world;
+        float p3Dc[3];
+        for (int r = 0; r < 3; r++) {                        // Rcw*p3Dw+tcw (same evaluation as mul3, 3x3 stride)
+            float t = Rcw[3 * r] * p3Dw[0];
+            t = t + Rcw[3 * r + 1] * p3Dw[1];
+            t = t + Rcw[3 * r + 2] * p3Dw[2];
+            p3Dc[r] = (float)((double)t + (double)tcw[r]);
+        }
+        if (p3Dc[2] < 0.0) continue;
+        const float invz = 1 / p3Dc[2];
+        const float x = p3Dc[0] * invz;
+        const float y = p3Dc[1] * invz;
+        const float u = fx * x + cx;
+        const float v = fy * y + cy;
+        if (!(u >= pKF->mnMinX && u < pKF->mnMaxX && v >= pKF->mnMinY && v < pKF->mnMaxY)) continue;
+        const float maxDistance = 1.2f * minMaxDistance[2 * iMP + 1];
+        const float minDistance = 0.8f * minMaxDistance[2 * iMP];
+        float PO[3];
+        for (int k = 0; k < 3; k++) PO[k] = p3Dw[k] - Ow[k];
+        double nrm = 0, dot = 0;
+        for (int k = 0; k < 3; k++) nrm += (double)PO[k] * (double)PO[k];
+        const float dist = (float)std::sqrt(nrm);
+        if (dist < minDistance || dist > maxDistance) continue;
+        for (int k = 0; k < 3; k++) dot += (double)PO[k] * (double)normals[3 * iMP + k];
+        if (dot < 0.5 * dist) continue;
+        const float ratio = minMaxDistance[2 * iMP + 1] / dist;
+        int nPredictedLevel = (int)std::ceil(std::log(ratio) / mfLogScaleFactor);
+        if (nPredictedLevel < 0) nPredictedLevel = 0;
+        else if (nPredictedLevel >= pKF->nScaleLevels) nPredictedLevel = pKF->nScaleLevels - 1;
+        const float radius = th * pKF->scaleFactors[nPredictedLevel];
+        const std::vector<size_t> vIndices = GetFeaturesInArea(*pKF, g, u, v, radius);
+        if (vIndices.empty()) continue;
+        int bestDist = 256, bestIdx = -1;
+        for (size_t idx : vIndices) {
+            if (vpMatched[idx]) continue;
+            const int kpLevel = pKF->keysUn[idx].octave;
+            if (kpLevel < nPredictedLevel - 1 || kpLevel > nPredictedLevel) continue;
+            const int d = DescriptorDistance(vpPoints[iMP].descriptor, pKF->descriptors + 32 * idx);
+            if (d < bestDist) { bestDist = d; bestIdx = (int)idx; }
+        }
+        if (bestDist <= TH_LOW) { vpMatched[bestIdx] = 1; match[bestIdx] = iMP; nmatches++; }
+    }
+    return nmatches;
+}
+
+// ORBmatcher::Fuse(pKF, Scw, vpPoints, th, vpReplacePoint), src/ORBmatcher.cc:1044-1168, up to the choice of bestIdx
+int orbo_fuse_select_sim3(const orbm_frame* pKF, const float* Rcw, const float* tcw, const float* Ow, const orbm_mappoint* vpPoints,
+                          int nPoints, const uint8_t* excluded, const float* normals, const float* minMaxDistance,
+                          float mfLogScaleFactor, float th, int32_t* bestIdxOut) {
+    Grid g; AssignFeaturesToGrid(*pKF, g);
+    const float fx = pKF->fx, fy = pKF->fy, cx = pKF->cx, cy = pKF->cy;
+    int nFused = 0;
+    for (int iMP = 0; iMP < nPoints; iMP++) {
+        bestIdxOut[iMP] = -1;
+        if (excluded[iMP]) continue;
+        const float* p3Dw = vpPoints[iMP].world;
+        float p3Dc[3];
+        for (int r = 0; r < 3; r++) {
+            float t = Rcw[3 * r] * p3Dw[0];
+            t = t + Rcw[3 * r + 1] * p3Dw[1];
+            t = t + Rcw[3 * r + 2] * p3Dw[2];
+            p3Dc[r] = (float)((double)t + (double)tcw[r]);
+        }
+        if (p3Dc[2] < 0.0f) continue;
+        const float invz = 1.0 / p3Dc[2];
+        const float x = p3Dc[0] * invz;
+        const float y = p3Dc[1] * invz;
+        const float u = fx * x + cx;
+        const float v = fy * y + cy;
+        if (!(u >= pKF->mnMinX && u < pKF->mnMaxX && v >= pKF->mnMinY && v < pKF->mnMaxY)) continue;
+        const float maxDistance = 1.2f * minMaxDistance[2 * iMP + 1];
+        const float minDistance = 0.8f * minMaxDistance[2 * iMP];
+        float PO[3];
+        for (int k = 0; k < 3; k++) PO[k] = p3Dw[k] - Ow[k];
+        double nrm = 0, dot = 0;
+        for (int k = 0; k < 3; k++) nrm += (double)PO[k] * (double)PO[k];
+        const float dist3D = (float)std::sqrt(nrm);
+        if (dist3D < minDistance || dist3D > maxDistance) continue;
+        for (int k = 0; k < 3; k++) dot += (double)PO[k] * (double)normals[3 * iMP + k];
+        if (dot < 0.5 * dist3D) continue;
+        const float ratio = minMaxDistance[2 * iMP + 1] / dist3D;
+        int nPredictedLevel = (int)std::ceil(std::log(ratio) / mfLogScaleFactor);
+        if (nPredictedLevel < 0) nPredictedLevel = 0;
+        else if (nPredictedLevel >= pKF->nScaleLevels) nPredictedLevel = pKF->nScaleLevels - 1;
+        const float radius = th * pKF->scaleFactors[nPredictedLevel];
+        const std::vector<size_t> vIndices = GetFeaturesInArea(*pKF, g, u, v, radius);
+        if (vIndices.empty()) continue;
+        int bestDist = INT_MAX, bestIdx = -1;
+        for (size_t idx : vIndices) {
+            const int kpLevel = pKF->keysUn[idx].octave;
+            if (kpLevel < nPredictedLevel - 1 || kpLevel > nPredictedLevel) continue;
+            const int d = DescriptorDistance(vpPoints[iMP].descriptor, pKF->descriptors + 32 * idx);
+            if (d < bestDist) { bestDist = d; bestIdx = (int)idx; }
+        }
+        if (bestDist <= TH_LOW) { bestIdxOut[iMP] = bestIdx; nFused++; }
+    }
+    return nFused;
+}
+
+// ORBmatcher::SearchBySim3, src/ORBmatcher.cc:1170-1394.  vbAlreadyMatched1/2 (:1199-1210) and isBad() arrive merged in
+// skip1/skip2; sR12, t12, sR21, t21 (:1187-1189) arrive evaluated.
+static void Sim3Direction(const orbm_frame* pKFa, const orbm_frame* pKFb, const orbm_mappoint* vpMapPointsA, const uint8_t* skipA,
+                          const float* minMaxA, float logScaleFactorB, const float* sRba, const float* tba,
+                          float fx, float fy, float cx, float cy, float th, std::vector<int>& vnMatchA) {
+    Grid g; AssignFeaturesToGrid(*pKFb, g);
+    const int NA = pKFa->N;
+    vnMatchA.assign(NA, -1);
+    const float* T = pKFa->Tcw;
+    for (int i = 0; i < NA; i++) {
+        if (!vpMapPointsA[i].valid || skipA[i]) continue;
+        const float* p3Dw = vpMapPointsA[i].world;
+        float pa[3], pb[3];
+        for (int r = 0; r < 3; r++) {                      // Raw*p3Dw + taw
+            float t = T[4 * r] * p3Dw[0];
+            t = t + T[4 * r + 1] * p3Dw[1];
+            t = t + T[4 * r + 2] * p3Dw[2];
+            pa[r] = (float)((double)t + (double)T[4 * r + 3]);
+        }
+        for (int r = 0; r < 3; r++) {                      // sRba*p3Dca + tba
+            float t = sRba[3 * r] * pa[0];
+            t = t + sRba[3 * r + 1] * pa[1];
+            t = t + sRba[3 * r + 2] * pa[2];
+            pb[r] = (float)((double)t + (double)tba[r]);
+        }
+        if (pb[2] < 0.0) continue;
+        const float invz = 1.0 / pb[2];
+        const float x = pb[0] * invz;
+        const float y = pb[1] * invz;
+        const float u = fx * x + cx;
+        const float v = fy * y + cy;
+        if (!(u >= pKFb->mnMinX && u < pKFb->mnMaxX && v >= pKFb->mnMinY && v < pKFb->mnMaxY)) continue;
+        const float maxDistance = 1.2f * minMaxA[2 * i + 1];
+        const float minDistance = 0.8f * minMaxA[2 * i];
+        double nrm = 0;
+        for (int k = 0; k < 3; k++) nrm += (double)pb[k] * (double)pb[k];
+        const float dist3D = (float)std::sqrt(nrm);
+        if (dist3D < minDistance || dist3D > maxDistance) continue;
+        const float ratio = minMaxA[2 * i + 1] / dist3D;
+        int nPredictedLevel = (int)std::ceil(std::log(ratio) / logScaleFactorB);
+        if (nPredictedLevel < 0) nPredictedLevel = 0;
+        else if (nPredictedLevel >= pKFb->nScaleLevels) nPredictedLevel = pKFb->nScaleLevels - 1;
+        const float radius = th * pKFb->scaleFactors[nPredictedLevel];
+        const std::vector<size_t> vIndices = GetFeaturesInArea(*pKFb, g, u, v, radius);
+        if (vIndices.empty()) continue;
+        int bestDist = INT_MAX, bestIdx = -1;
+        for (size_t idx : vIndices) {
+            const int oct = pKFb->keysUn[idx].octave;
+            if (oct < nPredictedLevel - 1 || oct > nPredictedLevel) continue;
+            const int dist = DescriptorDistance(vpMapPointsA[i].descriptor, pKFb->descriptors + 32 * idx);
+            if (dist < bestDist) { bestDist = dist; bestIdx = (int)idx; }
+        }
+        if (bestDist <= TH_HIGH) vnMatchA[i] = bestIdx;
+    }
+}
+
+int orbo_search_by_sim3(const orbm_frame* pKF1, const orbm_frame* pKF2, const orbm_mappoint* vpMapPoints1, const orbm_mappoint* vpMapPoints2,
+                        const uint8_t* skip1, const uint8_t* skip2, const float* minMax1, const float* minMax2, float logScaleFactor1,
+                        float logScaleFactor2, const float* sR12, const float* t12, const float* sR21, const float* t21, float th,
+                        int32_t* match12) {
+    const float fx = pKF1->fx, fy = pKF1->fy, cx = pKF1->cx, cy = pKF1->cy;
+    std::vector<int> vnMatch1, vnMatch2;
+    Sim3Direction(pKF1, pKF2, vpMapPoints1, skip1, minMax1, logScaleFactor2, sR21, t21, fx, fy, cx, cy, th, vnMatch1);
+    Sim3Direction(pKF2, pKF1, vpMapPoints2, skip2, minMax2, logScaleFactor1, sR12, t12, fx, fy, cx, cy, th, vnMatch2);
+    int nFound = 0;
+    for (int i1 = 0; i1 < pKF1->N; i1++) {
+        match12[i1] = -1;
+        const int idx2 = vnMatch1[i1];
+        if (idx2 >= 0) {
+            const int idx1 = vnMatch2[idx2];
+            if (idx1 == i1) { match12[i1] = idx2; nFound++; }
+        }
+    }
+    return nFound;
+}
+
 int orbo_search_by_projection_points(const orbm_frame* F, const orbm_mappoint* pts, int npts, const int32_t* frameObs,
                                      float th, float mfNNratio, int32_t* frameAssign) {
     Grid g; AssignFeaturesToGrid(*F, g);

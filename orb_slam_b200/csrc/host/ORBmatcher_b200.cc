@@ -323,6 +323,193 @@ int ORBmatcher::Fuse(KeyFrame* pKF, const std::vector<MapPoint*>& vpMapPoints, c
     return nFused;
 }
 
+// ---- the two Sim3 matchers of loop closing ----
+namespace b200 {
+// Scw -> Rcw (scale removed), tcw, Ow: the decomposition both functions open with (:299-303, :1052-1056)
+static void DecomposeSim3(const cv::Mat& Scw, float R[9], float t[3], float O[3]) {
+#ifndef ORB_B200_STANDALONE
+    // inside ORB-SLAM2: OpenCV itself evaluates the reference's expressions
+    const cv::Mat sR = Scw.rowRange(0, 3).colRange(0, 3);
+    const float scw = sqrt(sR.row(0).dot(sR.row(0)));
+    const cv::Mat Rm = sR / scw, tm = Scw.rowRange(0, 3).col(3) / scw;
+    const cv::Mat Om = -Rm.t() * tm;
+    for (int r = 0; r < 3; r++) {
+        for (int c = 0; c < 3; c++) R[3 * r + c] = Rm.at<float>(r, c);
+        t[r] = tm.at<float>(r); O[r] = Om.at<float>(r);
+    }
+#else
+    // include/minicv has no matrix algebra; the same values with OpenCV's arithmetic spelled out: Mat::dot sums in double,
+    // Mat / s scales by float(1. / s), the GEMM behind -A.t() * b sums double products and rounds once
+    double n2 = 0;
+    for (int c = 0; c < 3; c++) n2 += (double)Scw.at<float>(0, c) * (double)Scw.at<float>(0, c);
+    const float scw = (float)std::sqrt(n2);
+    const float inv = (float)(1. / (double)scw);
+    for (int r = 0; r < 3; r++) {
+        for (int c = 0; c < 3; c++) R[3 * r + c] = Scw.at<float>(r, c) * inv;
+        t[r] = Scw.at<float>(r, 3) * inv;
+    }
+    for (int r = 0; r < 3; r++) {
+        double a = 0;
+        for (int k = 0; k < 3; k++) a += (double)R[3 * k + r] * (double)t[k];
+        O[r] = (float)(-a);
+    }
+#endif
+}
+// per-point inputs shared by the two functions
+struct Sim3Points {
+    std::vector<orbm_mappoint> pts;
+    std::vector<float> minInv, maxInv, normals;
+    std::vector<uint8_t> excluded;
+    Sim3Points(const std::vector<MapPoint*>& vpPoints, const std::set<MapPoint*>& spAlreadyFound)
+        : pts(vpPoints.size()), minInv(vpPoints.size()), maxInv(vpPoints.size()), normals(3 * vpPoints.size()), excluded(vpPoints.size()) {
+        for (size_t i = 0; i < vpPoints.size(); i++) {
+            MapPoint* pMP = vpPoints[i];
+            FillPoint(pts[i], pMP);                                           // a NULL entry is rejected by the library (the reference dereferences it)
+            if (!pMP) continue;
+            excluded[i] = pMP->isBad() || spAlreadyFound.count(pMP);          // :315-316, :1073-1074
+            minInv[i] = pMP->GetMinDistanceInvariance(); maxInv[i] = pMP->GetMaxDistanceInvariance();
+            const cv::Mat Pn = pMP->GetNormal();
+            for (int k = 0; k < 3; k++) normals[3 * i + k] = Pn.at<float>(k);
+        }
+    }
+};
+}  // namespace b200
+
+// src/ORBmatcher.cc:290-403 (LoopClosing::ComputeSim3)
+int ORBmatcher::SearchByProjection(KeyFrame* pKF, cv::Mat Scw, const std::vector<MapPoint*>& vpPoints, std::vector<MapPoint*>& vpMatched, int th) {
+    float R[9], t[3], O[3];
+    b200::DecomposeSim3(Scw, R, t, O);
+    std::set<MapPoint*> spAlreadyFound(vpMatched.begin(), vpMatched.end());
+    spAlreadyFound.erase(static_cast<MapPoint*>(NULL));
+    orbm_frame kf;
+    b200::FillKeyFrame(kf, pKF);
+    b200::Sim3Points in(vpPoints, spAlreadyFound);
+    std::vector<uint8_t> matchedIn(std::max(pKF->N, 1));
+    for (int i = 0; i < pKF->N; i++) matchedIn[i] = vpMatched[i] != NULL;
+    std::vector<int32_t> match(std::max(pKF->N, 1), -2);
+    b200::PredictKFCtx pc = {&vpPoints, pKF};
+    int nmatches = 0;
+    b200::Check(orbm_search_by_projection_sim3(b200::MatcherContext(), &kf, R, t, O, in.pts.data(), (int)vpPoints.size(), in.excluded.data(),
+                                               in.normals.data(), in.minInv.data(), in.maxInv.data(), NULL, 0.f, b200::PredictKFThunk, &pc,
+                                               matchedIn.data(), th, match.data(), &nmatches),
+                "orbm_search_by_projection_sim3");
+    for (int i = 0; i < pKF->N; i++)
+        if (match[i] >= 0) vpMatched[i] = vpPoints[match[i]];                  // :395-399
+    return nmatches;
+}
+
+// src/ORBmatcher.cc:1044-1168 (LoopClosing::SearchAndFuse)
+int ORBmatcher::Fuse(KeyFrame* pKF, cv::Mat Scw, const std::vector<MapPoint*>& vpPoints, float th, std::vector<MapPoint*>& vpReplacePoint) {
+    float R[9], t[3], O[3];
+    b200::DecomposeSim3(Scw, R, t, O);
+    const std::set<MapPoint*> spAlreadyFound = pKF->GetMapPoints();
+    orbm_frame kf;
+    b200::FillKeyFrame(kf, pKF);
+    b200::Sim3Points in(vpPoints, spAlreadyFound);
+    const int nPoints = (int)vpPoints.size();
+    std::vector<int32_t> best(std::max(nPoints, 1), -1);
+    b200::PredictKFCtx pc = {&vpPoints, pKF};
+    b200::Check(orbm_fuse_select_sim3(b200::MatcherContext(), &kf, R, t, O, in.pts.data(), nPoints, in.excluded.data(), in.normals.data(),
+                                      in.minInv.data(), in.maxInv.data(), NULL, 0.f, b200::PredictKFThunk, &pc, th, best.data()),
+                "orbm_fuse_select_sim3");
+    // :1149-1163 in the reference's order: an AddMapPoint of an earlier point is what a later GetMapPoint(bestIdx) sees
+    int nFused = 0;
+    for (int iMP = 0; iMP < nPoints; iMP++) {
+        if (best[iMP] < 0) continue;
+        MapPoint* pMP = vpPoints[iMP];
+        MapPoint* pMPinKF = pKF->GetMapPoint(best[iMP]);
+        if (pMPinKF) {
+            if (!pMPinKF->isBad()) vpReplacePoint[iMP] = pMPinKF;
+        } else {
+            pMP->AddObservation(pKF, best[iMP]);
+            pKF->AddMapPoint(pMP, best[iMP]);
+        }
+        nFused++;
+    }
+    return nFused;
+}
+
+// src/ORBmatcher.cc:1170-1394 (LoopClosing::ComputeSim3)
+namespace b200 {
+// sR12, sR21, t21 of :1187-1189
+static void Sim3Terms(float s12, const cv::Mat& R12, const cv::Mat& t12, float sR12[9], float t12f[3], float sR21[9], float t21[3]) {
+#ifndef ORB_B200_STANDALONE
+    const cv::Mat A = s12 * R12, B = (1.0 / s12) * R12.t();
+    const cv::Mat c = -B * t12;
+    for (int r = 0; r < 3; r++) {
+        for (int k = 0; k < 3; k++) { sR12[3 * r + k] = A.at<float>(r, k); sR21[3 * r + k] = B.at<float>(r, k); }
+        t12f[r] = t12.at<float>(r); t21[r] = c.at<float>(r);
+    }
+#else
+    // OpenCV's arithmetic written out: alpha * Mat is a float product by float(alpha); the 3x3 * 3x1 product sums float
+    // products in float and applies the -1 of the unary minus in double
+    const float inv = (float)(1.0 / s12);
+    for (int r = 0; r < 3; r++) {
+        for (int k = 0; k < 3; k++) { sR12[3 * r + k] = R12.at<float>(r, k) * s12; sR21[3 * r + k] = R12.at<float>(k, r) * inv; }
+        t12f[r] = t12.at<float>(r);
+    }
+    for (int r = 0; r < 3; r++) {
+        float a = sR21[3 * r] * t12f[0];
+        a = a + sR21[3 * r + 1] * t12f[1];
+        a = a + sR21[3 * r + 2] * t12f[2];
+        t21[r] = (float)((double)a * -1.0);
+    }
+#endif
+}
+struct Sim3Side {
+    orbm_frame kf;
+    std::vector<orbm_mappoint> pts;
+    std::vector<float> minInv, maxInv;
+    std::vector<uint8_t> skip;
+    PredictKFCtx pc;
+    orbm_sim3_side side;
+    // pKF's points, PredictScale into pOther
+    Sim3Side(KeyFrame* pKF, KeyFrame* pOther, const std::vector<MapPoint*>& vp, const std::vector<bool>& vbAlreadyMatched)
+        : pts(vp.size()), minInv(vp.size()), maxInv(vp.size()), skip(vp.size()) {
+        FillKeyFrame(kf, pKF);
+        for (size_t i = 0; i < vp.size(); i++) {
+            MapPoint* pMP = vp[i];
+            FillPoint(pts[i], pMP);
+            if (!pMP) continue;
+            skip[i] = vbAlreadyMatched[i] || pMP->isBad();                    // :1220-1224
+            minInv[i] = pMP->GetMinDistanceInvariance(); maxInv[i] = pMP->GetMaxDistanceInvariance();
+        }
+        pc.pts = &vp; pc.pKF = pOther;
+        std::memset(&side, 0, sizeof(side));
+        side.kf = &kf; side.points = pts.data(); side.skip = skip.data();
+        side.min_distance_inv = minInv.data(); side.max_distance_inv = maxInv.data();
+        side.predict = PredictKFThunk; side.user = &pc;
+    }
+};
+}  // namespace b200
+
+int ORBmatcher::SearchBySim3(KeyFrame* pKF1, KeyFrame* pKF2, std::vector<MapPoint*>& vpMatches12, const float& s12, const cv::Mat& R12,
+                             const cv::Mat& t12, const float th) {
+    float sR12[9], t12f[3], sR21[9], t21[3];
+    b200::Sim3Terms(s12, R12, t12, sR12, t12f, sR21, t21);
+    const std::vector<MapPoint*> vpMapPoints1 = pKF1->GetMapPointMatches();
+    const int N1 = (int)vpMapPoints1.size();
+    const std::vector<MapPoint*> vpMapPoints2 = pKF2->GetMapPointMatches();
+    const int N2 = (int)vpMapPoints2.size();
+    std::vector<bool> vbAlreadyMatched1(N1, false), vbAlreadyMatched2(N2, false);
+    for (int i = 0; i < N1; i++) {                                            // :1199-1210
+        MapPoint* pMP = vpMatches12[i];
+        if (!pMP) continue;
+        vbAlreadyMatched1[i] = true;
+        const int idx2 = pMP->GetIndexInKeyFrame(pKF2);
+        if (idx2 >= 0 && idx2 < N2) vbAlreadyMatched2[idx2] = true;
+    }
+    b200::Sim3Side side1(pKF1, pKF2, vpMapPoints1, vbAlreadyMatched1), side2(pKF2, pKF1, vpMapPoints2, vbAlreadyMatched2);
+    assert(side1.kf.N == N1 && side2.kf.N == N2);
+    std::vector<int32_t> match12(std::max(N1, 1), -1);
+    int nFound = 0;
+    b200::Check(orbm_search_by_sim3(b200::MatcherContext(), &side1.side, &side2.side, sR12, t12f, sR21, t21, th, match12.data(), &nFound),
+                "orbm_search_by_sim3");
+    for (int i1 = 0; i1 < N1; i1++)
+        if (match12[i1] >= 0) vpMatches12[i1] = vpMapPoints2[match12[i1]];    // :1386
+    return nFound;
+}
+
 // src/ORBmatcher.cc:725-891 (LocalMapping::CreateNewMapPoints)
 int ORBmatcher::SearchForTriangulation(KeyFrame* pKF1, KeyFrame* pKF2, cv::Mat F12,
                                        std::vector<std::pair<size_t, size_t> >& vMatchedPairs, const bool bOnlyStereo) {

@@ -5,6 +5,7 @@
 #ifndef KEYFRAME_H
 #define KEYFRAME_H
 #include <cmath>
+#include <set>
 #include <vector>
 #include <opencv2/core/core.hpp>
 #include "Thirdparty/DBoW2/DBoW2/FeatureVector.h"
@@ -22,6 +23,12 @@ public:
     void EraseMapPointMatch(const size_t& idx) { mvpMapPoints[idx] = static_cast<MapPoint*>(NULL); }
     std::vector<MapPoint*> GetMapPointMatches() { return mvpMapPoints; }
     MapPoint* GetMapPoint(const size_t& idx) { return mvpMapPoints[idx]; }
+    std::set<MapPoint*> GetMapPoints() {                                   // src/KeyFrame.cc:235-248
+        std::set<MapPoint*> s;
+        for (size_t i = 0; i < mvpMapPoints.size(); i++)
+            if (mvpMapPoints[i] && !mvpMapPoints[i]->isBad()) s.insert(mvpMapPoints[i]);
+        return s;
+    }
     cv::Mat GetRotation() { return Rcw.clone(); }
     cv::Mat GetTranslation() { return tcw.clone(); }
     cv::Mat GetCameraCenter() { return Ow.clone(); }

@@ -27,6 +27,7 @@ public:
     int PredictScale(const float& currentDist, KeyFrame* pKF);            // src/MapPoint.cc:385-400 (defined in lite/KeyFrame.h)
     cv::Mat GetNormal() { return mNormalVector.clone(); }
     bool IsInKeyFrame(KeyFrame* pKF) { return mObservations.count(pKF) != 0; }
+    int GetIndexInKeyFrame(KeyFrame* pKF) { return mObservations.count(pKF) ? (int)mObservations[pKF] : -1; }   // src/MapPoint.cc:315-322
     // simplified stand-ins of src/MapPoint.cc:104-121 and :186-225 (single key frame bookkeeping; defined in lite/KeyFrame.h)
     void AddObservation(KeyFrame* pKF, size_t idx);
     void Replace(MapPoint* pMP);

@@ -501,3 +501,198 @@ int orbm_fuse_select(orbm_t* m, const orbm_frame* kf, const float* cameraCenter,
 }
 
 }  // extern "C"
+
+namespace {
+// Projection part shared by SearchByProjection(pKF, Scw, ...) (:318-359) and Fuse(pKF, Scw, ...) (:1072-1113): one window
+// query per point that survives the depth, image, distance-range and viewing-angle gates.  invzDouble: "1.0/z" (:1086)
+// instead of "1/z" (:327).
+int sim3_queries(const orbm_frame* kf, const float* Rcw, const float* tcw, const float* Ow, const orbm_mappoint* pts, int npts,
+                 const uint8_t* excluded, const float* normals, const float* minInv, const float* maxInv, const float* maxDistance,
+                 float logScaleFactor, orbm_predict_scale_fn predict, void* user, bool invzDouble, float th,
+                 std::vector<WQuery>& queries, std::vector<int>& meta) {
+    for (int i = 0; i < npts; i++) {
+        if (!pts[i].valid) return ORBX_E_INVALID;
+        if (excluded[i]) continue;
+        float p3Dc[3];
+        mat3_mul_add(Rcw, 3, pts[i].world, tcw, p3Dc);
+        if (p3Dc[2] < 0.0f) continue;
+        const float invz = invzDouble ? (float)(1.0 / p3Dc[2]) : 1 / p3Dc[2];
+        const float x = p3Dc[0] * invz, y = p3Dc[1] * invz;
+        const float u = kf->fx * x + kf->cx, v = kf->fy * y + kf->cy;
+        if (!(u >= kf->mnMinX && u < kf->mnMaxX && v >= kf->mnMinY && v < kf->mnMaxY)) continue;    // KeyFrame::IsInImage
+        double s2 = 0, dot = 0;
+        for (int k = 0; k < 3; k++) {
+            const float po = pts[i].world[k] - Ow[k];
+            s2 += (double)po * (double)po;
+            dot += (double)po * (double)normals[3 * i + k];
+        }
+        const float dist = (float)std::sqrt(s2);
+        if (dist < minInv[i] || dist > maxInv[i]) continue;
+        if (dot < 0.5 * dist) continue;
+        int nPredictedLevel;
+        if (predict) nPredictedLevel = predict(user, i, dist);
+        else {
+            const float ratio = maxDistance[i] / dist;
+            nPredictedLevel = (int)std::ceil(std::log(ratio) / logScaleFactor);
+            if (nPredictedLevel < 0) nPredictedLevel = 0;
+            else if (nPredictedLevel >= kf->nScaleLevels) nPredictedLevel = kf->nScaleLevels - 1;
+        }
+        if (nPredictedLevel < 0 || nPredictedLevel >= kf->nScaleLevels) return ORBX_E_INVALID;
+        WQuery q; std::memset(&q, 0, sizeof(q));
+        q.x = u; q.y = v; q.r = th * kf->scaleFactors[nPredictedLevel];
+        q.minLevel = nPredictedLevel - 1; q.maxLevel = nPredictedLevel;
+        set_desc(q, pts[i].descriptor);
+        queries.push_back(q); meta.push_back(i);
+    }
+    return 0;
+}
+}  // namespace
+
+extern "C" {
+
+int orbm_search_by_projection_sim3(orbm_t* m, const orbm_frame* kf, const float* Rcw, const float* tcw, const float* Ow,
+                                   const orbm_mappoint* pts, int npts, const uint8_t* excluded, const float* normals,
+                                   const float* minInv, const float* maxInv, const float* maxDistance, float logScaleFactor,
+                                   orbm_predict_scale_fn predict, void* user, const uint8_t* matchedIn, int th, int32_t* match,
+                                   int* nmatchesOut) {
+    if (!m || !kf || !Rcw || !tcw || !Ow || (!pts && npts) || npts < 0 || !match || !nmatchesOut || (kf->N > 0 && !matchedIn)) return ORBX_E_INVALID;
+    if (npts > 0 && (!excluded || !normals || !minInv || !maxInv || (!predict && !maxDistance))) return ORBX_E_INVALID;
+    if (kf->nScaleLevels <= 0) return ORBX_E_INVALID;
+    std::lock_guard<std::mutex> lk(m->mtx);
+    CKM(cudaSetDevice(m->device));
+    DeviceFrame d;
+    int rc = upload_frame(m, kf, d);
+    if (rc) return rc;
+    std::vector<WQuery> queries; std::vector<int> meta;
+    if ((rc = sim3_queries(kf, Rcw, tcw, Ow, pts, npts, excluded, normals, minInv, maxInv, maxDistance, logScaleFactor, predict, user,
+                           false, (float)th, queries, meta))) return rc;
+    std::vector<int32_t> offs; std::vector<int2> pairs;
+    if ((rc = run_queries(m, d, queries, offs, pairs))) return rc;
+    std::vector<uint8_t> matched(matchedIn, matchedIn + kf->N);
+    for (int i = 0; i < kf->N; i++) match[i] = -2;
+    int nmatches = 0;
+    for (size_t qi = 0; qi < queries.size(); qi++) {
+        int bestDist = 256, bestIdx = -1;
+        for (int k = offs[qi]; k < offs[qi + 1]; k++) {
+            const int idx = pairs[k].x;
+            if (matched[idx]) continue;                                        // :375-376
+            const int dist = pairs[k].y;
+            if (dist < bestDist) { bestDist = dist; bestIdx = idx; }
+        }
+        if (bestDist <= ORBM_TH_LOW) { match[bestIdx] = meta[qi]; matched[bestIdx] = 1; nmatches++; }
+    }
+    *nmatchesOut = nmatches;
+    return ORBX_OK;
+}
+
+int orbm_fuse_select_sim3(orbm_t* m, const orbm_frame* kf, const float* Rcw, const float* tcw, const float* Ow,
+                          const orbm_mappoint* pts, int npts, const uint8_t* excluded, const float* normals, const float* minInv,
+                          const float* maxInv, const float* maxDistance, float logScaleFactor, orbm_predict_scale_fn predict,
+                          void* user, float th, int32_t* bestIdxOut) {
+    if (!m || !kf || !Rcw || !tcw || !Ow || (!pts && npts) || npts < 0 || !bestIdxOut) return ORBX_E_INVALID;
+    if (npts > 0 && (!excluded || !normals || !minInv || !maxInv || (!predict && !maxDistance))) return ORBX_E_INVALID;
+    if (kf->nScaleLevels <= 0) return ORBX_E_INVALID;
+    std::lock_guard<std::mutex> lk(m->mtx);
+    CKM(cudaSetDevice(m->device));
+    DeviceFrame d;
+    int rc = upload_frame(m, kf, d);
+    if (rc) return rc;
+    for (int i = 0; i < npts; i++) bestIdxOut[i] = -1;
+    std::vector<WQuery> queries; std::vector<int> meta;
+    if ((rc = sim3_queries(kf, Rcw, tcw, Ow, pts, npts, excluded, normals, minInv, maxInv, maxDistance, logScaleFactor, predict, user,
+                           true, th, queries, meta))) return rc;
+    std::vector<int32_t> offs; std::vector<int2> pairs;
+    if ((rc = run_queries(m, d, queries, offs, pairs))) return rc;
+    for (size_t qi = 0; qi < queries.size(); qi++) {
+        int bestDist = 0x7fffffff, bestIdx = -1;                               // INT_MAX, :1126
+        for (int k = offs[qi]; k < offs[qi + 1]; k++)
+            if (pairs[k].y < bestDist) { bestDist = pairs[k].y; bestIdx = pairs[k].x; }
+        if (bestDist <= ORBM_TH_LOW) bestIdxOut[meta[qi]] = bestIdx;
+    }
+    return ORBX_OK;
+}
+
+}  // extern "C"
+
+namespace {
+// one direction of SearchBySim3 (:1215-1294 / :1296-1375): the points of `src` through its own pose and then `sR`,`t`
+// into `dst`; best[i] = keypoint of dst with bestDist <= TH_HIGH, else -1
+int sim3_direction(orbm_context* m, const orbm_sim3_side* src, const orbm_frame* dst, const float* sR, const float* t, float th,
+                   std::vector<int>& best) {
+    const orbm_frame* kf = src->kf;
+    best.assign(std::max(kf->N, 0), -1);
+    DeviceFrame d;
+    int rc = upload_frame(m, dst, d);
+    if (rc) return rc;
+    const float tw[3] = {kf->Tcw[3], kf->Tcw[7], kf->Tcw[11]};
+    std::vector<WQuery> queries; std::vector<int> meta;
+    for (int i = 0; i < kf->N; i++) {
+        if (!src->points[i].valid || src->skip[i]) continue;                     // !pMP || vbAlreadyMatched || isBad()
+        float pa[3], pb[3];
+        mat3_mul_add(kf->Tcw, 4, src->points[i].world, tw, pa);
+        mat3_mul_add(sR, 3, pa, t, pb);
+        if (pb[2] < 0.0f) continue;
+        const float invz = (float)(1.0 / pb[2]);
+        const float x = pb[0] * invz, y = pb[1] * invz;
+        const float u = kf->fx * x + kf->cx, v = kf->fy * y + kf->cy;            // pKF1's intrinsics in both directions (:1173-1176)
+        if (!(u >= dst->mnMinX && u < dst->mnMaxX && v >= dst->mnMinY && v < dst->mnMaxY)) continue;
+        double s2 = 0;
+        for (int k = 0; k < 3; k++) s2 += (double)pb[k] * (double)pb[k];
+        const float dist3D = (float)std::sqrt(s2);
+        if (dist3D < src->min_distance_inv[i] || dist3D > src->max_distance_inv[i]) continue;
+        int nPredictedLevel;
+        if (src->predict) nPredictedLevel = src->predict(src->user, i, dist3D);
+        else {
+            const float ratio = src->max_distance[i] / dist3D;
+            nPredictedLevel = (int)std::ceil(std::log(ratio) / src->log_scale_factor);
+            if (nPredictedLevel < 0) nPredictedLevel = 0;
+            else if (nPredictedLevel >= dst->nScaleLevels) nPredictedLevel = dst->nScaleLevels - 1;
+        }
+        if (nPredictedLevel < 0 || nPredictedLevel >= dst->nScaleLevels) return ORBX_E_INVALID;
+        WQuery q; std::memset(&q, 0, sizeof(q));
+        q.x = u; q.y = v; q.r = th * dst->scaleFactors[nPredictedLevel];
+        q.minLevel = nPredictedLevel - 1; q.maxLevel = nPredictedLevel;
+        set_desc(q, src->points[i].descriptor);
+        queries.push_back(q); meta.push_back(i);
+    }
+    std::vector<int32_t> offs; std::vector<int2> pairs;
+    if ((rc = run_queries(m, d, queries, offs, pairs))) return rc;
+    for (size_t qi = 0; qi < queries.size(); qi++) {
+        int bestDist = 0x7fffffff, bestIdx = -1;
+        for (int k = offs[qi]; k < offs[qi + 1]; k++)
+            if (pairs[k].y < bestDist) { bestDist = pairs[k].y; bestIdx = pairs[k].x; }
+        if (bestDist <= ORBM_TH_HIGH) best[meta[qi]] = bestIdx;
+    }
+    return 0;
+}
+}  // namespace
+
+extern "C" int orbm_search_by_sim3(orbm_t* m, const orbm_sim3_side* side1, const orbm_sim3_side* side2, const float* sR12, const float* t12,
+                                   const float* sR21, const float* t21, float th, int32_t* match12, int* nfound) {
+    if (!m || !side1 || !side2 || !side1->kf || !side2->kf || !sR12 || !t12 || !sR21 || !t21 || !match12 || !nfound) return ORBX_E_INVALID;
+    const orbm_sim3_side* sd[2] = {side1, side2};
+    for (int k = 0; k < 2; k++) {
+        const orbm_sim3_side* s = sd[k];
+        if (s->kf->N < 0 || s->kf->nScaleLevels <= 0) return ORBX_E_INVALID;
+        if (s->kf->N > 0 && (!s->points || !s->skip || !s->min_distance_inv || !s->max_distance_inv || (!s->predict && !s->max_distance)))
+            return ORBX_E_INVALID;
+    }
+    std::lock_guard<std::mutex> lk(m->mtx);
+    CKM(cudaSetDevice(m->device));
+    // the intrinsics of pKF1 project in both directions (:1173-1176): direction 2->1 reads them from side1's frame
+    orbm_frame k2as1 = *side2->kf;
+    k2as1.fx = side1->kf->fx; k2as1.fy = side1->kf->fy; k2as1.cx = side1->kf->cx; k2as1.cy = side1->kf->cy;
+    orbm_sim3_side s2 = *side2; s2.kf = &k2as1;
+    std::vector<int> vnMatch1, vnMatch2;
+    int rc;
+    if ((rc = sim3_direction(m, side1, side2->kf, sR21, t21, th, vnMatch1))) return rc;
+    if ((rc = sim3_direction(m, &s2, side1->kf, sR12, t12, th, vnMatch2))) return rc;
+    int n = 0;
+    for (int i1 = 0; i1 < side1->kf->N; i1++) {                                    // :1377-1391
+        const int idx2 = vnMatch1[i1];
+        match12[i1] = -1;
+        if (idx2 >= 0 && vnMatch2[idx2] == i1) { match12[i1] = idx2; n++; }
+    }
+    *nfound = n;
+    return ORBX_OK;
+}

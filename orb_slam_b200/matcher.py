@@ -95,6 +95,13 @@ class KeyFrameStruct(C.Structure):
                 ("has_point", C.c_void_p), ("featvec", C.c_void_p)]
 
 
+class Sim3SideStruct(C.Structure):
+    """orbm_sim3_side of include/orbm.h."""
+    _fields_ = [("kf", C.c_void_p), ("points", C.c_void_p), ("skip", C.c_void_p), ("min_distance_inv", C.c_void_p),
+                ("max_distance_inv", C.c_void_p), ("max_distance", C.c_void_p), ("log_scale_factor", C.c_float),
+                ("predict", C.c_void_p), ("user", C.c_void_p)]
+
+
 class KeyFrameView:
     """The members of ORB_SLAM2::KeyFrame that SearchForTriangulation reads."""
 
@@ -141,6 +148,12 @@ def _bind(L):
     L.orbm_search_by_projection_keyframe.restype = i
     L.orbm_fuse_select.argtypes = [vp, vp, vp, vp, vp, i, vp, vp, vp, vp, vp, f, vp, vp, f, vp]
     L.orbm_fuse_select.restype = i
+    L.orbm_search_by_projection_sim3.argtypes = [vp, vp, vp, vp, vp, vp, i, vp, vp, vp, vp, vp, f, vp, vp, vp, i, vp, C.POINTER(i)]
+    L.orbm_search_by_projection_sim3.restype = i
+    L.orbm_fuse_select_sim3.argtypes = [vp, vp, vp, vp, vp, vp, i, vp, vp, vp, vp, vp, f, vp, vp, f, vp]
+    L.orbm_fuse_select_sim3.restype = i
+    L.orbm_search_by_sim3.argtypes = [vp, vp, vp, vp, vp, vp, vp, f, vp, C.POINTER(i)]
+    L.orbm_search_by_sim3.restype = i
     L.orbm_search_for_triangulation.argtypes = [vp, vp, vp, vp, vp, vp, f, f, f, f, vp, vp, i, vp, i, i, vp, C.POINTER(i)]
     L.orbm_search_for_triangulation.restype = i
     L.orbm_search_by_bow.argtypes = [vp, i, vp, vp, vp, i, vp, vp, vp, vp, i, vp, f, i, vp, C.POINTER(i)]
@@ -292,6 +305,68 @@ class ORBmatcher:
                                     mn_inv.ctypes.data, mx_inv.ctypes.data, mx.ctypes.data, log_scale_factor, None, None, th,
                                     out.ctypes.data), "orbm_fuse_select")
         return out[: len(p)]
+
+    def _sim3_args(self, KF, Rcw, tcw, Ow, points, excluded, normals, min_max_distance, log_scale_factor):
+        f32 = lambda a: np.ascontiguousarray(a, np.float32)
+        p = np.ascontiguousarray(points, MAPPOINT_DTYPE)
+        mm = f32(min_max_distance).reshape(-1, 2)
+        keep = dict(R=f32(Rcw).ravel(), t=f32(tcw).ravel(), O=f32(Ow).ravel(), p=p, ex=np.ascontiguousarray(excluded, np.uint8),
+                    nr=f32(normals).reshape(-1, 3), mn=(np.float32(0.8) * mm[:, 0]).astype(np.float32),
+                    mx_inv=(np.float32(1.2) * mm[:, 1]).astype(np.float32), mx=np.ascontiguousarray(mm[:, 1]), sk=KF.struct())
+        if log_scale_factor is None:
+            log_scale_factor = float(np.log(np.float32(KF.mvScaleFactors[1])))
+        k = keep
+        args = [C.byref(k["sk"]), k["R"].ctypes.data, k["t"].ctypes.data, k["O"].ctypes.data, p.ctypes.data, len(p), k["ex"].ctypes.data,
+                k["nr"].ctypes.data, k["mn"].ctypes.data, k["mx_inv"].ctypes.data, k["mx"].ctypes.data, log_scale_factor, None, None]
+        return keep, args
+
+    def SearchByProjectionSim3(self, KF: Frame, Rcw, tcw, Ow, points, excluded, normals, min_max_distance, matched_in, th: int,
+                               log_scale_factor: float | None = None):
+        """SearchByProjection(pKF, Scw, vpPoints, vpMatched, th) (src/ORBmatcher.cc:290-403) with Scw decomposed by the caller.
+        Returns (nmatches, match) with match[idx] = iMP newly stored in vpMatched[idx], -2 untouched."""
+        c = self._c()
+        keep, args = self._sim3_args(KF, Rcw, tcw, Ow, points, excluded, normals, min_max_distance, log_scale_factor)
+        mi = np.ascontiguousarray(matched_in, np.uint8)
+        out = np.zeros(max(KF.N, 1), np.int32); n = C.c_int()
+        check(c._L.orbm_search_by_projection_sim3(c.h, *args, mi.ctypes.data, int(th), out.ctypes.data, C.byref(n)),
+              "orbm_search_by_projection_sim3")
+        return n.value, out[: KF.N]
+
+    def FuseSelectSim3(self, KF: Frame, Rcw, tcw, Ow, points, excluded, normals, min_max_distance, th: float,
+                       log_scale_factor: float | None = None):
+        """Selection part of Fuse(pKF, Scw, vpPoints, th, vpReplacePoint) (:1044-1168)."""
+        c = self._c()
+        keep, args = self._sim3_args(KF, Rcw, tcw, Ow, points, excluded, normals, min_max_distance, log_scale_factor)
+        out = np.zeros(max(len(keep["p"]), 1), np.int32)
+        check(c._L.orbm_fuse_select_sim3(c.h, *args, th, out.ctypes.data), "orbm_fuse_select_sim3")
+        return out[: len(keep["p"])]
+
+    def SearchBySim3(self, KF1: Frame, KF2: Frame, points1, points2, skip1, skip2, min_max_distance1, min_max_distance2,
+                     sR12, t12, sR21, t21, th: float):
+        """SearchBySim3 (src/ORBmatcher.cc:1170-1394).  points1/points2: the key frames' map points by keypoint (valid = 0:
+        none), skip = already matched or bad.  Returns (nFound, match12) with match12[i1] = keypoint of KF2 or -1."""
+        c = self._c()
+        f32 = lambda a: np.ascontiguousarray(a, np.float32)
+        keep = []
+
+        def side(KF, other, pts, skip, mm):
+            p = np.ascontiguousarray(pts, MAPPOINT_DTYPE); sk = np.ascontiguousarray(skip, np.uint8)
+            mm = f32(mm).reshape(-1, 2)
+            mn = (np.float32(0.8) * mm[:, 0]).astype(np.float32); mx_inv = (np.float32(1.2) * mm[:, 1]).astype(np.float32)
+            mx = np.ascontiguousarray(mm[:, 1]); st = KF.struct()
+            assert len(p) == KF.N and len(sk) == KF.N and len(mm) == KF.N
+            s = Sim3SideStruct()
+            s.kf = C.cast(C.pointer(st), C.c_void_p); s.points = p.ctypes.data; s.skip = sk.ctypes.data
+            s.min_distance_inv = mn.ctypes.data; s.max_distance_inv = mx_inv.ctypes.data; s.max_distance = mx.ctypes.data
+            s.log_scale_factor = float(np.log(np.float32(other.mvScaleFactors[1])))
+            keep.extend([p, sk, mn, mx_inv, mx, st])
+            return s
+        s1 = side(KF1, KF2, points1, skip1, min_max_distance1); s2 = side(KF2, KF1, points2, skip2, min_max_distance2)
+        a = [f32(sR12).ravel(), f32(t12).ravel(), f32(sR21).ravel(), f32(t21).ravel()]
+        out = np.zeros(max(KF1.N, 1), np.int32); n = C.c_int()
+        check(c._L.orbm_search_by_sim3(c.h, C.byref(s1), C.byref(s2), a[0].ctypes.data, a[1].ctypes.data, a[2].ctypes.data, a[3].ctypes.data,
+                                       th, out.ctypes.data, C.byref(n)), "orbm_search_by_sim3")
+        return n.value, out[: KF1.N]
 
     def _bow(self, variant, desc1, angle1, valid1, fv1: FeatureVector, desc2, angle2, valid2, fv2: FeatureVector):
         c = self._c()

@@ -318,19 +318,13 @@ int dropin_search_for_triangulation(const orbm_keyframe* kf1, const orbm_keyfram
     return n;
 }
 
-// ORBmatcher::Fuse(pKF, vpMapPoints, th) as LocalMapping::SearchInNeighbors calls it (LocalMapping.cc:411-417).
-// order[j] = index into the point table of the j-th entry of vpMapPoints (so one point can be listed twice);
-// kfPoint[idx] >= 0: the key frame already holds a map point at keypoint idx with that many observations (kfBad: isBad()).
-// Out: kfSlot[idx] = -1 empty, -2 the original point, >= 0 point-table index now stored there; pointBad[i] after the call.
-int dropin_fuse(const orbm_frame* kf, const float* invSigma2, const orbm_mappoint* pts, int npts, const float* minmax, const float* normals,
-                const uint8_t* inKF, const int32_t* order, int norder, const int32_t* kfPoint, const uint8_t* kfBad, float th,
-                int32_t* kfSlot, uint8_t* pointBad) {
-    KeyFrame K;
+// a KeyFrame stand-in filled from the orbm_frame view the Python scenes build
+static void keyframe_from_frame(KeyFrame& K, const orbm_frame* kf, const float* invSigma2) {
     K.N = kf->N;
     K.mvKeysUn.assign((const cv::KeyPoint*)kf->keysUn, (const cv::KeyPoint*)kf->keysUn + kf->N);
     K.mDescriptors.create(kf->N, 32, CV_8U);
     if (kf->N) std::memcpy(K.mDescriptors.data, kf->descriptors, (size_t)kf->N * 32);
-    K.mvuRight.assign(kf->uRight, kf->uRight + kf->N);
+    if (kf->uRight) K.mvuRight.assign(kf->uRight, kf->uRight + kf->N); else K.mvuRight.assign(kf->N, -1.0f);
     K.fx = kf->fx; K.fy = kf->fy; K.cx = kf->cx; K.cy = kf->cy; K.mbf = kf->bf;
     K.mnMinX = (int)kf->mnMinX; K.mnMaxX = (int)kf->mnMaxX; K.mnMinY = (int)kf->mnMinY; K.mnMaxY = (int)kf->mnMaxY;
     K.mfGridElementWidthInv = kf->gridElementWidthInv; K.mfGridElementHeightInv = kf->gridElementHeightInv;
@@ -346,6 +340,17 @@ int dropin_fuse(const orbm_frame* kf, const float* invSigma2, const orbm_mappoin
         for (int k = 0; k < 3; k++) s += (double)kf->Tcw[4 * k + i] * (double)kf->Tcw[4 * k + 3];
         K.Ow.at<float>(i) = (float)(s * -1.0);
     }
+}
+
+// ORBmatcher::Fuse(pKF, vpMapPoints, th) as LocalMapping::SearchInNeighbors calls it (LocalMapping.cc:411-417).
+// order[j] = index into the point table of the j-th entry of vpMapPoints (so one point can be listed twice);
+// kfPoint[idx] >= 0: the key frame already holds a map point at keypoint idx with that many observations (kfBad: isBad()).
+// Out: kfSlot[idx] = -1 empty, -2 the original point, >= 0 point-table index now stored there; pointBad[i] after the call.
+int dropin_fuse(const orbm_frame* kf, const float* invSigma2, const orbm_mappoint* pts, int npts, const float* minmax, const float* normals,
+                const uint8_t* inKF, const int32_t* order, int norder, const int32_t* kfPoint, const uint8_t* kfBad, float th,
+                int32_t* kfSlot, uint8_t* pointBad) {
+    KeyFrame K;
+    keyframe_from_frame(K, kf, invSigma2);
     std::vector<MapPoint> orig(kf->N), table(npts);
     KeyFrame other;                                                    // where listed points "already in a key frame" live
     other.mvuRight.assign(1, -1.0f); other.mvpMapPoints.assign(1, static_cast<MapPoint*>(NULL));
@@ -368,6 +373,102 @@ int dropin_fuse(const orbm_frame* kf, const float* invSigma2, const orbm_mappoin
         kfSlot[i] = !p ? -1 : (p == &orig[i] ? -2 : (int32_t)(p - table.data()));
     }
     for (int i = 0; i < npts; i++) pointBad[i] = table[i].mbBad;
+    return n;
+}
+
+static void sim3_table(std::vector<MapPoint>& table, const orbm_mappoint* pts, int npts, const float* minmax, const float* normals) {
+    for (int i = 0; i < npts; i++) {
+        point_from(table[i], pts[i]);
+        table[i].mfMinDistance = minmax[2 * i]; table[i].mfMaxDistance = minmax[2 * i + 1];
+        for (int k = 0; k < 3; k++) table[i].mNormalVector.at<float>(k) = normals[3 * i + k];
+    }
+}
+
+// ORBmatcher::SearchByProjection(pKF, Scw, vpPoints, vpMatched, th) as LoopClosing::ComputeSim3 calls it (LoopClosing.cc:393).
+// matched[idx] in/out: -1 NULL, -3 a point outside the table, >= 0 the table point stored in vpMatched[idx].
+int dropin_search_by_projection_sim3(const orbm_frame* kf, const float* Scw16, const orbm_mappoint* pts, int npts, const float* minmax,
+                                     const float* normals, int th, int32_t* matched) {
+    KeyFrame K;
+    std::vector<float> inv(kf->nScaleLevels, 1.0f);
+    keyframe_from_frame(K, kf, inv.data());
+    std::vector<MapPoint> table(npts), foreign(kf->N);
+    sim3_table(table, pts, npts, minmax, normals);
+    std::vector<MapPoint*> vp(npts), vpMatched(kf->N, static_cast<MapPoint*>(NULL));
+    for (int i = 0; i < npts; i++) vp[i] = &table[i];
+    for (int i = 0; i < kf->N; i++) vpMatched[i] = matched[i] >= 0 ? &table[matched[i]] : (matched[i] == -3 ? &foreign[i] : static_cast<MapPoint*>(NULL));
+    cv::Mat Scw(4, 4, CV_32F);
+    std::memcpy(Scw.data, Scw16, 64);
+    ORBmatcher matcher(0.75f, true);
+    const int n = matcher.SearchByProjection(&K, Scw, vp, vpMatched, th);
+    for (int i = 0; i < kf->N; i++) {
+        MapPoint* p = vpMatched[i];
+        matched[i] = !p ? -1 : (p == &foreign[i] ? -3 : (int32_t)(p - table.data()));
+    }
+    return n;
+}
+
+// ORBmatcher::Fuse(pKF, Scw, vpPoints, th, vpReplacePoint) as LoopClosing::SearchAndFuse calls it (LoopClosing.cc:585-586).
+// kfSlot[idx] in/out: -1 empty, -3 a point outside the table (kfBad[idx]: it isBad()), >= 0 table point held by the key frame.
+// replaced[iMP] out: -1 NULL, >= 0 table index, 1000000 + idx = the outside point of slot idx.
+int dropin_fuse_sim3(const orbm_frame* kf, const float* Scw16, const orbm_mappoint* pts, int npts, const float* minmax, const float* normals,
+                     const uint8_t* kfBad, float th, int32_t* kfSlot, int32_t* replaced) {
+    KeyFrame K;
+    std::vector<float> inv(kf->nScaleLevels, 1.0f);
+    keyframe_from_frame(K, kf, inv.data());
+    std::vector<MapPoint> table(npts), foreign(kf->N);
+    sim3_table(table, pts, npts, minmax, normals);
+    std::vector<MapPoint*> vp(npts), vpReplace(npts, static_cast<MapPoint*>(NULL));
+    for (int i = 0; i < npts; i++) vp[i] = &table[i];
+    K.mvpMapPoints.assign(kf->N, static_cast<MapPoint*>(NULL));
+    for (int i = 0; i < kf->N; i++) {
+        if (kfSlot[i] >= 0) K.mvpMapPoints[i] = &table[kfSlot[i]];
+        else if (kfSlot[i] == -3) { foreign[i].mbBad = kfBad[i] != 0; K.mvpMapPoints[i] = &foreign[i]; }
+    }
+    cv::Mat Scw(4, 4, CV_32F);
+    std::memcpy(Scw.data, Scw16, 64);
+    ORBmatcher matcher(0.8f, true);
+    const int n = matcher.Fuse(&K, Scw, vp, th, vpReplace);
+    for (int i = 0; i < kf->N; i++) {
+        MapPoint* p = K.mvpMapPoints[i];
+        kfSlot[i] = !p ? -1 : (p == &foreign[i] ? -3 : (int32_t)(p - table.data()));
+    }
+    for (int i = 0; i < npts; i++) {
+        MapPoint* p = vpReplace[i];
+        if (!p) replaced[i] = -1;
+        else if (p >= table.data() && p < table.data() + npts) replaced[i] = (int32_t)(p - table.data());
+        else replaced[i] = 1000000 + (int32_t)(p - foreign.data());
+    }
+    return n;
+}
+
+// ORBmatcher::SearchBySim3 as LoopClosing::ComputeSim3 calls it (LoopClosing.cc:371).  has1/has2: the key frames' map points by
+// keypoint (points given in pts1/pts2); prior12[i1] in/out: -1 NULL, else the keypoint of key frame 2 whose map point
+// vpMatches12[i1] holds (it is observed there, so vbAlreadyMatched2 marks it).
+int dropin_search_by_sim3(const orbm_frame* kf1, const orbm_frame* kf2, const orbm_mappoint* pts1, const orbm_mappoint* pts2,
+                          const float* minmax1, const float* minmax2, float s12, const float* R12, const float* t12, float th,
+                          int32_t* prior12) {
+    KeyFrame K1, K2;
+    std::vector<float> inv(kf1->nScaleLevels, 1.0f);
+    keyframe_from_frame(K1, kf1, inv.data()); keyframe_from_frame(K2, kf2, inv.data());
+    std::vector<MapPoint> s1(kf1->N), s2(kf2->N);
+    K1.mvpMapPoints.assign(kf1->N, static_cast<MapPoint*>(NULL)); K2.mvpMapPoints.assign(kf2->N, static_cast<MapPoint*>(NULL));
+    for (int i = 0; i < kf1->N; i++) {
+        if (!pts1[i].valid) continue;
+        point_from(s1[i], pts1[i]); s1[i].mfMinDistance = minmax1[2 * i]; s1[i].mfMaxDistance = minmax1[2 * i + 1];
+        s1[i].mObservations[&K1] = i; K1.mvpMapPoints[i] = &s1[i];
+    }
+    for (int i = 0; i < kf2->N; i++) {
+        if (!pts2[i].valid) continue;
+        point_from(s2[i], pts2[i]); s2[i].mfMinDistance = minmax2[2 * i]; s2[i].mfMaxDistance = minmax2[2 * i + 1];
+        s2[i].mObservations[&K2] = i; K2.mvpMapPoints[i] = &s2[i];
+    }
+    std::vector<MapPoint*> vpMatches12(kf1->N, static_cast<MapPoint*>(NULL));
+    for (int i = 0; i < kf1->N; i++) if (prior12[i] >= 0) vpMatches12[i] = &s2[prior12[i]];
+    cv::Mat R(3, 3, CV_32F), t(3, 1, CV_32F);
+    std::memcpy(R.data, R12, 36); std::memcpy(t.data, t12, 12);
+    ORBmatcher matcher(0.75f, true);
+    const int n = matcher.SearchBySim3(&K1, &K2, vpMatches12, s12, R, t, th);
+    for (int i = 0; i < kf1->N; i++) prior12[i] = vpMatches12[i] ? (int32_t)(vpMatches12[i] - s2.data()) : -1;
     return n;
 }
 

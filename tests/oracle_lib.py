@@ -174,6 +174,9 @@ def _bind_matcher(L):
     L.orbo_search_by_projection_points.argtypes = [vp, vp, i, vp, f, f, vp]
     L.orbo_bf2nn.argtypes = [vp, i, vp, C.c_size_t, C.c_uint32, vp]
     L.orbo_search_by_projection_keyframe.argtypes = [vp, vp, i, vp, f, vp, vp, vp, f, i, i, vp]
+    L.orbo_search_by_projection_sim3.argtypes = [vp, vp, vp, vp, vp, i, vp, vp, vp, f, vp, i, vp]
+    L.orbo_fuse_select_sim3.argtypes = [vp, vp, vp, vp, vp, i, vp, vp, vp, f, f, vp]
+    L.orbo_search_by_sim3.argtypes = [vp, vp, vp, vp, vp, vp, vp, vp, f, f, vp, vp, vp, vp, f, vp]
     L.orbo_fuse_select.argtypes = [vp, vp, vp, vp, i, vp, vp, vp, f, f, vp]
     L.orbo_search_for_triangulation.argtypes = [vp, vp, vp, vp, vp, f, f, f, f, vp, vp, vp, i, i, vp]
     L.orbo_search_by_bow_kf_frame.argtypes = [vp, vp, vp, i, vp, vp, vp, i, vp, f, i, vp]
@@ -267,6 +270,45 @@ class OracleMatcher:
         self.L.orbo_fuse_select(C.byref(s), None, sg.ctypes.data, p.ctypes.data, len(p), ik.ctypes.data, nr.ctypes.data, mm.ctypes.data,
                                 log_scale_factor, th, out.ctypes.data)
         return out[: len(p)]
+
+    def _sim3(self, KF, Rcw, tcw, Ow, points, excluded, normals, min_max_distance, log_scale_factor):
+        from orb_slam_b200.matcher import MAPPOINT_DTYPE
+        f32 = lambda a: np.ascontiguousarray(a, np.float32)
+        k = dict(R=f32(Rcw).ravel(), t=f32(tcw).ravel(), O=f32(Ow).ravel(), p=np.ascontiguousarray(points, MAPPOINT_DTYPE),
+                 ex=np.ascontiguousarray(excluded, np.uint8), nr=f32(normals).reshape(-1, 3), mm=f32(min_max_distance).reshape(-1, 2), s=KF.struct())
+        if log_scale_factor is None:
+            log_scale_factor = float(np.log(np.float32(KF.mvScaleFactors[1])))
+        args = [C.byref(k["s"]), k["R"].ctypes.data, k["t"].ctypes.data, k["O"].ctypes.data, k["p"].ctypes.data, len(k["p"]), k["ex"].ctypes.data,
+                k["nr"].ctypes.data, k["mm"].ctypes.data, log_scale_factor]
+        return k, args
+
+    def SearchByProjectionSim3(self, KF, Rcw, tcw, Ow, points, excluded, normals, min_max_distance, matched_in, th, log_scale_factor=None):
+        k, args = self._sim3(KF, Rcw, tcw, Ow, points, excluded, normals, min_max_distance, log_scale_factor)
+        mi = np.ascontiguousarray(matched_in, np.uint8)
+        out = np.zeros(max(KF.N, 1), np.int32)
+        n = self.L.orbo_search_by_projection_sim3(*args, mi.ctypes.data, int(th), out.ctypes.data)
+        return n, out[: KF.N]
+
+    def FuseSelectSim3(self, KF, Rcw, tcw, Ow, points, excluded, normals, min_max_distance, th, log_scale_factor=None):
+        k, args = self._sim3(KF, Rcw, tcw, Ow, points, excluded, normals, min_max_distance, log_scale_factor)
+        out = np.zeros(max(len(k["p"]), 1), np.int32)
+        self.L.orbo_fuse_select_sim3(*args, th, out.ctypes.data)
+        return out[: len(k["p"])]
+
+    def SearchBySim3(self, KF1, KF2, points1, points2, skip1, skip2, mm1, mm2, sR12, t12, sR21, t21, th):
+        from orb_slam_b200.matcher import MAPPOINT_DTYPE
+        f32 = lambda a: np.ascontiguousarray(a, np.float32)
+        p1 = np.ascontiguousarray(points1, MAPPOINT_DTYPE); p2 = np.ascontiguousarray(points2, MAPPOINT_DTYPE)
+        k1 = np.ascontiguousarray(skip1, np.uint8); k2 = np.ascontiguousarray(skip2, np.uint8)
+        m1 = f32(mm1).reshape(-1, 2); m2 = f32(mm2).reshape(-1, 2)
+        a = [f32(sR12).ravel(), f32(t12).ravel(), f32(sR21).ravel(), f32(t21).ravel()]
+        s1, s2 = KF1.struct(), KF2.struct()
+        out = np.zeros(max(KF1.N, 1), np.int32)
+        n = self.L.orbo_search_by_sim3(C.byref(s1), C.byref(s2), p1.ctypes.data, p2.ctypes.data, k1.ctypes.data, k2.ctypes.data,
+                                       m1.ctypes.data, m2.ctypes.data, float(np.log(np.float32(KF1.mvScaleFactors[1]))),
+                                       float(np.log(np.float32(KF2.mvScaleFactors[1]))), a[0].ctypes.data, a[1].ctypes.data,
+                                       a[2].ctypes.data, a[3].ctypes.data, th, out.ctypes.data)
+        return n, out[: KF1.N]
 
     def SearchByBoWFrame(self, descKF, angleKFun, validKF, fvKF, descF, angleF, fvF):
         d1 = np.ascontiguousarray(descKF, np.uint8).reshape(-1, 32); d2 = np.ascontiguousarray(descF, np.uint8).reshape(-1, 32)

@@ -219,3 +219,84 @@ def bow_scene(seed=0, n1=1500, n2=1600, *, n_nodes=64, p_common=0.7, flips=12, p
     v1 = (rng.random(n1) < p_valid).astype(np.uint8)
     v2 = (rng.random(n2) < p_valid).astype(np.uint8)
     return dict(desc1=d1, desc2=d2, angle1=a1, angle2=a2, valid1=v1, valid2=v2, fv1=featvec(d1, drop1), fv2=featvec(d2, drop2))
+
+
+def sim3_terms(s12, R12, t12):
+    """sR12, sR21, t21 of src/ORBmatcher.cc:1187-1189 with OpenCV's arithmetic written out: a scaled Mat is a float product by
+    float(alpha), the 3x3 * 3x1 product sums float products and the alpha = -1 of the unary minus is applied in double."""
+    s12 = np.float32(s12); R12 = np.asarray(R12, np.float32); t12 = np.asarray(t12, np.float32)
+    sR12 = (R12 * s12).astype(np.float32)
+    sR21 = (R12.T * np.float32(1.0 / np.float64(s12))).astype(np.float32)
+    t21 = np.zeros(3, np.float32)
+    for r in range(3):
+        acc = np.float32(sR21[r, 0] * t12[0])
+        acc = np.float32(acc + np.float32(sR21[r, 1] * t12[1]))
+        acc = np.float32(acc + np.float32(sR21[r, 2] * t12[2]))
+        t21[r] = np.float32(np.float64(acc) * -1.0)
+    return sR12, sR21, t21
+
+
+def sim3_scene(seed=0, n=1500, extra=300, s12=1.08, flips=5):
+    """Two key frames of a loop candidate for ORBmatcher::SearchBySim3.  Key frame 1 at the origin of its map, key frame 2 at
+    pose T2w in a drifted map; camera-1 coordinates = s12 R12 camera-2 coordinates + t12.  n points are seen by both (keypoints
+    at each other's projections plus noise, descriptors up to `flips` bits apart, octaves compatible with PredictScale);
+    `extra` unrelated keypoints with map points on each side; some slots without point, bad points, already-matched ones."""
+    from orb_slam_b200._lib import KEYPOINT_DTYPE
+    rng = np.random.default_rng(seed)
+    K = KITTI_K.astype(np.float64)
+    fx, fy, cx, cy = K[0, 0], K[1, 1], K[0, 2], K[1, 2]
+    sf = scale_factors(8, 1.2).astype(np.float64)
+    a = 0.01
+    R12 = np.array([[np.cos(a), 0, np.sin(a)], [0, 1, 0], [-np.sin(a), 0, np.cos(a)]], np.float32)
+    t12 = np.array([0.3, -0.05, 0.4], np.float32)
+    sR12, sR21, t21 = sim3_terms(s12, R12, t12)
+    b = -0.02
+    R2w = np.array([[np.cos(b), -np.sin(b), 0], [np.sin(b), np.cos(b), 0], [0, 0, 1]], np.float32)
+    T2w = np.eye(4, dtype=np.float32); T2w[:3, :3] = R2w; T2w[:3, 3] = [5.0, -1.0, 2.0]
+    N = n + extra
+
+    def keys(N):
+        k = np.zeros(N, KEYPOINT_DTYPE)
+        k["x"] = rng.uniform(20, 1220, N); k["y"] = rng.uniform(20, 355, N)
+        k["octave"] = rng.integers(0, 8, N); k["angle"] = rng.uniform(0, 360, N); k["size"] = 31
+        return k
+    k1, k2 = keys(N), keys(N)
+    d1 = rng.integers(0, 256, (N, 32), dtype=np.uint8); d2 = rng.integers(0, 256, (N, 32), dtype=np.uint8)
+    z = rng.uniform(5, 40, N)
+    P1 = np.stack([(k1["x"] - cx) * z / fx, (k1["y"] - cy) * z / fy, z], axis=1)          # camera-1 = world-1 coordinates
+    i2 = rng.permutation(N)[:n]                                                          # shared point i <-> keypoint i2[i] of key frame 2
+    Pc2 = P1[:n] @ sR21.astype(np.float64).T + t21                                        # in camera 2
+    ok = Pc2[:, 2] > 1.0
+    k2["x"][i2] = np.where(ok, fx * Pc2[:, 0] / Pc2[:, 2] + cx + rng.normal(0, 0.5, n), k2["x"][i2])
+    k2["y"][i2] = np.where(ok, fy * Pc2[:, 1] / Pc2[:, 2] + cy + rng.normal(0, 0.5, n), k2["y"][i2])
+    d2[i2] = d1[:n]
+    for _ in range(flips):
+        d2[i2, rng.integers(0, 32, n)] ^= (1 << rng.integers(0, 8, n)).astype(np.uint8)
+    k2["octave"][i2] = np.clip(k1["octave"][:n] + rng.integers(-1, 2, n), 0, 7)
+    # key frame 2's own map points: camera-2 coordinates back through T2w
+    z2 = rng.uniform(5, 40, N)
+    Pc2_all = np.stack([(k2["x"] - cx) * z2 / fx, (k2["y"] - cy) * z2 / fy, z2], axis=1)
+    Pc2_all[i2] = np.where(ok[:, None], Pc2 + rng.normal(0, 0.01, Pc2.shape), Pc2_all[i2])
+    W2 = (Pc2_all - T2w[:3, 3].astype(np.float64)) @ R2w.astype(np.float64)               # R2w^T (p - t2w)
+    Pc1_of2 = Pc2_all @ sR12.astype(np.float64).T + t12                                   # where key frame 2's points fall in camera 1
+
+    def points(world, desc, koct_other, dist_other):
+        p = np.zeros(N, MAPPOINT_DTYPE)
+        p["world"] = world.astype(np.float32); p["descriptor"] = desc
+        p["valid"] = rng.random(N) < 0.9; p["bad"] = rng.random(N) < 0.04
+        # mfMaxDistance such that PredictScale in the other key frame gives the other keypoint's octave or one above
+        mx = dist_other * sf[1] ** (koct_other + rng.uniform(-0.9, 0.9, N))
+        mm = np.stack([mx / sf[-1], mx], axis=1).astype(np.float32)
+        return p, mm
+    oct2_for1 = k2["octave"].copy().astype(np.float64); oct2_for1[:] = rng.integers(0, 8, N)
+    o2 = np.full(N, 3.0); o2[:n] = k2["octave"][i2]
+    dist_1in2 = np.linalg.norm(np.concatenate([Pc2, P1[n:] @ sR21.astype(np.float64).T + t21]), axis=1)
+    pts1, mm1 = points(P1, d1, o2, dist_1in2)
+    o1 = np.full(N, 3.0); o1[i2] = k1["octave"][:n]
+    pts2, mm2 = points(W2, d2, o1, np.linalg.norm(Pc1_of2, axis=1))
+    kf1 = make_frame(k1, d1, 1241, 376)
+    kf2 = make_frame(k2, d2, 1241, 376, Tcw=T2w)
+    skip1 = (pts1["bad"].astype(bool) | (rng.random(N) < 0.1)).astype(np.uint8)
+    skip2 = (pts2["bad"].astype(bool) | (rng.random(N) < 0.1)).astype(np.uint8)
+    return dict(kf1=kf1, kf2=kf2, pts1=pts1, pts2=pts2, mm1=mm1, mm2=mm2, skip1=skip1, skip2=skip2, s12=np.float32(s12), R12=R12,
+                t12=t12, sR12=sR12, sR21=sR21, t21=t21, i2=i2)

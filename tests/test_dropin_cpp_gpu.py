@@ -277,3 +277,114 @@ def test_fuse_member(H):
     ok = pts["valid"] == 1                                        # NULL entries have no MapPoint object behind them
     np.testing.assert_array_equal(got_bad.astype(bool)[ok], p_bad[ok])
     assert (p_bad & ~pts["bad"].astype(bool))[ok].sum() > 10      # replacements did happen
+
+
+def _sim3_scene():
+    (ka, da), (kb, db) = scenes.extract_pair(OracleExtractor, 1241, 376, 2000, 38, (3, -2))
+    src = scenes.make_frame(ka, da, 1241, 376)
+    kf = scenes.make_frame(kb, db, 1241, 376, stereo=False, seed=9)
+    kf.mvuRight = np.full(kf.N, -1, np.float32)
+    pts, mm, normals, _ = scenes.fuse_points(src, seed=41)
+    # 150 points listed a second time: both copies choose the same keypoint
+    pts = np.concatenate([pts, pts[:150]]); mm = np.concatenate([mm, mm[:150]]); normals = np.concatenate([normals, normals[:150]])
+    pts["valid"] = 1
+    # Scw = [s R | t]; the decomposition of src/ORBmatcher.cc:299-303 with OpenCV's arithmetic written out
+    a, s = np.float32(-0.008), np.float32(1.07)
+    R = np.array([[np.cos(a), 0, np.sin(a)], [0, 1, 0], [-np.sin(a), 0, np.cos(a)]], np.float32)
+    Scw = np.eye(4, dtype=np.float32)
+    Scw[:3, :3] = s * R
+    Scw[:3, 3] = [0.04, 0.01, 0.25]
+    r0 = Scw[0, :3].astype(np.float64)
+    scw = np.float32(np.sqrt((r0[0] * r0[0] + r0[1] * r0[1]) + r0[2] * r0[2]))
+    inv = np.float32(1.0 / np.float64(scw))
+    Rcw = (Scw[:3, :3] * inv).astype(np.float32)
+    tcw = (Scw[:3, 3] * inv).astype(np.float32)
+    Rd, td = Rcw.astype(np.float64), tcw.astype(np.float64)
+    Ow = np.array([-((Rd[0, r] * td[0] + Rd[1, r] * td[1]) + Rd[2, r] * td[2]) for r in range(3)]).astype(np.float32)
+    return kf, pts, mm, normals, Scw, Rcw, tcw, Ow
+
+
+def test_search_by_projection_sim3_member(H):
+    """ORBmatcher::SearchByProjection(pKF, Scw, vpPoints, vpMatched, th): Scw decomposed by the member, vpMatched edited in place"""
+    from orb_slam_b200.matcher import MAPPOINT_DTYPE
+    kf, pts, mm, normals, Scw, Rcw, tcw, Ow = _sim3_scene()
+    rng = np.random.default_rng(42)
+    matched = np.full(kf.N, -1, np.int32)
+    taken = rng.random(kf.N) < 0.3
+    matched[taken] = -3
+    own = np.nonzero(taken)[0][:200]                                    # 200 slots hold points of the table itself -> spAlreadyFound
+    matched[own] = rng.choice(len(pts), len(own), replace=False)
+    excluded = pts["bad"].astype(bool).copy()
+    excluded[matched[matched >= 0]] = True
+    n_o, m_o = OracleMatcher(0.75, True).SearchByProjectionSim3(kf, Rcw, tcw, Ow, pts, excluded.astype(np.uint8), normals, mm, matched != -1, 10)
+    expect = np.where(m_o >= 0, m_o, matched)
+    p = lambda a: C.c_void_p(a.ctypes.data)
+    sk = kf.struct()
+    ptsc = np.ascontiguousarray(pts, MAPPOINT_DTYPE); mmc = np.ascontiguousarray(mm, np.float32); nrc = np.ascontiguousarray(normals, np.float32)
+    got = matched.copy()
+    n = H.dropin_search_by_projection_sim3(C.byref(sk), p(Scw), p(ptsc), len(pts), p(mmc), p(nrc), 10, p(got))
+    assert n == n_o and n > 20
+    np.testing.assert_array_equal(got, expect)
+
+
+def test_fuse_sim3_member(H):
+    """ORBmatcher::Fuse(pKF, Scw, vpPoints, th, vpReplacePoint): selection on the device, vpReplacePoint / AddMapPoint in the
+    reference's order (a slot filled by an earlier point is what a later one is told to replace)"""
+    from orb_slam_b200.matcher import MAPPOINT_DTYPE
+    kf, pts, mm, normals, Scw, Rcw, tcw, Ow = _sim3_scene()
+    rng = np.random.default_rng(43)
+    slot = np.where(rng.random(kf.N) < 0.4, -3, -1).astype(np.int32)
+    own = np.nonzero(slot == -3)[0][:150]
+    slot[own] = rng.choice(len(pts), len(own), replace=False)           # key-frame points that are also in vpPoints
+    kf_bad = ((slot == -3) & (rng.random(kf.N) < 0.15)).astype(np.uint8)
+    excluded = pts["bad"].astype(bool).copy()
+    held = slot[slot >= 0]
+    excluded[held[~pts["bad"][held].astype(bool)]] = True               # GetMapPoints() leaves bad points out
+    best = OracleMatcher(0.8, True).FuseSelectSim3(kf, Rcw, tcw, Ow, pts, excluded.astype(np.uint8), normals, mm, 4.0)
+    exp_slot = slot.copy(); exp_rep = np.full(len(pts), -1, np.int32); n_exp = 0
+    for i in range(len(pts)):
+        b = best[i]
+        if b < 0:
+            continue
+        if exp_slot[b] != -1:
+            bad = kf_bad[b] if exp_slot[b] == -3 else pts["bad"][exp_slot[b]]
+            if not bad:
+                exp_rep[i] = 1000000 + b if exp_slot[b] == -3 else exp_slot[b]
+        else:
+            exp_slot[b] = i
+        n_exp += 1
+    p = lambda a: C.c_void_p(a.ctypes.data)
+    sk = kf.struct()
+    ptsc = np.ascontiguousarray(pts, MAPPOINT_DTYPE); mmc = np.ascontiguousarray(mm, np.float32); nrc = np.ascontiguousarray(normals, np.float32)
+    got_slot = slot.copy(); got_rep = np.zeros(len(pts), np.int32)
+    n = H.dropin_fuse_sim3(C.byref(sk), p(Scw), p(ptsc), len(pts), p(mmc), p(nrc), p(kf_bad), C.c_float(4.0), p(got_slot), p(got_rep))
+    assert n == n_exp and n > 20
+    np.testing.assert_array_equal(got_slot, exp_slot)
+    np.testing.assert_array_equal(got_rep, exp_rep)
+    assert (exp_rep >= 1000000).sum() > 3 and ((exp_rep >= 0) & (exp_rep < 1000000)).sum() > 3 and (exp_slot != slot).sum() > 3
+
+
+def test_search_by_sim3_member(H):
+    """ORBmatcher::SearchBySim3: the member forms sR12 / sR21 / t21, the already-matched flags (GetIndexInKeyFrame) and writes
+    vpMatches12; prior matches stay and block their keypoints on both sides"""
+    from orb_slam_b200.matcher import MAPPOINT_DTYPE
+    sc = scenes.sim3_scene(seed=5, s12=1.05)
+    kf1, kf2, pts1, pts2 = sc["kf1"], sc["kf2"], sc["pts1"], sc["pts2"]
+    rng = np.random.default_rng(44)
+    prior = np.full(kf1.N, -1, np.int32)
+    cand = np.nonzero(pts2["valid"] == 1)[0]
+    slots = rng.choice(kf1.N, 200, replace=False)
+    prior[slots] = rng.choice(cand, 200, replace=False)                 # 200 matches a previous step (SearchByBoW) already made
+    skip1 = (pts1["bad"].astype(bool) | (prior >= 0)).astype(np.uint8)
+    skip2 = pts2["bad"].astype(bool).copy(); skip2[prior[prior >= 0]] = True
+    n_o, m_o = OracleMatcher(0.75, True).SearchBySim3(kf1, kf2, pts1, pts2, skip1, skip2.astype(np.uint8), sc["mm1"], sc["mm2"],
+                                                      sc["sR12"], sc["t12"], sc["sR21"], sc["t21"], 7.5)
+    expect = np.where(m_o >= 0, m_o, prior)
+    p = lambda a: C.c_void_p(a.ctypes.data)
+    k1, k2 = kf1.struct(), kf2.struct()
+    p1 = np.ascontiguousarray(pts1, MAPPOINT_DTYPE); p2 = np.ascontiguousarray(pts2, MAPPOINT_DTYPE)
+    got = prior.copy()
+    n = H.dropin_search_by_sim3(C.byref(k1), C.byref(k2), p(p1), p(p2), p(sc["mm1"]), p(sc["mm2"]), C.c_float(sc["s12"]),
+                                p(np.ascontiguousarray(sc["R12"])), p(sc["t12"]), C.c_float(7.5), p(got))
+    assert n == n_o and n > 300
+    np.testing.assert_array_equal(got, expect)

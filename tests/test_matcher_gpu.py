@@ -139,6 +139,51 @@ def test_fuse_select(ctx, stereo, th, tz):
     assert not np.any(in_kf[sel]) and np.all(pts["valid"][sel] == 1) and not np.any(pts["bad"][sel])
 
 
+@pytest.mark.parametrize("scale,tz,th", [(1.0, 0.2, 10), (1.15, -0.3, 10), (0.9, 1.0, 4)])
+def test_sim3_matchers(ctx, scale, tz, th):
+    """Loop closing's SearchByProjection(pKF, Scw, vpPoints, vpMatched, th) (:290-403) and Fuse(pKF, Scw, ...) (:1044-1168)"""
+    from orb_slam_b200.matcher import ORBmatcher
+    (ka, da), (kb, db) = scenes.extract_pair(OracleExtractor, 1241, 376, 2000, 37, (2, 3))
+    src = scenes.make_frame(ka, da, 1241, 376)
+    kf = scenes.make_frame(kb, db, 1241, 376)
+    pts, mm, normals, in_kf = scenes.fuse_points(src, seed=31)
+    pts["valid"] = 1
+    excluded = (pts["bad"].astype(bool) | in_kf.astype(bool)).astype(np.uint8)
+    # a similarity with scale `scale`: the functions receive it decomposed (rotation without the scale, tcw / s, camera centre)
+    a = np.float32(0.01)
+    R = np.array([[np.cos(a), -np.sin(a), 0], [np.sin(a), np.cos(a), 0], [0, 0, 1]], np.float32)
+    t = (np.array([0.03, -0.02, tz], np.float32) / np.float32(scale)).astype(np.float32)
+    Ow = (-(R.T.astype(np.float64) @ t.astype(np.float64))).astype(np.float32)
+    matched_in = (np.random.default_rng(32).random(kf.N) < 0.3).astype(np.uint8)
+    n_g, m_g = ORBmatcher(0.75, True, ctx).SearchByProjectionSim3(kf, R, t, Ow, pts, excluded, normals, mm, matched_in, th)
+    n_o, m_o = OracleMatcher(0.75, True).SearchByProjectionSim3(kf, R, t, Ow, pts, excluded, normals, mm, matched_in, th)
+    assert n_g == n_o and n_o > 20
+    assert np.array_equal(m_g, m_o)
+    hit = m_g >= 0
+    assert not np.any(matched_in[hit]) and not np.any(excluded[m_g[hit]]) and len(np.unique(m_g[hit])) == hit.sum()
+    b_g = ORBmatcher(0.75, True, ctx).FuseSelectSim3(kf, R, t, Ow, pts, excluded, normals, mm, float(th))
+    b_o = OracleMatcher(0.75, True).FuseSelectSim3(kf, R, t, Ow, pts, excluded, normals, mm, float(th))
+    assert np.array_equal(b_g, b_o) and (b_o >= 0).sum() > 20
+    assert not np.any(excluded[b_g >= 0])
+
+
+@pytest.mark.parametrize("seed,s12,th", [(0, 1.08, 7.5), (1, 0.93, 7.5), (2, 1.0, 3.0)])
+def test_search_by_sim3(ctx, seed, s12, th):
+    """ORBmatcher::SearchBySim3 (:1170-1394): both projection directions and the agreement check"""
+    from orb_slam_b200.matcher import ORBmatcher
+    sc = scenes.sim3_scene(seed=seed, s12=s12)
+    args = (sc["kf1"], sc["kf2"], sc["pts1"], sc["pts2"], sc["skip1"], sc["skip2"], sc["mm1"], sc["mm2"], sc["sR12"], sc["t12"],
+            sc["sR21"], sc["t21"], th)
+    n_g, m_g = ORBmatcher(0.75, True, ctx).SearchBySim3(*args)
+    n_o, m_o = OracleMatcher(0.75, True).SearchBySim3(*args)
+    assert n_g == n_o and np.array_equal(m_g, m_o)
+    assert n_o > 300
+    i1 = np.nonzero(m_o >= 0)[0]
+    assert not np.any(sc["skip1"][i1]) and not np.any(sc["skip2"][m_o[i1]]) and len(np.unique(m_o[i1])) == len(i1)
+    shared = i1[i1 < len(sc["i2"])]
+    assert (m_o[shared] == sc["i2"][shared]).mean() > 0.95              # the planted correspondences are what it finds
+
+
 def test_bruteforce_2nn_and_sharded_merge(ctx):
     import ctypes as C
     import torch
