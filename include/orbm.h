@@ -243,6 +243,61 @@ int orbm_search_for_triangulation(orbm_t* m, const orbm_keyframe* kf1, const orb
                                   const float* scale_factors2, const float* level_sigma2_2, int nlevels, const float* F12,
                                   int onlyStereo, int checkOrientation, int32_t* matches12, int* nmatches);
 
+/* ---- Frame::ComputeBoW / KeyFrame::ComputeBoW (src/Frame.cc:521-528, src/KeyFrame.cc:59-68) =
+ * ORBVocabulary::transform(features, BowVector, FeatureVector, levelsup = 4)
+ * (Thirdparty/DBoW2/DBoW2/TemplatedVocabulary.h:1126-1194; the per-feature tree descent :1217-1259 with
+ * FORB::distance, Thirdparty/DBoW2/DBoW2/FORB.cpp:84-104, runs on the device).  SURVEY §8(f) rank 3.
+ *
+ * A vocabulary is the tree loadFromTextFile builds (TemplatedVocabulary.h:1338-1426): node 0 is the root, node
+ * ids follow the line order of the file, a node's children are kept in the order they were appended, words are
+ * numbered in the order their leaf lines appear. */
+typedef struct orbm_vocab orbm_vocab_t;
+
+/* DBoW2::WeightingType / ScoringType (Thirdparty/DBoW2/DBoW2/BowVector.h:36-55) */
+#define ORBM_W_TF_IDF 0
+#define ORBM_W_TF 1
+#define ORBM_W_IDF 2
+#define ORBM_W_BINARY 3
+#define ORBM_S_L1_NORM 0
+#define ORBM_S_L2_NORM 1
+#define ORBM_S_CHI_SQUARE 2
+#define ORBM_S_KL 3
+#define ORBM_S_BHATTACHARYYA 4
+#define ORBM_S_DOT_PRODUCT 5
+
+/* From flat arrays: nnodes includes the root; parent[i] (i >= 1) < nnodes is the node a line's first field names
+ * (parent[0] ignored); is_leaf[i] = the line's second field > 0; desc = nnodes x 32 bytes (row 0 ignored);
+ * weight[i] = the line's last field.  k and L are the header's m_k and m_L (L bounds the descent depth and sets
+ * the FeatureVector level L - levelsup; k is informational). */
+int orbm_vocab_create(orbm_t* m, int k, int L, int scoring, int weighting, int nnodes, const int32_t* parent,
+                      const uint8_t* is_leaf, const uint8_t* desc, const double* weight, orbm_vocab_t** out);
+/* The text format of Vocabulary/ORBvoc.txt as TemplatedVocabulary::loadFromTextFile reads it. */
+int orbm_vocab_load_text(orbm_t* m, const char* path, orbm_vocab_t** out);
+void orbm_vocab_destroy(orbm_vocab_t* v);
+int orbm_vocab_info(const orbm_vocab_t* v, int* k, int* L, int* nnodes, int* nwords, int* scoring, int* weighting);
+
+/* transform(feature, word_id, weight, &nid, levelsup) for n features (host pointers): word_id[i], node_id[i]
+ * (the ancestor at level L - levelsup; 0 = root when that level is <= 0), weight[i] (may be NULL). */
+int orbm_vocab_descend(orbm_t* m, const orbm_vocab_t* v, const uint8_t* desc, int n, int levelsup, uint32_t* word_id,
+                       uint32_t* node_id, double* weight);
+/* Same on DEVICE pointers (e.g. the extractor's descriptor output of a whole batch): word_node[i] = {word id,
+ * node id}.  Enqueued on the context stream. */
+int orbm_vocab_descend_device(orbm_t* m, const orbm_vocab_t* v, const uint8_t* d_desc, size_t n, int levelsup,
+                              uint32_t* d_word_node);
+/* transform(features, v, fv, levelsup): the BowVector flattened in map order (word ids ascending, values after the
+ * scoring type's normalisation) and the FeatureVector as an orbm_featvec layout.  Capacities: word_ids/word_vals n
+ * entries, node_ids n, node_start n + 1, items n. */
+int orbm_vocab_transform(orbm_t* m, const orbm_vocab_t* v, const uint8_t* desc, int n, int levelsup, uint32_t* word_ids,
+                         double* word_vals, int* nwords, uint32_t* node_ids, int32_t* node_start, uint32_t* items,
+                         int* nnodes);
+
+/* ---- MapPoint::ComputeDistinctiveDescriptors (src/MapPoint.cc:241-306), batched over map points.  SURVEY §8(f)
+ * rank 4.  Point p owns the descriptors start[p]..start[p+1] of desc (its observations in std::map<KeyFrame*,size_t>
+ * order, bad key frames already dropped, :264-270).  best[p] = index (relative to start[p]) of the descriptor with
+ * the least median distance to the others - the element [0.5*(N-1)] of its sorted distance row, first row wins
+ * ties (:288-301); -1 for a point without descriptors (the reference returns early, :272-273). */
+int orbm_distinctive_descriptors(orbm_t* m, const uint8_t* desc, const int32_t* start, int npoints, int32_t* best);
+
 #ifdef __cplusplus
 }
 #endif

@@ -4,6 +4,7 @@
 #include <algorithm>
 #include <cmath>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <mutex>
 #include <vector>
@@ -12,6 +13,7 @@
 #include "hamming.cuh"
 #include "window.cuh"
 #include "bow.cuh"
+#include "vocab.cuh"
 
 using namespace orbm;
 
@@ -197,3 +199,4 @@ int orbm_popc_peak(orbm_t* m, double* popc_per_s) {
 
 #include "window_host.inl"
 #include "bow_host.inl"
+#include "vocab_host.inl"

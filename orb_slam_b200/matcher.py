@@ -82,6 +82,17 @@ class FeatureVector:
                       else np.zeros(0, np.uint32))
         self.items = np.ascontiguousarray(self.items, np.uint32)
 
+    @classmethod
+    def from_flat(cls, node_ids, start, items):
+        fv = cls({})
+        fv.node_ids = np.ascontiguousarray(node_ids, np.uint32).copy()
+        fv.start = np.ascontiguousarray(start, np.int32).copy()
+        fv.items = np.ascontiguousarray(items, np.uint32).copy()
+        return fv
+
+    def as_dict(self):
+        return {int(k): self.items[self.start[j]:self.start[j + 1]].tolist() for j, k in enumerate(self.node_ids)}
+
     def struct(self) -> FeatVecStruct:
         s = FeatVecStruct()
         s.nnodes = len(self.node_ids)

@@ -110,3 +110,45 @@ def synth_descriptors(n: int, seed: int) -> np.ndarray:
     with np.errstate(over="ignore"):
         v = splitmix64(splitmix64(np.uint64(seed)) ^ idx)
     return v.view(np.uint8)[: n * 32].reshape(n, 32).copy()
+
+
+def synth_vocabulary(k: int = 10, L: int = 6, seed: int = 0xB0C, stop_fraction: float = 0.01):
+    """A synthetic ORB vocabulary with the shape of Vocabulary/ORBvoc.txt (k = 10, L = 6: 1 111 111 nodes, 10^6
+    words; the real file is absent from the reference tree).  Returns (parent, is_leaf, desc, weight) indexed by
+    node id, node 0 = root, ids level by level so a parent precedes its children.  A child's descriptor is its
+    parent's with a level-dependent number of random bit flips (cluster centres spread out near the root, tight
+    near the leaves); leaf weights look like idf values, `stop_fraction` of them 0 (stopped words)."""
+    rng = np.random.default_rng(seed)
+    counts = [k ** l for l in range(L + 1)]
+    n = sum(counts)
+    parent = np.zeros(n, np.int32)
+    desc = np.zeros((n, 32), np.uint8)
+    first = np.cumsum([0] + counts)           # first id of each level
+    for l in range(1, L + 1):
+        ids = np.arange(first[l], first[l + 1])
+        par = first[l - 1] + (ids - first[l]) // k
+        parent[ids] = par
+        if l == 1:
+            desc[ids] = rng.integers(0, 256, (len(ids), 32), dtype=np.uint8)
+        else:
+            p_flip = 0.5 * (0.55 ** (l - 1))              # per-bit flip probability
+            for c0 in range(0, len(ids), 1 << 16):                # chunks: 256 random draws per node
+                c = slice(c0, c0 + (1 << 16))
+                flips = np.packbits(rng.random((len(ids[c]), 256), dtype=np.float32) < p_flip, axis=1)
+                desc[ids[c]] = desc[par[c]] ^ flips
+    is_leaf = np.zeros(n, np.uint8)
+    is_leaf[first[L]:] = 1
+    weight = np.zeros(n, np.float64)
+    nl = counts[L]
+    w = np.log(rng.uniform(1.5, 4000.0, nl))
+    w[rng.random(nl) < stop_fraction] = 0.0
+    weight[first[L]:] = w
+    return parent, is_leaf, desc, weight
+
+
+def vocabulary_text(k, L, parent, is_leaf, desc, weight, scoring=0, weighting=0, trailing_newline=False) -> str:
+    """The ORBvoc.txt text format (what TemplatedVocabulary::saveToTextFile writes / loadFromTextFile reads)."""
+    lines = [f"{k} {L}  {scoring} {weighting}"]
+    for i in range(1, len(parent)):
+        lines.append(f"{int(parent[i])} {int(is_leaf[i])} " + " ".join(str(int(b)) for b in desc[i]) + f" {float(weight[i])!r}")
+    return "\n".join(lines) + ("\n" if trailing_newline else "")

@@ -341,3 +341,122 @@ class OracleMatcher:
                                                  float(K2[0, 0]), float(K2[1, 1]), float(K2[0, 2]), float(K2[1, 2]), sf.ctypes.data,
                                                  sg.ctypes.data, F12.ctypes.data, int(bOnlyStereo), int(self.checkOri), out.ctypes.data)
         return n, out[: kf1.N]
+
+
+# ---------------- vocabulary (oracle/orb_oracle_vocab.cc) and the reference's own DBoW2 (oracle/_ref/libdbow2_ref.so)
+DBOW2_REF_SO = os.path.join(ROOT, "oracle", "_ref", "libdbow2_ref.so")
+_dbow2 = None
+
+
+def have_dbow2_ref() -> bool:
+    return os.path.exists(DBOW2_REF_SO)
+
+
+def _flat_transform(fn, h, desc, levelsup):
+    d = np.ascontiguousarray(desc, np.uint8).reshape(-1, 32)
+    n = len(d)
+    wid = np.zeros(max(n, 1), np.uint32); wv = np.zeros(max(n, 1), np.float64)
+    nid = np.zeros(max(n, 1), np.uint32); st = np.zeros(n + 1, np.int32); it = np.zeros(max(n, 1), np.uint32)
+    nw, nn = C.c_int(), C.c_int()
+    fn(h, d.ctypes.data, n, levelsup, wid.ctypes.data, wv.ctypes.data, C.byref(nw), nid.ctypes.data, st.ctypes.data,
+       it.ctypes.data, C.byref(nn))
+    fv = {int(nid[j]): it[st[j]:st[j + 1]].tolist() for j in range(nn.value)}
+    return wid[:nw.value].copy(), wv[:nw.value].copy(), fv
+
+
+class OracleVocabulary:
+    """CPU restatement of ORBVocabulary (oracle/orb_oracle_vocab.cc)."""
+
+    def __init__(self, handle):
+        self._h = handle
+
+    @staticmethod
+    def _lib():
+        L = oracle()
+        if not getattr(L, "_vocab_bound", False):
+            vp, i = C.c_void_p, C.c_int
+            L.orbo_vocab_create.restype = vp; L.orbo_vocab_create.argtypes = [i, i, i, i, i, vp, vp, vp, vp]
+            L.orbo_vocab_load_text.restype = vp; L.orbo_vocab_load_text.argtypes = [C.c_char_p]
+            L.orbo_vocab_destroy.argtypes = [vp]; L.orbo_vocab_destroy.restype = None
+            L.orbo_vocab_words.argtypes = [vp]; L.orbo_vocab_nodes.argtypes = [vp]
+            L.orbo_vocab_descend.argtypes = [vp, vp, i, i, vp, vp, vp]; L.orbo_vocab_descend.restype = None
+            L.orbo_vocab_transform.argtypes = [vp, vp, i, i, vp, vp, C.POINTER(i), vp, vp, vp, C.POINTER(i)]
+            L.orbo_distinctive_descriptors.argtypes = [vp, vp, i, vp]; L.orbo_distinctive_descriptors.restype = None
+            L._vocab_bound = True
+        return L
+
+    @classmethod
+    def from_arrays(cls, k, L, parent, is_leaf, desc, weight, scoring=0, weighting=0):
+        parent = np.ascontiguousarray(parent, np.int32); is_leaf = np.ascontiguousarray(is_leaf, np.uint8)
+        desc = np.ascontiguousarray(desc, np.uint8).reshape(-1, 32); weight = np.ascontiguousarray(weight, np.float64)
+        h = cls._lib().orbo_vocab_create(k, L, scoring, weighting, len(parent), parent.ctypes.data, is_leaf.ctypes.data,
+                                         desc.ctypes.data, weight.ctypes.data)
+        return cls(C.c_void_p(h))
+
+    @classmethod
+    def loadFromTextFile(cls, path):
+        h = cls._lib().orbo_vocab_load_text(str(path).encode())
+        assert h, path
+        return cls(C.c_void_p(h))
+
+    def __del__(self):
+        try:
+            if self._h:
+                self._lib().orbo_vocab_destroy(self._h); self._h = None
+        except Exception:
+            pass
+
+    def size(self):
+        return self._lib().orbo_vocab_words(self._h)
+
+    def nodes(self):
+        return self._lib().orbo_vocab_nodes(self._h)
+
+    def descend(self, desc, levelsup=4):
+        d = np.ascontiguousarray(desc, np.uint8).reshape(-1, 32)
+        n = len(d)
+        w = np.zeros(n, np.uint32); nid = np.zeros(n, np.uint32); wt = np.zeros(n, np.float64)
+        self._lib().orbo_vocab_descend(self._h, d.ctypes.data, n, levelsup, w.ctypes.data, nid.ctypes.data, wt.ctypes.data)
+        return w, nid, wt
+
+    def transform(self, desc, levelsup=4):
+        return _flat_transform(self._lib().orbo_vocab_transform, self._h, desc, levelsup)
+
+
+def oracle_distinctive_descriptors(desc, start):
+    d = np.ascontiguousarray(desc, np.uint8).reshape(-1, 32)
+    start = np.ascontiguousarray(start, np.int32)
+    best = np.zeros(max(len(start) - 1, 1), np.int32)
+    OracleVocabulary._lib().orbo_distinctive_descriptors(d.ctypes.data, start.ctypes.data, len(start) - 1, best.ctypes.data)
+    return best[:len(start) - 1]
+
+
+class RefVocabulary:
+    """The reference's own DBoW2 TemplatedVocabulary<FORB::TDescriptor, FORB> (oracle/_ref/libdbow2_ref.so)."""
+
+    def __init__(self, path):
+        global _dbow2
+        if _dbow2 is None:
+            L = C.CDLL(DBOW2_REF_SO)
+            vp, i = C.c_void_p, C.c_int
+            L.refvoc_load_text.restype = vp; L.refvoc_load_text.argtypes = [C.c_char_p]
+            L.refvoc_free.argtypes = [vp]; L.refvoc_free.restype = None
+            L.refvoc_size.argtypes = [vp]; L.refvoc_size.restype = C.c_uint
+            L.refvoc_transform.argtypes = [vp, vp, i, i, vp, vp, C.POINTER(i), vp, vp, vp, C.POINTER(i)]
+            _dbow2 = L
+        self._L = _dbow2
+        self._h = C.c_void_p(self._L.refvoc_load_text(str(path).encode()))
+        assert self._h, path
+
+    def __del__(self):
+        try:
+            if self._h:
+                self._L.refvoc_free(self._h); self._h = None
+        except Exception:
+            pass
+
+    def size(self):
+        return self._L.refvoc_size(self._h)
+
+    def transform(self, desc, levelsup=4):
+        return _flat_transform(self._L.refvoc_transform, self._h, desc, levelsup)

@@ -300,3 +300,75 @@ def sim3_scene(seed=0, n=1500, extra=300, s12=1.08, flips=5):
     skip2 = (pts2["bad"].astype(bool) | (rng.random(N) < 0.1)).astype(np.uint8)
     return dict(kf1=kf1, kf2=kf2, pts1=pts1, pts2=pts2, mm1=mm1, mm2=mm2, skip1=skip1, skip2=skip2, s12=np.float32(s12), R12=R12,
                 t12=t12, sR12=sR12, sR21=sR21, t21=t21, i2=i2)
+
+
+# ---------------------------------------------------------------- vocabulary scenes (ComputeBoW)
+def unbalanced_vocabulary(k=7, L=4, seed=3, p_leaf=0.2, stop_fraction=0.1, min_leaf_level=1):
+    """Small vocabulary in the id order HKmeansStep creates (a node's children get consecutive ids, then each child's
+    subtree follows: Thirdparty/DBoW2/DBoW2/TemplatedVocabulary.h:640-760), with ragged child counts and leaves at
+    different depths (none above `min_leaf_level`: transform() leaves the FeatureVector node id uninitialised when a leaf is
+    shallower than level L - levelsup).  Returns (parent, is_leaf, desc, weight)."""
+    rng = np.random.default_rng(seed)
+    parent, leaf, desc, weight = [0], [0], [np.zeros(32, np.uint8)], [0.0]
+
+    def grow(node, level):
+        nchild = int(rng.integers(2, k + 1))
+        ids = []
+        for _ in range(nchild):
+            ids.append(len(parent))
+            parent.append(node); leaf.append(0); weight.append(0.0)
+            if level == 1:
+                desc.append(rng.integers(0, 256, 32, dtype=np.uint8))
+            else:
+                flips = np.packbits(rng.random(256) < 0.5 * 0.55 ** (level - 1))
+                desc.append(desc[node] ^ flips)
+        for c in ids:
+            if level < L and (level < min_leaf_level or rng.random() > p_leaf):
+                grow(c, level + 1)
+            else:
+                leaf[c] = 1
+                weight[c] = 0.0 if rng.random() < stop_fraction else float(np.log(rng.uniform(1.5, 4000.0)))
+
+    grow(0, 1)
+    return (np.array(parent, np.int32), np.array(leaf, np.uint8), np.stack(desc).astype(np.uint8),
+            np.array(weight, np.float64))
+
+
+def vocabulary_queries(desc, is_leaf, n, seed=5, max_flips=40):
+    """n query descriptors: vocabulary leaves with 0..max_flips random bit flips (exact ties and near-ties between
+    sibling centres occur), every fourth one uniformly random."""
+    rng = np.random.default_rng(seed)
+    leaves = np.flatnonzero(is_leaf)
+    q = desc[rng.choice(leaves, n)].copy()
+    for i in range(n):
+        if i % 4 == 3:
+            q[i] = rng.integers(0, 256, 32, dtype=np.uint8)
+        else:
+            bits = rng.choice(256, int(rng.integers(0, max_flips + 1)), replace=False)
+            for b in bits:
+                q[i, b >> 3] ^= np.uint8(1 << (b & 7))
+    return q
+
+
+def observation_lists(npoints, seed=9, max_obs=12, big=(40, 77, 150)):
+    """Descriptor lists of map points for ComputeDistinctiveDescriptors: a true descriptor per point observed with
+    noise 1..max_obs times (plus a few long lists, an empty one and duplicates that force median ties)."""
+    rng = np.random.default_rng(seed)
+    descs, start = [], [0]
+    sizes = [int(rng.integers(1, max_obs + 1)) for _ in range(npoints)]
+    for j, b in enumerate(big):
+        if j < npoints:
+            sizes[(j * 7 + 3) % npoints] = b
+    if npoints > 5:
+        sizes[5] = 0
+    for p, n in enumerate(sizes):
+        base = rng.integers(0, 256, 32, dtype=np.uint8)
+        for o in range(n):
+            d = base.copy()
+            if not (p % 3 == 0 and o % 2 == 1):          # every other observation of every third point is an exact duplicate
+                for b in rng.choice(256, int(rng.integers(0, 30)), replace=False):
+                    d[b >> 3] ^= np.uint8(1 << (b & 7))
+            descs.append(d)
+        start.append(start[-1] + n)
+    D = np.stack(descs).astype(np.uint8) if descs else np.zeros((0, 32), np.uint8)
+    return D, np.array(start, np.int32)
