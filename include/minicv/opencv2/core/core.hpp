@@ -206,6 +206,10 @@ public:
         for (int i = 0; i < rows; i++) std::memmove(dst.ptr(i), ptr(i), (size_t)cols * elemSize());
     }
 
+#ifdef MINICV_MAT_EXTRA_MEMBERS     // hook for the oracle's reference build (oracle/ref_build/cvstub): float algebra members
+    MINICV_MAT_EXTRA_MEMBERS
+#endif
+
 private:
     std::shared_ptr<uchar> owner;   // null for user-owned memory
 };

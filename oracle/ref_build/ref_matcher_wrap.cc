@@ -1,0 +1,319 @@
+// ORACLE reference build (test infrastructure, never linked into the product): drives the REFERENCE's own
+// src/ORBmatcher.cc, src/Frame.cc, src/KeyFrame.cc, src/MapPoint.cc (+ Map.cc, KeyFrameDatabase.cc, Thirdparty/DBoW2),
+// compiled unmodified from /root/reference where they lie (oracle/Makefile `make ref`), through the same flat
+// argument lists as the CPU restatement in oracle/orb_oracle_matcher.cc / orb_oracle_bow.cc / orb_oracle_vocab.cc
+// (orbref_X has the signature of orbo_X), so tests can run one scene through both and demand identical results.
+// The objects (Frame, KeyFrame, MapPoint) are the reference's classes; this file only fills their members.
+#include <algorithm>
+#include <cassert>
+#include <cmath>
+#include <cstring>
+#include <fstream>
+#include <iostream>
+#include <limits>
+#include <list>
+#include <map>
+#include <memory>
+#include <mutex>
+#include <numeric>
+#include <set>
+#include <sstream>
+#include <string>
+#include <thread>
+#include <vector>
+#include <opencv2/opencv.hpp>
+#include "Thirdparty/DBoW2/DBoW2/FORB.h"
+#include "Thirdparty/DBoW2/DBoW2/TemplatedVocabulary.h"
+
+#define private public          // test harness access to Frame::AssignFeaturesToGrid and the MapPoint / KeyFrame state
+#define protected public
+#include "ORBmatcher.h"
+#include "Frame.h"
+#include "KeyFrame.h"
+#include "MapPoint.h"
+#include "Map.h"
+#include "Converter.h"
+#undef private
+#undef protected
+
+#include <cmath>
+#include <cstring>
+#include <map>
+#include <memory>
+#include <set>
+#include <vector>
+
+#include "../../include/orbm.h"
+
+namespace ORB_SLAM2 {
+std::vector<cv::Mat> Converter::toDescriptorVector(const cv::Mat& Descriptors) {     // src/Converter.cc:27-35
+    std::vector<cv::Mat> vDesc;
+    vDesc.reserve(Descriptors.rows);
+    for (int j = 0; j < Descriptors.rows; j++) vDesc.push_back(Descriptors.row(j));
+    return vDesc;
+}
+}  // namespace ORB_SLAM2
+
+using namespace ORB_SLAM2;
+
+namespace {
+
+struct World {                                   // owns every object of one call
+    Map map;
+    std::vector<std::unique_ptr<Frame>> frames;
+    std::vector<KeyFrame*> keyframes;            // leaked deliberately small: KeyFrame has no public destructor issues, but
+    std::vector<MapPoint*> points;               // MapPoint/KeyFrame are only ever heap objects in the reference
+    ~World() { for (MapPoint* p : points) delete p; for (KeyFrame* k : keyframes) delete k; }
+};
+
+Frame* make_frame(World& w, const orbm_frame* f) {
+    Frame* F = new Frame();
+    w.frames.emplace_back(F);
+    F->mpORBvocabulary = NULL; F->mpORBextractorLeft = F->mpORBextractorRight = NULL; F->mTimeStamp = 0; F->mThDepth = 0;
+    F->mnId = Frame::nNextId++; F->mpReferenceKF = NULL;
+    F->N = f->N;
+    F->mvKeys.assign((const cv::KeyPoint*)f->keys, (const cv::KeyPoint*)f->keys + f->N);
+    F->mvKeysUn.assign((const cv::KeyPoint*)f->keysUn, (const cv::KeyPoint*)f->keysUn + f->N);
+    F->mDescriptors.create(f->N, 32, CV_8U);
+    if (f->N) std::memcpy(F->mDescriptors.data, f->descriptors, (size_t)f->N * 32);
+    if (f->uRight) F->mvuRight.assign(f->uRight, f->uRight + f->N); else F->mvuRight.assign(f->N, -1.0f);
+    F->mvDepth.assign(f->N, -1.0f);
+    F->mvpMapPoints.assign(f->N, static_cast<MapPoint*>(NULL));
+    F->mvbOutlier.assign(f->N, false);
+    Frame::mnMinX = f->mnMinX; Frame::mnMaxX = f->mnMaxX; Frame::mnMinY = f->mnMinY; Frame::mnMaxY = f->mnMaxY;
+    Frame::mfGridElementWidthInv = f->gridElementWidthInv; Frame::mfGridElementHeightInv = f->gridElementHeightInv;
+    Frame::fx = f->fx; Frame::fy = f->fy; Frame::cx = f->cx; Frame::cy = f->cy;
+    Frame::invfx = 1.0f / f->fx; Frame::invfy = 1.0f / f->fy;
+    F->mbf = f->bf; F->mb = f->b;
+    F->mnScaleLevels = f->nScaleLevels;
+    F->mvScaleFactors.assign(f->scaleFactors, f->scaleFactors + f->nScaleLevels);
+    F->mfScaleFactor = f->nScaleLevels > 1 ? f->scaleFactors[1] : 1.2f;
+    F->mfLogScaleFactor = std::log(F->mfScaleFactor);
+    F->mvInvScaleFactors.resize(f->nScaleLevels); F->mvLevelSigma2.resize(f->nScaleLevels); F->mvInvLevelSigma2.resize(f->nScaleLevels);
+    for (int i = 0; i < f->nScaleLevels; i++) {
+        F->mvInvScaleFactors[i] = 1.0f / F->mvScaleFactors[i];
+        F->mvLevelSigma2[i] = F->mvScaleFactors[i] * F->mvScaleFactors[i];
+        F->mvInvLevelSigma2[i] = 1.0f / F->mvLevelSigma2[i];
+    }
+    cv::Mat Tcw(4, 4, CV_32F);
+    std::memcpy(Tcw.data, f->Tcw, 64);
+    F->SetPose(Tcw);                             // src/Frame.cc:328-340 (UpdatePoseMatrices)
+    F->AssignFeaturesToGrid();                   // src/Frame.cc:292-311
+    return F;
+}
+
+KeyFrame* g_refKF = NULL;                        // reference key frame of every synthetic MapPoint
+
+MapPoint* make_point(World& w, const orbm_mappoint& s) {
+    if (!s.valid) return NULL;
+    cv::Mat pos(3, 1, CV_32F);
+    for (int k = 0; k < 3; k++) pos.at<float>(k) = s.world[k];
+    MapPoint* p = new MapPoint(pos, g_refKF, &w.map);        // src/MapPoint.cc:32-44
+    w.points.push_back(p);
+    p->mDescriptor.create(1, 32, CV_8U);
+    std::memcpy(p->mDescriptor.data, s.descriptor, 32);
+    p->nObs = s.observations; p->mbBad = s.bad != 0;
+    p->mbTrackInView = s.trackInView != 0; p->mTrackProjX = s.trackProjX; p->mTrackProjY = s.trackProjY; p->mTrackProjXR = s.trackProjXR;
+    p->mTrackViewCos = s.trackViewCos; p->mnTrackScaleLevel = s.trackScaleLevel;
+    return p;
+}
+
+MapPoint* make_plain_point(World& w, int nObs, bool bad) {
+    orbm_mappoint s;
+    std::memset(&s, 0, sizeof s);
+    s.valid = 1; s.observations = nObs; s.bad = bad;
+    return make_point(w, s);
+}
+
+struct RefKFGuard {                              // a KeyFrame built from an empty Frame, for MapPoint's constructor
+    World& w;
+    explicit RefKFGuard(World& w_) : w(w_) {
+        static const float sf[1] = {1.0f};
+        orbm_frame e;
+        std::memset(&e, 0, sizeof e);
+        e.mnMaxX = 1; e.mnMaxY = 1; e.gridElementWidthInv = 64; e.gridElementHeightInv = 48; e.fx = e.fy = 1; e.scaleFactors = sf; e.nScaleLevels = 1;
+        e.Tcw[0] = e.Tcw[5] = e.Tcw[10] = e.Tcw[15] = 1;
+        const float sMinX = Frame::mnMinX, sMaxX = Frame::mnMaxX, sMinY = Frame::mnMinY, sMaxY = Frame::mnMaxY;
+        Frame* F = make_frame(w, &e);
+        g_refKF = new KeyFrame(*F, &w.map, NULL);
+        w.keyframes.push_back(g_refKF);
+        Frame::mnMinX = sMinX; Frame::mnMaxX = sMaxX; Frame::mnMinY = sMinY; Frame::mnMaxY = sMaxY;
+    }
+    ~RefKFGuard() { g_refKF = NULL; }
+};
+
+void set_featvec(DBoW2::FeatureVector& out, const orbm_featvec* fv) {
+    out.clear();
+    if (!fv) return;
+    for (int k = 0; k < fv->nnodes; k++)
+        for (int t = fv->start[k]; t < fv->start[k + 1]; t++) out.addFeature(fv->node_ids[k], fv->items[t]);
+}
+
+// a Frame that only carries descriptors, angles (mvKeys and mvKeysUn) and a feature vector
+Frame* make_bow_frame(World& w, const uint8_t* desc, const float* angle, int n, const orbm_featvec* fv) {
+    static const float sf[1] = {1.0f};
+    std::vector<orbx_keypoint> keys((size_t)n);
+    for (int i = 0; i < n; i++) { std::memset(&keys[i], 0, sizeof(orbx_keypoint)); keys[i].angle = angle[i]; keys[i].class_id = -1; }
+    orbm_frame e;
+    std::memset(&e, 0, sizeof e);
+    e.N = n; e.keys = keys.data(); e.keysUn = keys.data(); e.descriptors = desc;
+    e.mnMaxX = 1; e.mnMaxY = 1; e.gridElementWidthInv = 64; e.gridElementHeightInv = 48; e.fx = e.fy = 1; e.scaleFactors = sf; e.nScaleLevels = 1;
+    e.Tcw[0] = e.Tcw[5] = e.Tcw[10] = e.Tcw[15] = 1;
+    Frame* F = make_frame(w, &e);
+    set_featvec(F->mFeatVec, fv);
+    return F;
+}
+
+}  // namespace
+
+extern "C" {
+
+void orbref_grid_build(const orbm_frame* f, int32_t* cell_start, int32_t* items) {
+    World w;
+    Frame* F = make_frame(w, f);
+    int n = 0;
+    for (int ix = 0; ix < FRAME_GRID_COLS; ix++)
+        for (int iy = 0; iy < FRAME_GRID_ROWS; iy++) {
+            cell_start[ix * FRAME_GRID_ROWS + iy] = n;
+            for (size_t v : F->mGrid[ix][iy]) items[n++] = (int32_t)v;
+        }
+    cell_start[FRAME_GRID_COLS * FRAME_GRID_ROWS] = n;
+}
+
+int orbref_features_in_area(const orbm_frame* f, float x, float y, float r, int minLevel, int maxLevel, int32_t* out, int cap) {
+    World w;
+    Frame* F = make_frame(w, f);
+    std::vector<size_t> v = F->GetFeaturesInArea(x, y, r, minLevel, maxLevel);      // src/Frame.cc:410-495
+    for (size_t i = 0; i < v.size() && (int)i < cap; i++) out[i] = (int32_t)v[i];
+    return (int)v.size();
+}
+
+int orbref_search_for_initialization(const orbm_frame* f1, const orbm_frame* f2, float* prev, int32_t* vnMatches12, int windowSize,
+                                     float mfNNratio, int mbCheckOrientation) {
+    World w;
+    Frame* F1 = make_frame(w, f1);
+    Frame* F2 = make_frame(w, f2);
+    std::vector<cv::Point2f> vbPrevMatched((size_t)f1->N);
+    for (int i = 0; i < f1->N; i++) vbPrevMatched[i] = cv::Point2f(prev[2 * i], prev[2 * i + 1]);
+    std::vector<int> m12;
+    ORBmatcher matcher(mfNNratio, mbCheckOrientation != 0);
+    const int n = matcher.SearchForInitialization(*F1, *F2, vbPrevMatched, m12, windowSize);   // src/ORBmatcher.cc:417-588
+    for (int i = 0; i < f1->N; i++) { vnMatches12[i] = m12[i]; prev[2 * i] = vbPrevMatched[i].x; prev[2 * i + 1] = vbPrevMatched[i].y; }
+    return n;
+}
+
+int orbref_search_by_projection_frame(const orbm_frame* c, const orbm_frame* l, const orbm_mappoint* lp, const int32_t* curObs, float th,
+                                      int bMono, int checkOri, int32_t* curAssign) {
+    World w;
+    RefKFGuard g(w);
+    Frame* C = make_frame(w, c);
+    Frame* L = make_frame(w, l);
+    std::map<MapPoint*, int> lastIndex;
+    for (int i = 0; i < l->N; i++) {
+        L->mvpMapPoints[i] = make_point(w, lp[i]);
+        L->mvbOutlier[i] = lp[i].outlier != 0;
+        if (L->mvpMapPoints[i]) lastIndex[L->mvpMapPoints[i]] = i;
+    }
+    std::vector<MapPoint*> before((size_t)c->N, static_cast<MapPoint*>(NULL));
+    for (int i = 0; i < c->N; i++)
+        if (curObs[i] >= 0) before[i] = C->mvpMapPoints[i] = make_plain_point(w, curObs[i], false);
+    ORBmatcher matcher(0.9f, checkOri != 0);
+    const int n = matcher.SearchByProjection(*C, *L, th, bMono != 0);                // src/ORBmatcher.cc:1396-1538
+    for (int i = 0; i < c->N; i++) {
+        MapPoint* p = C->mvpMapPoints[i];
+        if (p == before[i]) curAssign[i] = -2;
+        else if (!p) curAssign[i] = -1;
+        else curAssign[i] = lastIndex.at(p);
+    }
+    return n;
+}
+
+int orbref_search_by_projection_points(const orbm_frame* f, const orbm_mappoint* pts, int npts, const int32_t* frameObs, float th,
+                                       float mfNNratio, int32_t* frameAssign) {
+    World w;
+    RefKFGuard g(w);
+    Frame* F = make_frame(w, f);
+    std::vector<MapPoint*> vp((size_t)npts);
+    std::map<MapPoint*, int> index;
+    for (int i = 0; i < npts; i++) { vp[i] = make_point(w, pts[i]); if (vp[i]) index[vp[i]] = i; }
+    std::vector<MapPoint*> before((size_t)f->N, static_cast<MapPoint*>(NULL));
+    for (int i = 0; i < f->N; i++)
+        if (frameObs[i] >= 0) before[i] = F->mvpMapPoints[i] = make_plain_point(w, frameObs[i], false);
+    ORBmatcher matcher(mfNNratio, true);
+    const int n = matcher.SearchByProjection(*F, vp, th);                           // src/ORBmatcher.cc:45-129
+    for (int i = 0; i < f->N; i++) {
+        MapPoint* p = F->mvpMapPoints[i];
+        frameAssign[i] = p == before[i] ? -2 : index.at(p);
+    }
+    return n;
+}
+
+int orbref_search_by_bow_kf_frame(const uint8_t* descKF, const float* angleKFun, const uint8_t* validKF, int nKF, const orbm_featvec* fvKF,
+                                  const uint8_t* descF, const float* angleF, int nF, const orbm_featvec* fvF, float mfNNratio,
+                                  int mbCheckOrientation, int32_t* vpMapPointMatches) {
+    World w;
+    RefKFGuard g(w);
+    Frame* FK = make_bow_frame(w, descKF, angleKFun, nKF, fvKF);
+    std::map<MapPoint*, int> index;
+    for (int i = 0; i < nKF; i++)
+        if (validKF[i]) { FK->mvpMapPoints[i] = make_plain_point(w, 1, false); index[FK->mvpMapPoints[i]] = i; }
+    KeyFrame* pKF = new KeyFrame(*FK, &w.map, NULL);
+    w.keyframes.push_back(pKF);
+    Frame* F = make_bow_frame(w, descF, angleF, nF, fvF);
+    std::vector<MapPoint*> matches;
+    ORBmatcher matcher(mfNNratio, mbCheckOrientation != 0);
+    const int n = matcher.SearchByBoW(pKF, *F, matches);                            // src/ORBmatcher.cc:159-288
+    for (int i = 0; i < nF; i++) vpMapPointMatches[i] = matches[i] ? index.at(matches[i]) : -1;
+    return n;
+}
+
+int orbref_search_by_bow_kf_kf(const uint8_t* desc1, const float* angle1, const uint8_t* valid1, int n1, const orbm_featvec* fv1,
+                               const uint8_t* desc2, const float* angle2, const uint8_t* valid2, int n2, const orbm_featvec* fv2,
+                               float mfNNratio, int mbCheckOrientation, int32_t* vpMatches12) {
+    World w;
+    RefKFGuard g(w);
+    Frame* A = make_bow_frame(w, desc1, angle1, n1, fv1);
+    Frame* B = make_bow_frame(w, desc2, angle2, n2, fv2);
+    for (int i = 0; i < n1; i++) if (valid1[i]) A->mvpMapPoints[i] = make_plain_point(w, 1, false);
+    std::map<MapPoint*, int> index2;
+    for (int i = 0; i < n2; i++) if (valid2[i]) { B->mvpMapPoints[i] = make_plain_point(w, 1, false); index2[B->mvpMapPoints[i]] = i; }
+    KeyFrame* pKF1 = new KeyFrame(*A, &w.map, NULL);
+    KeyFrame* pKF2 = new KeyFrame(*B, &w.map, NULL);
+    w.keyframes.push_back(pKF1); w.keyframes.push_back(pKF2);
+    std::vector<MapPoint*> m12;
+    ORBmatcher matcher(mfNNratio, mbCheckOrientation != 0);
+    const int n = matcher.SearchByBoW(pKF1, pKF2, m12);                             // src/ORBmatcher.cc:590-723
+    for (int i = 0; i < n1; i++) vpMatches12[i] = m12[i] ? index2.at(m12[i]) : -1;
+    return n;
+}
+
+// MapPoint::ComputeDistinctiveDescriptors (src/MapPoint.cc:241-306): point p is observed by one key frame per
+// descriptor of its list.  std::map<KeyFrame*,size_t> iterates in pointer order, so order[] returns, per point, the
+// list position of the k-th observation in map order (the caller feeds the restatement the list in that order);
+// chosen receives the 32 bytes the reference stored in mDescriptor, has[p] = 0 when it returned early.
+void orbref_distinctive_descriptors(const uint8_t* desc, const int32_t* start, int npoints, uint8_t* chosen, uint8_t* has, int32_t* order) {
+    World w;
+    RefKFGuard g(w);
+    static const float zero = 0;
+    for (int p = 0; p < npoints; p++) {
+        const int n = start[p + 1] - start[p];
+        MapPoint* mp = make_plain_point(w, 0, false);
+        std::map<KeyFrame*, int> listPos;
+        for (int o = 0; o < n; o++) {
+            Frame* F = make_bow_frame(w, desc + (size_t)(start[p] + o) * 32, &zero, 1, NULL);
+            KeyFrame* kf = new KeyFrame(*F, &w.map, NULL);
+            w.keyframes.push_back(kf);
+            mp->AddObservation(kf, 0);
+            listPos[kf] = o;
+        }
+        int k = 0;
+        for (std::map<KeyFrame*, size_t>::iterator it = mp->mObservations.begin(); it != mp->mObservations.end(); ++it, ++k)
+            order[start[p] + k] = listPos[it->first];
+        mp->mDescriptor.release();
+        mp->ComputeDistinctiveDescriptors();
+        has[p] = !mp->mDescriptor.empty();
+        if (has[p]) std::memcpy(chosen + (size_t)p * 32, mp->mDescriptor.data, 32);
+    }
+}
+
+}  // extern "C"

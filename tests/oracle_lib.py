@@ -460,3 +460,49 @@ class RefVocabulary:
 
     def transform(self, desc, levelsup=4):
         return _flat_transform(self._L.refvoc_transform, self._h, desc, levelsup)
+
+
+# ---------------- the reference's own ORBmatcher.cc / Frame.cc / KeyFrame.cc / MapPoint.cc (oracle/_ref/liborbmatcher_ref.so)
+MATCHER_REF_SO = os.path.join(ROOT, "oracle", "_ref", "liborbmatcher_ref.so")
+_matcher_ref = None
+
+
+def have_matcher_ref() -> bool:
+    return os.path.exists(MATCHER_REF_SO)
+
+
+class _RefProxy:
+    """Looks up orbo_X as orbref_X in the reference build, with the oracle's argtypes (the signatures are identical)."""
+
+    def __init__(self):
+        global _matcher_ref
+        if _matcher_ref is None:
+            _matcher_ref = C.CDLL(MATCHER_REF_SO)
+        self._ref, self._oracle = _matcher_ref, _bind_matcher(oracle())
+
+    def __getattr__(self, name):
+        fn = getattr(self._ref, name.replace("orbo_", "orbref_"))      # AttributeError when the wrapper lacks it
+        fn.argtypes = getattr(self._oracle, name).argtypes
+        return fn
+
+
+class RefMatcher(OracleMatcher):
+    """Same call shape as OracleMatcher, executed by the reference's own object code."""
+
+    def __init__(self, nnratio=0.6, checkOri=True):
+        self.L = _RefProxy()
+        self.nnratio = float(np.float32(nnratio)); self.checkOri = bool(checkOri)
+
+
+def ref_distinctive_descriptors(desc, start):
+    """MapPoint::ComputeDistinctiveDescriptors of the reference build: (chosen descriptor bytes, has flag, observation order)."""
+    global _matcher_ref
+    if _matcher_ref is None:
+        _matcher_ref = C.CDLL(MATCHER_REF_SO)
+    d = np.ascontiguousarray(desc, np.uint8).reshape(-1, 32); start = np.ascontiguousarray(start, np.int32)
+    npts = len(start) - 1
+    chosen = np.zeros((max(npts, 1), 32), np.uint8); has = np.zeros(max(npts, 1), np.uint8); order = np.zeros(max(len(d), 1), np.int32)
+    vp = C.c_void_p
+    _matcher_ref.orbref_distinctive_descriptors.argtypes = [vp, vp, C.c_int, vp, vp, vp]
+    _matcher_ref.orbref_distinctive_descriptors(d.ctypes.data, start.ctypes.data, npts, chosen.ctypes.data, has.ctypes.data, order.ctypes.data)
+    return chosen[:npts], has[:npts], order[:len(d)]
