@@ -316,4 +316,43 @@ void orbref_distinctive_descriptors(const uint8_t* desc, const int32_t* start, i
     }
 }
 
+
+// Frame::ComputeStereoMatches (src/Frame.cc:630-872) by the reference's own code on two reference ORBextractors that
+// have just extracted the left / right image (as the stereo Frame constructor does, :88-110).  Returns what the
+// restatement needs to repeat the call on identical inputs: both key point sets, descriptors and the pyramid levels
+// (levels: per image the w_l x h_l level images concatenated; dims: nlevels x (w, h)).  cap = capacity in key points.
+int orbref_compute_stereo_matches(const uint8_t* imgL, const uint8_t* imgR, int wI, int hI, int nfeatures, float scaleFactor, int nlevels,
+                                  int iniTh, int minTh, float mbf, float mb, int cap, orbx_keypoint* keysL, uint8_t* descL, int* nL,
+                                  orbx_keypoint* keysR, uint8_t* descR, int* nR, uint8_t* levelsL, uint8_t* levelsR, int* dims,
+                                  float* mvuRight, float* mvDepth) {
+    ORBextractor exL(nfeatures, scaleFactor, nlevels, iniTh, minTh), exR(nfeatures, scaleFactor, nlevels, iniTh, minTh);
+    World w;
+    Frame* F = new Frame();
+    w.frames.emplace_back(F);
+    F->mpORBextractorLeft = &exL; F->mpORBextractorRight = &exR;
+    cv::Mat imL(hI, wI, CV_8UC1, (void*)imgL), imR(hI, wI, CV_8UC1, (void*)imgR);
+    F->ExtractORB(0, imL);                          // src/Frame.cc:320-326
+    F->ExtractORB(1, imR);
+    F->N = (int)F->mvKeys.size();
+    F->mvScaleFactors = exL.GetScaleFactors(); F->mvInvScaleFactors = exL.GetInverseScaleFactors();
+    F->mnScaleLevels = nlevels;
+    F->mbf = mbf; F->mb = mb;
+    const int NR = (int)F->mvKeysRight.size();
+    if (F->N > cap || NR > cap) return -1;
+    F->ComputeStereoMatches();
+    *nL = F->N; *nR = NR;
+    std::memcpy(keysL, F->mvKeys.data(), (size_t)F->N * sizeof(orbx_keypoint));
+    std::memcpy(keysR, F->mvKeysRight.data(), (size_t)NR * sizeof(orbx_keypoint));
+    for (int i = 0; i < F->N; i++) std::memcpy(descL + (size_t)i * 32, F->mDescriptors.ptr(i), 32);
+    for (int i = 0; i < NR; i++) std::memcpy(descR + (size_t)i * 32, F->mDescriptorsRight.ptr(i), 32);
+    size_t off = 0;
+    for (int l = 0; l < nlevels; l++) {
+        const cv::Mat& a = exL.mvImagePyramid[l]; const cv::Mat& b = exR.mvImagePyramid[l];
+        dims[2 * l] = a.cols; dims[2 * l + 1] = a.rows;
+        for (int y = 0; y < a.rows; y++) { std::memcpy(levelsL + off, a.ptr(y), a.cols); std::memcpy(levelsR + off, b.ptr(y), a.cols); off += a.cols; }
+    }
+    for (int i = 0; i < F->N; i++) { mvuRight[i] = F->mvuRight[i]; mvDepth[i] = F->mvDepth[i]; }
+    return 0;
+}
+
 }  // extern "C"

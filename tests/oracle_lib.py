@@ -506,3 +506,52 @@ def ref_distinctive_descriptors(desc, start):
     _matcher_ref.orbref_distinctive_descriptors.argtypes = [vp, vp, C.c_int, vp, vp, vp]
     _matcher_ref.orbref_distinctive_descriptors(d.ctypes.data, start.ctypes.data, npts, chosen.ctypes.data, has.ctypes.data, order.ctypes.data)
     return chosen[:npts], has[:npts], order[:len(d)]
+
+
+def ref_stereo(imgL, imgR, nfeatures, scaleFactor, nlevels, iniTh, minTh, mbf, mb):
+    """Reference extraction of both images + the reference's own Frame::ComputeStereoMatches.
+    Returns (kL, dL, kR, dR, levelsL, levelsR, mvuRight, mvDepth); levels are lists of (h_l, w_l) arrays."""
+    global _matcher_ref
+    if _matcher_ref is None:
+        _matcher_ref = C.CDLL(MATCHER_REF_SO)
+    imgL = np.ascontiguousarray(imgL, np.uint8); imgR = np.ascontiguousarray(imgR, np.uint8)
+    h, w = imgL.shape
+    cap = nfeatures * 2 + 64
+    kL = np.zeros(cap, KP); kR = np.zeros(cap, KP); dL = np.zeros((cap, 32), np.uint8); dR = np.zeros((cap, 32), np.uint8)
+    lvL = np.zeros(w * h * 4, np.uint8); lvR = np.zeros(w * h * 4, np.uint8); dims = np.zeros(2 * nlevels, np.int32)
+    u = np.zeros(cap, np.float32); z = np.zeros(cap, np.float32)
+    nL, nR = C.c_int(), C.c_int()
+    vp, i, f = C.c_void_p, C.c_int, C.c_float
+    fn = _matcher_ref.orbref_compute_stereo_matches
+    fn.argtypes = [vp, vp, i, i, i, f, i, i, i, f, f, i, vp, vp, C.POINTER(i), vp, vp, C.POINTER(i), vp, vp, vp, vp, vp]
+    rc = fn(imgL.ctypes.data, imgR.ctypes.data, w, h, nfeatures, scaleFactor, nlevels, iniTh, minTh, mbf, mb, cap, kL.ctypes.data,
+            dL.ctypes.data, C.byref(nL), kR.ctypes.data, dR.ctypes.data, C.byref(nR), lvL.ctypes.data, lvR.ctypes.data, dims.ctypes.data,
+            u.ctypes.data, z.ctypes.data)
+    assert rc == 0
+    levelsL, levelsR, off = [], [], 0
+    for l in range(nlevels):
+        wl, hl = int(dims[2 * l]), int(dims[2 * l + 1])
+        levelsL.append(lvL[off:off + wl * hl].reshape(hl, wl).copy()); levelsR.append(lvR[off:off + wl * hl].reshape(hl, wl).copy())
+        off += wl * hl
+    return kL[:nL.value], dL[:nL.value], kR[:nR.value], dR[:nR.value], levelsL, levelsR, u[:nL.value], z[:nL.value]
+
+
+def oracle_stereo_matches_on_levels(kL, dL, kR, dR, levelsL, levelsR, scale_factors, mbf, mb):
+    """orbo_compute_stereo_matches on explicit (unbordered) level images."""
+    L = oracle()
+    n = len(levelsL)
+    levelsL = [np.ascontiguousarray(a) for a in levelsL]; levelsR = [np.ascontiguousarray(a) for a in levelsR]
+    pL = (C.c_void_p * n)(*[a.ctypes.data for a in levelsL]); pR = (C.c_void_p * n)(*[a.ctypes.data for a in levelsR])
+    sL = (C.c_size_t * n)(*[a.strides[0] for a in levelsL]); sR = (C.c_size_t * n)(*[a.strides[0] for a in levelsR])
+    cols = (C.c_int * n)(*[a.shape[1] for a in levelsL])
+    sf = np.ascontiguousarray(scale_factors, np.float32); isf = (np.float32(1.0) / sf).astype(np.float32)
+    kL = np.ascontiguousarray(kL, KP); kR = np.ascontiguousarray(kR, KP)
+    dL = np.ascontiguousarray(dL, np.uint8); dR = np.ascontiguousarray(dR, np.uint8)
+    u = np.zeros(len(kL), np.float32); z = np.zeros(len(kL), np.float32)
+    L.orbo_compute_stereo_matches.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p,
+                                              C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                              C.c_int, C.c_float, C.c_float, C.c_void_p, C.c_void_p]
+    kept = L.orbo_compute_stereo_matches(kL.ctypes.data, len(kL), dL.ctypes.data, kR.ctypes.data, len(kR), dR.ctypes.data,
+                                         sf.ctypes.data, isf.ctypes.data, n, pL, pR, sL, sR, cols, levelsL[0].shape[0],
+                                         mbf, mb, u.ctypes.data, z.ctypes.data)
+    return u, z, kept

@@ -101,3 +101,17 @@ def test_distinctive_descriptors():
         assert bool(has[p]) == (best[p] >= 0)
         if best[p] >= 0:
             assert np.array_equal(Dp[start[p] + best[p]], chosen[p]), p
+
+
+@pytest.mark.parametrize("w,h,nf,disp,seed", [(752, 480, 1000, 14, 3), (1241, 376, 2000, 23, 4), (640, 480, 800, 5, 6)])
+def test_compute_stereo_matches(w, h, nf, disp, seed):
+    """Frame::ComputeStereoMatches: the reference's own Frame.cc on reference-extracted key points and pyramids against the
+    restatement (oracle/orb_oracle_stereo.cc) on the same key points and pyramid levels."""
+    from orb_slam_b200.synth import synth_frame
+    from tests.oracle_lib import oracle_stereo_matches_on_levels, ref_stereo
+    left, right = synth_frame(w, h, seed), synth_frame(w, h, seed, shift=(-disp, 0))
+    mbf, mb = 386.1448, 0.5371
+    kL, dL, kR, dR, lvL, lvR, u_r, z_r = ref_stereo(left, right, nf, 1.2, 8, 20, 7, mbf, mb)
+    u_o, z_o, kept = oracle_stereo_matches_on_levels(kL, dL, kR, dR, lvL, lvR, scenes.scale_factors(8, 1.2), mbf, mb)
+    assert (u_r >= 0).sum() > 0.4 * len(kL) and kept == (u_r >= 0).sum()
+    assert np.array_equal(u_o, u_r) and np.array_equal(z_o, z_r)
