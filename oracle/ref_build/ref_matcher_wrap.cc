@@ -166,6 +166,13 @@ Frame* make_bow_frame(World& w, const uint8_t* desc, const float* angle, int n, 
 
 }  // namespace
 
+namespace {
+void set_distances(MapPoint* p, const float* minMaxDistance, int i) {
+    if (p) { p->mfMinDistance = minMaxDistance[2 * i]; p->mfMaxDistance = minMaxDistance[2 * i + 1]; }
+}
+template <typename T> void assign_const(const std::vector<T>& dst, const T* src, int n) { const_cast<std::vector<T>&>(dst).assign(src, src + n); }
+}  // namespace
+
 extern "C" {
 
 void orbref_grid_build(const orbm_frame* f, int32_t* cell_start, int32_t* items) {
@@ -353,6 +360,263 @@ int orbref_compute_stereo_matches(const uint8_t* imgL, const uint8_t* imgR, int 
     }
     for (int i = 0; i < F->N; i++) { mvuRight[i] = F->mvuRight[i]; mvDepth[i] = F->mvDepth[i]; }
     return 0;
+}
+
+
+
+// ORBmatcher::SearchByProjection(CurrentFrame, pKF, sAlreadyFound, th, ORBdist), src/ORBmatcher.cc:1540-1667
+int orbref_search_by_projection_keyframe(const orbm_frame* c, const orbm_mappoint* vpMPs, int n, const float* minMaxDistance,
+                                         float mfLogScaleFactor, const uint8_t* sAlreadyFound, const float* kfAngle,
+                                         const uint8_t* curHasPoint, float th, int ORBdist, int checkOri, int32_t* curAssign) {
+    World w;
+    RefKFGuard g(w);
+    std::vector<uint8_t> zero((size_t)n * 32, 0);
+    Frame* K = make_bow_frame(w, zero.data(), kfAngle, n, NULL);
+    Frame* Cf = make_frame(w, c);                   // last: the Frame statics (bounds, intrinsics, grid scale) are the current frame's
+    Cf->mfLogScaleFactor = mfLogScaleFactor;
+    std::map<MapPoint*, int> index;
+    std::set<MapPoint*> found;
+    for (int i = 0; i < n; i++) {
+        MapPoint* p = K->mvpMapPoints[i] = make_point(w, vpMPs[i]);
+        set_distances(p, minMaxDistance, i);
+        if (p) { index[p] = i; if (sAlreadyFound[i]) found.insert(p); }
+    }
+    KeyFrame* pKF = new KeyFrame(*K, &w.map, NULL);
+    w.keyframes.push_back(pKF);
+    std::vector<MapPoint*> before((size_t)c->N, static_cast<MapPoint*>(NULL));
+    for (int i = 0; i < c->N; i++) if (curHasPoint[i]) before[i] = Cf->mvpMapPoints[i] = make_plain_point(w, 1, false);
+    ORBmatcher matcher(0.9f, checkOri != 0);
+    const int nm = matcher.SearchByProjection(*Cf, pKF, found, th, ORBdist);
+    for (int i = 0; i < c->N; i++) {
+        MapPoint* p = Cf->mvpMapPoints[i];
+        curAssign[i] = p == before[i] ? -2 : (p ? index.at(p) : -1);
+    }
+    return nm;
+}
+
+// ORBmatcher::Fuse(pKF, vpMapPoints, th), src/ORBmatcher.cc:893-1040.  The key frame starts without map points; a fused
+// point ends up observed by pKF at bestIdx, either itself or - when two points chose the same key point and one replaced
+// the other (MapPoint::Replace) - through the survivor of its replacement chain.  Returns nFused.
+int orbref_fuse_select(const orbm_frame* kf, const float* cameraCenter, const float* mvInvLevelSigma2, const orbm_mappoint* vpMapPoints,
+                       int nMPs, const uint8_t* inKeyFrame, const float* normals, const float* minMaxDistance, float mfLogScaleFactor,
+                       float th, int32_t* bestIdxOut) {
+    World w;
+    RefKFGuard g(w);
+    Frame* K = make_frame(w, kf);
+    K->mfLogScaleFactor = mfLogScaleFactor;
+    KeyFrame* pKF = new KeyFrame(*K, &w.map, NULL);
+    w.keyframes.push_back(pKF);
+    assign_const(pKF->mvInvLevelSigma2, mvInvLevelSigma2, kf->nScaleLevels);
+    if (cameraCenter) for (int k = 0; k < 3; k++) pKF->Ow.at<float>(k) = cameraCenter[k];
+    std::vector<MapPoint*> vp((size_t)nMPs);
+    for (int i = 0; i < nMPs; i++) {
+        MapPoint* p = vp[i] = make_point(w, vpMapPoints[i]);
+        set_distances(p, minMaxDistance, i);
+        if (!p) continue;
+        for (int k = 0; k < 3; k++) p->mNormalVector.at<float>(k) = normals[3 * i + k];
+        if (inKeyFrame[i]) p->mObservations[pKF] = 0;          // IsInKeyFrame(pKF) without occupying a key point
+    }
+    ORBmatcher matcher(0.6f, true);
+    const int nFused = matcher.Fuse(pKF, vp, th);
+    for (int i = 0; i < nMPs; i++) {
+        bestIdxOut[i] = -1;
+        MapPoint* p = vp[i];
+        if (!p || inKeyFrame[i] || vpMapPoints[i].bad) continue;
+        while (p->mpReplaced) p = p->mpReplaced;
+        bestIdxOut[i] = p->GetIndexInKeyFrame(pKF);
+    }
+    return nFused;
+}
+
+// ORBmatcher::SearchForTriangulation(pKF1, pKF2, F12, vMatchedPairs, bOnlyStereo), src/ORBmatcher.cc:725-891
+int orbref_search_for_triangulation(const orbm_keyframe* k1, const orbm_keyframe* k2, const float* Cw, const float* R2w, const float* t2w,
+                                    float fx, float fy, float cx, float cy, const float* mvScaleFactors, const float* mvLevelSigma2,
+                                    const float* F12, int bOnlyStereo, int mbCheckOrientation, int32_t* vMatches12) {
+    World w;
+    RefKFGuard g(w);
+    KeyFrame* pKF[2];
+    const orbm_keyframe* src[2] = {k1, k2};
+    for (int s = 0; s < 2; s++) {
+        const orbm_keyframe* k = src[s];
+        static const float one[8] = {1, 1, 1, 1, 1, 1, 1, 1};
+        orbm_frame e;
+        std::memset(&e, 0, sizeof e);
+        e.N = k->N; e.keys = k->keysUn; e.keysUn = k->keysUn; e.descriptors = k->descriptors; e.uRight = k->uRight;
+        e.mnMaxX = 1; e.mnMaxY = 1; e.gridElementWidthInv = 64; e.gridElementHeightInv = 48;
+        e.fx = fx; e.fy = fy; e.cx = cx; e.cy = cy; e.scaleFactors = one; e.nScaleLevels = 8;
+        e.Tcw[0] = e.Tcw[5] = e.Tcw[10] = e.Tcw[15] = 1;
+        if (s == 1) for (int r = 0; r < 3; r++) { for (int q = 0; q < 3; q++) e.Tcw[4 * r + q] = R2w[3 * r + q]; e.Tcw[4 * r + 3] = t2w[r]; }
+        Frame* F = make_frame(w, &e);
+        set_featvec(F->mFeatVec, k->featvec);
+        for (int i = 0; i < k->N; i++) if (k->has_point[i]) F->mvpMapPoints[i] = make_plain_point(w, 1, false);
+        pKF[s] = new KeyFrame(*F, &w.map, NULL);
+        w.keyframes.push_back(pKF[s]);
+    }
+    for (int k = 0; k < 3; k++) pKF[0]->Ow.at<float>(k) = Cw[k];
+    int nl = 0;
+    for (int i = 0; i < k2->N; i++) nl = std::max(nl, k2->keysUn[i].octave + 1);
+    for (int i = 0; i < k1->N; i++) nl = std::max(nl, k1->keysUn[i].octave + 1);
+    assign_const(pKF[1]->mvScaleFactors, mvScaleFactors, nl);
+    assign_const(pKF[1]->mvLevelSigma2, mvLevelSigma2, nl);
+    cv::Mat F(3, 3, CV_32F);
+    std::memcpy(F.data, F12, 36);
+    std::vector<std::pair<size_t, size_t> > pairs;
+    ORBmatcher matcher(0.6f, mbCheckOrientation != 0);
+    const int n = matcher.SearchForTriangulation(pKF[0], pKF[1], F, pairs, bOnlyStereo != 0);
+    for (int i = 0; i < k1->N; i++) vMatches12[i] = -1;
+    for (size_t i = 0; i < pairs.size(); i++) vMatches12[pairs[i].first] = (int32_t)pairs[i].second;
+    return n;
+}
+
+
+// The decomposition of Scw both Sim3 functions start with (src/ORBmatcher.cc:299-303, :1052-1056), evaluated with the same
+// matrix algebra the reference build uses, so a test can hand the restatement exactly what the reference computed inside.
+void orbref_decompose_scw(const float* Scw16, float* RcwOut, float* tcwOut, float* OwOut) {
+    cv::Mat Scw(4, 4, CV_32F);
+    std::memcpy(Scw.data, Scw16, 64);
+    cv::Mat sRcw = Scw.rowRange(0, 3).colRange(0, 3);
+    const float scw = sqrt(sRcw.row(0).dot(sRcw.row(0)));
+    cv::Mat Rcw = sRcw / scw;
+    cv::Mat tcw = Scw.rowRange(0, 3).col(3) / scw;
+    cv::Mat Ow = -Rcw.t() * tcw;
+    for (int r = 0; r < 3; r++) { for (int c = 0; c < 3; c++) RcwOut[3 * r + c] = Rcw.at<float>(r, c); tcwOut[r] = tcw.at<float>(r); OwOut[r] = Ow.at<float>(r); }
+}
+
+namespace {
+struct Sim3Points {
+    std::vector<MapPoint*> vp;
+    std::map<MapPoint*, int> index;
+};
+Sim3Points make_sim3_points(World& w, const orbm_mappoint* pts, int n, const float* normals, const float* minMaxDistance) {
+    Sim3Points r;
+    r.vp.resize((size_t)n);
+    for (int i = 0; i < n; i++) {
+        MapPoint* p = r.vp[i] = make_point(w, pts[i]);
+        if (!p) continue;
+        set_distances(p, minMaxDistance, i);
+        if (normals) for (int k = 0; k < 3; k++) p->mNormalVector.at<float>(k) = normals[3 * i + k];
+        r.index[p] = i;
+    }
+    return r;
+}
+}  // namespace
+
+// ORBmatcher::SearchByProjection(pKF, Scw, vpPoints, vpMatched, th), src/ORBmatcher.cc:290-403.  excluded[i] = isBad() ||
+// spAlreadyFound.count(pMP): the non-bad excluded points are stored in vpMatched slots flagged by matchedIn (the rest of
+// those slots hold unrelated points); excluded points that find no slot are made bad, which the function treats alike.
+int orbref_search_by_projection_sim3(const orbm_frame* kf, const float* Scw16, const orbm_mappoint* vpPoints, int n, const uint8_t* excluded,
+                                     const float* normals, const float* minMaxDistance, float mfLogScaleFactor, const uint8_t* matchedIn,
+                                     int th, int32_t* match) {
+    World w;
+    RefKFGuard g(w);
+    Frame* K = make_frame(w, kf);
+    K->mfLogScaleFactor = mfLogScaleFactor;
+    KeyFrame* pKF = new KeyFrame(*K, &w.map, NULL);
+    w.keyframes.push_back(pKF);
+    Sim3Points P = make_sim3_points(w, vpPoints, n, normals, minMaxDistance);
+    std::vector<MapPoint*> vpMatched((size_t)kf->N, static_cast<MapPoint*>(NULL));
+    int slot = 0;
+    for (int i = 0; i < n; i++) {
+        if (!excluded[i] || vpPoints[i].bad) continue;
+        while (slot < kf->N && !matchedIn[slot]) slot++;
+        if (slot < kf->N) vpMatched[slot++] = P.vp[i]; else P.vp[i]->mbBad = true;
+    }
+    for (int i = 0; i < kf->N; i++) if (matchedIn[i] && !vpMatched[i]) vpMatched[i] = make_plain_point(w, 1, false);
+    const std::vector<MapPoint*> before = vpMatched;
+    cv::Mat Scw(4, 4, CV_32F);
+    std::memcpy(Scw.data, Scw16, 64);
+    ORBmatcher matcher(0.75f, true);
+    const int nm = matcher.SearchByProjection(pKF, Scw, P.vp, vpMatched, th);
+    for (int i = 0; i < kf->N; i++) match[i] = vpMatched[i] == before[i] ? -2 : P.index.at(vpMatched[i]);
+    return nm;
+}
+
+// ORBmatcher::Fuse(pKF, Scw, vpPoints, th, vpReplacePoint), src/ORBmatcher.cc:1044-1168.  Every key point of pKF holds a map
+// point (the non-bad excluded points first: spAlreadyFound = pKF->GetMapPoints()), so the chosen key point of point iMP is
+// the slot of vpReplacePoint[iMP].
+int orbref_fuse_select_sim3(const orbm_frame* kf, const float* Scw16, const orbm_mappoint* vpPoints, int nPoints, const uint8_t* excluded,
+                            const float* normals, const float* minMaxDistance, float mfLogScaleFactor, float th, int32_t* bestIdxOut) {
+    World w;
+    RefKFGuard g(w);
+    Frame* K = make_frame(w, kf);
+    K->mfLogScaleFactor = mfLogScaleFactor;
+    Sim3Points P = make_sim3_points(w, vpPoints, nPoints, normals, minMaxDistance);
+    std::map<MapPoint*, int> slotOf;
+    int slot = 0;
+    for (int i = 0; i < nPoints; i++) {
+        if (!excluded[i] || vpPoints[i].bad) continue;
+        if (slot < kf->N) { K->mvpMapPoints[slot] = P.vp[i]; slotOf[P.vp[i]] = slot++; } else P.vp[i]->mbBad = true;
+    }
+    for (; slot < kf->N; slot++) { K->mvpMapPoints[slot] = make_plain_point(w, 1, false); slotOf[K->mvpMapPoints[slot]] = slot; }
+    KeyFrame* pKF = new KeyFrame(*K, &w.map, NULL);
+    w.keyframes.push_back(pKF);
+    cv::Mat Scw(4, 4, CV_32F);
+    std::memcpy(Scw.data, Scw16, 64);
+    std::vector<MapPoint*> vpReplacePoint((size_t)nPoints, static_cast<MapPoint*>(NULL));
+    ORBmatcher matcher(0.75f, true);
+    const int nFused = matcher.Fuse(pKF, Scw, P.vp, th, vpReplacePoint);
+    for (int i = 0; i < nPoints; i++) bestIdxOut[i] = vpReplacePoint[i] ? slotOf.at(vpReplacePoint[i]) : -1;
+    return nFused;
+}
+
+// ORBmatcher::SearchBySim3(pKF1, pKF2, vpMatches12, s12, R12, t12, th), src/ORBmatcher.cc:1170-1394.  skipK[i] = already
+// matched || bad: the already-matched state is built through vpMatches12 (a stored point whose GetIndexInKeyFrame(pKF2)
+// names the key point of key frame 2 to block); where no slot of key frame 1 is free for that, the point is made bad,
+// which the function treats alike.
+int orbref_search_by_sim3(const orbm_frame* k1, const orbm_frame* k2, const orbm_mappoint* pts1, const orbm_mappoint* pts2, const uint8_t* skip1,
+                          const uint8_t* skip2, const float* minMax1, const float* minMax2, float logScaleFactor1, float logScaleFactor2,
+                          float s12, const float* R12, const float* t12, float th, int32_t* match12) {
+    World w;
+    RefKFGuard g(w);
+    Frame* F1 = make_frame(w, k1);
+    Frame* F2 = make_frame(w, k2);
+    F1->mfLogScaleFactor = logScaleFactor1; F2->mfLogScaleFactor = logScaleFactor2;
+    Sim3Points P1 = make_sim3_points(w, pts1, k1->N, NULL, minMax1), P2 = make_sim3_points(w, pts2, k2->N, NULL, minMax2);
+    F1->mvpMapPoints = P1.vp; F2->mvpMapPoints = P2.vp;
+    KeyFrame* pKF1 = new KeyFrame(*F1, &w.map, NULL);
+    KeyFrame* pKF2 = new KeyFrame(*F2, &w.map, NULL);
+    w.keyframes.push_back(pKF1); w.keyframes.push_back(pKF2);
+    std::vector<MapPoint*> vpMatches12((size_t)k1->N, static_cast<MapPoint*>(NULL));
+    std::vector<int> free1;                              // slots of key frame 1 that may carry an "already matched" entry
+    for (int i = 0; i < k1->N; i++) {
+        if (!skip1[i] || !P1.vp[i] || pts1[i].bad) continue;
+        vpMatches12[i] = make_plain_point(w, 1, false);  // not observed by key frame 2: GetIndexInKeyFrame = -1
+        free1.push_back(i);
+    }
+    for (int i = 0; i < k1->N; i++) if (!P1.vp[i] || pts1[i].bad) free1.push_back(i);
+    size_t used = 0;
+    for (int j = 0; j < k2->N; j++) {
+        if (!skip2[j] || !P2.vp[j] || pts2[j].bad) continue;
+        if (used < free1.size()) {
+            MapPoint* d = vpMatches12[free1[used]];
+            if (!d) d = vpMatches12[free1[used]] = make_plain_point(w, 1, false);
+            d->mObservations[pKF2] = (size_t)j;
+            used++;
+        } else P2.vp[j]->mbBad = true;
+    }
+    const std::vector<MapPoint*> before = vpMatches12;
+    cv::Mat R(3, 3, CV_32F), t(3, 1, CV_32F);
+    std::memcpy(R.data, R12, 36);
+    for (int k = 0; k < 3; k++) t.at<float>(k) = t12[k];
+    ORBmatcher matcher(0.75f, true);
+    const int nFound = matcher.SearchBySim3(pKF1, pKF2, vpMatches12, s12, R, t, th);
+    for (int i = 0; i < k1->N; i++) match12[i] = vpMatches12[i] == before[i] ? -1 : P2.index.at(vpMatches12[i]);
+    return nFound;
+}
+
+
+// The cvstub matrix algebra itself, for tests/test_cvprim_golden.py::test_mat_algebra_golden (cv2 4.13 vectors):
+// out = [A*x + c (3), A*x (3), -A.t()*x (3), (-A)*x (3), norm(x) (1)] written with the expressions the reference uses.
+void orbref_algebra_probe(const float* A9, const float* x3, const float* c3, float* out) {
+    cv::Mat A(3, 3, CV_32F), x(3, 1, CV_32F), c(3, 1, CV_32F);
+    std::memcpy(A.data, A9, 36);
+    for (int k = 0; k < 3; k++) { x.at<float>(k) = x3[k]; c.at<float>(k) = c3[k]; }
+    cv::Mat r1 = A * x + c;
+    cv::Mat r2 = A * x;
+    cv::Mat r3 = -A.t() * x;
+    cv::Mat r4 = -A * x;
+    for (int k = 0; k < 3; k++) { out[k] = r1.at<float>(k); out[3 + k] = r2.at<float>(k); out[6 + k] = r3.at<float>(k); out[9 + k] = r4.at<float>(k); }
+    out[12] = (float)cv::norm(x);
 }
 
 }  // extern "C"

@@ -258,7 +258,8 @@ class OracleMatcher:
                                                       ang.ctypes.data, has.ctypes.data, th, int(ORBdist), int(self.checkOri), out.ctypes.data)
         return n, out[: cur.N]
 
-    def FuseSelect(self, KF, inv_level_sigma2, points, in_keyframe, normals, min_max_distance, th=3.0, log_scale_factor=None):
+    def FuseSelect(self, KF, inv_level_sigma2, points, in_keyframe, normals, min_max_distance, th=3.0, log_scale_factor=None,
+                   camera_center=None):
         from orb_slam_b200.matcher import MAPPOINT_DTYPE
         p = np.ascontiguousarray(points, MAPPOINT_DTYPE); mm = np.ascontiguousarray(min_max_distance, np.float32).reshape(-1, 2)
         ik = np.ascontiguousarray(in_keyframe, np.uint8); nr = np.ascontiguousarray(normals, np.float32).reshape(-1, 3)
@@ -267,7 +268,8 @@ class OracleMatcher:
             log_scale_factor = float(np.log(np.float32(KF.mvScaleFactors[1])))
         out = np.zeros(max(len(p), 1), np.int32)
         s = KF.struct()
-        self.L.orbo_fuse_select(C.byref(s), None, sg.ctypes.data, p.ctypes.data, len(p), ik.ctypes.data, nr.ctypes.data, mm.ctypes.data,
+        cc = None if camera_center is None else np.ascontiguousarray(camera_center, np.float32)
+        self.L.orbo_fuse_select(C.byref(s), None if cc is None else cc.ctypes.data, sg.ctypes.data, p.ctypes.data, len(p), ik.ctypes.data, nr.ctypes.data, mm.ctypes.data,
                                 log_scale_factor, th, out.ctypes.data)
         return out[: len(p)]
 
@@ -555,3 +557,59 @@ def oracle_stereo_matches_on_levels(kL, dL, kR, dR, levelsL, levelsR, scale_fact
                                          sf.ctypes.data, isf.ctypes.data, n, pL, pR, sL, sR, cols, levelsL[0].shape[0],
                                          mbf, mb, u.ctypes.data, z.ctypes.data)
     return u, z, kept
+
+
+def _mref():
+    global _matcher_ref
+    if _matcher_ref is None:
+        _matcher_ref = C.CDLL(MATCHER_REF_SO)
+    return _matcher_ref
+
+
+def ref_decompose_scw(Scw):
+    S = np.ascontiguousarray(Scw, np.float32).reshape(4, 4)
+    R = np.zeros((3, 3), np.float32); t = np.zeros(3, np.float32); O = np.zeros(3, np.float32)
+    fn = _mref().orbref_decompose_scw
+    fn.argtypes = [C.c_void_p] * 4; fn.restype = None
+    fn(S.ctypes.data, R.ctypes.data, t.ctypes.data, O.ctypes.data)
+    return R, t, O
+
+
+def ref_sim3_projection(KF, Scw, points, excluded, normals, min_max_distance, matched_in, th, fuse=False):
+    """The reference's SearchByProjection(pKF, Scw, ...) (fuse=False) / Fuse(pKF, Scw, ...) (fuse=True)."""
+    from orb_slam_b200.matcher import MAPPOINT_DTYPE
+    f32 = lambda a: np.ascontiguousarray(a, np.float32)
+    S = f32(Scw).reshape(4, 4); p = np.ascontiguousarray(points, MAPPOINT_DTYPE); ex = np.ascontiguousarray(excluded, np.uint8)
+    nr = f32(normals).reshape(-1, 3); mm = f32(min_max_distance).reshape(-1, 2); s = KF.struct()
+    lsf = float(np.log(np.float32(KF.mvScaleFactors[1])))
+    vp, i, f = C.c_void_p, C.c_int, C.c_float
+    if fuse:
+        out = np.zeros(max(len(p), 1), np.int32)
+        fn = _mref().orbref_fuse_select_sim3
+        fn.argtypes = [vp, vp, vp, i, vp, vp, vp, f, f, vp]
+        n = fn(C.byref(s), S.ctypes.data, p.ctypes.data, len(p), ex.ctypes.data, nr.ctypes.data, mm.ctypes.data, lsf, float(th), out.ctypes.data)
+        return n, out[:len(p)]
+    mi = np.ascontiguousarray(matched_in, np.uint8)
+    out = np.zeros(max(KF.N, 1), np.int32)
+    fn = _mref().orbref_search_by_projection_sim3
+    fn.argtypes = [vp, vp, vp, i, vp, vp, vp, f, vp, i, vp]
+    n = fn(C.byref(s), S.ctypes.data, p.ctypes.data, len(p), ex.ctypes.data, nr.ctypes.data, mm.ctypes.data, lsf, mi.ctypes.data, int(th),
+           out.ctypes.data)
+    return n, out[:KF.N]
+
+
+def ref_search_by_sim3(KF1, KF2, points1, points2, skip1, skip2, mm1, mm2, s12, R12, t12, th):
+    from orb_slam_b200.matcher import MAPPOINT_DTYPE
+    f32 = lambda a: np.ascontiguousarray(a, np.float32)
+    p1 = np.ascontiguousarray(points1, MAPPOINT_DTYPE); p2 = np.ascontiguousarray(points2, MAPPOINT_DTYPE)
+    k1 = np.ascontiguousarray(skip1, np.uint8); k2 = np.ascontiguousarray(skip2, np.uint8)
+    m1 = f32(mm1).reshape(-1, 2); m2 = f32(mm2).reshape(-1, 2); R = f32(R12).reshape(3, 3); t = f32(t12).ravel()
+    s1, s2 = KF1.struct(), KF2.struct()
+    out = np.zeros(max(KF1.N, 1), np.int32)
+    vp, f = C.c_void_p, C.c_float
+    fn = _mref().orbref_search_by_sim3
+    fn.argtypes = [vp, vp, vp, vp, vp, vp, vp, vp, f, f, f, vp, vp, f, vp]
+    n = fn(C.byref(s1), C.byref(s2), p1.ctypes.data, p2.ctypes.data, k1.ctypes.data, k2.ctypes.data, m1.ctypes.data, m2.ctypes.data,
+           float(np.log(np.float32(KF1.mvScaleFactors[1]))), float(np.log(np.float32(KF2.mvScaleFactors[1]))), float(s12), R.ctypes.data,
+           t.ctypes.data, float(th), out.ctypes.data)
+    return n, out[:KF1.N]

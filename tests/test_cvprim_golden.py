@@ -100,3 +100,23 @@ def test_config_size_hashes(case):
 def test_atan2_hash():
     m = np.random.default_rng(77).integers(-749 * 15 * 255, 749 * 15 * 255, (2, 200000)).astype(np.float32)
     assert sha(atan2(np.ascontiguousarray(m[0]), np.ascontiguousarray(m[1]))) == HASHES["atan2_200k_seed77"]
+
+
+def test_mat_algebra_golden():
+    """The CV_32F matrix algebra of oracle/ref_build/cvstub (what the reference's ORBmatcher.cc / Frame.cc / KeyFrame.cc are
+    compiled against in oracle/_ref) reproduces cv2 4.13 bit for bit: A*x+c, A*x, -A.t()*x, (-A)*x, norm(x)."""
+    import ctypes as C
+    import pytest
+    from tests.oracle_lib import MATCHER_REF_SO, have_matcher_ref
+    if not have_matcher_ref():
+        pytest.skip("oracle/_ref/liborbmatcher_ref.so not built (needs /root/reference)")
+    z = np.load(os.path.join(os.path.dirname(__file__), "golden", "cv_algebra.npz"))
+    L = C.CDLL(MATCHER_REF_SO)
+    L.orbref_algebra_probe.argtypes = [C.c_void_p] * 4; L.orbref_algebra_probe.restype = None
+    A, x, c, gold = z["A"], z["x"], z["c"], z["out"]
+    got = np.zeros_like(gold)
+    for i in range(len(A)):
+        a, xi, ci = np.ascontiguousarray(A[i]), np.ascontiguousarray(x[i]), np.ascontiguousarray(c[i])
+        L.orbref_algebra_probe(a.ctypes.data, xi.ctypes.data, ci.ctypes.data, got[i].ctypes.data)
+    for name, sl in (("A*x+c", slice(0, 3)), ("A*x", slice(3, 6)), ("-A.t()*x", slice(6, 9)), ("(-A)*x", slice(9, 12)), ("norm", slice(12, 13))):
+        assert np.array_equal(got[:, sl].view(np.uint32), gold[:, sl].view(np.uint32)), name
