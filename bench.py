@@ -387,6 +387,60 @@ def run_stereo_frontend(local_rank, with_cpu):
     return out
 
 
+def run_vocabulary(local_rank, with_cpu):
+    """SURVEY 8(f) rows 3 and 4: Frame::ComputeBoW (ORBVocabulary::transform, levelsup 4) on the descriptors of one KITTI frame
+    against a synthetic vocabulary of the ORBvoc shape (k = 10, L = 6, 10^6 words; the real file is absent), the tree descent
+    alone on a device-resident batch, and MapPoint::ComputeDistinctiveDescriptors for 20 000 map points in one call."""
+    import torch
+    from orb_slam_b200 import ORBextractor
+    from orb_slam_b200._lib import check, lib
+    from orb_slam_b200.matcher import MatcherContext
+    from orb_slam_b200.synth import synth_frame, synth_vocabulary
+    from orb_slam_b200.vocabulary import ORBVocabulary, compute_distinctive_descriptors
+    from tests import scenes
+    ctx = MatcherContext(local_rank)
+    arrays = synth_vocabulary(10, 6)
+    voc = ORBVocabulary.from_arrays(ctx, 10, 6, *arrays)
+    ex = ORBextractor(NFEAT, 1.2, 8, 20, 7, device=local_rank)
+    descs = [ex(synth_frame(W_, H_, 700 + i))[1] for i in range(4)]
+    ex.close()
+
+    def med(fn, reps):
+        ts = []
+        for i in range(reps):
+            t0 = time.perf_counter(); r = fn(i); ts.append(time.perf_counter() - t0)
+        return float(np.median(ts[2:]) * 1e3), r
+    out = {"vocabulary": "synthetic k=10 L=6, %d nodes, %d words (TF-IDF, L1)" % (voc.nnodes, voc.nwords)}
+    t, r = med(lambda i: voc.transform(descs[i % 4], 4), 30)
+    out["compute_bow_ms"] = t; out["bow_words"] = int(len(r[0])); out["featvec_nodes"] = int(len(r[2].node_ids))
+    # descent only, descriptors already in HBM (a batch of 512 frames x 2000)
+    big = torch.from_numpy(np.concatenate(descs)).cuda().repeat(128 * 4, 1)[: 512 * NFEAT].contiguous()
+    res = torch.zeros((big.shape[0], 2), dtype=torch.int32, device="cuda")
+    torch.cuda.synchronize()
+    L = lib()
+    for rep in range(6):
+        if rep == 2:
+            check(L.orbm_synchronize(ctx.h), "sync"); t0 = time.perf_counter()
+        check(L.orbm_vocab_descend_device(ctx.h, voc._h, big.data_ptr(), big.shape[0], 4, res.data_ptr()), "descend")
+    check(L.orbm_synchronize(ctx.h), "sync")
+    dt = (time.perf_counter() - t0) / 4
+    out["descend_batch"] = {"features": int(big.shape[0]), "ms": dt * 1e3, "features_per_s": big.shape[0] / dt,
+                            "node_descriptor_GBps": big.shape[0] * 6 * 10 * 32 / dt / 1e9}
+    D, start = scenes.observation_lists(20000, seed=5, max_obs=10, big=())
+    t, best = med(lambda i: compute_distinctive_descriptors(ctx, D, start), 8)
+    out["distinctive_descriptors"] = {"map_points": 20000, "descriptors": int(len(D)), "ms": t}
+    if with_cpu:
+        from tests import oracle_lib
+        ov = oracle_lib.OracleVocabulary.from_arrays(10, 6, *arrays)
+        t, ro = med(lambda i: ov.transform(descs[i % 4], 4), 12)
+        out["cpu_port"] = {"compute_bow_ms": t, "bow_words": int(len(ro[0]))}
+        t, ob = med(lambda i: oracle_lib.oracle_distinctive_descriptors(D, start), 4)
+        out["cpu_port"]["distinctive_descriptors_ms"] = t
+        out["identical_to_cpu_port"] = bool(np.array_equal(r[0], ro[0]) and np.array_equal(r[1], ro[1]) and np.array_equal(best, ob))
+    voc.close(); ctx.close()
+    return out
+
+
 def run_ours(args, rank, world, local_rank):
     import torch
     from orb_slam_b200 import KEYPOINT_DTYPE, ORBextractor
@@ -553,6 +607,7 @@ def run_ours(args, rank, world, local_rank):
             line["hamming_2nn"] = ham
         if world == 1 and not args.no_frontend:
             line["kitti_stereo_frontend"] = run_stereo_frontend(local_rank, not args.no_cpu)
+            line["vocabulary"] = run_vocabulary(local_rank, not args.no_cpu)
         if world == 1 and not args.no_cpu:
             from tests import oracle_lib
             kind = "reference" if oracle_lib.have_ref() else "port"
@@ -578,7 +633,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--batch", type=int, default=512, help="frames per step per GPU")
-    ap.add_argument("--cpu-frames", type=int, default=384, help="frames in the bounded CPU sample")
+    ap.add_argument("--cpu-frames", type=int, default=768, help="frames in the bounded CPU sample")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-hamming", action="store_true")
     ap.add_argument("--no-frontend", action="store_true")

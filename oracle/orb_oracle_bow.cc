@@ -6,8 +6,8 @@
 // The two feature vectors are rebuilt as std::map<unsigned, std::vector<unsigned>> (= DBoW2::FeatureVector) from the
 // flattened orbm_featvec and the loops follow the reference statement by statement (iterators, lower_bound,
 // continue's, '<=' vs '<' on TH_LOW).  Map points are represented by what the loops read of them: a validity flag
-// (pointer non-NULL and !isBad()).  Parity unpinned by reference object code: ORBmatcher.cc needs OpenCV/DBoW2/g2o
-// headers to compile.
+// (pointer non-NULL and !isBad()).  Pinned: bit-exact against the reference's own ORBmatcher.cc object code
+// (oracle/_ref/liborbmatcher_ref.so, tests/test_oracle_matcher_vs_ref_cpu.py), SearchForTriangulation included.
 #include <cmath>
 #include <cstdint>
 #include <cstring>

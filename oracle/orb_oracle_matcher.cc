@@ -9,10 +9,12 @@
 //   Frame::AssignFeaturesToGrid / PosInGrid / GetFeaturesInArea   src/Frame.cc:292-311, :504-518, :410-495
 // plus the exhaustive 2-NN of SURVEY §8(a) M6.  Plain sequential loops over the
 // reference's own data layout (vector<size_t> mGrid[64][48]); the data-carrier
-// structs are those of include/orbm.h.  Parity of this file is pinned by
-// construction only (the reference has no tests or fixtures for the matcher and its
-// ORBmatcher.cc cannot be compiled without OpenCV/DBoW2/g2o headers): "parity unpinned"
-// for the matcher rows; the small-matrix float algebra is pinned to cv2 4.13 (tests/golden).
+// structs are those of include/orbm.h.
+// Pinned: every function here is bit-exact against the REFERENCE'S OWN OBJECT CODE - src/ORBmatcher.cc, Frame.cc,
+// KeyFrame.cc, MapPoint.cc compiled unmodified into oracle/_ref/liborbmatcher_ref.so (`make ref`,
+// oracle/ref_build/ref_matcher_wrap.cc) - on the shared scenes of tests/test_oracle_matcher_vs_ref_cpu.py; the CV_32F
+// matrix algebra those files are compiled against (oracle/ref_build/cvstub) is bit-exact against cv2 4.13 golden
+// vectors (tests/golden/cv_algebra.npz).  The reference itself ships no tests or fixtures for the matcher.
 #include <climits>
 #include <cmath>
 #include <cstdint>

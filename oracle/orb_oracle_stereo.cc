@@ -2,8 +2,9 @@
 // CPU restatement of Frame::ComputeStereoMatches (reference src/Frame.cc:630-872) on plain arrays: row-band candidate
 // table (:647-673), coarse Hamming match with thOrbDist = (TH_HIGH+TH_LOW)/2 (:639,:692-751), 11x11 SAD refinement over
 // +-5 px on the pyramid level of the left keypoint (:756-812), parabola sub-pixel fit (:822-835), disparity gate
-// (:841-856) and the median-based outlier cut (:858-871).  Parity pin: restatement + line citations only (Frame.cc
-// cannot be compiled here: it pulls the whole ORB-SLAM2 / DBoW2 / OpenCV header tree).
+// (:841-856) and the median-based outlier cut (:858-871).  Pinned: bit-exact against the reference's own Frame.cc object
+// code run on two reference ORBextractors (oracle/_ref/liborbmatcher_ref.so: orbref_compute_stereo_matches;
+// tests/test_oracle_matcher_vs_ref_cpu.py::test_compute_stereo_matches).
 #include <algorithm>
 #include <climits>
 #include <cmath>

@@ -17,7 +17,7 @@ class KeyFrame {
 public:
     KeyFrame() : fx(0), fy(0), cx(0), cy(0), mbf(0), N(0), mnScaleLevels(0), mfScaleFactor(0), mfLogScaleFactor(0), mnMinX(0), mnMinY(0),
                  mnMaxX(0), mnMaxY(0), mfGridElementWidthInv(0), mfGridElementHeightInv(0), Rcw(3, 3, CV_32F), tcw(3, 1, CV_32F),
-                 Ow(3, 1, CV_32F) {}
+                 Ow(3, 1, CV_32F), mbBad(false) {}
     void AddMapPoint(MapPoint* pMP, const size_t& idx) { mvpMapPoints[idx] = pMP; }
     void ReplaceMapPointMatch(const size_t& idx, MapPoint* pMP) { mvpMapPoints[idx] = pMP; }
     void EraseMapPointMatch(const size_t& idx) { mvpMapPoints[idx] = static_cast<MapPoint*>(NULL); }
@@ -29,6 +29,7 @@ public:
             if (mvpMapPoints[i] && !mvpMapPoints[i]->isBad()) s.insert(mvpMapPoints[i]);
         return s;
     }
+    bool isBad() { return mbBad; }                                        // src/KeyFrame.cc:562-566
     cv::Mat GetRotation() { return Rcw.clone(); }
     cv::Mat GetTranslation() { return tcw.clone(); }
     cv::Mat GetCameraCenter() { return Ow.clone(); }
@@ -49,6 +50,7 @@ public:
     // test access (protected in the reference)
     std::vector<MapPoint*> mvpMapPoints;
     cv::Mat Rcw, tcw, Ow;
+    bool mbBad;
 };
 
 inline int MapPoint::PredictScale(const float& currentDist, KeyFrame* pKF) {

@@ -28,6 +28,11 @@ public:
     cv::Mat GetNormal() { return mNormalVector.clone(); }
     bool IsInKeyFrame(KeyFrame* pKF) { return mObservations.count(pKF) != 0; }
     int GetIndexInKeyFrame(KeyFrame* pKF) { return mObservations.count(pKF) ? (int)mObservations[pKF] : -1; }   // src/MapPoint.cc:315-322
+    void ComputeDistinctiveDescriptors();                                 // src/MapPoint.cc:241-306 -> MapPoint_b200.cc
+    // the two locked accesses of ComputeDistinctiveDescriptors (:248-253, :302-305); in the ORB-SLAM2 tree they are two
+    // small members added to MapPoint because mMutexFeatures / mObservations / mDescriptor are protected
+    bool GatherObservations(std::map<KeyFrame*, size_t>& obs) { if (mbBad) return false; obs = mObservations; return true; }
+    void StoreDescriptor(const cv::Mat& d) { mDescriptor = d.clone(); }
     // simplified stand-ins of src/MapPoint.cc:104-121 and :186-225 (single key frame bookkeeping; defined in lite/KeyFrame.h)
     void AddObservation(KeyFrame* pKF, size_t idx);
     void Replace(MapPoint* pMP);

@@ -5,11 +5,11 @@
 #ifndef __D_T_FEATURE_VECTOR__
 #define __D_T_FEATURE_VECTOR__
 #include <map>
+#include "BowVector.h"
 #include <vector>
 
 namespace DBoW2 {
 
-typedef unsigned int NodeId;
 
 class FeatureVector : public std::map<NodeId, std::vector<unsigned int> > {
 public:

@@ -10,6 +10,8 @@
 
 #include "ORBextractor.h"
 #include "ORBmatcher.h"
+#include "ORBVocabulary_b200.h"
+#include "b200_context.h"
 #include "orbm.h"
 
 using namespace ORB_SLAM2;
@@ -470,6 +472,68 @@ int dropin_search_by_sim3(const orbm_frame* kf1, const orbm_frame* kf2, const or
     const int n = matcher.SearchBySim3(&K1, &K2, vpMatches12, s12, R, t, th);
     for (int i = 0; i < kf1->N; i++) prior12[i] = vpMatches12[i] ? (int32_t)(vpMatches12[i] - s2.data()) : -1;
     return n;
+}
+
+
+// Frame::ComputeBoW (src/Frame.cc:521-528) with an ORBVocabularyB200 loaded from a text file: toDescriptorVector's row
+// headers in, DBoW2::BowVector / FeatureVector out (flattened in map order).  use_rows = 0 passes the matrix itself.
+int dropin_compute_bow(const char* vocabularyFile, const uint8_t* desc, int n, int levelsup, int use_rows, uint32_t* wordIds, double* wordVals,
+                       int* nwords, uint32_t* nodeIds, int32_t* nodeStart, uint32_t* items, int* nnodes) {
+    ORBVocabularyB200 voc;
+    if (!voc.loadFromTextFile(vocabularyFile)) return -1;
+    cv::Mat mDescriptors(n, 32, CV_8U);
+    if (n) std::memcpy(mDescriptors.data, desc, (size_t)n * 32);
+    DBoW2::BowVector mBowVec;
+    DBoW2::FeatureVector mFeatVec;
+    if (use_rows) {
+        std::vector<cv::Mat> vCurrentDesc;                      // Converter::toDescriptorVector, src/Converter.cc:27-35
+        vCurrentDesc.reserve(n);
+        for (int j = 0; j < n; j++) vCurrentDesc.push_back(mDescriptors.row(j));
+        voc.transform(vCurrentDesc, mBowVec, mFeatVec, levelsup);
+    } else voc.transform(mDescriptors, mBowVec, mFeatVec, levelsup);
+    int k = 0;
+    for (DBoW2::BowVector::const_iterator it = mBowVec.begin(); it != mBowVec.end(); ++it, ++k) { wordIds[k] = it->first; wordVals[k] = it->second; }
+    *nwords = k;
+    int nn = 0, pos = 0;
+    for (DBoW2::FeatureVector::const_iterator it = mFeatVec.begin(); it != mFeatVec.end(); ++it, ++nn) {
+        nodeIds[nn] = it->first; nodeStart[nn] = pos;
+        for (size_t j = 0; j < it->second.size(); j++) items[pos++] = it->second[j];
+    }
+    nodeStart[nn] = pos;
+    *nnodes = nn;
+    return (int)voc.size();
+}
+
+// MapPoint::ComputeDistinctiveDescriptors (src/MapPoint.cc:241-306): point p is observed by one key frame per descriptor
+// of its list (bad_kf marks key frames whose isBad() is true); batch != 0 goes through b200::ComputeDistinctiveDescriptors
+// (all points in one device call), else the member is called per point.  chosen: 32 bytes per point, has[p] = 0 when the
+// point keeps its previous (empty) descriptor.  order: list positions in std::map<KeyFrame*, size_t> iteration order.
+void dropin_distinctive_descriptors(const uint8_t* desc, const int32_t* start, const uint8_t* bad_kf, int npoints, int batch,
+                                    uint8_t* chosen, uint8_t* has, int32_t* order) {
+    const int total = start[npoints];
+    std::vector<KeyFrame> kfs((size_t)total);
+    std::vector<MapPoint> pts((size_t)npoints);
+    std::vector<MapPoint*> vp;
+    for (int p = 0; p < npoints; p++) {
+        for (int o = start[p]; o < start[p + 1]; o++) {
+            KeyFrame& kf = kfs[o];
+            kf.mDescriptors.create(1, 32, CV_8U);
+            std::memcpy(kf.mDescriptors.data, desc + (size_t)o * 32, 32);
+            kf.mbBad = bad_kf[o] != 0;
+            pts[p].mObservations[&kf] = 0;
+        }
+        int k = 0;
+        for (std::map<KeyFrame*, size_t>::iterator it = pts[p].mObservations.begin(); it != pts[p].mObservations.end(); ++it, ++k)
+            order[start[p] + k] = (int32_t)(it->first - kfs.data()) - start[p];
+        pts[p].mDescriptor.release();
+        vp.push_back(&pts[p]);
+    }
+    if (batch) b200::ComputeDistinctiveDescriptors(vp);
+    else for (int p = 0; p < npoints; p++) pts[p].ComputeDistinctiveDescriptors();
+    for (int p = 0; p < npoints; p++) {
+        has[p] = !pts[p].mDescriptor.empty();
+        if (has[p]) std::memcpy(chosen + (size_t)p * 32, pts[p].mDescriptor.data, 32);
+    }
 }
 
 }  // extern "C"

@@ -388,3 +388,59 @@ def test_search_by_sim3_member(H):
                                 p(np.ascontiguousarray(sc["R12"])), p(sc["t12"]), C.c_float(7.5), p(got))
     assert n == n_o and n > 300
     np.testing.assert_array_equal(got, expect)
+
+
+# ---------------------------------------------------------------- ORBVocabularyB200 / MapPoint::ComputeDistinctiveDescriptors
+@pytest.mark.parametrize("use_rows", [1, 0])
+@pytest.mark.parametrize("k,L,levelsup,trailing", [(10, 4, 2, True), (7, 4, 2, False)])
+def test_vocabulary_class_compute_bow(H, tmp_path, k, L, levelsup, trailing, use_rows):
+    """Frame::ComputeBoW through ORBVocabularyB200 (loadFromTextFile + virtual transform) against the vocabulary oracle"""
+    from orb_slam_b200.synth import synth_vocabulary, vocabulary_text
+    from tests.oracle_lib import OracleVocabulary
+    arrays = synth_vocabulary(k, L, seed=5, stop_fraction=0.04) if k == 10 else scenes.unbalanced_vocabulary(k, L, seed=8, min_leaf_level=2)
+    path = tmp_path / "voc.txt"
+    path.write_text(vocabulary_text(k, L, *arrays, trailing_newline=trailing))
+    q = scenes.vocabulary_queries(arrays[2], arrays[1], 1800, seed=k)
+    n = len(q)
+    wid = np.zeros(n, np.uint32); wv = np.zeros(n, np.float64); nid = np.zeros(n, np.uint32); st = np.zeros(n + 1, np.int32)
+    it = np.zeros(n, np.uint32); nw, nn = C.c_int(), C.c_int()
+    vp = C.c_void_p
+    H.dropin_compute_bow.argtypes = [C.c_char_p, vp, C.c_int, C.c_int, C.c_int, vp, vp, C.POINTER(C.c_int), vp, vp, vp, C.POINTER(C.c_int)]
+    words = H.dropin_compute_bow(str(path).encode(), q.ctypes.data, n, levelsup, use_rows, wid.ctypes.data, wv.ctypes.data, C.byref(nw),
+                                 nid.ctypes.data, st.ctypes.data, it.ctypes.data, C.byref(nn))
+    assert words == int(arrays[1].sum())
+    o = OracleVocabulary.from_arrays(k, L, *arrays)
+    owid, owv, ofv = o.transform(q, levelsup)
+    assert np.array_equal(wid[:nw.value], owid) and np.array_equal(wv[:nw.value], owv)
+    assert {int(nid[j]): it[st[j]:st[j + 1]].tolist() for j in range(nn.value)} == ofv
+    assert H.dropin_compute_bow(str(tmp_path / "missing.txt").encode(), q.ctypes.data, n, levelsup, use_rows, wid.ctypes.data, wv.ctypes.data,
+                                C.byref(nw), nid.ctypes.data, st.ctypes.data, it.ctypes.data, C.byref(nn)) == -1
+
+
+@pytest.mark.parametrize("batch", [1, 0])
+def test_mappoint_compute_distinctive_descriptors(H, batch):
+    from tests.oracle_lib import oracle_distinctive_descriptors
+    D, start = scenes.observation_lists(300 if batch else 40, seed=12)
+    rng = np.random.default_rng(3)
+    bad = (rng.random(len(D)) < 0.1).astype(np.uint8)
+    bad[start[7]:start[8]] = 1                                   # a point whose key frames are all bad keeps its descriptor
+    npts = len(start) - 1
+    chosen = np.zeros((npts, 32), np.uint8); has = np.zeros(npts, np.uint8); order = np.zeros(len(D), np.int32)
+    vp = C.c_void_p
+    H.dropin_distinctive_descriptors.argtypes = [vp, vp, vp, C.c_int, C.c_int, vp, vp, vp]
+    H.dropin_distinctive_descriptors.restype = None
+    H.dropin_distinctive_descriptors(D.ctypes.data, start.ctypes.data, bad.ctypes.data, npts, batch, chosen.ctypes.data, has.ctypes.data,
+                                     order.ctypes.data)
+    # the restatement on each point's good observations in the order the std::map iterated them
+    rows, ostart = [], [0]
+    for p in range(npts):
+        idx = start[p] + order[start[p]:start[p + 1]]
+        idx = idx[bad[idx] == 0]
+        rows.append(D[idx]); ostart.append(ostart[-1] + len(idx))
+    Dp = np.concatenate(rows) if rows else np.zeros((0, 32), np.uint8)
+    best = oracle_distinctive_descriptors(Dp, np.array(ostart, np.int32))
+    assert not has[7] and has.sum() > npts * 0.8
+    for p in range(npts):
+        assert bool(has[p]) == (best[p] >= 0), p
+        if best[p] >= 0:
+            assert np.array_equal(Dp[ostart[p] + best[p]], chosen[p]), p
