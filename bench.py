@@ -436,7 +436,9 @@ def run_vocabulary(local_rank, with_cpu):
         out["cpu_port"] = {"compute_bow_ms": t, "bow_words": int(len(ro[0]))}
         t, ob = med(lambda i: oracle_lib.oracle_distinctive_descriptors(D, start), 4)
         out["cpu_port"]["distinctive_descriptors_ms"] = t
-        out["identical_to_cpu_port"] = bool(np.array_equal(r[0], ro[0]) and np.array_equal(r[1], ro[1]) and np.array_equal(best, ob))
+        a, b = voc.transform(descs[0], 4), ov.transform(descs[0], 4)
+        out["identical_to_cpu_port"] = bool(np.array_equal(a[0], b[0]) and np.array_equal(a[1], b[1]) and a[2].as_dict() == b[2]
+                                            and np.array_equal(best, ob))
     voc.close(); ctx.close()
     return out
 
