@@ -95,6 +95,18 @@ int orbm_search_for_initialization(orbm_t* m, const orbm_frame* F1, const orbm_f
                                    int32_t* matches12, int windowSize, float nnratio, int checkOrientation,
                                    int* nmatches);
 
+/* SearchForInitialization for MANY frame pairs in one call, on DEVICE-resident frames: the layout is the output of
+ * orbx_extract_batch_device (d_keys [nframes][cap] cv::KeyPoint, d_desc [nframes][cap][32], d_n [nframes]); key points are
+ * used as mvKeysUn (no distortion).  d_pairs: npairs x (f1, f2) frame indices, or NULL for the consecutive pairs (p, p+1)
+ * (then npairs <= nframes - 1).  d_prev: [npairs][cap][2] vbPrevMatched in/out, or NULL: each F1's own key-point positions
+ * (Tracking::MonocularInitialization, src/Tracking.cc:590-596) and no write-back.  Grid bounds as in orbm_frame.
+ * Out: d_matches12 [npairs][cap] (vnMatches12, -1 = none), d_nmatches [npairs].  Enqueued on the context stream; BASELINE.json
+ * configs[2] (EuRoC batch).  Each pair's queries are replayed in order by one warp, so results equal the per-pair function. */
+int orbm_search_for_initialization_batch_device(orbm_t* m, const orbx_keypoint* d_keys, const uint8_t* d_desc, const int32_t* d_n,
+                                                int cap, int nframes, const int32_t* d_pairs, int npairs, float mnMinX, float mnMinY,
+                                                float gridElementWidthInv, float gridElementHeightInv, float* d_prev, int windowSize,
+                                                float nnratio, int checkOrientation, int32_t* d_matches12, int32_t* d_nmatches);
+
 /* MapPoint fields read by the projection matchers. */
 typedef struct orbm_mappoint {
     float world[3];            /* GetWorldPos() */

@@ -1,0 +1,192 @@
+// ORBmatcher::SearchForInitialization (reference src/ORBmatcher.cc:417-588) for MANY frame pairs at once, entirely on the
+// device: the frames are the extractor's batch output as it lies in HBM (cv::KeyPoint[frames][cap], descriptors
+// [frames][cap][32], counts[frames]); nothing travels to the host.  BASELINE.json configs[2] (EuRoC batch, frame i against
+// frame i+1, window 100, nnratio 0.9, rotation histogram).
+//   grid_build_batch_kernel : Frame::AssignFeaturesToGrid / PosInGrid (src/Frame.cc:292-311, :504-518), one block per frame
+//   init_match_batch_kernel : one warp per pair replays the function's loop in query order - the queries of a pair are
+//                             order-dependent (vMatchedDistance / vnMatches21 stealing, :488, :513-517), the pairs are not.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include "window.cuh"
+
+namespace orbm {
+
+__global__ void __launch_bounds__(1024) grid_build_batch_kernel(const orbx_keypoint* __restrict__ keys, const int32_t* __restrict__ counts,
+                                                                int cap, GridParams g, int32_t* __restrict__ cellOf,
+                                                                int32_t* __restrict__ cellStart, int32_t* __restrict__ items) {
+    __shared__ int cnt[GRID_CELLS + 1];
+    __shared__ int warpSum[32];
+    const int f = blockIdx.x;
+    const orbx_keypoint* keysUn = keys + (size_t)f * cap;
+    const int N = min(counts[f], cap);
+    cellOf += (size_t)f * cap; items += (size_t)f * cap; cellStart += (size_t)f * (GRID_CELLS + 1);
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    for (int c = tid; c <= GRID_CELLS; c += blockDim.x) cnt[c] = 0;
+    __syncthreads();
+    for (int i = tid; i < N; i += blockDim.x) {
+        const int px = (int)roundf(__fmul_rn(__fsub_rn(keysUn[i].x, g.minX), g.invW));       // :507-509
+        const int py = (int)roundf(__fmul_rn(__fsub_rn(keysUn[i].y, g.minY), g.invH));
+        int c = -1;
+        if (!(px < 0 || px >= ORBM_GRID_COLS || py < 0 || py >= ORBM_GRID_ROWS)) { c = px * ORBM_GRID_ROWS + py; atomicAdd(&cnt[c], 1); }
+        cellOf[i] = c;
+    }
+    __syncthreads();
+    const int per = (GRID_CELLS + blockDim.x - 1) / blockDim.x;
+    const int b = min(tid * per, GRID_CELLS), e = min(b + per, GRID_CELLS);
+    int s = 0;
+    for (int c = b; c < e; c++) s += cnt[c];
+    int inc = s;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) { const int t = __shfl_up_sync(0xffffffffu, inc, d); if (lane >= d) inc += t; }
+    if (lane == 31) warpSum[wid] = inc;
+    __syncthreads();
+    int base = 0;
+    for (int k = 0; k < wid; k++) base += warpSum[k];
+    int run = base + inc - s;
+    for (int c = b; c < e; c++) { const int v = cnt[c]; cnt[c] = run; cellStart[c] = run; run += v; }
+    if (tid == blockDim.x - 1) { cnt[GRID_CELLS] = run; cellStart[GRID_CELLS] = run; }
+    __syncthreads();
+    for (int i = tid; i < N; i += blockDim.x) {          // stable placement (push_back order, :300-310)
+        const int c = cellOf[i];
+        if (c < 0) continue;
+        int rank = 0;
+        for (int j = 0; j < i; j++) rank += (cellOf[j] == c);
+        items[cnt[c] + rank] = i;
+    }
+}
+
+struct InitBatchArgs {
+    const orbx_keypoint* keys; const uint32_t* desc; const int32_t* counts; int cap;
+    const int32_t* pairs; int npairs;                    // (f1, f2) per pair, or NULL: (p, p + 1)
+    const int32_t* cellStart; const int32_t* items;      // per frame, from grid_build_batch_kernel
+    GridParams g;
+    float windowSize, nnratio; int checkOri;
+    float* prev;                                         // [npairs][cap][2] vbPrevMatched in/out, or NULL: F1's own key points
+    int32_t* matchedDistance; int32_t* matches21;        // [npairs][cap] scratch
+    uint8_t* bins;                                       // [npairs][cap] scratch: rotation bin of an accepted query
+    int32_t* matches12; int32_t* nmatches;               // out: [npairs][cap], [npairs]
+};
+
+__global__ void __launch_bounds__(128) init_match_batch_kernel(InitBatchArgs a) {
+    const int lane = threadIdx.x & 31;
+    const int p = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (p >= a.npairs) return;
+    const int f1 = a.pairs ? a.pairs[2 * p] : p, f2 = a.pairs ? a.pairs[2 * p + 1] : p + 1;
+    const int N1 = min(a.counts[f1], a.cap), N2 = min(a.counts[f2], a.cap);
+    const orbx_keypoint* K1 = a.keys + (size_t)f1 * a.cap;
+    const orbx_keypoint* K2 = a.keys + (size_t)f2 * a.cap;
+    const uint32_t* D1 = a.desc + (size_t)f1 * a.cap * 8;
+    const uint32_t* D2 = a.desc + (size_t)f2 * a.cap * 8;
+    const int32_t* cellStart = a.cellStart + (size_t)f2 * (GRID_CELLS + 1);
+    const int32_t* items = a.items + (size_t)f2 * a.cap;
+    int32_t* md = a.matchedDistance + (size_t)p * a.cap;
+    int32_t* m21 = a.matches21 + (size_t)p * a.cap;
+    int32_t* m12 = a.matches12 + (size_t)p * a.cap;
+    uint8_t* bins = a.bins + (size_t)p * a.cap;
+    float* prev = a.prev ? a.prev + (size_t)p * a.cap * 2 : nullptr;
+    for (int i = lane; i < a.cap; i += 32) { m12[i] = -1; bins[i] = 255; }
+    for (int i = lane; i < N2; i += 32) { md[i] = 0x7fffffff; m21[i] = -1; }        // vMatchedDistance(INT_MAX), vnMatches21(-1), :436-437
+    __syncwarp();
+    int hist = 0;                                        // lane b < 30 holds rotHist[b].size()
+    const float factor = __fdiv_rn(1.0f, (float)ORBM_HISTO_LENGTH);
+    constexpr uint32_t NONE = 0xffffffffu;               // NONE >> 20 = 0xfff: "no distance", above every real one (<= 256)
+    for (int i1 = 0; i1 < N1; i1++) {
+        const orbx_keypoint kp1 = K1[i1];
+        if (kp1.octave > 0) continue;                    // :451
+        WQuery q;
+        q.x = prev ? prev[2 * i1] : kp1.x; q.y = prev ? prev[2 * i1 + 1] : kp1.y; q.r = a.windowSize;
+        q.minLevel = 0; q.maxLevel = 0;
+        const CellRange cr = window_cells(q, a.g);
+        if (cr.empty) continue;
+        const uint4 d0 = *(const uint4*)(D1 + (size_t)i1 * 8), d1 = *(const uint4*)(D1 + (size_t)i1 * 8 + 4);
+        uint32_t best = NONE;                            // (dist << 20) | position in GetFeaturesInArea order
+        int bestIdx = -1;
+        uint32_t second = 0xfff;
+        int pos = 0;
+        for (int ix = cr.x0; ix <= cr.x1; ix++) {
+            const int s = cellStart[ix * ORBM_GRID_ROWS + cr.y0], e = cellStart[ix * ORBM_GRID_ROWS + cr.y1 + 1];
+            for (int k0 = s; k0 < e; k0 += 32) {
+                const int k = k0 + lane;
+                bool ok = false;
+                int idx = -1;
+                if (k < e) {
+                    idx = items[k];
+                    const orbx_keypoint kp = K2[idx];
+                    ok = kp.octave == 0;                 // minLevel = maxLevel = 0, :449-479
+                    const float dx = __fsub_rn(kp.x, q.x), dy = __fsub_rn(kp.y, q.y);
+                    if (!(fabsf(dx) < q.r && fabsf(dy) < q.r)) ok = false;
+                }
+                const unsigned m = __ballot_sync(0xffffffffu, ok);
+                if (ok) {
+                    const uint4 e0 = *(const uint4*)(D2 + (size_t)idx * 8), e1 = *(const uint4*)(D2 + (size_t)idx * 8 + 4);
+                    const uint32_t dist = __popc(d0.x ^ e0.x) + __popc(d0.y ^ e0.y) + __popc(d0.z ^ e0.z) + __popc(d0.w ^ e0.w) +
+                                          __popc(d1.x ^ e1.x) + __popc(d1.y ^ e1.y) + __popc(d1.z ^ e1.z) + __popc(d1.w ^ e1.w);
+                    if (!(__ldcg(&md[idx]) <= (int)dist)) {          // :488
+                        const uint32_t key = (dist << 20) | (uint32_t)(pos + __popc(m & ((1u << lane) - 1)));
+                        if (key < best) { second = best >> 20; best = key; bestIdx = idx; }
+                        else if (dist < second) second = dist;
+                    }
+                }
+                pos += __popc(m);
+            }
+        }
+        if (pos == 0) continue;                          // vIndices2.empty(), :458
+        // warp top-2: first strict minimum (the position breaks ties), second smallest distance counted with multiplicity
+        uint32_t wb = best;
+#pragma unroll
+        for (int sft = 16; sft > 0; sft >>= 1) wb = min(wb, __shfl_xor_sync(0xffffffffu, wb, sft));
+        if (wb == NONE) continue;                        // every candidate skipped: bestDist stays INT_MAX
+        const unsigned owner = __ballot_sync(0xffffffffu, best == wb);
+        const int bestIdx2 = __shfl_sync(0xffffffffu, bestIdx, __ffs(owner) - 1);
+        uint32_t sec = best == wb ? second : (best >> 20);
+#pragma unroll
+        for (int sft = 16; sft > 0; sft >>= 1) sec = min(sec, __shfl_xor_sync(0xffffffffu, sec, sft));
+        const int bestDist = (int)(wb >> 20);
+        const int bestDist2 = sec >= 0xfff ? 0x7fffffff : (int)sec;
+        if (bestDist <= ORBM_TH_LOW && (float)bestDist < __fmul_rn((float)bestDist2, a.nnratio)) {      // :505-509
+            int bin = -1;
+            if (a.checkOri) {                            // :528-540
+                float rot = __fsub_rn(kp1.angle, K2[bestIdx2].angle);
+                if (rot < 0.0f) rot = __fadd_rn(rot, 360.0f);
+                bin = (int)roundf(__fmul_rn(rot, factor));
+                if (bin == ORBM_HISTO_LENGTH) bin = 0;
+                if (lane == bin) hist++;
+            }
+            if (lane == 0) {
+                const int prevOwner = __ldcg(&m21[bestIdx2]);
+                if (prevOwner >= 0) __stcg(&m12[prevOwner], -1);       // :513-517
+                __stcg(&m12[i1], bestIdx2); __stcg(&m21[bestIdx2], i1); __stcg(&md[bestIdx2], bestDist);
+                if (bin >= 0) bins[i1] = (uint8_t)bin;
+            }
+            __syncwarp();
+        }
+    }
+    __syncwarp();
+    if (a.checkOri) {                                    // ComputeThreeMaxima (:1679-1723) on the bin sizes, then :548-578
+        int max1 = 0, max2 = 0, max3 = 0, ind1 = -1, ind2 = -1, ind3 = -1;
+        for (int i = 0; i < ORBM_HISTO_LENGTH; i++) {
+            const int sz = __shfl_sync(0xffffffffu, hist, i);
+            if (sz > max1) { max3 = max2; max2 = max1; max1 = sz; ind3 = ind2; ind2 = ind1; ind1 = i; }
+            else if (sz > max2) { max3 = max2; max2 = sz; ind3 = ind2; ind2 = i; }
+            else if (sz > max3) { max3 = sz; ind3 = i; }
+        }
+        if ((float)max2 < __fmul_rn(0.1f, (float)max1)) { ind2 = -1; ind3 = -1; }
+        else if ((float)max3 < __fmul_rn(0.1f, (float)max1)) ind3 = -1;
+        for (int i = lane; i < N1; i += 32) {
+            const int b = bins[i];
+            if (b != 255 && b != ind1 && b != ind2 && b != ind3 && __ldcg(&m12[i]) >= 0) __stcg(&m12[i], -1);
+        }
+        __syncwarp();
+    }
+    int cnt = 0;
+    for (int i0 = 0; i0 < N1; i0 += 32) {
+        const int i = i0 + lane;
+        const int m = i < N1 ? __ldcg(&m12[i]) : -1;
+        if (m >= 0 && prev) { prev[2 * i] = K2[m].x; prev[2 * i + 1] = K2[m].y; }    // :582-584
+        cnt += __popc(__ballot_sync(0xffffffffu, m >= 0));
+    }
+    if (lane == 0) a.nmatches[p] = cnt;
+}
+
+}  // namespace orbm

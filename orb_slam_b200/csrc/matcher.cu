@@ -13,6 +13,7 @@
 #include "hamming.cuh"
 #include "window.cuh"
 #include "bow.cuh"
+#include "initbatch.cuh"
 #include "vocab.cuh"
 
 using namespace orbm;

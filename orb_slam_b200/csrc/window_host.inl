@@ -696,3 +696,35 @@ extern "C" int orbm_search_by_sim3(orbm_t* m, const orbm_sim3_side* side1, const
     *nfound = n;
     return ORBX_OK;
 }
+
+// SearchForInitialization over many pairs of device-resident frames (initbatch.cuh)
+extern "C" int orbm_search_for_initialization_batch_device(orbm_t* m, const orbx_keypoint* d_keys, const uint8_t* d_desc, const int32_t* d_n,
+                                                           int cap, int nframes, const int32_t* d_pairs, int npairs, float mnMinX,
+                                                           float mnMinY, float invW, float invH, float* d_prev, int windowSize,
+                                                           float nnratio, int checkOri, int32_t* d_matches12, int32_t* d_nmatches) {
+    if (!m || !d_keys || !d_desc || !d_n || cap <= 0 || nframes <= 0 || npairs < 0 || !d_matches12 || !d_nmatches) return ORBX_E_INVALID;
+    if (!d_pairs && npairs > nframes - 1) return ORBX_E_INVALID;
+    if (((uintptr_t)d_desc & 15) || cap >= (1 << 20)) return ORBX_E_INVALID;
+    if (npairs == 0) return ORBX_OK;
+    std::lock_guard<std::mutex> lk(m->mtx);
+    CKM(cudaSetDevice(m->device));
+    int rc;
+    const size_t fc = (size_t)nframes * cap, pc = (size_t)npairs * cap;
+    if ((rc = m->w0.reserve(fc * 4))) return rc;                                   // cellOf
+    if ((rc = m->w1.reserve((size_t)nframes * (GRID_CELLS + 1) * 4))) return rc;    // cellStart
+    if ((rc = m->w2.reserve(fc * 4))) return rc;                                   // items
+    if ((rc = m->w3.reserve(pc * 4))) return rc;                                   // vMatchedDistance
+    if ((rc = m->w4.reserve(pc * 4))) return rc;                                   // vnMatches21
+    if ((rc = m->w5.reserve(pc))) return rc;                                       // rotation bins
+    const GridParams g{mnMinX, mnMinY, invW, invH};
+    grid_build_batch_kernel<<<nframes, 1024, 0, m->stream>>>(d_keys, d_n, cap, g, (int32_t*)m->w0.p, (int32_t*)m->w1.p, (int32_t*)m->w2.p);
+    InitBatchArgs a{};
+    a.keys = d_keys; a.desc = (const uint32_t*)d_desc; a.counts = d_n; a.cap = cap; a.pairs = d_pairs; a.npairs = npairs;
+    a.cellStart = (const int32_t*)m->w1.p; a.items = (const int32_t*)m->w2.p; a.g = g;
+    a.windowSize = (float)windowSize; a.nnratio = nnratio; a.checkOri = checkOri; a.prev = d_prev;
+    a.matchedDistance = (int32_t*)m->w3.p; a.matches21 = (int32_t*)m->w4.p; a.bins = (uint8_t*)m->w5.p;
+    a.matches12 = d_matches12; a.nmatches = d_nmatches;
+    init_match_batch_kernel<<<(npairs + 3) / 4, 128, 0, m->stream>>>(a);
+    CKM(cudaGetLastError());
+    return ORBX_OK;
+}

@@ -191,6 +191,28 @@ class MatcherContext:
         except Exception:
             pass
 
+    def search_for_initialization_batch_device(self, d_keys, d_desc, d_n, cap, nframes, width, height, *, d_pairs=None, npairs=None,
+                                               d_prev=None, windowSize=100, nnratio=0.9, checkOri=True, d_matches12=None,
+                                               d_nmatches=None):
+        """orbm_search_for_initialization_batch_device: every argument named d_* is a device pointer (int).  The grid is
+        that of an undistorted width x height image (src/Frame.cc:606-612, :126-127)."""
+        L = self._L
+        if not hasattr(L, "_init_batch_bound"):
+            vp, i, f = C.c_void_p, C.c_int, C.c_float
+            L.orbm_search_for_initialization_batch_device.argtypes = [vp, vp, vp, vp, i, i, vp, i, f, f, f, f, vp, i, f, i, vp, vp]
+            L.orbm_search_for_initialization_batch_device.restype = i
+            L._init_batch_bound = True
+        if npairs is None:
+            npairs = nframes - 1
+        invW = float(np.float32(FRAME_GRID_COLS) / (np.float32(width) - np.float32(0)))
+        invH = float(np.float32(FRAME_GRID_ROWS) / (np.float32(height) - np.float32(0)))
+        check(L.orbm_search_for_initialization_batch_device(self.h, d_keys, d_desc, d_n, cap, nframes, d_pairs, npairs, 0.0, 0.0, invW, invH,
+                                                            d_prev, int(windowSize), float(np.float32(nnratio)), int(checkOri), d_matches12,
+                                                            d_nmatches), "orbm_search_for_initialization_batch_device")
+
+    def synchronize(self):
+        check(self._L.orbm_synchronize(self.h), "orbm_synchronize")
+
     def popc_peak(self) -> float:
         v = C.c_double()
         check(self._L.orbm_popc_peak(self.h, C.byref(v)), "orbm_popc_peak")

@@ -1,0 +1,99 @@
+"""GPU parity of orbm_search_for_initialization_batch_device (ORBmatcher::SearchForInitialization, src/ORBmatcher.cc:417-588,
+for many device-resident frame pairs at once; BASELINE.json configs[2]) against the CPU oracle run pair by pair on the very
+key points and descriptors the extractor left in HBM: vnMatches12, the match counts and vbPrevMatched are identical."""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+from orb_slam_b200.synth import synth_frame
+from tests import scenes
+from tests.oracle_lib import OracleMatcher
+
+pytestmark = pytest.mark.gpu
+
+
+def extract_on_device(ex, frames):
+    import torch
+    from orb_slam_b200._lib import check
+    n, h, w = frames.shape
+    cap = ex.max_keypoints(w, h)
+    d_img = torch.from_numpy(frames).cuda()
+    d_k = torch.zeros((n, cap, 28), dtype=torch.uint8, device="cuda")
+    d_d = torch.zeros((n, cap, 32), dtype=torch.uint8, device="cuda")
+    d_n = torch.zeros(n, dtype=torch.int32, device="cuda")
+    L = ex._L
+    torch.cuda.synchronize()
+    check(L.orbx_extract_batch_device(ex.handle, d_img.data_ptr(), n, w, h, w, w * h, d_k.data_ptr(), d_d.data_ptr(), cap, d_n.data_ptr()),
+          "orbx_extract_batch_device")
+    check(L.orbx_synchronize(ex.handle), "orbx_synchronize")
+    return d_k, d_d, d_n, cap
+
+
+@pytest.mark.parametrize("w,h,nf,nframes,win,ratio,ori,use_prev,use_pairs",
+                         [(752, 480, 1000, 12, 100, 0.9, True, False, False), (752, 480, 1000, 6, 30, 0.6, True, True, False),
+                          (640, 480, 500, 5, 100, 0.9, False, False, True), (1241, 376, 2000, 4, 50, 0.8, True, True, True)])
+def test_batch_matches_oracle_pair_by_pair(w, h, nf, nframes, win, ratio, ori, use_prev, use_pairs):
+    import torch
+    from orb_slam_b200 import KEYPOINT_DTYPE, ORBextractor
+    from orb_slam_b200.matcher import MatcherContext
+    frames = np.stack([synth_frame(w, h, 40, shift=(3 * i, -2 * i)) for i in range(nframes)])
+    ex = ORBextractor(nf, 1.2, 8, 20, 7, device=0)
+    d_k, d_d, d_n, cap = extract_on_device(ex, frames)
+    ctx = MatcherContext(0)
+    if use_pairs:
+        pairs = np.array([(i, j) for i in range(nframes) for j in range(nframes) if i != j][:: 3], np.int32)
+    else:
+        pairs = np.array([(i, i + 1) for i in range(nframes - 1)], np.int32)
+    d_pairs = torch.from_numpy(pairs).cuda() if use_pairs else None
+    npairs = len(pairs)
+    k_h = d_k.cpu().numpy().view(KEYPOINT_DTYPE).reshape(nframes, cap); d_h = d_d.cpu().numpy(); n_h = d_n.cpu().numpy()
+    rng = np.random.default_rng(7)
+    prev_h = np.zeros((npairs, cap, 2), np.float32)
+    for p, (f1, _) in enumerate(pairs):
+        prev_h[p, :, 0] = k_h[f1]["x"] + rng.uniform(-8, 8, cap); prev_h[p, :, 1] = k_h[f1]["y"] + rng.uniform(-8, 8, cap)
+    d_prev = torch.from_numpy(prev_h).cuda() if use_prev else None
+    d_m = torch.full((npairs, cap), -7, dtype=torch.int32, device="cuda"); d_nm = torch.zeros(npairs, dtype=torch.int32, device="cuda")
+    torch.cuda.synchronize()
+    ctx.search_for_initialization_batch_device(d_k.data_ptr(), d_d.data_ptr(), d_n.data_ptr(), cap, nframes, w, h,
+                                               d_pairs=None if d_pairs is None else d_pairs.data_ptr(), npairs=npairs,
+                                               d_prev=None if d_prev is None else d_prev.data_ptr(), windowSize=win, nnratio=ratio,
+                                               checkOri=ori, d_matches12=d_m.data_ptr(), d_nmatches=d_nm.data_ptr())
+    ctx.synchronize()
+    m, nm = d_m.cpu().numpy(), d_nm.cpu().numpy()
+    prev_out = d_prev.cpu().numpy() if use_prev else None
+    o = OracleMatcher(ratio, ori)
+    total = 0
+    for p, (f1, f2) in enumerate(pairs):
+        F1 = scenes.make_frame(k_h[f1, :n_h[f1]], d_h[f1, :n_h[f1]], w, h)
+        F2 = scenes.make_frame(k_h[f2, :n_h[f2]], d_h[f2, :n_h[f2]], w, h)
+        prev = (prev_h[p, :n_h[f1]].copy() if use_prev else
+                np.ascontiguousarray(np.stack([F1.mvKeysUn["x"], F1.mvKeysUn["y"]], 1), np.float32))
+        n_o, m_o = o.SearchForInitialization(F1, F2, prev, win)
+        assert nm[p] == n_o, p
+        assert np.array_equal(m[p, :n_h[f1]], m_o), p
+        assert (m[p, n_h[f1]:] == -1).all()
+        if use_prev:
+            assert np.array_equal(prev_out[p, :n_h[f1]], prev), p
+        total += n_o
+    assert total > 20 * npairs or win < 100
+    ex.close(); ctx.close()
+
+
+def test_batch_edge_cases():
+    import torch
+    from orb_slam_b200.matcher import MatcherContext
+    ctx = MatcherContext(0)
+    cap, nframes = 64, 3
+    d_k = torch.zeros((nframes, cap, 28), dtype=torch.uint8, device="cuda"); d_d = torch.zeros((nframes, cap, 32), dtype=torch.uint8, device="cuda")
+    d_n = torch.zeros(nframes, dtype=torch.int32, device="cuda")                    # frames without key points
+    d_m = torch.full((2, cap), 5, dtype=torch.int32, device="cuda"); d_nm = torch.full((2,), 9, dtype=torch.int32, device="cuda")
+    ctx.search_for_initialization_batch_device(d_k.data_ptr(), d_d.data_ptr(), d_n.data_ptr(), cap, nframes, 752, 480,
+                                               d_matches12=d_m.data_ptr(), d_nmatches=d_nm.data_ptr())
+    ctx.synchronize()
+    assert (d_m.cpu().numpy() == -1).all() and (d_nm.cpu().numpy() == 0).all()
+    from orb_slam_b200 import FrontendError
+    with pytest.raises(FrontendError):                                             # more consecutive pairs than frames allow
+        ctx.search_for_initialization_batch_device(d_k.data_ptr(), d_d.data_ptr(), d_n.data_ptr(), cap, nframes, 752, 480, npairs=3,
+                                                   d_matches12=d_m.data_ptr(), d_nmatches=d_nm.data_ptr())
+    ctx.close()
