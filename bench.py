@@ -443,6 +443,67 @@ def run_vocabulary(local_rank, with_cpu):
     return out
 
 
+def run_euroc_batch(local_rank, with_cpu, nframes=1024):
+    """BASELINE.json configs[2]: EuRoC-shape 752x480 monocular frame batch (1024 frames), nFeatures 1000, then
+    SearchForInitialization (window 100, nnratio 0.9, rotation histogram) on every consecutive pair - extraction and
+    matching both on device-resident data, no host round trip in between."""
+    import torch
+    from orb_slam_b200 import KEYPOINT_DTYPE, ORBextractor
+    from orb_slam_b200._lib import check
+    from orb_slam_b200.matcher import MatcherContext
+    from orb_slam_b200.synth import synth_frame
+    from tests import scenes
+    w, h, nf, distinct = 752, 480, 1000, 32
+    base = np.stack([synth_frame(w, h, 900, shift=(2 * i, -i)) for i in range(distinct)])
+    order = [(i % (2 * distinct - 2)) for i in range(nframes)]
+    order = [j if j < distinct else 2 * distinct - 2 - j for j in order]          # 0..31..1..0..: neighbours differ by one shift step
+    d_img = torch.from_numpy(base).cuda()[torch.tensor(order, device="cuda")].contiguous()
+    ex = ORBextractor(nf, 1.2, 8, 20, 7, device=local_rank)
+    ctx = MatcherContext(local_rank)
+    cap = ex.max_keypoints(w, h)
+    d_k = torch.zeros((nframes, cap, 28), dtype=torch.uint8, device="cuda")
+    d_d = torch.zeros((nframes, cap, 32), dtype=torch.uint8, device="cuda")
+    d_n = torch.zeros(nframes, dtype=torch.int32, device="cuda")
+    d_m = torch.zeros((nframes - 1, cap), dtype=torch.int32, device="cuda"); d_nm = torch.zeros(nframes - 1, dtype=torch.int32, device="cuda")
+    L = ex._L
+
+    def extract():
+        check(L.orbx_extract_batch_device(ex.handle, d_img.data_ptr(), nframes, w, h, w, w * h, d_k.data_ptr(), d_d.data_ptr(), cap,
+                                          d_n.data_ptr()), "orbx_extract_batch_device")
+        check(L.orbx_synchronize(ex.handle), "sync")
+
+    def match():
+        ctx.search_for_initialization_batch_device(d_k.data_ptr(), d_d.data_ptr(), d_n.data_ptr(), cap, nframes, w, h,
+                                                   d_matches12=d_m.data_ptr(), d_nmatches=d_nm.data_ptr())
+        ctx.synchronize()
+    torch.cuda.synchronize()
+    te, tm = [], []
+    for rep in range(5):
+        t0 = time.perf_counter(); extract(); t1 = time.perf_counter(); match(); t2 = time.perf_counter()
+        te.append(t1 - t0); tm.append(t2 - t1)
+    te, tm = float(np.median(te[1:])), float(np.median(tm[1:]))
+    nm = d_nm.cpu().numpy()
+    out = {"workload": "BASELINE.json configs[2]: %d frames 752x480, nFeatures 1000; SearchForInitialization(window 100, 0.9) on %d consecutive pairs"
+                       % (nframes, nframes - 1),
+           "extract_ms": te * 1e3, "match_ms": tm * 1e3, "frames_per_s_extract_and_match": nframes / (te + tm),
+           "pairs_per_s_match": (nframes - 1) / tm, "mean_matches_per_pair": float(nm.mean())}
+    if with_cpu:
+        from tests import oracle_lib
+        k_h = d_k[:9].cpu().numpy().view(KEYPOINT_DTYPE).reshape(9, cap); d_h = d_d[:9].cpu().numpy(); n_h = d_n[:9].cpu().numpy()
+        o = oracle_lib.OracleMatcher(0.9, True)
+        ts, same = [], True
+        m_h = d_m[:8].cpu().numpy()
+        for p in range(8):
+            F1 = scenes.make_frame(k_h[p, :n_h[p]], d_h[p, :n_h[p]], w, h); F2 = scenes.make_frame(k_h[p + 1, :n_h[p + 1]], d_h[p + 1, :n_h[p + 1]], w, h)
+            prev = np.ascontiguousarray(np.stack([F1.mvKeysUn["x"], F1.mvKeysUn["y"]], 1), np.float32)
+            t0 = time.perf_counter(); n_o, m_o = o.SearchForInitialization(F1, F2, prev, 100); ts.append(time.perf_counter() - t0)
+            same = same and n_o == int(nm[p]) and np.array_equal(m_o, m_h[p, :n_h[p]])
+        out["cpu_port"] = {"match_ms_per_pair": float(np.median(ts) * 1e3), "pairs_per_s_one_core": 1.0 / float(np.median(ts))}
+        out["identical_to_cpu_port"] = bool(same)
+    ex.close(); ctx.close()
+    return out
+
+
 def run_ours(args, rank, world, local_rank):
     import torch
     from orb_slam_b200 import KEYPOINT_DTYPE, ORBextractor
@@ -610,6 +671,7 @@ def run_ours(args, rank, world, local_rank):
         if world == 1 and not args.no_frontend:
             line["kitti_stereo_frontend"] = run_stereo_frontend(local_rank, not args.no_cpu)
             line["vocabulary"] = run_vocabulary(local_rank, not args.no_cpu)
+            line["euroc_batch"] = run_euroc_batch(local_rank, not args.no_cpu)
         if world == 1 and not args.no_cpu:
             from tests import oracle_lib
             kind = "reference" if oracle_lib.have_ref() else "port"

@@ -13,9 +13,10 @@
 namespace orbm {
 
 __global__ void __launch_bounds__(1024) grid_build_batch_kernel(const orbx_keypoint* __restrict__ keys, const int32_t* __restrict__ counts,
-                                                                int cap, GridParams g, int32_t* __restrict__ cellOf,
+                                                                int cap, GridParams g, int onlyLevel, int32_t* __restrict__ cellOf,
                                                                 int32_t* __restrict__ cellStart, int32_t* __restrict__ items) {
     __shared__ int cnt[GRID_CELLS + 1];
+    __shared__ int fill[GRID_CELLS];
     __shared__ int warpSum[32];
     const int f = blockIdx.x;
     const orbx_keypoint* keysUn = keys + (size_t)f * cap;
@@ -28,7 +29,11 @@ __global__ void __launch_bounds__(1024) grid_build_batch_kernel(const orbx_keypo
         const int px = (int)roundf(__fmul_rn(__fsub_rn(keysUn[i].x, g.minX), g.invW));       // :507-509
         const int py = (int)roundf(__fmul_rn(__fsub_rn(keysUn[i].y, g.minY), g.invH));
         int c = -1;
-        if (!(px < 0 || px >= ORBM_GRID_COLS || py < 0 || py >= ORBM_GRID_ROWS)) { c = px * ORBM_GRID_ROWS + py; atomicAdd(&cnt[c], 1); }
+        // onlyLevel >= 0: a grid of that pyramid level's key points alone - what GetFeaturesInArea(x, y, r, l, l) returns from the
+        // full grid, in the same order (the level gate of :449-479 only drops entries)
+        if (!(px < 0 || px >= ORBM_GRID_COLS || py < 0 || py >= ORBM_GRID_ROWS) && (onlyLevel < 0 || keysUn[i].octave == onlyLevel)) {
+            c = px * ORBM_GRID_ROWS + py; atomicAdd(&cnt[c], 1);
+        }
         cellOf[i] = c;
     }
     __syncthreads();
@@ -47,12 +52,24 @@ __global__ void __launch_bounds__(1024) grid_build_batch_kernel(const orbx_keypo
     for (int c = b; c < e; c++) { const int v = cnt[c]; cnt[c] = run; cellStart[c] = run; run += v; }
     if (tid == blockDim.x - 1) { cnt[GRID_CELLS] = run; cellStart[GRID_CELLS] = run; }
     __syncthreads();
-    for (int i = tid; i < N; i += blockDim.x) {          // stable placement (push_back order, :300-310)
+    // placement: scatter with a per-cell counter, then order each cell's few entries ascending = push_back order (:300-310)
+    for (int c = tid; c < GRID_CELLS; c += blockDim.x) fill[c] = 0;
+    __syncthreads();
+    for (int i = tid; i < N; i += blockDim.x) {
         const int c = cellOf[i];
-        if (c < 0) continue;
-        int rank = 0;
-        for (int j = 0; j < i; j++) rank += (cellOf[j] == c);
-        items[cnt[c] + rank] = i;
+        if (c >= 0) items[cnt[c] + atomicAdd(&fill[c], 1)] = i;
+    }
+    __syncthreads();
+    for (int c = tid; c < GRID_CELLS; c += blockDim.x) {
+        const int n = fill[c];
+        if (n < 2) continue;
+        int32_t* it = items + cnt[c];
+        for (int x = 1; x < n; x++) {                    // insertion sort of a handful of indices
+            const int v = it[x];
+            int y = x - 1;
+            while (y >= 0 && it[y] > v) { it[y + 1] = it[y]; y--; }
+            it[y + 1] = v;
+        }
     }
 }
 
@@ -104,14 +121,31 @@ __global__ void __launch_bounds__(128) init_match_batch_kernel(InitBatchArgs a) 
         int bestIdx = -1;
         uint32_t second = 0xfff;
         int pos = 0;
-        for (int ix = cr.x0; ix <= cr.x1; ix++) {
-            const int s = cellStart[ix * ORBM_GRID_ROWS + cr.y0], e = cellStart[ix * ORBM_GRID_ROWS + cr.y1 + 1];
-            for (int k0 = s; k0 < e; k0 += 32) {
-                const int k = k0 + lane;
+        // The window's cells (ix, y0..y1) are one contiguous item range per grid column; up to 32 columns are fetched at once
+        // (lane = column) and their ranges walked as ONE flattened sequence, which is the reference's enumeration order
+        // (ix outer, iy inner, insertion order) in ceil(total / 32) steps instead of one dependent step per column.
+        for (int c0 = cr.x0; c0 <= cr.x1; c0 += 32) {
+            const int ix = c0 + lane;
+            int s = 0, len = 0;
+            if (ix <= cr.x1) { s = cellStart[ix * ORBM_GRID_ROWS + cr.y0]; len = cellStart[ix * ORBM_GRID_ROWS + cr.y1 + 1] - s; }
+            int incl = len;
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) { const int t = __shfl_up_sync(0xffffffffu, incl, d); if (lane >= d) incl += t; }
+            const int total = __shfl_sync(0xffffffffu, incl, 31);
+            for (int t0 = 0; t0 < total; t0 += 32) {
+                const int t = t0 + lane;
+                int col = 0;                             // first column whose inclusive end exceeds t
+#pragma unroll
+                for (int step = 16; step > 0; step >>= 1) {
+                    const int v = __shfl_sync(0xffffffffu, incl, col + step - 1);
+                    if (t >= v) col += step;
+                }
+                col = min(col, 31);
+                const int cs = __shfl_sync(0xffffffffu, s, col), cincl = __shfl_sync(0xffffffffu, incl, col), clen = __shfl_sync(0xffffffffu, len, col);
                 bool ok = false;
                 int idx = -1;
-                if (k < e) {
-                    idx = items[k];
+                if (t < total) {
+                    idx = items[cs + (t - (cincl - clen))];
                     const orbx_keypoint kp = K2[idx];
                     ok = kp.octave == 0;                 // minLevel = maxLevel = 0, :449-479
                     const float dx = __fsub_rn(kp.x, q.x), dy = __fsub_rn(kp.y, q.y);

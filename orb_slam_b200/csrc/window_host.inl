@@ -717,7 +717,7 @@ extern "C" int orbm_search_for_initialization_batch_device(orbm_t* m, const orbx
     if ((rc = m->w4.reserve(pc * 4))) return rc;                                   // vnMatches21
     if ((rc = m->w5.reserve(pc))) return rc;                                       // rotation bins
     const GridParams g{mnMinX, mnMinY, invW, invH};
-    grid_build_batch_kernel<<<nframes, 1024, 0, m->stream>>>(d_keys, d_n, cap, g, (int32_t*)m->w0.p, (int32_t*)m->w1.p, (int32_t*)m->w2.p);
+    grid_build_batch_kernel<<<nframes, 1024, 0, m->stream>>>(d_keys, d_n, cap, g, 0, (int32_t*)m->w0.p, (int32_t*)m->w1.p, (int32_t*)m->w2.p);
     InitBatchArgs a{};
     a.keys = d_keys; a.desc = (const uint32_t*)d_desc; a.counts = d_n; a.cap = cap; a.pairs = d_pairs; a.npairs = npairs;
     a.cellStart = (const int32_t*)m->w1.p; a.items = (const int32_t*)m->w2.p; a.g = g;
