@@ -127,6 +127,15 @@ int orbx_stereo_match(orbx_t* left, orbx_t* right, int frame, const orbx_keypoin
                       const orbx_keypoint* keysR, const uint8_t* descR, int nR, float mbf, float mb, float* uRight,
                       float* depth, int* n_matched);
 
+/* The same for a batch of n stereo pairs, device-resident end to end: both extractors have just run
+ * orbx_extract_batch_device on the n left / n right images (their pyramids are still resident), and d_keys* / d_desc* / d_n*
+ * are those calls' outputs ([n][cap] key points, [n][cap][32] descriptors, [n] counts).  d_uRight / d_depth: [n][cap]
+ * (mvuRight / mvDepth, -1 = no match, entries past a frame's count untouched), d_nMatched: [n].  Enqueued on left's stream
+ * (orbx_stream(left)); BASELINE.json configs[1] as a batch. */
+int orbx_stereo_match_batch_device(orbx_t* left, orbx_t* right, int n, const orbx_keypoint* d_keysL, const uint8_t* d_descL,
+                                   const int* d_nL, const orbx_keypoint* d_keysR, const uint8_t* d_descR, const int* d_nR, int cap,
+                                   float mbf, float mb, float* d_uRight, float* d_depth, int* d_nMatched);
+
 /* Number of kernel launches one orbx_extract_batch* call enqueues (for bench.py's gpu_launches). */
 int orbx_launches_per_call(const orbx_t* ex);
 

@@ -56,6 +56,8 @@ def lib() -> C.CDLL:
     L.orbx_get_level.argtypes = [vp, i, i, i, i, vp, sz]; L.orbx_get_level.restype = i
     L.orbx_get_candidates.argtypes = [vp, i, i, vp, i, C.POINTER(i)]; L.orbx_get_candidates.restype = i
     L.orbx_stereo_match.argtypes = [vp, vp, i, vp, vp, i, vp, vp, i, f, f, vp, vp, C.POINTER(i)]; L.orbx_stereo_match.restype = i
+    L.orbx_stereo_match_batch_device.argtypes = [vp, vp, i, vp, vp, vp, vp, vp, vp, i, f, f, vp, vp, vp]
+    L.orbx_stereo_match_batch_device.restype = i
     L.orbx_launches_per_call.argtypes = [vp]; L.orbx_launches_per_call.restype = i
     L.orbx_set_profiling.argtypes = [vp, i]; L.orbx_set_profiling.restype = i
     L.orbx_stage_times.argtypes = [vp, vp, i]; L.orbx_stage_times.restype = i

@@ -890,7 +890,7 @@ int orbx_stereo_match(orbx_t* left, orbx_t* right, int frame, const orbx_keypoin
     a.mbf = mbf; a.maxD = mbf / mb;                           // minZ = mb, maxD = mbf / minZ, :678-682
     a.uRight = (float*)(d + oU); a.depth = (float*)(d + oZ); a.sad = (int*)(d + oS);
     stereo_match_kernel<<<(nL + 7) / 8, 256, 0, st>>>(a);
-    stereo_outlier_kernel<<<1, 1024, 0, st>>>(nL, a.sad, a.uRight, a.depth, (int*)(d + oN));
+    stereo_outlier_kernel<<<1, 1024, 0, st>>>(nL, a.sad, a.uRight, a.depth, (int*)(d + oN), 0, nullptr);
     CK(cudaGetLastError());
     CK(cudaMemcpyAsync(uRight, a.uRight, (size_t)nL * 4, cudaMemcpyDeviceToHost, st));
     CK(cudaMemcpyAsync(depth, a.depth, (size_t)nL * 4, cudaMemcpyDeviceToHost, st));
@@ -898,6 +898,55 @@ int orbx_stereo_match(orbx_t* left, orbx_t* right, int frame, const orbx_keypoin
     CK(cudaMemcpyAsync(&nm, d + oN, 4, cudaMemcpyDeviceToHost, st));
     CK(cudaStreamSynchronize(st));
     if (n_matched) *n_matched = nm;
+    return ORBX_OK;
+}
+
+// Frame::ComputeStereoMatches for a whole batch of stereo pairs whose images both extractors have just processed with
+// orbx_extract_batch_device (same n): key points, descriptors and counts are those calls' device outputs, the pyramids are
+// still resident in the two workspaces of each extractor.  Enqueued on left's stream.
+int orbx_stereo_match_batch_device(orbx_t* left, orbx_t* right, int n, const orbx_keypoint* d_keysL, const uint8_t* d_descL,
+                                   const int* d_nL, const orbx_keypoint* d_keysR, const uint8_t* d_descR, const int* d_nR, int cap,
+                                   float mbf, float mb, float* d_uRight, float* d_depth, int* d_nMatched) {
+    if (!left || !right || n <= 0 || !d_keysL || !d_descL || !d_nL || !d_keysR || !d_descR || !d_nR || cap <= 0 || cap >= 65536 ||
+        !d_uRight || !d_depth || !d_nMatched || !(mb > 0))
+        return ORBX_E_INVALID;
+    std::lock_guard<std::mutex> lk(left->mtx);
+    const int h0 = (n + 1) / 2, h1 = n - h0;                  // the split orbx_extract_batch_device made
+    if (!left->haveGeom || !right->haveGeom || left->device != right->device || left->g.width != right->g.width ||
+        left->g.height != right->g.height || left->nlevels != right->nlevels || left->ws[0].lastFrames != h0 ||
+        right->ws[0].lastFrames != h0 || (h1 && (left->ws[1].lastFrames != h1 || right->ws[1].lastFrames != h1)))
+        return ORBX_E_INVALID;
+    CK(cudaSetDevice(left->device));
+    for (auto& w : right->ws) CK(cudaStreamSynchronize(w.stream));          // the right pyramids are complete
+    CK(cudaStreamSynchronize(left->ws[1].stream));
+    orbx_extractor* e = left;
+    const size_t need = (size_t)n * cap * 4 + 256;                           // SAD scratch
+    if (e->stereoBytes < need) {
+        CK(cudaStreamSynchronize(e->stream));
+        cudaFree(e->d_stereo); e->d_stereo = nullptr; e->stereoBytes = 0;
+        CK(cudaMalloc(&e->d_stereo, need));
+        e->stereoBytes = need;
+    }
+    cudaStream_t st = e->stream;
+    for (int half = 0; half < 2; half++) {
+        const int f0 = half ? h0 : 0, cnt = half ? h1 : h0;
+        if (cnt == 0) continue;
+        const size_t o = (size_t)f0 * cap;
+        StereoArgs a{};
+        a.keysL = d_keysL + o; a.descL = (const uint32_t*)(d_descL + o * 32); a.keysR = d_keysR + o; a.descR = (const uint32_t*)(d_descR + o * 32);
+        a.pyrL = left->ws[half].d_pyr; a.pyrR = right->ws[half].d_pyr; a.pyrFrameStride = e->g.pyrBytes;
+        a.nlevels = e->nlevels;
+        for (int l = 0; l < e->nlevels; l++) {
+            a.pyrOff[l] = e->g.lv[l].pyrOff; a.pitch[l] = e->g.lv[l].pitch; a.cols[l] = e->g.lv[l].w;
+            a.sf[l] = e->sf[l]; a.isf[l] = e->isf[l];
+        }
+        a.mbf = mbf; a.maxD = mbf / mb;
+        a.uRight = d_uRight + o; a.depth = d_depth + o; a.sad = (int*)e->d_stereo + o;
+        a.cap = cap; a.nLdev = d_nL + f0; a.nRdev = d_nR + f0;
+        stereo_match_kernel<<<dim3((cap + 7) / 8, cnt), 256, 0, st>>>(a);
+        stereo_outlier_kernel<<<cnt, 1024, 0, st>>>(0, a.sad, a.uRight, a.depth, d_nMatched + f0, cap, a.nLdev);
+    }
+    CK(cudaGetLastError());
     return ORBX_OK;
 }
 

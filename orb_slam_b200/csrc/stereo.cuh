@@ -23,14 +23,25 @@ struct StereoArgs {
     float sf[ORB_MAX_LEVELS], isf[ORB_MAX_LEVELS];
     float mbf, maxD;
     float* uRight; float* depth; int* sad;          // [nL]; sad = -1 where unmatched
+    // batch of frames (blockIdx.y = frame): every array above is [frames][cap], the counts come from the device
+    int cap;                                        // 0: single frame
+    const int* nLdev; const int* nRdev;
+    unsigned long long pyrFrameStride;
 };
 
 __global__ void __launch_bounds__(256) stereo_match_kernel(StereoArgs a) {
     const int lane = threadIdx.x & 31;
     const int iL = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
-    if (iL >= a.nL) return;
-    const orbx_keypoint kpL = a.keysL[iL];
-    if (lane == 0) { a.uRight[iL] = -1.0f; a.depth[iL] = -1.0f; a.sad[iL] = -1; }     // :634-635
+    // (the argument block stays in the constant bank: frame offsets go to locals)
+    const size_t fr = a.cap ? blockIdx.y : 0, fo = fr * (size_t)a.cap;
+    const int nL = a.cap ? min(a.nLdev[fr], a.cap) : a.nL, nR = a.cap ? min(a.nRdev[fr], a.cap) : a.nR;
+    const orbx_keypoint* keysL = a.keysL + fo; const uint32_t* descL = a.descL + fo * 8;
+    const orbx_keypoint* keysR = a.keysR + fo; const uint32_t* descR = a.descR + fo * 8;
+    const uint8_t* pyrL = a.pyrL + fr * a.pyrFrameStride; const uint8_t* pyrR = a.pyrR + fr * a.pyrFrameStride;
+    float* uRight = a.uRight + fo; float* depth = a.depth + fo; int* sad = a.sad + fo;
+    if (iL >= nL) return;
+    const orbx_keypoint kpL = keysL[iL];
+    if (lane == 0) { uRight[iL] = -1.0f; depth[iL] = -1.0f; sad[iL] = -1; }     // :634-635
     const int levelL = kpL.octave;
     const float vL = kpL.y, uL = kpL.x;
     const int rowL = (int)vL;                                   // vRowIndices[vL]
@@ -38,11 +49,11 @@ __global__ void __launch_bounds__(256) stereo_match_kernel(StereoArgs a) {
     if (maxU < 0) return;
     uint32_t dl[8];
 #pragma unroll
-    for (int k = 0; k < 8; k++) dl[k] = a.descL[(size_t)iL * 8 + k];
+    for (int k = 0; k < 8; k++) dl[k] = descL[(size_t)iL * 8 + k];
     // ---- coarse match: lowest Hamming distance below TH_HIGH, lowest iR on ties (strict '<' in ascending iR)
     uint32_t best = (100u << 16);                               // (bestDist = TH_HIGH, no index)
-    for (int iR = lane; iR < a.nR; iR += 32) {
-        const orbx_keypoint kpR = a.keysR[iR];
+    for (int iR = lane; iR < nR; iR += 32) {
+        const orbx_keypoint kpR = keysR[iR];
         const float r = __fmul_rn(2.0f, a.sf[kpR.octave]);
         const int maxr = (int)ceilf(__fadd_rn(kpR.y, r)), minr = (int)floorf(__fsub_rn(kpR.y, r));
         if (rowL < minr || rowL > maxr) continue;              // iR is not in vRowIndices[vL]
@@ -50,7 +61,7 @@ __global__ void __launch_bounds__(256) stereo_match_kernel(StereoArgs a) {
         if (!(kpR.x >= minU && kpR.x <= maxU)) continue;
         int d = 0;
 #pragma unroll
-        for (int k = 0; k < 8; k++) d += __popc(dl[k] ^ a.descR[(size_t)iR * 8 + k]);
+        for (int k = 0; k < 8; k++) d += __popc(dl[k] ^ descR[(size_t)iR * 8 + k]);
         if (d < 100) best = min(best, ((uint32_t)d << 16) | (uint32_t)iR);
     }
 #pragma unroll
@@ -59,7 +70,7 @@ __global__ void __launch_bounds__(256) stereo_match_kernel(StereoArgs a) {
     if (!(bestDist < 75)) return;                               // thOrbDist = (TH_HIGH + TH_LOW) / 2, :639,:757
     const int bestIdxR = (int)(best & 0xffffu);
     // ---- SAD refinement on level `levelL` of both pyramids
-    const float uR0 = a.keysR[bestIdxR].x;
+    const float uR0 = keysR[bestIdxR].x;
     const float sc = a.isf[levelL];
     const float scaleduL = roundf(__fmul_rn(kpL.x, sc)), scaledvL = roundf(__fmul_rn(kpL.y, sc));
     const float scaleduR0 = roundf(__fmul_rn(uR0, sc));
@@ -67,8 +78,8 @@ __global__ void __launch_bounds__(256) stereo_match_kernel(StereoArgs a) {
     const float iniu = scaleduR0 + L - w, endu = scaleduR0 + L + w + 1;
     if (iniu < 0 || endu >= (float)a.cols[levelL]) return;     // :789
     const int pitch = a.pitch[levelL];
-    const uint8_t* imL = a.pyrL + a.pyrOff[levelL] + (size_t)ORB_EDGE * pitch + ORB_XPAD;
-    const uint8_t* imR = a.pyrR + a.pyrOff[levelL] + (size_t)ORB_EDGE * pitch + ORB_XPAD;
+    const uint8_t* imL = pyrL + a.pyrOff[levelL] + (size_t)ORB_EDGE * pitch + ORB_XPAD;
+    const uint8_t* imR = pyrR + a.pyrOff[levelL] + (size_t)ORB_EDGE * pitch + ORB_XPAD;
     const int v0 = (int)(scaledvL - w), uL0 = (int)(scaleduL - w), uRc = (int)scaleduR0;
     const int cL = imL[(v0 + w) * pitch + uL0 + w];
     // lane owns window pixels p = lane, lane+32, lane+64, lane+96 (< 121)
@@ -108,13 +119,18 @@ __global__ void __launch_bounds__(256) stereo_match_kernel(StereoArgs a) {
     float disparity = __fsub_rn(uL, bestuR);
     if (disparity >= 0 && disparity < a.maxD) {
         if (disparity <= 0) { disparity = 0.01f; bestuR = (float)((double)uL - 0.01); }
-        if (lane == 0) { a.depth[iL] = __fdiv_rn(a.mbf, disparity); a.uRight[iL] = bestuR; a.sad[iL] = bestS; }
+        if (lane == 0) { depth[iL] = __fdiv_rn(a.mbf, disparity); uRight[iL] = bestuR; sad[iL] = bestS; }
     }
 }
 
 // median-based outlier cut over the matched keypoints of one frame (single block)
+// (batch: one block per frame, cap > 0, counts from nLdev)
 __global__ void __launch_bounds__(1024) stereo_outlier_kernel(int nL, const int* __restrict__ sad, float* uRight, float* depth,
-                                                              int* nMatched) {
+                                                              int* nMatched, int cap, const int* __restrict__ nLdev) {
+    if (cap) {
+        const size_t f = blockIdx.x, o = f * (size_t)cap;
+        nL = min(nLdev[f], cap); sad += o; uRight += o; depth += o; nMatched += f;
+    }
     __shared__ int hist[256];
     __shared__ int sel[4];        // [0] = number of matches, [1] = chosen high byte, [2] = rank inside it, [3] = median
     const int tid = threadIdx.x;

@@ -118,6 +118,16 @@ class ORBextractor:
               "orbx_stereo_match")
         return u, z, n.value
 
+    def stereo_match_batch_device(self, right: "ORBextractor", n, d_keysL, d_descL, d_nL, d_keysR, d_descR, d_nR, cap, mbf, mb,
+                                  d_uRight, d_depth, d_nMatched):
+        """Frame::ComputeStereoMatches for the n stereo pairs both extractors have just processed with
+        orbx_extract_batch_device; every d_* argument is a device pointer (int).  Enqueued on this extractor's stream."""
+        check(self._L.orbx_stereo_match_batch_device(self._h, right._h, n, d_keysL, d_descL, d_nL, d_keysR, d_descR, d_nR, cap,
+                                                     mbf, mb, d_uRight, d_depth, d_nMatched), "orbx_stereo_match_batch_device")
+
+    def synchronize(self):
+        check(self._L.orbx_synchronize(self._h), "orbx_synchronize")
+
     @property
     def handle(self):
         return self._h

@@ -42,3 +42,52 @@ def test_stereo_edge_cases():
     assert len(kb) == 0
     u, z, n = a.stereo_match(b, ka, da, kb, db.reshape(-1, 32), 40.0, 0.08)
     assert n == 0 and (u == -1).all() and (z == -1).all()
+
+
+@pytest.mark.parametrize("w,h,nf,n", [(1241, 376, 2000, 5), (752, 480, 1000, 2), (640, 480, 500, 1)])
+def test_stereo_batch_device_equals_oracle_frame_by_frame(w, h, nf, n):
+    """orbx_stereo_match_batch_device: n stereo pairs extracted and matched without leaving the device; mvuRight / mvDepth of every
+    pair bit-exact against the oracle run on that pair's own key points, descriptors and pyramids."""
+    import torch
+    from orb_slam_b200 import KEYPOINT_DTYPE, ORBextractor
+    from orb_slam_b200._lib import check
+    disps = [23, 9, 0, 41, 15][:n]
+    lefts = np.stack([synth_frame(w, h, 80 + i) for i in range(n)])
+    rights = np.stack([synth_frame(w, h, 80 + i, shift=(-disps[i], 0)) for i in range(n)])
+    rng = np.random.default_rng(3)
+    rights = np.clip(rights.astype(np.int16) + rng.integers(-3, 4, rights.shape), 0, 255).astype(np.uint8)   # sensor noise
+    if n > 1:
+        rights[1] = 90                                                 # a textureless right image: no right key points
+    mbf = float(KITTI_BF); mb = float(np.float32(KITTI_BF) / KITTI_K[0, 0])
+    gl, gr = ORBextractor(nf, 1.2, 8, 20, 7), ORBextractor(nf, 1.2, 8, 20, 7)
+    cap = gl.max_keypoints(w, h)
+    dev = {}
+    for name, ex, imgs in (("L", gl, lefts), ("R", gr, rights)):
+        d_img = torch.from_numpy(imgs).cuda()
+        d_k = torch.zeros((n, cap, 28), dtype=torch.uint8, device="cuda"); d_d = torch.zeros((n, cap, 32), dtype=torch.uint8, device="cuda")
+        d_n = torch.zeros(n, dtype=torch.int32, device="cuda")
+        torch.cuda.synchronize()
+        check(ex._L.orbx_extract_batch_device(ex.handle, d_img.data_ptr(), n, w, h, w, w * h, d_k.data_ptr(), d_d.data_ptr(), cap,
+                                              d_n.data_ptr()), "orbx_extract_batch_device")
+        dev[name] = (d_img, d_k, d_d, d_n)
+    d_u = torch.full((n, cap), 7.0, dtype=torch.float32, device="cuda"); d_z = torch.full((n, cap), 7.0, dtype=torch.float32, device="cuda")
+    d_nm = torch.full((n,), -5, dtype=torch.int32, device="cuda")
+    torch.cuda.synchronize()
+    gl.stereo_match_batch_device(gr, n, dev["L"][1].data_ptr(), dev["L"][2].data_ptr(), dev["L"][3].data_ptr(), dev["R"][1].data_ptr(),
+                                 dev["R"][2].data_ptr(), dev["R"][3].data_ptr(), cap, mbf, mb, d_u.data_ptr(), d_z.data_ptr(), d_nm.data_ptr())
+    gl.synchronize()
+    u, z, nm = d_u.cpu().numpy(), d_z.cpu().numpy(), d_nm.cpu().numpy()
+    kL = dev["L"][1].cpu().numpy().view(KEYPOINT_DTYPE).reshape(n, cap); dL = dev["L"][2].cpu().numpy(); nL = dev["L"][3].cpu().numpy()
+    kR = dev["R"][1].cpu().numpy().view(KEYPOINT_DTYPE).reshape(n, cap); dR = dev["R"][2].cpu().numpy(); nR = dev["R"][3].cpu().numpy()
+    for i in range(n):
+        ol, orr = OracleExtractor(nf, 1.2, 8, 20, 7), OracleExtractor(nf, 1.2, 8, 20, 7)
+        ol(lefts[i]); orr(rights[i])                                   # the oracle's pyramids (bit-exact with the device's)
+        ou, oz, on = oracle_stereo_matches(ol, orr, kL[i, :nL[i]], dL[i, :nL[i]], kR[i, :nR[i]], dR[i, :nR[i]].reshape(-1, 32), mbf, mb)
+        assert nm[i] == on, i
+        assert u[i, :nL[i]].tobytes() == ou.tobytes() and z[i, :nL[i]].tobytes() == oz.tobytes(), i
+        assert (u[i, nL[i]:] == 7.0).all()                             # entries past the frame's count untouched
+        if i != 1:
+            assert on > 0.3 * nL[i]
+        else:
+            assert on == 0 and nR[i] == 0
+    gl.close(); gr.close()
