@@ -504,6 +504,53 @@ def run_euroc_batch(local_rank, with_cpu, nframes=1024):
     return out
 
 
+def run_stereo_batch(local_rank, npairs=256):
+    """BASELINE.json configs[1] as a batch: npairs KITTI-size stereo pairs; both images extracted on the device (one extractor
+    per camera, as src/Frame.cc:94-103) and Frame::ComputeStereoMatches on all pairs, nothing leaving HBM in between."""
+    import torch
+    from orb_slam_b200 import ORBextractor
+    from orb_slam_b200._lib import check
+    from orb_slam_b200.synth import synth_frame
+    from tests import scenes
+    distinct = 8
+    L_ = np.stack([synth_frame(W_, H_, 600 + i) for i in range(distinct)])
+    R_ = np.stack([synth_frame(W_, H_, 600 + i, shift=(-(9 + 4 * i), 0)) for i in range(distinct)])
+    rng = np.random.default_rng(1)
+    R_ = np.clip(R_.astype(np.int16) + rng.integers(-3, 4, R_.shape), 0, 255).astype(np.uint8)
+    idx = torch.arange(npairs, device="cuda") % distinct
+    dL, dR = torch.from_numpy(L_).cuda()[idx].contiguous(), torch.from_numpy(R_).cuda()[idx].contiguous()
+    exL, exR = ORBextractor(NFEAT, 1.2, 8, 20, 7, device=local_rank), ORBextractor(NFEAT, 1.2, 8, 20, 7, device=local_rank)
+    cap = exL.max_keypoints(W_, H_)
+    out = {}
+    bufs = {}
+    for name in "LR":
+        bufs[name] = (torch.zeros((npairs, cap, 28), dtype=torch.uint8, device="cuda"), torch.zeros((npairs, cap, 32), dtype=torch.uint8, device="cuda"),
+                      torch.zeros(npairs, dtype=torch.int32, device="cuda"))
+    d_u = torch.zeros((npairs, cap), dtype=torch.float32, device="cuda"); d_z = torch.zeros((npairs, cap), dtype=torch.float32, device="cuda")
+    d_nm = torch.zeros(npairs, dtype=torch.int32, device="cuda")
+    mbf = float(scenes.KITTI_BF); mb = float(np.float32(scenes.KITTI_BF) / scenes.KITTI_K[0, 0])
+    torch.cuda.synchronize()
+    te, ts = [], []
+    for rep in range(5):
+        t0 = time.perf_counter()
+        for ex, img, (k, d, n) in ((exL, dL, bufs["L"]), (exR, dR, bufs["R"])):
+            check(ex._L.orbx_extract_batch_device(ex.handle, img.data_ptr(), npairs, W_, H_, W_, W_ * H_, k.data_ptr(), d.data_ptr(), cap,
+                                                  n.data_ptr()), "orbx_extract_batch_device")
+        exL.synchronize(); exR.synchronize()
+        t1 = time.perf_counter()
+        exL.stereo_match_batch_device(exR, npairs, bufs["L"][0].data_ptr(), bufs["L"][1].data_ptr(), bufs["L"][2].data_ptr(),
+                                      bufs["R"][0].data_ptr(), bufs["R"][1].data_ptr(), bufs["R"][2].data_ptr(), cap, mbf, mb,
+                                      d_u.data_ptr(), d_z.data_ptr(), d_nm.data_ptr())
+        exL.synchronize()
+        t2 = time.perf_counter()
+        te.append(t1 - t0); ts.append(t2 - t1)
+    te, ts = float(np.median(te[1:])), float(np.median(ts[1:]))
+    out = {"stereo_pairs": npairs, "extract_both_ms": te * 1e3, "stereo_match_ms": ts * 1e3, "stereo_pairs_per_s": npairs / (te + ts),
+           "mean_stereo_matches": float(d_nm.float().mean().item())}
+    exL.close(); exR.close()
+    return out
+
+
 def run_ours(args, rank, world, local_rank):
     import torch
     from orb_slam_b200 import KEYPOINT_DTYPE, ORBextractor
@@ -670,6 +717,7 @@ def run_ours(args, rank, world, local_rank):
             line["hamming_2nn"] = ham
         if world == 1 and not args.no_frontend:
             line["kitti_stereo_frontend"] = run_stereo_frontend(local_rank, not args.no_cpu)
+            line["kitti_stereo_frontend"]["batch"] = run_stereo_batch(local_rank)
             line["vocabulary"] = run_vocabulary(local_rank, not args.no_cpu)
             line["euroc_batch"] = run_euroc_batch(local_rank, not args.no_cpu)
         if world == 1 and not args.no_cpu:

@@ -920,7 +920,12 @@ int orbx_stereo_match_batch_device(orbx_t* left, orbx_t* right, int n, const orb
     for (auto& w : right->ws) CK(cudaStreamSynchronize(w.stream));          // the right pyramids are complete
     CK(cudaStreamSynchronize(left->ws[1].stream));
     orbx_extractor* e = left;
-    const size_t need = (size_t)n * cap * 4 + 256;                           // SAD scratch
+    const int nRows = e->g.height;
+    const bool rows = nRows <= STEREO_MAX_ROWS;                              // else: every right key point is scanned
+    const size_t oRowStart = ((size_t)n * cap * 4 + 255) & ~(size_t)255;
+    const size_t oRowItems = oRowStart + (rows ? (((size_t)n * (nRows + 1) * 4 + 255) & ~(size_t)255) : 0);
+    const int rowItemsCap = cap * STEREO_BAND_MAX;
+    const size_t need = oRowItems + (rows ? (size_t)n * rowItemsCap * 2 : 0) + 256;      // SAD scratch | rowStart | rowItems
     if (e->stereoBytes < need) {
         CK(cudaStreamSynchronize(e->stream));
         cudaFree(e->d_stereo); e->d_stereo = nullptr; e->stereoBytes = 0;
@@ -943,6 +948,13 @@ int orbx_stereo_match_batch_device(orbx_t* left, orbx_t* right, int n, const orb
         a.mbf = mbf; a.maxD = mbf / mb;
         a.uRight = d_uRight + o; a.depth = d_depth + o; a.sad = (int*)e->d_stereo + o;
         a.cap = cap; a.nLdev = d_nL + f0; a.nRdev = d_nR + f0;
+        if (rows) {
+            a.nRows = nRows; a.rowItemsCap = rowItemsCap;
+            int* rowStart = (int*)(e->d_stereo + oRowStart) + (size_t)f0 * (nRows + 1);
+            unsigned short* rowItems = (unsigned short*)(e->d_stereo + oRowItems) + (size_t)f0 * rowItemsCap;
+            stereo_rows_kernel<<<cnt, 1024, 0, st>>>(a.keysR, a.nRdev, cap, a, rowStart, rowItems);
+            a.rowStart = rowStart; a.rowItems = rowItems;
+        }
         stereo_match_kernel<<<dim3((cap + 7) / 8, cnt), 256, 0, st>>>(a);
         stereo_outlier_kernel<<<cnt, 1024, 0, st>>>(0, a.sad, a.uRight, a.depth, d_nMatched + f0, cap, a.nLdev);
     }

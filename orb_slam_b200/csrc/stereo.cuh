@@ -27,7 +27,53 @@ struct StereoArgs {
     int cap;                                        // 0: single frame
     const int* nLdev; const int* nRdev;
     unsigned long long pyrFrameStride;
+    // vRowIndices (:647-673) of every frame as a CSR over image rows (stereo_rows_kernel), or NULL: scan all right key points
+    const int* rowStart; const unsigned short* rowItems; int nRows; int rowItemsCap;
 };
+
+constexpr int STEREO_MAX_ROWS = 4096;
+constexpr int STEREO_BAND_MAX = 20;                 // rows one right key point can enter: 2 * ceil(2 * scaleFactor[level]) + 2
+
+// vRowIndices: right key point iR is a candidate on the image rows floor(y - r) .. ceil(y + r), r = 2 * mvScaleFactors[octave]
+// (:658-673).  One block per frame; the order inside a row is free because the match below reduces over (distance, iR).
+__global__ void __launch_bounds__(1024) stereo_rows_kernel(const orbx_keypoint* __restrict__ keysR, const int* __restrict__ nRdev, int cap,
+                                                           StereoArgs a, int* __restrict__ rowStart, unsigned short* __restrict__ rowItems) {
+    __shared__ int cnt[STEREO_MAX_ROWS + 1];
+    __shared__ int warpSum[32];
+    const int f = blockIdx.x, tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    const int nR = min(nRdev[f], cap), nRows = a.nRows;
+    keysR += (size_t)f * cap; rowStart += (size_t)f * (nRows + 1); rowItems += (size_t)f * a.rowItemsCap;
+    for (int r = tid; r <= nRows; r += blockDim.x) cnt[r] = 0;
+    __syncthreads();
+    for (int iR = tid; iR < nR; iR += blockDim.x) {
+        const orbx_keypoint kp = keysR[iR];
+        const float r = __fmul_rn(2.0f, a.sf[kp.octave]);
+        const int maxr = min((int)ceilf(__fadd_rn(kp.y, r)), nRows - 1), minr = max((int)floorf(__fsub_rn(kp.y, r)), 0);
+        for (int y = minr; y <= maxr; y++) atomicAdd(&cnt[y], 1);
+    }
+    __syncthreads();
+    const int per = (nRows + blockDim.x - 1) / blockDim.x;
+    const int b = min(tid * per, nRows), e = min(b + per, nRows);
+    int s = 0;
+    for (int r = b; r < e; r++) s += cnt[r];
+    int inc = s;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) { const int t = __shfl_up_sync(0xffffffffu, inc, d); if (lane >= d) inc += t; }
+    if (lane == 31) warpSum[wid] = inc;
+    __syncthreads();
+    int base = 0;
+    for (int k = 0; k < wid; k++) base += warpSum[k];
+    int run = base + inc - s;
+    for (int r = b; r < e; r++) { const int v = cnt[r]; cnt[r] = run; rowStart[r] = run; run += v; }
+    if (tid == blockDim.x - 1) rowStart[nRows] = run;
+    __syncthreads();
+    for (int iR = tid; iR < nR; iR += blockDim.x) {
+        const orbx_keypoint kp = keysR[iR];
+        const float r = __fmul_rn(2.0f, a.sf[kp.octave]);
+        const int maxr = min((int)ceilf(__fadd_rn(kp.y, r)), nRows - 1), minr = max((int)floorf(__fsub_rn(kp.y, r)), 0);
+        for (int y = minr; y <= maxr; y++) rowItems[atomicAdd(&cnt[y], 1)] = (unsigned short)iR;
+    }
+}
 
 __global__ void __launch_bounds__(256) stereo_match_kernel(StereoArgs a) {
     const int lane = threadIdx.x & 31;
@@ -52,6 +98,22 @@ __global__ void __launch_bounds__(256) stereo_match_kernel(StereoArgs a) {
     for (int k = 0; k < 8; k++) dl[k] = descL[(size_t)iL * 8 + k];
     // ---- coarse match: lowest Hamming distance below TH_HIGH, lowest iR on ties (strict '<' in ascending iR)
     uint32_t best = (100u << 16);                               // (bestDist = TH_HIGH, no index)
+    if (a.rowStart) {                                           // the row's candidate list (vRowIndices[vL])
+        if (rowL >= 0 && rowL < a.nRows) {
+            const int* rs = a.rowStart + fr * (size_t)(a.nRows + 1);
+            const unsigned short* ri = a.rowItems + fr * (size_t)a.rowItemsCap;
+            for (int k = rs[rowL] + lane, e = rs[rowL + 1]; k < e; k += 32) {
+                const int iR = ri[k];
+                const orbx_keypoint kpR = keysR[iR];
+                if (kpR.octave < levelL - 1 || kpR.octave > levelL + 1) continue;
+                if (!(kpR.x >= minU && kpR.x <= maxU)) continue;
+                int d = 0;
+#pragma unroll
+                for (int w8 = 0; w8 < 8; w8++) d += __popc(dl[w8] ^ descR[(size_t)iR * 8 + w8]);
+                if (d < 100) best = min(best, ((uint32_t)d << 16) | (uint32_t)iR);
+            }
+        }
+    } else
     for (int iR = lane; iR < nR; iR += 32) {
         const orbx_keypoint kpR = keysR[iR];
         const float r = __fmul_rn(2.0f, a.sf[kpR.octave]);
