@@ -9,12 +9,15 @@
 
 #include "MapPoint.h"
 #include "KeyFrame.h"
+#include <mutex>
 #include "b200_context.h"
 
 namespace ORB_SLAM2 {
 
+#if defined(ORB_B200_STANDALONE) || defined(ORB_B200_MAPPOINT_ACCESSORS)
 namespace b200 {
 
+// needs MapPoint::GatherObservations / StoreDescriptor (two small accessors)
 void ComputeDistinctiveDescriptors(const std::vector<MapPoint*>& vpMPs) {
     std::vector<unsigned char> rows;
     std::vector<int32_t> start(1, 0);
@@ -49,9 +52,40 @@ void ComputeDistinctiveDescriptors(const std::vector<MapPoint*>& vpMPs) {
 }
 
 }  // namespace b200
+#endif
 
+// The member itself needs no change to include/MapPoint.h: it gathers and stores under mMutexFeatures exactly where the
+// reference does (:246-253, :302-305) and hands the distance matrix + median selection (:274-301) to the device.
 void MapPoint::ComputeDistinctiveDescriptors() {
-    b200::ComputeDistinctiveDescriptors(std::vector<MapPoint*>(1, this));
+    std::vector<unsigned char> rows;
+    std::map<KeyFrame*, size_t> observations;
+    {
+#ifndef ORB_B200_STANDALONE
+        std::unique_lock<std::mutex> lock1(mMutexFeatures);
+#endif
+        if (mbBad) return;
+        observations = mObservations;
+    }
+    if (observations.empty()) return;
+    for (std::map<KeyFrame*, size_t>::iterator mit = observations.begin(), mend = observations.end(); mit != mend; mit++) {
+        KeyFrame* pKF = mit->first;
+        if (!pKF->isBad()) {
+            rows.resize(rows.size() + 32);
+            std::memcpy(&rows[rows.size() - 32], pKF->mDescriptors.ptr((int)mit->second), 32);
+        }
+    }
+    if (rows.empty()) return;
+    const int32_t start[2] = {0, (int32_t)(rows.size() / 32)};
+    int32_t best = 0;
+    b200::Check(orbm_distinctive_descriptors(b200::MatcherContext(), rows.data(), start, 1, &best), "orbm_distinctive_descriptors");
+    cv::Mat d(1, 32, CV_8U);
+    std::memcpy(d.data, &rows[(size_t)best * 32], 32);
+    {
+#ifndef ORB_B200_STANDALONE
+        std::unique_lock<std::mutex> lock(mMutexFeatures);
+#endif
+        mDescriptor = d.clone();
+    }
 }
 
 }  // namespace ORB_SLAM2

@@ -4,6 +4,8 @@ import glob
 import os
 import re
 
+import pytest
+
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 
@@ -66,3 +68,18 @@ def test_cpp_dropin_library_exports_the_reference_class_symbols():
                  "ORB_SLAM2::Frame::PosInGrid(cv::KeyPoint const&, int&, int&)"]:
         assert want in syms, want
     ctypes.CDLL(so)
+
+
+@pytest.mark.skipif(not os.path.isdir("/root/reference/include"), reason="needs the reference tree (build container only)")
+@pytest.mark.parametrize("src", ["ORBmatcher_b200.cc", "Frame_grid_b200.cc", "ORBVocabulary_b200.cc", "MapPoint_b200.cc"])
+def test_host_sources_compile_against_the_references_own_headers(src):
+    """INTEGRATION.md's claim, checked: without -DORB_B200_STANDALONE and without host/lite on the include path, the drop-in
+    member implementations compile against the reference's include/{ORBmatcher,Frame,KeyFrame,MapPoint,ORBVocabulary}.h and
+    its Thirdparty/DBoW2 (OpenCV supplied by include/minicv + oracle/ref_build/cvstub, as for oracle/_ref)."""
+    import subprocess
+    host = os.path.join(ROOT, "orb_slam_b200", "csrc", "host")
+    cmd = ["g++", "-std=c++14", "-fsyntax-only", "-w", "-I" + host, "-I" + os.path.join(ROOT, "include"),
+           "-I" + os.path.join(ROOT, "oracle", "ref_build", "cvstub"), "-I" + os.path.join(ROOT, "include", "minicv"),
+           "-I/root/reference/include", "-I/root/reference", os.path.join(host, src)]
+    r = subprocess.run(cmd, capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr[-2000:]
