@@ -312,11 +312,13 @@ def run_stereo_frontend(local_rank, with_cpu):
     pairs = [(synth_frame(W_, H_, 500, shift=(-2 * i, 0)), synth_frame(W_, H_, 500, shift=(-2 * i - 15, 0))) for i in range(6)]
     out = {}
 
+    from concurrent.futures import ThreadPoolExecutor
+    pool = ThreadPoolExecutor(max_workers=1)             # the second host thread of src/Frame.cc:94-103, kept alive between frames
+
     def extract_pair(l, r, a, b):
-        res = [None, None]
-        t = threading.Thread(target=lambda: res.__setitem__(1, b(r)))
-        t.start(); res[0] = a(l); t.join()
-        return res
+        fut = pool.submit(b, r)
+        left = a(l)
+        return [left, fut.result()]
 
     def one(l, r, a, b, stereo, proj, last):
         t0 = time.perf_counter()
@@ -383,6 +385,7 @@ def run_stereo_frontend(local_rank, with_cpu):
         out["cpu_port"] = loop(oa, ob, lambda kl, dl, kr, dr: oracle_lib.oracle_stereo_matches(oa, ob, kl, dl, kr, dr, mbf, mb),
                                lambda cur, lastF, pts, obs: om.SearchByProjectionFrame(cur, lastF, pts, obs, 7.0, False)[0],
                                lambda *x: oracle_lib.OracleMatcher(0.7, True).SearchByBoWFrame(*x)[0], 8)
+    pool.shutdown()
     exL.close(); exR.close(); ctx.close()
     return out
 

@@ -71,6 +71,7 @@ struct orbx_extractor {
     cudaStream_t sIn = nullptr, sOut = nullptr;
     cudaEvent_t evIn[ORBX_NBUF] = {}, evCompute[ORBX_NBUF] = {}, evOut[ORBX_NBUF] = {};
     uint8_t* d_stereo = nullptr; size_t stereoBytes = 0;     // scratch of orbx_stereo_match
+    uint8_t* h_stereo = nullptr; size_t hStereoBytes = 0;    // its pinned staging: one H2D and one D2H per call
     int launches = 0;
     bool profile = false;                    // record one CUDA event per stage boundary
     int profiledHalves = 0;
@@ -515,6 +516,7 @@ void orbx_destroy(orbx_t* e) {
     for (auto& w : e->ws) if (w.stream) cudaStreamSynchronize(w.stream);
     free_workspace(e);
     cudaFree(e->d_err); cudaFree(e->d_stereo);
+    if (e->h_stereo) cudaFreeHost(e->h_stereo);
     for (int hlf = 0; hlf < 2; hlf++) for (int i = 0; i < 8; i++) if (e->ev[hlf][i]) cudaEventDestroy(e->ev[hlf][i]);
     if (e->evFork) cudaEventDestroy(e->evFork);
     if (e->evJoin) cudaEventDestroy(e->evJoin);
@@ -861,8 +863,12 @@ int orbx_stereo_match(orbx_t* left, orbx_t* right, int frame, const orbx_keypoin
     const size_t kb = sizeof(orbx_keypoint);
     const size_t oKL = 0, oDL = oKL + (((size_t)nL * kb + 255) & ~(size_t)255), oKR = oDL + (size_t)nL * 32 + 256;
     const size_t oDR = oKR + (((size_t)nR * kb + 255) & ~(size_t)255), oU = oDR + (size_t)std::max(nR, 1) * 32 + 256;
-    const size_t oZ = oU + (size_t)nL * 4 + 256, oS = oZ + (size_t)nL * 4 + 256, oN = oS + (size_t)nL * 4 + 256, need = oN + 256;
+    const size_t oZ = oU + (size_t)nL * 4 + 256, oS = oZ + (size_t)nL * 4 + 256, oN = oS + (size_t)nL * 4 + 256;
     orbx_extractor* e = left;
+    const int nRows = e->g.height;
+    const bool rows = nRows <= STEREO_MAX_ROWS && nR > 0;                    // vRowIndices as a CSR over image rows
+    const size_t oRS = oN + 256, oRI = oRS + (rows ? (((size_t)(nRows + 1) * 4 + 255) & ~(size_t)255) : 0);
+    const size_t need = oRI + (rows ? (size_t)nR * STEREO_BAND_MAX * 2 : 0) + 256;
     if (e->stereoBytes < need) {
         CK(cudaStreamSynchronize(e->stream));
         cudaFree(e->d_stereo); e->d_stereo = nullptr; e->stereoBytes = 0;
@@ -871,12 +877,21 @@ int orbx_stereo_match(orbx_t* left, orbx_t* right, int frame, const orbx_keypoin
     }
     uint8_t* d = e->d_stereo;
     cudaStream_t st = e->stream;
-    CK(cudaMemcpyAsync(d + oKL, keysL, (size_t)nL * kb, cudaMemcpyHostToDevice, st));
-    CK(cudaMemcpyAsync(d + oDL, descL, (size_t)nL * 32, cudaMemcpyHostToDevice, st));
-    if (nR) {
-        CK(cudaMemcpyAsync(d + oKR, keysR, (size_t)nR * kb, cudaMemcpyHostToDevice, st));
-        CK(cudaMemcpyAsync(d + oDR, descR, (size_t)nR * 32, cudaMemcpyHostToDevice, st));
+    // inputs packed in one pinned block with the device layout (one H2D), outputs fetched as one block (one D2H): seven
+    // separate copies of pageable memory cost more than the kernels
+    const size_t outBytes = oN + 4 - oU;
+    const size_t hNeed = oU + outBytes;
+    if (e->hStereoBytes < hNeed) {
+        CK(cudaStreamSynchronize(e->stream));
+        if (e->h_stereo) cudaFreeHost(e->h_stereo);
+        e->h_stereo = nullptr; e->hStereoBytes = 0;
+        CK(cudaMallocHost(&e->h_stereo, hNeed + 4096));
+        e->hStereoBytes = hNeed + 4096;
     }
+    uint8_t* hs = e->h_stereo;
+    std::memcpy(hs + oKL, keysL, (size_t)nL * kb); std::memcpy(hs + oDL, descL, (size_t)nL * 32);
+    if (nR) { std::memcpy(hs + oKR, keysR, (size_t)nR * kb); std::memcpy(hs + oDR, descR, (size_t)nR * 32); }
+    CK(cudaMemcpyAsync(d, hs, oDR + (size_t)nR * 32, cudaMemcpyHostToDevice, st));
     StereoArgs a{};
     a.keysL = (const orbx_keypoint*)(d + oKL); a.descL = (const uint32_t*)(d + oDL); a.nL = nL;
     a.keysR = (const orbx_keypoint*)(d + oKR); a.descR = (const uint32_t*)(d + oDR); a.nR = nR;
@@ -889,14 +904,19 @@ int orbx_stereo_match(orbx_t* left, orbx_t* right, int frame, const orbx_keypoin
     }
     a.mbf = mbf; a.maxD = mbf / mb;                           // minZ = mb, maxD = mbf / minZ, :678-682
     a.uRight = (float*)(d + oU); a.depth = (float*)(d + oZ); a.sad = (int*)(d + oS);
+    if (rows) {
+        a.nRows = nRows; a.rowItemsCap = nR * STEREO_BAND_MAX;
+        stereo_rows_kernel<<<1, 1024, 0, st>>>(a.keysR, nullptr, nR, a, (int*)(d + oRS), (unsigned short*)(d + oRI));
+        a.rowStart = (const int*)(d + oRS); a.rowItems = (const unsigned short*)(d + oRI);
+    }
     stereo_match_kernel<<<(nL + 7) / 8, 256, 0, st>>>(a);
     stereo_outlier_kernel<<<1, 1024, 0, st>>>(nL, a.sad, a.uRight, a.depth, (int*)(d + oN), 0, nullptr);
     CK(cudaGetLastError());
-    CK(cudaMemcpyAsync(uRight, a.uRight, (size_t)nL * 4, cudaMemcpyDeviceToHost, st));
-    CK(cudaMemcpyAsync(depth, a.depth, (size_t)nL * 4, cudaMemcpyDeviceToHost, st));
-    int nm = 0;
-    CK(cudaMemcpyAsync(&nm, d + oN, 4, cudaMemcpyDeviceToHost, st));
+    CK(cudaMemcpyAsync(hs + oU, d + oU, outBytes, cudaMemcpyDeviceToHost, st));
     CK(cudaStreamSynchronize(st));
+    std::memcpy(uRight, hs + oU, (size_t)nL * 4); std::memcpy(depth, hs + oZ, (size_t)nL * 4);
+    int nm = 0;
+    std::memcpy(&nm, hs + oN, 4);
     if (n_matched) *n_matched = nm;
     return ORBX_OK;
 }

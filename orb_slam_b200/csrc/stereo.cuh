@@ -41,7 +41,7 @@ __global__ void __launch_bounds__(1024) stereo_rows_kernel(const orbx_keypoint* 
     __shared__ int cnt[STEREO_MAX_ROWS + 1];
     __shared__ int warpSum[32];
     const int f = blockIdx.x, tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
-    const int nR = min(nRdev[f], cap), nRows = a.nRows;
+    const int nR = nRdev ? min(nRdev[f], cap) : cap, nRows = a.nRows;        // single frame: cap = the right key point count
     keysR += (size_t)f * cap; rowStart += (size_t)f * (nRows + 1); rowItems += (size_t)f * a.rowItemsCap;
     for (int r = tid; r <= nRows; r += blockDim.x) cnt[r] = 0;
     __syncthreads();
