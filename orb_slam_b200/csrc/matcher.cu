@@ -59,7 +59,8 @@ struct orbm_context {
     int numSMs = 148;
     cudaStream_t stream = nullptr;
     DevBuf part, q, out, w0, w1, w2, w3, w4, w5;
-    PinBuf h0, h1;
+    PinBuf h0, h1, hf;
+    size_t lastPairs = 0;                    // candidate pairs the previous window search produced
     std::mutex mtx;
 };
 
@@ -86,7 +87,7 @@ void orbm_destroy(orbm_t* m) {
     cudaSetDevice(m->device);
     cudaStreamSynchronize(m->stream);
     for (DevBuf* b : {&m->part, &m->q, &m->out, &m->w0, &m->w1, &m->w2, &m->w3, &m->w4, &m->w5}) b->release();
-    m->h0.release(); m->h1.release();
+    m->h0.release(); m->h1.release(); m->hf.release();
     cudaStreamDestroy(m->stream);
     delete m;
 }

@@ -95,7 +95,7 @@ __global__ void __launch_bounds__(256) window_kernel(const WQuery* __restrict__ 
                                                      const orbx_keypoint* __restrict__ keysUn,
                                                      const uint32_t* __restrict__ desc, const int32_t* __restrict__ cellStart,
                                                      const int32_t* __restrict__ items, int32_t* __restrict__ counts,
-                                                     const int32_t* __restrict__ offs, int2* __restrict__ out) {
+                                                     const int32_t* __restrict__ offs, int2* __restrict__ out, int outCap) {
     const int lane = threadIdx.x & 31;
     const int qi = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     if (qi >= nq) return;
@@ -129,7 +129,8 @@ __global__ void __launch_bounds__(256) window_kernel(const WQuery* __restrict__ 
                     int dist = 0;
 #pragma unroll
                     for (int w = 0; w < 8; w++) dist += __popc(q.desc[w] ^ d[w]);
-                    out[base + n + __popc(m & ((1u << lane) - 1))] = make_int2(idx, dist);
+                    const int slot = base + n + __popc(m & ((1u << lane) - 1));
+                    if (slot < outCap) out[slot] = make_int2(idx, dist);      // (the host re-runs with a larger buffer when offs[nq] > outCap)
                 }
                 n += __popc(m);
             }

@@ -17,9 +17,13 @@ int upload_frame(orbm_context* m, const orbm_frame* f, DeviceFrame& d) {
     if ((rc = m->w1.reserve(N * 32))) return rc;
     if ((rc = m->w2.reserve((GRID_CELLS + 1) * 4 + N * 4))) return rc;     // cellStart | cellOf
     if ((rc = m->w3.reserve(N * 4))) return rc;                            // items
-    if (f->N > 0) {
-        CKM(cudaMemcpyAsync(m->w0.p, f->keysUn, (size_t)f->N * sizeof(orbx_keypoint), cudaMemcpyHostToDevice, m->stream));
-        CKM(cudaMemcpyAsync(m->w1.p, f->descriptors, (size_t)f->N * 32, cudaMemcpyHostToDevice, m->stream));
+    if (f->N > 0) {                                    // through the pinned block: pageable sources stall the stream
+        const size_t kb = (size_t)f->N * sizeof(orbx_keypoint), db = (size_t)f->N * 32, ko = (kb + 255) & ~(size_t)255;
+        if ((rc = m->hf.reserve(ko + db))) return rc;
+        CKM(cudaStreamSynchronize(m->stream));         // (the block may still feed the previous call's copies)
+        std::memcpy(m->hf.p, f->keysUn, kb); std::memcpy((uint8_t*)m->hf.p + ko, f->descriptors, db);
+        CKM(cudaMemcpyAsync(m->w0.p, m->hf.p, kb, cudaMemcpyHostToDevice, m->stream));
+        CKM(cudaMemcpyAsync(m->w1.p, (uint8_t*)m->hf.p + ko, db, cudaMemcpyHostToDevice, m->stream));
     }
     d.keysUn = (const orbx_keypoint*)m->w0.p; d.desc = (const uint32_t*)m->w1.p;
     int32_t* cellStart = (int32_t*)m->w2.p; int32_t* cellOf = cellStart + GRID_CELLS + 1;
@@ -30,7 +34,9 @@ int upload_frame(orbm_context* m, const orbm_frame* f, DeviceFrame& d) {
     return 0;
 }
 
-// runs the window queries against the uploaded frame; lists[q] = offs[q]..offs[q+1] in `pairs`
+// runs the window queries against the uploaded frame; lists[q] = offs[q]..offs[q+1] in `pairs`.
+// Count, scan and fill are enqueued back to back against a pair buffer sized from the query count, and offsets and pairs
+// come back in one pinned block: ONE host synchronisation per call (a second round only if the buffer was too small).
 int run_queries(orbm_context* m, const DeviceFrame& d, const std::vector<WQuery>& queries, std::vector<int32_t>& offs,
                 std::vector<int2>& pairs) {
     const int nq = (int)queries.size();
@@ -39,21 +45,34 @@ int run_queries(orbm_context* m, const DeviceFrame& d, const std::vector<WQuery>
     if (nq == 0) return 0;
     int rc;
     if ((rc = m->w4.reserve((size_t)nq * sizeof(WQuery) + (size_t)(2 * nq + 2) * 4))) return rc;
+    if ((rc = m->h0.reserve((size_t)nq * sizeof(WQuery)))) return rc;
     WQuery* dq = (WQuery*)m->w4.p;
     int32_t* dcnt = (int32_t*)(dq + nq); int32_t* doff = dcnt + nq;
-    CKM(cudaMemcpyAsync(dq, queries.data(), (size_t)nq * sizeof(WQuery), cudaMemcpyHostToDevice, m->stream));
+    std::memcpy(m->h0.p, queries.data(), (size_t)nq * sizeof(WQuery));
+    CKM(cudaMemcpyAsync(dq, m->h0.p, (size_t)nq * sizeof(WQuery), cudaMemcpyHostToDevice, m->stream));
     const dim3 grid((nq + 7) / 8);
-    window_kernel<false><<<grid, 256, 0, m->stream>>>(dq, nq, d.g, d.keysUn, d.desc, d.cellStart, d.items, dcnt, nullptr, nullptr);
+    window_kernel<false><<<grid, 256, 0, m->stream>>>(dq, nq, d.g, d.keysUn, d.desc, d.cellStart, d.items, dcnt, nullptr, nullptr, 0);
     scan_counts_kernel<<<1, 1024, 0, m->stream>>>(dcnt, nq, doff);
-    CKM(cudaMemcpyAsync(offs.data(), doff, (size_t)(nq + 1) * 4, cudaMemcpyDeviceToHost, m->stream));
-    CKM(cudaStreamSynchronize(m->stream));
-    const int total = offs[nq];
-    if (total == 0) return 0;
-    if ((rc = m->w5.reserve((size_t)total * sizeof(int2)))) return rc;
-    window_kernel<true><<<grid, 256, 0, m->stream>>>(dq, nq, d.g, d.keysUn, d.desc, d.cellStart, d.items, nullptr, doff, (int2*)m->w5.p);
-    pairs.resize(total);
-    CKM(cudaMemcpyAsync(pairs.data(), m->w5.p, (size_t)total * sizeof(int2), cudaMemcpyDeviceToHost, m->stream));
-    CKM(cudaStreamSynchronize(m->stream));
+    // sized from the previous call's total (tracking repeats the same searches frame after frame)
+    size_t cap = std::max((size_t)nq * 8 + 1024, m->lastPairs + m->lastPairs / 4 + 256);
+    for (int round = 0; round < 2; round++) {
+        const size_t offBytes = (((size_t)nq + 1) * 4 + 15) & ~(size_t)15;
+        if ((rc = m->w5.reserve(cap * sizeof(int2)))) return rc;
+        if ((rc = m->h1.reserve(offBytes + cap * sizeof(int2)))) return rc;
+        window_kernel<true><<<grid, 256, 0, m->stream>>>(dq, nq, d.g, d.keysUn, d.desc, d.cellStart, d.items, nullptr, doff, (int2*)m->w5.p, (int)cap);
+        uint8_t* h = (uint8_t*)m->h1.p;
+        CKM(cudaMemcpyAsync(h, doff, (size_t)(nq + 1) * 4, cudaMemcpyDeviceToHost, m->stream));
+        CKM(cudaMemcpyAsync(h + offBytes, m->w5.p, cap * sizeof(int2), cudaMemcpyDeviceToHost, m->stream));
+        CKM(cudaStreamSynchronize(m->stream));
+        std::memcpy(offs.data(), h, (size_t)(nq + 1) * 4);
+        const size_t total = (size_t)offs[nq];
+        m->lastPairs = total;
+        if (total <= cap) {
+            pairs.assign((const int2*)(h + offBytes), (const int2*)(h + offBytes) + total);
+            break;
+        }
+        cap = total;                                   // rare: dense windows; second round with the exact size
+    }
     CKM(cudaGetLastError());
     return 0;
 }
