@@ -363,11 +363,11 @@ static int enqueue_pipeline(orbx_extractor* e, int wi, const uint8_t* src, size_
         int off = 0;
         for (int l = 0; l < g.nlevels; l++) {
             const LevelGeom& v = g.lv[l];
-            b.rowOff[l] = off;
-            off += v.h + 2 * ORB_EDGE;
+            b.grpOff[l] = off;
+            off += (v.h + 2 * ORB_EDGE + BORDER_ROWS - 1) / BORDER_ROWS;
             b.pyrOff[l] = v.pyrOff; b.w[l] = v.w; b.h[l] = v.h; b.pitch[l] = v.pitch;
         }
-        b.rowOff[g.nlevels] = off;
+        b.grpOff[g.nlevels] = off;
         border_kernel<<<dim3((off + 7) / 8, frames), 256, 0, st>>>(b);
         launches++;
     }

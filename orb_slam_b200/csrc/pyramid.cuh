@@ -434,39 +434,65 @@ __global__ void __launch_bounds__(PYR_THREADS) pyr_level_kernel(PyrArgs a) {
 }
 
 // BORDER_REFLECT_101 frame of 19 pixels around every level (copyMakeBorder,
-// :1364-1365,:1372-1373).  One warp per bordered row: the 19 top and bottom rows are
-// full-width copies of the reflected interior row, all other rows get their 2 x 19 side pixels.
+// :1364-1365,:1372-1373).  One warp per group of BORDER_ROWS consecutive bordered rows: the 19 top and
+// bottom rows are full-width copies of the reflected interior row, every row gets its 2 x 19 side pixels.
+// All loads of a group are issued before its stores (the kernel is latency-bound: a row is a few dozen bytes).
+constexpr int BORDER_ROWS = 4;
 struct BorderArgs {
     uint8_t* pyr;                 // frame 0 pyramid block
     unsigned long long pyrFrameStride;
     int nlevels;
-    int rowOff[ORB_MAX_LEVELS + 1];    // prefix sum of bordered rows (h + 38) per level
+    int grpOff[ORB_MAX_LEVELS + 1];    // prefix sum of row groups, ceil((h + 38) / BORDER_ROWS) per level
     unsigned long long pyrOff[ORB_MAX_LEVELS];
     int w[ORB_MAX_LEVELS], h[ORB_MAX_LEVELS], pitch[ORB_MAX_LEVELS];
 };
 
 __global__ void __launch_bounds__(256) border_kernel(BorderArgs a) {
     const int lane = threadIdx.x & 31;
-    const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
-    if (row >= a.rowOff[a.nlevels]) return;
+    const int grp = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (grp >= a.grpOff[a.nlevels]) return;
     int l = 0;
-    while (row >= a.rowOff[l + 1]) l++;
-    const int by = row - a.rowOff[l];                    // row of the bordered plane
+    while (grp >= a.grpOff[l + 1]) l++;
+    const int by0 = (grp - a.grpOff[l]) * BORDER_ROWS;   // first row of the group in the bordered plane
     const int w = a.w[l], h = a.h[l], pitch = a.pitch[l];
     uint8_t* plane = a.pyr + (size_t)blockIdx.y * a.pyrFrameStride + a.pyrOff[l];
-    const int sy = reflect101(by - ORB_EDGE, h);
-    const uint8_t* srow = plane + (size_t)(sy + ORB_EDGE) * pitch + ORB_XPAD;     // interior row it mirrors
-    uint8_t* drow = plane + (size_t)by * pitch + ORB_XPAD;
-    if (by < ORB_EDGE || by >= ORB_EDGE + h) {
-        // interior part as 32-bit words (both rows start 16-byte aligned), then the two side strips
-        const uint32_t* s4 = (const uint32_t*)srow;
-        uint32_t* d4 = (uint32_t*)drow;
-        for (int i = lane; i < (w + 3) / 4; i += 32) d4[i] = s4[i];      // may run up to 3 bytes into the right strip: rewritten below
+    const uint8_t* srow[BORDER_ROWS];
+    uint8_t* drow[BORDER_ROWS];
+    bool live[BORDER_ROWS], full[BORDER_ROWS];
+#pragma unroll
+    for (int k = 0; k < BORDER_ROWS; k++) {
+        const int by = by0 + k;
+        live[k] = by < h + 2 * ORB_EDGE;
+        full[k] = live[k] && (by < ORB_EDGE || by >= ORB_EDGE + h);
+        const int sy = live[k] ? reflect101(by - ORB_EDGE, h) : 0;
+        srow[k] = plane + (size_t)(sy + ORB_EDGE) * pitch + ORB_XPAD;     // interior row it mirrors
+        drow[k] = plane + (size_t)by * pitch + ORB_XPAD;
+    }
+    // top / bottom rows: the interior part as 16-byte vectors (rows start 16-byte aligned)
+    const int nvec = (w + 15) / 16;
+    bool any = false;
+#pragma unroll
+    for (int k = 0; k < BORDER_ROWS; k++) any |= full[k];
+    if (any) {                                           // warp-uniform
+        for (int i0 = 0; i0 < nvec; i0 += 32) {
+            const int i = i0 + lane;
+            uint4 v[BORDER_ROWS];
+#pragma unroll
+            for (int k = 0; k < BORDER_ROWS; k++) if (full[k] && i < nvec) v[k] = __ldcg((const uint4*)srow[k] + i);
+#pragma unroll
+            for (int k = 0; k < BORDER_ROWS; k++) if (full[k] && i < nvec) *((uint4*)drow[k] + i) = v[k];   // up to 15 bytes into the right strip: rewritten below
+        }
         __syncwarp();
     }
     if (lane < ORB_EDGE) {
-        drow[-1 - lane] = srow[1 + lane];                                 // column -1-k mirrors column 1+k
-        drow[w + lane] = srow[w - 2 - lane];                              // column w+k mirrors column w-2-k
+        uint8_t vl[BORDER_ROWS], vr[BORDER_ROWS];
+#pragma unroll
+        for (int k = 0; k < BORDER_ROWS; k++) if (live[k]) { vl[k] = srow[k][1 + lane]; vr[k] = srow[k][w - 2 - lane]; }
+#pragma unroll
+        for (int k = 0; k < BORDER_ROWS; k++) if (live[k]) {
+            drow[k][-1 - lane] = vl[k];                                   // column -1-k mirrors column 1+k
+            drow[k][w + lane] = vr[k];                                    // column w+k mirrors column w-2-k
+        }
     }
 }
 
