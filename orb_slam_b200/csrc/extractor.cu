@@ -33,7 +33,8 @@ using namespace orbx;
 
 static inline int host_round_even(float v) { return (int)lrintf(v); }   // cvRound
 
-#define ORBX_NBUF 4     // input / result buffers in flight in the host-buffer pipeline (the host runs this many chunks ahead)
+#define ORBX_NBUF 6     // input / result buffers in flight in the host-buffer pipeline (the host runs this many chunks ahead)
+#define ORBX_NWS 4      // kernel workspaces / compute streams; the device-batch path uses the first two, the host-buffer path all
 
 struct orbx_extractor {
     int device = 0;
@@ -50,9 +51,10 @@ struct orbx_extractor {
     ResizeTap* d_tabs = nullptr;
     std::vector<ResizeTap> h_tabs;                   // host copy: per-tile source extents go into the kernel arguments
     uint8_t* d_in[ORBX_NBUF] = {}; size_t inBytes = 0;   // double-buffered H2D targets (host layout kept: linear copies)
-    // Two complete kernel workspaces, each with its own compute stream: neighbouring chunks (host path) or the two halves
-    // of a batch (device path) run concurrently, so the latency-bound stages of one (quadtree, describe) fill the issue
-    // slots the ALU-bound stages of the other (pyramid/FAST, cell NMS) leave idle.
+    // Complete kernel workspaces, each with its own compute stream: neighbouring chunks (host path, all four) or the two
+    // halves of a batch (device path, the first two) run concurrently, so the latency-bound stages of one (quadtree,
+    // describe) fill the issue slots the ALU-bound stages of the others (pyramid/FAST, cell NMS) leave idle.  Workspaces
+    // 2 and 3 exist only once the host-buffer path has been used.
     struct Workspace {
         cudaStream_t stream = nullptr;
         uint8_t *d_pyr = nullptr, *d_blur = nullptr, *d_score = nullptr;
@@ -60,7 +62,7 @@ struct orbx_extractor {
         uint32_t *d_keyA = nullptr, *d_keyB = nullptr, *d_valA = nullptr, *d_valB = nullptr, *d_sel = nullptr;
         int *d_candCount = nullptr, *d_selCount = nullptr;
         int lastFrames = 0;
-    } ws[2];
+    } ws[ORBX_NWS];
     int lastWs = 0;                          // workspace holding the most recent frames (introspection, stereo)
     cudaEvent_t evFork = nullptr, evJoin = nullptr;
     int* d_err = nullptr;
@@ -272,7 +274,8 @@ static int ensure_workspace(orbx_extractor* e, int width, int height, int frames
     e->h_tabs = tabs;
     const size_t cells = (size_t)std::max(g.totalCells, 1) * F;
     const size_t cands = (size_t)std::max<unsigned long long>(g.candTotal, 64) * F;
-    for (auto& w : e->ws) {
+    for (int wi = 0; wi < (needInput || hadInput ? ORBX_NWS : 2); wi++) {
+        orbx_extractor::Workspace& w = e->ws[wi];
         CK(cudaMalloc(&w.d_pyr, g.pyrBytes * F));
         CK(cudaMalloc(&w.d_blur, g.planeBytes * F));
         CK(cudaMalloc(&w.d_score, g.planeBytes * F));
@@ -469,7 +472,7 @@ int orbx_create(orbx_t** out, int nfeatures, float scaleFactor, int nlevels, int
     init_tables(e);
     cudaError_t rc = cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking);
     e->ws[0].stream = e->stream;
-    if (rc == cudaSuccess) rc = cudaStreamCreateWithFlags(&e->ws[1].stream, cudaStreamNonBlocking);
+    for (int wi = 1; wi < ORBX_NWS && rc == cudaSuccess; wi++) rc = cudaStreamCreateWithFlags(&e->ws[wi].stream, cudaStreamNonBlocking);
     if (rc == cudaSuccess) rc = cudaEventCreateWithFlags(&e->evFork, cudaEventDisableTiming);
     if (rc == cudaSuccess) rc = cudaEventCreateWithFlags(&e->evJoin, cudaEventDisableTiming);
     if (rc == cudaSuccess) rc = cudaStreamCreateWithFlags(&e->sIn, cudaStreamNonBlocking);
@@ -520,7 +523,7 @@ void orbx_destroy(orbx_t* e) {
     for (int hlf = 0; hlf < 2; hlf++) for (int i = 0; i < 8; i++) if (e->ev[hlf][i]) cudaEventDestroy(e->ev[hlf][i]);
     if (e->evFork) cudaEventDestroy(e->evFork);
     if (e->evJoin) cudaEventDestroy(e->evJoin);
-    if (e->ws[1].stream) cudaStreamDestroy(e->ws[1].stream);
+    for (int wi = 1; wi < ORBX_NWS; wi++) if (e->ws[wi].stream) cudaStreamDestroy(e->ws[wi].stream);
     for (int b = 0; b < ORBX_NBUF; b++) {
         cudaFree(e->d_in[b]);
         if (e->h_in[b]) cudaFreeHost(e->h_in[b]);
@@ -627,8 +630,14 @@ int orbx_extract_batch(orbx_t* e, const uint8_t* const* images, int n, int width
     for (int i = 0; i < n; i++) if (!images[i]) return ORBX_E_INVALID;
     std::lock_guard<std::mutex> lk(e->mtx);
     CK(cudaSetDevice(e->device));
+    // H2D straight from the caller's buffers when they are page-locked, else through pinned staging; same for D2H
+    bool inPinned = is_pinned(images[0]) && is_pinned(images[n - 1]);
+    const bool outPinnedMem = is_pinned(keypoints) && is_pinned(descriptors) &&
+                              is_pinned(keypoints + (size_t)n * capacity - 1) && is_pinned(descriptors + (size_t)n * capacity * 32 - 1);
+    if (inPinned && step > 2 * (size_t)width) inPinned = false;          // very sparse rows: pack through staging instead
     static const int chunkFrames = [] { const char* v = std::getenv("ORBX_CHUNK_FRAMES"); const int c = v ? std::atoi(v) : 0; return c > 0 ? c : ORBX_CHUNK; }();
-    const int chunk = std::min(n, chunkFrames);
+    // pageable buffers: the host thread's staging copies set the pace, and they run faster through smaller (cache-resident) chunks
+    const int chunk = std::min(n, inPinned && outPinnedMem ? chunkFrames : std::max(1, chunkFrames / 2));
     int rc = ensure_workspace(e, width, height, chunk, true);
     if (rc != ORBX_OK) return rc;
     const FrameGeom& g = e->g;
@@ -636,14 +645,10 @@ int orbx_extract_batch(orbx_t* e, const uint8_t* const* images, int n, int width
     const int F = e->capFrames;
     const size_t head = res_head(F);
     const size_t kpBytes = sizeof(orbx_keypoint);
-    // H2D straight from the caller's buffers when they are page-locked, else through pinned staging; same for D2H
-    bool inPinned = is_pinned(images[0]) && is_pinned(images[n - 1]);
-    const bool outPinned = capacity >= cap && is_pinned(keypoints) && is_pinned(descriptors) &&
-                           is_pinned(keypoints + (size_t)n * capacity - 1) && is_pinned(descriptors + (size_t)n * capacity * 32 - 1);
+    const bool outPinned = capacity >= cap && outPinnedMem;
     // The device copy keeps the host layout (row pitch = step) so that every H2D is a LINEAR copy: a 2-D copy of
     // 1241-byte rows into a padded pitch runs at 10 GB/s on this box, a linear one at 55 GB/s (tools/copybench.cu).
     // The level-0 kernel reads unaligned rows with aligned word loads + funnel shifts.
-    if (inPinned && step > 2 * (size_t)width) inPinned = false;          // very sparse rows: pack through staging instead
     const size_t devPitch = inPinned ? step : (size_t)width;
     const size_t devStride = devPitch * height;
     if (!inPinned) {
@@ -659,7 +664,8 @@ int orbx_extract_batch(orbx_t* e, const uint8_t* const* images, int n, int width
         }
     }
     if (e->inBytes < devStride * F + 64) {
-        CK(cudaStreamSynchronize(e->sIn)); CK(cudaStreamSynchronize(e->ws[0].stream)); CK(cudaStreamSynchronize(e->ws[1].stream));
+        CK(cudaStreamSynchronize(e->sIn));
+        for (auto& w : e->ws) CK(cudaStreamSynchronize(w.stream));
         for (int b = 0; b < ORBX_NBUF; b++) {
             cudaFree(e->d_in[b]); e->d_in[b] = nullptr;
             CK(cudaMalloc(&e->d_in[b], devStride * F + 64));
@@ -672,9 +678,19 @@ int orbx_extract_batch(orbx_t* e, const uint8_t* const* images, int n, int width
     {
         int f = 0;
         auto push = [&](int c) { cStart.push_back(f); cCount.push_back(c); f += c; };
-        if (n >= 2 * chunk && chunk >= 8) { push(chunk / 4); push(chunk / 2); }
-        while (n - f > chunk) push(chunk);
-        if (n - f > 0) push(n - f);
+        if (n >= 4 * chunk && chunk >= 8) {
+            // ramp up over the four compute streams, full chunks, ramp down (the streams drain together and the last
+            // copy-out is short)
+            const int q = chunk / 4, hlf = chunk / 2, mid = n - 2 * (2 * q + 2 * hlf);
+            push(q); push(q); push(hlf); push(hlf);
+            if (mid % chunk) push(mid % chunk);
+            for (int i = 0; i < mid / chunk; i++) push(chunk);
+            push(hlf); push(hlf); push(q); push(n - f);
+        } else {
+            if (n >= 2 * chunk && chunk >= 8) { push(chunk / 4); push(chunk / 2); }
+            while (n - f > chunk) push(chunk);
+            if (n - f > 0) push(n - f);
+        }
     }
     const int nchunks = (int)cStart.size();
     int status = ORBX_OK;
@@ -715,7 +731,7 @@ int orbx_extract_batch(orbx_t* e, const uint8_t* const* images, int n, int width
         if (status != ORBX_OK) break;
         // a call with a single chunk (one frame: Tracking's case) runs copy-in, kernels and copy-out on one stream:
         // no cross-stream event hops on the latency path
-        cudaStream_t cst = e->ws[k & 1].stream;                          // workspace / compute stream of this parity
+        cudaStream_t cst = e->ws[k % ORBX_NWS].stream;                   // workspace / compute stream of this chunk
         cudaStream_t sIn = nchunks == 1 ? cst : e->sIn, sOut = nchunks == 1 ? cst : e->sOut;
         // ---- copy-in stream: d_in[b] is free once the compute of chunk k - ORBX_NBUF has finished
         if (k >= ORBX_NBUF) CK(cudaStreamWaitEvent(sIn, e->evCompute[b], 0));
@@ -751,7 +767,7 @@ int orbx_extract_batch(orbx_t* e, const uint8_t* const* images, int n, int width
         orbx_keypoint* d_kps = (orbx_keypoint*)(e->d_res[b] + head);
         uint8_t* d_desc = e->d_res[b] + head + (size_t)F * cap * kpBytes;
         CK(cudaMemsetAsync(d_err, 0, sizeof(int), cst));
-        rc = enqueue_pipeline(e, k & 1, e->d_in[b], devPitch, devStride, nf, d_kps, d_desc, cap, d_n, d_err, nullptr);
+        rc = enqueue_pipeline(e, k % ORBX_NWS, e->d_in[b], devPitch, devStride, nf, d_kps, d_desc, cap, d_n, d_err, nullptr);
         if (rc != ORBX_OK) { status = rc; break; }
         CK(cudaEventRecord(e->evCompute[b], cst));
         mark(k, 3, cst);
@@ -773,7 +789,8 @@ int orbx_extract_batch(orbx_t* e, const uint8_t* const* images, int n, int width
     }
     while (status == ORBX_OK && finalized < nchunks) { rc = finalize(finalized++); if (rc != ORBX_OK) status = rc; }
     if (nchunks > 1 || status != ORBX_OK) {     // (a single chunk was fully waited for by finalize)
-        CK(cudaStreamSynchronize(e->sIn)); CK(cudaStreamSynchronize(e->ws[0].stream)); CK(cudaStreamSynchronize(e->ws[1].stream));
+        CK(cudaStreamSynchronize(e->sIn));
+        for (auto& w : e->ws) CK(cudaStreamSynchronize(w.stream));
         CK(cudaStreamSynchronize(e->sOut));
     }
     if (trace) {
@@ -859,7 +876,7 @@ int orbx_stereo_match(orbx_t* left, orbx_t* right, int frame, const orbx_keypoin
         return ORBX_E_INVALID;
     CK(cudaSetDevice(left->device));
     CK(cudaStreamSynchronize(right->ws[right->lastWs].stream));   // the right pyramid is complete
-    if (left->lastWs) CK(cudaStreamSynchronize(left->ws[1].stream));
+    if (left->lastWs) CK(cudaStreamSynchronize(left->ws[left->lastWs].stream));
     const size_t kb = sizeof(orbx_keypoint);
     const size_t oKL = 0, oDL = oKL + (((size_t)nL * kb + 255) & ~(size_t)255), oKR = oDL + (size_t)nL * 32 + 256;
     const size_t oDR = oKR + (((size_t)nR * kb + 255) & ~(size_t)255), oU = oDR + (size_t)std::max(nR, 1) * 32 + 256;
