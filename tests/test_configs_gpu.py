@@ -21,19 +21,35 @@ def same(gk, gd, ok, od):
     assert (gd == od).all(axis=1).mean() >= 0.999 if len(gd) else True
 
 
-def test_batch_across_chunks_equals_single_frame_calls():
-    """70 frames = one full pipeline chunk of 64 + a ragged one; every frame must equal its own single-frame call"""
-    from orb_slam_b200 import ORBextractor
-    w, h, nf, n = 321, 243, 300, 70
+@pytest.mark.parametrize("n,pinned", [(70, False), (150, False), (260, True)])
+def test_batch_across_chunks_equals_single_frame_calls(n, pinned):
+    """Batches that cross the host-buffer pipeline's chunking: 70 pageable frames = 8 + 16 + 32 + a ragged chunk; 150
+    pageable (32-frame chunks) and 260 page-locked frames (64-frame chunks) take the ramp-up / ramp-down schedule over
+    the four compute streams and wrap around the six buffer sets.  Every frame must equal its own single-frame call."""
+    import torch
+    from orb_slam_b200 import KEYPOINT_DTYPE, ORBextractor
+    from orb_slam_b200._lib import check
+    w, h, nf = 321, 243, 300
     imgs = np.stack([synth_frame(w, h, 200 + (i % 9), shift=(i % 40, -(i % 40))) for i in range(n)])
     ex = ORBextractor(nf, 1.2, 8, 20, 7)
-    batch = ex.extract_batch(imgs)
+    if pinned:
+        cap = ex.max_keypoints(w, h)
+        pin = torch.from_numpy(imgs).pin_memory()
+        kp = torch.empty((n, cap, 28), dtype=torch.uint8, pin_memory=True)
+        dp = torch.empty((n, cap, 32), dtype=torch.uint8, pin_memory=True)
+        cnt = np.zeros(n, np.int32)
+        ptrs = (C.c_void_p * n)(*[pin.data_ptr() + i * w * h for i in range(n)])
+        check(ex._L.orbx_extract_batch(ex.handle, ptrs, n, w, h, w, kp.data_ptr(), dp.data_ptr(), cap, cnt.ctypes.data),
+              "orbx_extract_batch")
+        batch = [(kp.numpy()[i, : cnt[i]].copy().view(KEYPOINT_DTYPE).reshape(-1), dp.numpy()[i, : cnt[i]].copy()) for i in range(n)]
+    else:
+        batch = ex.extract_batch(imgs)
     one = ORBextractor(nf, 1.2, 8, 20, 7)
-    for i in (0, 1, 31, 63, 64, 65, 69):
+    for i in sorted({0, 1, 7, 8, 15, 16, 31, 32, 47, 48, 63, 64, 65, 69, n // 2, n - 17, n - 9, n - 8, n - 1}):
         k, d = one(imgs[i])
         assert k.tobytes() == batch[i][0].tobytes() and np.array_equal(d, batch[i][1]), i
     cpu = OracleExtractor(nf, 1.2, 8, 20, 7)
-    for i in (0, 64, 69):
+    for i in (0, 64, n - 1):
         same(*batch[i], *cpu(imgs[i]))
 
 
