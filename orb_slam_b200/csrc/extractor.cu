@@ -74,6 +74,12 @@ struct orbx_extractor {
     cudaEvent_t evIn[ORBX_NBUF] = {}, evCompute[ORBX_NBUF] = {}, evOut[ORBX_NBUF] = {};
     uint8_t* d_stereo = nullptr; size_t stereoBytes = 0;     // scratch of orbx_stereo_match
     uint8_t* h_stereo = nullptr; size_t hStereoBytes = 0;    // its pinned staging: one H2D and one D2H per call
+    // single-frame call with pageable buffers (Tracking's case): the copy-in, the 12 launches and the copy-out are
+    // captured once into a CUDA graph and replayed - one launch call instead of sixteen on the latency path, which is
+    // what two host threads (the stereo pair, reference src/Frame.cc:94-103) otherwise serialise on in the driver
+    cudaGraphExec_t oneExec = nullptr;
+    unsigned long long allocGen = 0, oneGen = 0;     // buffer generation the graph was captured for
+    int oneLaunches = 0;
     int launches = 0;
     bool profile = false;                    // record one CUDA event per stage boundary
     int profiledHalves = 0;
@@ -267,6 +273,7 @@ static int ensure_workspace(orbx_extractor* e, int width, int height, int frames
     const bool hadInput = e->d_res[1] != nullptr;
     CK(cudaStreamSynchronize(e->sIn)); CK(cudaStreamSynchronize(e->sOut));
     free_workspace(e);
+    e->allocGen++;
     e->g = g;
     const size_t F = (size_t)newCap;
     CK(cudaMalloc(&e->d_tabs, std::max<size_t>(tabs.size(), 1) * sizeof(ResizeTap)));
@@ -517,6 +524,7 @@ void orbx_destroy(orbx_t* e) {
     if (!e) return;
     cudaSetDevice(e->device);
     for (auto& w : e->ws) if (w.stream) cudaStreamSynchronize(w.stream);
+    if (e->oneExec) cudaGraphExecDestroy(e->oneExec);
     free_workspace(e);
     cudaFree(e->d_err); cudaFree(e->d_stereo);
     if (e->h_stereo) cudaFreeHost(e->h_stereo);
@@ -666,6 +674,7 @@ int orbx_extract_batch(orbx_t* e, const uint8_t* const* images, int n, int width
                 CK(cudaMallocHost(&e->h_in[b], need));
             }
             e->hInBytes = need;
+            e->allocGen++;
         }
     }
     if (e->inBytes < devStride * F + 64) {
@@ -676,6 +685,50 @@ int orbx_extract_batch(orbx_t* e, const uint8_t* const* images, int n, int width
             CK(cudaMalloc(&e->d_in[b], devStride * F + 64));
         }
         e->inBytes = devStride * F + 64;
+        e->allocGen++;
+    }
+    static const bool trace = std::getenv("ORBX_TRACE") != nullptr;
+    static const bool noGraph = std::getenv("ORBX_NO_GRAPH") != nullptr;
+    if (n == 1 && !inPinned && !outPinned && !e->profile && !trace && !noGraph) {
+        cudaStream_t cst = e->ws[0].stream;
+        uint8_t* stage = e->h_in[0];                     // (every call ends synchronised: the staging buffers are free)
+        if (step == (size_t)width) std::memcpy(stage, images[0], (size_t)width * height);
+        else for (int y = 0; y < height; y++) std::memcpy(stage + (size_t)y * width, images[0] + (size_t)y * step, width);
+        int* d_n = (int*)e->d_res[0];
+        orbx_keypoint* d_kps = (orbx_keypoint*)(e->d_res[0] + head);
+        uint8_t* d_desc = e->d_res[0] + head + (size_t)F * cap * kpBytes;
+        if (!e->oneExec || e->oneGen != e->allocGen) {
+            if (e->oneExec) { cudaGraphExecDestroy(e->oneExec); e->oneExec = nullptr; }
+            e->launches = 0;
+            CK(cudaStreamBeginCapture(cst, cudaStreamCaptureModeThreadLocal));
+            cudaError_t ce = cudaMemcpyAsync(e->d_in[0], stage, (size_t)width * height, cudaMemcpyHostToDevice, cst);
+            if (ce == cudaSuccess) ce = cudaMemsetAsync(d_n + F, 0, sizeof(int), cst);
+            rc = ce == cudaSuccess ? enqueue_pipeline(e, 0, e->d_in[0], devPitch, devStride, 1, d_kps, d_desc, cap, d_n, d_n + F, nullptr) : (int)ce;
+            if (rc == ORBX_OK) {
+                ce = cudaMemcpyAsync(e->h_res[0], e->d_res[0], head, cudaMemcpyDeviceToHost, cst);
+                if (ce == cudaSuccess) ce = cudaMemcpyAsync(e->h_res[0] + head, d_kps, (size_t)cap * kpBytes, cudaMemcpyDeviceToHost, cst);
+                if (ce == cudaSuccess) ce = cudaMemcpyAsync(e->h_res[0] + head + (size_t)F * cap * kpBytes, d_desc, (size_t)cap * 32, cudaMemcpyDeviceToHost, cst);
+                rc = (int)ce;
+            }
+            cudaGraph_t graph = nullptr;
+            const cudaError_t ee = cudaStreamEndCapture(cst, &graph);
+            if (rc == ORBX_OK && ee != cudaSuccess) rc = (int)ee;
+            if (rc == ORBX_OK) rc = (int)cudaGraphInstantiate(&e->oneExec, graph, 0);
+            if (graph) cudaGraphDestroy(graph);
+            if (rc != ORBX_OK) { e->oneExec = nullptr; cudaGetLastError(); return rc; }
+            e->oneGen = e->allocGen; e->oneLaunches = e->launches;
+        }
+        e->launches = e->oneLaunches; e->ws[0].lastFrames = 1; e->lastWs = 0;
+        CK(cudaGraphLaunch(e->oneExec, cst));
+        CK(cudaStreamSynchronize(cst));
+        const int* h_n = (const int*)e->h_res[0];
+        if (h_n[F] != 0) { std::fprintf(stderr, "orbx: device consistency check %d failed\n", h_n[F]); return ORBX_E_INTERNAL; }
+        const int kq = h_n[0];
+        n_out[0] = kq;
+        if (kq > capacity) return ORBX_E_CAPACITY;
+        std::memcpy(keypoints, e->h_res[0] + head, (size_t)kq * kpBytes);
+        std::memcpy(descriptors, e->h_res[0] + head + (size_t)F * cap * kpBytes, (size_t)kq * 32);
+        return ORBX_OK;
     }
     // chunk schedule: a short first and second chunk (the device starts after a quarter of a chunk has arrived instead
     // of a whole one), full chunks, and whatever is left as a short tail (short drain)
@@ -701,7 +754,6 @@ int orbx_extract_batch(orbx_t* e, const uint8_t* const* images, int n, int width
     int status = ORBX_OK;
     e->launches = 0;
     // ORBX_TRACE=1: device timeline of the chunk pipeline (debug aid; costs five timing events per chunk)
-    static const bool trace = std::getenv("ORBX_TRACE") != nullptr;
     std::vector<cudaEvent_t> tev;
     if (trace) { tev.resize((size_t)nchunks * 5 + 1); for (auto& t : tev) cudaEventCreate(&t); cudaEventRecord(tev.back(), e->sIn); }
     auto mark = [&](int k, int what, cudaStream_t st) { if (trace) cudaEventRecord(tev[(size_t)k * 5 + what], st); };
