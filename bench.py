@@ -554,6 +554,27 @@ def run_stereo_batch(local_rank, npairs=256):
     return out
 
 
+def bind_to_gpu_cpus(local_rank):
+    """Multi-GPU runs: keep the rank's host thread (and the pinned buffers it first-touches) on the CPUs the driver
+    reports as local to its GPU, so H2D / D2H do not cross sockets.  Best effort; a no-op when NVML has no affinity."""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        try:
+            import torch
+            h = pynvml.nvmlDeviceGetHandleByUUID(("GPU-" + str(torch.cuda.get_device_properties(local_rank).uuid)).encode())
+        except Exception:
+            h = pynvml.nvmlDeviceGetHandleByIndex(local_rank)
+        ncpu = os.cpu_count() or 1
+        words = pynvml.nvmlDeviceGetCpuAffinity(h, (ncpu + 63) // 64)
+        cpus = {64 * i + b for i, wd in enumerate(words) for b in range(64) if (int(wd) >> b) & 1}
+        cpus &= os.sched_getaffinity(0)
+        if cpus:
+            os.sched_setaffinity(0, cpus)
+    except Exception:
+        pass
+
+
 def run_ours(args, rank, world, local_rank):
     import torch
     from orb_slam_b200 import KEYPOINT_DTYPE, ORBextractor
@@ -561,8 +582,9 @@ def run_ours(args, rank, world, local_rank):
 
     dist = None
     if world > 1:
-        if os.environ.get("NCCL_DEBUG", "VERSION").upper() == "VERSION":
-            os.environ["NCCL_DEBUG"] = "WARN"          # keep stdout to the one JSON line
+        if os.environ.get("NCCL_DEBUG", "").upper() in ("VERSION", "WARN"):
+            del os.environ["NCCL_DEBUG"]               # both levels print "NCCL version ..." on stdout: keep it to the one JSON line
+        bind_to_gpu_cpus(local_rank)
         import torch.distributed as dist_
         dist = dist_
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
