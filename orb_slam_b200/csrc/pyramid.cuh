@@ -404,31 +404,35 @@ __global__ void __launch_bounds__(PYR_THREADS) pyr_level_kernel(PyrArgs a) {
         *(uint32_t*)(a.score + (size_t)frame * a.planeFrameStride + (size_t)y * a.pitch + ORB_XPAD + gx) = s;
     }
 
-    // ---- vertical blur pass: warp `wid` owns tile rows 4*wid..4*wid+3, sliding 7-row window in registers ----
+    // ---- vertical blur pass: warp `wid` owns tile rows 4*wid..4*wid+3.  The ten row sums a lane needs per pixel are
+    //      paired vertically, P[j] = (H[j], H[j+1]) as u16x2, so that one DP2A applies two taps:
+    //      out[k] = (18,34).P[k] + (48,56).P[k+2] + (48,34).P[k+4] + (0,18).P[k+5] ----
     {
         const unsigned short* col = Hs + 4 * lane;
-        uint32_t u[7][4];                                // unpacked row sums of the 7 window rows, pixel order
+        uint2 v[10];
 #pragma unroll
-        for (int j = 0; j < 6; j++) {
-            const uint2 v = *(const uint2*)(col + (4 * wid + j) * TW);
-            u[j][0] = v.x & 0xffffu; u[j][2] = v.x >> 16; u[j][1] = v.y & 0xffffu; u[j][3] = v.y >> 16;
+        for (int j = 0; j < 10; j++) v[j] = *(const uint2*)(col + (4 * wid + j) * TW);     // .x = (H(c), H(c+2)), .y = (H(c+1), H(c+3))
+        uint32_t P[9][4];                                 // pixel order c, c+1, c+2, c+3
+#pragma unroll
+        for (int j = 0; j < 9; j++) {
+            P[j][0] = __byte_perm(v[j].x, v[j + 1].x, 0x5410); P[j][2] = __byte_perm(v[j].x, v[j + 1].x, 0x7632);
+            P[j][1] = __byte_perm(v[j].y, v[j + 1].y, 0x5410); P[j][3] = __byte_perm(v[j].y, v[j + 1].y, 0x7632);
         }
 #pragma unroll
         for (int k = 0; k < 4; k++) {
-            const int r = 4 * wid + k, y = y0 + r;
-            const uint2 v = *(const uint2*)(col + (r + 6) * TW);
-            u[6][0] = v.x & 0xffffu; u[6][2] = v.x >> 16; u[6][1] = v.y & 0xffffu; u[6][3] = v.y >> 16;
+            const int y = y0 + 4 * wid + k;
             uint32_t o[4];
 #pragma unroll
-            for (int j = 0; j < 4; j++)
-                o[j] = (18u * (u[0][j] + u[6][j]) + 34u * (u[1][j] + u[5][j]) + 48u * (u[2][j] + u[4][j]) + 56u * u[3][j] + 32768u) >> 16;
+            for (int q = 0; q < 4; q++) {
+                uint32_t acc = __dp2a_lo(P[k][q], 18u | (34u << 8), 32768u);
+                acc = __dp2a_lo(P[k + 2][q], 48u | (56u << 8), acc);
+                acc = __dp2a_lo(P[k + 4][q], 48u | (34u << 8), acc);
+                acc = __dp2a_lo(P[k + 5][q], 18u << 8, acc);
+                o[q] = acc >> 16;
+            }
             if (y < h && gx < w)
                 *(uint32_t*)(a.blur + (size_t)frame * a.planeFrameStride + (size_t)y * a.pitch + ORB_XPAD + gx) =
                     o[0] | (o[1] << 8) | (o[2] << 16) | (o[3] << 24);
-#pragma unroll
-            for (int i = 0; i < 6; i++)
-#pragma unroll
-                for (int j = 0; j < 4; j++) u[i][j] = u[i + 1][j];
         }
     }
 }

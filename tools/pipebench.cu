@@ -1,6 +1,7 @@
 // Issue-rate microbenchmark for the integer instructions the front-end kernels are built from (tools only).
 // ops per clock per SM = threads * iters * chains / (time * clock * SMs)
 #include <cuda_runtime.h>
+#include <cuda_fp16.h>
 #include <cstdint>
 #include <cstdio>
 
@@ -16,7 +17,20 @@ template <int OP> __device__ __forceinline__ uint32_t op(uint32_t a, uint32_t b,
     if (OP == 8) return __popc(a) + b;                 // POPC + add
     if (OP == 9) return a * b + c;                     // IMAD
     if (OP == 10) return __vimax3_u16x2(a, b, c);
+    if (OP == 11) { __half2 r = __hmin2(*(__half2*)&a, *(__half2*)&b); return *(uint32_t*)&r; }     // HMNMX2 on the raw u16x2 bits (values < 0x7c00 order like integers)
+    if (OP == 14) return __dp2a_lo(a, b, c);           // IDP.2A
+    if (OP == 17) { uint32_t r; asm volatile("lop3.b32 %0, %1, %2, %3, 0x6a;" : "=r"(r) : "r"(a), "r"(b), "r"(c)); return r; }      // one LOP3
+    if (OP == 18) { uint32_t r; asm volatile("shf.r.wrap.b32 %0, %1, %2, 16;" : "=r"(r) : "r"(a), "r"(b)); return r; }               // SHF.R.W
+    if (OP == 19) { uint32_t r; asm volatile("shr.u32 %0, %1, 8;" : "=r"(r) : "r"(a)); return r ^ b; }                               // SHF + LOP3
     return a;
+}
+// mixes: even chains one instruction, odd chains another (do two pipes overlap, or is the issue slot the limit?)
+template <int OP> __device__ __forceinline__ uint32_t opi(uint32_t a, uint32_t b, uint32_t c, int i) {
+    if (OP == 12) return (i & 1) ? op<11>(a, b, c) : op<2>(a, b, c);      // HMNMX2 / VIMNMX.U16x2
+    if (OP == 13) return (i & 1) ? op<9>(a, b, c) : op<2>(a, b, c);       // IMAD / VIMNMX.U16x2
+    if (OP == 15) return (i & 1) ? op<14>(a, b, c) : op<2>(a, b, c);      // IDP.2A / VIMNMX.U16x2
+    if (OP == 16) return (i & 1) ? op<7>(a, b, c) : op<2>(a, b, c);       // PRMT / VIMNMX.U16x2
+    return op<OP>(a, b, c);
 }
 
 template <int OP> __global__ void k(uint32_t* out, int iters, uint32_t seed) {
@@ -25,7 +39,7 @@ template <int OP> __global__ void k(uint32_t* out, int iters, uint32_t seed) {
     for (int i = 0; i < 8; i++) v[i] = seed + i * 0x01010101u + threadIdx.x;
     for (int it = 0; it < iters; it++) {
 #pragma unroll
-        for (int i = 0; i < 8; i++) v[i] = op<OP>(v[i], b, c);
+        for (int i = 0; i < 8; i++) v[i] = opi<OP>(v[i], b, c, i);
         b += 0x00010001u;
     }
     uint32_t s = 0;
@@ -63,5 +77,14 @@ int main() {
     run<7>("PRMT", d, p.multiProcessorCount, mhz);
     run<8>("POPC + IADD", d, p.multiProcessorCount, mhz);
     run<9>("IMAD", d, p.multiProcessorCount, mhz);
+    run<11>("HMNMX2 (raw u16x2 bits)", d, p.multiProcessorCount, mhz);
+    run<14>("IDP.2A", d, p.multiProcessorCount, mhz);
+    run<12>("HMNMX2 | VIMNMX.U16x2 mix", d, p.multiProcessorCount, mhz);
+    run<13>("IMAD | VIMNMX.U16x2 mix", d, p.multiProcessorCount, mhz);
+    run<15>("IDP.2A | VIMNMX.U16x2 mix", d, p.multiProcessorCount, mhz);
+    run<16>("PRMT | VIMNMX.U16x2 mix", d, p.multiProcessorCount, mhz);
+    run<17>("LOP3 (a & b) ^ c", d, p.multiProcessorCount, mhz);
+    run<18>("SHF funnelshift_r 16", d, p.multiProcessorCount, mhz);
+    run<19>("(a >> 8) & b", d, p.multiProcessorCount, mhz);
     return 0;
 }
