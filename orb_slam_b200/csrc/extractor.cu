@@ -831,7 +831,10 @@ int orbx_extract_batch(orbx_t* e, const uint8_t* const* images, int n, int width
         // ---- copy-out stream
         if (nchunks > 1) CK(cudaStreamWaitEvent(sOut, e->evCompute[b], 0));
         CK(cudaMemcpyAsync(e->h_res[b], e->d_res[b], head, cudaMemcpyDeviceToHost, sOut));
-        if (outPinned) {
+        if (outPinned && capacity == cap) {              // the caller's rows are as long as the device's: linear copies
+            CK(cudaMemcpyAsync(keypoints + (size_t)f0 * cap, d_kps, (size_t)nf * cap * kpBytes, cudaMemcpyDeviceToHost, sOut));
+            CK(cudaMemcpyAsync(descriptors + (size_t)f0 * cap * 32, d_desc, (size_t)nf * cap * 32, cudaMemcpyDeviceToHost, sOut));
+        } else if (outPinned) {
             CK(cudaMemcpy2DAsync(keypoints + (size_t)f0 * capacity, (size_t)capacity * kpBytes, d_kps, (size_t)cap * kpBytes,
                                  (size_t)cap * kpBytes, nf, cudaMemcpyDeviceToHost, sOut));
             CK(cudaMemcpy2DAsync(descriptors + (size_t)f0 * capacity * 32, (size_t)capacity * 32, d_desc, (size_t)cap * 32,
