@@ -50,7 +50,7 @@ struct orbx_extractor {
     int capFrames = 0;                       // frames EACH workspace is sized for
     ResizeTap* d_tabs = nullptr;
     std::vector<ResizeTap> h_tabs;                   // host copy: per-tile source extents go into the kernel arguments
-    uint8_t* d_in[ORBX_NBUF] = {}; size_t inBytes = 0;   // double-buffered H2D targets (host layout kept: linear copies)
+    uint8_t* d_in[ORBX_NBUF] = {}; size_t inBytes = 0;   // H2D targets, one per buffer set (host layout kept: linear copies)
     // Complete kernel workspaces, each with its own compute stream: neighbouring chunks (host path, all four) or the two
     // halves of a batch (device path, the first two) run concurrently, so the latency-bound stages of one (quadtree,
     // describe) fill the issue slots the ALU-bound stages of the others (pyramid/FAST, cell NMS) leave idle.  Workspaces
@@ -782,7 +782,7 @@ int orbx_extract_batch(orbx_t* e, const uint8_t* const* images, int n, int width
     for (int k = 0; k < nchunks; k++) {
         const int b = k % ORBX_NBUF, f0 = cStart[k], nf = cCount[k];
         // buffer set b was last used by chunk k - ORBX_NBUF: finish it on the host before its staging is reused.  The
-        // host therefore runs up to ORBX_NBUF chunks ahead of the device, which keeps both copy engines and the two
+        // host therefore runs up to ORBX_NBUF chunks ahead of the device, which keeps both copy engines and the
         // compute streams fed.
         while (status == ORBX_OK && finalized <= k - ORBX_NBUF) { rc = finalize(finalized++); if (rc != ORBX_OK) status = rc; }
         if (status != ORBX_OK) break;
@@ -815,7 +815,7 @@ int orbx_extract_batch(orbx_t* e, const uint8_t* const* images, int n, int width
         }
         CK(cudaEventRecord(e->evIn[b], sIn));
         mark(k, 1, sIn);
-        // ---- compute stream: needs the input, and d_res[b] drained by the copy-out of chunk k-2
+        // ---- compute stream: needs the input, and d_res[b] drained by the copy-out of chunk k - ORBX_NBUF
         if (nchunks > 1) CK(cudaStreamWaitEvent(cst, e->evIn[b], 0));
         if (k >= ORBX_NBUF) CK(cudaStreamWaitEvent(cst, e->evOut[b], 0));
         mark(k, 2, cst);
