@@ -307,16 +307,18 @@ static int ensure_workspace(orbx_extractor* e, int width, int height, int frames
     // kernel attributes
     CK(cudaFuncSetAttribute(quadtree_kernel<QT_THREADS_BATCH>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)qt_smem_bytes(g.nodeCap, QT_THREADS_BATCH)));
     CK(cudaFuncSetAttribute(quadtree_kernel<QT_THREADS_LATENCY>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(qt_smem_bytes(g.nodeCap, QT_THREADS_LATENCY) + (size_t)QT_KEYS_SMEM * 16)));
-    CK(cudaFuncSetAttribute(pyr_level_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
-    CK(cudaFuncSetAttribute(pyr_level_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
+    CK(cudaFuncSetAttribute(pyr_level_kernel<false, TH_BATCH>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
+    CK(cudaFuncSetAttribute(pyr_level_kernel<true, TH_BATCH>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
+    CK(cudaFuncSetAttribute(pyr_level_kernel<false, TH_LATENCY>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
+    CK(cudaFuncSetAttribute(pyr_level_kernel<true, TH_LATENCY>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
     return ORBX_OK;
 }
 
-static void pyr_smem_for(const LevelGeom& prev, const LevelGeom& cur, int& cols, int& rows, size_t& bytes) {
+static void pyr_smem_for(int TH, const LevelGeom& prev, const LevelGeom& cur, int& cols, int& rows, size_t& bytes) {
     const double sx = (double)prev.w / cur.w, sy = (double)prev.h / cur.h;
     cols = (((int)std::ceil((TW + 2 * HALO) * sx) + 3 + 16 + 16) + 15) & ~15;
     rows = (int)std::ceil((TH + 2 * HALO) * sy) + 4;
-    bytes = pyr_smem_bytes(false, rows, cols);
+    bytes = pyr_smem_bytes(TH, false, rows, cols);
 }
 
 // Enqueue the whole pipeline for `frames` frames whose level-0 source is (src, pitch, frameStride).
@@ -328,7 +330,11 @@ static int enqueue_pipeline(orbx_extractor* e, int wi, const uint8_t* src, size_
     cudaStream_t st = w.stream;
     int launches = 0;
     if (evs) CK(cudaEventRecord(evs[0], st));
-    // 1. pyramid + blur + FAST score, level by level (level l reads level l-1)
+    // 1. pyramid + blur + FAST score, level by level (level l reads level l-1).  A handful of frames: the eight dependent
+    //    launches are the critical path and none of them fills the GPU - tiles of half the height halve the serial work
+    //    of a CTA and double the CTAs
+    const bool lowTiles = frames <= PYR_LATENCY_FRAMES;
+    const int TH = lowTiles ? TH_LATENCY : TH_BATCH;
     for (int l = 0; l < g.nlevels; l++) {
         const LevelGeom& v = g.lv[l];
         PyrArgs a{};
@@ -339,8 +345,9 @@ static int enqueue_pipeline(orbx_extractor* e, int wi, const uint8_t* src, size_
         if (l == 0) {
             a.src = src; a.srcFrameStride = srcFrameStride; a.srcPitch = (int)srcPitch; a.srcX0 = 0;
             a.sw = v.w; a.sh = v.h;
-            const size_t smem = pyr_smem_bytes(true, 0, 0);
-            pyr_level_kernel<true><<<grid, PYR_THREADS, smem, st>>>(a);
+            const size_t smem = pyr_smem_bytes(TH, true, 0, 0);
+            if (lowTiles) pyr_level_kernel<true, TH_LATENCY><<<grid, PYR_THREADS, smem, st>>>(a);
+            else pyr_level_kernel<true, TH_BATCH><<<grid, PYR_THREADS, smem, st>>>(a);
         } else {
             const LevelGeom& p = g.lv[l - 1];
             a.src = w.d_pyr + p.pyrOff + (size_t)ORB_EDGE * p.pitch; a.srcFrameStride = g.pyrBytes;
@@ -360,8 +367,9 @@ static int enqueue_pipeline(orbx_extractor* e, int wi, const uint8_t* src, size_
                 }
             }
             size_t smem;
-            pyr_smem_for(p, v, a.srcTileCols, a.srcTileRows, smem);
-            pyr_level_kernel<false><<<grid, PYR_THREADS, smem, st>>>(a);
+            pyr_smem_for(TH, p, v, a.srcTileCols, a.srcTileRows, smem);
+            if (lowTiles) pyr_level_kernel<false, TH_LATENCY><<<grid, PYR_THREADS, smem, st>>>(a);
+            else pyr_level_kernel<false, TH_BATCH><<<grid, PYR_THREADS, smem, st>>>(a);
         }
         launches++;
     }

@@ -21,11 +21,12 @@
 namespace orbx {
 
 constexpr int TW = 128;          // tile width  (pixels)
-constexpr int TH = 32;           // tile height
+constexpr int TH_BATCH = 32;     // tile height: throughput variant
+constexpr int TH_LATENCY = 16;   // tile height of the few-frames variant: twice the CTAs, half the serial work in each
+constexpr int PYR_LATENCY_FRAMES = 2;   // calls with at most this many frames take the few-frames variant
 constexpr int HALO = 3;          // FAST ring radius == blur radius
 constexpr int TCOL0 = 4;         // shared-memory byte of tile pixel x0 in a T row (keeps 4-pixel groups word-aligned)
 constexpr int TS = 144;          // shared-memory row stride of the level tile (bytes)
-constexpr int TROWS = TH + 2 * HALO;
 constexpr int TBYTES = 136;      // T bytes written per row: byte b <-> level column x0 - 4 + b
 constexpr int HQS = 136;         // u16 stride of the horizontally resized staging rows
 constexpr int PYR_THREADS = 256;
@@ -168,21 +169,24 @@ struct PyrArgs {
 // shared memory carve-up (bytes).  T is live from the resize to the row pass; everything else lives in one region R
 // behind it that is used twice: [tap tables | Hq | staged source rows] while T is being built, then
 // [Hs | pair planes PA, PB] once T is complete.  54 KB per CTA at every level -> four CTAs per SM.
-__host__ __device__ inline size_t pyr_smem_T() { return (size_t)TROWS * TS; }
+__host__ __device__ inline size_t pyr_smem_T(int trows) { return (size_t)trows * TS; }
 __host__ __device__ inline size_t pyr_smem_taps() { return (size_t)TBYTES * sizeof(TapX) + 40 * sizeof(TapX); }
-__host__ __device__ inline size_t pyr_smem_Hs() { return (size_t)TROWS * TW * 2; }
+__host__ __device__ inline size_t pyr_smem_Hs(int trows) { return (size_t)trows * TW * 2; }
 __host__ __device__ inline size_t pyr_smem_Hq(int srcRows) { return (((size_t)srcRows * HQS * 2) + 15) & ~(size_t)15; }
-__host__ __device__ inline size_t pyr_smem_planes() { return (size_t)2 * TROWS * 32 * sizeof(uint4); }     // PA + PB
-__host__ __device__ inline size_t pyr_smem_bytes(bool level0, int srcRows, int srcCols) {
-    const size_t late = pyr_smem_Hs() + pyr_smem_planes();
-    if (level0) return pyr_smem_T() + late;
+__host__ __device__ inline size_t pyr_smem_planes(int trows) { return (size_t)2 * trows * 32 * sizeof(uint4); }     // PA + PB
+__host__ __device__ inline size_t pyr_smem_bytes(int th, bool level0, int srcRows, int srcCols) {
+    const int trows = th + 2 * HALO;
+    const size_t late = pyr_smem_Hs(trows) + pyr_smem_planes(trows);
+    if (level0) return pyr_smem_T(trows) + late;
     const size_t stage = (size_t)srcRows * srcCols + 16;            // +16: S[o0 + 1] of the last column
     const size_t early = pyr_smem_taps() + pyr_smem_Hq(srcRows) + stage;
-    return pyr_smem_T() + (early > late ? early : late);
+    return pyr_smem_T(trows) + (early > late ? early : late);
 }
 
-template <bool LEVEL0>
+template <bool LEVEL0, int TH>
 __global__ void __launch_bounds__(PYR_THREADS) pyr_level_kernel(PyrArgs a) {
+    constexpr int TROWS = TH + 2 * HALO;
+    constexpr int RPW = TH / (PYR_THREADS / 32);          // tile rows per warp in the FAST and vertical-blur passes
     extern __shared__ __align__(16) uint8_t smem[];
     uint8_t* T = smem;                                   // TROWS x TS level tile with halo
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
@@ -193,8 +197,8 @@ __global__ void __launch_bounds__(PYR_THREADS) pyr_level_kernel(PyrArgs a) {
     unsigned short* Hs;                                  // TROWS x TW blur row sums, [group][A.lo A.hi B.lo B.hi]
     uint4* PA;                                           // TROWS x 32 pair planes (see fast_score4); PB = PA + TROWS * 32
 
-    Hs = (unsigned short*)(smem + pyr_smem_T());
-    PA = (uint4*)(smem + pyr_smem_T() + pyr_smem_Hs());
+    Hs = (unsigned short*)(smem + pyr_smem_T(TROWS));
+    PA = (uint4*)(smem + pyr_smem_T(TROWS) + pyr_smem_Hs(TROWS));
     if (LEVEL0) {
         // level 0 is the caller's image: copy with REFLECT_101 halo (copyMakeBorder, :1372); byte b of a T row is
         // column x0 - 4 + b.  Rows arrive at any alignment (the device copy keeps the host row step): interior
@@ -257,9 +261,9 @@ __global__ void __launch_bounds__(PYR_THREADS) pyr_level_kernel(PyrArgs a) {
             *(uint32_t*)(T + ty * TS + 4 * q) = v;
         }
     } else {
-        TapX* tapx = (TapX*)(smem + pyr_smem_T());
+        TapX* tapx = (TapX*)(smem + pyr_smem_T(TROWS));
         TapX* tapy = tapx + TBYTES;
-        unsigned short* Hq = (unsigned short*)(smem + pyr_smem_T() + pyr_smem_taps());   // source rows after the horizontal pass (h >> 4)
+        unsigned short* Hq = (unsigned short*)(smem + pyr_smem_T(TROWS) + pyr_smem_taps());   // source rows after the horizontal pass (h >> 4)
         uint8_t* S = (uint8_t*)Hq + pyr_smem_Hq(a.srcTileRows);                          // staged source rows
         // source rows/columns this tile touches
         const int ylo = max(0, y0 - HALO), yhi = min(h - 1, y0 + TH + HALO - 1);
@@ -363,7 +367,7 @@ __global__ void __launch_bounds__(PYR_THREADS) pyr_level_kernel(PyrArgs a) {
     // ---- level plane: 16 pixels per thread ------------------------------------
     {
         const int vx = (tid & 7) * 16, vy = tid >> 3;
-        if ((y0 + vy < h) && (x0 + vx < w)) {
+        if (vy < TH && (y0 + vy < h) && (x0 + vx < w)) {
             const uint32_t* t = (const uint32_t*)(T + (vy + HALO) * TS + TCOL0 + vx);
             const uint4 v = make_uint4(t[0], t[1], t[2], t[3]);
             *(uint4*)(a.pyr + (size_t)frame * a.pyrFrameStride + (size_t)(ORB_EDGE + y0 + vy) * a.pitch + ORB_XPAD + x0 + vx) = v;
@@ -384,11 +388,11 @@ __global__ void __launch_bounds__(PYR_THREADS) pyr_level_kernel(PyrArgs a) {
     }
     __syncthreads();      // planes and Hs complete
 
-    // ---- FAST score: warp `wid` owns tile rows 4*wid..4*wid+3, lane = 4-pixel group ----
+    // ---- FAST score: warp `wid` owns tile rows RPW*wid..RPW*wid+RPW-1, lane = 4-pixel group ----
     const int gx = x0 + 4 * lane;                        // level column of the group's first pixel
 #pragma unroll 1
-    for (int k = 0; k < 4; k++) {
-        const int r = 4 * wid + k, y = y0 + r;
+    for (int k = 0; k < RPW; k++) {
+        const int r = RPW * wid + k, y = y0 + r;
         if (y >= h || gx >= w) continue;
         uint32_t s = 0;
         if (y >= ORB_EDGE && y < h - ORB_EDGE && gx + 3 >= ORB_EDGE && gx < w - ORB_EDGE) {
@@ -404,23 +408,23 @@ __global__ void __launch_bounds__(PYR_THREADS) pyr_level_kernel(PyrArgs a) {
         *(uint32_t*)(a.score + (size_t)frame * a.planeFrameStride + (size_t)y * a.pitch + ORB_XPAD + gx) = s;
     }
 
-    // ---- vertical blur pass: warp `wid` owns tile rows 4*wid..4*wid+3.  The ten row sums a lane needs per pixel are
+    // ---- vertical blur pass: warp `wid` owns tile rows RPW*wid..RPW*wid+RPW-1.  The RPW + 6 row sums a lane needs per pixel are
     //      paired vertically, P[j] = (H[j], H[j+1]) as u16x2, so that one DP2A applies two taps:
     //      out[k] = (18,34).P[k] + (48,56).P[k+2] + (48,34).P[k+4] + (0,18).P[k+5] ----
     {
         const unsigned short* col = Hs + 4 * lane;
-        uint2 v[10];
+        uint2 v[RPW + 6];
 #pragma unroll
-        for (int j = 0; j < 10; j++) v[j] = *(const uint2*)(col + (4 * wid + j) * TW);     // .x = (H(c), H(c+2)), .y = (H(c+1), H(c+3))
-        uint32_t P[9][4];                                 // pixel order c, c+1, c+2, c+3
+        for (int j = 0; j < RPW + 6; j++) v[j] = *(const uint2*)(col + (RPW * wid + j) * TW);     // .x = (H(c), H(c+2)), .y = (H(c+1), H(c+3))
+        uint32_t P[RPW + 5][4];                                 // pixel order c, c+1, c+2, c+3
 #pragma unroll
-        for (int j = 0; j < 9; j++) {
+        for (int j = 0; j < RPW + 5; j++) {
             P[j][0] = __byte_perm(v[j].x, v[j + 1].x, 0x5410); P[j][2] = __byte_perm(v[j].x, v[j + 1].x, 0x7632);
             P[j][1] = __byte_perm(v[j].y, v[j + 1].y, 0x5410); P[j][3] = __byte_perm(v[j].y, v[j + 1].y, 0x7632);
         }
 #pragma unroll
-        for (int k = 0; k < 4; k++) {
-            const int y = y0 + 4 * wid + k;
+        for (int k = 0; k < RPW; k++) {
+            const int y = y0 + RPW * wid + k;
             uint32_t o[4];
 #pragma unroll
             for (int q = 0; q < 4; q++) {
