@@ -112,6 +112,14 @@ int orbx_level_size(const orbx_t* ex, int level, int* width, int* height);
 int orbx_get_level(orbx_t* ex, int frame, int level, int border, int blurred, uint8_t* dst,
                    size_t dst_step);
 
+/* The whole bordered pyramid of frame `frame` of the last call in ONE device-to-host copy, into a page-locked buffer
+ * the instance owns.  Level l is the (w_l + 38) x (h_l + 38) bordered image; its interior pixel (0, 0) - what
+ * mvImagePyramid[l] points at, src/ORBextractor.cc:1353-1354 - lies at *base + interior_offset[l], rows are pitch[l]
+ * bytes apart (the device layout), and the 19 border pixels are addressable around it exactly as
+ * in the reference's ROI of `temp`.  The buffer is overwritten by the next orbx_pyramid_host call of this instance and
+ * freed by orbx_destroy.  interior_offset and pitch receive orbx_levels() entries. */
+int orbx_pyramid_host(orbx_t* ex, int frame, const uint8_t** base, size_t* interior_offset, size_t* pitch);
+
 /* Introspection for the parity tests: the FAST candidates of one level in the
  * order of vToDistributeKeys (src/ORBextractor.cc:938-1002) as (x, y, response)
  * int triples, coordinates relative to (minBorderX, minBorderY) = (16, 16). */

@@ -54,6 +54,7 @@ def lib() -> C.CDLL:
     L.orbx_synchronize.argtypes = [vp]; L.orbx_synchronize.restype = i
     L.orbx_level_size.argtypes = [vp, i, C.POINTER(i), C.POINTER(i)]; L.orbx_level_size.restype = i
     L.orbx_get_level.argtypes = [vp, i, i, i, i, vp, sz]; L.orbx_get_level.restype = i
+    L.orbx_pyramid_host.argtypes = [vp, i, C.POINTER(vp), vp, vp]; L.orbx_pyramid_host.restype = i
     L.orbx_get_candidates.argtypes = [vp, i, i, vp, i, C.POINTER(i)]; L.orbx_get_candidates.restype = i
     L.orbx_stereo_match.argtypes = [vp, vp, i, vp, vp, i, vp, vp, i, f, f, vp, vp, C.POINTER(i)]; L.orbx_stereo_match.restype = i
     L.orbx_stereo_match_batch_device.argtypes = [vp, vp, i, vp, vp, vp, vp, vp, vp, i, f, f, vp, vp, vp]

@@ -74,6 +74,7 @@ struct orbx_extractor {
     cudaEvent_t evIn[ORBX_NBUF] = {}, evCompute[ORBX_NBUF] = {}, evOut[ORBX_NBUF] = {};
     uint8_t* d_stereo = nullptr; size_t stereoBytes = 0;     // scratch of orbx_stereo_match
     uint8_t* h_stereo = nullptr; size_t hStereoBytes = 0;    // its pinned staging: one H2D and one D2H per call
+    uint8_t* h_pyr = nullptr; size_t hPyrBytes = 0;          // orbx_pyramid_host: page-locked copy of one frame's pyramid
     // single-frame call with pageable buffers (Tracking's case): the copy-in, the 12 launches and the copy-out are
     // captured once into a CUDA graph and replayed - one launch call instead of sixteen on the latency path, which is
     // what two host threads (the stereo pair, reference src/Frame.cc:94-103) otherwise serialise on in the driver
@@ -536,6 +537,7 @@ void orbx_destroy(orbx_t* e) {
     free_workspace(e);
     cudaFree(e->d_err); cudaFree(e->d_stereo);
     if (e->h_stereo) cudaFreeHost(e->h_stereo);
+    if (e->h_pyr) cudaFreeHost(e->h_pyr);
     for (int hlf = 0; hlf < 2; hlf++) for (int i = 0; i < 8; i++) if (e->ev[hlf][i]) cudaEventDestroy(e->ev[hlf][i]);
     if (e->evFork) cudaEventDestroy(e->evFork);
     for (auto& ev : e->evJoin) if (ev) cudaEventDestroy(ev);
@@ -900,6 +902,30 @@ int orbx_get_level(orbx_t* e, int frame, int level, int border, int blurred, uin
     else src = w.d_pyr + (size_t)frame * e->g.pyrBytes + v.pyrOff + (size_t)(ORB_EDGE - border) * v.pitch + ORB_XPAD - border;
     CK(cudaMemcpy2DAsync(dst, dst_step, src, v.pitch, v.w + 2 * border, v.h + 2 * border, cudaMemcpyDeviceToHost, e->stream));
     CK(cudaStreamSynchronize(e->stream));
+    return ORBX_OK;
+}
+
+int orbx_pyramid_host(orbx_t* e, int frame, const uint8_t** base, size_t* interior_offset, size_t* pitch) {
+    if (!e || !e->haveGeom || frame < 0 || frame >= e->ws[e->lastWs].lastFrames || !base || !interior_offset || !pitch)
+        return ORBX_E_INVALID;
+    std::lock_guard<std::mutex> lk(e->mtx);
+    CK(cudaSetDevice(e->device));
+    const FrameGeom& g = e->g;
+    if (e->hPyrBytes < g.pyrBytes) {
+        if (e->h_pyr) cudaFreeHost(e->h_pyr);
+        e->h_pyr = nullptr; e->hPyrBytes = 0;
+        CK(cudaMallocHost(&e->h_pyr, g.pyrBytes));
+        e->hPyrBytes = g.pyrBytes;
+    }
+    cudaStream_t st = e->ws[e->lastWs].stream;
+    CK(cudaMemcpyAsync(e->h_pyr, e->ws[e->lastWs].d_pyr + (size_t)frame * g.pyrBytes, g.pyrBytes, cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    for (int l = 0; l < g.nlevels; l++) {
+        const LevelGeom& v = g.lv[l];
+        interior_offset[l] = (size_t)v.pyrOff + (size_t)ORB_EDGE * v.pitch + ORB_XPAD;
+        pitch[l] = (size_t)v.pitch;
+    }
+    *base = e->h_pyr;
     return ORBX_OK;
 }
 

@@ -45,15 +45,24 @@ ORBextractor::~ORBextractor() { orbx_destroy(mpDev); }
 void ORBextractor::DownloadPyramid(int width, int height) {
     (void)width; (void)height;
     const int B = 19;                                   // EDGE_THRESHOLD, src/ORBextractor.cc:74
+    if (mbDownloadPyramid) {
+        // one device-to-host copy of the whole bordered pyramid into the instance's page-locked buffer; the levels are
+        // headers over it: mvImagePyramid[l] = ROI at (19, 19) of the bordered level, :1353-1354 (valid until the next call)
+        const uint8_t* base = nullptr;
+        std::vector<size_t> off(nlevels), pitch(nlevels);
+        check(orbx_pyramid_host(mpDev, 0, &base, off.data(), pitch.data()), "orbx_pyramid_host");
+        for (int l = 0; l < nlevels; l++) {
+            int w = 0, h = 0;
+            check(orbx_level_size(mpDev, l, &w, &h), "orbx_level_size");
+            mvImagePyramid[l] = cv::Mat(h, w, CV_8UC1, const_cast<uint8_t*>(base) + off[l], pitch[l]);
+        }
+        return;
+    }
     for (int l = 0; l < nlevels; l++) {
         int w = 0, h = 0;
         check(orbx_level_size(mpDev, l, &w, &h), "orbx_level_size");
         cv::Mat& lv = mvImagePyramid[l];
-        if (mbDownloadPyramid) {
-            cv::Mat temp(h + 2 * B, w + 2 * B, CV_8UC1);
-            check(orbx_get_level(mpDev, 0, l, B, 0, temp.data, temp.step), "orbx_get_level");
-            lv = temp(cv::Rect(B, B, w, h));            // :1353-1354
-        } else if (lv.rows != h || lv.cols != w) {
+        if (lv.rows != h || lv.cols != w) {             // sizes only (Frame.cc:642 reads .rows): zeroed pixels
             cv::Mat temp(h + 2 * B, w + 2 * B, CV_8UC1);
             std::memset(temp.data, 0, temp.step * temp.rows);
             lv = temp(cv::Rect(B, B, w, h));

@@ -37,3 +37,20 @@ for i in range(50):
     if i >= 10:
         acc += t
 print("single-frame stage ms:", dict(zip(["pyramid_blur_fast", "border", "cell_nms", "quadtree", "describe"], (acc / 40).round(4).tolist())))
+# the stereo constructor's pattern through the C++ drop-in class: two ORBextractor instances on two std::threads
+# (reference src/Frame.cc:94-103), mvImagePyramid downloaded as the class does by default; per-pair time from the
+# difference of a long and a short run (constructors excluded)
+harness = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tests", "cpp", "libdropin_harness.so")
+if os.path.exists(harness):
+    Hn = C.CDLL(harness)
+    right = synth_frame(W, H, 3, shift=(-20, 0))
+    kl = np.empty((cap, 28), np.uint8); dl = np.empty((cap, 32), np.uint8); kr = np.empty((cap, 28), np.uint8); dr = np.empty((cap, 32), np.uint8)
+    nl, nr = C.c_int(), C.c_int()
+    def run(reps):
+        t0 = time.perf_counter()
+        Hn.dropin_extract_stereo(C.c_void_p(img.ctypes.data), C.c_void_p(right.ctypes.data), W, H, 2000, C.c_void_p(kl.ctypes.data), C.c_void_p(dl.ctypes.data),
+                                 C.byref(nl), C.c_void_p(kr.ctypes.data), C.c_void_p(dr.ctypes.data), C.byref(nr), cap, reps)
+        return time.perf_counter() - t0
+    run(3)
+    a = min(run(5) for _ in range(3)); b = min(run(205) for _ in range(3))
+    print(f"C++ drop-in stereo pair (2 std::threads spawned per pair, pyramids downloaded): {(b - a) / 200 * 1e3:.3f} ms per pair, n = {nl.value}/{nr.value}")
