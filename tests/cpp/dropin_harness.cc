@@ -1,6 +1,7 @@
 // Test harness (tests/ only): drives the C++ drop-in classes ORB_SLAM2::ORBextractor / ORBmatcher / Frame the way
 // Frame.cc and Tracking.cc drive the reference's (Frame::ExtractORB src/Frame.cc:320-326; Tracking.cc:635-644,
 // :921-944, :1236-1243), and hands the results to pytest as plain arrays.
+#include <chrono>
 #include <cstring>
 #include <cmath>
 #include <memory>
@@ -123,6 +124,36 @@ int dropin_stereo_frame(const uint8_t* left, const uint8_t* right, int w, int h,
     F.ComputeStereoMatches();
     *nl = F.N;
     for (int i = 0; i < F.N && i < cap; i++) { kl[i] = F.mvKeys[i]; uRight[i] = F.mvuRight[i]; depth[i] = F.mvDepth[i]; }
+    return 0;
+}
+
+// timing aid (tools/latency_run.py): the same stereo constructor `reps` times on persistent extractors; mean milliseconds
+// of the two-thread extraction and of ComputeStereoMatches
+int dropin_time_stereo_frame(const uint8_t* left, const uint8_t* right, int w, int h, int nfeatures, float mbf, float mb,
+                             int downloadPyramid, int reps, double* msExtract, double* msMatch, int* nMatched) {
+    ORBextractor exL(nfeatures, 1.2f, 8, 20, 7), exR(nfeatures, 1.2f, 8, 20, 7);
+    exL.SetPyramidDownload(downloadPyramid != 0); exR.SetPyramidDownload(downloadPyramid != 0);
+    cv::Mat imL(h, w, CV_8UC1, (void*)left, (size_t)w), imR(h, w, CV_8UC1, (void*)right, (size_t)w);
+    double te = 0, tm = 0;
+    int matched = 0;
+    for (int r = -3; r < reps; r++) {                    // three untimed warm-up rounds
+        Frame F;
+        F.mpORBextractorLeft = &exL; F.mpORBextractorRight = &exR;
+        const auto t0 = std::chrono::steady_clock::now();
+        std::thread tl([&] { exL(imL, cv::Mat(), F.mvKeys, F.mDescriptors); });
+        std::thread tr([&] { exR(imR, cv::Mat(), F.mvKeysRight, F.mDescriptorsRight); });
+        tl.join(); tr.join();
+        const auto t1 = std::chrono::steady_clock::now();
+        F.N = (int)F.mvKeys.size();
+        F.mvScaleFactors = exL.GetScaleFactors(); F.mvInvScaleFactors = exL.GetInverseScaleFactors();
+        F.mbf = mbf; F.mb = mb;
+        F.ComputeStereoMatches();
+        const auto t2 = std::chrono::steady_clock::now();
+        if (r >= 0) { te += std::chrono::duration<double, std::milli>(t1 - t0).count(); tm += std::chrono::duration<double, std::milli>(t2 - t1).count(); }
+        matched = 0;
+        for (int i = 0; i < F.N; i++) matched += F.mvuRight[i] >= 0;
+    }
+    *msExtract = te / reps; *msMatch = tm / reps; *nMatched = matched;
     return 0;
 }
 

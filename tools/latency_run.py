@@ -54,3 +54,8 @@ if os.path.exists(harness):
     run(3)
     a = min(run(5) for _ in range(3)); b = min(run(205) for _ in range(3))
     print(f"C++ drop-in stereo pair (2 std::threads spawned per pair, pyramids downloaded): {(b - a) / 200 * 1e3:.3f} ms per pair, n = {nl.value}/{nr.value}")
+    me, mm, nm = C.c_double(), C.c_double(), C.c_int()
+    for dl_ in (1, 0):
+        Hn.dropin_time_stereo_frame(C.c_void_p(img.ctypes.data), C.c_void_p(right.ctypes.data), W, H, 2000, C.c_float(386.1448), C.c_float(0.537),
+                                    dl_, 200, C.byref(me), C.byref(mm), C.byref(nm))
+        print(f"C++ stereo Frame constructor, pyramids {'downloaded' if dl_ else 'kept on the device'}: ExtractORB x2 {me.value:.3f} ms + ComputeStereoMatches {mm.value:.3f} ms per pair ({nm.value} stereo matches)")
