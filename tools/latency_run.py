@@ -59,3 +59,22 @@ if os.path.exists(harness):
         Hn.dropin_time_stereo_frame(C.c_void_p(img.ctypes.data), C.c_void_p(right.ctypes.data), W, H, 2000, C.c_float(386.1448), C.c_float(0.537),
                                     dl_, 200, C.byref(me), C.byref(mm), C.byref(nm))
         print(f"C++ stereo Frame constructor, pyramids {'downloaded' if dl_ else 'kept on the device'}: ExtractORB x2 {me.value:.3f} ms + ComputeStereoMatches {mm.value:.3f} ms per pair ({nm.value} stereo matches)")
+# do two single-frame chains overlap on the device?  (two extractors, device-resident input, enqueued from one thread)
+exB = ORBextractor(2000, 1.2, 8, 20, 7); hB = exB.handle
+dk2 = torch.empty((cap, 28), dtype=torch.uint8, device="cuda"); dd2 = torch.empty((cap, 32), dtype=torch.uint8, device="cuda"); dn2 = torch.zeros(4, dtype=torch.int32, device="cuda")
+check(L.orbx_set_profiling(h, 0), "prof")
+def dev(hh, k_, d_, n_):
+    check(L.orbx_extract_batch_device(hh, dimg.data_ptr(), 1, W, H, 1280, 1280 * H, k_.data_ptr(), d_.data_ptr(), cap, n_.data_ptr()), "dev")
+for both in (False, True):
+    ts = []
+    for i in range(60):
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        dev(h, dk, dd, dn)
+        if both:
+            dev(hB, dk2, dd2, dn2)
+        L.orbx_synchronize(h)
+        if both:
+            L.orbx_synchronize(hB)
+        ts.append(time.perf_counter() - t0)
+    print(f"device-resident single-frame chain{'s x2 on two instances' if both else ''}: {np.median(ts[10:]) * 1e3:.3f} ms")
