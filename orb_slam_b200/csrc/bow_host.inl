@@ -58,25 +58,32 @@ extern "C" int orbm_search_by_bow(orbm_t* m, int variant,
             total += (size_t)(e2 - s2);
         }
     }
-    std::vector<uint16_t> dist(total);
+    const uint16_t* dist = nullptr;                      // the distances, in the context's page-locked result buffer
     if (!rows.empty()) {
+        // one page-locked block in, one out: [desc1 | desc2 | items2 | rows] -> device, distances back
         const size_t nitems2 = (size_t)fv2->start[fv2->nnodes];      // > 0: some row has candidates
+        auto al = [](size_t v) { return (v + 255) & ~(size_t)255; };
+        const size_t o1 = 0, o2 = o1 + al((size_t)n1 * 32), o3 = o2 + al((size_t)n2 * 32), o4 = o3 + al(nitems2 * 4);
+        const size_t inBytes = o4 + al(rows.size() * sizeof(BowRow));
         int rc;
-        if ((rc = m->w0.reserve((size_t)n1 * 32))) return rc;
-        if ((rc = m->w1.reserve((size_t)n2 * 32))) return rc;
-        if ((rc = m->w2.reserve(nitems2 * 4))) return rc;
-        if ((rc = m->w3.reserve(rows.size() * sizeof(BowRow)))) return rc;
+        if ((rc = m->h0.reserve(inBytes))) return rc;
+        if ((rc = m->h1.reserve(total * 2))) return rc;
+        if ((rc = m->w0.reserve(inBytes))) return rc;
         if ((rc = m->w4.reserve(total * 2))) return rc;
-        CKM(cudaMemcpyAsync(m->w0.p, desc1, (size_t)n1 * 32, cudaMemcpyHostToDevice, m->stream));
-        CKM(cudaMemcpyAsync(m->w1.p, desc2, (size_t)n2 * 32, cudaMemcpyHostToDevice, m->stream));
-        CKM(cudaMemcpyAsync(m->w2.p, fv2->items, nitems2 * 4, cudaMemcpyHostToDevice, m->stream));
-        CKM(cudaMemcpyAsync(m->w3.p, rows.data(), rows.size() * sizeof(BowRow), cudaMemcpyHostToDevice, m->stream));
+        uint8_t* hb = (uint8_t*)m->h0.p;
+        std::memcpy(hb + o1, desc1, (size_t)n1 * 32);
+        std::memcpy(hb + o2, desc2, (size_t)n2 * 32);
+        std::memcpy(hb + o3, fv2->items, nitems2 * 4);
+        std::memcpy(hb + o4, rows.data(), rows.size() * sizeof(BowRow));
+        uint8_t* db = (uint8_t*)m->w0.p;
+        CKM(cudaMemcpyAsync(db, hb, inBytes, cudaMemcpyHostToDevice, m->stream));
         const int nrows = (int)rows.size();
-        bow_dist_kernel<<<(nrows + 7) / 8, 256, 0, m->stream>>>((const BowRow*)m->w3.p, nrows, (const uint32_t*)m->w0.p,
-                                                                 (const uint32_t*)m->w1.p, (const uint32_t*)m->w2.p, (uint16_t*)m->w4.p);
+        bow_dist_kernel<<<(nrows + 7) / 8, 256, 0, m->stream>>>((const BowRow*)(db + o4), nrows, (const uint32_t*)(db + o1),
+                                                                 (const uint32_t*)(db + o2), (const uint32_t*)(db + o3), (uint16_t*)m->w4.p);
         CKM(cudaGetLastError());
-        CKM(cudaMemcpyAsync(dist.data(), m->w4.p, total * 2, cudaMemcpyDeviceToHost, m->stream));
+        CKM(cudaMemcpyAsync(m->h1.p, m->w4.p, total * 2, cudaMemcpyDeviceToHost, m->stream));
         CKM(cudaStreamSynchronize(m->stream));
+        dist = (const uint16_t*)m->h1.p;
     }
     // ---- replay
     std::vector<int> rotHist[ORBM_HISTO_LENGTH];
@@ -84,7 +91,7 @@ extern "C" int orbm_search_by_bow(orbm_t* m, int variant,
     int nm = 0;
     for (const BowRow& r : rows) {
         int bestDist1 = 256, bestIdx2 = -1, bestDist2 = 256;
-        const uint16_t* d = dist.data() + r.out;
+        const uint16_t* d = dist + r.out;
         for (int j = 0; j < r.cnt2; j++) {
             const uint32_t i2 = fv2->items[r.off2 + j];
             if (variant == ORBM_BOW_KEYFRAME_FRAME) { if (match[i2] >= 0) continue; }          // :209-210
