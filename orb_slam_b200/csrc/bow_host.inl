@@ -206,13 +206,18 @@ extern "C" int orbm_search_for_triangulation(orbm_t* m, const orbm_keyframe* kf1
     int rc;
     if ((rc = m->w0.reserve(off))) return rc;
     uint8_t* base = (uint8_t*)m->w0.p;
-    auto up = [&](size_t o, const void* src, size_t bytes) { return bytes ? cudaMemcpyAsync(base + o, src, bytes, cudaMemcpyHostToDevice, m->stream) : cudaSuccess; };
-    CKM(up(oDesc1, kf1->descriptors, (size_t)n1 * 32)); CKM(up(oDesc2, kf2->descriptors, (size_t)n2 * 32));
-    CKM(up(oKeys1, kf1->keysUn, (size_t)n1 * sizeof(orbx_keypoint))); CKM(up(oKeys2, kf2->keysUn, (size_t)n2 * sizeof(orbx_keypoint)));
-    CKM(up(oUr1, kf1->uRight, (size_t)n1 * 4)); CKM(up(oUr2, kf2->uRight, (size_t)n2 * 4));
-    CKM(up(oHas2, kf2->has_point, (size_t)n2)); CKM(up(oItems2, fv2->items, nitems2 * 4));
-    CKM(up(oRows, rows.data(), rows.size() * sizeof(BowRow)));
-    CKM(up(oSf, scaleFactors2, (size_t)nlevels * 4)); CKM(up(oSig, levelSigma2, (size_t)nlevels * 4));
+    // every input is staged at its device offset in one page-locked block: one H2D per call
+    if ((rc = m->h0.reserve(oMatch))) return rc;
+    if ((rc = m->h1.reserve((size_t)std::max(n1, 1) * 4))) return rc;
+    uint8_t* hb = (uint8_t*)m->h0.p;
+    auto up = [&](size_t o, const void* src, size_t bytes) { if (bytes) std::memcpy(hb + o, src, bytes); };
+    up(oDesc1, kf1->descriptors, (size_t)n1 * 32); up(oDesc2, kf2->descriptors, (size_t)n2 * 32);
+    up(oKeys1, kf1->keysUn, (size_t)n1 * sizeof(orbx_keypoint)); up(oKeys2, kf2->keysUn, (size_t)n2 * sizeof(orbx_keypoint));
+    up(oUr1, kf1->uRight, (size_t)n1 * 4); up(oUr2, kf2->uRight, (size_t)n2 * 4);
+    up(oHas2, kf2->has_point, (size_t)n2); up(oItems2, fv2->items, nitems2 * 4);
+    up(oRows, rows.data(), rows.size() * sizeof(BowRow));
+    up(oSf, scaleFactors2, (size_t)nlevels * 4); up(oSig, levelSigma2, (size_t)nlevels * 4);
+    CKM(cudaMemcpyAsync(base, hb, oMatch, cudaMemcpyHostToDevice, m->stream));
     CKM(cudaMemsetAsync(base + oMatch, 0xff, (size_t)n1 * 4, m->stream));                      // -1
     ta.rows = (const BowRow*)(base + oRows); ta.nrows = (int)rows.size();
     ta.desc1 = (const uint32_t*)(base + oDesc1); ta.desc2 = (const uint32_t*)(base + oDesc2); ta.items2 = (const uint32_t*)(base + oItems2);
@@ -222,8 +227,9 @@ extern "C" int orbm_search_for_triangulation(orbm_t* m, const orbm_keyframe* kf1
     ta.matches12 = (int32_t*)(base + oMatch);
     triangulation_match_kernel<<<(ta.nrows + 7) / 8, 256, 0, m->stream>>>(ta);
     CKM(cudaGetLastError());
-    CKM(cudaMemcpyAsync(matches12, base + oMatch, (size_t)n1 * 4, cudaMemcpyDeviceToHost, m->stream));
+    CKM(cudaMemcpyAsync(m->h1.p, base + oMatch, (size_t)n1 * 4, cudaMemcpyDeviceToHost, m->stream));
     CKM(cudaStreamSynchronize(m->stream));
+    std::memcpy(matches12, m->h1.p, (size_t)n1 * 4);
     // rotation consistency (:829-875): only the bin sizes matter, every entry of a losing bin is dropped
     int nm = 0;
     std::vector<int> rotHist[ORBM_HISTO_LENGTH];

@@ -159,7 +159,9 @@ int vocab_descend_host(orbm_t* m, const orbm_vocab_t* v, const uint8_t* desc, in
     if ((rc = m->w0.reserve((size_t)n * 32))) return rc;
     if ((rc = m->w1.reserve((size_t)n * 8))) return rc;
     if ((rc = m->h1.reserve((size_t)n * 8))) return rc;
-    CKM(cudaMemcpyAsync(m->w0.p, desc, (size_t)n * 32, cudaMemcpyHostToDevice, m->stream));
+    if ((rc = m->h0.reserve((size_t)n * 32))) return rc;
+    std::memcpy(m->h0.p, desc, (size_t)n * 32);          // page-locked staging: the H2D is a plain DMA
+    CKM(cudaMemcpyAsync(m->w0.p, m->h0.p, (size_t)n * 32, cudaMemcpyHostToDevice, m->stream));
     vocab_descend_kernel<<<(unsigned)(((size_t)n * VOC_GROUP + 255) / 256), 256, 0, m->stream>>>(v->dev(), (const uint4*)m->w0.p, (size_t)n,
                                                                                                    levelsup, (uint2*)m->w1.p);
     CKM(cudaGetLastError());
