@@ -75,6 +75,28 @@ def test_tables_match_oracle():
         gpu.close()
 
 
+@pytest.mark.parametrize("w,h,nf,kind,idx", CASES)
+def test_batch_tiles_match_oracle(w, h, nf, kind, idx):
+    """Calls of one or two frames take K1's 16-row tiles (TH_LATENCY), larger batches the 32-row tiles: the same shapes
+    again as a three-frame batch, planes of the last frame included."""
+    from orb_slam_b200 import ORBextractor
+    img = make_image(w, h, kind, idx)
+    imgs = np.stack([img[::-1].copy(), np.ascontiguousarray(img[:, ::-1]), img])
+    gpu = ORBextractor(nf, 1.2, 8, 20, 7)
+    cpu = OracleExtractor(nf, 1.2, 8, 20, 7)
+    res = gpu.extract_batch(imgs)
+    for i in (0, 1):
+        compare(*res[i], *cpu(imgs[i]))
+    ok, od = cpu(img)                                    # the oracle's planes now belong to imgs[2]
+    compare(*res[2], ok, od)
+    for l in range(8):
+        assert np.array_equal(gpu.get_level(l, frame=2, border=19), cpu.get_level(l, border=19)), f"pyramid level {l}"
+        ob = cpu.get_level(l, blurred=True)
+        if ob is not None:
+            assert np.array_equal(gpu.get_level(l, frame=2, blurred=True), ob), f"blurred level {l}"
+    gpu.close()
+
+
 def test_batch_equals_single_and_is_repeatable():
     from orb_slam_b200 import ORBextractor
     imgs = np.stack([synth_frame(752, 480, 10 + i) for i in range(5)])
