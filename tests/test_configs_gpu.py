@@ -98,10 +98,13 @@ def test_empty_flat_and_unsupported_images():
 def test_4k_stress_frame(w, h, nf):
     from orb_slam_b200 import ORBextractor
     img = synth_frame(w, h, 21)
-    gk, gd = ORBextractor(nf, 1.2, 8, 20, 7)(img)
+    ex = ORBextractor(nf, 1.2, 8, 20, 7)
+    gk, gd = ex(img)                                     # one frame: 16-row K1 tiles
     ok, od = OracleExtractor(nf, 1.2, 8, 20, 7)(img)
     assert len(ok) >= nf
     same(gk, gd, ok, od)
+    for bk, bd in ex.extract_batch(np.stack([img] * 3)):  # a batch: 32-row tiles
+        assert bk.tobytes() == gk.tobytes() and np.array_equal(bd, gd)
 
 
 def test_other_extractor_settings():
