@@ -45,7 +45,18 @@ static void point_from(MapPoint& p, const orbm_mappoint& s) {
     p.mTrackViewCos = s.trackViewCos; p.mnTrackScaleLevel = s.trackScaleLevel;
 }
 
+// wall time of the last timed class call (tools/latency_run.py reads it through dropin_last_ms)
+static double g_lastMs = 0;
+template <class F> static int timed(F&& f) {
+    const auto t0 = std::chrono::steady_clock::now();
+    const int r = f();
+    g_lastMs = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+    return r;
+}
+
 extern "C" {
+
+double dropin_last_ms() { return g_lastMs; }
 
 // ORBextractor::operator() through the C++ class.  levels: optional buffer receiving the concatenated bordered
 // (w+38)x(h+38) buffers behind mvImagePyramid[l]; returns the keypoint count.
@@ -184,7 +195,7 @@ int dropin_search_for_initialization(const orbm_frame* f1, const orbm_frame* f2,
     for (int i = 0; i < f1->N; i++) vbPrevMatched[i] = cv::Point2f(prev[2 * i], prev[2 * i + 1]);
     std::vector<int> vnMatches12;
     ORBmatcher matcher(nnratio, checkOri != 0);
-    const int n = matcher.SearchForInitialization(*F1, *F2, vbPrevMatched, vnMatches12, windowSize);
+    const int n = timed([&] { return matcher.SearchForInitialization(*F1, *F2, vbPrevMatched, vnMatches12, windowSize); });
     for (int i = 0; i < f1->N; i++) { m12[i] = vnMatches12[i]; prev[2 * i] = vbPrevMatched[i].x; prev[2 * i + 1] = vbPrevMatched[i].y; }
     return n;
 }
@@ -201,7 +212,7 @@ int dropin_search_by_projection_frame(const orbm_frame* cur, const orbm_frame* l
         if (curObs[i] >= 0) { curPts[i].nObs = curObs[i]; C->mvpMapPoints[i] = &curPts[i]; }
     std::vector<MapPoint*> before = C->mvpMapPoints;
     ORBmatcher matcher(0.9f, checkOri != 0);
-    const int n = matcher.SearchByProjection(*C, *L, th, bMono != 0);
+    const int n = timed([&] { return matcher.SearchByProjection(*C, *L, th, bMono != 0); });
     for (int i = 0; i < cur->N; i++) {
         MapPoint* p = C->mvpMapPoints[i];
         if (p == before[i]) assign[i] = -2;
@@ -221,7 +232,7 @@ int dropin_search_by_projection_points(const orbm_frame* f, const orbm_mappoint*
         if (obs[i] >= 0) { held[i].nObs = obs[i]; F->mvpMapPoints[i] = &held[i]; }
     std::vector<MapPoint*> before = F->mvpMapPoints;
     ORBmatcher matcher(nnratio, true);
-    const int n = matcher.SearchByProjection(*F, vp, th);
+    const int n = timed([&] { return matcher.SearchByProjection(*F, vp, th); });
     for (int i = 0; i < f->N; i++) {
         MapPoint* p = F->mvpMapPoints[i];
         assign[i] = (p == before[i]) ? -2 : (int32_t)(p - mps.data());
@@ -261,7 +272,7 @@ int dropin_search_by_bow_frame(const uint8_t* desc1, const float* angle1, const 
         for (int t = fv2->start[k]; t < fv2->start[k + 1]; t++) F.mFeatVec.addFeature(fv2->node_ids[k], fv2->items[t]);
     std::vector<MapPoint*> vpMapPointMatches(3, reinterpret_cast<MapPoint*>(8));      // must be replaced, not appended to
     ORBmatcher matcher(nnratio, checkOri != 0);
-    const int n = matcher.SearchByBoW(&K, F, vpMapPointMatches);
+    const int n = timed([&] { return matcher.SearchByBoW(&K, F, vpMapPointMatches); });
     if ((int)vpMapPointMatches.size() != n2) return -1000;
     for (int i = 0; i < n2; i++) match[i] = vpMapPointMatches[i] ? (int32_t)(vpMapPointMatches[i] - store.data()) : -1;
     return n;
@@ -276,7 +287,7 @@ int dropin_search_by_bow_keyframes(const uint8_t* desc1, const float* angle1, co
     keyframe_from(K2, s2, desc2, angle2, valid2, bad2, n2, fv2);
     std::vector<MapPoint*> vpMatches12;
     ORBmatcher matcher(nnratio, checkOri != 0);
-    const int n = matcher.SearchByBoW(&K1, &K2, vpMatches12);
+    const int n = timed([&] { return matcher.SearchByBoW(&K1, &K2, vpMatches12); });
     if ((int)vpMatches12.size() != n1) return -1000;
     for (int i = 0; i < n1; i++) match[i] = vpMatches12[i] ? (int32_t)(vpMatches12[i] - s2.data()) : -1;
     return n;
@@ -306,7 +317,7 @@ int dropin_search_by_projection_keyframe(const orbm_frame* cur, const orbm_mappo
     for (int i = 0; i < cur->N; i++) if (curHas[i]) C->mvpMapPoints[i] = &held[i];
     std::vector<MapPoint*> before = C->mvpMapPoints;
     ORBmatcher matcher(0.9f, checkOri != 0);
-    const int nm = matcher.SearchByProjection(*C, &K, sFound, th, ORBdist);
+    const int nm = timed([&] { return matcher.SearchByProjection(*C, &K, sFound, th, ORBdist); });
     for (int i = 0; i < cur->N; i++) {
         MapPoint* p = C->mvpMapPoints[i];
         if (p == before[i]) assign[i] = -2;
@@ -345,7 +356,7 @@ int dropin_search_for_triangulation(const orbm_keyframe* kf1, const orbm_keyfram
     std::memcpy(F.data, F12, 36);
     std::vector<std::pair<size_t, size_t> > vMatchedPairs(2);
     ORBmatcher matcher(0.6f, checkOri != 0);
-    const int n = matcher.SearchForTriangulation(&K1, &K2, F, vMatchedPairs, onlyStereo != 0);
+    const int n = timed([&] { return matcher.SearchForTriangulation(&K1, &K2, F, vMatchedPairs, onlyStereo != 0); });
     if ((int)vMatchedPairs.size() != n || n > cap) return -1000;
     for (int i = 0; i < n; i++) { pairs[2 * i] = (int32_t)vMatchedPairs[i].first; pairs[2 * i + 1] = (int32_t)vMatchedPairs[i].second; }
     return n;
@@ -400,7 +411,7 @@ int dropin_fuse(const orbm_frame* kf, const float* invSigma2, const orbm_mappoin
     std::vector<MapPoint*> vp(norder);
     for (int j = 0; j < norder; j++) vp[j] = (order[j] >= 0 && pts[order[j]].valid) ? &table[order[j]] : static_cast<MapPoint*>(NULL);
     ORBmatcher matcher(0.6f, true);
-    const int n = matcher.Fuse(&K, vp, th);
+    const int n = timed([&] { return matcher.Fuse(&K, vp, th); });
     for (int i = 0; i < kf->N; i++) {
         MapPoint* p = K.mvpMapPoints[i];
         kfSlot[i] = !p ? -1 : (p == &orig[i] ? -2 : (int32_t)(p - table.data()));
@@ -432,7 +443,7 @@ int dropin_search_by_projection_sim3(const orbm_frame* kf, const float* Scw16, c
     cv::Mat Scw(4, 4, CV_32F);
     std::memcpy(Scw.data, Scw16, 64);
     ORBmatcher matcher(0.75f, true);
-    const int n = matcher.SearchByProjection(&K, Scw, vp, vpMatched, th);
+    const int n = timed([&] { return matcher.SearchByProjection(&K, Scw, vp, vpMatched, th); });
     for (int i = 0; i < kf->N; i++) {
         MapPoint* p = vpMatched[i];
         matched[i] = !p ? -1 : (p == &foreign[i] ? -3 : (int32_t)(p - table.data()));
@@ -460,7 +471,7 @@ int dropin_fuse_sim3(const orbm_frame* kf, const float* Scw16, const orbm_mappoi
     cv::Mat Scw(4, 4, CV_32F);
     std::memcpy(Scw.data, Scw16, 64);
     ORBmatcher matcher(0.8f, true);
-    const int n = matcher.Fuse(&K, Scw, vp, th, vpReplace);
+    const int n = timed([&] { return matcher.Fuse(&K, Scw, vp, th, vpReplace); });
     for (int i = 0; i < kf->N; i++) {
         MapPoint* p = K.mvpMapPoints[i];
         kfSlot[i] = !p ? -1 : (p == &foreign[i] ? -3 : (int32_t)(p - table.data()));
@@ -500,7 +511,7 @@ int dropin_search_by_sim3(const orbm_frame* kf1, const orbm_frame* kf2, const or
     cv::Mat R(3, 3, CV_32F), t(3, 1, CV_32F);
     std::memcpy(R.data, R12, 36); std::memcpy(t.data, t12, 12);
     ORBmatcher matcher(0.75f, true);
-    const int n = matcher.SearchBySim3(&K1, &K2, vpMatches12, s12, R, t, th);
+    const int n = timed([&] { return matcher.SearchBySim3(&K1, &K2, vpMatches12, s12, R, t, th); });
     for (int i = 0; i < kf1->N; i++) prior12[i] = vpMatches12[i] ? (int32_t)(vpMatches12[i] - s2.data()) : -1;
     return n;
 }
