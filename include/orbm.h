@@ -62,6 +62,35 @@ int orbm_bf2nn(orbm_t* m, const uint8_t* queries, int nq, const uint8_t* d_db, s
 int orbm_accept_low_ratio(orbm_top2 r, float nnratio);
 /* measured integer-pipe peak: 32-bit popc per second of this GPU (microbenchmark) */
 int orbm_popc_peak(orbm_t* m, double* popc_per_s);
+/* same for LOP3, the instruction that binds the 2-NN kernel (16 per pair against 4 POPC) */
+int orbm_lop3_peak(orbm_t* m, double* lop3_per_s);
+
+/* ---- The database of M6 split across GPUs (BASELINE.json configs[3]: 4096 queries against a
+ * 10^7-row keyframe-descriptor database on 8 GPUs).  One orbm_shard per GPU, one process or thread each.  A query
+ * scans this GPU's rows (bf2nn, global row indices), all-gathers the per-shard (i1, d1, d2) records with
+ * ncclAllGather on the context stream (nq x 8 bytes per rank over NVLink) and merges them exactly: the result on
+ * every rank equals orbm_bf2nn over the concatenated database (ties -> lowest global row = the ascending strict-'<'
+ * scan of src/ORBmatcher.cc:205-226).  NCCL is loaded at run time (libnccl.so.2); world == 1 needs none.
+ * The C++ caller this serves: relocalisation / loop-candidate matching, src/Tracking.cc:1393-1554. */
+#define ORBM_NCCL_ID_BYTES 128
+typedef struct orbm_shard orbm_shard_t;
+/* ncclGetUniqueId: call on one rank, hand the 128 bytes to the others by any means (MPI, a file, a TCP store). */
+int orbm_nccl_unique_id(uint8_t* id128);
+int orbm_nccl_version(int* version);
+/* ncclCommInitRank on m's device: COLLECTIVE - every rank of the group must call it.  id128 may be NULL when world == 1. */
+int orbm_shard_create(orbm_shard_t** out, orbm_t* m, const uint8_t* id128, int rank, int world);
+/* The same on a communicator the application already has (an ncclComm_t, not destroyed by orbm_shard_destroy). */
+int orbm_shard_create_with_comm(orbm_shard_t** out, orbm_t* m, void* nccl_comm, int rank, int world);
+void orbm_shard_destroy(orbm_shard_t* s);
+/* This rank's rows = global rows [idx_base, idx_base + n): a device pointer the caller keeps alive (16-byte aligned) ... */
+int orbm_shard_set_rows(orbm_shard_t* s, const uint8_t* d_rows, size_t n, uint32_t idx_base);
+/* ... or host rows copied into HBM owned by the shard. */
+int orbm_shard_upload_rows(orbm_shard_t* s, const uint8_t* rows, size_t n, uint32_t idx_base);
+/* Queries are identical on every rank (device pointer); d_out: nq merged records.  Enqueued on the context stream;
+ * COLLECTIVE when world > 1. */
+int orbm_shard_bf2nn_device(orbm_shard_t* s, const uint8_t* d_queries, int nq, orbm_top2* d_out);
+/* Host-buffer form: H2D of the queries, the query above, D2H of the merged records, synchronised. */
+int orbm_shard_bf2nn(orbm_shard_t* s, const uint8_t* queries, int nq, orbm_top2* out);
 
 /* ---- Frame grid (src/Frame.cc:292-311 AssignFeaturesToGrid, :504-518 PosInGrid,
  * :410-495 GetFeaturesInArea) and the windowed matchers built on it. */

@@ -619,4 +619,22 @@ void orbref_algebra_probe(const float* A9, const float* x3, const float* c3, flo
     out[12] = (float)cv::norm(x);
 }
 
+// Exhaustive best / second-best scan written the way the reference's matchers scan one vocabulary node
+// (src/ORBmatcher.cc:205-226): a row header per candidate and the reference's own ORBmatcher::DescriptorDistance
+// (:1728-1744).  Used as the timed CPU baseline of the Hamming 2-NN leg and to pin orbo_bf2nn.
+void orbref_bf2nn(const uint8_t* q, int nq, const uint8_t* db, size_t ndb, uint32_t idx_base, orbm_top2* out) {
+    const cv::Mat Q(nq, 32, CV_8U, (void*)q), D((int)ndb, 32, CV_8U, (void*)db);
+    for (int i = 0; i < nq; i++) {
+        const cv::Mat& dQ = Q.row(i);
+        int bestDist1 = 256, bestDist2 = 256; uint32_t bestIdx = 0xffffffffu;
+        for (size_t r = 0; r < ndb; r++) {
+            const cv::Mat& dD = D.row((int)r);
+            const int dist = ORBmatcher::DescriptorDistance(dQ, dD);
+            if (dist < bestDist1) { bestDist2 = bestDist1; bestDist1 = dist; bestIdx = idx_base + (uint32_t)r; }
+            else if (dist < bestDist2) bestDist2 = dist;
+        }
+        out[i].i1 = bestIdx; out[i].d1 = (uint16_t)bestDist1; out[i].d2 = (uint16_t)bestDist2;
+    }
+}
+
 }  // extern "C"

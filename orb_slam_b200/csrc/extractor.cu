@@ -977,7 +977,8 @@ int orbx_stereo_match(orbx_t* left, orbx_t* right, int frame, const orbx_keypoin
     const size_t oZ = oU + (size_t)nL * 4 + 256, oS = oZ + (size_t)nL * 4 + 256, oN = oS + (size_t)nL * 4 + 256;
     orbx_extractor* e = left;
     const int nRows = e->g.height;
-    const bool rows = nRows <= STEREO_MAX_ROWS && nR > 0;                    // vRowIndices as a CSR over image rows
+    // vRowIndices as a CSR over image rows (only while a key point's row band fits the list's per-point capacity)
+    const bool rows = nRows <= STEREO_MAX_ROWS && nR > 0 && stereo_band_rows(e->sf[e->nlevels - 1]) <= STEREO_BAND_MAX;
     const size_t oRS = oN + 256, oRI = oRS + (rows ? (((size_t)(nRows + 1) * 4 + 255) & ~(size_t)255) : 0);
     const size_t need = oRI + (rows ? (size_t)nR * STEREO_BAND_MAX * 2 : 0) + 256;
     if (e->stereoBytes < need) {
@@ -1052,7 +1053,7 @@ int orbx_stereo_match_batch_device(orbx_t* left, orbx_t* right, int n, const orb
     CK(cudaStreamSynchronize(left->ws[1].stream));
     orbx_extractor* e = left;
     const int nRows = e->g.height;
-    const bool rows = nRows <= STEREO_MAX_ROWS;                              // else: every right key point is scanned
+    const bool rows = nRows <= STEREO_MAX_ROWS && stereo_band_rows(e->sf[e->nlevels - 1]) <= STEREO_BAND_MAX;   // else: every right key point is scanned
     const size_t oRowStart = ((size_t)n * cap * 4 + 255) & ~(size_t)255;
     const size_t oRowItems = oRowStart + (rows ? (((size_t)n * (nRows + 1) * 4 + 255) & ~(size_t)255) : 0);
     const int rowItemsCap = cap * STEREO_BAND_MAX;

@@ -5,9 +5,9 @@
 // Layout: every thread keeps 4 query descriptors (32 registers) and their
 // top-2 state; the database streams through shared memory in 128-row tiles
 // (cp.async, double buffered) and every warp reads a row as two broadcast
-// 128-bit loads.  The inner loop is 8 LOP3.XOR + 6 LOP3 (carry-save adders) + 5 POPC
-// + adds per pair: the bound is the integer POPC / ALU pipes, not HBM (a shard is read
-// once per query tile).
+// 128-bit loads.  The inner loop is 8 LOP3.XOR + 8 LOP3 (four carry-save adders) + 4 POPC
+// + 3 adds + 1 compare per pair: the bound is the ALU pipe (LOP3 issues at half rate) with
+// the POPC pipe close behind, not HBM (a shard is read once per query tile).
 // top-2 is kept as packed keys (distance << 23 | local row) so the update is
 // min/max only, and equal distances resolve to the lowest row = the
 // reference's strict '<' scan in ascending index.
@@ -30,6 +30,11 @@ __device__ __forceinline__ void cp_async16(void* smem, const void* gmem) {
 }
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;"); }
 template <int N> __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N)); }
+
+// 3-input logic with the truth table spelled out (one LOP3 each; immLut = f(0xF0, 0xCC, 0xAA))
+__device__ __forceinline__ uint32_t lop_xor(uint32_t a, uint32_t b) { uint32_t r; asm("lop3.b32 %0, %1, %2, 0, 0x3c;" : "=r"(r) : "r"(a), "r"(b)); return r; }
+__device__ __forceinline__ uint32_t lop_xor3(uint32_t a, uint32_t b, uint32_t c) { uint32_t r; asm("lop3.b32 %0, %1, %2, %3, 0x96;" : "=r"(r) : "r"(a), "r"(b), "r"(c)); return r; }
+__device__ __forceinline__ uint32_t lop_maj(uint32_t a, uint32_t b, uint32_t c) { uint32_t r; asm("lop3.b32 %0, %1, %2, %3, 0xe8;" : "=r"(r) : "r"(a), "r"(b), "r"(c)); return r; }
 
 struct Top2Key { unsigned long long k1, k2; };   // (distance << 32 | global row), ascending
 
@@ -90,13 +95,17 @@ __global__ void __launch_bounds__(BF_THREADS) bf2nn_kernel(const uint32_t* __res
                 // 256-bit Hamming distance with 4 POPC instead of 8: carry-save adders (LOP3 xor3 / majority) compress
                 // the eight XOR words to two weight-1, one weight-2 and one weight-4 word first.  POPC costs four ALU
                 // issue slots, a LOP3 one.
-                const uint32_t x0 = qr[j][0] ^ w0.x, x1 = qr[j][1] ^ w0.y, x2 = qr[j][2] ^ w0.z, x3 = qr[j][3] ^ w0.w;
-                const uint32_t x4 = qr[j][4] ^ w1.x, x5 = qr[j][5] ^ w1.y, x6 = qr[j][6] ^ w1.z, x7 = qr[j][7] ^ w1.w;
-                const uint32_t s1 = x0 ^ x1 ^ x2, c1 = (x0 & x1) | (x2 & (x0 | x1));
-                const uint32_t s2 = x3 ^ x4 ^ x5, c2 = (x3 & x4) | (x5 & (x3 | x4));
-                const uint32_t s3 = x6 ^ x7 ^ s1, c3 = (x6 & x7) | (s1 & (x6 | x7));
-                const uint32_t t2 = c1 ^ c2 ^ c3, f4 = (c1 & c2) | (c3 & (c1 | c2));
-                d[j] = __popc(s2) + __popc(s3) + 2u * __popc(t2) + 4u * __popc(f4);
+                // The adders are written as lop3.b32 with fixed truth tables (0x96 = a^b^c, 0xe8 = majority): left to
+                // the compiler, the query XORs get folded into the adders as other 3-input functions and the pair ends
+                // up with ~23 LOP3 instead of 8 XOR + 8 adder halves = 16 (profiles/r2_bf2nn_sass.md).
+                const uint32_t x0 = lop_xor(qr[j][0], w0.x), x1 = lop_xor(qr[j][1], w0.y), x2 = lop_xor(qr[j][2], w0.z);
+                const uint32_t x3 = lop_xor(qr[j][3], w0.w), x4 = lop_xor(qr[j][4], w1.x), x5 = lop_xor(qr[j][5], w1.y);
+                const uint32_t x6 = lop_xor(qr[j][6], w1.z), x7 = lop_xor(qr[j][7], w1.w);
+                const uint32_t s1 = lop_xor3(x0, x1, x2), c1 = lop_maj(x0, x1, x2);
+                const uint32_t s2 = lop_xor3(x3, x4, x5), c2 = lop_maj(x3, x4, x5);
+                const uint32_t s3 = lop_xor3(x6, x7, s1), c3 = lop_maj(x6, x7, s1);
+                const uint32_t t2 = lop_xor3(c1, c2, c3), f4 = lop_maj(c1, c2, c3);
+                d[j] = (__popc(s2) + __popc(s3)) + ((__popc(t2) + (__popc(f4) << 1)) << 1);
                 any |= d[j] < thr[j];
             }
             // rows arrive in ascending index, so a row enters the top-2 only with a strictly smaller distance than the
@@ -175,6 +184,24 @@ __global__ void popc_peak_kernel(unsigned* out, int iters, unsigned seed) {
     unsigned s = 0;
 #pragma unroll
     for (int k = 0; k < 8; k++) s += acc[k];
+    if (s == 0xdeadbeefu) out[0] = s;
+}
+
+// ALU-pipe microbenchmark: 8 independent lop3 chains per thread (the instruction that binds bf2nn_kernel: 16 per pair)
+__global__ void lop3_peak_kernel(unsigned* out, int iters, unsigned seed) {
+    unsigned a[8], b[8];
+#pragma unroll
+    for (int k = 0; k < 8; k++) { a[k] = seed * (threadIdx.x + 1) + k * 0x9e3779b9u; b[k] = a[k] * 0x85ebca6bu + 1u; }
+    for (int i = 0; i < iters; i++) {
+#pragma unroll
+        for (int k = 0; k < 8; k++) {
+            a[k] = lop_maj(a[k], b[k], a[(k + 1) & 7]);
+            b[k] = lop_xor3(b[k], a[k], b[(k + 3) & 7]);
+        }
+    }
+    unsigned s = 0;
+#pragma unroll
+    for (int k = 0; k < 8; k++) s += a[k] ^ b[k];
     if (s == 0xdeadbeefu) out[0] = s;
 }
 

@@ -120,12 +120,9 @@ void orbm_three_maxima(const int32_t* counts, int L, int* ind1, int* ind2, int* 
     else if (max3 < 0.1f * (float)max1) { *ind3 = -1; }
 }
 
-int orbm_bf2nn_device(orbm_t* m, const uint8_t* d_queries, int nq, const uint8_t* d_db, size_t ndb, uint32_t idx_base,
-                      orbm_top2* d_out) {
-    if (!m || !d_queries || nq <= 0 || !d_out || (ndb && !d_db)) return ORBX_E_INVALID;
-    if (((uintptr_t)d_queries & 15) || ((uintptr_t)d_db & 15)) return ORBX_E_INVALID;
-    std::lock_guard<std::mutex> lk(m->mtx);
-    CKM(cudaSetDevice(m->device));
+// caller holds m->mtx
+static int bf2nn_device_locked(orbm_t* m, const uint8_t* d_queries, int nq, const uint8_t* d_db, size_t ndb, uint32_t idx_base,
+                               orbm_top2* d_out) {
     const int qtiles = (nq + BF_QTILE - 1) / BF_QTILE;
     // enough slices for ~4 resident blocks per SM, at least one 128-row tile each, at most 2^23 rows each
     int slices = std::max(1, (m->numSMs * 4 + qtiles - 1) / qtiles);
@@ -145,6 +142,15 @@ int orbm_bf2nn_device(orbm_t* m, const uint8_t* d_queries, int nq, const uint8_t
     return ORBX_OK;
 }
 
+int orbm_bf2nn_device(orbm_t* m, const uint8_t* d_queries, int nq, const uint8_t* d_db, size_t ndb, uint32_t idx_base,
+                      orbm_top2* d_out) {
+    if (!m || !d_queries || nq <= 0 || !d_out || (ndb && !d_db)) return ORBX_E_INVALID;
+    if (((uintptr_t)d_queries & 15) || ((uintptr_t)d_db & 15)) return ORBX_E_INVALID;
+    std::lock_guard<std::mutex> lk(m->mtx);
+    CKM(cudaSetDevice(m->device));
+    return bf2nn_device_locked(m, d_queries, nq, d_db, ndb, idx_base, d_out);
+}
+
 int orbm_merge_top2_device(orbm_t* m, const orbm_top2* d_parts, int nparts, int nq, orbm_top2* d_out) {
     if (!m || !d_parts || nparts <= 0 || nq <= 0 || !d_out) return ORBX_E_INVALID;
     std::lock_guard<std::mutex> lk(m->mtx);
@@ -154,16 +160,16 @@ int orbm_merge_top2_device(orbm_t* m, const orbm_top2* d_parts, int nparts, int 
     return ORBX_OK;
 }
 
+// One lock over staging, kernels and readback: m->q / m->out / m->part are shared by every call on this context.
 int orbm_bf2nn(orbm_t* m, const uint8_t* queries, int nq, const uint8_t* d_db, size_t ndb, uint32_t idx_base, orbm_top2* out) {
-    if (!m || !queries || nq <= 0 || !out) return ORBX_E_INVALID;
-    {
-        std::lock_guard<std::mutex> lk(m->mtx);
-        CKM(cudaSetDevice(m->device));
-        int rc = m->q.reserve((size_t)nq * 32); if (rc) return rc;
-        rc = m->out.reserve((size_t)nq * sizeof(orbm_top2)); if (rc) return rc;
-        CKM(cudaMemcpyAsync(m->q.p, queries, (size_t)nq * 32, cudaMemcpyHostToDevice, m->stream));
-    }
-    int rc = orbm_bf2nn_device(m, (const uint8_t*)m->q.p, nq, d_db, ndb, idx_base, (orbm_top2*)m->out.p);
+    if (!m || !queries || nq <= 0 || !out || (ndb && !d_db)) return ORBX_E_INVALID;
+    if ((uintptr_t)d_db & 15) return ORBX_E_INVALID;
+    std::lock_guard<std::mutex> lk(m->mtx);
+    CKM(cudaSetDevice(m->device));
+    int rc = m->q.reserve((size_t)nq * 32); if (rc) return rc;
+    rc = m->out.reserve((size_t)nq * sizeof(orbm_top2)); if (rc) return rc;
+    CKM(cudaMemcpyAsync(m->q.p, queries, (size_t)nq * 32, cudaMemcpyHostToDevice, m->stream));
+    rc = bf2nn_device_locked(m, (const uint8_t*)m->q.p, nq, d_db, ndb, idx_base, (orbm_top2*)m->out.p);
     if (rc) return rc;
     CKM(cudaMemcpyAsync(out, m->out.p, (size_t)nq * sizeof(orbm_top2), cudaMemcpyDeviceToHost, m->stream));
     CKM(cudaStreamSynchronize(m->stream));
@@ -174,31 +180,40 @@ int orbm_accept_low_ratio(orbm_top2 r, float nnratio) {
     return r.d1 <= ORBM_TH_LOW && (float)r.d1 < nnratio * (float)r.d2;
 }
 
-int orbm_popc_peak(orbm_t* m, double* popc_per_s) {
-    if (!m || !popc_per_s) return ORBX_E_INVALID;
+// thread-instructions per second of one integer instruction, measured on this GPU: which = 0 POPC, 1 LOP3
+static int pipe_peak(orbm_t* m, int which, double* per_s) {
+    if (!m || !per_s) return ORBX_E_INVALID;
     std::lock_guard<std::mutex> lk(m->mtx);
     CKM(cudaSetDevice(m->device));
     int rc = m->out.reserve(64); if (rc) return rc;
     cudaEvent_t e0, e1;
     CKM(cudaEventCreate(&e0)); CKM(cudaEventCreate(&e1));
     const int iters = 4096, blocks = m->numSMs * 8, threads = 256;
-    popc_peak_kernel<<<blocks, threads, 0, m->stream>>>((unsigned*)m->out.p, 64, 1u);
+    auto launch = [&](int it, unsigned seed) {
+        if (which == 0) popc_peak_kernel<<<blocks, threads, 0, m->stream>>>((unsigned*)m->out.p, it, seed);
+        else lop3_peak_kernel<<<blocks, threads, 0, m->stream>>>((unsigned*)m->out.p, it, seed);
+    };
+    launch(64, 1u);
     float best = 1e30f;
     for (int rep = 0; rep < 3; rep++) {
         CKM(cudaEventRecord(e0, m->stream));
-        popc_peak_kernel<<<blocks, threads, 0, m->stream>>>((unsigned*)m->out.p, iters, 7u + rep);
+        launch(iters, 7u + rep);
         CKM(cudaEventRecord(e1, m->stream));
         CKM(cudaEventSynchronize(e1));
         float ms; CKM(cudaEventElapsedTime(&ms, e0, e1));
         best = std::min(best, ms);
     }
     cudaEventDestroy(e0); cudaEventDestroy(e1);
-    *popc_per_s = (double)blocks * threads * iters * 8 / (best * 1e-3);
+    *per_s = (double)blocks * threads * iters * (which == 0 ? 8 : 16) / (best * 1e-3);
     return ORBX_OK;
 }
+
+int orbm_popc_peak(orbm_t* m, double* popc_per_s) { return pipe_peak(m, 0, popc_per_s); }
+int orbm_lop3_peak(orbm_t* m, double* lop3_per_s) { return pipe_peak(m, 1, lop3_per_s); }
 
 }  // extern "C"
 
 #include "window_host.inl"
 #include "bow_host.inl"
 #include "vocab_host.inl"
+#include "shard_host.inl"

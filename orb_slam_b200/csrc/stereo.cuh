@@ -32,7 +32,10 @@ struct StereoArgs {
 };
 
 constexpr int STEREO_MAX_ROWS = 4096;
-constexpr int STEREO_BAND_MAX = 20;                 // rows one right key point can enter: 2 * ceil(2 * scaleFactor[level]) + 2
+constexpr int STEREO_BAND_MAX = 20;                 // rows one right key point can enter with the default settings (8 levels, 1.2): at most 17
+// rows one right key point can enter: ceil(y + r) - floor(y - r) + 1 <= 2 * ceil(r) + 3 with r = 2 * scaleFactor[top level];
+// configurations above STEREO_BAND_MAX (e.g. scaleFactor 1.5, or 12 levels) scan every right key point instead
+__host__ inline int stereo_band_rows(float sfTop) { return 2 * (int)ceilf(2.0f * sfTop) + 3; }
 
 // vRowIndices: right key point iR is a candidate on the image rows floor(y - r) .. ceil(y + r), r = 2 * mvScaleFactors[octave]
 // (:658-673).  One block per frame; the order inside a row is free because the match below reduces over (distance, iR).
@@ -71,7 +74,10 @@ __global__ void __launch_bounds__(1024) stereo_rows_kernel(const orbx_keypoint* 
         const orbx_keypoint kp = keysR[iR];
         const float r = __fmul_rn(2.0f, a.sf[kp.octave]);
         const int maxr = min((int)ceilf(__fadd_rn(kp.y, r)), nRows - 1), minr = max((int)floorf(__fsub_rn(kp.y, r)), 0);
-        for (int y = minr; y <= maxr; y++) rowItems[atomicAdd(&cnt[y], 1)] = (unsigned short)iR;
+        for (int y = minr; y <= maxr; y++) {
+            const int pos = atomicAdd(&cnt[y], 1);
+            if (pos < a.rowItemsCap) rowItems[pos] = (unsigned short)iR;       // (the host sizes the list from the real band bound)
+        }
     }
 }
 

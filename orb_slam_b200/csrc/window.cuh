@@ -33,6 +33,7 @@ __global__ void __launch_bounds__(1024) grid_build_kernel(const orbx_keypoint* _
                                                           int32_t* __restrict__ cellOf, int32_t* __restrict__ cellStart,
                                                           int32_t* __restrict__ items) {
     __shared__ int cnt[GRID_CELLS + 1];
+    __shared__ int fill[GRID_CELLS];
     __shared__ int warpSum[32];
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
     for (int c = tid; c <= GRID_CELLS; c += blockDim.x) cnt[c] = 0;
@@ -62,13 +63,24 @@ __global__ void __launch_bounds__(1024) grid_build_kernel(const orbx_keypoint* _
     for (int c = b; c < e; c++) { const int v = cnt[c]; cnt[c] = run; cellStart[c] = run; run += v; }
     if (tid == blockDim.x - 1) { cnt[GRID_CELLS] = run; cellStart[GRID_CELLS] = run; }
     __syncthreads();
-    // stable placement: rank of i among earlier keypoints of the same cell
+    // placement: scatter with a per-cell counter, then order each cell's few entries ascending = push_back order (:300-310)
+    for (int c = tid; c < GRID_CELLS; c += blockDim.x) fill[c] = 0;
+    __syncthreads();
     for (int i = tid; i < N; i += blockDim.x) {
         const int c = cellOf[i];
-        if (c < 0) continue;
-        int rank = 0;
-        for (int j = 0; j < i; j++) rank += (cellOf[j] == c);
-        items[cnt[c] + rank] = i;
+        if (c >= 0) items[cnt[c] + atomicAdd(&fill[c], 1)] = i;
+    }
+    __syncthreads();
+    for (int c = tid; c < GRID_CELLS; c += blockDim.x) {
+        const int n = fill[c];
+        if (n < 2) continue;
+        int32_t* it = items + cnt[c];
+        for (int x = 1; x < n; x++) {                    // insertion sort of a handful of indices
+            const int v = it[x];
+            int y = x - 1;
+            while (y >= 0 && it[y] > v) { it[y + 1] = it[y]; y--; }
+            it[y + 1] = v;
+        }
     }
 }
 

@@ -147,6 +147,16 @@ def _bind(L):
     L.orbm_merge_top2_device.argtypes = [vp, vp, i, i, vp]; L.orbm_merge_top2_device.restype = i
     L.orbm_bf2nn.argtypes = [vp, vp, i, vp, sz, C.c_uint32, vp]; L.orbm_bf2nn.restype = i
     L.orbm_popc_peak.argtypes = [vp, C.POINTER(C.c_double)]; L.orbm_popc_peak.restype = i
+    L.orbm_lop3_peak.argtypes = [vp, C.POINTER(C.c_double)]; L.orbm_lop3_peak.restype = i
+    L.orbm_nccl_unique_id.argtypes = [vp]; L.orbm_nccl_unique_id.restype = i
+    L.orbm_nccl_version.argtypes = [C.POINTER(i)]; L.orbm_nccl_version.restype = i
+    L.orbm_shard_create.argtypes = [C.POINTER(vp), vp, vp, i, i]; L.orbm_shard_create.restype = i
+    L.orbm_shard_create_with_comm.argtypes = [C.POINTER(vp), vp, vp, i, i]; L.orbm_shard_create_with_comm.restype = i
+    L.orbm_shard_destroy.argtypes = [vp]; L.orbm_shard_destroy.restype = None
+    L.orbm_shard_set_rows.argtypes = [vp, vp, sz, C.c_uint32]; L.orbm_shard_set_rows.restype = i
+    L.orbm_shard_upload_rows.argtypes = [vp, vp, sz, C.c_uint32]; L.orbm_shard_upload_rows.restype = i
+    L.orbm_shard_bf2nn_device.argtypes = [vp, vp, i, vp]; L.orbm_shard_bf2nn_device.restype = i
+    L.orbm_shard_bf2nn.argtypes = [vp, vp, i, vp]; L.orbm_shard_bf2nn.restype = i
     L.orbm_grid_build.argtypes = [vp, vp, vp, vp]; L.orbm_grid_build.restype = i
     L.orbm_features_in_area.argtypes = [vp, vp, f, f, f, i, i, vp, i, C.POINTER(i)]; L.orbm_features_in_area.restype = i
     L.orbm_search_for_initialization.argtypes = [vp, vp, vp, vp, vp, i, f, i, C.POINTER(i)]
@@ -216,6 +226,11 @@ class MatcherContext:
     def popc_peak(self) -> float:
         v = C.c_double()
         check(self._L.orbm_popc_peak(self.h, C.byref(v)), "orbm_popc_peak")
+        return v.value
+
+    def lop3_peak(self) -> float:
+        v = C.c_double()
+        check(self._L.orbm_lop3_peak(self.h, C.byref(v)), "orbm_lop3_peak")
         return v.value
 
     def grid_build(self, F: Frame):

@@ -45,18 +45,98 @@ def have_ref() -> bool:
     return os.path.exists(REF_SO)
 
 
+def _bind_ref(path) -> C.CDLL:
+    L = C.CDLL(path)
+    vp, i, f = C.c_void_p, C.c_int, C.c_float
+    L.orbref_create.restype = vp; L.orbref_create.argtypes = [i, f, i, i, i]
+    L.orbref_destroy.argtypes = [vp]
+    L.orbref_extract.argtypes = [vp, vp, i, i, i, i, vp, vp, i]
+    L.orbref_level_size.argtypes = [vp, i, vp, vp]
+    L.orbref_get_level.argtypes = [vp, i, i, vp, i]
+    return L
+
+
 def ref() -> C.CDLL:
     global _ref
     if _ref is None:
-        L = C.CDLL(REF_SO)
-        vp, i, f = C.c_void_p, C.c_int, C.c_float
-        L.orbref_create.restype = vp; L.orbref_create.argtypes = [i, f, i, i, i]
-        L.orbref_destroy.argtypes = [vp]
-        L.orbref_extract.argtypes = [vp, vp, i, i, i, i, vp, vp, i]
-        L.orbref_level_size.argtypes = [vp, i, vp, vp]
-        L.orbref_get_level.argtypes = [vp, i, i, vp, i]
-        _ref = L
+        _ref = _bind_ref(REF_SO)
     return _ref
+
+
+# ---- the reference built a second time for TIMING with its own flags (-O3 -march=..., oracle/Makefile ref_timed) ----
+_X86_V3 = {"avx", "avx2", "bmi1", "bmi2", "f16c", "fma", "abm", "movbe", "xsave"}
+_X86_V4 = _X86_V3 | {"avx512f", "avx512bw", "avx512cd", "avx512dq", "avx512vl"}
+_ISA_PREFIXES = ("avx", "amx", "bmi", "fma", "f16c", "gfni", "vaes", "vpclmul", "sha", "sse", "ssse", "popcnt", "movbe", "abm",
+                 "adx", "aes", "pclmul", "rdrand", "rdseed", "clwb", "clflushopt", "movdir", "cldemote", "serialize", "xsave",
+                 "rdpid", "fsgsbase", "pku", "waitpkg", "enqcmd", "uintr", "hreset", "ptwrite", "wbnoinvd", "lahf", "cx16")
+
+
+def _cpu_flags():
+    try:
+        for ln in open("/proc/cpuinfo"):
+            if ln.startswith("flags"):
+                return set(ln.split(":", 1)[1].split())
+    except OSError:
+        pass
+    return set()
+
+
+def timed_variant():
+    """(directory, description) of the fastest reference build this host CPU can execute: this container's
+    -march=native build when the host has every ISA flag the build machine had, else x86-64-v4 / -v3, else the
+    portable parity build (-O3, no -march).  Chosen by cpuid flags only; nothing is executed to probe."""
+    base = os.path.join(ROOT, "oracle", "_ref")
+    have = _cpu_flags()
+    cands = []
+    nat = os.path.join(base, "timed_native")
+    try:
+        built = set(open(os.path.join(nat, "build_cpu_flags.txt")).read().split(":", 1)[1].split())
+        need = {f for f in built if f.startswith(_ISA_PREFIXES)}
+        cands.append((nat, need))
+    except (OSError, IndexError):
+        pass
+    cands.append((os.path.join(base, "timed_v4"), _X86_V4))
+    cands.append((os.path.join(base, "timed_v3"), _X86_V3))
+    for d, need in cands:
+        if os.path.exists(os.path.join(d, "liborb_ref.so")) and need <= have:
+            flags = "-O3 -march=?"
+            try:
+                flags = open(os.path.join(d, "cxxflags.txt")).read().strip()
+                if d == nat:
+                    flags += " (" + open(os.path.join(d, "march.txt")).read().split()[-1] + ")"
+            except (OSError, IndexError):
+                pass
+            return d, flags
+    return base, "-O3 -ffp-contract=off (portable parity build, no -march)"
+
+
+_timed = {}
+
+
+def ref_timed() -> tuple:
+    """(bound liborb_ref.so of the timed build, flags string)"""
+    d, flags = timed_variant()
+    if d not in _timed:
+        _timed[d] = _bind_ref(os.path.join(d, "liborb_ref.so"))
+    return _timed[d], flags
+
+
+def ref_timed_bf2nn():
+    """(callable(q, db) -> orbm_top2 array running orbref_bf2nn of the timed matcher build, flags) or (None, why)"""
+    d, flags = timed_variant()
+    so = os.path.join(d, "liborbmatcher_ref.so")
+    if not os.path.exists(so):
+        return None, "no reference matcher build"
+    L = C.CDLL(so)
+    L.orbref_bf2nn.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_size_t, C.c_uint32, C.c_void_p]
+    from orb_slam_b200.matcher import TOP2_DTYPE
+
+    def run(q, db):
+        q = np.ascontiguousarray(q, np.uint8); db = np.ascontiguousarray(db, np.uint8)
+        out = np.zeros(len(q), TOP2_DTYPE)
+        L.orbref_bf2nn(q.ctypes.data, len(q), db.ctypes.data, len(db), 0, out.ctypes.data)
+        return out
+    return run, flags
 
 
 class OracleExtractor:
@@ -112,8 +192,8 @@ class OracleExtractor:
 class RefExtractor:
     """The reference's own ORBextractor (oracle/_ref), canonical tie-break by default."""
 
-    def __init__(self, nfeatures, scaleFactor, nlevels, iniTh, minTh):
-        self.L = ref()
+    def __init__(self, nfeatures, scaleFactor, nlevels, iniTh, minTh, lib=None):
+        self.L = lib if lib is not None else ref()          # lib: a timed build (ref_timed()), bench.py only
         self.h = self.L.orbref_create(nfeatures, scaleFactor, nlevels, iniTh, minTh)
         self.nfeatures = nfeatures; self.nlevels = nlevels
 

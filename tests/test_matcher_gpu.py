@@ -238,3 +238,18 @@ def test_sharded_database_nccl_two_ranks():
            "--master-port", str(port), os.path.join(root, "tests", "dist_worker.py"), "nccl", "300001", "512"]
     r = subprocess.run(cmd, capture_output=True, text=True, timeout=600, cwd=root)
     assert r.returncode == 0 and "DIST_OK" in r.stdout, r.stdout[-2000:] + r.stderr[-2000:]
+
+
+def test_sharded_window_matching_nccl_two_ranks():
+    """SearchForInitialization over a frame sequence split across 2 GPUs (pair_slice: the boundary pair stays with the
+    lower rank), product extraction + batch matcher on each rank, per-pair results against the oracle"""
+    import os, socket, subprocess, sys
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs >= 2 GPUs")
+    s = socket.socket(); s.bind(("127.0.0.1", 0)); port = s.getsockname()[1]; s.close()
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr", "127.0.0.1",
+           "--master-port", str(port), os.path.join(root, "tests", "dist_worker.py"), "nccl", "pairs", "9"]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=600, cwd=root)
+    assert r.returncode == 0 and "DIST_OK" in r.stdout, r.stdout[-2000:] + r.stderr[-2000:]

@@ -33,3 +33,26 @@ def test_gloo_allgather_merge_equals_global_scan(world, ndb):
     env = dict(os.environ, OMP_NUM_THREADS="1")
     r = subprocess.run(cmd, capture_output=True, text=True, timeout=300, env=env, cwd=ROOT)
     assert r.returncode == 0 and "DIST_OK" in r.stdout, r.stdout[-2000:] + r.stderr[-2000:]
+
+
+def test_pair_slice_covers_every_consecutive_pair_once():
+    from orb_slam_b200.sharded import pair_slice
+    for n, world in ((1024, 1), (1024, 2), (1024, 8), (1023, 4), (10, 3), (3, 8), (1, 2), (0, 2)):
+        pairs = []
+        for r in range(world):
+            lo, hi, npairs = pair_slice(n, world, r)
+            slo, shi = shard_range(n, world, r)
+            assert lo == slo and hi in (shi, shi + 1)                  # at most one frame of overlap, taken from the next slice
+            assert npairs == 0 or lo + npairs < hi
+            pairs += [lo + p for p in range(npairs)]                   # pair (i, i + 1) is named by its first frame
+            assert all(slo <= i < shi for i in pairs[len(pairs) - npairs:])      # ... which lies in this rank's own slice
+        assert sorted(pairs) == list(range(max(n - 1, 0))) and len(set(pairs)) == len(pairs)
+
+
+def test_gloo_boundary_pair_belongs_to_the_lower_rank():
+    """SearchForInitialization over a 7-frame sequence on 2 ranks: results per pair equal the single-process run"""
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr", "127.0.0.1",
+           "--master-port", str(free_port()), os.path.join(ROOT, "tests", "dist_worker.py"), "gloo", "pairs", "7"]
+    env = dict(os.environ, OMP_NUM_THREADS="1")
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=300, env=env, cwd=ROOT)
+    assert r.returncode == 0 and "DIST_OK" in r.stdout, r.stdout[-2000:] + r.stderr[-2000:]
