@@ -658,7 +658,11 @@ int orbx_extract_batch(orbx_t* e, const uint8_t* const* images, int n, int width
     const bool outPinnedMem = is_pinned(keypoints) && is_pinned(descriptors) &&
                               is_pinned(keypoints + (size_t)n * capacity - 1) && is_pinned(descriptors + (size_t)n * capacity * 32 - 1);
     if (inPinned && step > 2 * (size_t)width) inPinned = false;          // very sparse rows: pack through staging instead
-    static const int chunkFrames = [] { const char* v = std::getenv("ORBX_CHUNK_FRAMES"); const int c = v ? std::atoi(v) : 0; return c > 0 ? c : ORBX_CHUNK; }();
+    // ORBX_CHUNK frames of KITTI size are ~30 MB of pixels: larger frames travel in proportionally fewer frames per chunk, so
+    // that copy-in, compute and copy-out of neighbouring chunks still overlap (a 64-frame 1080p batch is otherwise one chunk)
+    static const int chunkEnv = [] { const char* v = std::getenv("ORBX_CHUNK_FRAMES"); const int c = v ? std::atoi(v) : 0; return c > 0 ? c : 0; }();
+    const size_t frameBytes = (size_t)width * height;
+    const int chunkFrames = chunkEnv ? chunkEnv : (int)std::min<size_t>(ORBX_CHUNK, std::max<size_t>(2, ((size_t)ORBX_CHUNK * 1241 * 376 + frameBytes / 2) / frameBytes));
     // pageable buffers: the host thread's staging copies set the pace, and they run faster through smaller (cache-resident) chunks
     const int chunk = std::min(n, inPinned && outPinnedMem ? chunkFrames : std::max(1, chunkFrames / 2));
     int rc = ensure_workspace(e, width, height, chunk, true);

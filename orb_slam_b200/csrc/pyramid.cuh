@@ -166,6 +166,192 @@ struct PyrArgs {
     uint32_t tileY[PYR_MAX_TILES_Y];   // per tile row: first | last source row
 };
 
+// ---- the phases of a tile once the level tile T (TROWS x TS bytes, halo included) is complete in shared memory ----
+
+// level plane: 16 pixels per thread
+template <int TH>
+__device__ __forceinline__ void tile_store_plane(const PyrArgs& a, const uint8_t* __restrict__ T, int frame, int x0, int y0, int tid) {
+    const int vx = (tid & 7) * 16, vy = tid >> 3;
+    if (vy < TH && (y0 + vy < a.h) && (x0 + vx < a.w)) {
+        const uint32_t* t = (const uint32_t*)(T + (vy + HALO) * TS + TCOL0 + vx);
+        const uint4 v = make_uint4(t[0], t[1], t[2], t[3]);
+        *(uint4*)(a.pyr + (size_t)frame * a.pyrFrameStride + (size_t)(ORB_EDGE + y0 + vy) * a.pitch + ORB_XPAD + x0 + vx) = v;
+    }
+}
+
+// row pass: one warp per T row, one 4-pixel group per lane: split the row into its stride-2 pixel pairs
+// (kept in the pair planes for FAST) and form the horizontal blur sums
+template <int TH>
+__device__ __forceinline__ void tile_row_pass(const uint8_t* __restrict__ T, unsigned short* __restrict__ Hs, uint4* __restrict__ PA,
+                                              uint4* __restrict__ PB, int h, int y0, int wid, int lane) {
+    constexpr int TROWS = TH + 2 * HALO;
+    const int rEnd = min(TROWS, h + 2 * HALO - y0);       // rows below the image + halo feed nothing that is stored
+    for (int r = wid; r < rEnd; r += PYR_THREADS / 32) {
+        const RowPairs p = row_pairs((const uint32_t*)(T + r * TS) + lane);
+        PA[r * 32 + lane] = make_uint4(p.x1, p.em, p.om, p.x2);
+        PB[r * 32 + lane] = make_uint4(p.ol, p.x4, p.x3, p.er);
+        uint32_t A, B;
+        hblur4(p, A, B);
+        *(uint2*)(Hs + r * TW + 4 * lane) = make_uint2(A, B);
+    }
+}
+
+// FAST score: warp `wid` owns tile rows RPW*wid..RPW*wid+RPW-1, lane = 4-pixel group
+template <int TH>
+__device__ __forceinline__ void tile_fast_pass(const PyrArgs& a, const uint4* __restrict__ PA, const uint4* __restrict__ PB, int frame,
+                                               int x0, int y0, int wid, int lane) {
+    constexpr int RPW = TH / (PYR_THREADS / 32);
+    const int w = a.w, h = a.h;
+    const int gx = x0 + 4 * lane;                        // level column of the group's first pixel
+#pragma unroll 1
+    for (int k = 0; k < RPW; k++) {
+        const int r = RPW * wid + k, y = y0 + r;
+        if (y >= h || gx >= w) continue;
+        uint32_t s = 0;
+        if (y >= ORB_EDGE && y < h - ORB_EDGE && gx + 3 >= ORB_EDGE && gx < w - ORB_EDGE) {
+            s = fast_score4(PA, PB, r, lane, a.minTh);
+            if (gx < ORB_EDGE || gx + 3 >= w - ORB_EDGE) {           // group straddles the detection area
+                uint32_t m = 0;
+#pragma unroll
+                for (int j = 0; j < 4; j++)
+                    if (gx + j >= ORB_EDGE && gx + j < w - ORB_EDGE) m |= 0xffu << (8 * j);
+                s &= m;
+            }
+        }
+        *(uint32_t*)(a.score + (size_t)frame * a.planeFrameStride + (size_t)y * a.pitch + ORB_XPAD + gx) = s;
+    }
+}
+
+// vertical blur pass: warp `wid` owns tile rows RPW*wid..RPW*wid+RPW-1.  The RPW + 6 row sums a lane needs per pixel are
+// paired vertically, P[j] = (H[j], H[j+1]) as u16x2, so that one DP2A applies two taps:
+// out[k] = (18,34).P[k] + (48,56).P[k+2] + (48,34).P[k+4] + (0,18).P[k+5]
+template <int TH>
+__device__ __forceinline__ void tile_vblur_pass(const PyrArgs& a, const unsigned short* __restrict__ Hs, int frame, int x0, int y0,
+                                                int wid, int lane) {
+    constexpr int RPW = TH / (PYR_THREADS / 32);
+    const int w = a.w, h = a.h;
+    const int gx = x0 + 4 * lane;
+    const unsigned short* col = Hs + 4 * lane;
+    uint2 v[RPW + 6];
+#pragma unroll
+    for (int j = 0; j < RPW + 6; j++) v[j] = *(const uint2*)(col + (RPW * wid + j) * TW);     // .x = (H(c), H(c+2)), .y = (H(c+1), H(c+3))
+    uint32_t P[RPW + 5][4];                                 // pixel order c, c+1, c+2, c+3
+#pragma unroll
+    for (int j = 0; j < RPW + 5; j++) {
+        P[j][0] = __byte_perm(v[j].x, v[j + 1].x, 0x5410); P[j][2] = __byte_perm(v[j].x, v[j + 1].x, 0x7632);
+        P[j][1] = __byte_perm(v[j].y, v[j + 1].y, 0x5410); P[j][3] = __byte_perm(v[j].y, v[j + 1].y, 0x7632);
+    }
+#pragma unroll
+    for (int k = 0; k < RPW; k++) {
+        const int y = y0 + RPW * wid + k;
+        uint32_t o[4];
+#pragma unroll
+        for (int q = 0; q < 4; q++) {
+            uint32_t acc = __dp2a_lo(P[k][q], 18u | (34u << 8), 32768u);
+            acc = __dp2a_lo(P[k + 2][q], 48u | (56u << 8), acc);
+            acc = __dp2a_lo(P[k + 4][q], 48u | (34u << 8), acc);
+            acc = __dp2a_lo(P[k + 5][q], 18u << 8, acc);
+            o[q] = acc >> 16;
+        }
+        if (y < h && gx < w)
+            *(uint32_t*)(a.blur + (size_t)frame * a.planeFrameStride + (size_t)y * a.pitch + ORB_XPAD + gx) =
+                o[0] | (o[1] << 8) | (o[2] << 16) | (o[3] << 24);
+    }
+}
+
+// ---- building the level tile T of a resized level from staged source rows S (dense rows of `scols` bytes) ----
+
+// per-tile tap tables: T byte b <-> level column x0 - 4 + b (b = 0 and b = 135 unused -> zero weights)
+template <int TH>
+__device__ __forceinline__ void tile_build_taps(const PyrArgs& a, TapX* __restrict__ tapx, TapX* __restrict__ tapy, int x0, int y0,
+                                                int sx_lo, int sy_lo, int tid) {
+    constexpr int TROWS = TH + 2 * HALO;
+    const int w = a.w, h = a.h;
+    if (tid < TBYTES) {
+        const int x = x0 - 4 + tid;
+        TapX t; t.o0 = 0; t.o1 = 0; t.a0 = 0; t.a1 = 0;
+        if (tid >= 1 && tid <= TW + 2 * HALO && x < w + HALO) {
+            const ResizeTap s = a.xtab[reflect101(x, w)];
+            t.o0 = (unsigned short)(s.s0 - sx_lo); t.o1 = (unsigned short)(s.s1 - sx_lo); t.a0 = s.a0; t.a1 = s.a1;
+        }
+        tapx[tid] = t;
+    } else if (tid >= 192 && tid < 192 + TROWS) {
+        const int ty = tid - 192, y = y0 - HALO + ty;
+        TapX t; t.o0 = 0; t.o1 = 0; t.a0 = 0; t.a1 = 0;
+        if (y < h + HALO) {
+            const ResizeTap s = a.ytab[reflect101(y, h)];
+            t.o0 = (unsigned short)(s.s0 - sy_lo); t.o1 = (unsigned short)(s.s1 - sy_lo); t.a0 = s.a0; t.a1 = s.a1;
+        }
+        tapy[ty] = t;
+    }
+}
+
+// Both resize passes: thread = (4-column group q, row slot); 34 groups x 7 slots = 238 active threads, so the
+// column taps of the horizontal pass are decoded once per thread and stay in registers.
+// horizontal pass (HResizeLinear, int32): Hq[r][b] = (S[r][o0]*a0 + S[r][o0+1]*a1) >> 4.
+// o1 == o0 + 1 whenever a1 != 0 (the x taps collapse the weight, not the index, at the borders).
+// A group's four tap pairs lie within 8 consecutive source bytes (scale < 2): fetch that window as three
+// aligned words + two funnel shifts, pick each (S[o], S[o+1]) pair with a per-thread constant PRMT selector
+// and weight it with one DP2A.
+__device__ __forceinline__ void tile_hresize(const PyrArgs& a, const uint8_t* __restrict__ S, int scols, int nrows,
+                                             const TapX* __restrict__ tapx, unsigned short* __restrict__ Hq, int x0, int tid) {
+    const int q = tid % (TBYTES / 4), slot = tid / (TBYTES / 4);
+    const bool live = slot < 7 && x0 - 4 + 4 * q < a.w + HALO;     // groups right of the image + halo are never read
+    if (!live) return;
+    int o[4];
+    uint32_t wt[4];
+    int base = 0x7fffffff;
+#pragma unroll
+    for (int j = 0; j < 4; j++) {
+        const uint2 tp = *(const uint2*)(tapx + 4 * q + j);
+        o[j] = (int)(tp.x & 0xffffu); wt[j] = tp.y;                 // a0 | a1 << 16
+        if (wt[j]) base = min(base, o[j]);
+    }
+    if (base == 0x7fffffff) base = 0;
+    uint32_t sel[4];
+    bool bad = false;
+#pragma unroll
+    for (int j = 0; j < 4; j++) {
+        const int d = wt[j] ? o[j] - base : 0;
+        bad |= d > 6;
+        sel[j] = (uint32_t)d | ((uint32_t)(d + 1) << 4);
+    }
+    if (bad) atomicExch(a.err, 202);
+    const int wb = base >> 2;
+    const unsigned sh = 8u * (unsigned)(base & 3);
+    for (int r = slot; r < nrows; r += 7) {
+        const uint32_t* Sw = (const uint32_t*)(S + r * scols) + wb;
+        const uint32_t w0 = Sw[0], w1 = Sw[1], w2 = Sw[2];
+        const uint32_t X0 = __funnelshift_r(w0, w1, sh), X1 = __funnelshift_r(w1, w2, sh);
+        uint32_t hh[4];
+#pragma unroll
+        for (int j = 0; j < 4; j++) hh[j] = __dp2a_lo(wt[j], __byte_perm(X0, X1, sel[j]), 0u) >> 4;
+        *(uint2*)(Hq + r * HQS + 4 * q) = make_uint2(hh[0] | (hh[1] << 16), hh[2] | (hh[3] << 16));
+    }
+}
+
+// vertical pass (VResizeLinear 8u): ((b0*H0)>>16) + ((b1*H1)>>16) + 2 >> 2; (b*lo16(u))>>16 == umulhi(u<<16, b)
+template <int TH>
+__device__ __forceinline__ void tile_vresize(const PyrArgs& a, const TapX* __restrict__ tapy, const unsigned short* __restrict__ Hq,
+                                             uint8_t* __restrict__ T, int x0, int y0, int tid) {
+    constexpr int TROWS = TH + 2 * HALO;
+    const int q = tid % (TBYTES / 4), slot = tid / (TBYTES / 4);
+    const bool live = slot < 7 && x0 - 4 + 4 * q < a.w + HALO;
+    if (!live) return;
+    const int tyEnd = min(TROWS, a.h + 2 * HALO - y0);             // T rows below the image + halo are never read
+    for (int ty = slot; ty < tyEnd; ty += 7) {
+        const uint2 tp = *(const uint2*)(tapy + ty);
+        const uint32_t b0 = tp.y & 0xffffu, b1 = tp.y >> 16;     // weights are in [0, 2048]
+        const uint2 u0 = *(const uint2*)(Hq + (tp.x & 0xffffu) * HQS + 4 * q);
+        const uint2 u1 = *(const uint2*)(Hq + (tp.x >> 16) * HQS + 4 * q);
+        const uint32_t v0 = (__umulhi(u0.x << 16, b0) + __umulhi(u1.x << 16, b1) + 2u) >> 2;
+        const uint32_t v1 = (__umulhi(u0.x & 0xffff0000u, b0) + __umulhi(u1.x & 0xffff0000u, b1) + 2u) >> 2;
+        const uint32_t v2 = (__umulhi(u0.y << 16, b0) + __umulhi(u1.y << 16, b1) + 2u) >> 2;
+        const uint32_t v3 = (__umulhi(u0.y & 0xffff0000u, b0) + __umulhi(u1.y & 0xffff0000u, b1) + 2u) >> 2;
+        *(uint32_t*)(T + ty * TS + 4 * q) = v0 | (v1 << 8) | (v2 << 16) | (v3 << 24);
+    }
+}
+
 // shared memory carve-up (bytes).  T is live from the resize to the row pass; everything else lives in one region R
 // behind it that is used twice: [tap tables | Hq | staged source rows] while T is being built, then
 // [Hs | pair planes PA, PB] once T is complete.  54 KB per CTA at every level -> four CTAs per SM.
@@ -285,160 +471,20 @@ __global__ void __launch_bounds__(PYR_THREADS) pyr_level_kernel(PyrArgs a) {
             const uint4 v = __ldg((const uint4*)(src + (size_t)(sy_lo + r) * a.srcPitch + a.srcX0 + sx_lo + 16 * c));
             *(uint4*)(S + r * scols + 16 * c) = v;
         }
-        // per-tile tap tables: T byte b <-> level column x0 - 4 + b (b = 0 and b = 135 unused -> zero weights)
-        if (tid < TBYTES) {
-            const int x = x0 - 4 + tid;
-            TapX t; t.o0 = 0; t.o1 = 0; t.a0 = 0; t.a1 = 0;
-            if (tid >= 1 && tid <= TW + 2 * HALO && x < w + HALO) {
-                const ResizeTap s = a.xtab[reflect101(x, w)];
-                t.o0 = (unsigned short)(s.s0 - sx_lo); t.o1 = (unsigned short)(s.s1 - sx_lo); t.a0 = s.a0; t.a1 = s.a1;
-            }
-            tapx[tid] = t;
-        } else if (tid >= 192 && tid < 192 + TROWS) {
-            const int ty = tid - 192, y = y0 - HALO + ty;
-            TapX t; t.o0 = 0; t.o1 = 0; t.a0 = 0; t.a1 = 0;
-            if (y < h + HALO) {
-                const ResizeTap s = a.ytab[reflect101(y, h)];
-                t.o0 = (unsigned short)(s.s0 - sy_lo); t.o1 = (unsigned short)(s.s1 - sy_lo); t.a0 = s.a0; t.a1 = s.a1;
-            }
-            tapy[ty] = t;
-        }
+        tile_build_taps<TH>(a, tapx, tapy, x0, y0, sx_lo, sy_lo, tid);
         __syncthreads();
-        // Both passes: thread = (4-column group q, row slot); 34 groups x 7 slots = 238 active threads, so the
-        // column taps of the horizontal pass are decoded once per thread and stay in registers.
-        const int q = tid % (TBYTES / 4), slot = tid / (TBYTES / 4);
-        const bool live = slot < 7 && x0 - 4 + 4 * q < w + HALO;     // groups right of the image + halo are never read
-        const int tyEnd = min(TROWS, h + 2 * HALO - y0);             // T rows below the image + halo are never read
-        if (live) {
-            // horizontal pass (HResizeLinear, int32): Hq[r][b] = (S[r][o0]*a0 + S[r][o0+1]*a1) >> 4.
-            // o1 == o0 + 1 whenever a1 != 0 (the x taps collapse the weight, not the index, at the borders).
-            // A group's four tap pairs lie within 8 consecutive source bytes (scale < 2): fetch that window as three
-            // aligned words + two funnel shifts, pick each (S[o], S[o+1]) pair with a per-thread constant PRMT selector
-            // and weight it with one DP2A.
-            int o[4];
-            uint32_t wt[4];
-            int base = 0x7fffffff;
-#pragma unroll
-            for (int j = 0; j < 4; j++) {
-                const uint2 tp = *(const uint2*)(tapx + 4 * q + j);
-                o[j] = (int)(tp.x & 0xffffu); wt[j] = tp.y;                 // a0 | a1 << 16
-                if (wt[j]) base = min(base, o[j]);
-            }
-            if (base == 0x7fffffff) base = 0;
-            uint32_t sel[4];
-            bool bad = false;
-#pragma unroll
-            for (int j = 0; j < 4; j++) {
-                const int d = wt[j] ? o[j] - base : 0;
-                bad |= d > 6;
-                sel[j] = (uint32_t)d | ((uint32_t)(d + 1) << 4);
-            }
-            if (bad) atomicExch(a.err, 202);
-            const int wb = base >> 2;
-            const unsigned sh = 8u * (unsigned)(base & 3);
-            for (int r = slot; r < nrows; r += 7) {
-                const uint32_t* Sw = (const uint32_t*)(S + r * scols) + wb;
-                const uint32_t w0 = Sw[0], w1 = Sw[1], w2 = Sw[2];
-                const uint32_t X0 = __funnelshift_r(w0, w1, sh), X1 = __funnelshift_r(w1, w2, sh);
-                uint32_t hh[4];
-#pragma unroll
-                for (int j = 0; j < 4; j++) hh[j] = __dp2a_lo(wt[j], __byte_perm(X0, X1, sel[j]), 0u) >> 4;
-                *(uint2*)(Hq + r * HQS + 4 * q) = make_uint2(hh[0] | (hh[1] << 16), hh[2] | (hh[3] << 16));
-            }
-        }
+        tile_hresize(a, S, scols, nrows, tapx, Hq, x0, tid);
         __syncthreads();
-        if (live) {
-            // vertical pass (VResizeLinear 8u): ((b0*H0)>>16) + ((b1*H1)>>16) + 2 >> 2; (b*lo16(u))>>16 == umulhi(u<<16, b)
-            for (int ty = slot; ty < tyEnd; ty += 7) {
-                const uint2 tp = *(const uint2*)(tapy + ty);
-                const uint32_t b0 = tp.y & 0xffffu, b1 = tp.y >> 16;     // weights are in [0, 2048]
-                const uint2 u0 = *(const uint2*)(Hq + (tp.x & 0xffffu) * HQS + 4 * q);
-                const uint2 u1 = *(const uint2*)(Hq + (tp.x >> 16) * HQS + 4 * q);
-                const uint32_t v0 = (__umulhi(u0.x << 16, b0) + __umulhi(u1.x << 16, b1) + 2u) >> 2;
-                const uint32_t v1 = (__umulhi(u0.x & 0xffff0000u, b0) + __umulhi(u1.x & 0xffff0000u, b1) + 2u) >> 2;
-                const uint32_t v2 = (__umulhi(u0.y << 16, b0) + __umulhi(u1.y << 16, b1) + 2u) >> 2;
-                const uint32_t v3 = (__umulhi(u0.y & 0xffff0000u, b0) + __umulhi(u1.y & 0xffff0000u, b1) + 2u) >> 2;
-                *(uint32_t*)(T + ty * TS + 4 * q) = v0 | (v1 << 8) | (v2 << 16) | (v3 << 24);
-            }
-        }
+        tile_vresize<TH>(a, tapy, Hq, T, x0, y0, tid);
     }
     __syncthreads();
 
-    // ---- level plane: 16 pixels per thread ------------------------------------
-    {
-        const int vx = (tid & 7) * 16, vy = tid >> 3;
-        if (vy < TH && (y0 + vy < h) && (x0 + vx < w)) {
-            const uint32_t* t = (const uint32_t*)(T + (vy + HALO) * TS + TCOL0 + vx);
-            const uint4 v = make_uint4(t[0], t[1], t[2], t[3]);
-            *(uint4*)(a.pyr + (size_t)frame * a.pyrFrameStride + (size_t)(ORB_EDGE + y0 + vy) * a.pitch + ORB_XPAD + x0 + vx) = v;
-        }
-    }
-
-    // ---- row pass: one warp per T row, one 4-pixel group per lane: split the row into its stride-2 pixel pairs
-    //      (kept in the pair planes for FAST) and form the horizontal blur sums ----
+    tile_store_plane<TH>(a, T, frame, x0, y0, tid);
     uint4* PB = PA + TROWS * 32;
-    const int rEnd = min(TROWS, h + 2 * HALO - y0);       // rows below the image + halo feed nothing that is stored
-    for (int r = wid; r < rEnd; r += PYR_THREADS / 32) {
-        const RowPairs p = row_pairs((const uint32_t*)(T + r * TS) + lane);
-        PA[r * 32 + lane] = make_uint4(p.x1, p.em, p.om, p.x2);
-        PB[r * 32 + lane] = make_uint4(p.ol, p.x4, p.x3, p.er);
-        uint32_t A, B;
-        hblur4(p, A, B);
-        *(uint2*)(Hs + r * TW + 4 * lane) = make_uint2(A, B);
-    }
+    tile_row_pass<TH>(T, Hs, PA, PB, h, y0, wid, lane);
     __syncthreads();      // planes and Hs complete
-
-    // ---- FAST score: warp `wid` owns tile rows RPW*wid..RPW*wid+RPW-1, lane = 4-pixel group ----
-    const int gx = x0 + 4 * lane;                        // level column of the group's first pixel
-#pragma unroll 1
-    for (int k = 0; k < RPW; k++) {
-        const int r = RPW * wid + k, y = y0 + r;
-        if (y >= h || gx >= w) continue;
-        uint32_t s = 0;
-        if (y >= ORB_EDGE && y < h - ORB_EDGE && gx + 3 >= ORB_EDGE && gx < w - ORB_EDGE) {
-            s = fast_score4(PA, PB, r, lane, a.minTh);
-            if (gx < ORB_EDGE || gx + 3 >= w - ORB_EDGE) {           // group straddles the detection area
-                uint32_t m = 0;
-#pragma unroll
-                for (int j = 0; j < 4; j++)
-                    if (gx + j >= ORB_EDGE && gx + j < w - ORB_EDGE) m |= 0xffu << (8 * j);
-                s &= m;
-            }
-        }
-        *(uint32_t*)(a.score + (size_t)frame * a.planeFrameStride + (size_t)y * a.pitch + ORB_XPAD + gx) = s;
-    }
-
-    // ---- vertical blur pass: warp `wid` owns tile rows RPW*wid..RPW*wid+RPW-1.  The RPW + 6 row sums a lane needs per pixel are
-    //      paired vertically, P[j] = (H[j], H[j+1]) as u16x2, so that one DP2A applies two taps:
-    //      out[k] = (18,34).P[k] + (48,56).P[k+2] + (48,34).P[k+4] + (0,18).P[k+5] ----
-    {
-        const unsigned short* col = Hs + 4 * lane;
-        uint2 v[RPW + 6];
-#pragma unroll
-        for (int j = 0; j < RPW + 6; j++) v[j] = *(const uint2*)(col + (RPW * wid + j) * TW);     // .x = (H(c), H(c+2)), .y = (H(c+1), H(c+3))
-        uint32_t P[RPW + 5][4];                                 // pixel order c, c+1, c+2, c+3
-#pragma unroll
-        for (int j = 0; j < RPW + 5; j++) {
-            P[j][0] = __byte_perm(v[j].x, v[j + 1].x, 0x5410); P[j][2] = __byte_perm(v[j].x, v[j + 1].x, 0x7632);
-            P[j][1] = __byte_perm(v[j].y, v[j + 1].y, 0x5410); P[j][3] = __byte_perm(v[j].y, v[j + 1].y, 0x7632);
-        }
-#pragma unroll
-        for (int k = 0; k < RPW; k++) {
-            const int y = y0 + RPW * wid + k;
-            uint32_t o[4];
-#pragma unroll
-            for (int q = 0; q < 4; q++) {
-                uint32_t acc = __dp2a_lo(P[k][q], 18u | (34u << 8), 32768u);
-                acc = __dp2a_lo(P[k + 2][q], 48u | (56u << 8), acc);
-                acc = __dp2a_lo(P[k + 4][q], 48u | (34u << 8), acc);
-                acc = __dp2a_lo(P[k + 5][q], 18u << 8, acc);
-                o[q] = acc >> 16;
-            }
-            if (y < h && gx < w)
-                *(uint32_t*)(a.blur + (size_t)frame * a.planeFrameStride + (size_t)y * a.pitch + ORB_XPAD + gx) =
-                    o[0] | (o[1] << 8) | (o[2] << 16) | (o[3] << 24);
-        }
-    }
+    tile_fast_pass<TH>(a, PA, PB, frame, x0, y0, wid, lane);
+    tile_vblur_pass<TH>(a, Hs, frame, x0, y0, wid, lane);
 }
 
 // BORDER_REFLECT_101 frame of 19 pixels around every level (copyMakeBorder,
