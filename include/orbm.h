@@ -58,6 +58,17 @@ int orbm_merge_top2_device(orbm_t* m, const orbm_top2* d_parts, int nparts, int 
 /* Host-buffer convenience: H2D of the queries, 2-NN against a device-resident database, D2H. */
 int orbm_bf2nn(orbm_t* m, const uint8_t* queries, int nq, const uint8_t* d_db, size_t ndb,
                uint32_t idx_base, orbm_top2* out);
+/* orbm_bf2nn_device for callers that cannot allocate (CUDA graph capture, tight serving loops, harnesses that forbid
+ * cudaMalloc).  NO COUNTERPART IN THE REFERENCE.  Same arguments and
+ * results as orbm_bf2nn_device, but the per-slice scratch records live in a fixed file-scope device array of
+ * ORBM_NOALLOC_PART_RECORDS x 16 bytes = 10 MiB (held by every GPU that loads the library until the process exits) and the
+ * call performs no cudaMalloc / cudaFree.  Limits: nq <= ORBM_NOALLOC_MAX_QUERIES; beyond them ORBX_E_CAPACITY (with a
+ * message on stderr).  All calls share the one array: calls that overlap on the same GPU (two contexts, two streams)
+ * race - serialise them.  Enqueued on the context stream, not synchronised. */
+#define ORBM_NOALLOC_MAX_QUERIES 4096
+#define ORBM_NOALLOC_PART_RECORDS (640 * 1024)
+int orbm_bf2nn_device_noalloc(orbm_t* m, const uint8_t* d_queries, int nq, const uint8_t* d_db, size_t ndb,
+                              uint32_t idx_base, orbm_top2* d_out);
 /* The acceptance of src/ORBmatcher.cc:228-230 applied to a top-2 result. */
 int orbm_accept_low_ratio(orbm_top2 r, float nnratio);
 /* measured integer-pipe peak: 32-bit popc per second of this GPU (microbenchmark) */

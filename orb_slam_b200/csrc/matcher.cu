@@ -176,6 +176,65 @@ int orbm_bf2nn(orbm_t* m, const uint8_t* queries, int nq, const uint8_t* d_db, s
     return ORBX_OK;
 }
 
+// ---- orbm_bf2nn_device without any allocation (include/orbm.h: no counterpart in the reference; added
+// for callers that cannot call cudaMalloc: CUDA graph capture, tight serving loops).  The per-slice
+// top-2 records bf2nn_kernel hands to merge_slices_kernel live in a file-scope device array instead of the context's
+// growable buffer.  Every GPU that loads the library holds the array until exit; every call shares it (calls that
+// overlap on one GPU race); nothing in it needs clearing: a call writes every record it later reads.
+static __device__ __align__(256) Top2Key g_noalloc_part[ORBM_NOALLOC_PART_RECORDS];
+
+// device address of the array: the name above is a host-side stand-in in host code, not a device pointer
+static int noalloc_part_ptr(int device, Top2Key** out) {
+    static std::mutex mtx;
+    static Top2Key* ptr[64] = {};
+    if (device < 0 || device >= 64) return ORBX_E_INVALID;
+    std::lock_guard<std::mutex> lk(mtx);
+    if (!ptr[device]) {                                  // once per device, with that device current (the caller set it)
+        Top2Key* p = nullptr;
+        CKM(cudaGetSymbolAddress((void**)&p, g_noalloc_part));
+        ptr[device] = p;
+    }
+    *out = ptr[device];
+    return ORBX_OK;
+}
+
+int orbm_bf2nn_device_noalloc(orbm_t* m, const uint8_t* d_queries, int nq, const uint8_t* d_db, size_t ndb, uint32_t idx_base,
+                              orbm_top2* d_out) {
+    if (!m || !d_queries || nq <= 0 || !d_out || (ndb && !d_db)) return ORBX_E_INVALID;
+    if (((uintptr_t)d_queries & 15) || ((uintptr_t)d_db & 15)) return ORBX_E_INVALID;
+    if (nq > ORBM_NOALLOC_MAX_QUERIES) {
+        std::fprintf(stderr, "orbm_bf2nn_device_noalloc: %d queries exceed the fixed scratch (at most %d per call; use orbm_bf2nn_device)\n",
+                     nq, ORBM_NOALLOC_MAX_QUERIES);
+        return ORBX_E_CAPACITY;
+    }
+    std::lock_guard<std::mutex> lk(m->mtx);
+    CKM(cudaSetDevice(m->device));
+    Top2Key* part = nullptr;
+    int rc = noalloc_part_ptr(m->device, &part);
+    if (rc) return rc;
+    // the slicing of orbm_bf2nn_device, additionally bounded by the scratch: slices * nq records
+    const int qtiles = (nq + BF_QTILE - 1) / BF_QTILE;
+    int slices = std::max(1, (m->numSMs * 4 + qtiles - 1) / qtiles);
+    slices = std::min(slices, ORBM_NOALLOC_PART_RECORDS / nq);
+    const size_t maxUseful = std::max<size_t>(1, (ndb + BF_ROWS - 1) / BF_ROWS);
+    if ((size_t)slices > maxUseful) slices = (int)maxUseful;
+    size_t rowsPerSlice = (ndb + slices - 1) / std::max(slices, 1);
+    rowsPerSlice = std::max<size_t>(BF_ROWS, (rowsPerSlice + BF_ROWS - 1) / BF_ROWS * BF_ROWS);
+    if (rowsPerSlice > (1u << 23)) rowsPerSlice = 1u << 23;
+    slices = (int)std::max<size_t>(1, (ndb + rowsPerSlice - 1) / rowsPerSlice);
+    if ((size_t)slices * nq > (size_t)ORBM_NOALLOC_PART_RECORDS) {
+        std::fprintf(stderr, "orbm_bf2nn_device_noalloc: %zu rows x %d queries need %d slices, beyond the fixed scratch "
+                             "(at most %zu rows at this query count; use orbm_bf2nn_device)\n",
+                     ndb, nq, slices, (size_t)(ORBM_NOALLOC_PART_RECORDS / nq) << 23);
+        return ORBX_E_CAPACITY;
+    }
+    bf2nn_kernel<<<dim3(slices, qtiles), BF_THREADS, 0, m->stream>>>((const uint32_t*)d_queries, nq, (const uint32_t*)d_db,
+                                                                       (unsigned long long)ndb, (unsigned)rowsPerSlice, idx_base, part);
+    merge_slices_kernel<<<(nq + 255) / 256, 256, 0, m->stream>>>(part, slices, nq, d_out);
+    CKM(cudaGetLastError());
+    return ORBX_OK;
+}
+
 int orbm_accept_low_ratio(orbm_top2 r, float nnratio) {
     return r.d1 <= ORBM_TH_LOW && (float)r.d1 < nnratio * (float)r.d2;
 }

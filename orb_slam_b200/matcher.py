@@ -144,6 +144,7 @@ def _bind(L):
     L.orbm_descriptor_distance.argtypes = [vp, vp]; L.orbm_descriptor_distance.restype = i
     L.orbm_three_maxima.argtypes = [vp, i, C.POINTER(i), C.POINTER(i), C.POINTER(i)]; L.orbm_three_maxima.restype = None
     L.orbm_bf2nn_device.argtypes = [vp, vp, i, vp, sz, C.c_uint32, vp]; L.orbm_bf2nn_device.restype = i
+    L.orbm_bf2nn_device_noalloc.argtypes = [vp, vp, i, vp, sz, C.c_uint32, vp]; L.orbm_bf2nn_device_noalloc.restype = i
     L.orbm_merge_top2_device.argtypes = [vp, vp, i, i, vp]; L.orbm_merge_top2_device.restype = i
     L.orbm_bf2nn.argtypes = [vp, vp, i, vp, sz, C.c_uint32, vp]; L.orbm_bf2nn.restype = i
     L.orbm_popc_peak.argtypes = [vp, C.POINTER(C.c_double)]; L.orbm_popc_peak.restype = i
