@@ -75,6 +75,9 @@ int orbm_accept_low_ratio(orbm_top2 r, float nnratio);
 int orbm_popc_peak(orbm_t* m, double* popc_per_s);
 /* same for LOP3, the instruction that binds the 2-NN kernel (16 per pair against 4 POPC) */
 int orbm_lop3_peak(orbm_t* m, double* lop3_per_s);
+/* ... and for the whole per-pair instruction mix of the 2-NN kernel (16 LOP3 + 4 POPC + the weighted sum) on register
+ * operands: pairs per second this GPU can evaluate with that mix, the kernel's speed of light */
+int orbm_pair_mix_peak(orbm_t* m, double* pairs_per_s);
 
 /* ---- The database of M6 split across GPUs (BASELINE.json configs[3]: 4096 queries against a
  * 10^7-row keyframe-descriptor database on 8 GPUs).  One orbm_shard per GPU, one process or thread each.  A query

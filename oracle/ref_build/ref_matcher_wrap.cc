@@ -6,6 +6,7 @@
 // The objects (Frame, KeyFrame, MapPoint) are the reference's classes; this file only fills their members.
 #include <algorithm>
 #include <cassert>
+#include <chrono>
 #include <cmath>
 #include <cstring>
 #include <fstream>
@@ -55,6 +56,8 @@ std::vector<cv::Mat> Converter::toDescriptorVector(const cv::Mat& Descriptors) {
 }  // namespace ORB_SLAM2
 
 using namespace ORB_SLAM2;
+
+static double g_last_ms = 0.0;     // tools/dropin_latency.py: the reference member timed beside the drop-in member
 
 namespace {
 
@@ -175,6 +178,8 @@ template <typename T> void assign_const(const std::vector<T>& dst, const T* src,
 
 extern "C" {
 
+double orbref_last_ms() { return g_last_ms; }
+
 void orbref_grid_build(const orbm_frame* f, int32_t* cell_start, int32_t* items) {
     World w;
     Frame* F = make_frame(w, f);
@@ -204,7 +209,9 @@ int orbref_search_for_initialization(const orbm_frame* f1, const orbm_frame* f2,
     for (int i = 0; i < f1->N; i++) vbPrevMatched[i] = cv::Point2f(prev[2 * i], prev[2 * i + 1]);
     std::vector<int> m12;
     ORBmatcher matcher(mfNNratio, mbCheckOrientation != 0);
+    const auto t0_ = std::chrono::steady_clock::now();      // wall time of the member call alone: orbref_last_ms()
     const int n = matcher.SearchForInitialization(*F1, *F2, vbPrevMatched, m12, windowSize);   // src/ORBmatcher.cc:417-588
+    g_last_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0_).count();
     for (int i = 0; i < f1->N; i++) { vnMatches12[i] = m12[i]; prev[2 * i] = vbPrevMatched[i].x; prev[2 * i + 1] = vbPrevMatched[i].y; }
     return n;
 }
@@ -225,7 +232,9 @@ int orbref_search_by_projection_frame(const orbm_frame* c, const orbm_frame* l, 
     for (int i = 0; i < c->N; i++)
         if (curObs[i] >= 0) before[i] = C->mvpMapPoints[i] = make_plain_point(w, curObs[i], false);
     ORBmatcher matcher(0.9f, checkOri != 0);
+    const auto t0_ = std::chrono::steady_clock::now();      // wall time of the member call alone: orbref_last_ms()
     const int n = matcher.SearchByProjection(*C, *L, th, bMono != 0);                // src/ORBmatcher.cc:1396-1538
+    g_last_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0_).count();
     for (int i = 0; i < c->N; i++) {
         MapPoint* p = C->mvpMapPoints[i];
         if (p == before[i]) curAssign[i] = -2;
@@ -247,7 +256,9 @@ int orbref_search_by_projection_points(const orbm_frame* f, const orbm_mappoint*
     for (int i = 0; i < f->N; i++)
         if (frameObs[i] >= 0) before[i] = F->mvpMapPoints[i] = make_plain_point(w, frameObs[i], false);
     ORBmatcher matcher(mfNNratio, true);
+    const auto t0_ = std::chrono::steady_clock::now();      // wall time of the member call alone: orbref_last_ms()
     const int n = matcher.SearchByProjection(*F, vp, th);                           // src/ORBmatcher.cc:45-129
+    g_last_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0_).count();
     for (int i = 0; i < f->N; i++) {
         MapPoint* p = F->mvpMapPoints[i];
         frameAssign[i] = p == before[i] ? -2 : index.at(p);
@@ -269,7 +280,9 @@ int orbref_search_by_bow_kf_frame(const uint8_t* descKF, const float* angleKFun,
     Frame* F = make_bow_frame(w, descF, angleF, nF, fvF);
     std::vector<MapPoint*> matches;
     ORBmatcher matcher(mfNNratio, mbCheckOrientation != 0);
+    const auto t0_ = std::chrono::steady_clock::now();      // wall time of the member call alone: orbref_last_ms()
     const int n = matcher.SearchByBoW(pKF, *F, matches);                            // src/ORBmatcher.cc:159-288
+    g_last_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0_).count();
     for (int i = 0; i < nF; i++) vpMapPointMatches[i] = matches[i] ? index.at(matches[i]) : -1;
     return n;
 }
@@ -289,7 +302,9 @@ int orbref_search_by_bow_kf_kf(const uint8_t* desc1, const float* angle1, const 
     w.keyframes.push_back(pKF1); w.keyframes.push_back(pKF2);
     std::vector<MapPoint*> m12;
     ORBmatcher matcher(mfNNratio, mbCheckOrientation != 0);
+    const auto t0_ = std::chrono::steady_clock::now();      // wall time of the member call alone: orbref_last_ms()
     const int n = matcher.SearchByBoW(pKF1, pKF2, m12);                             // src/ORBmatcher.cc:590-723
+    g_last_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0_).count();
     for (int i = 0; i < n1; i++) vpMatches12[i] = m12[i] ? index2.at(m12[i]) : -1;
     return n;
 }
@@ -346,7 +361,9 @@ int orbref_compute_stereo_matches(const uint8_t* imgL, const uint8_t* imgR, int 
     F->mbf = mbf; F->mb = mb;
     const int NR = (int)F->mvKeysRight.size();
     if (F->N > cap || NR > cap) return -1;
+    const auto t0_ = std::chrono::steady_clock::now();      // wall time of the member call alone: orbref_last_ms()
     F->ComputeStereoMatches();
+    g_last_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0_).count();
     *nL = F->N; *nR = NR;
     std::memcpy(keysL, F->mvKeys.data(), (size_t)F->N * sizeof(orbx_keypoint));
     std::memcpy(keysR, F->mvKeysRight.data(), (size_t)NR * sizeof(orbx_keypoint));
@@ -386,7 +403,9 @@ int orbref_search_by_projection_keyframe(const orbm_frame* c, const orbm_mappoin
     std::vector<MapPoint*> before((size_t)c->N, static_cast<MapPoint*>(NULL));
     for (int i = 0; i < c->N; i++) if (curHasPoint[i]) before[i] = Cf->mvpMapPoints[i] = make_plain_point(w, 1, false);
     ORBmatcher matcher(0.9f, checkOri != 0);
+    const auto t0_ = std::chrono::steady_clock::now();      // wall time of the member call alone: orbref_last_ms()
     const int nm = matcher.SearchByProjection(*Cf, pKF, found, th, ORBdist);
+    g_last_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0_).count();
     for (int i = 0; i < c->N; i++) {
         MapPoint* p = Cf->mvpMapPoints[i];
         curAssign[i] = p == before[i] ? -2 : (p ? index.at(p) : -1);
@@ -417,7 +436,9 @@ int orbref_fuse_select(const orbm_frame* kf, const float* cameraCenter, const fl
         if (inKeyFrame[i]) p->mObservations[pKF] = 0;          // IsInKeyFrame(pKF) without occupying a key point
     }
     ORBmatcher matcher(0.6f, true);
+    const auto t0_ = std::chrono::steady_clock::now();      // wall time of the member call alone: orbref_last_ms()
     const int nFused = matcher.Fuse(pKF, vp, th);
+    g_last_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0_).count();
     for (int i = 0; i < nMPs; i++) {
         bestIdxOut[i] = -1;
         MapPoint* p = vp[i];
@@ -462,7 +483,9 @@ int orbref_search_for_triangulation(const orbm_keyframe* k1, const orbm_keyframe
     std::memcpy(F.data, F12, 36);
     std::vector<std::pair<size_t, size_t> > pairs;
     ORBmatcher matcher(0.6f, mbCheckOrientation != 0);
+    const auto t0_ = std::chrono::steady_clock::now();      // wall time of the member call alone: orbref_last_ms()
     const int n = matcher.SearchForTriangulation(pKF[0], pKF[1], F, pairs, bOnlyStereo != 0);
+    g_last_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0_).count();
     for (int i = 0; i < k1->N; i++) vMatches12[i] = -1;
     for (size_t i = 0; i < pairs.size(); i++) vMatches12[pairs[i].first] = (int32_t)pairs[i].second;
     return n;
@@ -526,7 +549,9 @@ int orbref_search_by_projection_sim3(const orbm_frame* kf, const float* Scw16, c
     cv::Mat Scw(4, 4, CV_32F);
     std::memcpy(Scw.data, Scw16, 64);
     ORBmatcher matcher(0.75f, true);
+    const auto t0_ = std::chrono::steady_clock::now();      // wall time of the member call alone: orbref_last_ms()
     const int nm = matcher.SearchByProjection(pKF, Scw, P.vp, vpMatched, th);
+    g_last_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0_).count();
     for (int i = 0; i < kf->N; i++) match[i] = vpMatched[i] == before[i] ? -2 : P.index.at(vpMatched[i]);
     return nm;
 }
@@ -554,7 +579,9 @@ int orbref_fuse_select_sim3(const orbm_frame* kf, const float* Scw16, const orbm
     std::memcpy(Scw.data, Scw16, 64);
     std::vector<MapPoint*> vpReplacePoint((size_t)nPoints, static_cast<MapPoint*>(NULL));
     ORBmatcher matcher(0.75f, true);
+    const auto t0_ = std::chrono::steady_clock::now();      // wall time of the member call alone: orbref_last_ms()
     const int nFused = matcher.Fuse(pKF, Scw, P.vp, th, vpReplacePoint);
+    g_last_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0_).count();
     for (int i = 0; i < nPoints; i++) bestIdxOut[i] = vpReplacePoint[i] ? slotOf.at(vpReplacePoint[i]) : -1;
     return nFused;
 }
@@ -599,7 +626,9 @@ int orbref_search_by_sim3(const orbm_frame* k1, const orbm_frame* k2, const orbm
     std::memcpy(R.data, R12, 36);
     for (int k = 0; k < 3; k++) t.at<float>(k) = t12[k];
     ORBmatcher matcher(0.75f, true);
+    const auto t0_ = std::chrono::steady_clock::now();      // wall time of the member call alone: orbref_last_ms()
     const int nFound = matcher.SearchBySim3(pKF1, pKF2, vpMatches12, s12, R, t, th);
+    g_last_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0_).count();
     for (int i = 0; i < k1->N; i++) match12[i] = vpMatches12[i] == before[i] ? -1 : P2.index.at(vpMatches12[i]);
     return nFound;
 }

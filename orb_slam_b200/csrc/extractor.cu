@@ -17,6 +17,7 @@
 #include "describe.cuh"
 #include "geom.h"
 #include "pyramid.cuh"
+#include "pyramid_tma.cuh"
 #include "quadtree_kernel.cuh"
 #include "stereo.cuh"
 
@@ -62,7 +63,11 @@ struct orbx_extractor {
         uint32_t *d_keyA = nullptr, *d_keyB = nullptr, *d_valA = nullptr, *d_valB = nullptr, *d_sel = nullptr;
         int *d_candCount = nullptr, *d_selCount = nullptr;
         int lastFrames = 0;
+        // TMA descriptors of the bordered planes of levels 0..n-2 (the sources of levels 1..n-1), see pyramid_tma.cuh
+        CUtensorMap srcMap[ORB_MAX_LEVELS];
+        bool tma[ORB_MAX_LEVELS] = {};
     } ws[ORBX_NWS];
+    int numSMs = 148;
     int lastWs = 0;                          // workspace holding the most recent frames (introspection, stereo)
     cudaEvent_t evFork = nullptr, evJoin[ORBX_NWS] = {};
     int* d_err = nullptr;
@@ -259,6 +264,50 @@ static size_t res_bytes(const FrameGeom& g, int frames) {
 }
 static size_t res_head(int frames) { return ((size_t)(frames + 1) * 4 + 63) & ~(size_t)63; }
 
+// cuTensorMapEncodeTiled through the runtime's driver entry point lookup (no link-time libcuda dependency)
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static EncodeTiledFn encode_tiled_fn() {
+    static EncodeTiledFn fn = [] {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) != cudaSuccess || q != cudaDriverEntryPointSuccess) p = nullptr;
+        cudaGetLastError();
+        return (EncodeTiledFn)p;
+    }();
+    return fn;
+}
+
+static void pyr_smem_for(int TH, const LevelGeom& prev, const LevelGeom& cur, int& cols, int& rows, size_t& bytes);
+
+// Source-plane descriptors for the persistent TMA level kernel: level l (> 0) reads boxes of level l-1's bordered plane,
+// a 3-D tensor (byte in row, row, frame) with strides (pitch, pyrBytes).
+static void build_tensor_maps(orbx_extractor* e, orbx_extractor::Workspace& w, int capFrames) {
+    static const bool noTma = std::getenv("ORBX_NO_TMA") != nullptr;
+    const FrameGeom& g = e->g;
+    for (int l = 0; l < ORB_MAX_LEVELS; l++) w.tma[l] = false;
+    EncodeTiledFn enc = encode_tiled_fn();
+    if (!enc || noTma) return;
+    for (int l = 1; l < g.nlevels; l++) {
+        const LevelGeom& p = g.lv[l - 1];
+        const LevelGeom& v = g.lv[l];
+        int cols, rows; size_t bytes;
+        pyr_smem_for(TH_BATCH, p, v, cols, rows, bytes);
+        const int tilesX = (v.w + TW - 1) / TW, tilesY = (v.h + TH_BATCH - 1) / TH_BATCH;
+        if (!pyrt_fits(rows, cols) || tilesX > PYR_MAX_TILES_X || tilesY > PYR_MAX_TILES_Y) continue;
+        const cuuint64_t dims[3] = {(cuuint64_t)p.pitch, (cuuint64_t)(p.h + 2 * ORB_EDGE), (cuuint64_t)capFrames};
+        const cuuint64_t strides[2] = {(cuuint64_t)p.pitch, (cuuint64_t)g.pyrBytes};
+        const cuuint32_t box[3] = {(cuuint32_t)cols, (cuuint32_t)rows, 1u};
+        const cuuint32_t estr[3] = {1u, 1u, 1u};
+        const CUresult r = enc(&w.srcMap[l], CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, w.d_pyr + p.pyrOff, dims, strides, box, estr,
+                               CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                               CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+        w.tma[l] = r == CUDA_SUCCESS;
+        if (r != CUDA_SUCCESS) std::fprintf(stderr, "orbx: cuTensorMapEncodeTiled failed for level %d (%d): falling back to the staged-load kernel\n", l, (int)r);
+    }
+}
+
 // `frames` = frames per workspace
 static int ensure_workspace(orbx_extractor* e, int width, int height, int frames, bool needInput) {
     if (e->haveGeom && e->g.width == width && e->g.height == height && frames <= e->capFrames &&
@@ -297,6 +346,7 @@ static int ensure_workspace(orbx_extractor* e, int width, int height, int frames
         CK(cudaMalloc(&w.d_sel, (size_t)g.selTotal * F * 4));
         CK(cudaMalloc(&w.d_candCount, F * g.nlevels * 4));
         CK(cudaMalloc(&w.d_selCount, F * g.nlevels * 4));
+        build_tensor_maps(e, w, newCap);
     }
     e->resBytes = res_bytes(g, newCap);
     for (int b = 0; b < (needInput || hadInput ? ORBX_NBUF : 1); b++) {
@@ -312,6 +362,7 @@ static int ensure_workspace(orbx_extractor* e, int width, int height, int frames
     CK(cudaFuncSetAttribute(pyr_level_kernel<true, TH_BATCH>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
     CK(cudaFuncSetAttribute(pyr_level_kernel<false, TH_LATENCY>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
     CK(cudaFuncSetAttribute(pyr_level_kernel<true, TH_LATENCY>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
+    CK(cudaFuncSetAttribute(pyr_level_tma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pyrt_smem_bytes()));
     return ORBX_OK;
 }
 
@@ -370,7 +421,12 @@ static int enqueue_pipeline(orbx_extractor* e, int wi, const uint8_t* src, size_
             size_t smem;
             pyr_smem_for(TH, p, v, a.srcTileCols, a.srcTileRows, smem);
             if (lowTiles) pyr_level_kernel<false, TH_LATENCY><<<grid, PYR_THREADS, smem, st>>>(a);
-            else pyr_level_kernel<false, TH_BATCH><<<grid, PYR_THREADS, smem, st>>>(a);
+            else if (w.tma[l] && a.haveTiles) {
+                // persistent CTAs, source boxes by bulk tensor copy, the next tile's box in flight during FAST
+                const int total = (int)(grid.x * grid.y) * frames;
+                const int ctas = std::min(total, e->numSMs * 4);
+                pyr_level_tma_kernel<<<ctas, PYR_THREADS, pyrt_smem_bytes(), st>>>(a, w.srcMap[l], (int)grid.x, (int)grid.y, frames);
+            } else pyr_level_kernel<false, TH_BATCH><<<grid, PYR_THREADS, smem, st>>>(a);
         }
         launches++;
     }
@@ -483,6 +539,7 @@ int orbx_create(orbx_t** out, int nfeatures, float scaleFactor, int nlevels, int
     if (prop.major != 10) return ORBX_E_NO_DEVICE;       // built for sm_100a only
     CK(cudaSetDevice(device));
     orbx_extractor* e = new orbx_extractor();
+    e->numSMs = prop.multiProcessorCount;
     e->device = device; e->nfeatures = nfeatures; e->nlevels = nlevels; e->iniTh = iniThFAST; e->minTh = minThFAST;
     e->scaleFactor = scaleFactor;
     init_tables(e);

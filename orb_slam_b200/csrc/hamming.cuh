@@ -205,4 +205,33 @@ __global__ void lop3_peak_kernel(unsigned* out, int iters, unsigned seed) {
     if (s == 0xdeadbeefu) out[0] = s;
 }
 
+// The instruction mix of one (query, row) pair of bf2nn_kernel and nothing else - 8 LOP3 xor + 4 carry-save adders (8 LOP3) +
+// 4 POPC + the weighted sum - on register operands, four independent pairs per iteration like the kernel's four queries per
+// thread: the speed of light of that mix on this GPU (no shared-memory reads, no top-2 bookkeeping, no tile loop).
+__global__ void __launch_bounds__(BF_THREADS) mix_peak_kernel(unsigned* out, int iters, unsigned seed) {
+    uint32_t q[4][8], w[8], acc[4] = {0, 0, 0, 0};
+#pragma unroll
+    for (int k = 0; k < 8; k++) {
+        w[k] = seed * (threadIdx.x + 1) + k * 0x9e3779b9u;
+#pragma unroll
+        for (int j = 0; j < 4; j++) q[j][k] = w[k] * (0x85ebca6bu + 2 * j) + j;
+    }
+    for (int i = 0; i < iters; i++) {
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+            const uint32_t x0 = lop_xor(q[j][0], w[0]), x1 = lop_xor(q[j][1], w[1]), x2 = lop_xor(q[j][2], w[2]);
+            const uint32_t x3 = lop_xor(q[j][3], w[3]), x4 = lop_xor(q[j][4], w[4]), x5 = lop_xor(q[j][5], w[5]);
+            const uint32_t x6 = lop_xor(q[j][6], w[6]), x7 = lop_xor(q[j][7], w[7]);
+            const uint32_t s1 = lop_xor3(x0, x1, x2), c1 = lop_maj(x0, x1, x2);
+            const uint32_t s2 = lop_xor3(x3, x4, x5), c2 = lop_maj(x3, x4, x5);
+            const uint32_t s3 = lop_xor3(x6, x7, s1), c3 = lop_maj(x6, x7, s1);
+            const uint32_t t2 = lop_xor3(c1, c2, c3), f4 = lop_maj(c1, c2, c3);
+            acc[j] += (__popc(s2) + __popc(s3)) + ((__popc(t2) + (__popc(f4) << 1)) << 1);
+        }
+#pragma unroll
+        for (int k = 0; k < 8; k++) w[k] += acc[k & 3] + 0x9e3779b9u;      // the next "row" depends on nothing expensive
+    }
+    if ((acc[0] ^ acc[1] ^ acc[2] ^ acc[3]) == 0xdeadbeefu) out[0] = acc[0];
+}
+
 }  // namespace orbm

@@ -250,6 +250,7 @@ static int pipe_peak(orbm_t* m, int which, double* per_s) {
     const int iters = 4096, blocks = m->numSMs * 8, threads = 256;
     auto launch = [&](int it, unsigned seed) {
         if (which == 0) popc_peak_kernel<<<blocks, threads, 0, m->stream>>>((unsigned*)m->out.p, it, seed);
+        else if (which == 2) mix_peak_kernel<<<blocks, threads, 0, m->stream>>>((unsigned*)m->out.p, it, seed);
         else lop3_peak_kernel<<<blocks, threads, 0, m->stream>>>((unsigned*)m->out.p, it, seed);
     };
     launch(64, 1u);
@@ -263,12 +264,13 @@ static int pipe_peak(orbm_t* m, int which, double* per_s) {
         best = std::min(best, ms);
     }
     cudaEventDestroy(e0); cudaEventDestroy(e1);
-    *per_s = (double)blocks * threads * iters * (which == 0 ? 8 : 16) / (best * 1e-3);
+    *per_s = (double)blocks * threads * iters * (which == 0 ? 8 : which == 2 ? 4 : 16) / (best * 1e-3);
     return ORBX_OK;
 }
 
 int orbm_popc_peak(orbm_t* m, double* popc_per_s) { return pipe_peak(m, 0, popc_per_s); }
 int orbm_lop3_peak(orbm_t* m, double* lop3_per_s) { return pipe_peak(m, 1, lop3_per_s); }
+int orbm_pair_mix_peak(orbm_t* m, double* pairs_per_s) { return pipe_peak(m, 2, pairs_per_s); }
 
 }  // extern "C"
 

@@ -84,8 +84,17 @@ __global__ void __launch_bounds__(PYR_THREADS, 4) pyr_level_tma_kernel(const __g
         id.ty = r / tilesX; id.tx = r - id.ty * tilesX;
         return id;
     };
+    // the stride between a CTA's consecutive tiles, decomposed once: advancing is three adds with carries, no division
+    const TileId step = decode((int)gridDim.x);
+    auto advance = [&](TileId id) {
+        id.tx += step.tx; id.ty += step.ty; id.frame += step.frame;
+        if (id.tx >= tilesX) { id.tx -= tilesX; id.ty++; }
+        if (id.ty >= tilesY) { id.ty -= tilesY; id.frame++; }
+        return id;
+    };
     auto request = [&](const TileId& id) {               // one thread: arm the barrier, start the copy of the tile's source box
         const int sx_lo = (int)(a.tileX[id.tx] & 0xffffu), sy_lo = (int)(a.tileY[id.ty] & 0xffffu);
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");     // region A was last written through the generic proxy
         mbar_expect_tx(bar, boxBytes);
         tma_load_3d(smem_u32(S), &srcMap, a.srcX0 + sx_lo, ORB_EDGE + sy_lo, id.frame, bar);
     };
@@ -121,7 +130,7 @@ __global__ void __launch_bounds__(PYR_THREADS, 4) pyr_level_tma_kernel(const __g
         const bool more = tn < total;
         TileId nxt = cur;
         if (more) {
-            nxt = decode(tn);
+            nxt = advance(cur);
             if (tid == 0) request(nxt);
         }
         tile_fast_pass<TH>(a, PA, PB, frame, x0, y0, wid, lane);

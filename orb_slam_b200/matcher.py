@@ -149,6 +149,7 @@ def _bind(L):
     L.orbm_bf2nn.argtypes = [vp, vp, i, vp, sz, C.c_uint32, vp]; L.orbm_bf2nn.restype = i
     L.orbm_popc_peak.argtypes = [vp, C.POINTER(C.c_double)]; L.orbm_popc_peak.restype = i
     L.orbm_lop3_peak.argtypes = [vp, C.POINTER(C.c_double)]; L.orbm_lop3_peak.restype = i
+    L.orbm_pair_mix_peak.argtypes = [vp, C.POINTER(C.c_double)]; L.orbm_pair_mix_peak.restype = i
     L.orbm_nccl_unique_id.argtypes = [vp]; L.orbm_nccl_unique_id.restype = i
     L.orbm_nccl_version.argtypes = [C.POINTER(i)]; L.orbm_nccl_version.restype = i
     L.orbm_shard_create.argtypes = [C.POINTER(vp), vp, vp, i, i]; L.orbm_shard_create.restype = i
@@ -227,6 +228,11 @@ class MatcherContext:
     def popc_peak(self) -> float:
         v = C.c_double()
         check(self._L.orbm_popc_peak(self.h, C.byref(v)), "orbm_popc_peak")
+        return v.value
+
+    def pair_mix_peak(self) -> float:
+        v = C.c_double()
+        check(self._L.orbm_pair_mix_peak(self.h, C.byref(v)), "orbm_pair_mix_peak")
         return v.value
 
     def lop3_peak(self) -> float:
