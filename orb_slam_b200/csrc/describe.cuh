@@ -54,20 +54,21 @@ constexpr int DP_SV = 5;                       // staged row stride in vectors: 
 constexpr int DP_STRIDE = DP_SV * 16;
 constexpr int IP_ROWS = 2 * ORB_HALF_PATCH + 1;   // intensity-centroid disc: 31 rows
 constexpr int IP_VECS = 3;                     // 31 bytes starting anywhere inside a 16-byte vector fit in 3 vectors
-constexpr int DESC_KPW = 4;                    // keypoint slots per warp
-constexpr int DESC_SLOTS_PER_CTA = 8 * DESC_KPW;
+// keypoint slots per warp (template parameter of describe_kernel): 4 or 8 - chosen by the host from the size of the call
 
-__device__ uint32_t g_pattern_s8[256];         // bit_pattern_31_ as [pair k][descriptor byte] -> signed bytes (x0, y0, x1, y1) of test 8*byte + k
+__device__ uint32_t g_pattern_s8[256];         // bit_pattern_31_ as [pair k][descriptor byte] -> bytes (x0, y0, x1, y1) + 16 of test 8*byte + k
 // IC_Angle weights of disc row v = r - 15 (r = 0..30; row 31 is all zero), byte i <-> u = i - 15:
 // [r][0..1] = 1 inside the disc (|u| <= umax[|v|]), [r][2..3] = u + 15 inside the disc
 __device__ uint4 g_icw[32][4];
 
-// byte n of w sign-extended to 32 bits: PRMT with the sign-replicate selector bit (SEL = 0x8880 | n * 0x1111)
+// byte n of w holds a pattern coordinate + 16 (1..31): dropped into the low mantissa byte of 1.5 * 2^23 it reads as the
+// float 12582912 + (coordinate + 16), exactly; one subtraction leaves the coordinate as a float.  PRMT + FADD instead of
+// PRMT + I2F: the conversion unit runs at a quarter of the FP32 rate and was 32 conversions per keypoint and lane.
 template <unsigned SEL>
-__device__ __forceinline__ int sext_byte(uint32_t w) {
-    int r;
-    asm volatile("prmt.b32 %0, %1, %1, %2;" : "=r"(r) : "r"(w), "n"(SEL));     // volatile: keeps the 32 unpacked values out of loop-invariant registers
-    return r;
+__device__ __forceinline__ float coord_f(uint32_t w) {
+    uint32_t r;
+    asm volatile("prmt.b32 %0, %1, %2, %3;" : "=r"(r) : "r"(w), "r"(0x4B400000u), "n"(SEL));   // volatile: keeps the 32 unpacked values out of loop-invariant registers
+    return __fsub_rn(__uint_as_float(r), 12582928.0f);
 }
 
 // rowsum = sum of the row's disc pixels, su = sum of (u + 15) * pixel: 16 DP4A over the 32 bytes that start `sh/8` bytes
@@ -85,10 +86,14 @@ __device__ __forceinline__ void ic_row(const uint32_t (&W)[12], unsigned sh, con
     }
 }
 
+template <int KPW>
 __global__ void __launch_bounds__(256, 4) describe_kernel(DescArgs a) {
-    // A warp walks DESC_KPW consecutive selection slots.  Both patches of a keypoint are staged in shared memory with
-    // aligned, coalesced 128-bit loads (all in flight at once): the blurred patch for the 512 rotated-BRIEF gathers,
-    // the intensity-centroid disc so that every lane can pick up one disc row as three vectors.
+    // A warp owns KPW consecutive selection slots, slot `it` is lane `it`'s: its selection word, output index, moments, angle.
+    //   phase A, slot by slot: the intensity-centroid disc is staged in shared memory with aligned, coalesced 128-bit
+    //            loads so that every lane picks up one disc row as three vectors; the moments go to lane `it`;
+    //   then lanes 0..KPW-1 run fastAtan2 and the sin/cos of their own slot side by side (the only long scalar chain
+    //            of a keypoint: in a batch it costs a warp one pass for 32 keypoints instead of one per keypoint);
+    //   phase B, slot by slot: the blurred patch is staged the same way for the 512 rotated-BRIEF gathers.
     __shared__ uint4 s_icw[32 * 4];
     __shared__ uint4 s_blur[8][DP_ROWS * DP_SV];
     __shared__ uint4 s_img[8][32 * IP_VECS];
@@ -108,60 +113,52 @@ __global__ void __launch_bounds__(256, 4) describe_kernel(DescArgs a) {
         s_img[wid][31 * IP_VECS + 2] = make_uint4(0, 0, 0, 0);
     }
     __syncthreads();
-    const int slot0 = (blockIdx.x * 8 + wid) * DESC_KPW;
-    const int brow = (lane >> 3) + 4 * ((lane >> 2) & 1);     // blurred-patch row (mod 8) this lane stages
-    // test pair k of descriptor byte `lane` as four signed bytes (x0, y0, x1, y1), kept in registers for all slots
-    uint32_t pat[8];
-#pragma unroll
-    for (int k = 0; k < 8; k++) pat[k] = g_pattern_s8[k * 32 + lane];
-    // lane `it` holds the selection word of slot slot0 + it (fetched before the first keypoint needs it)
-    const uint32_t myC = (lane < DESC_KPW && slot0 + lane < a.selTotal) ? a.sel[(size_t)frame * a.selTotal + slot0 + lane] : 0u;
-#pragma unroll 1
-    for (int it = 0; it < DESC_KPW; it++) {
-        const int slot = slot0 + it;
-        if (slot >= a.selTotal) break;                   // warp-uniform
-        int l = 0;
-        while (slot >= a.selOff[l + 1]) l++;
-        const int i = slot - a.selOff[l];
-        if (i >= __shfl_sync(0xffffffffu, myCnt, l)) continue;
-        int before = lane < l ? myCnt : 0;
-#pragma unroll
-        for (int d = 16; d > 0; d >>= 1) before += __shfl_xor_sync(0xffffffffu, before, d);
-        const int outIdx = i + before;
-        if (outIdx >= a.cap) continue;                   // host reports ORBX_E_CAPACITY from nOut
-        const uint32_t c = __shfl_sync(0xffffffffu, myC, it);
-        const int x = (int)(c & 0xfff) + ORB_BORDER_MIN, y = (int)((c >> 12) & 0xfff) + ORB_BORDER_MIN;   // :1021-1022
-        const int pitch = a.pitch[l];
-
-        // ---- loads: rows start 16-byte aligned at interior column 0 and every row has >= 32 bytes behind column w,
-        //      so whole vectors around the patch can be read (keypoints sit >= 19 px inside the level)
-        const int bx0 = (x - ORB_EDGE) & ~15, ix0 = (x - ORB_HALF_PATCH) & ~15;
-        constexpr int NB = (DP_ROWS * DP_VECS + 31) / 32, NI = (IP_ROWS * IP_VECS + 31) / 32;
-        uint4 vb[NB], vi[NI];
-        {
-            const uint8_t* bl = a.blur + (size_t)frame * a.planeFrameStride + a.planeOff[l] + (size_t)(y - ORB_EDGE) * pitch + ORB_XPAD + bx0;
-            // lane -> (row, vector): a quarter-warp holds rows r and r + 4, whose staged vectors (80-byte row stride) fall
-            // into disjoint banks, so the 128-bit shared stores below are conflict-free
-            const uint8_t* p = bl + (size_t)brow * pitch + 16 * (lane & 3);
-#pragma unroll
-            for (int j = 0; j < NB; j++) {               // 8 rows per step
-                vb[j] = (brow + 8 * j < DP_ROWS) ? __ldg((const uint4*)p) : make_uint4(0, 0, 0, 0);
-                p += (size_t)8 * pitch;
-            }
-            const uint8_t* im = a.pyr + (size_t)frame * a.pyrFrameStride + a.pyrOff[l] + (size_t)(ORB_EDGE + y - ORB_HALF_PATCH) * pitch + ORB_XPAD + ix0;
-#pragma unroll
-            for (int j = 0; j < NI; j++) {               // lane t = row t/3, vector t%3
-                const int t = lane + 32 * j, r = t / IP_VECS, v = t - r * IP_VECS;
-                vi[j] = t < IP_ROWS * IP_VECS ? __ldg((const uint4*)(im + (size_t)r * pitch) + v) : make_uint4(0, 0, 0, 0);
-            }
+    const int slot0 = (blockIdx.x * 8 + wid) * KPW;
+    if (slot0 >= a.selTotal) return;                     // warp-uniform, after the only block-wide barrier
+    // ---- this lane's slot: level, index inside the level, output row
+    int myL = 0, myOut = -1;
+    uint32_t myC = 0;
+    {
+        const int slot = slot0 + lane;
+        if (lane < KPW && slot < a.selTotal) {
+            while (slot >= a.selOff[myL + 1]) myL++;
+            myC = a.sel[(size_t)frame * a.selTotal + slot];
         }
+        const int i = slot - a.selOff[myL];
+        int before = 0;                                  // keypoints of the lower levels: sum of their counts
 #pragma unroll
-        for (int j = 0; j < NB; j++) if (brow + 8 * j < DP_ROWS) s_blur[wid][(brow + 8 * j) * DP_SV + (lane & 3)] = vb[j];
+        for (int l = 0; l < ORB_MAX_LEVELS; l++) {
+            const int cl = __shfl_sync(0xffffffffu, myCnt, l);
+            if (l < myL) before += cl;
+        }
+        const int cntL = __shfl_sync(0xffffffffu, myCnt, myL);
+        if (lane < KPW && slot < a.selTotal && i < cntL && i + before < a.cap) myOut = i + before;   // (host reports ORBX_E_CAPACITY from nOut)
+    }
+    const unsigned live = __ballot_sync(0xffffffffu, myOut >= 0);
+    if (!live) return;
+    const int myX = (int)(myC & 0xfff) + ORB_BORDER_MIN, myY = (int)((myC >> 12) & 0xfff) + ORB_BORDER_MIN;   // :1021-1022
+
+    // ---- phase A: IC_Angle moments (:84-128): lane = disc row v + 15; m01 = sum v * rowsum(v), m10 = sum over rows of sum u * pixel
+    int myM10 = 0, myM01 = 0;
+#pragma unroll 1
+    for (int it = 0; it < KPW; it++) {
+        if (!((live >> it) & 1u)) continue;              // warp-uniform
+        const int x = __shfl_sync(0xffffffffu, myX, it), y = __shfl_sync(0xffffffffu, myY, it), l = __shfl_sync(0xffffffffu, myL, it);
+        const int pitch = a.pitch[l];
+        // rows start 16-byte aligned at interior column 0 and every row has >= 32 bytes behind column w, so whole vectors
+        // around the patch can be read (keypoints sit >= 19 px inside the level)
+        const int ix0 = (x - ORB_HALF_PATCH) & ~15;
+        constexpr int NI = (IP_ROWS * IP_VECS + 31) / 32;
+        uint4 vi[NI];
+        const uint8_t* im = a.pyr + (size_t)frame * a.pyrFrameStride + a.pyrOff[l] + (size_t)(ORB_EDGE + y - ORB_HALF_PATCH) * pitch + ORB_XPAD + ix0;
+#pragma unroll
+        for (int j = 0; j < NI; j++) {                   // lane t = row t/3, vector t%3
+            const int t = lane + 32 * j, r = t / IP_VECS, v = t - r * IP_VECS;
+            vi[j] = t < IP_ROWS * IP_VECS ? __ldg((const uint4*)(im + (size_t)r * pitch) + v) : make_uint4(0, 0, 0, 0);
+        }
 #pragma unroll
         for (int j = 0; j < NI; j++) { const int t = lane + 32 * j; if (t < IP_ROWS * IP_VECS) s_img[wid][t] = vi[j]; }
         __syncwarp();
-
-        // ---- IC_Angle (:84-128): lane = disc row v + 15; m01 = sum v * rowsum(v), m10 = sum over rows of sum u * pixel
         int m10, m01;
         {
             uint32_t W[12];
@@ -181,31 +178,64 @@ __global__ void __launch_bounds__(256, 4) describe_kernel(DescArgs a) {
             m10 = (int)su - ORB_HALF_PATCH * (int)rowsum;
             m01 = (lane - ORB_HALF_PATCH) * (int)rowsum;
         }
+        __syncwarp();                                    // the staged disc may be overwritten by the next slot
 #pragma unroll
         for (int d = 16; d > 0; d >>= 1) {
             m10 += __shfl_xor_sync(0xffffffffu, m10, d);
             m01 += __shfl_xor_sync(0xffffffffu, m01, d);
         }
-        const float angle = fast_atan2_deg((float)m01, (float)m10);
+        if (lane == it) { myM10 = m10; myM01 = m01; }
+    }
+    // ---- every live lane: orientation of its own keypoint and the rotation of the test pattern
+    float myAngle = 0.f, myCa = 1.f, mySb = 0.f;
+    if (myOut >= 0) {
+        myAngle = fast_atan2_deg((float)myM01, (float)myM10);
+        const float rad = __fmul_rn(myAngle, (float)(3.1415926535897932384626433832795 / 180.f));   // factorPI, :131
+        double s_, c_;
+        sincos((double)rad, &s_, &c_);                   // correctly-rounded stand-in for glibc cosf/sinf (:148)
+        myCa = (float)c_; mySb = (float)s_;
+    }
+    __syncwarp();
 
-        // ---- rotated BRIEF: lane i produces descriptor byte i (16 pattern points)
-        float ca = 0.f, sb = 0.f;
-        if (lane == 0) {
-            const float rad = __fmul_rn(angle, (float)(3.1415926535897932384626433832795 / 180.f));   // factorPI, :131
-            double s_, c_;
-            sincos((double)rad, &s_, &c_);       // correctly-rounded stand-in for glibc cosf/sinf (:148)
-            ca = (float)c_; sb = (float)s_;
+    // ---- phase B: rotated BRIEF, lane i produces descriptor byte i (16 pattern points)
+    const int brow = (lane >> 3) + 4 * ((lane >> 2) & 1);     // blurred-patch row (mod 8) this lane stages
+    // test pair k of descriptor byte `lane` as four biased bytes (x0, y0, x1, y1) + 16, kept in registers for all slots
+    uint32_t pat[8];
+#pragma unroll
+    for (int k = 0; k < 8; k++) pat[k] = g_pattern_s8[k * 32 + lane];
+#pragma unroll 1
+    for (int it = 0; it < KPW; it++) {
+        if (!((live >> it) & 1u)) continue;              // warp-uniform
+        const int x = __shfl_sync(0xffffffffu, myX, it), y = __shfl_sync(0xffffffffu, myY, it), l = __shfl_sync(0xffffffffu, myL, it);
+        const int outIdx = __shfl_sync(0xffffffffu, myOut, it);
+        const uint32_t c = __shfl_sync(0xffffffffu, myC, it);
+        const float angle = __shfl_sync(0xffffffffu, myAngle, it);
+        const float ca = __shfl_sync(0xffffffffu, myCa, it), sb = __shfl_sync(0xffffffffu, mySb, it);
+        const int pitch = a.pitch[l];
+        const int bx0 = (x - ORB_EDGE) & ~15;
+        constexpr int NB = (DP_ROWS * DP_VECS + 31) / 32;
+        uint4 vb[NB];
+        {
+            const uint8_t* bl = a.blur + (size_t)frame * a.planeFrameStride + a.planeOff[l] + (size_t)(y - ORB_EDGE) * pitch + ORB_XPAD + bx0;
+            // lane -> (row, vector): a quarter-warp holds rows r and r + 4, whose staged vectors (80-byte row stride) fall
+            // into disjoint banks, so the 128-bit shared stores below are conflict-free
+            const uint8_t* p = bl + (size_t)brow * pitch + 16 * (lane & 3);
+#pragma unroll
+            for (int j = 0; j < NB; j++) {               // 8 rows per step
+                vb[j] = (brow + 8 * j < DP_ROWS) ? __ldg((const uint4*)p) : make_uint4(0, 0, 0, 0);
+                p += (size_t)8 * pitch;
+            }
         }
-        ca = __shfl_sync(0xffffffffu, ca, 0);
-        sb = __shfl_sync(0xffffffffu, sb, 0);
+#pragma unroll
+        for (int j = 0; j < NB; j++) if (brow + 8 * j < DP_ROWS) s_blur[wid][(brow + 8 * j) * DP_SV + (lane & 3)] = vb[j];
+        __syncwarp();
         // patch centre, minus the integer image of the rounding constant in both index terms
         const uint8_t* bl = (const uint8_t*)s_blur[wid] + ORB_EDGE * DP_STRIDE + (x - bx0) - (ptrdiff_t)0x4B400000 * (DP_STRIDE + 1);
         int val = 0;
 #pragma unroll
         for (int k = 0; k < 8; k++) {
-            // sign-extending PRMT + int->float per coordinate (|coordinate| <= 15)
-            const float x0 = (float)sext_byte<0x8880>(pat[k]), y0 = (float)sext_byte<0x9991>(pat[k]);
-            const float x1 = (float)sext_byte<0xaaa2>(pat[k]), y1 = (float)sext_byte<0xbbb3>(pat[k]);
+            const float x0 = coord_f<0x7650>(pat[k]), y0 = coord_f<0x7651>(pat[k]);
+            const float x1 = coord_f<0x7652>(pat[k]), y1 = coord_f<0x7653>(pat[k]);
             // cvRound(x*b + y*a), cvRound(x*a - y*b) (:166-168): adding 1.5 * 2^23 leaves the round-to-nearest-even integer
             // in the low mantissa bits (|value| < 2^22), so the conversion stays on the FP32 pipe
             const float MAGIC = 12582912.0f;
@@ -216,7 +246,7 @@ __global__ void __launch_bounds__(256, 4) describe_kernel(DescArgs a) {
             const int t0 = bl[r0 * DP_STRIDE + q0], t1 = bl[r1 * DP_STRIDE + q1];
             val |= (t0 < t1) << k;
         }
-        __syncwarp();                                    // the staged patches may be overwritten by the next slot
+        __syncwarp();                                    // the staged patch may be overwritten by the next slot
         const size_t o = (size_t)frame * a.cap + outIdx;
         a.desc[o * 32 + lane] = (uint8_t)val;
         if (lane < 7) {

@@ -502,7 +502,15 @@ static int enqueue_pipeline(orbx_extractor* e, int wi, const uint8_t* src, size_
         d.scale[l] = v.scale; d.patchSize[l] = v.patchSize;
     }
     d.selOff[g.nlevels] = g.selTotal;
-    describe_kernel<<<dim3((g.selTotal + DESC_SLOTS_PER_CTA - 1) / DESC_SLOTS_PER_CTA, frames), 256, 0, st>>>(d);
+    // slots per warp: 8 in a batch (the per-keypoint scalar chain - atan2, sin/cos - runs once per 8 keypoints), 4 when the call
+    // holds a handful of frames (there the warp's serial chain is the latency).  32 per warp measured no better than 8
+    // (describe 2.12 vs 2.09 ms per 1024 KITTI frames; 2.29 before the per-lane trig) and costs the few-frames case.
+    static const int kpwEnv = [] { const char* v = std::getenv("ORBX_DESC_KPW"); return v ? std::atoi(v) : 0; }();
+    const long slots = (long)frames * g.selTotal;
+    const int kpw = kpwEnv == 4 || kpwEnv == 8 ? kpwEnv : slots >= 148L * 32 * 8 ? 8 : 4;
+    const dim3 dgrid((g.selTotal + 8 * kpw - 1) / (8 * kpw), frames);
+    if (kpw == 8) describe_kernel<8><<<dgrid, 256, 0, st>>>(d);
+    else describe_kernel<4><<<dgrid, 256, 0, st>>>(d);
     launches++;
     if (evs) CK(cudaEventRecord(evs[5], st));
     e->launches += launches;
@@ -562,8 +570,8 @@ int orbx_create(orbx_t** out, int nfeatures, float scaleFactor, int nlevels, int
         static uint32_t pat4[256];
         const signed char* pt = (const signed char*)orb_pattern_31;
         for (int t = 0; t < 256; t++) {
-            const unsigned char* q = (const unsigned char*)(pt + (t & 31) * 32 + (t >> 5) * 4);
-            pat4[t] = (uint32_t)q[0] | ((uint32_t)q[1] << 8) | ((uint32_t)q[2] << 16) | ((uint32_t)q[3] << 24);
+            const signed char* q = pt + (t & 31) * 32 + (t >> 5) * 4;                 // coordinates are in [-13, 13]: stored + 16
+            pat4[t] = (uint32_t)(q[0] + 16) | ((uint32_t)(q[1] + 16) << 8) | ((uint32_t)(q[2] + 16) << 16) | ((uint32_t)(q[3] + 16) << 24);
         }
         rc = cudaMemcpyToSymbol(g_pattern_s8, pat4, sizeof(pat4));
     }
