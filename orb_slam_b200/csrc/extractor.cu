@@ -7,7 +7,10 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <atomic>
+#include <memory>
 #include <mutex>
+#include <thread>
 #include <vector>
 
 #include "../../include/orbx.h"
@@ -857,6 +860,49 @@ int orbx_extract_batch(orbx_t* e, const uint8_t* const* images, int n, int width
         }
         return ORBX_OK;
     };
+    auto pack_chunk = [&](int k) {
+        const int b = k % ORBX_NBUF, f0 = cStart[k], nf = cCount[k];
+        for (int i = 0; i < nf; i++) {
+            uint8_t* dst = e->h_in[b] + (size_t)i * width * height;
+            const uint8_t* srcp = images[f0 + i];
+            if (step == (size_t)width) std::memcpy(dst, srcp, (size_t)width * height);
+            else for (int y = 0; y < height; y++) std::memcpy(dst + (size_t)y * width, srcp + (size_t)y * step, width);
+        }
+    };
+    // Pageable inputs: helper host threads pack the frames of the chunks ahead into the pinned staging buffers (thread t takes
+    // chunks t, t + P, ...) while this thread enqueues chunk k and copies finished results out.  All of it is plain memcpy,
+    // and one thread doing all of it set the pace of the whole call (~12 GB/s).  `done[k]` = chunk k staged, `recorded` =
+    // chunks whose H2D has been enqueued (its event tells a packer when a staging buffer is free again).
+    struct Packer {
+        std::vector<std::thread> th;
+        std::unique_ptr<std::atomic<int>[]> done;
+        std::atomic<int> recorded{0};
+        std::atomic<bool> stop{false};
+        ~Packer() { stop.store(true); for (auto& t : th) if (t.joinable()) t.join(); }
+    } packer;
+    static const int packEnv = [] { const char* v = std::getenv("ORBX_PACK_THREADS"); return v ? std::atoi(v) : -1; }();
+    // Off unless ORBX_PACK_THREADS asks for it: on a 16-core host with one GPU the call is not bound by this thread's copies
+    // once the caller's pages are resident (74.6 k frames/s with 0 helpers, 74.3 / 72.4 / 70.2 with 1 / 2 / 3; pinned: 81.3 k)
+    int nPack = packEnv >= 0 ? packEnv : 0;
+    nPack = std::min(nPack, std::min(ORBX_NBUF, nchunks / 2));
+    const bool usePacker = !inPinned && nPack >= 1;
+    if (usePacker) {
+        packer.done.reset(new std::atomic<int>[nchunks]);
+        for (int k = 0; k < nchunks; k++) packer.done[k].store(0);
+        for (int t = 0; t < nPack; t++)
+            packer.th.emplace_back([&, t] {
+                cudaSetDevice(e->device);
+                for (int k = t; k < nchunks && !packer.stop.load(); k += nPack) {
+                    if (k >= ORBX_NBUF) {                // staging buffer consumed by the H2D of chunk k - ORBX_NBUF?
+                        while (packer.recorded.load(std::memory_order_acquire) <= k - ORBX_NBUF && !packer.stop.load()) std::this_thread::yield();
+                        if (packer.stop.load()) return;
+                        cudaEventSynchronize(e->evIn[k % ORBX_NBUF]);
+                    }
+                    pack_chunk(k);
+                    packer.done[k].store(1, std::memory_order_release);
+                }
+            });
+    }
     int finalized = 0;                          // chunks [0, finalized) are complete on the host
     for (int k = 0; k < nchunks; k++) {
         const int b = k % ORBX_NBUF, f0 = cStart[k], nf = cCount[k];
@@ -883,16 +929,23 @@ int orbx_extract_batch(orbx_t* e, const uint8_t* const* images, int n, int width
                 i = j;
             }
         } else {
-            if (k >= ORBX_NBUF) CK(cudaEventSynchronize(e->evIn[b]));  // staging buffer b consumed by the H2D of chunk k - ORBX_NBUF
-            for (int i = 0; i < nf; i++) {
-                uint8_t* dst = e->h_in[b] + (size_t)i * width * height;
-                const uint8_t* srcp = images[f0 + i];
-                if (step == (size_t)width) std::memcpy(dst, srcp, (size_t)width * height);
-                else for (int y = 0; y < height; y++) std::memcpy(dst + (size_t)y * width, srcp + (size_t)y * step, width);
+            if (usePacker) {
+                // results that are ready are copied out while the packer is still busy with this chunk
+                while (!packer.done[k].load(std::memory_order_acquire)) {
+                    if (status == ORBX_OK && finalized < k && cudaEventQuery(e->evOut[finalized % ORBX_NBUF]) == cudaSuccess) {
+                        rc = finalize(finalized++);
+                        if (rc != ORBX_OK) status = rc;
+                    } else std::this_thread::yield();
+                }
+                if (status != ORBX_OK) break;
+            } else {
+                if (k >= ORBX_NBUF) CK(cudaEventSynchronize(e->evIn[b]));  // staging buffer b consumed by the H2D of chunk k - ORBX_NBUF
+                pack_chunk(k);
             }
             CK(cudaMemcpyAsync(e->d_in[b], e->h_in[b], (size_t)width * height * nf, cudaMemcpyHostToDevice, sIn));
         }
         CK(cudaEventRecord(e->evIn[b], sIn));
+        packer.recorded.store(k + 1, std::memory_order_release);
         mark(k, 1, sIn);
         // ---- compute stream: needs the input, and d_res[b] drained by the copy-out of chunk k - ORBX_NBUF
         if (nchunks > 1) CK(cudaStreamWaitEvent(cst, e->evIn[b], 0));
