@@ -743,7 +743,14 @@ extern "C" int orbm_search_for_initialization_batch_device(orbm_t* m, const orbx
     a.windowSize = (float)windowSize; a.nnratio = nnratio; a.checkOri = checkOri; a.prev = d_prev;
     a.matchedDistance = (int32_t*)m->w3.p; a.matches21 = (int32_t*)m->w4.p; a.bins = (uint8_t*)m->w5.p;
     a.matches12 = d_matches12; a.nmatches = d_nmatches;
-    init_match_batch_kernel<<<(npairs + 3) / 4, 128, 0, m->stream>>>(a);
+    static const bool noTeam = std::getenv("ORBM_NO_TEAM") != nullptr;
+    if (cap <= INIT_TEAM_MAX_CAP && !noTeam) {               // one block per pair: enumerator warps + one resolver warp
+        const size_t smem = init_team_smem(cap);
+        CKM(cudaFuncSetAttribute(init_match_team_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        init_match_team_kernel<<<npairs, (INIT_TEAM + 1) * 32, smem, m->stream>>>(a);
+    } else {
+        init_match_batch_kernel<<<(npairs + 3) / 4, 128, 0, m->stream>>>(a);
+    }
     CKM(cudaGetLastError());
     return ORBX_OK;
 }
