@@ -27,6 +27,7 @@ struct CellArgs {
     int nlevels;
     int iniTh, minTh;                 // the plane stores max(0, score + 1 - minTh)
     int totalCells;                   // per frame
+    int cellBegin, cellEnd;           // cells this launch handles (a level range): [cellBegin, cellEnd)
     // per level
     int cellOff[ORB_MAX_LEVELS + 1];
     int nCols[ORB_MAX_LEVELS], wCell[ORB_MAX_LEVELS], hCell[ORB_MAX_LEVELS];
@@ -181,9 +182,9 @@ __device__ __forceinline__ void cell_scan(const CellArgs& a, const uint8_t* __re
 __global__ void __launch_bounds__(256, 5) cell_nms_kernel(CellArgs a) {
     __shared__ unsigned s_masks[8][2][2][CELL_MASK_ROWS];
     const int lane = threadIdx.x & 31;
-    const int cell = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    const int cell = a.cellBegin + blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     const int frame = blockIdx.y;
-    if (cell >= a.totalCells) return;
+    if (cell >= a.cellEnd) return;
     unsigned (*masks)[2][CELL_MASK_ROWS] = s_masks[threadIdx.x >> 5];
     int l = 0;
     while (cell >= a.cellOff[l + 1]) l++;

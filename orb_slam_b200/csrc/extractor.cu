@@ -69,6 +69,9 @@ struct orbx_extractor {
         // TMA descriptors of the bordered planes of levels 0..n-2 (the sources of levels 1..n-1), see pyramid_tma.cuh
         CUtensorMap srcMap[ORB_MAX_LEVELS];
         bool tma[ORB_MAX_LEVELS] = {};
+        // side streams of the few-frames schedule (level 0's NMS + quadtree; the border kernel) and their fork / join events
+        cudaStream_t sB = nullptr, sC = nullptr;
+        cudaEvent_t evL0 = nullptr, evK1 = nullptr, evB = nullptr, evC = nullptr;
     } ws[ORBX_NWS];
     int numSMs = 148;
     int lastWs = 0;                          // workspace holding the most recent frames (introspection, stereo)
@@ -385,10 +388,81 @@ static int enqueue_pipeline(orbx_extractor* e, int wi, const uint8_t* src, size_
     cudaStream_t st = w.stream;
     int launches = 0;
     if (evs) CK(cudaEventRecord(evs[0], st));
+    // ---- argument blocks of the stages behind the pyramid
+    BorderArgs b{};
+    int borderGroups = 0;
+    {
+        b.pyr = w.d_pyr; b.pyrFrameStride = g.pyrBytes; b.nlevels = g.nlevels;
+        for (int l = 0; l < g.nlevels; l++) {
+            const LevelGeom& v = g.lv[l];
+            b.grpOff[l] = borderGroups;
+            borderGroups += (v.h + 2 * ORB_EDGE + BORDER_ROWS - 1) / BORDER_ROWS;
+            b.pyrOff[l] = v.pyrOff; b.w[l] = v.w; b.h[l] = v.h; b.pitch[l] = v.pitch;
+        }
+        b.grpOff[g.nlevels] = borderGroups;
+    }
+    CellArgs c{};
+    c.score = w.d_score; c.planeFrameStride = g.planeBytes; c.nlevels = g.nlevels; c.iniTh = g.iniTh; c.minTh = g.minTh;
+    c.totalCells = g.totalCells;
+    for (int l = 0; l < g.nlevels; l++) {
+        const LevelGeom& v = g.lv[l];
+        c.cellOff[l] = v.cellOff; c.nCols[l] = std::max(v.nCols, 1); c.wCell[l] = v.wCell; c.hCell[l] = v.hCell;
+        c.maxBX[l] = v.maxBorderX; c.maxBY[l] = v.maxBorderY; c.pitch[l] = v.pitch;
+        c.planeOff[l] = v.planeOff; c.slotOff[l] = v.slotOff; c.slotCap[l] = v.slotCap;
+    }
+    c.cellOff[g.nlevels] = g.totalCells;
+    c.slotFrameStride = g.slotTotal;
+    c.cellCount = w.d_cellCount; c.slots = w.d_slots; c.err = d_err;
+    QtArgs q{};
+    q.cand = w.d_cand; q.candFrameStride = g.candTotal; q.candCount = w.d_candCount;
+    q.cellCount = w.d_cellCount; q.cellOffs = w.d_cellOffs; q.slots = w.d_slots; q.slotFrameStride = g.slotTotal;
+    q.totalCells = g.totalCells;
+    q.keyA = w.d_keyA; q.keyB = w.d_keyB; q.valA = w.d_valA; q.valB = w.d_valB;
+    q.sel = w.d_sel; q.selCount = w.d_selCount; q.err = d_err;
+    q.nlevels = g.nlevels; q.selTotal = g.selTotal; q.nodeCap = g.nodeCap;
+    for (int l = 0; l < g.nlevels; l++) {
+        const LevelGeom& v = g.lv[l];
+        q.candOff[l] = v.candOff; q.N[l] = v.N; q.nIni[l] = v.nIni; q.qH[l] = v.qH; q.depth[l] = v.depth;
+        q.maxSel[l] = v.maxSel; q.selOff[l] = v.selOff; q.hX[l] = v.hX;
+        q.cellOff[l] = v.cellOff; q.slotOff[l] = v.slotOff; q.slotCap[l] = v.slotCap; q.candCap[l] = v.candCap;
+    }
+    q.cellOff[g.nlevels] = g.totalCells;
+    auto launch_border = [&](cudaStream_t s_) {
+        border_kernel<<<dim3((borderGroups + 7) / 8, frames), 256, 0, s_>>>(b);
+        launches++;
+    };
+    auto launch_nms = [&](cudaStream_t s_, int l0, int l1) {          // the cells of levels [l0, l1)
+        CellArgs cc = c;
+        cc.cellBegin = c.cellOff[l0]; cc.cellEnd = c.cellOff[l1];
+        if (cc.cellEnd > cc.cellBegin) {
+            cell_nms_kernel<<<dim3((cc.cellEnd - cc.cellBegin + 7) / 8, frames), 256, 0, s_>>>(cc);
+            launches++;
+        }
+    };
+    auto launch_qt = [&](cudaStream_t s_, int l0, int l1) {           // one block per (frame, level in [l0, l1))
+        QtArgs qq = q;
+        qq.levelBegin = l0;
+        // many frames: small blocks (throughput); a handful of frames: the level-0 block is the critical path, give it more threads
+        if (frames * g.nlevels >= 2 * 148) {
+            qq.keyCap = 0;
+            quadtree_kernel<QT_THREADS_BATCH><<<dim3(frames, l1 - l0), QT_THREADS_BATCH, qt_smem_bytes(g.nodeCap, QT_THREADS_BATCH), s_>>>(qq);
+        } else {
+            qq.keyCap = QT_KEYS_SMEM;            // one block per SM at most: the sort arrays live in shared memory
+            quadtree_kernel<QT_THREADS_LATENCY><<<dim3(frames, l1 - l0), QT_THREADS_LATENCY,
+                                                  qt_smem_bytes(g.nodeCap, QT_THREADS_LATENCY) + (size_t)QT_KEYS_SMEM * 16, s_>>>(qq);
+        }
+        launches++;
+    };
     // 1. pyramid + blur + FAST score, level by level (level l reads level l-1).  A handful of frames: the eight dependent
     //    launches are the critical path and none of them fills the GPU - tiles of half the height halve the serial work
     //    of a CTA and double the CTAs
     const bool lowTiles = frames <= PYR_LATENCY_FRAMES;
+    // A handful of frames: the dependent chain K1 x 8 -> border -> NMS -> quadtree -> describe is the latency.  Level 0's NMS
+    // and quadtree (the longest quadtree block by far) do not need levels 1..7: they start on a side stream as soon as K1's
+    // level 0 is done and run beside the remaining levels; the border kernel runs beside the quadtree.  Both join before
+    // describe_kernel.  (Captured into the single-frame CUDA graph like any other cross-stream dependency.)
+    static const bool noBranch = std::getenv("ORBX_NO_BRANCH") != nullptr;
+    const bool branch = lowTiles && !evs && g.nlevels >= 2 && !noBranch;
     const int TH = lowTiles ? TH_LATENCY : TH_BATCH;
     for (int l = 0; l < g.nlevels; l++) {
         const LevelGeom& v = g.lv[l];
@@ -432,67 +506,35 @@ static int enqueue_pipeline(orbx_extractor* e, int wi, const uint8_t* src, size_
             } else pyr_level_kernel<false, TH_BATCH><<<grid, PYR_THREADS, smem, st>>>(a);
         }
         launches++;
+        if (branch && l == 0) {
+            CK(cudaEventRecord(w.evL0, st));
+            CK(cudaStreamWaitEvent(w.sB, w.evL0, 0));
+            launch_nms(w.sB, 0, 1);
+            launch_qt(w.sB, 0, 1);
+            CK(cudaEventRecord(w.evB, w.sB));
+        }
     }
     if (evs) CK(cudaEventRecord(evs[1], st));
-    // 2. REFLECT_101 frames
-    {
-        BorderArgs b{};
-        b.pyr = w.d_pyr; b.pyrFrameStride = g.pyrBytes; b.nlevels = g.nlevels;
-        int off = 0;
-        for (int l = 0; l < g.nlevels; l++) {
-            const LevelGeom& v = g.lv[l];
-            b.grpOff[l] = off;
-            off += (v.h + 2 * ORB_EDGE + BORDER_ROWS - 1) / BORDER_ROWS;
-            b.pyrOff[l] = v.pyrOff; b.w[l] = v.w; b.h[l] = v.h; b.pitch[l] = v.pitch;
-        }
-        b.grpOff[g.nlevels] = off;
-        border_kernel<<<dim3((off + 7) / 8, frames), 256, 0, st>>>(b);
-        launches++;
-    }
-    if (evs) CK(cudaEventRecord(evs[2], st));
-    // 3. per-cell NMS + threshold fallback -> per-cell survivor lists (one launch, score plane read once)
-    CellArgs c{};
-    c.score = w.d_score; c.planeFrameStride = g.planeBytes; c.nlevels = g.nlevels; c.iniTh = g.iniTh; c.minTh = g.minTh;
-    c.totalCells = g.totalCells;
-    for (int l = 0; l < g.nlevels; l++) {
-        const LevelGeom& v = g.lv[l];
-        c.cellOff[l] = v.cellOff; c.nCols[l] = std::max(v.nCols, 1); c.wCell[l] = v.wCell; c.hCell[l] = v.hCell;
-        c.maxBX[l] = v.maxBorderX; c.maxBY[l] = v.maxBorderY; c.pitch[l] = v.pitch;
-        c.planeOff[l] = v.planeOff; c.slotOff[l] = v.slotOff; c.slotCap[l] = v.slotCap;
-    }
-    c.cellOff[g.nlevels] = g.totalCells;
-    c.slotFrameStride = g.slotTotal;
-    c.cellCount = w.d_cellCount; c.slots = w.d_slots; c.err = d_err;
-    if (g.totalCells > 0) {
-        cell_nms_kernel<<<dim3((g.totalCells + 7) / 8, frames), 256, 0, st>>>(c);
-        launches++;
-    }
-    if (evs) CK(cudaEventRecord(evs[3], st));
-    // 4. quadtree distribution (gathers the cell lists into vToDistributeKeys first)
-    QtArgs q{};
-    q.cand = w.d_cand; q.candFrameStride = g.candTotal; q.candCount = w.d_candCount;
-    q.cellCount = w.d_cellCount; q.cellOffs = w.d_cellOffs; q.slots = w.d_slots; q.slotFrameStride = g.slotTotal;
-    q.totalCells = g.totalCells;
-    q.keyA = w.d_keyA; q.keyB = w.d_keyB; q.valA = w.d_valA; q.valB = w.d_valB;
-    q.sel = w.d_sel; q.selCount = w.d_selCount; q.err = d_err;
-    q.nlevels = g.nlevels; q.selTotal = g.selTotal; q.nodeCap = g.nodeCap;
-    for (int l = 0; l < g.nlevels; l++) {
-        const LevelGeom& v = g.lv[l];
-        q.candOff[l] = v.candOff; q.N[l] = v.N; q.nIni[l] = v.nIni; q.qH[l] = v.qH; q.depth[l] = v.depth;
-        q.maxSel[l] = v.maxSel; q.selOff[l] = v.selOff; q.hX[l] = v.hX;
-        q.cellOff[l] = v.cellOff; q.slotOff[l] = v.slotOff; q.slotCap[l] = v.slotCap; q.candCap[l] = v.candCap;
-    }
-    q.cellOff[g.nlevels] = g.totalCells;
-    // many frames: small blocks (throughput); a handful of frames: the level-0 block is the critical path, give it more threads
-    if (frames * g.nlevels >= 2 * 148) {
-        q.keyCap = 0;
-        quadtree_kernel<QT_THREADS_BATCH><<<dim3(frames, g.nlevels), QT_THREADS_BATCH, qt_smem_bytes(g.nodeCap, QT_THREADS_BATCH), st>>>(q);
+    if (branch) {
+        // levels 1.. on the main stream; the REFLECT_101 frames (only the descriptors' stage reads them) beside them
+        CK(cudaEventRecord(w.evK1, st));
+        CK(cudaStreamWaitEvent(w.sC, w.evK1, 0));
+        launch_border(w.sC);
+        CK(cudaEventRecord(w.evC, w.sC));
+        launch_nms(st, 1, g.nlevels);
+        launch_qt(st, 1, g.nlevels);
+        CK(cudaStreamWaitEvent(st, w.evB, 0));
+        CK(cudaStreamWaitEvent(st, w.evC, 0));
     } else {
-        q.keyCap = QT_KEYS_SMEM;                 // one block per SM at most: the sort arrays live in shared memory
-        quadtree_kernel<QT_THREADS_LATENCY><<<dim3(frames, g.nlevels), QT_THREADS_LATENCY,
-                                              qt_smem_bytes(g.nodeCap, QT_THREADS_LATENCY) + (size_t)QT_KEYS_SMEM * 16, st>>>(q);
+        // 2. REFLECT_101 frames
+        launch_border(st);
+        if (evs) CK(cudaEventRecord(evs[2], st));
+        // 3. per-cell NMS + threshold fallback -> per-cell survivor lists (one launch, score plane read once)
+        launch_nms(st, 0, g.nlevels);
+        if (evs) CK(cudaEventRecord(evs[3], st));
+        // 4. quadtree distribution (gathers the cell lists into vToDistributeKeys first)
+        launch_qt(st, 0, g.nlevels);
     }
-    launches++;
     if (evs) CK(cudaEventRecord(evs[4], st));
     // 5. orientation, descriptors, output assembly
     DescArgs d{};
@@ -557,6 +599,13 @@ int orbx_create(orbx_t** out, int nfeatures, float scaleFactor, int nlevels, int
     cudaError_t rc = cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking);
     e->ws[0].stream = e->stream;
     for (int wi = 1; wi < ORBX_NWS && rc == cudaSuccess; wi++) rc = cudaStreamCreateWithFlags(&e->ws[wi].stream, cudaStreamNonBlocking);
+    for (int wi = 0; wi < ORBX_NWS && rc == cudaSuccess; wi++) {
+        orbx_extractor::Workspace& w = e->ws[wi];
+        rc = cudaStreamCreateWithFlags(&w.sB, cudaStreamNonBlocking);
+        if (rc == cudaSuccess) rc = cudaStreamCreateWithFlags(&w.sC, cudaStreamNonBlocking);
+        for (cudaEvent_t* ev : {&w.evL0, &w.evK1, &w.evB, &w.evC})
+            if (rc == cudaSuccess) rc = cudaEventCreateWithFlags(ev, cudaEventDisableTiming);
+    }
     if (rc == cudaSuccess) rc = cudaEventCreateWithFlags(&e->evFork, cudaEventDisableTiming);
     for (int wi = 0; wi < ORBX_NWS && rc == cudaSuccess; wi++) rc = cudaEventCreateWithFlags(&e->evJoin[wi], cudaEventDisableTiming);
     if (rc == cudaSuccess) rc = cudaStreamCreateWithFlags(&e->sIn, cudaStreamNonBlocking);
@@ -609,6 +658,11 @@ void orbx_destroy(orbx_t* e) {
     for (int hlf = 0; hlf < 2; hlf++) for (int i = 0; i < 8; i++) if (e->ev[hlf][i]) cudaEventDestroy(e->ev[hlf][i]);
     if (e->evFork) cudaEventDestroy(e->evFork);
     for (auto& ev : e->evJoin) if (ev) cudaEventDestroy(ev);
+    for (auto& w : e->ws) {
+        if (w.sB) { cudaStreamSynchronize(w.sB); cudaStreamDestroy(w.sB); }
+        if (w.sC) { cudaStreamSynchronize(w.sC); cudaStreamDestroy(w.sC); }
+        for (cudaEvent_t ev : {w.evL0, w.evK1, w.evB, w.evC}) if (ev) cudaEventDestroy(ev);
+    }
     for (int wi = 1; wi < ORBX_NWS; wi++) if (e->ws[wi].stream) cudaStreamDestroy(e->ws[wi].stream);
     for (int b = 0; b < ORBX_NBUF; b++) {
         cudaFree(e->d_in[b]);

@@ -58,7 +58,7 @@ __global__ void __launch_bounds__(NT) quadtree_kernel(QtArgs a) {
     QT_MARK(0);
     extern __shared__ __align__(16) uint8_t qsm[];
     const int tid = threadIdx.x;
-    const int l = blockIdx.y, frame = blockIdx.x;        // level-major launch order: the long level-0 blocks start first
+    const int l = a.levelBegin + blockIdx.y, frame = blockIdx.x;   // level-major launch order: the long level-0 blocks start first
     const int cap = a.nodeCap;
     QtSmem s;
     {
