@@ -32,7 +32,12 @@ def extract_on_device(ex, frames):
 
 @pytest.mark.parametrize("w,h,nf,nframes,win,ratio,ori,use_prev,use_pairs",
                          [(752, 480, 1000, 12, 100, 0.9, True, False, False), (752, 480, 1000, 6, 30, 0.6, True, True, False),
-                          (640, 480, 500, 5, 100, 0.9, False, False, True), (1241, 376, 2000, 4, 50, 0.8, True, True, True)])
+                          (640, 480, 500, 5, 100, 0.9, False, False, True), (1241, 376, 2000, 4, 50, 0.8, True, True, True),
+                          # ~870 level-0 key points and a window that covers the image: every query has more candidates than a
+                          # shared-memory list of the one-block-per-pair kernel holds (its resolver re-enumerates them)
+                          (752, 480, 4000, 4, 400, 0.9, True, False, False),
+                          # more key points per frame than the one-block-per-pair kernel's shared-memory state takes: one-warp kernel
+                          (752, 480, 9000, 3, 40, 0.9, True, True, False)])
 def test_batch_matches_oracle_pair_by_pair(w, h, nf, nframes, win, ratio, ori, use_prev, use_pairs):
     import torch
     from orb_slam_b200 import KEYPOINT_DTYPE, ORBextractor
@@ -77,6 +82,7 @@ def test_batch_matches_oracle_pair_by_pair(w, h, nf, nframes, win, ratio, ori, u
             assert np.array_equal(prev_out[p, :n_h[f1]], prev), p
         total += n_o
     assert total > 20 * npairs or win < 100
+    assert nf != 9000 or cap > 4096                       # (the case meant for the one-warp kernel really takes it)
     ex.close(); ctx.close()
 
 
