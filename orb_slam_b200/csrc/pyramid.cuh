@@ -105,27 +105,32 @@ __device__ __forceinline__ uint32_t fast_score_pair(const uint32_t (&P)[16], uin
 }
 
 // FAST score of the 4 pixels of group `g` on tile row r (0..TH-1), from the pair planes of the 7 tile rows r..r+6
-// (PA[row][g] = {x1, em, om, x2}, PB[row][g] = {ol, x4, x3, er}: each row's stride-2 pixel pairs are split out of
-// the level tile once, by the row pass, instead of once per ring row that needs them).
+// (PA[row][g] = {x1, x2, em, om}, PB[row][g] = {x4, x3, ol, er}: each row's stride-2 pixel pairs are split out of
+// the level tile once, by the row pass, instead of once per ring row that needs them).  The field order puts what the ring
+// rows dy = +-2 need (x1, x2 / x4, x3) and what the centre row needs of PA (em, om) into one 64-bit half each, so five of the
+// twelve reads are 64-bit: 30 shared-memory wavefronts per warp and row instead of 48 - the kernel's L1 data pipe is as busy
+// as its ALU pipe (64 % against 70 %, profiles/r2n_ncu_full_b512.md), and two thirds of its shared-memory reads are these.
 // Result: four bytes (pixel order) of max(0, score + 1 - minTh) - the score plane's encoding.
 __device__ __forceinline__ uint32_t fast_score4(const uint4* __restrict__ PA, const uint4* __restrict__ PB, int r, int g, int minTh) {
     const uint4* a = PA + r * 32 + g;
     const uint4* b = PB + r * 32 + g;
-    const uint4 a0 = a[0], a6 = a[6 * 32];                       // dy = -3, +3: x1 em om x2
-    const uint4 a1 = a[32], b1 = b[32], a5 = a[5 * 32], b5 = b[5 * 32];      // dy = -2, +2: x3 x2 x1 x4
-    const uint4 b2 = b[2 * 32], b4 = b[4 * 32];                  // dy = -1, +1: ol x4 x3 er
-    const uint4 a3 = a[3 * 32], b3 = b[3 * 32];                  // centre row: ol x4 x3 er + em om
+    const uint4 a0 = a[0], a6 = a[6 * 32];                       // dy = -3, +3: x1 x2 em om
+    const uint2 a1 = *(const uint2*)(a + 32), a5 = *(const uint2*)(a + 5 * 32);      // dy = -2, +2: x1 x2 ...
+    const uint2 b1 = *(const uint2*)(b + 32), b5 = *(const uint2*)(b + 5 * 32);      //              ... x4 x3
+    const uint4 b2 = b[2 * 32], b4 = b[4 * 32];                  // dy = -1, +1: x4 x3 ol er
+    const uint4 b3 = b[3 * 32];                                  // centre row: x4 x3 ol er
+    const uint2 a3 = *((const uint2*)(a + 3 * 32) + 1);          //           + em om
     // ring k -> (dx,dy): 0:(0,3) 1:(1,3) 2:(2,2) 3:(3,1) 4:(3,0) 5:(3,-1) 6:(2,-2) 7:(1,-3) 8:(0,-3) 9:(-1,-3)
     //                    10:(-2,-2) 11:(-3,-1) 12:(-3,0) 13:(-3,1) 14:(-2,2) 15:(-1,3)
     // pair A = pixels (c, c+2): offset dx -> -3:ol -2:x3 -1:x1 0:em 1:om 2:x2 3:x4
     // pair B = pixels (c+1, c+3):          -3:x3 -2:x1 -1:em 0:om 1:x2 2:x4 3:er
-    // uint4 fields: PA = (x: x1, y: em, z: om, w: x2), PB = (x: ol, y: x4, z: x3, w: er)
-    const uint32_t PAr[16] = {a6.y, a6.z, a5.w, b4.y, b3.y, b2.y, a1.w, a0.z,
-                              a0.y, a0.x, b1.z, b2.x, b3.x, b4.x, b5.z, a6.x};
-    const uint32_t PBr[16] = {a6.z, a6.w, b5.y, b4.w, b3.w, b2.w, b1.y, a0.w,
-                              a0.z, a0.y, a1.x, b2.z, b3.z, b4.z, a5.x, a6.y};
-    const uint32_t tA = fast_score_pair(PAr, a3.y);
-    const uint32_t tB = fast_score_pair(PBr, a3.z);
+    // fields: PA = (x: x1, y: x2, z: em, w: om), PB = (x: x4, y: x3, z: ol, w: er)
+    const uint32_t PAr[16] = {a6.z, a6.w, a5.y, b4.x, b3.x, b2.x, a1.y, a0.w,
+                              a0.z, a0.x, b1.y, b2.z, b3.z, b4.z, b5.y, a6.x};
+    const uint32_t PBr[16] = {a6.w, a6.y, b5.x, b4.w, b3.w, b2.w, b1.x, a0.y,
+                              a0.w, a0.z, a1.x, b2.y, b3.y, b4.y, a5.x, a6.z};
+    const uint32_t tA = fast_score_pair(PAr, a3.x);
+    const uint32_t tB = fast_score_pair(PBr, a3.y);
     // lanes hold score + 257; the plane stores max(0, score + 1 - minTh): 0 <=> not a corner at minTh
     const uint32_t D = 0x01000100u + (uint32_t)minTh * 0x00010001u;
     const uint32_t uA = __vmaxu2(tA, D) - D, uB = __vmaxu2(tB, D) - D;
@@ -188,8 +193,8 @@ __device__ __forceinline__ void tile_row_pass(const uint8_t* __restrict__ T, uns
     const int rEnd = min(TROWS, h + 2 * HALO - y0);       // rows below the image + halo feed nothing that is stored
     for (int r = wid; r < rEnd; r += PYR_THREADS / 32) {
         const RowPairs p = row_pairs((const uint32_t*)(T + r * TS) + lane);
-        PA[r * 32 + lane] = make_uint4(p.x1, p.em, p.om, p.x2);
-        PB[r * 32 + lane] = make_uint4(p.ol, p.x4, p.x3, p.er);
+        PA[r * 32 + lane] = make_uint4(p.x1, p.x2, p.em, p.om);
+        PB[r * 32 + lane] = make_uint4(p.x4, p.x3, p.ol, p.er);
         uint32_t A, B;
         hblur4(p, A, B);
         *(uint2*)(Hs + r * TW + 4 * lane) = make_uint2(A, B);
