@@ -65,6 +65,7 @@ struct orbx_extractor {
         uint32_t *d_cellCount = nullptr, *d_cellOffs = nullptr, *d_cand = nullptr, *d_slots = nullptr;
         uint32_t *d_keyA = nullptr, *d_keyB = nullptr, *d_valA = nullptr, *d_valB = nullptr, *d_sel = nullptr;
         int *d_candCount = nullptr, *d_selCount = nullptr;
+        int* d_qtTotals = nullptr;               // digit totals exchanged by the clusters of qt_presort_kernel
         int lastFrames = 0;
         // TMA descriptors of the bordered planes of levels 0..n-2 (the sources of levels 1..n-1), see pyramid_tma.cuh
         CUtensorMap srcMap[ORB_MAX_LEVELS];
@@ -233,6 +234,16 @@ static int build_geometry(orbx_extractor* e, int width, int height, FrameGeom& g
         v.patchSize = (float)(int)(31 * e->sf[l]);                       // :1013
     }
     g.totalCells = cellOff; g.selTotal = selOff;
+    // Large levels (tens of thousands of candidates): steps 0-2 of the quadtree stage run on a cluster of CTAs per (frame, level)
+    // (quadtree_presort.cuh).  Level sizes decrease, so the large ones are levels 0 .. presortLevels - 1.
+    static const bool noPresort = std::getenv("ORBX_NO_PRESORT") != nullptr;
+    g.presortLevels = 0; g.presortMaxCells = 0;
+    for (int l = 0; l < L && !noPresort; l++) {
+        if ((long)g.lv[l].w * g.lv[l].h < 600000L || g.lv[l].nCols == 0) break;
+        g.presortLevels = l + 1;
+        g.presortMaxCells = std::max(g.presortMaxCells, g.lv[l].nCols * g.lv[l].nRows);
+    }
+    if (qtp_smem_bytes(g.presortMaxCells) > 200 * 1024) { g.presortLevels = 0; g.presortMaxCells = 0; }
     g.pyrBytes = (pyrOff + 255) & ~255ULL; g.planeBytes = (planeOff + 255) & ~255ULL;
     g.candTotal = (candOff + 63) & ~63ULL;
     g.slotTotal = (slotOff + 63) & ~63ULL;
@@ -250,7 +261,7 @@ static void free_workspace(orbx_extractor* e) {
         cudaFree(w.d_pyr); cudaFree(w.d_blur); cudaFree(w.d_score);
         cudaFree(w.d_cellCount); cudaFree(w.d_cellOffs); cudaFree(w.d_cand); cudaFree(w.d_slots);
         cudaFree(w.d_keyA); cudaFree(w.d_keyB); cudaFree(w.d_valA); cudaFree(w.d_valB); cudaFree(w.d_sel);
-        cudaFree(w.d_candCount); cudaFree(w.d_selCount);
+        cudaFree(w.d_candCount); cudaFree(w.d_selCount); cudaFree(w.d_qtTotals); w.d_qtTotals = nullptr;
         w.d_pyr = w.d_blur = w.d_score = nullptr;
         w.d_cellCount = w.d_cellOffs = w.d_cand = w.d_slots = w.d_keyA = w.d_keyB = w.d_valA = w.d_valB = w.d_sel = nullptr;
         w.d_candCount = w.d_selCount = nullptr; w.lastFrames = 0;
@@ -352,6 +363,7 @@ static int ensure_workspace(orbx_extractor* e, int width, int height, int frames
         CK(cudaMalloc(&w.d_sel, (size_t)g.selTotal * F * 4));
         CK(cudaMalloc(&w.d_candCount, F * g.nlevels * 4));
         CK(cudaMalloc(&w.d_selCount, F * g.nlevels * 4));
+        if (g.presortLevels > 0) CK(cudaMalloc(&w.d_qtTotals, F * g.presortLevels * QTP_CTAS * 256 * sizeof(int)));
         build_tensor_maps(e, w, newCap);
     }
     e->resBytes = res_bytes(g, newCap);
@@ -369,6 +381,8 @@ static int ensure_workspace(orbx_extractor* e, int width, int height, int frames
     CK(cudaFuncSetAttribute(pyr_level_kernel<false, TH_LATENCY>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
     CK(cudaFuncSetAttribute(pyr_level_kernel<true, TH_LATENCY>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
     CK(cudaFuncSetAttribute(pyr_level_tma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pyrt_smem_bytes()));
+    if (g.presortLevels > 0)
+        CK(cudaFuncSetAttribute(qt_presort_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)qtp_smem_bytes(g.presortMaxCells)));
     return ORBX_OK;
 }
 
@@ -442,6 +456,26 @@ static int enqueue_pipeline(orbx_extractor* e, int wi, const uint8_t* src, size_
     auto launch_qt = [&](cudaStream_t s_, int l0, int l1) {           // one block per (frame, level in [l0, l1))
         QtArgs qq = q;
         qq.levelBegin = l0;
+        qq.presortMask = 0;
+        const int pre1 = std::min(l1, g.presortLevels);
+        // Large levels, and few enough (frame, level) pairs that one CTA each leaves most of the GPU idle: gather + path codes +
+        // radix sort on a cluster of eight CTAs per pair.  Measured: 16 x 3840x2160 (8 frames per stream): quadtree stage 2.19 ->
+        // 0.85 ms; 64 x 1920x1080 (32 per stream, 256 pairs): 0.62 -> 0.91 ms - there the pairs already fill the SMs.
+        if (pre1 > l0 && w.d_qtTotals && frames * g.nlevels <= e->numSMs) {
+            QtPresortArgs pa{};
+            pa.q = q; pa.q.levelBegin = l0; pa.levelBegin = l0; pa.totals = w.d_qtTotals; pa.maxCells = g.presortMaxCells;
+            cudaLaunchConfig_t cfg{};
+            cfg.gridDim = dim3(QTP_CTAS * frames, pre1 - l0); cfg.blockDim = dim3(QTP_THREADS);
+            cfg.dynamicSmemBytes = qtp_smem_bytes(g.presortMaxCells); cfg.stream = s_;
+            cudaLaunchAttribute at[1];
+            at[0].id = cudaLaunchAttributeClusterDimension;
+            at[0].val.clusterDim.x = QTP_CTAS; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+            cfg.attrs = at; cfg.numAttrs = 1;
+            if (cudaLaunchKernelEx(&cfg, qt_presort_kernel, pa) == cudaSuccess) {
+                for (int l = l0; l < pre1; l++) qq.presortMask |= 1u << l;
+                launches++;
+            } else cudaGetLastError();           // (cluster launch refused: the single-CTA path does the whole level)
+        }
         // many frames: small blocks (throughput); a handful of frames: the level-0 block is the critical path, give it more threads
         if (frames * g.nlevels >= 2 * 148) {
             qq.keyCap = 0;

@@ -56,6 +56,8 @@ struct FrameGeom {
     unsigned long long candTotal;    // candidate elements per frame
     unsigned long long slotTotal;    // cell slot elements per frame
     int nodeCap;             // quadtree node capacity (power of two) over all levels
+    int presortLevels;       // levels 0 .. presortLevels-1 are large: gathered / coded / sorted by a CTA cluster each
+    int presortMaxCells;     // cells of the largest of them
     LevelGeom lv[ORB_MAX_LEVELS];
 };
 

@@ -48,6 +48,7 @@ struct QtArgs {
     int* err;                        // device error flag
     int nlevels, selTotal, nodeCap;
     int levelBegin;                  // blockIdx.y = 0 is this level (a launch may cover a level range)
+    unsigned presortMask;            // bit l: steps 0-2 of level l were done by qt_presort_kernel (quadtree_presort.cuh)
     int keyCap;                      // keys per sort array that fit in the dynamic shared memory behind the node arrays (0 = none)
     unsigned long long candOff[ORB_MAX_LEVELS];
     int N[ORB_MAX_LEVELS], nIni[ORB_MAX_LEVELS], qH[ORB_MAX_LEVELS], depth[ORB_MAX_LEVELS];

@@ -1,6 +1,7 @@
 // quadtree_kernel: see quadtree.cuh for the formulation.
 #pragma once
 #include "quadtree.cuh"
+#include "quadtree_presort.cuh"
 
 namespace orbx {
 
@@ -84,8 +85,11 @@ __global__ void __launch_bounds__(NT) quadtree_kernel(QtArgs a) {
     //    of 32 (one per lane); chunk totals give every chunk its base, and inside a chunk the warp copies the
     //    concatenated lists element by element (lane t of a step finds its cell by a shuffle search over the lanes'
     //    running totals), so the copy is balanced however the survivors are spread over the cells.
+    const bool pre = (a.presortMask >> l) & 1u;           // large level: gathered, coded and sorted by qt_presort_kernel
     int M;
-    {
+    if (pre) {
+        M = a.candCount[frame * a.nlevels + l];
+    } else {
         const int nc = a.cellOff[l + 1] - a.cellOff[l];
         const uint32_t* cnt = a.cellCount + (size_t)frame * a.totalCells + a.cellOff[l];
         const int lane = tid & 31, wid = tid >> 5;
@@ -138,22 +142,27 @@ __global__ void __launch_bounds__(NT) quadtree_kernel(QtArgs a) {
 
     // sort arrays in shared memory when this launch reserved room for them (generic pointers from here on): the binary
     // searches of the passes below are chains of dependent loads, 10x shorter from shared memory than from L2
-    if (M <= a.keyCap) {
-        uint32_t* ks = (uint32_t*)(qsm + qt_smem_bytes(cap, NT));
-        kA = ks; kB = ks + a.keyCap; vA = ks + 2 * a.keyCap; vB = ks + 3 * a.keyCap;
+    int which;
+    if (pre) {
+        which = qtp_passes(depth, nIni) & 1;
+    } else {
+        if (M <= a.keyCap) {
+            uint32_t* ks = (uint32_t*)(qsm + qt_smem_bytes(cap, NT));
+            kA = ks; kB = ks + a.keyCap; vA = ks + 2 * a.keyCap; vB = ks + 3 * a.keyCap;
+        }
+        // 1. path codes
+        for (int i = tid; i < M; i += QT_THREADS) {
+            const uint32_t c = cand[i];
+            kA[i] = path_code((int)(c & 0xfff), (int)((c >> 12) & 0xfff), a.hX[l], nIni, a.qH[l], depth);
+            vA[i] = (c & 0xff000000u) | (uint32_t)i;
+        }
+        __syncthreads();
+        QT_MARK(2);
+        // 2. sort by code
+        int iniBits = 0;
+        while ((1 << iniBits) < nIni) iniBits++;
+        which = block_radix_sort<NT>(kA, vA, kB, vB, M, 2 * depth + iniBits, s.hist, s.warpTmp);
     }
-    // 1. path codes
-    for (int i = tid; i < M; i += QT_THREADS) {
-        const uint32_t c = cand[i];
-        kA[i] = path_code((int)(c & 0xfff), (int)((c >> 12) & 0xfff), a.hX[l], nIni, a.qH[l], depth);
-        vA[i] = (c & 0xff000000u) | (uint32_t)i;
-    }
-    __syncthreads();
-    QT_MARK(2);
-    // 2. sort by code
-    int iniBits = 0;
-    while ((1 << iniBits) < nIni) iniBits++;
-    const int which = block_radix_sort<NT>(kA, vA, kB, vB, M, 2 * depth + iniBits, s.hist, s.warpTmp);
     QT_MARK(3);
     const uint32_t* keys = which ? kB : kA;
     const uint32_t* vals = which ? vB : vA;
