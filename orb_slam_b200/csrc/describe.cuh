@@ -75,7 +75,7 @@ __device__ __forceinline__ float coord_f(uint32_t w) {
 // into word WQ of the 12 loaded words
 template <int WQ>
 __device__ __forceinline__ void ic_row(const uint32_t (&W)[12], unsigned sh, const uint4* __restrict__ wrow, uint32_t& rowsum, uint32_t& su) {
-    const uint4 o0 = wrow[0], o1 = wrow[1], u0 = wrow[2], u1 = wrow[3];
+    const uint4 o0 = wrow[0], o1 = wrow[32], u0 = wrow[64], u1 = wrow[96];
     const uint32_t one[8] = {o0.x, o0.y, o0.z, o0.w, o1.x, o1.y, o1.z, o1.w};
     const uint32_t uw[8] = {u0.x, u0.y, u0.z, u0.w, u1.x, u1.y, u1.z, u1.w};
 #pragma unroll
@@ -97,7 +97,9 @@ __global__ void __launch_bounds__(256, 4) describe_kernel(DescArgs a) {
     __shared__ uint4 s_icw[32 * 4];
     __shared__ uint4 s_blur[8][DP_ROWS * DP_SV];
     __shared__ uint4 s_img[8][32 * IP_VECS];
-    if (threadIdx.x < 128) s_icw[threadIdx.x] = ((const uint4*)g_icw)[threadIdx.x];
+    // transposed to [vector j][row]: the lanes of a warp read consecutive 16-byte vectors (row-major, 64 bytes per row, the eight
+    // lanes of a quarter-warp hit two banks groups four times each: 16 wavefronts per read instead of 4)
+    if (threadIdx.x < 128) s_icw[(threadIdx.x & 3) * 32 + (threadIdx.x >> 2)] = ((const uint4*)g_icw)[threadIdx.x];
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     const int frame = blockIdx.y;
     // level counts: lane k fetches count k
@@ -167,7 +169,7 @@ __global__ void __launch_bounds__(256, 4) describe_kernel(DescArgs a) {
             W[8] = i2.x; W[9] = i2.y; W[10] = i2.z; W[11] = i2.w;
             const int off = (x - ORB_HALF_PATCH) - ix0;     // 0..15, warp-uniform
             const unsigned sh = 8u * (unsigned)(off & 3);
-            const uint4* wrow = s_icw + lane * 4;
+            const uint4* wrow = s_icw + lane;            // vector j of this lane's row at wrow[32 * j]
             uint32_t rowsum = 0, su = 0;
             switch (off >> 2) {
                 case 0: ic_row<0>(W, sh, wrow, rowsum, su); break;
