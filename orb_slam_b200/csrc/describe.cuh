@@ -74,10 +74,9 @@ __device__ __forceinline__ float coord_f(uint32_t w) {
 // rowsum = sum of the row's disc pixels, su = sum of (u + 15) * pixel: 16 DP4A over the 32 bytes that start `sh/8` bytes
 // into word WQ of the 12 loaded words
 template <int WQ>
-__device__ __forceinline__ void ic_row(const uint32_t (&W)[12], unsigned sh, const uint4* __restrict__ wrow, uint32_t& rowsum, uint32_t& su) {
-    const uint4 o0 = wrow[0], o1 = wrow[32], u0 = wrow[64], u1 = wrow[96];
-    const uint32_t one[8] = {o0.x, o0.y, o0.z, o0.w, o1.x, o1.y, o1.z, o1.w};
-    const uint32_t uw[8] = {u0.x, u0.y, u0.z, u0.w, u1.x, u1.y, u1.z, u1.w};
+__device__ __forceinline__ void ic_row(const uint32_t (&W)[12], unsigned sh, const uint4 (&wt)[4], uint32_t& rowsum, uint32_t& su) {
+    const uint32_t one[8] = {wt[0].x, wt[0].y, wt[0].z, wt[0].w, wt[1].x, wt[1].y, wt[1].z, wt[1].w};
+    const uint32_t uw[8] = {wt[2].x, wt[2].y, wt[2].z, wt[2].w, wt[3].x, wt[3].y, wt[3].z, wt[3].w};
 #pragma unroll
     for (int k = 0; k < 8; k++) {
         const uint32_t d = __funnelshift_r(W[WQ + k], W[WQ + k + 1], sh);
@@ -140,6 +139,10 @@ __global__ void __launch_bounds__(256, 4) describe_kernel(DescArgs a) {
     if (!live) return;
     const int myX = (int)(myC & 0xfff) + ORB_BORDER_MIN, myY = (int)((myC >> 12) & 0xfff) + ORB_BORDER_MIN;   // :1021-1022
 
+    // this lane's disc-row weights (the same for every keypoint): in registers for the whole warp's slots
+    uint4 icw[4];
+#pragma unroll
+    for (int j = 0; j < 4; j++) icw[j] = s_icw[32 * j + lane];
     // ---- phase A: IC_Angle moments (:84-128): lane = disc row v + 15; m01 = sum v * rowsum(v), m10 = sum over rows of sum u * pixel
     int myM10 = 0, myM01 = 0;
 #pragma unroll 1
@@ -169,13 +172,13 @@ __global__ void __launch_bounds__(256, 4) describe_kernel(DescArgs a) {
             W[8] = i2.x; W[9] = i2.y; W[10] = i2.z; W[11] = i2.w;
             const int off = (x - ORB_HALF_PATCH) - ix0;     // 0..15, warp-uniform
             const unsigned sh = 8u * (unsigned)(off & 3);
-            const uint4* wrow = s_icw + lane;            // vector j of this lane's row at wrow[32 * j]
+
             uint32_t rowsum = 0, su = 0;
             switch (off >> 2) {
-                case 0: ic_row<0>(W, sh, wrow, rowsum, su); break;
-                case 1: ic_row<1>(W, sh, wrow, rowsum, su); break;
-                case 2: ic_row<2>(W, sh, wrow, rowsum, su); break;
-                default: ic_row<3>(W, sh, wrow, rowsum, su); break;
+                case 0: ic_row<0>(W, sh, icw, rowsum, su); break;
+                case 1: ic_row<1>(W, sh, icw, rowsum, su); break;
+                case 2: ic_row<2>(W, sh, icw, rowsum, su); break;
+                default: ic_row<3>(W, sh, icw, rowsum, su); break;
             }
             m10 = (int)su - ORB_HALF_PATCH * (int)rowsum;
             m01 = (lane - ORB_HALF_PATCH) * (int)rowsum;
