@@ -188,4 +188,65 @@ __device__ int block_radix_sort(uint32_t* kA, uint32_t* vA, uint32_t* kB, uint32
     return which;
 }
 
+// ---- sort of DISTINCT keys by bucket, then rank --------------------------------------------------------------------------
+// The path codes of distinct pixels are distinct (quadtree_kernel checks it, error 101), so the sorted order does not depend on
+// the algorithm.  A counting pass scatters the keys into buckets of their top bits (shared-memory atomics; the order inside a
+// bucket is whatever the atomics made it), then every key finds its final place by counting the smaller keys of its own bucket.
+// A bucket is a small box of the level and holds a few keys; the rank step is quadratic in the bucket size, so the caller keeps
+// the radix sort for inputs with a large bucket.  Two passes over the keys and one scan of the bucket counts instead of the
+// radix sort's three rounds of (histogram by match_any, scan of 256 x warps counters, scatter by match_any).
+template <int NT> struct QtBucket {
+    static constexpr int LOG = NT >= 512 ? 11 : 9;       // NB + 1 counters must fit in the 256 x warps words of the radix histogram
+    static constexpr int NB = 1 << LOG;
+    static constexpr int MAXB = 64;                      // larger bucket anywhere -> radix sort
+};
+
+// bc[b] = number of keys of bucket b = key >> sh (counted by the caller while it produced kA / vA), bc[NB] unused.
+// Returns false (nothing moved) when some bucket exceeds MAXB; otherwise the sorted pairs are back in kA / vA.
+template <int NT>
+__device__ bool block_bucket_sort(uint32_t* kA, uint32_t* vA, uint32_t* kB, uint32_t* vB, int M, int sh, int* bc, int* warpTmp) {
+    constexpr int NB = QtBucket<NT>::NB;
+    const int tid = threadIdx.x;
+    int big = 0;
+    for (int i = tid; i < NB; i += NT) big |= bc[i] > QtBucket<NT>::MAXB;
+    if (__syncthreads_or(big)) return false;
+    block_scan_excl<NT>(bc, NB, warpTmp);                // bc[b] = first position of bucket b
+    for (int i = tid; i < M; i += NT) {
+        const uint32_t k = kA[i];
+        const int p = atomicAdd(&bc[k >> sh], 1);
+        kB[p] = k; vB[p] = vA[i];
+    }
+    __syncthreads();                                     // now bc[b] = end of bucket b = start of bucket b + 1
+    for (int p = tid; p < M; p += NT) {
+        const uint32_t k = kB[p];
+        const int b = (int)(k >> sh);
+        const int s0 = b ? bc[b - 1] : 0, e0 = bc[b];
+        int r = 0;
+        for (int j = s0; j < e0; j++) { const uint32_t kj = kB[j]; r += (kj < k) || (kj == k && j < p); }
+        kA[s0 + r] = k; vA[s0 + r] = vB[p];
+    }
+    __syncthreads();
+    return true;
+}
+
+// exclusive block scan of one register value per thread (one barrier); wt = NT / 32 words of shared scratch that no thread
+// touches again before the next block barrier
+template <int NT>
+__device__ __forceinline__ uint32_t block_excl_reg(uint32_t mine, uint32_t* wt, uint32_t& total) {
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    uint32_t inc = mine;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        const uint32_t t = __shfl_up_sync(0xffffffffu, inc, d);
+        if (lane >= d) inc += t;
+    }
+    if (lane == 31) wt[wid] = inc;
+    __syncthreads();
+    uint32_t base = 0;
+    total = 0;
+#pragma unroll
+    for (int k = 0; k < NT / 32; k++) { const uint32_t v = wt[k]; if (k < wid) base += v; total += v; }
+    return base + inc - mine;
+}
+
 }  // namespace orbx

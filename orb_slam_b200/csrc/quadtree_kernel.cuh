@@ -32,6 +32,26 @@ __device__ __forceinline__ int split_node(const uint32_t* keys, uint32_t lo, uin
     return (n1 > 0) + (n2 > 0) + (n3 > 0) + (n4 > 0);
 }
 
+// the same with the three searches side by side over [lo, hi): they are independent, so their chains of dependent reads overlap
+__device__ __forceinline__ int split_node3(const uint32_t* keys, uint32_t lo, uint32_t hi, int dep, int depth,
+                                           uint32_t& c1, uint32_t& c2, uint32_t& c3, int& ne) {
+    const int shift = 2 * (depth - 1 - dep);
+    uint32_t l1 = lo, h1 = hi, l2 = lo, h2 = hi, l3 = lo, h3 = hi;
+    while ((l1 < h1) | (l2 < h2) | (l3 < h3)) {
+        const uint32_t m1 = (l1 + h1) >> 1, m2 = (l2 + h2) >> 1, m3 = (l3 + h3) >> 1;
+        const uint32_t d1 = l1 < h1 ? (keys[m1] >> shift) & 3u : 0u;
+        const uint32_t d2 = l2 < h2 ? (keys[m2] >> shift) & 3u : 0u;
+        const uint32_t d3 = l3 < h3 ? (keys[m3] >> shift) & 3u : 0u;
+        if (l1 < h1) { if (d1 >= 1u) h1 = m1; else l1 = m1 + 1; }
+        if (l2 < h2) { if (d2 >= 2u) h2 = m2; else l2 = m2 + 1; }
+        if (l3 < h3) { if (d3 >= 3u) h3 = m3; else l3 = m3 + 1; }
+    }
+    c1 = l1; c2 = l2; c3 = l3;
+    const uint32_t n1 = c1 - lo, n2 = c2 - c1, n3 = c3 - c2, n4 = hi - c3;
+    ne = (n1 > 1) + (n2 > 1) + (n3 > 1) + (n4 > 1);
+    return (n1 > 0) + (n2 > 0) + (n3 > 0) + (n4 > 0);
+}
+
 // writes the non-empty children of a node in push order n1..n4; push index p0.. ; list position = totalPushed-1-p
 __device__ __forceinline__ void emit_children(uint32_t* nlo, uint32_t* nhi, uint8_t* ndep, uint32_t lo, uint32_t c1,
                                               uint32_t c2, uint32_t c3, uint32_t hi, int dep, int p0, int totalPushed) {
@@ -150,18 +170,27 @@ __global__ void __launch_bounds__(NT) quadtree_kernel(QtArgs a) {
             uint32_t* ks = (uint32_t*)(qsm + qt_smem_bytes(cap, NT));
             kA = ks; kB = ks + a.keyCap; vA = ks + 2 * a.keyCap; vB = ks + 3 * a.keyCap;
         }
-        // 1. path codes
+        // 1. path codes, and the bucket counts of the sort
+        int iniBits = 0;
+        while ((1 << iniBits) < nIni) iniBits++;
+        const int bits = 2 * depth + iniBits;
+        const int sh = max(0, bits - QtBucket<NT>::LOG);
+        int* bc = (int*)s.hist;
+        for (int i = tid; i <= QtBucket<NT>::NB; i += QT_THREADS) bc[i] = 0;
+        __syncthreads();
         for (int i = tid; i < M; i += QT_THREADS) {
             const uint32_t c = cand[i];
-            kA[i] = path_code((int)(c & 0xfff), (int)((c >> 12) & 0xfff), a.hX[l], nIni, a.qH[l], depth);
+            const uint32_t code = path_code((int)(c & 0xfff), (int)((c >> 12) & 0xfff), a.hX[l], nIni, a.qH[l], depth);
+            kA[i] = code;
             vA[i] = (c & 0xff000000u) | (uint32_t)i;
+            atomicAdd(&bc[code >> sh], 1);
         }
         __syncthreads();
         QT_MARK(2);
-        // 2. sort by code
-        int iniBits = 0;
-        while ((1 << iniBits) < nIni) iniBits++;
-        which = block_radix_sort<NT>(kA, vA, kB, vB, M, 2 * depth + iniBits, s.hist, s.warpTmp);
+        // 2. sort by code: buckets + ranks, or the radix sort when a bucket is large
+        which = 0;
+        if (!block_bucket_sort<NT>(kA, vA, kB, vB, M, sh, bc, s.warpTmp))
+            which = block_radix_sort<NT>(kA, vA, kB, vB, M, bits, s.hist, s.warpTmp);
     }
     QT_MARK(3);
     const uint32_t* keys = which ? kB : kA;
@@ -188,6 +217,9 @@ __global__ void __launch_bounds__(NT) quadtree_kernel(QtArgs a) {
     bool finish = false;
     int fresh = 0;            // number of nodes created by the last pass (front of the list)
     bool priority = false;
+    constexpr int PER = NT >= 512 ? 1 : 512 / NT;        // nodes per thread of the register-resident passes (lists of up to 512 nodes)
+    uint32_t* scr = s.hist;                              // block-scan scratch of those passes (the sort is done with it)
+    int passNo = 0;
     QT_MARK(4);
 #ifdef QT_PROFILE
     int qtIter = 0;
@@ -202,9 +234,111 @@ __global__ void __launch_bounds__(NT) quadtree_kernel(QtArgs a) {
         uint32_t* clo = s.lo[cur]; uint32_t* chi = s.hi[cur]; uint8_t* cdep = s.dep[cur];
         uint32_t* nlo = s.lo[cur ^ 1]; uint32_t* nhi = s.hi[cur ^ 1]; uint8_t* ndep = s.dep[cur ^ 1];
         const int prevSize = n;
-        if (tid == 0) { s.misc[0] = 0; s.misc[1] = 0x7fffffff; s.misc[2] = 0; }
+        passNo ^= 1;
+        if (tid == 0) { s.misc[0] = 0; s.misc[1] = 0x7fffffff; s.misc[2] = 0; s.misc[4 + passNo] = 0; }
         __syncthreads();
-        if (!priority) {
+        if (!priority && n <= NT * PER) {
+            // ---- breadth pass of a short list (:726-789), PER nodes per thread: the splits stay in registers, both prefix sums
+            //      (children pushed / nodes that stay) are one packed scan with one barrier.  The passes of a level are a
+            //      chain of block barriers; this form has three per pass.
+            uint32_t lo_[PER], hi_[PER], c1_[PER], c2_[PER], c3_[PER], pk_[PER];
+            int dp_[PER];
+            uint32_t sum = 0;
+            int neLocal = 0;
+#pragma unroll
+            for (int k = 0; k < PER; k++) {
+                const int i = tid * PER + k;
+                pk_[k] = 0; lo_[k] = hi_[k] = 0; dp_[k] = 0; c1_[k] = c2_[k] = c3_[k] = 0;
+                if (i < n) {
+                    lo_[k] = clo[i]; hi_[k] = chi[i]; dp_[k] = cdep[i];
+                    if (hi_[k] - lo_[k] > 1) {
+                        if (dp_[k] >= depth) atomicExch(a.err, 102);
+                        else {
+                            int ne;
+                            pk_[k] = (uint32_t)split_node3(keys, lo_[k], hi_[k], dp_[k], depth, c1_[k], c2_[k], c3_[k], ne);
+                            neLocal += ne;
+                        }
+                    } else pk_[k] = 1u << 16;
+                }
+                sum += pk_[k];
+            }
+            neLocal = __reduce_add_sync(0xffffffffu, neLocal);
+            if ((tid & 31) == 0 && neLocal) atomicAdd(&s.misc[4 + passNo], neLocal);
+            uint32_t total;
+            uint32_t ex = block_excl_reg<NT>(sum, scr, total);        // low half: children pushed before mine, high half: stayers
+            const int totalPushed = (int)(total & 0xffffu), totalNoMore = (int)(total >> 16);
+            if (totalPushed + totalNoMore > cap) { if (tid == 0) atomicExch(a.err, 103); break; }
+#pragma unroll
+            for (int k = 0; k < PER; k++) {
+                const int i = tid * PER + k;
+                if (i < n) {
+                    if (hi_[k] - lo_[k] > 1) {
+                        if (dp_[k] < depth) emit_children(nlo, nhi, ndep, lo_[k], c1_[k], c2_[k], c3_[k], hi_[k], dp_[k], (int)(ex & 0xffffu), totalPushed);
+                    } else { const int pos = totalPushed + (int)(ex >> 16); nlo[pos] = lo_[k]; nhi[pos] = hi_[k]; ndep[pos] = (uint8_t)dp_[k]; }
+                }
+                ex += pk_[k];
+            }
+            __syncthreads();
+            n = totalPushed + totalNoMore;
+            fresh = totalPushed;
+            cur ^= 1;
+            const int nToExpand = s.misc[4 + passNo];                 // (this slot is cleared again two passes from now)
+            if (n >= N || n == prevSize) finish = true;
+            else if (n + nToExpand * 3 > N) priority = true;
+        } else if (priority && PER == 1 && n <= NT) {
+            // ---- priority pass of a short list (:805-874), one node per thread.  The expandable nodes are ordered by
+            //      ranking (count, creation seq) keys against each other - they are distinct - instead of a sorting network;
+            //      the walk's running list size, where it stops and the children's places all come from ONE scan of the
+            //      children counts: after t + 1 splits the list has grown by (children so far) - (t + 1).
+            const int i = tid;
+            uint32_t lo = 0, hi = 0;
+            int dp = 0;
+            unsigned long long key = 0;
+            if (i < n) {
+                lo = clo[i]; hi = chi[i]; dp = cdep[i];
+                if (i < fresh && hi - lo > 1) key = ((unsigned long long)(hi - lo) << 32) | (uint32_t)(fresh - 1 - i);
+            }
+            if (i < fresh) s.skey[i] = key;
+            const int ne = __syncthreads_count(key != 0);
+            int rank = -1;
+            if (key) {
+                int r = 0;
+                for (int j = 0; j < fresh; j++) r += s.skey[j] > key;
+                rank = r;
+                s.sA[r] = i;                                          // walk order -> node
+            }
+            __syncthreads();
+            uint32_t plo = 0, phi = 0, c1 = 0, c2 = 0, c3 = 0, nc = 0;
+            int pdp = 0;
+            if (tid < ne) {
+                const int pi = s.sA[tid];
+                plo = clo[pi]; phi = chi[pi]; pdp = cdep[pi];
+                if (pdp >= depth) atomicExch(a.err, 102);
+                else { int dummy; nc = (uint32_t)split_node3(keys, plo, phi, pdp, depth, c1, c2, c3, dummy); }
+            }
+            uint32_t allNc;
+            const uint32_t exA = block_excl_reg<NT>(nc, scr, allNc);
+            if (tid < ne) {
+                s.sB[tid] = (int)(exA + nc);
+                if (n + (int)(exA + nc) - (tid + 1) >= N) atomicMin(&s.misc[1], tid);      // first split that fills the list (:867-868)
+            }
+            __syncthreads();
+            const int tStop = (s.misc[1] == 0x7fffffff) ? ne - 1 : s.misc[1];
+            const int nProc = tStop + 1;                                 // 0 when ne == 0
+            const int totalPushed = nProc > 0 ? s.sB[tStop] : 0;
+            const int newSize = n + totalPushed - nProc;
+            const bool keep = i < n && !(rank >= 0 && rank < nProc);    // split nodes leave the list
+            uint32_t kept;
+            const uint32_t exK = block_excl_reg<NT>(keep ? 1u : 0u, scr + 32, kept);
+            if (totalPushed + (int)kept > cap) { if (tid == 0) atomicExch(a.err, 103); break; }
+            if (tid < nProc && pdp < depth) emit_children(nlo, nhi, ndep, plo, c1, c2, c3, phi, pdp, (int)exA, totalPushed);
+            if (keep) { const int pos = totalPushed + (int)exK; nlo[pos] = lo; nhi[pos] = hi; ndep[pos] = (uint8_t)dp; }
+            __syncthreads();
+            n = newSize;
+            fresh = totalPushed;
+            cur ^= 1;
+            if (n >= N || n == prevSize) finish = true;
+        } else if (!priority) {
             // ---- breadth pass: split every node with more than one key (:726-789)
             int neLocal = 0;
             for (int i = tid; i < n; i += QT_THREADS) {

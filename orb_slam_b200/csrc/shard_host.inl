@@ -88,12 +88,12 @@ int orbm_nccl_version(int* version) {
 
 int orbm_shard_create(orbm_shard_t** out, orbm_t* m, const uint8_t* id128, int rank, int world) {
     if (!out || !m || world < 1 || rank < 0 || rank >= world || (world > 1 && !id128)) return ORBX_E_INVALID;
+    if (world > 1 && !nccl_api().ok) return ORBX_E_UNSUPPORTED;
+    if (world > 1) CKM(cudaSetDevice(m->device));
     orbm_shard* s = new orbm_shard();
     s->m = m; s->rank = rank; s->world = world;
     if (world > 1) {
         const NcclApi& a = nccl_api();
-        if (!a.ok) { delete s; return ORBX_E_UNSUPPORTED; }
-        CKM(cudaSetDevice(m->device));
         ncclUniqueId id;
         std::memcpy(&id, id128, sizeof(id));
         ncclResult_t r = a.CommInitRank(&s->comm, world, id, rank);      // collective over all ranks
