@@ -6,7 +6,7 @@
 namespace orbx {
 
 struct QtSmem {
-    uint32_t* lo[2]; uint32_t* hi[2]; uint8_t* dep[2];
+    uint32_t* lo0; uint32_t* lo1; uint32_t* hi0; uint32_t* hi1; uint8_t* dep0; uint8_t* dep1;   // (no arrays: an index would push the struct into local memory)
     uint32_t* b1; uint32_t* b2; uint32_t* b3;
     int* sA; int* sB; int* sC;
     unsigned long long* skey;
@@ -85,14 +85,14 @@ __global__ void __launch_bounds__(NT) quadtree_kernel(QtArgs a) {
     {
         uint8_t* p = qsm;
         s.skey = (unsigned long long*)p; p += (size_t)cap * 8;
-        s.lo[0] = (uint32_t*)p; p += (size_t)cap * 4; s.lo[1] = (uint32_t*)p; p += (size_t)cap * 4;
-        s.hi[0] = (uint32_t*)p; p += (size_t)cap * 4; s.hi[1] = (uint32_t*)p; p += (size_t)cap * 4;
+        s.lo0 = (uint32_t*)p; p += (size_t)cap * 4; s.lo1 = (uint32_t*)p; p += (size_t)cap * 4;
+        s.hi0 = (uint32_t*)p; p += (size_t)cap * 4; s.hi1 = (uint32_t*)p; p += (size_t)cap * 4;
         s.b1 = (uint32_t*)p; p += (size_t)cap * 4; s.b2 = (uint32_t*)p; p += (size_t)cap * 4; s.b3 = (uint32_t*)p; p += (size_t)cap * 4;
         s.sA = (int*)p; p += (size_t)cap * 4; s.sB = (int*)p; p += (size_t)cap * 4; s.sC = (int*)p; p += (size_t)cap * 4;
         s.hist = (uint32_t*)p; p += 256 * QT_WARPS * 4;
         s.warpTmp = (int*)p; p += QT_WARPS * 4;
         s.misc = (int*)p; p += 64;
-        s.dep[0] = p; p += cap; s.dep[1] = p;
+        s.dep0 = p; p += cap; s.dep1 = p;
     }
     int* selCount = a.selCount + frame * a.nlevels + l;
     const int depth = a.depth[l], N = a.N[l], nIni = a.nIni[l];
@@ -106,9 +106,12 @@ __global__ void __launch_bounds__(NT) quadtree_kernel(QtArgs a) {
     //    concatenated lists element by element (lane t of a step finds its cell by a shuffle search over the lanes'
     //    running totals), so the copy is balanced however the survivors are spread over the cells.
     const bool pre = (a.presortMask >> l) & 1u;           // large level: gathered, coded and sorted by qt_presort_kernel
-    int M;
+    int M, which;
     if (pre) {
         M = a.candCount[frame * a.nlevels + l];
+        QT_MARK(1);
+        if (M <= 0) { if (tid == 0) *selCount = 0; return; }
+        which = qtp_passes(depth, nIni) & 1;
     } else {
         const int nc = a.cellOff[l + 1] - a.cellOff[l];
         const uint32_t* cnt = a.cellCount + (size_t)frame * a.totalCells + a.cellOff[l];
@@ -122,13 +125,31 @@ __global__ void __launch_bounds__(NT) quadtree_kernel(QtArgs a) {
             for (int d = 16; d > 0; d >>= 1) v += __shfl_xor_sync(0xffffffffu, v, d);
             if (lane == 0) chunkSum[ch] = v;
         }
+        // bucket counters of the sort (step 2), filled while the candidates pass through registers
+        int iniBits = 0;
+        while ((1 << iniBits) < nIni) iniBits++;
+        const int bits = 2 * depth + iniBits;
+        const int sh = max(0, bits - QtBucket<NT>::LOG);
+        int* bc = (int*)s.hist;
+        for (int i = tid; i <= QtBucket<NT>::NB; i += QT_THREADS) bc[i] = 0;
         __syncthreads();
         int total = 0;
         for (int ch = 0; ch < nchunks; ch++) total += chunkSum[ch];
         M = total;
         if (M > a.candCap[l]) { if (tid == 0) { atomicExch(a.err, 105); *selCount = 0; a.candCount[frame * a.nlevels + l] = 0; } return; }
+        if (tid == 0) a.candCount[frame * a.nlevels + l] = M;
+        if (M <= 0) { if (tid == 0) *selCount = 0; return; }
+        // sort arrays in shared memory when this launch reserved room for them (generic pointers from here on): the binary
+        // searches of the passes below are chains of dependent loads, 10x shorter from shared memory than from L2
+        if (M <= a.keyCap) {
+            uint32_t* ks = (uint32_t*)(qsm + qt_smem_bytes(cap, NT));
+            kA = ks; kB = ks + a.keyCap; vA = ks + 2 * a.keyCap; vB = ks + 3 * a.keyCap;
+        }
+        // 0 + 1. candidate list, path codes (sort keys) and the (response, candidate index) sort values in one sweep
         const uint32_t* slots = a.slots + (size_t)frame * a.slotFrameStride + a.slotOff[l];
         const int scap = a.slotCap[l];
+        const float hX = a.hX[l];
+        const int qH = a.qH[l];
         for (int ch = wid; ch < nchunks; ch += QT_WARPS) {
             int base = 0;
             for (int k = 0; k < ch; k++) base += chunkSum[k];
@@ -141,51 +162,40 @@ __global__ void __launch_bounds__(NT) quadtree_kernel(QtArgs a) {
                 if (lane >= d) incl += t;
             }
             const int T = __shfl_sync(0xffffffffu, incl, 31);
-            for (int t0 = 0; t0 < T; t0 += 32) {
-                const int t = t0 + lane;
-                int j = 0;                                       // first lane whose running total exceeds t
+            constexpr int GU = 4;                                // candidate words fetched ahead of the path-code arithmetic
+            for (int t0 = 0; t0 < T; t0 += 32 * GU) {
+                uint32_t cw[GU];
 #pragma unroll
-                for (int step = 16; step > 0; step >>= 1) {
-                    const int v = __shfl_sync(0xffffffffu, incl, j + step - 1);
-                    if (v <= t) j += step;
+                for (int u = 0; u < GU; u++) {
+                    cw[u] = 0;
+                    if (t0 + 32 * u >= T) continue;              // warp-uniform
+                    const int t = t0 + 32 * u + lane;
+                    int j = 0;                                   // first lane whose running total exceeds t
+#pragma unroll
+                    for (int step = 16; step > 0; step >>= 1) {
+                        const int v = __shfl_sync(0xffffffffu, incl, j + step - 1);
+                        if (v <= t) j += step;
+                    }
+                    j = min(j, 31);
+                    const int startj = __shfl_sync(0xffffffffu, incl - nmine, j);
+                    if (t < T) cw[u] = slots[(size_t)(ch * 32 + j) * scap + (t - startj)];
                 }
-                j = min(j, 31);
-                const int startj = __shfl_sync(0xffffffffu, incl - nmine, j);
-                if (t < T) cand[base + t] = slots[(size_t)(ch * 32 + j) * scap + (t - startj)];
+#pragma unroll
+                for (int u = 0; u < GU; u++) {
+                    const int t = t0 + 32 * u + lane;
+                    if (t < T) {
+                        const int i = base + t;
+                        cand[i] = cw[u];
+                        const uint32_t code = path_code((int)(cw[u] & 0xfff), (int)((cw[u] >> 12) & 0xfff), hX, nIni, qH, depth);
+                        kA[i] = code;
+                        vA[i] = (cw[u] & 0xff000000u) | (uint32_t)i;
+                        atomicAdd(&bc[code >> sh], 1);
+                    }
+                }
             }
         }
-        if (tid == 0) a.candCount[frame * a.nlevels + l] = M;
         __syncthreads();
-    }
-    QT_MARK(1);
-    if (M <= 0) { if (tid == 0) *selCount = 0; return; }
-
-    // sort arrays in shared memory when this launch reserved room for them (generic pointers from here on): the binary
-    // searches of the passes below are chains of dependent loads, 10x shorter from shared memory than from L2
-    int which;
-    if (pre) {
-        which = qtp_passes(depth, nIni) & 1;
-    } else {
-        if (M <= a.keyCap) {
-            uint32_t* ks = (uint32_t*)(qsm + qt_smem_bytes(cap, NT));
-            kA = ks; kB = ks + a.keyCap; vA = ks + 2 * a.keyCap; vB = ks + 3 * a.keyCap;
-        }
-        // 1. path codes, and the bucket counts of the sort
-        int iniBits = 0;
-        while ((1 << iniBits) < nIni) iniBits++;
-        const int bits = 2 * depth + iniBits;
-        const int sh = max(0, bits - QtBucket<NT>::LOG);
-        int* bc = (int*)s.hist;
-        for (int i = tid; i <= QtBucket<NT>::NB; i += QT_THREADS) bc[i] = 0;
-        __syncthreads();
-        for (int i = tid; i < M; i += QT_THREADS) {
-            const uint32_t c = cand[i];
-            const uint32_t code = path_code((int)(c & 0xfff), (int)((c >> 12) & 0xfff), a.hX[l], nIni, a.qH[l], depth);
-            kA[i] = code;
-            vA[i] = (c & 0xff000000u) | (uint32_t)i;
-            atomicAdd(&bc[code >> sh], 1);
-        }
-        __syncthreads();
+        QT_MARK(1);
         QT_MARK(2);
         // 2. sort by code: buckets + ranks, or the radix sort when a bucket is large
         which = 0;
@@ -207,7 +217,7 @@ __global__ void __launch_bounds__(NT) quadtree_kernel(QtArgs a) {
         int n = 0;
         for (int i = 0; i < nIni; i++) {
             const uint32_t lo = s.b1[i], hi = s.b1[i + 1];
-            if (hi > lo) { s.lo[0][n] = lo; s.hi[0][n] = hi; s.dep[0][n] = 0; n++; }
+            if (hi > lo) { s.lo0[n] = lo; s.hi0[n] = hi; s.dep0[n] = 0; n++; }
         }
         s.misc[3] = n;
     }
@@ -217,7 +227,7 @@ __global__ void __launch_bounds__(NT) quadtree_kernel(QtArgs a) {
     bool finish = false;
     int fresh = 0;            // number of nodes created by the last pass (front of the list)
     bool priority = false;
-    constexpr int PER = NT >= 512 ? 1 : 512 / NT;        // nodes per thread of the register-resident passes (lists of up to 512 nodes)
+    constexpr int SHORT = 4 * NT;                        // lists up to this long take the passes with register scans (one barrier per NT nodes)
     uint32_t* scr = s.hist;                              // block-scan scratch of those passes (the sort is done with it)
     int passNo = 0;
     QT_MARK(4);
@@ -231,52 +241,55 @@ __global__ void __launch_bounds__(NT) quadtree_kernel(QtArgs a) {
         if (tid == 0 && blockIdx.x == 0 && blockIdx.y == 0) g_qt_clock[40 + min(qtIter, 19)] = priority ? -n : n;
         qtIter++;
 #endif
-        uint32_t* clo = s.lo[cur]; uint32_t* chi = s.hi[cur]; uint8_t* cdep = s.dep[cur];
-        uint32_t* nlo = s.lo[cur ^ 1]; uint32_t* nhi = s.hi[cur ^ 1]; uint8_t* ndep = s.dep[cur ^ 1];
+        uint32_t* clo = cur ? s.lo1 : s.lo0; uint32_t* chi = cur ? s.hi1 : s.hi0; uint8_t* cdep = cur ? s.dep1 : s.dep0;
+        uint32_t* nlo = cur ? s.lo0 : s.lo1; uint32_t* nhi = cur ? s.hi0 : s.hi1; uint8_t* ndep = cur ? s.dep0 : s.dep1;
         const int prevSize = n;
         passNo ^= 1;
         if (tid == 0) { s.misc[0] = 0; s.misc[1] = 0x7fffffff; s.misc[2] = 0; s.misc[4 + passNo] = 0; }
         __syncthreads();
-        if (!priority && n <= NT * PER) {
-            // ---- breadth pass of a short list (:726-789), PER nodes per thread: the splits stay in registers, both prefix sums
-            //      (children pushed / nodes that stay) are one packed scan with one barrier.  The passes of a level are a
-            //      chain of block barriers; this form has three per pass.
-            uint32_t lo_[PER], hi_[PER], c1_[PER], c2_[PER], c3_[PER], pk_[PER];
-            int dp_[PER];
-            uint32_t sum = 0;
+        if (!priority && n <= SHORT) {
+            // ---- breadth pass of a short list (:726-789).  Node i belongs to thread i % NT (slice i / NT): the nodes' searches
+            //      run side by side, and both prefix sums (children pushed / nodes that stay) are one packed register scan
+            //      per slice with one barrier.  The passes of a level are a chain of block barriers; this form has three for a
+            //      list of up to NT nodes.
+            const int nsl = (n + NT - 1) / NT;
             int neLocal = 0;
-#pragma unroll
-            for (int k = 0; k < PER; k++) {
-                const int i = tid * PER + k;
-                pk_[k] = 0; lo_[k] = hi_[k] = 0; dp_[k] = 0; c1_[k] = c2_[k] = c3_[k] = 0;
+            uint32_t base = 0;
+            for (int sl = 0; sl < nsl; sl++) {
+                const int i = sl * NT + tid;
+                uint32_t pk = 0;
                 if (i < n) {
-                    lo_[k] = clo[i]; hi_[k] = chi[i]; dp_[k] = cdep[i];
-                    if (hi_[k] - lo_[k] > 1) {
-                        if (dp_[k] >= depth) atomicExch(a.err, 102);
+                    const uint32_t lo = clo[i], hi = chi[i];
+                    const int dp = cdep[i];
+                    if (hi - lo > 1) {
+                        if (dp >= depth) atomicExch(a.err, 102);
                         else {
+                            uint32_t c1, c2, c3;
                             int ne;
-                            pk_[k] = (uint32_t)split_node3(keys, lo_[k], hi_[k], dp_[k], depth, c1_[k], c2_[k], c3_[k], ne);
+                            pk = (uint32_t)split_node3(keys, lo, hi, dp, depth, c1, c2, c3, ne);
+                            s.b1[i] = c1; s.b2[i] = c2; s.b3[i] = c3;
                             neLocal += ne;
                         }
-                    } else pk_[k] = 1u << 16;
+                    } else pk = 1u << 16;
                 }
-                sum += pk_[k];
+                uint32_t tot;
+                const uint32_t ex = base + block_excl_reg<NT>(pk, scr + 32 * (sl & 1), tot);
+                base += tot;
+                if (i < n) s.sB[i] = (int)ex;                          // low half: children pushed before mine, high half: stayers
             }
             neLocal = __reduce_add_sync(0xffffffffu, neLocal);
             if ((tid & 31) == 0 && neLocal) atomicAdd(&s.misc[4 + passNo], neLocal);
-            uint32_t total;
-            uint32_t ex = block_excl_reg<NT>(sum, scr, total);        // low half: children pushed before mine, high half: stayers
-            const int totalPushed = (int)(total & 0xffffu), totalNoMore = (int)(total >> 16);
+            const int totalPushed = (int)(base & 0xffffu), totalNoMore = (int)(base >> 16);
             if (totalPushed + totalNoMore > cap) { if (tid == 0) atomicExch(a.err, 103); break; }
-#pragma unroll
-            for (int k = 0; k < PER; k++) {
-                const int i = tid * PER + k;
+            for (int sl = 0; sl < nsl; sl++) {
+                const int i = sl * NT + tid;
                 if (i < n) {
-                    if (hi_[k] - lo_[k] > 1) {
-                        if (dp_[k] < depth) emit_children(nlo, nhi, ndep, lo_[k], c1_[k], c2_[k], c3_[k], hi_[k], dp_[k], (int)(ex & 0xffffu), totalPushed);
-                    } else { const int pos = totalPushed + (int)(ex >> 16); nlo[pos] = lo_[k]; nhi[pos] = hi_[k]; ndep[pos] = (uint8_t)dp_[k]; }
+                    const uint32_t lo = clo[i], hi = chi[i], ex = (uint32_t)s.sB[i];
+                    const int dp = cdep[i];
+                    if (hi - lo > 1) {
+                        if (dp < depth) emit_children(nlo, nhi, ndep, lo, s.b1[i], s.b2[i], s.b3[i], hi, dp, (int)(ex & 0xffffu), totalPushed);
+                    } else { const int pos = totalPushed + (int)(ex >> 16); nlo[pos] = lo; nhi[pos] = hi; ndep[pos] = (uint8_t)dp; }
                 }
-                ex += pk_[k];
             }
             __syncthreads();
             n = totalPushed + totalNoMore;
@@ -285,54 +298,90 @@ __global__ void __launch_bounds__(NT) quadtree_kernel(QtArgs a) {
             const int nToExpand = s.misc[4 + passNo];                 // (this slot is cleared again two passes from now)
             if (n >= N || n == prevSize) finish = true;
             else if (n + nToExpand * 3 > N) priority = true;
-        } else if (priority && PER == 1 && n <= NT) {
-            // ---- priority pass of a short list (:805-874), one node per thread.  The expandable nodes are ordered by
-            //      ranking (count, creation seq) keys against each other - they are distinct - instead of a sorting network;
-            //      the walk's running list size, where it stops and the children's places all come from ONE scan of the
+        } else if (priority && n <= SHORT) {
+            // ---- priority pass of a short list (:805-874).  The expandable nodes are put in walk order by ranking their
+            //      (count, creation seq) keys against each other - the keys are distinct - instead of a sorting network; the
+            //      walk's running list size, the split it stops at and the children's places all come from ONE scan of the
             //      children counts: after t + 1 splits the list has grown by (children so far) - (t + 1).
-            const int i = tid;
-            uint32_t lo = 0, hi = 0;
-            int dp = 0;
-            unsigned long long key = 0;
-            if (i < n) {
-                lo = clo[i]; hi = chi[i]; dp = cdep[i];
-                if (i < fresh && hi - lo > 1) key = ((unsigned long long)(hi - lo) << 32) | (uint32_t)(fresh - 1 - i);
+            const int nsl = (n + NT - 1) / NT;
+            int cntLocal = 0;
+            for (int sl = 0; sl < nsl; sl++) {
+                const int i = sl * NT + tid;
+                if (i < fresh) {
+                    const uint32_t cnt = chi[i] - clo[i];
+                    const unsigned long long key = cnt > 1 ? ((unsigned long long)cnt << 32) | (uint32_t)(fresh - 1 - i) : 0ull;
+                    s.skey[i] = key;
+                    cntLocal += key != 0;
+                }
             }
-            if (i < fresh) s.skey[i] = key;
-            const int ne = __syncthreads_count(key != 0);
-            int rank = -1;
-            if (key) {
-                int r = 0;
-                for (int j = 0; j < fresh; j++) r += s.skey[j] > key;
-                rank = r;
-                s.sA[r] = i;                                          // walk order -> node
+            cntLocal = __reduce_add_sync(0xffffffffu, cntLocal);
+            if ((tid & 31) == 0 && cntLocal) atomicAdd(&s.misc[2], cntLocal);
+            __syncthreads();
+            const int ne = s.misc[2];
+            for (int sl = 0; sl < nsl; sl++) {
+                const int i = sl * NT + tid;
+                if (i < n) {
+                    int rank = -1;
+                    const unsigned long long key = i < fresh ? s.skey[i] : 0ull;
+                    if (key) {
+                        int r = 0;
+                        for (int j = 0; j < fresh; j++) r += s.skey[j] > key;
+                        rank = r;
+                        s.sA[r] = i;                                  // walk order -> node
+                    }
+                    s.sC[i] = rank;                                   // node -> walk order
+                }
             }
             __syncthreads();
-            uint32_t plo = 0, phi = 0, c1 = 0, c2 = 0, c3 = 0, nc = 0;
-            int pdp = 0;
-            if (tid < ne) {
-                const int pi = s.sA[tid];
-                plo = clo[pi]; phi = chi[pi]; pdp = cdep[pi];
-                if (pdp >= depth) atomicExch(a.err, 102);
-                else { int dummy; nc = (uint32_t)split_node3(keys, plo, phi, pdp, depth, c1, c2, c3, dummy); }
-            }
-            uint32_t allNc;
-            const uint32_t exA = block_excl_reg<NT>(nc, scr, allNc);
-            if (tid < ne) {
-                s.sB[tid] = (int)(exA + nc);
-                if (n + (int)(exA + nc) - (tid + 1) >= N) atomicMin(&s.misc[1], tid);      // first split that fills the list (:867-868)
+            int* ncOf = (int*)s.skey;                                 // (the keys are not needed any more)
+            const int nslE = (ne + NT - 1) / NT;
+            uint32_t base = 0;
+            for (int sl = 0; sl < nslE; sl++) {
+                const int t = sl * NT + tid;
+                uint32_t nc = 0;
+                if (t < ne) {
+                    const int pi = s.sA[t];
+                    const int pdp = cdep[pi];
+                    if (pdp >= depth) atomicExch(a.err, 102);
+                    else {
+                        uint32_t c1, c2, c3;
+                        int dummy;
+                        nc = (uint32_t)split_node3(keys, clo[pi], chi[pi], pdp, depth, c1, c2, c3, dummy);
+                        s.b1[t] = c1; s.b2[t] = c2; s.b3[t] = c3;
+                    }
+                }
+                uint32_t tot;
+                const uint32_t ex = base + block_excl_reg<NT>(nc, scr + 32 * (sl & 1), tot);
+                base += tot;
+                if (t < ne) {
+                    s.sB[t] = (int)ex; ncOf[t] = (int)nc;
+                    if (n + (int)(ex + nc) - (t + 1) >= N) atomicMin(&s.misc[1], t);      // first split that fills the list (:867-868)
+                }
             }
             __syncthreads();
             const int tStop = (s.misc[1] == 0x7fffffff) ? ne - 1 : s.misc[1];
             const int nProc = tStop + 1;                                 // 0 when ne == 0
-            const int totalPushed = nProc > 0 ? s.sB[tStop] : 0;
-            const int newSize = n + totalPushed - nProc;
-            const bool keep = i < n && !(rank >= 0 && rank < nProc);    // split nodes leave the list
-            uint32_t kept;
-            const uint32_t exK = block_excl_reg<NT>(keep ? 1u : 0u, scr + 32, kept);
-            if (totalPushed + (int)kept > cap) { if (tid == 0) atomicExch(a.err, 103); break; }
-            if (tid < nProc && pdp < depth) emit_children(nlo, nhi, ndep, plo, c1, c2, c3, phi, pdp, (int)exA, totalPushed);
-            if (keep) { const int pos = totalPushed + (int)exK; nlo[pos] = lo; nhi[pos] = hi; ndep[pos] = (uint8_t)dp; }
+            const int totalPushed = nProc > 0 ? s.sB[tStop] + ncOf[tStop] : 0;
+            const int newSize = n + totalPushed - nProc;                 // the nProc split nodes leave the list
+            if (newSize > cap) { if (tid == 0) atomicExch(a.err, 103); break; }
+            base = 0;
+            for (int sl = 0; sl < nsl; sl++) {
+                const int i = sl * NT + tid;
+                bool keep = false;
+                if (i < n) { const int rank = s.sC[i]; keep = !(rank >= 0 && rank < nProc); }
+                uint32_t tot;
+                const uint32_t ex = base + block_excl_reg<NT>(keep ? 1u : 0u, scr + 64 + 32 * (sl & 1), tot);
+                base += tot;
+                if (keep) { const int pos = totalPushed + (int)ex; nlo[pos] = clo[i]; nhi[pos] = chi[i]; ndep[pos] = cdep[i]; }
+            }
+            for (int sl = 0; sl < nslE; sl++) {
+                const int t = sl * NT + tid;
+                if (t < nProc) {
+                    const int pi = s.sA[t];
+                    const int pdp = cdep[pi];
+                    if (pdp < depth) emit_children(nlo, nhi, ndep, clo[pi], s.b1[t], s.b2[t], s.b3[t], chi[pi], pdp, s.sB[t], totalPushed);
+                }
+            }
             __syncthreads();
             n = newSize;
             fresh = totalPushed;
@@ -461,7 +510,7 @@ __global__ void __launch_bounds__(NT) quadtree_kernel(QtArgs a) {
     // 4. retain the best key of every node, list order (:885-904): highest response, earliest candidate on ties
     if (n > a.maxSel[l]) { if (tid == 0) atomicExch(a.err, 104); n = a.maxSel[l]; }
     uint32_t* sel = a.sel + (size_t)frame * a.selTotal + a.selOff[l];
-    const uint32_t* flo = s.lo[cur]; const uint32_t* fhi = s.hi[cur];
+    const uint32_t* flo = cur ? s.lo1 : s.lo0; const uint32_t* fhi = cur ? s.hi1 : s.hi0;
     for (int i = tid; i < n; i += QT_THREADS) {
         uint32_t best = 0;
         for (uint32_t k = flo[i]; k < fhi[i]; k++) {
