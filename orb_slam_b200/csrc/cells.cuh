@@ -15,6 +15,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include "geom.h"
+#include "pdl.cuh"
 
 namespace orbx {
 
@@ -191,6 +192,8 @@ __global__ void __launch_bounds__(256, 5) cell_nms_kernel(CellArgs a) {
     const int c = cell - a.cellOff[l];
     const int i = c / a.nCols[l], j = c - i * a.nCols[l];
     const CellBox b = cell_box(a, l, i, j);
+    pdl_wait();                                          // the score planes are complete (few-frames schedule, pdl.cuh)
+    pdl_launch_dependents();
     uint32_t* cnt = a.cellCount + (size_t)frame * a.totalCells + cell;
     if (!b.valid) { if (lane == 0) *cnt = 0; return; }
     if (b.x1 - b.x0 > CELL_MAX_DIM || b.y1 - b.y0 > CELL_MAX_DIM) { if (lane == 0) { *cnt = 0; atomicExch(a.err, 302); } return; }

@@ -7,6 +7,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include "geom.h"
+#include "pdl.cuh"
 #include "../../include/orbx.h"
 
 namespace orbx {
@@ -101,6 +102,7 @@ __global__ void __launch_bounds__(256, 4) describe_kernel(DescArgs a) {
     if (threadIdx.x < 128) s_icw[(threadIdx.x & 3) * 32 + (threadIdx.x >> 2)] = ((const uint4*)g_icw)[threadIdx.x];
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     const int frame = blockIdx.y;
+    pdl_wait();                                          // the selections are complete (few-frames schedule, pdl.cuh)
     // level counts: lane k fetches count k
     const int myCnt = lane < a.nlevels ? a.selCount[frame * a.nlevels + lane] : 0;
     if (blockIdx.x == 0 && wid == 0) {

@@ -91,6 +91,7 @@ struct orbx_extractor {
     // captured once into a CUDA graph and replayed - one launch call instead of sixteen on the latency path, which is
     // what two host threads (the stereo pair, reference src/Frame.cc:94-103) otherwise serialise on in the driver
     cudaGraphExec_t oneExec = nullptr;
+    bool pdlRefused = false;                         // programmatic dependent launches could not be captured / launched on this driver
     unsigned long long allocGen = 0, oneGen = 0;     // buffer generation the graph was captured for
     int oneLaunches = 0;
     int launches = 0;
@@ -394,6 +395,44 @@ static void pyr_smem_for(int TH, const LevelGeom& prev, const LevelGeom& cur, in
 }
 
 // Enqueue the whole pipeline for `frames` frames whose level-0 source is (src, pitch, frameStride).
+// Kernel launch, optionally as a programmatic dependent of the kernel before it on the stream (pdl.cuh).
+template <typename Arg>
+static void launch_k(void (*kernel)(Arg), dim3 grid, int block, size_t smem, cudaStream_t st, bool pdl, const Arg& arg) {
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = grid; cfg.blockDim = dim3((unsigned)block); cfg.dynamicSmemBytes = smem; cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at; cfg.numAttrs = pdl ? 1 : 0;
+    cudaLaunchKernelEx(&cfg, kernel, arg);               // (errors surface in the caller's cudaGetLastError)
+}
+
+// Can this driver launch and capture programmatic dependent launches?  (Asked once per extractor; if not, the few-frames
+// schedule launches its kernels the ordinary way.)
+__global__ void pdl_probe_kernel(int* p) { pdl_wait(); pdl_launch_dependents(); if (p && threadIdx.x == 0xffff) *p = 0; }
+static bool probe_pdl(cudaStream_t st) {
+    int* none = nullptr;
+    cudaGraph_t graph = nullptr;
+    cudaGraphExec_t exec = nullptr;
+    bool ok = false;
+    if (cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal) != cudaSuccess) { cudaGetLastError(); return false; }
+    launch_k(pdl_probe_kernel, dim3(1), 32, 0, st, false, none);
+    launch_k(pdl_probe_kernel, dim3(1), 32, 0, st, true, none);
+    const cudaError_t le = cudaGetLastError();
+    const cudaError_t ce = cudaStreamEndCapture(st, &graph);
+    if (le == cudaSuccess && ce == cudaSuccess && graph && cudaGraphInstantiate(&exec, graph, 0) == cudaSuccess)
+        ok = cudaGraphLaunch(exec, st) == cudaSuccess && cudaStreamSynchronize(st) == cudaSuccess;
+    if (exec) cudaGraphExecDestroy(exec);
+    if (graph) cudaGraphDestroy(graph);
+    if (ok) {                                            // and outside a graph
+        launch_k(pdl_probe_kernel, dim3(1), 32, 0, st, false, none);
+        launch_k(pdl_probe_kernel, dim3(1), 32, 0, st, true, none);
+        ok = cudaGetLastError() == cudaSuccess && cudaStreamSynchronize(st) == cudaSuccess;
+    }
+    cudaGetLastError();
+    return ok;
+}
+
 // Enqueue the whole pipeline for `frames` frames on workspace `wi` (its stream).  `evs` (profiling) = 6 events or null.
 static int enqueue_pipeline(orbx_extractor* e, int wi, const uint8_t* src, size_t srcPitch, size_t srcFrameStride, int frames,
                             orbx_keypoint* d_kps, uint8_t* d_desc, int cap, int* d_nOut, int* d_err, cudaEvent_t* evs) {
@@ -445,15 +484,17 @@ static int enqueue_pipeline(orbx_extractor* e, int wi, const uint8_t* src, size_
         border_kernel<<<dim3((borderGroups + 7) / 8, frames), 256, 0, s_>>>(b);
         launches++;
     };
-    auto launch_nms = [&](cudaStream_t s_, int l0, int l1) {          // the cells of levels [l0, l1)
+    // `dep` (here and below): the launch directly follows, on its stream, the kernel whose output it reads, and the call is a
+    // few-frames one: launch it as that kernel's programmatic dependent
+    auto launch_nms = [&](cudaStream_t s_, int l0, int l1, bool dep) {          // the cells of levels [l0, l1)
         CellArgs cc = c;
         cc.cellBegin = c.cellOff[l0]; cc.cellEnd = c.cellOff[l1];
         if (cc.cellEnd > cc.cellBegin) {
-            cell_nms_kernel<<<dim3((cc.cellEnd - cc.cellBegin + 7) / 8, frames), 256, 0, s_>>>(cc);
+            launch_k(cell_nms_kernel, dim3((cc.cellEnd - cc.cellBegin + 7) / 8, frames), 256, 0, s_, dep, cc);
             launches++;
         }
     };
-    auto launch_qt = [&](cudaStream_t s_, int l0, int l1) {           // one block per (frame, level in [l0, l1))
+    auto launch_qt = [&](cudaStream_t s_, int l0, int l1, bool dep) {           // one block per (frame, level in [l0, l1))
         QtArgs qq = q;
         qq.levelBegin = l0;
         qq.presortMask = 0;
@@ -482,8 +523,8 @@ static int enqueue_pipeline(orbx_extractor* e, int wi, const uint8_t* src, size_
             quadtree_kernel<QT_THREADS_BATCH><<<dim3(frames, l1 - l0), QT_THREADS_BATCH, qt_smem_bytes(g.nodeCap, QT_THREADS_BATCH), s_>>>(qq);
         } else {
             qq.keyCap = QT_KEYS_SMEM;            // one block per SM at most: the sort arrays live in shared memory
-            quadtree_kernel<QT_THREADS_LATENCY><<<dim3(frames, l1 - l0), QT_THREADS_LATENCY,
-                                                  qt_smem_bytes(g.nodeCap, QT_THREADS_LATENCY) + (size_t)QT_KEYS_SMEM * 16, s_>>>(qq);
+            launch_k(quadtree_kernel<QT_THREADS_LATENCY>, dim3(frames, l1 - l0), QT_THREADS_LATENCY,
+                     qt_smem_bytes(g.nodeCap, QT_THREADS_LATENCY) + (size_t)QT_KEYS_SMEM * 16, s_, dep && !qq.presortMask, qq);
         }
         launches++;
     };
@@ -497,6 +538,10 @@ static int enqueue_pipeline(orbx_extractor* e, int wi, const uint8_t* src, size_
     // describe_kernel.  (Captured into the single-frame CUDA graph like any other cross-stream dependency.)
     static const bool noBranch = std::getenv("ORBX_NO_BRANCH") != nullptr;
     const bool branch = lowTiles && !evs && g.nlevels >= 2 && !noBranch;
+    // ... and every kernel of that chain that directly follows its producer is launched as its programmatic dependent: the
+    // next kernel's blocks are resident and past their prologue when the producer's last block retires (pdl.cuh)
+    static const bool noPdl = std::getenv("ORBX_NO_PDL") != nullptr;
+    const bool pdl = lowTiles && !evs && !noPdl && !e->pdlRefused;
     const int TH = lowTiles ? TH_LATENCY : TH_BATCH;
     for (int l = 0; l < g.nlevels; l++) {
         const LevelGeom& v = g.lv[l];
@@ -531,7 +576,7 @@ static int enqueue_pipeline(orbx_extractor* e, int wi, const uint8_t* src, size_
             }
             size_t smem;
             pyr_smem_for(TH, p, v, a.srcTileCols, a.srcTileRows, smem);
-            if (lowTiles) pyr_level_kernel<false, TH_LATENCY><<<grid, PYR_THREADS, smem, st>>>(a);
+            if (lowTiles) launch_k(pyr_level_kernel<false, TH_LATENCY>, grid, PYR_THREADS, smem, st, pdl, a);
             else if (w.tma[l] && a.haveTiles) {
                 // persistent CTAs, source boxes by bulk tensor copy, the next tile's box in flight during FAST
                 const int total = (int)(grid.x * grid.y) * frames;
@@ -543,8 +588,8 @@ static int enqueue_pipeline(orbx_extractor* e, int wi, const uint8_t* src, size_
         if (branch && l == 0) {
             CK(cudaEventRecord(w.evL0, st));
             CK(cudaStreamWaitEvent(w.sB, w.evL0, 0));
-            launch_nms(w.sB, 0, 1);
-            launch_qt(w.sB, 0, 1);
+            launch_nms(w.sB, 0, 1, false);               // (follows an event, not a kernel, on its stream)
+            launch_qt(w.sB, 0, 1, pdl);
             CK(cudaEventRecord(w.evB, w.sB));
         }
     }
@@ -555,8 +600,8 @@ static int enqueue_pipeline(orbx_extractor* e, int wi, const uint8_t* src, size_
         CK(cudaStreamWaitEvent(w.sC, w.evK1, 0));
         launch_border(w.sC);
         CK(cudaEventRecord(w.evC, w.sC));
-        launch_nms(st, 1, g.nlevels);
-        launch_qt(st, 1, g.nlevels);
+        launch_nms(st, 1, g.nlevels, pdl);
+        launch_qt(st, 1, g.nlevels, pdl);
         CK(cudaStreamWaitEvent(st, w.evB, 0));
         CK(cudaStreamWaitEvent(st, w.evC, 0));
     } else {
@@ -564,10 +609,10 @@ static int enqueue_pipeline(orbx_extractor* e, int wi, const uint8_t* src, size_
         launch_border(st);
         if (evs) CK(cudaEventRecord(evs[2], st));
         // 3. per-cell NMS + threshold fallback -> per-cell survivor lists (one launch, score plane read once)
-        launch_nms(st, 0, g.nlevels);
+        launch_nms(st, 0, g.nlevels, false);             // (follows the border kernel; its input is K1's)
         if (evs) CK(cudaEventRecord(evs[3], st));
         // 4. quadtree distribution (gathers the cell lists into vToDistributeKeys first)
-        launch_qt(st, 0, g.nlevels);
+        launch_qt(st, 0, g.nlevels, pdl);
     }
     if (evs) CK(cudaEventRecord(evs[4], st));
     // 5. orientation, descriptors, output assembly
@@ -589,7 +634,7 @@ static int enqueue_pipeline(orbx_extractor* e, int wi, const uint8_t* src, size_
     const int kpw = kpwEnv == 4 || kpwEnv == 8 ? kpwEnv : slots >= 148L * 32 * 8 ? 8 : 4;
     const dim3 dgrid((g.selTotal + 8 * kpw - 1) / (8 * kpw), frames);
     if (kpw == 8) describe_kernel<8><<<dgrid, 256, 0, st>>>(d);
-    else describe_kernel<4><<<dgrid, 256, 0, st>>>(d);
+    else launch_k(describe_kernel<4>, dgrid, 256, 0, st, pdl, d);     // (directly behind the quadtree kernel on this stream)
     launches++;
     if (evs) CK(cudaEventRecord(evs[5], st));
     e->launches += launches;
@@ -640,6 +685,7 @@ int orbx_create(orbx_t** out, int nfeatures, float scaleFactor, int nlevels, int
         for (cudaEvent_t* ev : {&w.evL0, &w.evK1, &w.evB, &w.evC})
             if (rc == cudaSuccess) rc = cudaEventCreateWithFlags(ev, cudaEventDisableTiming);
     }
+    if (rc == cudaSuccess) e->pdlRefused = !probe_pdl(e->stream);
     if (rc == cudaSuccess) rc = cudaEventCreateWithFlags(&e->evFork, cudaEventDisableTiming);
     for (int wi = 0; wi < ORBX_NWS && rc == cudaSuccess; wi++) rc = cudaEventCreateWithFlags(&e->evJoin[wi], cudaEventDisableTiming);
     if (rc == cudaSuccess) rc = cudaStreamCreateWithFlags(&e->sIn, cudaStreamNonBlocking);

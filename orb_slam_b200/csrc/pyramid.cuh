@@ -17,6 +17,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include "geom.h"
+#include "pdl.cuh"
 
 namespace orbx {
 
@@ -471,12 +472,14 @@ __global__ void __launch_bounds__(PYR_THREADS) pyr_level_kernel(PyrArgs a) {
         const int nvec = (sx_hi - sx_lo) / 16 + 1;
         const int nrows = sy_hi - sy_lo + 1;
         if (nrows > a.srcTileRows || nvec * 16 > scols) { if (tid == 0) atomicExch(a.err, 201); return; }   // block-uniform
+        tile_build_taps<TH>(a, tapx, tapy, x0, y0, sx_lo, sy_lo, tid);     // constant tables: before the wait
+        pdl_wait();                                             // level l - 1 is complete (few-frames schedule, pdl.cuh)
+        pdl_launch_dependents();
         for (int i = tid; i < nrows * nvec; i += PYR_THREADS) {
             const int r = i / nvec, c = i - r * nvec;
             const uint4 v = __ldg((const uint4*)(src + (size_t)(sy_lo + r) * a.srcPitch + a.srcX0 + sx_lo + 16 * c));
             *(uint4*)(S + r * scols + 16 * c) = v;
         }
-        tile_build_taps<TH>(a, tapx, tapy, x0, y0, sx_lo, sy_lo, tid);
         __syncthreads();
         tile_hresize(a, S, scols, nrows, tapx, Hq, x0, tid);
         __syncthreads();

@@ -1,6 +1,7 @@
 // quadtree_kernel: see quadtree.cuh for the formulation.
 #pragma once
 #include "quadtree.cuh"
+#include "pdl.cuh"
 #include "quadtree_presort.cuh"
 
 namespace orbx {
@@ -94,6 +95,8 @@ __global__ void __launch_bounds__(NT) quadtree_kernel(QtArgs a) {
         s.misc = (int*)p; p += 64;
         s.dep0 = p; p += cap; s.dep1 = p;
     }
+    pdl_wait();                                          // the cells' survivor lists are complete (few-frames schedule, pdl.cuh)
+    pdl_launch_dependents();
     int* selCount = a.selCount + frame * a.nlevels + l;
     const int depth = a.depth[l], N = a.N[l], nIni = a.nIni[l];
     const size_t off = (size_t)frame * a.candFrameStride + a.candOff[l];
