@@ -518,7 +518,12 @@ static int enqueue_pipeline(orbx_extractor* e, int wi, const uint8_t* src, size_
             } else cudaGetLastError();           // (cluster launch refused: the single-CTA path does the whole level)
         }
         // many frames: small blocks (throughput); a handful of frames: the level-0 block is the critical path, give it more threads
-        if (frames * g.nlevels >= 2 * 148) {
+        // ORBX_QT_GENERAL=1 (tests): the general passes and the radix sort for every list, whatever its length
+        static const bool qtGeneral = std::getenv("ORBX_QT_GENERAL") != nullptr;
+        const bool batchBlocks = frames * g.nlevels >= 2 * 148;
+        qq.shortMax = qtGeneral ? 0 : (batchBlocks ? QtBucket<QT_THREADS_BATCH>::SHORT : QtBucket<QT_THREADS_LATENCY>::SHORT);
+        qq.bucketMax = qtGeneral ? 0 : QtBucket<QT_THREADS_BATCH>::MAXB;
+        if (batchBlocks) {
             qq.keyCap = 0;
             quadtree_kernel<QT_THREADS_BATCH><<<dim3(frames, l1 - l0), QT_THREADS_BATCH, qt_smem_bytes(g.nodeCap, QT_THREADS_BATCH), s_>>>(qq);
         } else {

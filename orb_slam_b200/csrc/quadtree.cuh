@@ -50,6 +50,8 @@ struct QtArgs {
     int levelBegin;                  // blockIdx.y = 0 is this level (a launch may cover a level range)
     unsigned presortMask;            // bit l: steps 0-2 of level l were done by qt_presort_kernel (quadtree_presort.cuh)
     int keyCap;                      // keys per sort array that fit in the dynamic shared memory behind the node arrays (0 = none)
+    int shortMax;                    // lists up to this long take the register-scan passes (0: always the general passes)
+    int bucketMax;                   // largest bucket the bucket + rank sort accepts (0: always the radix sort)
     unsigned long long candOff[ORB_MAX_LEVELS];
     int N[ORB_MAX_LEVELS], nIni[ORB_MAX_LEVELS], qH[ORB_MAX_LEVELS], depth[ORB_MAX_LEVELS];
     int maxSel[ORB_MAX_LEVELS], selOff[ORB_MAX_LEVELS];
@@ -198,17 +200,18 @@ __device__ int block_radix_sort(uint32_t* kA, uint32_t* vA, uint32_t* kB, uint32
 template <int NT> struct QtBucket {
     static constexpr int LOG = NT >= 512 ? 11 : 9;       // NB + 1 counters must fit in the 256 x warps words of the radix histogram
     static constexpr int NB = 1 << LOG;
-    static constexpr int MAXB = 64;                      // larger bucket anywhere -> radix sort
+    static constexpr int MAXB = 64;                      // larger bucket anywhere -> radix sort (QtArgs::bucketMax)
+    static constexpr int SHORT = 8 * NT;                 // QtArgs::shortMax
 };
 
 // bc[b] = number of keys of bucket b = key >> sh (counted by the caller while it produced kA / vA), bc[NB] unused.
-// Returns false (nothing moved) when some bucket exceeds MAXB; otherwise the sorted pairs are back in kA / vA.
+// Returns false (nothing moved) when some bucket exceeds maxBucket; otherwise the sorted pairs are back in kA / vA.
 template <int NT>
-__device__ bool block_bucket_sort(uint32_t* kA, uint32_t* vA, uint32_t* kB, uint32_t* vB, int M, int sh, int* bc, int* warpTmp) {
+__device__ bool block_bucket_sort(uint32_t* kA, uint32_t* vA, uint32_t* kB, uint32_t* vB, int M, int sh, int* bc, int* warpTmp, int maxBucket) {
     constexpr int NB = QtBucket<NT>::NB;
     const int tid = threadIdx.x;
     int big = 0;
-    for (int i = tid; i < NB; i += NT) big |= bc[i] > QtBucket<NT>::MAXB;
+    for (int i = tid; i < NB; i += NT) big |= bc[i] > maxBucket;
     if (__syncthreads_or(big)) return false;
     block_scan_excl<NT>(bc, NB, warpTmp);                // bc[b] = first position of bucket b
     for (int i = tid; i < M; i += NT) {

@@ -202,7 +202,7 @@ __global__ void __launch_bounds__(NT) quadtree_kernel(QtArgs a) {
         QT_MARK(2);
         // 2. sort by code: buckets + ranks, or the radix sort when a bucket is large
         which = 0;
-        if (!block_bucket_sort<NT>(kA, vA, kB, vB, M, sh, bc, s.warpTmp))
+        if (!block_bucket_sort<NT>(kA, vA, kB, vB, M, sh, bc, s.warpTmp, a.bucketMax))
             which = block_radix_sort<NT>(kA, vA, kB, vB, M, bits, s.hist, s.warpTmp);
     }
     QT_MARK(3);
@@ -230,7 +230,7 @@ __global__ void __launch_bounds__(NT) quadtree_kernel(QtArgs a) {
     bool finish = false;
     int fresh = 0;            // number of nodes created by the last pass (front of the list)
     bool priority = false;
-    constexpr int SHORT = 4 * NT;                        // lists up to this long take the passes with register scans (one barrier per NT nodes)
+    const int SHORT = a.shortMax;                        // lists up to this long take the passes with register scans (one barrier per NT nodes)
     uint32_t* scr = s.hist;                              // block-scan scratch of those passes (the sort is done with it)
     int passNo = 0;
     QT_MARK(4);

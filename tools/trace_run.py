@@ -3,7 +3,7 @@ sys.path.insert(0, '/root/repo')
 from orb_slam_b200 import ORBextractor
 from orb_slam_b200._lib import check
 from orb_slam_b200.synth import synth_frame
-W,H,B=1241,376,512
+W,H,B=1241,376,1024
 fr=np.stack([synth_frame(W,H,i) for i in range(8)])
 host=torch.empty((B,H,W),dtype=torch.uint8,pin_memory=True); host.numpy()[:]=np.concatenate([fr]*(B//8))
 ex=ORBextractor(2000,1.2,8,20,7); L=ex._L; h=ex.handle; cap=ex.max_keypoints(W,H)
