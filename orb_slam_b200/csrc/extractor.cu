@@ -66,6 +66,8 @@ struct orbx_extractor {
         uint32_t *d_keyA = nullptr, *d_keyB = nullptr, *d_valA = nullptr, *d_valB = nullptr, *d_sel = nullptr;
         int *d_candCount = nullptr, *d_selCount = nullptr;
         int* d_qtTotals = nullptr;               // digit totals exchanged by the clusters of qt_presort_kernel
+        int* d_qtBuckets = nullptr;              // ... and their bucket counts / fill counters, [frames][presortLevels][2][QTP_NB]
+        int* d_qtWhich = nullptr;                // [frames][nlevels] where qt_presort_kernel left the sorted pairs
         int lastFrames = 0;
         // TMA descriptors of the bordered planes of levels 0..n-2 (the sources of levels 1..n-1), see pyramid_tma.cuh
         CUtensorMap srcMap[ORB_MAX_LEVELS];
@@ -263,6 +265,7 @@ static void free_workspace(orbx_extractor* e) {
         cudaFree(w.d_cellCount); cudaFree(w.d_cellOffs); cudaFree(w.d_cand); cudaFree(w.d_slots);
         cudaFree(w.d_keyA); cudaFree(w.d_keyB); cudaFree(w.d_valA); cudaFree(w.d_valB); cudaFree(w.d_sel);
         cudaFree(w.d_candCount); cudaFree(w.d_selCount); cudaFree(w.d_qtTotals); w.d_qtTotals = nullptr;
+        cudaFree(w.d_qtBuckets); w.d_qtBuckets = nullptr; cudaFree(w.d_qtWhich); w.d_qtWhich = nullptr;
         w.d_pyr = w.d_blur = w.d_score = nullptr;
         w.d_cellCount = w.d_cellOffs = w.d_cand = w.d_slots = w.d_keyA = w.d_keyB = w.d_valA = w.d_valB = w.d_sel = nullptr;
         w.d_candCount = w.d_selCount = nullptr; w.lastFrames = 0;
@@ -364,7 +367,11 @@ static int ensure_workspace(orbx_extractor* e, int width, int height, int frames
         CK(cudaMalloc(&w.d_sel, (size_t)g.selTotal * F * 4));
         CK(cudaMalloc(&w.d_candCount, F * g.nlevels * 4));
         CK(cudaMalloc(&w.d_selCount, F * g.nlevels * 4));
-        if (g.presortLevels > 0) CK(cudaMalloc(&w.d_qtTotals, F * g.presortLevels * QTP_CTAS * 256 * sizeof(int)));
+        if (g.presortLevels > 0) {
+            CK(cudaMalloc(&w.d_qtTotals, F * g.presortLevels * QTP_CTAS * 256 * sizeof(int)));
+            CK(cudaMalloc(&w.d_qtBuckets, F * g.presortLevels * 2 * QTP_NB * sizeof(int)));
+            CK(cudaMalloc(&w.d_qtWhich, F * g.nlevels * sizeof(int)));
+        }
         build_tensor_maps(e, w, newCap);
     }
     e->resBytes = res_bytes(g, newCap);
@@ -495,9 +502,12 @@ static int enqueue_pipeline(orbx_extractor* e, int wi, const uint8_t* src, size_
         }
     };
     auto launch_qt = [&](cudaStream_t s_, int l0, int l1, bool dep) {           // one block per (frame, level in [l0, l1))
+        // ORBX_QT_GENERAL=1 (tests): the general passes and the radix sort for every list, whatever its length
+        static const bool qtGeneral = std::getenv("ORBX_QT_GENERAL") != nullptr;
         QtArgs qq = q;
         qq.levelBegin = l0;
         qq.presortMask = 0;
+        qq.preWhich = w.d_qtWhich;
         const int pre1 = std::min(l1, g.presortLevels);
         // Large levels, and few enough (frame, level) pairs that one CTA each leaves most of the GPU idle: gather + path codes +
         // radix sort on a cluster of eight CTAs per pair.  Measured: 16 x 3840x2160 (8 frames per stream): quadtree stage 2.19 ->
@@ -505,6 +515,9 @@ static int enqueue_pipeline(orbx_extractor* e, int wi, const uint8_t* src, size_
         if (pre1 > l0 && w.d_qtTotals && frames * g.nlevels <= e->numSMs) {
             QtPresortArgs pa{};
             pa.q = q; pa.q.levelBegin = l0; pa.levelBegin = l0; pa.totals = w.d_qtTotals; pa.maxCells = g.presortMaxCells;
+            pa.q.bucketMax = qtGeneral ? 0 : QtBucket<QTP_THREADS>::MAXB;
+            pa.buckets = w.d_qtBuckets; pa.which = w.d_qtWhich;
+            cudaMemsetAsync(w.d_qtBuckets + (size_t)l0 * frames * 2 * QTP_NB, 0, (size_t)frames * (pre1 - l0) * 2 * QTP_NB * sizeof(int), s_);
             cudaLaunchConfig_t cfg{};
             cfg.gridDim = dim3(QTP_CTAS * frames, pre1 - l0); cfg.blockDim = dim3(QTP_THREADS);
             cfg.dynamicSmemBytes = qtp_smem_bytes(g.presortMaxCells); cfg.stream = s_;
@@ -518,8 +531,6 @@ static int enqueue_pipeline(orbx_extractor* e, int wi, const uint8_t* src, size_
             } else cudaGetLastError();           // (cluster launch refused: the single-CTA path does the whole level)
         }
         // many frames: small blocks (throughput); a handful of frames: the level-0 block is the critical path, give it more threads
-        // ORBX_QT_GENERAL=1 (tests): the general passes and the radix sort for every list, whatever its length
-        static const bool qtGeneral = std::getenv("ORBX_QT_GENERAL") != nullptr;
         const bool batchBlocks = frames * g.nlevels >= 2 * 148;
         qq.shortMax = qtGeneral ? 0 : (batchBlocks ? QtBucket<QT_THREADS_BATCH>::SHORT : QtBucket<QT_THREADS_LATENCY>::SHORT);
         qq.bucketMax = qtGeneral ? 0 : QtBucket<QT_THREADS_BATCH>::MAXB;

@@ -49,6 +49,7 @@ struct QtArgs {
     int nlevels, selTotal, nodeCap;
     int levelBegin;                  // blockIdx.y = 0 is this level (a launch may cover a level range)
     unsigned presortMask;            // bit l: steps 0-2 of level l were done by qt_presort_kernel (quadtree_presort.cuh)
+    const int* preWhich;             // [frames][nlevels] left by qt_presort_kernel: bit 0 = buffer with the sorted pairs, bit 1 = check for duplicates
     int keyCap;                      // keys per sort array that fit in the dynamic shared memory behind the node arrays (0 = none)
     int shortMax;                    // lists up to this long take the register-scan passes (0: always the general passes)
     int bucketMax;                   // largest bucket the bucket + rank sort accepts (0: always the radix sort)

@@ -110,11 +110,14 @@ __global__ void __launch_bounds__(NT) quadtree_kernel(QtArgs a) {
     //    running totals), so the copy is balanced however the survivors are spread over the cells.
     const bool pre = (a.presortMask >> l) & 1u;           // large level: gathered, coded and sorted by qt_presort_kernel
     int M, which;
+    bool checkDup = true;
     if (pre) {
         M = a.candCount[frame * a.nlevels + l];
         QT_MARK(1);
         if (M <= 0) { if (tid == 0) *selCount = 0; return; }
-        which = qtp_passes(depth, nIni) & 1;
+        const int pw = a.preWhich[frame * a.nlevels + l];
+        which = pw & 1;
+        checkDup = (pw & 2) != 0;                         // (the bucket + rank sort has looked at every key's neighbours already)
     } else {
         const int nc = a.cellOff[l + 1] - a.cellOff[l];
         const uint32_t* cnt = a.cellCount + (size_t)frame * a.totalCells + a.cellOff[l];
@@ -209,8 +212,9 @@ __global__ void __launch_bounds__(NT) quadtree_kernel(QtArgs a) {
     const uint32_t* keys = which ? kB : kA;
     const uint32_t* vals = which ? vB : vA;
     // distinct pixels must have distinct codes (depth was sized for it on the host)
-    for (int i = tid + 1; i < M; i += QT_THREADS)
-        if (keys[i] == keys[i - 1]) atomicExch(a.err, 101);
+    if (checkDup)
+        for (int i = tid + 1; i < M; i += QT_THREADS)
+            if (keys[i] == keys[i - 1]) atomicExch(a.err, 101);
 
     // 3. initial nodes in push_back order, empty ones erased (:663-699)
     // (boundaries of the nIni ranges by nIni + 1 threads, then thread 0 compacts the non-empty ones in order)

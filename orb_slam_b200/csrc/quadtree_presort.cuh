@@ -22,16 +22,29 @@ namespace orbx {
 constexpr int QTP_CTAS = 8;                    // cluster size (portable maximum)
 constexpr int QTP_THREADS = 512;
 constexpr int QTP_WARPS = QTP_THREADS / 32;
+constexpr int QTP_LOG = 14;                    // buckets of the bucket + rank sort (quadtree.cuh) per (frame, level): counters in global memory
+constexpr int QTP_NB = 1 << QTP_LOG;
 
 struct QtPresortArgs {
     QtArgs q;
     int levelBegin;                            // blockIdx.y = 0 is this level
-    int* totals;                               // [frames][levels of the launch][QTP_CTAS][256] digit totals of a pass
+    int* totals;                               // [level][frame][QTP_CTAS][256] digit totals of a radix pass
     int maxCells;                              // cells of the largest level of the launch (sizes the scan array)
+    int* buckets;                              // [level][frame][2][QTP_NB], the launch's levels zeroed before it: bucket counts, fill counters
+    int* which;                                // [frames][nlevels] out: bit 0 = buffer holding the sorted pairs, bit 1 = duplicates not checked yet
 };
 
+// the exclusive scan array serves the cell counts first and the bucket counts afterwards
+__host__ __device__ inline int qtp_scan_words(int maxCells) { const int c = (maxCells + 31) & ~31; return c > QTP_NB + 32 ? c : QTP_NB + 32; }
 __host__ __device__ inline size_t qtp_smem_bytes(int maxCells) {
-    return (size_t)((maxCells + 31) & ~31) * 4 + (size_t)256 * QTP_WARPS * 4 + 256 * 4 * 2 + QTP_WARPS * 4 + 64;
+    return (size_t)qtp_scan_words(maxCells) * 4 + (size_t)256 * QTP_WARPS * 4 + 256 * 4 * 2 + QTP_WARPS * 4 + 64;
+}
+
+// number of 8-bit passes the sort of a level takes (-> which ping-pong buffer holds the result)
+__host__ __device__ inline int qtp_passes(int depth, int nIni) {
+    int iniBits = 0;
+    while ((1 << iniBits) < nIni) iniBits++;
+    return (2 * depth + iniBits + 7) / 8;
 }
 
 __global__ void __launch_bounds__(QTP_THREADS) qt_presort_kernel(QtPresortArgs pa) {
@@ -39,8 +52,8 @@ __global__ void __launch_bounds__(QTP_THREADS) qt_presort_kernel(QtPresortArgs p
     cg::cluster_group cluster = cg::this_cluster();
     const QtArgs& a = pa.q;
     extern __shared__ __align__(16) uint8_t psm[];
-    int* offs = (int*)psm;                                            // exclusive scan of the level's cell counts
-    uint32_t* hist = (uint32_t*)(offs + ((pa.maxCells + 31) & ~31));  // [256][QTP_WARPS]
+    int* offs = (int*)psm;                                            // exclusive scan of the level's cell counts, then of the bucket counts
+    uint32_t* hist = (uint32_t*)(offs + qtp_scan_words(pa.maxCells)); // [256][QTP_WARPS]
     int* gbase = (int*)(hist + 256 * QTP_WARPS);                      // [256] global base of a digit for this CTA
     int* dsum = gbase + 256;                                          // [256] scratch of the digit scan
     int* warpTmp = dsum + 256;
@@ -52,7 +65,16 @@ __global__ void __launch_bounds__(QTP_THREADS) qt_presort_kernel(QtPresortArgs p
     uint32_t* cand = a.cand + off;
     uint32_t* kA = a.keyA + off; uint32_t* kB = a.keyB + off;
     uint32_t* vA = a.valA + off; uint32_t* vB = a.valB + off;
-    int* totals = pa.totals + ((size_t)(frame * gridDim.y + blockIdx.y) * QTP_CTAS) * 256;
+    // scratch of this (level, frame) pair: indexed by the level itself, so that two launches of one call (the few-frames schedule
+    // runs level 0 on a side stream beside the other levels) never share a slot
+    const size_t pairIdx = (size_t)l * (gridDim.x / QTP_CTAS) + frame;
+    int* totals = pa.totals + pairIdx * QTP_CTAS * 256;
+    int* gcnt = pa.buckets + pairIdx * 2 * QTP_NB;
+    int* gfill = gcnt + QTP_NB;
+    int iniBits = 0;
+    while ((1 << iniBits) < nIni) iniBits++;
+    const int bits = 2 * depth + iniBits;
+    const int sh = max(0, bits - QTP_LOG);
 
     // ---- 0. gather: the cells' survivor lists in cell row-major order (:952-1002)
     const int nc = a.cellOff[l + 1] - a.cellOff[l];
@@ -94,26 +116,63 @@ __global__ void __launch_bounds__(QTP_THREADS) qt_presort_kernel(QtPresortArgs p
                 }
                 j = min(j, 31);
                 const int startj = __shfl_sync(0xffffffffu, incl - nmine, j);
-                if (t < T) cand[base + t] = slots[(size_t)(ch * 32 + j) * scap + (t - startj)];
+                if (t < T) {
+                    // ---- 1. path code (sort key), (response, candidate index) sort value and the bucket count, in the same sweep
+                    const uint32_t cw = slots[(size_t)(ch * 32 + j) * scap + (t - startj)];
+                    const int i = base + t;
+                    cand[i] = cw;
+                    const uint32_t code = path_code((int)(cw & 0xfff), (int)((cw >> 12) & 0xfff), a.hX[l], nIni, a.qH[l], depth);
+                    kA[i] = code;
+                    vA[i] = (cw & 0xff000000u) | (uint32_t)i;
+                    atomicAdd(&gcnt[code >> sh], 1);
+                }
             }
         }
     }
     __threadfence();
-    cluster.sync();                                      // vToDistributeKeys complete
+    cluster.sync();                                      // vToDistributeKeys, codes and bucket counts complete
 
-    // ---- 1. path codes of this CTA's eighth of the candidates
     const int i0 = (int)((long long)M * rank / QTP_CTAS), i1 = (int)((long long)M * (rank + 1) / QTP_CTAS);
-    for (int i = i0 + tid; i < i1; i += QTP_THREADS) {
-        const uint32_t c = cand[i];
-        kA[i] = path_code((int)(c & 0xfff), (int)((c >> 12) & 0xfff), a.hX[l], nIni, a.qH[l], depth);
-        vA[i] = (c & 0xff000000u) | (uint32_t)i;
+    // ---- 2a. bucket + rank sort (quadtree.cuh): every CTA scans the bucket counts (cheap, redundant), places its eighth of the
+    //      keys behind a global fill counter per bucket, and after a cluster barrier ranks its eighth of the placed keys inside
+    //      their buckets.  One scattered write per key instead of the radix sort's three: the scattered writes of all the
+    //      clusters are what the L2 limits here.
+    int* bst = offs;
+    int big = 0;
+    for (int i = tid; i < QTP_NB; i += QTP_THREADS) { const int v = __ldcg(&gcnt[i]); bst[i] = v; big |= v > a.bucketMax; }
+    if (!__syncthreads_or(big)) {
+        block_scan_excl<QTP_THREADS>(bst, QTP_NB, warpTmp);
+        if (tid == 0) bst[QTP_NB] = M;
+        __syncthreads();
+        for (int i = i0 + tid; i < i1; i += QTP_THREADS) {
+            const uint32_t k = __ldcg(&kA[i]);
+            const int b = (int)(k >> sh);
+            const int p = bst[b] + atomicAdd(&gfill[b], 1);
+            kB[p] = k; vB[p] = __ldcg(&vA[i]);
+        }
+        __threadfence();
+        cluster.sync();                                  // every key sits in its bucket
+        bool dup = false;
+        for (int p = i0 + tid; p < i1; p += QTP_THREADS) {
+            const uint32_t k = __ldcg(&kB[p]);
+            const int b = (int)(k >> sh);
+            const int s0 = bst[b], e0 = bst[b + 1];
+            int r = 0;
+            for (int j = s0; j < e0; j++) {
+                const uint32_t kj = __ldcg(&kB[j]);
+                r += (kj < k) || (kj == k && j < p);
+                dup |= kj == k && j != p;
+            }
+            kA[s0 + r] = k; vA[s0 + r] = __ldcg(&vB[p]);
+        }
+        if (dup) atomicExch(a.err, 101);                 // distinct pixels must have distinct codes
+        if (tid == 0 && rank == 0) pa.which[frame * a.nlevels + l] = 0;
+        return;
     }
-    __syncthreads();
+    if (tid == 0 && rank == 0) pa.which[frame * a.nlevels + l] = (qtp_passes(depth, nIni) & 1) | 2;
 
-    // ---- 2. stable LSD radix sort, the CTA's keys being the index range [i0, i1) of the current input buffer
-    int iniBits = 0;
-    while ((1 << iniBits) < nIni) iniBits++;
-    const int bits = 2 * depth + iniBits;
+    // ---- 2b. a crowded bucket somewhere: stable LSD radix sort, the CTA's keys being the index range [i0, i1) of the current
+    //      input buffer
     const int per = ((((i1 - i0) + QTP_WARPS - 1) / QTP_WARPS) + 31) & ~31;
     const int wb = min(i0 + wid * per, i1), we = min(wb + per, i1);
     int which = 0;
@@ -194,11 +253,5 @@ __global__ void __launch_bounds__(QTP_THREADS) qt_presort_kernel(QtPresortArgs p
     }
 }
 
-// number of 8-bit passes the sort of a level takes (-> which ping-pong buffer holds the result)
-__host__ __device__ inline int qtp_passes(int depth, int nIni) {
-    int iniBits = 0;
-    while ((1 << iniBits) < nIni) iniBits++;
-    return (2 * depth + iniBits + 7) / 8;
-}
 
 }  // namespace orbx

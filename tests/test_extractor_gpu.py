@@ -142,7 +142,8 @@ def test_quadtree_general_passes_and_radix_sort():
     """quadtree_kernel keeps two forms of its list passes and of its sort: the register-scan passes and the bucket + rank sort
     (taken for the list lengths and bucket sizes of ordinary frames) and the general passes with the radix sort (long lists,
     crowded buckets).  ORBX_QT_GENERAL=1 (read once per process) sends every list through the general form: the same parity
-    tests again in a child process, single-frame blocks (512 threads) and batch blocks (128 threads)."""
+    tests again in a child process: single-frame blocks (512 threads), batch blocks (128 threads) and the cluster pre-sort of
+    large levels (qt_presort_kernel, the 4K frame)."""
     import os
     import subprocess
     import sys
@@ -150,7 +151,8 @@ def test_quadtree_general_passes_and_radix_sort():
     env = dict(os.environ, ORBX_QT_GENERAL="1")
     r = subprocess.run([sys.executable, "-m", "pytest", "tests/test_extractor_gpu.py", "tests/test_configs_gpu.py", "-q", "-x", "-m", "gpu",
                         "-p", "no:cacheprovider", "-k",
-                        "test_extract_matches_oracle or test_batch_tiles_match_oracle or test_batch_across_chunks or test_other_extractor_settings"],
+                        "test_extract_matches_oracle or test_batch_tiles_match_oracle or test_batch_across_chunks or test_other_extractor_settings "
+                        "or test_4k_stress_frame"],
                        cwd=root, env=env, capture_output=True, text=True, timeout=1500)
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-2000:]
     assert " passed" in r.stdout and "failed" not in r.stdout
