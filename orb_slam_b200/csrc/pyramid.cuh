@@ -112,9 +112,7 @@ __device__ __forceinline__ uint32_t fast_score_pair(const uint32_t (&P)[16], uin
 // twelve reads are 64-bit: 30 shared-memory wavefronts per warp and row instead of 48 - the kernel's L1 data pipe is as busy
 // as its ALU pipe (64 % against 70 %, profiles/r2n_ncu_full_b512.md), and two thirds of its shared-memory reads are these.
 // Result: four bytes (pixel order) of max(0, score + 1 - minTh) - the score plane's encoding.
-__device__ __forceinline__ uint32_t fast_score4(const uint4* __restrict__ PA, const uint4* __restrict__ PB, int r, int g, int minTh) {
-    const uint4* a = PA + r * 32 + g;
-    const uint4* b = PB + r * 32 + g;
+__device__ __forceinline__ uint32_t fast_score4(const uint4* __restrict__ a, const uint4* __restrict__ b, int minTh) {   // a, b: PA / PB at [r][g]
     const uint4 a0 = a[0], a6 = a[6 * 32];                       // dy = -3, +3: x1 x2 em om
     const uint2 a1 = *(const uint2*)(a + 32), a5 = *(const uint2*)(a + 5 * 32);      // dy = -2, +2: x1 x2 ...
     const uint2 b1 = *(const uint2*)(b + 32), b5 = *(const uint2*)(b + 5 * 32);      //              ... x4 x3
@@ -209,22 +207,26 @@ __device__ __forceinline__ void tile_fast_pass(const PyrArgs& a, const uint4* __
     constexpr int RPW = TH / (PYR_THREADS / 32);
     const int w = a.w, h = a.h;
     const int gx = x0 + 4 * lane;                        // level column of the group's first pixel
-#pragma unroll 1
-    for (int k = 0; k < RPW; k++) {
-        const int r = RPW * wid + k, y = y0 + r;
-        if (y >= h || gx >= w) continue;
-        uint32_t s = 0;
-        if (y >= ORB_EDGE && y < h - ORB_EDGE && gx + 3 >= ORB_EDGE && gx < w - ORB_EDGE) {
-            s = fast_score4(PA, PB, r, lane, a.minTh);
-            if (gx < ORB_EDGE || gx + 3 >= w - ORB_EDGE) {           // group straddles the detection area
-                uint32_t m = 0;
+    if (gx >= w) return;                                 // (no barrier inside this pass)
+    // everything that does not change from row to row is formed once: the plane pointers and the store pointer advance by a
+    // row per step, the column part of the detection-area test and the mask of a group that straddles the area's edge are fixed
+    const int r0 = RPW * wid;
+    const uint4* pa = PA + r0 * 32 + lane;
+    const uint4* pb = PB + r0 * 32 + lane;
+    uint8_t* sp = a.score + (size_t)frame * a.planeFrameStride + (size_t)(y0 + r0) * a.pitch + ORB_XPAD + gx;
+    const bool colIn = gx + 3 >= ORB_EDGE && gx < w - ORB_EDGE;
+    uint32_t colMask = 0;
 #pragma unroll
-                for (int j = 0; j < 4; j++)
-                    if (gx + j >= ORB_EDGE && gx + j < w - ORB_EDGE) m |= 0xffu << (8 * j);
-                s &= m;
-            }
-        }
-        *(uint32_t*)(a.score + (size_t)frame * a.planeFrameStride + (size_t)y * a.pitch + ORB_XPAD + gx) = s;
+    for (int j = 0; j < 4; j++)
+        if (gx + j >= ORB_EDGE && gx + j < w - ORB_EDGE) colMask |= 0xffu << (8 * j);
+    const int rows = min(RPW, h - (y0 + r0));            // tile rows of this warp inside the image
+    const int yLo = ORB_EDGE - (y0 + r0), yHi = h - ORB_EDGE - (y0 + r0);    // k in [yLo, yHi) is inside the detection area
+#pragma unroll 1
+    for (int k = 0; k < rows; k++) {
+        uint32_t s = 0;
+        if (colIn && k >= yLo && k < yHi) s = fast_score4(pa, pb, a.minTh) & colMask;
+        *(uint32_t*)sp = s;
+        sp += a.pitch; pa += 32; pb += 32;
     }
 }
 
