@@ -128,7 +128,8 @@ def test_edge_cases():
     # empty image: outputs untouched
     assert gpu(np.zeros((0, 0), np.uint8)) == (None, None)
     # other thresholds / scale factors
-    for nf, sf, nl, ini, mn in [(1500, 1.5, 5, 30, 10), (800, 1.1, 10, 12, 5)]:
+    # (one and two levels: the few-frames schedule without / with its level-0 fork)
+    for nf, sf, nl, ini, mn in [(1500, 1.5, 5, 30, 10), (800, 1.1, 10, 12, 5), (500, 1.2, 1, 20, 7), (600, 1.3, 2, 20, 7)]:
         g2 = ORBextractor(nf, sf, nl, ini, mn)
         c2 = OracleExtractor(nf, sf, nl, ini, mn)
         img = synth_frame(640, 480, 20)
