@@ -53,6 +53,7 @@ struct orbx_extractor {
     bool haveGeom = false;
     int capFrames = 0;                       // frames EACH workspace is sized for
     ResizeTap* d_tabs = nullptr;
+    uint32_t* d_qcode = nullptr;                     // path-code tables of the quadtree stage (quadtree.cuh), all levels
     std::vector<ResizeTap> h_tabs;                   // host copy: per-tile source extents go into the kernel arguments
     uint8_t* d_in[ORBX_NBUF] = {}; size_t inBytes = 0;   // H2D targets, one per buffer set (host layout kept: linear copies)
     // Complete kernel workspaces, each with its own compute stream: neighbouring chunks (host path, all four) or the two
@@ -260,6 +261,7 @@ static int build_geometry(orbx_extractor* e, int width, int height, FrameGeom& g
 // ---------------------------------------------------------------------------
 static void free_workspace(orbx_extractor* e) {
     cudaFree(e->d_tabs); e->d_tabs = nullptr;
+    cudaFree(e->d_qcode); e->d_qcode = nullptr;
     for (auto& w : e->ws) {
         cudaFree(w.d_pyr); cudaFree(w.d_blur); cudaFree(w.d_score);
         cudaFree(w.d_cellCount); cudaFree(w.d_cellOffs); cudaFree(w.d_cand); cudaFree(w.d_slots);
@@ -350,6 +352,20 @@ static int ensure_workspace(orbx_extractor* e, int width, int height, int frames
     CK(cudaMalloc(&e->d_tabs, std::max<size_t>(tabs.size(), 1) * sizeof(ResizeTap)));
     if (!tabs.empty()) CK(cudaMemcpy(e->d_tabs, tabs.data(), tabs.size() * sizeof(ResizeTap), cudaMemcpyHostToDevice));
     e->h_tabs = tabs;
+    {
+        // path codes of the quadtree stage by column and by row (a candidate's coordinates are 12-bit fields: 4096 entries each)
+        std::vector<uint32_t> qc;
+        for (int l = 0; l < e->g.nlevels; l++) {
+            LevelGeom& v = e->g.lv[l];
+            v.codeXOff = (int)qc.size(); v.codeYOff = v.codeXOff + 4096;
+            qc.resize(qc.size() + 8192, 0u);
+            if (v.nCols > 0)
+                path_code_tables(v.hX, v.nIni, v.qH, v.depth, std::min(4096, std::max(v.qW, 0) + 1), std::min(4096, std::max(v.qH, 0) + 1),
+                                 qc.data() + v.codeXOff, qc.data() + v.codeYOff);
+        }
+        CK(cudaMalloc(&e->d_qcode, std::max<size_t>(qc.size(), 1) * sizeof(uint32_t)));
+        if (!qc.empty()) CK(cudaMemcpy(e->d_qcode, qc.data(), qc.size() * sizeof(uint32_t), cudaMemcpyHostToDevice));
+    }
     const size_t cells = (size_t)std::max(g.totalCells, 1) * F;
     const size_t cands = (size_t)std::max<unsigned long long>(g.candTotal, 64) * F;
     for (int wi = 0; wi < (needInput || hadInput ? ORBX_NWS : 2); wi++) {
@@ -480,11 +496,13 @@ static int enqueue_pipeline(orbx_extractor* e, int wi, const uint8_t* src, size_
     q.keyA = w.d_keyA; q.keyB = w.d_keyB; q.valA = w.d_valA; q.valB = w.d_valB;
     q.sel = w.d_sel; q.selCount = w.d_selCount; q.err = d_err;
     q.nlevels = g.nlevels; q.selTotal = g.selTotal; q.nodeCap = g.nodeCap;
+    q.codeTab = e->d_qcode;
     for (int l = 0; l < g.nlevels; l++) {
         const LevelGeom& v = g.lv[l];
         q.candOff[l] = v.candOff; q.N[l] = v.N; q.nIni[l] = v.nIni; q.qH[l] = v.qH; q.depth[l] = v.depth;
         q.maxSel[l] = v.maxSel; q.selOff[l] = v.selOff; q.hX[l] = v.hX;
         q.cellOff[l] = v.cellOff; q.slotOff[l] = v.slotOff; q.slotCap[l] = v.slotCap; q.candCap[l] = v.candCap;
+        q.codeXOff[l] = v.codeXOff; q.codeYOff[l] = v.codeYOff;
     }
     q.cellOff[g.nlevels] = g.totalCells;
     auto launch_border = [&](cudaStream_t s_) {

@@ -38,6 +38,7 @@ struct LevelGeom {
     int qW, qH;              // maxX-minX, maxY-minY
     int depth;               // number of 2-bit digits in a path code
     int iniBits;             // bits for the initial node index
+    int codeXOff, codeYOff;  // this level's column / row parts of the path codes inside the code table (quadtree.cuh)
     int maxSel;              // upper bound on retained keypoints: max(N+3, 4*nIni)
     int selOff;              // slot offset inside one frame's selection array
     // output

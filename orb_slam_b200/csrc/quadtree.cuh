@@ -54,6 +54,10 @@ struct QtArgs {
     int shortMax;                    // lists up to this long take the register-scan passes (0: always the general passes)
     int bucketMax;                   // largest bucket the bucket + rank sort accepts (0: always the radix sort)
     unsigned long long candOff[ORB_MAX_LEVELS];
+    // path codes by table: the column comparisons of DivideNode depend on x alone and the row comparisons on y alone, so a
+    // candidate's code is codeTab[codeXOff[l] + x] | codeTab[codeYOff[l] + y] (tables built once per frame size, path_code_tables)
+    const uint32_t* codeTab;
+    int codeXOff[ORB_MAX_LEVELS], codeYOff[ORB_MAX_LEVELS];
     int N[ORB_MAX_LEVELS], nIni[ORB_MAX_LEVELS], qH[ORB_MAX_LEVELS], depth[ORB_MAX_LEVELS];
     int maxSel[ORB_MAX_LEVELS], selOff[ORB_MAX_LEVELS];
     float hX[ORB_MAX_LEVELS];
@@ -109,11 +113,18 @@ __device__ __forceinline__ uint32_t key_lower_bound(const uint32_t* keys, uint32
     return lo;
 }
 
-// path code of one candidate: replays DivideNode's box arithmetic from the initial node down
-__device__ __forceinline__ uint32_t path_code(int x, int y, float hX, int nIni, int qH, int depth) {
+// path code of one candidate: replays DivideNode's box arithmetic from the initial node down.  (Reference form of the code; the
+// kernels read it from the tables below, which are this function evaluated per column and per row.)
+__host__ __device__ __forceinline__ uint32_t path_code(int x, int y, float hX, int nIni, int qH, int depth) {
+#ifdef __CUDA_ARCH__
     int ini = (int)__fdiv_rn((float)x, hX);                    // vpIniNodes[kp.pt.x/hX], :682
     ini = min(ini, nIni - 1);
     int ulx = (int)__fmul_rn(hX, (float)ini), urx = (int)__fmul_rn(hX, (float)(ini + 1));   // :667-668
+#else
+    int ini = (int)((float)x / hX);                            // (host: IEEE float ops, the library is built with -ffp-contract=off)
+    ini = ini < nIni - 1 ? ini : nIni - 1;
+    int ulx = (int)(hX * (float)ini), urx = (int)(hX * (float)(ini + 1));
+#endif
     int uly = 0, bry = qH;
     uint32_t code = (uint32_t)ini;
     for (int t = 0; t < depth; t++) {
@@ -125,6 +136,18 @@ __device__ __forceinline__ uint32_t path_code(int x, int y, float hX, int nIni, 
         code = (code << 2) | q;
     }
     return code;
+}
+
+// The column digits (bit 0 of every 2-bit digit) and the initial node index depend on x alone, the row digits (bit 1) on y
+// alone: path_code(x, y) = path_code(x, 0) & XMASK | path_code(0, y) & YMASK.  Host: fills xs[0..nx) and ys[0..ny).
+inline void path_code_tables(float hX, int nIni, int qH, int depth, int nx, int ny, uint32_t* xs, uint32_t* ys) {
+    uint32_t ymask = 0;
+    for (int t = 0; t < depth; t++) ymask |= 2u << (2 * t);
+    for (int x = 0; x < nx; x++) xs[x] = path_code(x, 0, hX, nIni, qH, depth) & ~ymask;
+    for (int y = 0; y < ny; y++) ys[y] = path_code(0, y, hX, nIni, qH, depth) & ymask;
+}
+__device__ __forceinline__ uint32_t path_code_lookup(const QtArgs& a, int l, uint32_t cw) {
+    return __ldg(&a.codeTab[a.codeXOff[l] + (int)(cw & 0xfff)]) | __ldg(&a.codeTab[a.codeYOff[l] + (int)((cw >> 12) & 0xfff)]);
 }
 
 // stable LSD radix sort of (key,val) pairs by `bits` low bits of key; returns 0 if the result is in A, 1 if in B

@@ -154,8 +154,6 @@ __global__ void __launch_bounds__(NT) quadtree_kernel(QtArgs a) {
         // 0 + 1. candidate list, path codes (sort keys) and the (response, candidate index) sort values in one sweep
         const uint32_t* slots = a.slots + (size_t)frame * a.slotFrameStride + a.slotOff[l];
         const int scap = a.slotCap[l];
-        const float hX = a.hX[l];
-        const int qH = a.qH[l];
         for (int ch = wid; ch < nchunks; ch += QT_WARPS) {
             int base = 0;
             for (int k = 0; k < ch; k++) base += chunkSum[k];
@@ -192,7 +190,7 @@ __global__ void __launch_bounds__(NT) quadtree_kernel(QtArgs a) {
                     if (t < T) {
                         const int i = base + t;
                         cand[i] = cw[u];
-                        const uint32_t code = path_code((int)(cw[u] & 0xfff), (int)((cw[u] >> 12) & 0xfff), hX, nIni, qH, depth);
+                        const uint32_t code = path_code_lookup(a, l, cw[u]);
                         kA[i] = code;
                         vA[i] = (cw[u] & 0xff000000u) | (uint32_t)i;
                         atomicAdd(&bc[code >> sh], 1);

@@ -121,7 +121,7 @@ __global__ void __launch_bounds__(QTP_THREADS) qt_presort_kernel(QtPresortArgs p
                     const uint32_t cw = slots[(size_t)(ch * 32 + j) * scap + (t - startj)];
                     const int i = base + t;
                     cand[i] = cw;
-                    const uint32_t code = path_code((int)(cw & 0xfff), (int)((cw >> 12) & 0xfff), a.hX[l], nIni, a.qH[l], depth);
+                    const uint32_t code = path_code_lookup(a, l, cw);
                     kA[i] = code;
                     vA[i] = (cw & 0xff000000u) | (uint32_t)i;
                     atomicAdd(&gcnt[code >> sh], 1);
