@@ -6,9 +6,12 @@
 // the (deterministic) ceil-halving of the initial boxes.  So every candidate
 // gets a PATH CODE - initial node index followed by one 2-bit child digit per
 // subdivision depth (n1=0 UL, n2=1 UR, n3=2 BL, n4=3 BR, decided by the very
-// comparisons of :603-617) - the candidates are radix-sorted by that code once,
-// and from then on every node of the tree is a contiguous range of the sorted
-// array: splitting a node is three binary searches, no data moves.  The list
+// comparisons of :603-617; by table: the column digits depend on x alone, the row
+// digits on y alone) - the candidates are sorted by that code once (the codes of
+// distinct pixels are distinct: buckets of the top bits, then ranks inside a bucket;
+// a stable radix sort for inputs with a crowded bucket), and from then on every
+// node of the tree is a contiguous range of the sorted array: splitting a node is
+// three binary searches, no data moves.  The list
 // itself (front-to-back order, push_front of children, erase of parents, the
 // breadth passes and the "largest node first" passes with their early exit) is
 // replayed exactly on ranges, with block-wide scans replacing the sequential

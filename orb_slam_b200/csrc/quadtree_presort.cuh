@@ -1,16 +1,19 @@
-// Steps 0-2 of the quadtree stage (gather vToDistributeKeys, path codes, stable radix sort by path code; see
-// quadtree_kernel.cuh) for LARGE levels, spread over a thread-block cluster of eight CTAs per (frame, level).
+// Steps 0-2 of the quadtree stage (gather vToDistributeKeys, path codes, sort by path code; see quadtree_kernel.cuh) for
+// LARGE levels, spread over a thread-block cluster of eight CTAs per (frame, level).
 //
 // quadtree_kernel runs one CTA per (frame, level); at 1080p / 4K the level-0 block holds 20 000 - 90 000 candidates and the
 // single-CTA radix sort of their path codes in global memory is 55 - 80 % of the stage (phase clocks: 1.7 of 2.2 ms at 4K).
 // The order-dependent part - replaying DistributeOctTree's list on the sorted ranges - stays with that one CTA; what it
 // consumes is order-independent and is produced here:
-//   0. every CTA scans the level's cell counts (cheap, redundant) and copies its eighth of the cells' survivor lists;
-//   1. path codes of its eighth of the candidates;
-//   2. LSD radix sort, 8 bits per pass: per-warp digit histograms of the CTA's contiguous key range, the eight CTAs' digit
-//      totals exchanged through a small global scratch between two cluster barriers, then the stable scatter.  Key i of the
-//      input lies in CTA floor(8i/M), warp by contiguous sub-range, so "digit, then CTA, then warp, then position" is the
-//      input order: the sort is stable exactly like the single-CTA one.
+//   0. every CTA scans the level's cell counts (cheap, redundant) and copies its eighth of the cells' survivor lists,
+//   1. giving every candidate its path code and counting it into one of 16 384 buckets (global counters) on the way;
+//   2a. bucket + rank sort (the codes are distinct): after a cluster barrier every CTA scans the bucket counts, places its
+//      eighth of the keys behind a global fill counter per bucket and, after a second barrier, ranks its eighth of the placed
+//      keys inside their buckets - one scattered write per key;
+//   2b. inputs with a crowded bucket: LSD radix sort, 8 bits per pass: per-warp digit histograms of the CTA's contiguous key
+//      range, the eight CTAs' digit totals exchanged through a small global scratch between two cluster barriers, then the
+//      stable scatter.  Key i of the input lies in CTA floor(8i/M), warp by contiguous sub-range, so "digit, then CTA, then
+//      warp, then position" is the input order: the sort is stable exactly like the single-CTA one.
 // The cluster barrier (barrier.cluster, release/acquire) is the only inter-CTA synchronisation; the CTAs of a cluster are
 // co-scheduled by the hardware, so the waits cannot deadlock.
 #pragma once
