@@ -94,6 +94,7 @@ struct orbx_extractor {
     // captured once into a CUDA graph and replayed - one launch call instead of sixteen on the latency path, which is
     // what two host threads (the stereo pair, reference src/Frame.cc:94-103) otherwise serialise on in the driver
     cudaGraphExec_t oneExec = nullptr;
+    bool graphRefused = false;                       // the single-frame graph could not be captured / instantiated on this driver
     bool pdlRefused = false;                         // programmatic dependent launches could not be captured / launched on this driver
     unsigned long long allocGen = 0, oneGen = 0;     // buffer generation the graph was captured for
     int oneLaunches = 0;
@@ -939,7 +940,7 @@ int orbx_extract_batch(orbx_t* e, const uint8_t* const* images, int n, int width
     }
     static const bool trace = std::getenv("ORBX_TRACE") != nullptr;
     static const bool noGraph = std::getenv("ORBX_NO_GRAPH") != nullptr;
-    if (n == 1 && !inPinned && !outPinned && !e->profile && !trace && !noGraph) {
+    if (n == 1 && !inPinned && !outPinned && !e->profile && !trace && !noGraph && !e->graphRefused) {
         cudaStream_t cst = e->ws[0].stream;
         uint8_t* stage = e->h_in[0];                     // (every call ends synchronised: the staging buffers are free)
         if (step == (size_t)width) std::memcpy(stage, images[0], (size_t)width * height);
@@ -965,9 +966,14 @@ int orbx_extract_batch(orbx_t* e, const uint8_t* const* images, int n, int width
             if (rc == ORBX_OK && ee != cudaSuccess) rc = (int)ee;
             if (rc == ORBX_OK) rc = (int)cudaGraphInstantiate(&e->oneExec, graph, 0);
             if (graph) cudaGraphDestroy(graph);
-            if (rc != ORBX_OK) { e->oneExec = nullptr; cudaGetLastError(); return rc; }
-            e->oneGen = e->allocGen; e->oneLaunches = e->launches;
+            if (rc != ORBX_OK) {                         // capture / instantiation refused: ordinary stream launches from now on
+                e->oneExec = nullptr; e->graphRefused = true; cudaGetLastError();
+                std::fprintf(stderr, "orbx: CUDA graph of the single-frame chain refused (%d): stream launches instead\n", rc);
+            } else { e->oneGen = e->allocGen; e->oneLaunches = e->launches; }
         }
+    }
+    if (n == 1 && !inPinned && !outPinned && !e->profile && !trace && !noGraph && !e->graphRefused) {
+        cudaStream_t cst = e->ws[0].stream;
         e->launches = e->oneLaunches; e->ws[0].lastFrames = 1; e->lastWs = 0;
         CK(cudaGraphLaunch(e->oneExec, cst));
         CK(cudaStreamSynchronize(cst));
