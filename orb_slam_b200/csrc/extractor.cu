@@ -403,8 +403,8 @@ static int ensure_workspace(orbx_extractor* e, int width, int height, int frames
     CK(cudaFuncSetAttribute(quadtree_kernel<QT_THREADS_LATENCY>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(qt_smem_bytes(g.nodeCap, QT_THREADS_LATENCY) + (size_t)QT_KEYS_SMEM * 16)));
     CK(cudaFuncSetAttribute(pyr_level_kernel<false, TH_BATCH>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
     CK(cudaFuncSetAttribute(pyr_level_kernel<true, TH_BATCH>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
-    CK(cudaFuncSetAttribute(pyr_level_kernel<false, TH_LATENCY>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
-    CK(cudaFuncSetAttribute(pyr_level_kernel<true, TH_LATENCY>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
+    CK(cudaFuncSetAttribute(pyr_level_kernel<false, TH_LATENCY, PYR_THREADS_LATENCY>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
+    CK(cudaFuncSetAttribute(pyr_level_kernel<true, TH_LATENCY, PYR_THREADS_LATENCY>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
     CK(cudaFuncSetAttribute(pyr_level_tma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pyrt_smem_bytes()));
     if (g.presortLevels > 0)
         CK(cudaFuncSetAttribute(qt_presort_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)qtp_smem_bytes(g.presortMaxCells)));
@@ -589,7 +589,7 @@ static int enqueue_pipeline(orbx_extractor* e, int wi, const uint8_t* src, size_
             a.src = src; a.srcFrameStride = srcFrameStride; a.srcPitch = (int)srcPitch; a.srcX0 = 0;
             a.sw = v.w; a.sh = v.h;
             const size_t smem = pyr_smem_bytes(TH, true, 0, 0);
-            if (lowTiles) pyr_level_kernel<true, TH_LATENCY><<<grid, PYR_THREADS, smem, st>>>(a);
+            if (lowTiles) pyr_level_kernel<true, TH_LATENCY, PYR_THREADS_LATENCY><<<grid, PYR_THREADS_LATENCY, smem, st>>>(a);
             else pyr_level_kernel<true, TH_BATCH><<<grid, PYR_THREADS, smem, st>>>(a);
         } else {
             const LevelGeom& p = g.lv[l - 1];
@@ -611,7 +611,7 @@ static int enqueue_pipeline(orbx_extractor* e, int wi, const uint8_t* src, size_
             }
             size_t smem;
             pyr_smem_for(TH, p, v, a.srcTileCols, a.srcTileRows, smem);
-            if (lowTiles) launch_k(pyr_level_kernel<false, TH_LATENCY>, grid, PYR_THREADS, smem, st, pdl, a);
+            if (lowTiles) launch_k(pyr_level_kernel<false, TH_LATENCY, PYR_THREADS_LATENCY>, grid, PYR_THREADS_LATENCY, smem, st, pdl, a);
             else if (w.tma[l] && a.haveTiles) {
                 // persistent CTAs, source boxes by bulk tensor copy, the next tile's box in flight during FAST
                 const int total = (int)(grid.x * grid.y) * frames;

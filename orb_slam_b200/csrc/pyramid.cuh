@@ -31,6 +31,7 @@ constexpr int TS = 144;          // shared-memory row stride of the level tile (
 constexpr int TBYTES = 136;      // T bytes written per row: byte b <-> level column x0 - 4 + b
 constexpr int HQS = 136;         // u16 stride of the horizontally resized staging rows
 constexpr int PYR_THREADS = 256;
+constexpr int PYR_THREADS_LATENCY = 512;     // calls of a frame or two (see pyr_level_kernel)
 
 __device__ __forceinline__ int reflect101(int p, int len) {
     // gfedcb|abcdefgh|gfedcba ; callers guarantee -len < p < 2*len-1
@@ -185,12 +186,12 @@ __device__ __forceinline__ void tile_store_plane(const PyrArgs& a, const uint8_t
 
 // row pass: one warp per T row, one 4-pixel group per lane: split the row into its stride-2 pixel pairs
 // (kept in the pair planes for FAST) and form the horizontal blur sums
-template <int TH>
+template <int TH, int NT = PYR_THREADS>
 __device__ __forceinline__ void tile_row_pass(const uint8_t* __restrict__ T, unsigned short* __restrict__ Hs, uint4* __restrict__ PA,
                                               uint4* __restrict__ PB, int h, int y0, int wid, int lane) {
     constexpr int TROWS = TH + 2 * HALO;
     const int rEnd = min(TROWS, h + 2 * HALO - y0);       // rows below the image + halo feed nothing that is stored
-    for (int r = wid; r < rEnd; r += PYR_THREADS / 32) {
+    for (int r = wid; r < rEnd; r += NT / 32) {
         const RowPairs p = row_pairs((const uint32_t*)(T + r * TS) + lane);
         PA[r * 32 + lane] = make_uint4(p.x1, p.x2, p.em, p.om);
         PB[r * 32 + lane] = make_uint4(p.x4, p.x3, p.ol, p.er);
@@ -201,10 +202,10 @@ __device__ __forceinline__ void tile_row_pass(const uint8_t* __restrict__ T, uns
 }
 
 // FAST score: warp `wid` owns tile rows RPW*wid..RPW*wid+RPW-1, lane = 4-pixel group
-template <int TH>
+template <int TH, int NT = PYR_THREADS>
 __device__ __forceinline__ void tile_fast_pass(const PyrArgs& a, const uint4* __restrict__ PA, const uint4* __restrict__ PB, int frame,
                                                int x0, int y0, int wid, int lane) {
-    constexpr int RPW = TH / (PYR_THREADS / 32);
+    constexpr int RPW = TH / (NT / 32);
     const int w = a.w, h = a.h;
     const int gx = x0 + 4 * lane;                        // level column of the group's first pixel
     if (gx >= w) return;                                 // (no barrier inside this pass)
@@ -233,10 +234,10 @@ __device__ __forceinline__ void tile_fast_pass(const PyrArgs& a, const uint4* __
 // vertical blur pass: warp `wid` owns tile rows RPW*wid..RPW*wid+RPW-1.  The RPW + 6 row sums a lane needs per pixel are
 // paired vertically, P[j] = (H[j], H[j+1]) as u16x2, so that one DP2A applies two taps:
 // out[k] = (18,34).P[k] + (48,56).P[k+2] + (48,34).P[k+4] + (0,18).P[k+5]
-template <int TH>
+template <int TH, int NT = PYR_THREADS>
 __device__ __forceinline__ void tile_vblur_pass(const PyrArgs& a, const unsigned short* __restrict__ Hs, int frame, int x0, int y0,
                                                 int wid, int lane) {
-    constexpr int RPW = TH / (PYR_THREADS / 32);
+    constexpr int RPW = TH / (NT / 32);
     const int w = a.w, h = a.h;
     const int gx = x0 + 4 * lane;
     const unsigned short* col = Hs + 4 * lane;
@@ -301,10 +302,12 @@ __device__ __forceinline__ void tile_build_taps(const PyrArgs& a, TapX* __restri
 // A group's four tap pairs lie within 8 consecutive source bytes (scale < 2): fetch that window as three
 // aligned words + two funnel shifts, pick each (S[o], S[o+1]) pair with a per-thread constant PRMT selector
 // and weight it with one DP2A.
+template <int NT = PYR_THREADS>
 __device__ __forceinline__ void tile_hresize(const PyrArgs& a, const uint8_t* __restrict__ S, int scols, int nrows,
                                              const TapX* __restrict__ tapx, unsigned short* __restrict__ Hq, int x0, int tid) {
+    constexpr int SLOTS = NT / (TBYTES / 4);             // row slots: 7 at 256 threads, 15 at 512
     const int q = tid % (TBYTES / 4), slot = tid / (TBYTES / 4);
-    const bool live = slot < 7 && x0 - 4 + 4 * q < a.w + HALO;     // groups right of the image + halo are never read
+    const bool live = slot < SLOTS && x0 - 4 + 4 * q < a.w + HALO;     // groups right of the image + halo are never read
     if (!live) return;
     int o[4];
     uint32_t wt[4];
@@ -327,7 +330,7 @@ __device__ __forceinline__ void tile_hresize(const PyrArgs& a, const uint8_t* __
     if (bad) atomicExch(a.err, 202);
     const int wb = base >> 2;
     const unsigned sh = 8u * (unsigned)(base & 3);
-    for (int r = slot; r < nrows; r += 7) {
+    for (int r = slot; r < nrows; r += SLOTS) {
         const uint32_t* Sw = (const uint32_t*)(S + r * scols) + wb;
         const uint32_t w0 = Sw[0], w1 = Sw[1], w2 = Sw[2];
         const uint32_t X0 = __funnelshift_r(w0, w1, sh), X1 = __funnelshift_r(w1, w2, sh);
@@ -339,15 +342,16 @@ __device__ __forceinline__ void tile_hresize(const PyrArgs& a, const uint8_t* __
 }
 
 // vertical pass (VResizeLinear 8u): ((b0*H0)>>16) + ((b1*H1)>>16) + 2 >> 2; (b*lo16(u))>>16 == umulhi(u<<16, b)
-template <int TH>
+template <int TH, int NT = PYR_THREADS>
 __device__ __forceinline__ void tile_vresize(const PyrArgs& a, const TapX* __restrict__ tapy, const unsigned short* __restrict__ Hq,
                                              uint8_t* __restrict__ T, int x0, int y0, int tid) {
     constexpr int TROWS = TH + 2 * HALO;
+    constexpr int SLOTS = NT / (TBYTES / 4);
     const int q = tid % (TBYTES / 4), slot = tid / (TBYTES / 4);
-    const bool live = slot < 7 && x0 - 4 + 4 * q < a.w + HALO;
+    const bool live = slot < SLOTS && x0 - 4 + 4 * q < a.w + HALO;
     if (!live) return;
     const int tyEnd = min(TROWS, a.h + 2 * HALO - y0);             // T rows below the image + halo are never read
-    for (int ty = slot; ty < tyEnd; ty += 7) {
+    for (int ty = slot; ty < tyEnd; ty += SLOTS) {
         const uint2 tp = *(const uint2*)(tapy + ty);
         const uint32_t b0 = tp.y & 0xffffu, b1 = tp.y >> 16;     // weights are in [0, 2048]
         const uint2 u0 = *(const uint2*)(Hq + (tp.x & 0xffffu) * HQS + 4 * q);
@@ -377,10 +381,14 @@ __host__ __device__ inline size_t pyr_smem_bytes(int th, bool level0, int srcRow
     return pyr_smem_T(trows) + (early > late ? early : late);
 }
 
-template <bool LEVEL0, int TH>
-__global__ void __launch_bounds__(PYR_THREADS) pyr_level_kernel(PyrArgs a) {
+// NT threads per CTA: 256 in batches; calls of a frame or two run the same phases with 512 (one tile row per warp in the FAST and
+// blur passes, 15 row slots in the resize passes): the eight dependent launches are the call's latency, and a CTA's serial chain
+// through its phases is most of a launch
+template <bool LEVEL0, int TH, int NT = PYR_THREADS>
+__global__ void __launch_bounds__(NT) pyr_level_kernel(PyrArgs a) {
     constexpr int TROWS = TH + 2 * HALO;
-    constexpr int RPW = TH / (PYR_THREADS / 32);          // tile rows per warp in the FAST and vertical-blur passes
+    constexpr int NW = NT / 32;
+    static_assert(TH % NW == 0 && NT >= 192 + TROWS, "tile rows per warp / tap-table threads");
     extern __shared__ __align__(16) uint8_t smem[];
     uint8_t* T = smem;                                   // TROWS x TS level tile with halo
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
@@ -411,10 +419,11 @@ __global__ void __launch_bounds__(PYR_THREADS) pyr_level_kernel(PyrArgs a) {
             const int half = lane >> 4, c = lane & 15;
             const int xb = x0 - 4 + 8 * c;
             const bool inner = xb >= 4 && xb + 11 < w;       // the three aligned words stay inside the row
-            uint2 v[3];
+            constexpr int NJ = (TROWS + 2 * NW - 1) / (2 * NW);      // two rows per warp and step
+            uint2 v[NJ];
 #pragma unroll
-            for (int j = 0; j < 3; j++) {
-                const int ty = 2 * (wid + 8 * j) + half;
+            for (int j = 0; j < NJ; j++) {
+                const int ty = 2 * (wid + NW * j) + half;
                 const int y = y0 - HALO + ty;
                 v[j] = make_uint2(0u, 0u);
                 if (ty < TROWS && y < h + HALO) {
@@ -431,8 +440,8 @@ __global__ void __launch_bounds__(PYR_THREADS) pyr_level_kernel(PyrArgs a) {
                 }
             }
 #pragma unroll
-            for (int j = 0; j < 3; j++) {
-                const int ty = 2 * (wid + 8 * j) + half;
+            for (int j = 0; j < NJ; j++) {
+                const int ty = 2 * (wid + NW * j) + half;
                 if (ty < TROWS) *(uint2*)(T + ty * TS + 8 * c) = v[j];
             }
         }
@@ -477,24 +486,24 @@ __global__ void __launch_bounds__(PYR_THREADS) pyr_level_kernel(PyrArgs a) {
         tile_build_taps<TH>(a, tapx, tapy, x0, y0, sx_lo, sy_lo, tid);     // constant tables: before the wait
         pdl_wait();                                             // level l - 1 is complete (few-frames schedule, pdl.cuh)
         pdl_launch_dependents();
-        for (int i = tid; i < nrows * nvec; i += PYR_THREADS) {
+        for (int i = tid; i < nrows * nvec; i += NT) {
             const int r = i / nvec, c = i - r * nvec;
             const uint4 v = __ldg((const uint4*)(src + (size_t)(sy_lo + r) * a.srcPitch + a.srcX0 + sx_lo + 16 * c));
             *(uint4*)(S + r * scols + 16 * c) = v;
         }
         __syncthreads();
-        tile_hresize(a, S, scols, nrows, tapx, Hq, x0, tid);
+        tile_hresize<NT>(a, S, scols, nrows, tapx, Hq, x0, tid);
         __syncthreads();
-        tile_vresize<TH>(a, tapy, Hq, T, x0, y0, tid);
+        tile_vresize<TH, NT>(a, tapy, Hq, T, x0, y0, tid);
     }
     __syncthreads();
 
     tile_store_plane<TH>(a, T, frame, x0, y0, tid);
     uint4* PB = PA + TROWS * 32;
-    tile_row_pass<TH>(T, Hs, PA, PB, h, y0, wid, lane);
+    tile_row_pass<TH, NT>(T, Hs, PA, PB, h, y0, wid, lane);
     __syncthreads();      // planes and Hs complete
-    tile_fast_pass<TH>(a, PA, PB, frame, x0, y0, wid, lane);
-    tile_vblur_pass<TH>(a, Hs, frame, x0, y0, wid, lane);
+    tile_fast_pass<TH, NT>(a, PA, PB, frame, x0, y0, wid, lane);
+    tile_vblur_pass<TH, NT>(a, Hs, frame, x0, y0, wid, lane);
 }
 
 // BORDER_REFLECT_101 frame of 19 pixels around every level (copyMakeBorder,
