@@ -662,13 +662,14 @@ static int enqueue_pipeline(orbx_extractor* e, int wi, const uint8_t* src, size_
     }
     d.selOff[g.nlevels] = g.selTotal;
     // slots per warp: 8 in a batch (the per-keypoint scalar chain - atan2, sin/cos - runs once per 8 keypoints), 4 when the call
-    // holds a handful of frames (there the warp's serial chain is the latency).  32 per warp measured no better than 8
+    // holds a handful of frames, 2 for a frame or two (there the warp's serial chain is the latency: 14.6 -> 11.4 us per frame).  32 per warp measured no better than 8
     // (describe 2.12 vs 2.09 ms per 1024 KITTI frames; 2.29 before the per-lane trig) and costs the few-frames case.
     static const int kpwEnv = [] { const char* v = std::getenv("ORBX_DESC_KPW"); return v ? std::atoi(v) : 0; }();
     const long slots = (long)frames * g.selTotal;
-    const int kpw = kpwEnv == 4 || kpwEnv == 8 ? kpwEnv : slots >= 148L * 32 * 8 ? 8 : 4;
+    const int kpw = kpwEnv == 2 || kpwEnv == 4 || kpwEnv == 8 ? kpwEnv : slots >= 148L * 32 * 8 ? 8 : lowTiles ? 2 : 4;
     const dim3 dgrid((g.selTotal + 8 * kpw - 1) / (8 * kpw), frames);
     if (kpw == 8) describe_kernel<8><<<dgrid, 256, 0, st>>>(d);
+    else if (kpw == 2) launch_k(describe_kernel<2>, dgrid, 256, 0, st, pdl, d);     // a frame or two: the warp's serial chain is the latency
     else launch_k(describe_kernel<4>, dgrid, 256, 0, st, pdl, d);     // (directly behind the quadtree kernel on this stream)
     launches++;
     if (evs) CK(cudaEventRecord(evs[5], st));
